@@ -1,0 +1,144 @@
+// Shared host/device plumbing for the sm_100a kernels: context, error capture, Arrow bitmap access.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+
+#include "arrow1_b200.h"
+
+struct b200_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  int num_sms = 148;
+  int64_t launches = 0;
+  std::string error;
+  // small device scratch owned by the context (flags, counters); grown on demand
+  void* scratch = nullptr;
+  size_t scratch_bytes = 0;
+  // pinned host word block for scalar read-backs
+  int64_t* host_words = nullptr;
+};
+
+int b200_fail(b200_ctx* ctx, int code, const char* fmt, ...);
+int b200_ctx_reserve_scratch(b200_ctx* ctx, size_t bytes);
+
+#define B200_CUDA(ctx, expr)                                                              \
+  do {                                                                                    \
+    cudaError_t _e = (expr);                                                              \
+    if (_e != cudaSuccess)                                                                \
+      return b200_fail((ctx), _e == cudaErrorMemoryAllocation ? B200_OUT_OF_MEMORY        \
+                                                              : B200_UNKNOWN_ERROR,       \
+                       "CUDA error %s at %s:%d: %s", cudaGetErrorName(_e), __FILE__,      \
+                       __LINE__, cudaGetErrorString(_e));                                 \
+  } while (0)
+
+#define B200_RETURN_NOT_OK(expr) \
+  do {                           \
+    int _s = (expr);             \
+    if (_s != B200_OK) return _s; \
+  } while (0)
+
+// launch bookkeeping + error check after every kernel launch
+#define B200_LAUNCHED(ctx)                     \
+  do {                                         \
+    (ctx)->launches++;                         \
+    B200_CUDA((ctx), cudaGetLastError());      \
+  } while (0)
+
+static inline int b200_type_bits(int t) {
+  switch (t) {
+    case B200_BOOL: return 1;
+    case B200_UINT8: case B200_INT8: return 8;
+    case B200_UINT16: case B200_INT16: return 16;
+    case B200_UINT32: case B200_INT32: case B200_FLOAT: return 32;
+    case B200_UINT64: case B200_INT64: case B200_DOUBLE: return 64;
+    default: return 0;
+  }
+}
+
+static inline size_t b200_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// ------------------------------------------------------------------------------------------
+// Arrow bitmaps on the device.  A (pointer, bit offset) pair is normalised to an 8-byte aligned
+// word pointer plus a bit offset; reading the aligned words that cover the wanted bits never
+// leaves the allocation (CUDA allocations are >= 256-byte aligned and sized).
+struct BitmapRef {
+  const uint64_t* words;  // 8-byte aligned; nullptr = "all ones"
+  int64_t bit_offset;     // >= 0
+};
+
+static inline BitmapRef make_bitmap_ref(const void* p, int64_t offset_bits) {
+  BitmapRef r;
+  if (p == nullptr) {
+    r.words = nullptr;
+    r.bit_offset = 0;
+    return r;
+  }
+  uintptr_t a = reinterpret_cast<uintptr_t>(p);
+  r.words = reinterpret_cast<const uint64_t*>(a & ~uintptr_t(7));
+  r.bit_offset = offset_bits + int64_t(a & 7) * 8;
+  return r;
+}
+
+#ifdef __CUDACC__
+// 64 bits of the bitmap starting at logical bit `pos` (LSB = bit pos).  Bits at or beyond
+// `length` are returned as 0.  A null bitmap reads as all ones (inside the length).
+__device__ __forceinline__ uint64_t bitmap_load64(const BitmapRef& b, int64_t pos, int64_t length) {
+  if (pos >= length) return 0;
+  uint64_t w;
+  if (b.words == nullptr) {
+    w = ~uint64_t(0);
+  } else {
+    int64_t bit = b.bit_offset + pos;
+    int64_t wi = bit >> 6;
+    int sh = int(bit & 63);
+    uint64_t lo = __ldg(b.words + wi);
+    w = lo >> sh;
+    int64_t last_bit = b.bit_offset + (length - 1);
+    if (sh != 0 && (wi + 1) <= (last_bit >> 6)) {
+      uint64_t hi = __ldg(b.words + wi + 1);
+      w |= hi << (64 - sh);
+    }
+  }
+  int64_t remain = length - pos;
+  if (remain < 64) w &= (uint64_t(1) << remain) - 1;
+  return w;
+}
+
+__device__ __forceinline__ uint32_t bitmap_load32(const BitmapRef& b, int64_t pos, int64_t length) {
+  if (pos >= length) return 0;
+  uint32_t w;
+  if (b.words == nullptr) {
+    w = ~uint32_t(0);
+  } else {
+    int64_t bit = b.bit_offset + pos;
+    const uint32_t* w32 = reinterpret_cast<const uint32_t*>(b.words);
+    int64_t wi = bit >> 5;
+    int sh = int(bit & 31);
+    uint32_t lo = __ldg(w32 + wi);
+    uint32_t hi = 0;
+    int64_t last_bit = b.bit_offset + (length - 1);
+    if (sh != 0 && (wi + 1) <= (last_bit >> 5)) hi = __ldg(w32 + wi + 1);
+    w = __funnelshift_r(lo, hi, sh);
+  }
+  int64_t remain = length - pos;
+  if (remain < 32) w &= (uint32_t(1) << remain) - 1;
+  return w;
+}
+
+__device__ __forceinline__ bool bitmap_get(const BitmapRef& b, int64_t pos) {
+  if (b.words == nullptr) return true;
+  int64_t bit = b.bit_offset + pos;
+  const uint8_t* bytes = reinterpret_cast<const uint8_t*>(b.words);
+  return (__ldg(bytes + (bit >> 3)) >> (bit & 7)) & 1;
+}
+
+__device__ __forceinline__ unsigned lanemask_lt() {
+  unsigned m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+#endif

@@ -1,0 +1,95 @@
+// Context: one device + one stream, error message storage, small scratch (SURVEY §8b "Threading").
+#include <stdarg.h>
+
+#include "common.cuh"
+
+int b200_fail(b200_ctx* ctx, int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (ctx) ctx->error = buf;
+  return code;
+}
+
+int b200_ctx_reserve_scratch(b200_ctx* ctx, size_t bytes) {
+  if (bytes <= ctx->scratch_bytes) return B200_OK;
+  if (ctx->scratch) {
+    B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    B200_CUDA(ctx, cudaFree(ctx->scratch));
+    ctx->scratch = nullptr;
+    ctx->scratch_bytes = 0;
+  }
+  bytes = b200_align_up(bytes, 1 << 20);
+  B200_CUDA(ctx, cudaMalloc(&ctx->scratch, bytes));
+  ctx->scratch_bytes = bytes;
+  return B200_OK;
+}
+
+extern "C" {
+
+const char* b200_version(void) { return "arrow1_b200 0.1 (sm_100a)"; }
+
+int b200_ctx_create(int device, void* cu_stream, b200_ctx** out) {
+  if (!out) return B200_INVALID;
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    // no CPU fallback: fail loudly
+    fprintf(stderr, "arrow1_b200: no CUDA device available (%s)\n",
+            e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    return B200_UNKNOWN_ERROR;
+  }
+  if (device < 0 || device >= n) return B200_INVALID;
+  b200_ctx* ctx = new b200_ctx();
+  ctx->device = device;
+  ctx->stream = reinterpret_cast<cudaStream_t>(cu_stream);
+  if (cudaSetDevice(device) != cudaSuccess) {
+    delete ctx;
+    return B200_UNKNOWN_ERROR;
+  }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) ctx->num_sms = prop.multiProcessorCount;
+  if (prop.major < 10) {
+    fprintf(stderr, "arrow1_b200: device %d is sm_%d%d; this library is built for sm_100a only\n",
+            device, prop.major, prop.minor);
+    delete ctx;
+    return B200_NOT_IMPLEMENTED;
+  }
+  if (cudaMallocHost(reinterpret_cast<void**>(&ctx->host_words), 64 * sizeof(int64_t)) != cudaSuccess) {
+    delete ctx;
+    return B200_OUT_OF_MEMORY;
+  }
+  *out = ctx;
+  return B200_OK;
+}
+
+int b200_ctx_destroy(b200_ctx* ctx) {
+  if (!ctx) return B200_OK;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  if (ctx->scratch) cudaFree(ctx->scratch);
+  if (ctx->host_words) cudaFreeHost(ctx->host_words);
+  delete ctx;
+  return B200_OK;
+}
+
+int b200_ctx_set_stream(b200_ctx* ctx, void* cu_stream) {
+  if (!ctx) return B200_INVALID;
+  ctx->stream = reinterpret_cast<cudaStream_t>(cu_stream);
+  return B200_OK;
+}
+
+int b200_ctx_synchronize(b200_ctx* ctx) {
+  if (!ctx) return B200_INVALID;
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return B200_OK;
+}
+
+const char* b200_last_error(b200_ctx* ctx) { return ctx ? ctx->error.c_str() : "null context"; }
+
+int64_t b200_ctx_launch_count(b200_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+}  // extern "C"

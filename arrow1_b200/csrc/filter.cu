@@ -1,0 +1,409 @@
+// Filter: order-preserving stream compaction of a fixed-width column by a boolean mask, with
+// validity propagation.  Replaces GetFilterOutputSize + PrimitiveFilter + PrimitiveFilterImpl
+// (reference compute/kernels/vector_selection.cc:61-88, 570-835).
+//
+// Two kernels:
+//   filter_plan_kernel   popcount scan of the mask (∧ / ∨¬ its validity): per-tile exclusive output
+//                        offsets (4096-row tiles grouped in 64-tile super-tiles) and the output
+//                        length; the last block to finish scans the super-tile totals.
+//   filter_apply_kernel  one 4096-row tile per CTA; warp ballots are replaced by the mask words
+//                        themselves (the mask IS the ballot), ranks are popc(mask & lanemask_lt),
+//                        values are gathered with predicated coalesced loads and written to
+//                        consecutive output slots; validity bits (and boolean values) are
+//                        compacted with REDUX.OR and appended as whole 32-bit words.
+// HBM roofline: 8 B/row values + 3/8 B/row bitmaps read, s*(8+1/8) B/row written.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kTileRows = 4096;       // rows per apply CTA
+constexpr int kTilesPerSuper = 64;    // tiles per plan CTA
+constexpr int kSuperRows = kTileRows * kTilesPerSuper;
+constexpr int kThreads = 256;
+
+struct PlanHeader {       // first 64 bytes of a plan
+  int64_t out_length;     // total number of emitted rows
+  uint32_t done_counter;  // blocks finished (threadfence reduction)
+  uint32_t pad;
+  int64_t reserved[6];
+};
+static_assert(sizeof(PlanHeader) == 64, "plan header");
+
+struct PlanView {
+  PlanHeader* header;
+  int64_t* super_prefix;   // [n_super] exclusive prefix of emitted rows per super-tile
+  int64_t* super_total;    // [n_super]
+  uint32_t* tile_prefix;   // [n_tiles] exclusive prefix inside the super-tile
+};
+
+inline int64_t n_tiles_for(int64_t length) { return (length + kTileRows - 1) / kTileRows; }
+inline int64_t n_super_for(int64_t length) { return (length + kSuperRows - 1) / kSuperRows; }
+
+inline size_t plan_bytes_for(int64_t length) {
+  int64_t nt = n_tiles_for(length), ns = n_super_for(length);
+  return sizeof(PlanHeader) + b200_align_up(size_t(ns) * 16, 64) + b200_align_up(size_t(nt) * 4, 64) + 64;
+}
+
+inline PlanView plan_view(void* plan, int64_t length) {
+  PlanView v;
+  int64_t ns = n_super_for(length);
+  char* p = reinterpret_cast<char*>(plan);
+  v.header = reinterpret_cast<PlanHeader*>(p);
+  v.super_prefix = reinterpret_cast<int64_t*>(p + sizeof(PlanHeader));
+  v.super_total = v.super_prefix + ns;
+  v.tile_prefix = reinterpret_cast<uint32_t*>(p + sizeof(PlanHeader) + b200_align_up(size_t(ns) * 16, 64));
+  return v;
+}
+
+__device__ __forceinline__ uint32_t warp_inclusive_scan(uint32_t v) {
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, v, d);
+    if (lane >= d) v += t;
+  }
+  return v;
+}
+
+// emitted-row word: DROP keeps filter ∧ valid; EMIT_NULL keeps filter ∨ ¬valid
+// (vector_selection.cc:61-88).  `inrange` masks rows beyond the array length.
+__device__ __forceinline__ uint64_t emit_word64(uint64_t f, uint64_t fv, uint64_t inrange, int null_sel) {
+  return null_sel ? ((f | ~fv) & inrange) : (f & fv);
+}
+
+__global__ void __launch_bounds__(kThreads)
+filter_plan_kernel(BitmapRef f, BitmapRef fv, int64_t length, int null_sel, int64_t n_tiles, PlanView plan) {
+  __shared__ uint32_t partial[16][8];
+  __shared__ uint32_t tile_counts[kTilesPerSuper];
+  __shared__ bool is_last;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int64_t super = blockIdx.x;
+  const int64_t row0 = super * int64_t(kSuperRows);
+  const BitmapRef ones{nullptr, 0};
+  // word w = i*256 + t of the super-tile; tile of that word = i*4 + t/64
+#pragma unroll 4
+  for (int i = 0; i < 16; ++i) {
+    int64_t pos = row0 + (int64_t(i) * 256 + t) * 64;
+    uint32_t c = 0;
+    if (pos < length) {
+      uint64_t fw = bitmap_load64(f, pos, length);
+      uint64_t vw = bitmap_load64(fv, pos, length);
+      uint64_t in = bitmap_load64(ones, pos, length);
+      c = __popcll(emit_word64(fw, vw, in, null_sel));
+    }
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (lane == 0) partial[i][warp] = c;
+  }
+  __syncthreads();
+  uint32_t cnt = 0;
+  if (t < kTilesPerSuper) {
+    int i = t >> 2, q = t & 3;
+    cnt = partial[i][2 * q] + partial[i][2 * q + 1];
+    tile_counts[t] = cnt;
+  }
+  __syncthreads();
+  if (t < kTilesPerSuper) {
+    // exclusive scan over 64 counts: two warps
+    uint32_t incl = warp_inclusive_scan(cnt);
+    uint32_t add = 0;
+    if (t >= 32) {
+      for (int j = 0; j < 32; ++j) add += tile_counts[j];
+    }
+    int64_t tile = super * kTilesPerSuper + t;
+    if (tile < n_tiles) plan.tile_prefix[tile] = incl - cnt + add;
+    if (t == kTilesPerSuper - 1) plan.super_total[super] = int64_t(incl) + add;
+  }
+  // threadfence reduction: the last block scans the super-tile totals
+  __threadfence();
+  __syncthreads();
+  if (t == 0) {
+    uint32_t ticket = atomicAdd(&plan.header->done_counter, 1u);
+    is_last = (ticket == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  // single-block scan of n_super totals (<= a few thousand even at 1 B rows)
+  __shared__ int64_t carry_s;
+  __shared__ int64_t warp_sums[8];
+  if (t == 0) carry_s = 0;
+  __syncthreads();
+  const int64_t ns = gridDim.x;
+  const volatile int64_t* totals = plan.super_total;
+  for (int64_t base = 0; base < ns; base += kThreads) {
+    int64_t idx = base + t;
+    int64_t v = idx < ns ? totals[idx] : 0;
+    int64_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      int64_t o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    int64_t wpre = 0;
+    for (int w = 0; w < warp; ++w) wpre += warp_sums[w];
+    int64_t carry = carry_s;
+    if (idx < ns) plan.super_prefix[idx] = carry + wpre + incl - v;
+    __syncthreads();
+    if (t == kThreads - 1) carry_s = carry + wpre + incl;
+    __syncthreads();
+  }
+  if (t == 0) {
+    plan.header->out_length = carry_s;
+    plan.header->done_counter = 0;
+  }
+}
+
+struct ApplyArgs {
+  BitmapRef f, fv, vv;   // mask data, mask validity, values validity
+  BitmapRef vbits;       // values data as a bitmap (BOOL only)
+  const void* vdata;     // values data, already shifted by the element offset (non-BOOL)
+  int64_t length;
+  int null_sel;
+  const int64_t* super_prefix;
+  const uint32_t* tile_prefix;
+  void* out_data;
+  uint32_t* out_valid;   // nullable
+};
+
+// Appends compacted bit groups to an output bitmap as whole 32-bit words.  All lanes carry the
+// same (warp-uniform) state; lane 0 performs the memory operations.  Words shared with a
+// neighbouring warp/tile (first and last of the range) are merged with atomicOr into the
+// zero-initialised output, interior words are plain stores.
+struct BitAppender {
+  uint32_t* out;
+  int64_t word;
+  uint64_t acc;
+  int nacc;
+  bool first_shared;
+  __device__ __forceinline__ void init(uint32_t* o, int64_t start_bit) {
+    out = o;
+    word = start_bit >> 5;
+    nacc = int(start_bit & 31);
+    acc = 0;
+    first_shared = nacc != 0;
+  }
+  __device__ __forceinline__ void append(uint32_t bits, int n, int lane) {
+    acc |= uint64_t(bits) << nacc;
+    nacc += n;
+    if (nacc >= 32) {
+      if (lane == 0) {
+        uint32_t w = uint32_t(acc);
+        if (first_shared) {
+          if (w) atomicOr(out + word, w);
+        } else {
+          out[word] = w;
+        }
+      }
+      first_shared = false;
+      ++word;
+      acc >>= 32;
+      nacc -= 32;
+    }
+  }
+  __device__ __forceinline__ void finish(int lane) {
+    if (nacc > 0 && lane == 0) {
+      uint32_t w = uint32_t(acc);
+      if (w) atomicOr(out + word, w);
+    }
+  }
+};
+
+template <typename T, bool kBool, bool kHasValid>
+__global__ void __launch_bounds__(kThreads)
+filter_apply_kernel(ApplyArgs a) {
+  __shared__ uint32_t warp_totals[8];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int64_t tile = blockIdx.x;
+  const int64_t out_base = a.super_prefix[tile / kTilesPerSuper] + a.tile_prefix[tile];
+  const int64_t wrow0 = tile * int64_t(kTileRows) + int64_t(warp) * 512;
+  const BitmapRef ones{nullptr, 0};
+
+  uint32_t e = 0, iv = 0, vvw = 0, dbw = 0;
+  if (lane < 16) {
+    int64_t r = wrow0 + lane * 32;
+    if (r < a.length) {
+      uint32_t f = bitmap_load32(a.f, r, a.length);
+      uint32_t fv = bitmap_load32(a.fv, r, a.length);
+      uint32_t in = bitmap_load32(ones, r, a.length);
+      iv = f & fv;
+      e = a.null_sel ? ((f | ~fv) & in) : iv;
+      if (kHasValid) vvw = bitmap_load32(a.vv, r, a.length);
+      if (kBool) dbw = bitmap_load32(a.vbits, r, a.length);
+    }
+  }
+  const uint32_t cnt = __popc(e);
+  const uint32_t incl = warp_inclusive_scan(cnt);
+  const uint32_t step_prefix = incl - cnt;
+  const uint32_t wtotal = __shfl_sync(0xffffffffu, incl, 31);
+  if (lane == 0) warp_totals[warp] = wtotal;
+  __syncthreads();
+  uint32_t wprefix = 0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w)
+    if (w < warp) wprefix += warp_totals[w];
+  if (wtotal == 0) return;  // warp-uniform: nothing emitted by this warp
+
+  const int64_t wout = out_base + wprefix;
+  BitAppender valid_app, data_app;
+  if (kHasValid) valid_app.init(a.out_valid, wout);
+  if (kBool) data_app.init(reinterpret_cast<uint32_t*>(a.out_data), wout);
+  const T* vals = reinterpret_cast<const T*>(a.vdata);
+  T* out = reinterpret_cast<T*>(a.out_data);
+  const unsigned lt = lanemask_lt();
+
+#pragma unroll
+  for (int s = 0; s < 16; ++s) {
+    const uint32_t es = __shfl_sync(0xffffffffu, e, s);
+    if (es == 0) continue;  // warp-uniform
+    const uint32_t ivs = __shfl_sync(0xffffffffu, iv, s);
+    const uint32_t ps = __shfl_sync(0xffffffffu, step_prefix, s);
+    const bool emit = (es >> lane) & 1u;
+    const bool isv = (ivs >> lane) & 1u;
+    const uint32_t rank = __popc(es & lt);
+    if (!kBool) {
+      T v = T(0);  // an emitted filter-null writes zero (vector_selection.cc:743-746)
+      if (isv) v = vals[wrow0 + s * 32 + lane];
+      if (emit) out[wout + ps + rank] = v;
+    } else {
+      const uint32_t ds = __shfl_sync(0xffffffffu, dbw, s);
+      const uint32_t bit = (isv && ((ds >> lane) & 1u)) ? (1u << rank) : 0u;
+      const uint32_t cw = __reduce_or_sync(0xffffffffu, bit);
+      data_app.append(cw, __popc(es), lane);
+    }
+    if (kHasValid) {
+      const uint32_t vs = __shfl_sync(0xffffffffu, vvw, s);
+      const uint32_t bit = (isv && ((vs >> lane) & 1u)) ? (1u << rank) : 0u;
+      const uint32_t cw = __reduce_or_sync(0xffffffffu, bit);
+      valid_app.append(cw, __popc(es), lane);
+    }
+  }
+  if (kHasValid) valid_app.finish(lane);
+  if (kBool) data_app.finish(lane);
+}
+
+int check_mask(b200_ctx* ctx, const b200_col* mask) {
+  if (!mask) return b200_fail(ctx, B200_INVALID, "filter: null mask descriptor");
+  // FilterMetaFunction: "Filter argument must be boolean type" (vector_selection.cc:1885-1887)
+  if (mask->type != B200_BOOL)
+    return b200_fail(ctx, B200_NOT_IMPLEMENTED, "Filter argument must be boolean type");
+  if (mask->length < 0 || mask->offset < 0) return b200_fail(ctx, B200_INVALID, "filter: negative length/offset");
+  if (mask->length > 0 && mask->data == nullptr) return b200_fail(ctx, B200_INVALID, "filter: mask has no data buffer");
+  return B200_OK;
+}
+
+template <typename T, bool kBool>
+int launch_apply(b200_ctx* ctx, const ApplyArgs& a, int64_t n_tiles) {
+  dim3 grid((unsigned)n_tiles), block(kThreads);
+  if (a.out_valid)
+    filter_apply_kernel<T, kBool, true><<<grid, block, 0, ctx->stream>>>(a);
+  else
+    filter_apply_kernel<T, kBool, false><<<grid, block, 0, ctx->stream>>>(a);
+  B200_LAUNCHED(ctx);
+  return B200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_filter_plan_bytes(int64_t mask_length, size_t* out_bytes) {
+  if (!out_bytes || mask_length < 0) return B200_INVALID;
+  *out_bytes = plan_bytes_for(mask_length);
+  return B200_OK;
+}
+
+const int64_t* b200_filter_plan_length_ptr(const void* plan) {
+  return &reinterpret_cast<const PlanHeader*>(plan)->out_length;
+}
+
+int b200_filter_plan(b200_ctx* ctx, const b200_col* mask, int null_selection, void* plan, int64_t* out_len) {
+  if (!ctx) return B200_INVALID;
+  B200_RETURN_NOT_OK(check_mask(ctx, mask));
+  if (!plan) return b200_fail(ctx, B200_INVALID, "filter_plan: null plan buffer");
+  if (null_selection != 0 && null_selection != 1) return b200_fail(ctx, B200_INVALID, "filter: bad null_selection");
+  const int64_t length = mask->length;
+  PlanView pv = plan_view(plan, length);
+  // out_length = 0 and done_counter = 0 before the scan starts
+  B200_CUDA(ctx, cudaMemsetAsync(pv.header, 0, sizeof(PlanHeader), ctx->stream));
+  if (length > 0) {
+    BitmapRef f = make_bitmap_ref(mask->data, mask->offset);
+    BitmapRef fv = make_bitmap_ref(mask->validity, mask->offset);
+    filter_plan_kernel<<<(unsigned)n_super_for(length), kThreads, 0, ctx->stream>>>(
+        f, fv, length, null_selection, n_tiles_for(length), pv);
+    B200_LAUNCHED(ctx);
+  }
+  if (out_len) {
+    B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words, &pv.header->out_length, sizeof(int64_t),
+                                   cudaMemcpyDeviceToHost, ctx->stream));
+    B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *out_len = ctx->host_words[0];
+  }
+  return B200_OK;
+}
+
+int b200_filter_count(b200_ctx* ctx, const b200_col* mask, int null_selection, int64_t* out_len) {
+  if (!ctx || !out_len) return B200_INVALID;
+  B200_RETURN_NOT_OK(check_mask(ctx, mask));
+  size_t bytes = plan_bytes_for(mask->length);
+  B200_RETURN_NOT_OK(b200_ctx_reserve_scratch(ctx, bytes));
+  return b200_filter_plan(ctx, mask, null_selection, ctx->scratch, out_len);
+}
+
+int b200_filter_out_spec(const b200_col* values, const b200_col* mask, int null_selection,
+                         int* allocate_validity, int64_t* out_null_count) {
+  if (!values || !mask) return B200_INVALID;
+  // GetPrimitiveArg: null_count is 0 when there is no validity bitmap (util_internal.cc:56)
+  int64_t vnc = values->validity ? values->null_count : 0;
+  int64_t fnc = mask->validity ? mask->null_count : 0;
+  // PrimitiveFilter (vector_selection.cc:799-812)
+  if (out_null_count) *out_null_count = (vnc == 0 && (null_selection == 0 || fnc == 0)) ? 0 : -1;
+  if (allocate_validity) *allocate_validity = (vnc != 0 || fnc != 0) ? 1 : 0;
+  return B200_OK;
+}
+
+int b200_filter_apply(b200_ctx* ctx, const b200_col* values, const b200_col* mask, int null_selection,
+                      const void* plan, void* out_data, void* out_validity, int64_t out_capacity) {
+  if (!ctx) return B200_INVALID;
+  B200_RETURN_NOT_OK(check_mask(ctx, mask));
+  if (!values || !plan) return b200_fail(ctx, B200_INVALID, "filter_apply: null argument");
+  // ExecBatchIterator: "Array arguments must all be the same length" (compute/exec.cc:186-189)
+  if (values->length != mask->length)
+    return b200_fail(ctx, B200_INVALID, "Array arguments must all be the same length");
+  const int bits = b200_type_bits(values->type);
+  if (bits == 0) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "filter: unsupported values type %d", values->type);
+  if (out_capacity < 0) return b200_fail(ctx, B200_INVALID, "filter_apply: negative out_capacity");
+  const int64_t length = mask->length;
+  if (length == 0 || out_capacity == 0) return B200_OK;
+  if (!out_data) return b200_fail(ctx, B200_INVALID, "filter_apply: null out_data");
+  if ((reinterpret_cast<uintptr_t>(out_data) & 7) || (reinterpret_cast<uintptr_t>(out_validity) & 7))
+    return b200_fail(ctx, B200_INVALID, "filter_apply: output buffers must be 8-byte aligned");
+  PlanView pv = plan_view(const_cast<void*>(plan), length);
+  ApplyArgs a;
+  a.f = make_bitmap_ref(mask->data, mask->offset);
+  a.fv = make_bitmap_ref(mask->validity, mask->offset);
+  a.vv = make_bitmap_ref(values->validity, values->offset);
+  a.vbits = make_bitmap_ref(values->data, values->offset);
+  a.vdata = bits >= 8 ? reinterpret_cast<const char*>(values->data) + values->offset * (bits / 8) : nullptr;
+  a.length = length;
+  a.null_sel = null_selection;
+  a.super_prefix = pv.super_prefix;
+  a.tile_prefix = pv.tile_prefix;
+  a.out_data = out_data;
+  a.out_valid = reinterpret_cast<uint32_t*>(out_validity);
+  const size_t bitmap_bytes = b200_align_up(size_t((out_capacity + 7) / 8), 4);
+  if (out_validity) B200_CUDA(ctx, cudaMemsetAsync(out_validity, 0, bitmap_bytes, ctx->stream));
+  if (bits == 1) B200_CUDA(ctx, cudaMemsetAsync(out_data, 0, bitmap_bytes, ctx->stream));
+  const int64_t nt = n_tiles_for(length);
+  switch (bits) {
+    case 1: return launch_apply<uint8_t, true>(ctx, a, nt);
+    case 8: return launch_apply<uint8_t, false>(ctx, a, nt);
+    case 16: return launch_apply<uint16_t, false>(ctx, a, nt);
+    case 32: return launch_apply<uint32_t, false>(ctx, a, nt);
+    case 64: return launch_apply<uint64_t, false>(ctx, a, nt);
+  }
+  return b200_fail(ctx, B200_NOT_IMPLEMENTED, "filter: bit width %d", bits);
+}
+
+}  // extern "C"

@@ -1,0 +1,233 @@
+/*
+ * arrow1_b200.h — C ABI of the B200-native (sm_100a) Filter / SortIndices / grouped-aggregate
+ * hot path of Arrow C++ 5.0.0-SNAPSHOT (reference: zhztheplayer/arrow-1).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no Arrow and no torch types.  Every
+ * pointer inside a b200_col, and every `out_*` / `scratch` pointer, is a DEVICE pointer in the
+ * address space of the context's device unless the parameter is documented as host.  The
+ * reference interface each entry point replaces is cited as file:line under
+ * /root/reference/cpp/src/arrow/ .
+ *
+ * Conventions
+ *  - every function returns a b200_status; the values equal arrow::StatusCode (status.h:78-97)
+ *    so the Arrow-side glue maps them with a cast.  b200_last_error() holds the message.
+ *  - all work is enqueued on the context's CUDA stream.  A call returns without synchronising
+ *    unless it hands a host-visible scalar back (an output length, num_groups), in which case it
+ *    synchronises that stream only.
+ *  - bitmaps are Arrow bitmaps: LSB-first, bit i of the array is bit (offset + i) of the buffer.
+ *  - no CPU fallback exists: without a CUDA device every compute entry point fails.
+ */
+#ifndef ARROW1_B200_H
+#define ARROW1_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B200_API __attribute__((visibility("default")))
+#else
+#define B200_API
+#endif
+
+/* == arrow::StatusCode, status.h:78-97 */
+typedef enum b200_status {
+  B200_OK = 0,
+  B200_OUT_OF_MEMORY = 1,
+  B200_KEY_ERROR = 2,
+  B200_TYPE_ERROR = 3,
+  B200_INVALID = 4,
+  B200_IO_ERROR = 5,
+  B200_CAPACITY_ERROR = 6,
+  B200_INDEX_ERROR = 7,
+  B200_UNKNOWN_ERROR = 9,
+  B200_NOT_IMPLEMENTED = 10
+} b200_status;
+
+/* == arrow::Type::type for the fixed-width primitives on the path, type_fwd.h (enum Type) */
+typedef enum b200_type {
+  B200_BOOL = 1,
+  B200_UINT8 = 2,
+  B200_INT8 = 3,
+  B200_UINT16 = 4,
+  B200_INT16 = 5,
+  B200_UINT32 = 6,
+  B200_INT32 = 7,
+  B200_UINT64 = 8,
+  B200_INT64 = 9,
+  B200_FLOAT = 11,
+  B200_DOUBLE = 12
+} b200_type;
+
+/* Device column descriptor: mirror of compute::internal::PrimitiveArg
+ * (compute/kernels/util_internal.h:35-47) over ArrayData (array/data.h:73-245), EXCEPT that
+ * `data` is the start of buffers[1] and is NOT pre-shifted by `offset` (simpler for the glue:
+ * data = buffers[1]->address(), offset = ArrayData::offset for every bit width). */
+typedef struct b200_col {
+  const void* validity; /* device; NULL = no validity bitmap (== no nulls)                 */
+  const void* data;     /* device; values buffer (bitmap when type == B200_BOOL)          */
+  int32_t type;         /* b200_type                                                       */
+  int32_t reserved;
+  int64_t length;       /* elements                                                        */
+  int64_t offset;       /* elements (bits for bitmaps)                                     */
+  int64_t null_count;   /* -1 = unknown (kUnknownNullCount); ignored if validity == NULL   */
+} b200_col;
+
+/* Mutable twin used for outputs the library fills. */
+typedef struct b200_out_col {
+  void* validity; /* device; may be NULL where the operation documents it */
+  void* data;     /* device */
+  int32_t type;
+  int32_t reserved;
+  int64_t length;
+  int64_t null_count; /* filled by the library: exact count or -1 */
+} b200_out_col;
+
+typedef struct b200_ctx b200_ctx;
+
+/* ---- context ------------------------------------------------------------------------------
+ * One context = one device + one stream (SURVEY §8b "Threading").  `cu_stream` is a
+ * cudaStream_t / CUstream owned by the caller (NULL = the legacy default stream).
+ * Replaces: the role ExecContext plays for CPU kernels (compute/exec.h:58-120) plus the
+ * CudaContext a CudaBuffer belongs to (gpu/cuda_context.h:211-308). */
+B200_API int b200_ctx_create(int device, void* cu_stream, b200_ctx** out);
+B200_API int b200_ctx_destroy(b200_ctx* ctx);
+B200_API int b200_ctx_set_stream(b200_ctx* ctx, void* cu_stream);
+B200_API int b200_ctx_synchronize(b200_ctx* ctx);
+/* message of the last failure on this context ("" if none); valid until the next call */
+B200_API const char* b200_last_error(b200_ctx* ctx);
+/* number of kernels this context has launched since creation (bench.py's gpu_launches) */
+B200_API int64_t b200_ctx_launch_count(b200_ctx* ctx);
+B200_API const char* b200_version(void);
+
+/* ---- Filter -------------------------------------------------------------------------------
+ * null_selection: 0 = FilterOptions::DROP, 1 = FilterOptions::EMIT_NULL (api_vector.h:37-49).
+ *
+ * b200_filter_count     == GetFilterOutputSize                 (kernels/vector_selection.cc:61-88)
+ * b200_filter_plan      == the same scan, keeping per-tile output offsets on the device so that
+ *                          several columns can be compacted by one mask (FilterRecordBatch /
+ *                          FilterTable, vector_selection.cc:1776-1866, reuse one index vector)
+ * b200_filter_apply     == PrimitiveFilterImpl<T>::Exec        (vector_selection.cc:570-764)
+ * b200_filter_out_spec  == the null_count / allocate_validity rules of PrimitiveFilter
+ *                                                              (vector_selection.cc:799-812)
+ * Caller flow (== PrimitiveFilter, vector_selection.cc:786-835): plan -> allocate -> apply.
+ */
+B200_API int b200_filter_plan_bytes(int64_t mask_length, size_t* out_bytes);
+B200_API int b200_filter_count(b200_ctx* ctx, const b200_col* mask, int null_selection,
+                               int64_t* out_len /* host */);
+/* `plan` is device scratch of b200_filter_plan_bytes(mask->length) bytes.  If out_len (host) is
+ * non-NULL the stream is synchronised and the output length returned; if NULL the call is
+ * fully asynchronous (the length stays on the device inside the plan). */
+B200_API int b200_filter_plan(b200_ctx* ctx, const b200_col* mask, int null_selection, void* plan,
+                              int64_t* out_len /* host, nullable */);
+/* Compacts `values` by the planned mask.  out_capacity = number of elements the output buffers
+ * hold: the planned out_len, or mask->length when the caller skipped the host read-back.
+ * out_data holds out_capacity elements of the value width (a bitmap for B200_BOOL);
+ * out_validity holds out_capacity bits, or is NULL when b200_filter_out_spec says no validity
+ * is allocated.  Output buffers are 8-byte aligned and bitmap buffers are sized to a multiple of
+ * 8 bytes (Arrow pads to 64); bitmaps come back zero-padded, like KernelContext::AllocateBitmap
+ * (compute/kernel.cc:51-59). */
+B200_API int b200_filter_apply(b200_ctx* ctx, const b200_col* values, const b200_col* mask,
+                               int null_selection, const void* plan, void* out_data,
+                               void* out_validity /* nullable */, int64_t out_capacity);
+B200_API int b200_filter_out_spec(const b200_col* values, const b200_col* mask, int null_selection,
+                                  int* allocate_validity, int64_t* out_null_count);
+/* device address of the int64 output length inside a plan (for fully asynchronous callers) */
+B200_API const int64_t* b200_filter_plan_length_ptr(const void* plan);
+
+/* ---- SortIndices --------------------------------------------------------------------------
+ * order: 0 = SortOrder::Ascending, 1 = SortOrder::Descending (api_vector.h:61-66).
+ * == ArraySortIndices<UInt64Type, T>::Exec with ArrayCompareSorter / ArrayCountOrCompareSorter
+ *    (kernels/vector_sort.cc:374-575): a STABLE sort of the row numbers; non-null non-NaN values
+ *    first, then NaNs, then nulls, the last two in row order, for both orders.
+ * out_indices: uint64[values->length] (device), never null (OUTPUT_NOT_NULL, vector_sort.cc:1747).
+ * `index_base` is added to every emitted index (ChunkedArraySorter's `offset`, vector_sort.cc:657-832;
+ * also the shard base of the multi-GPU sample sort).  scratch: device, >= *_scratch_bytes. */
+B200_API int b200_sort_indices_scratch_bytes(int64_t length, size_t* out_bytes);
+B200_API int b200_sort_indices(b200_ctx* ctx, const b200_col* values, int order,
+                               uint64_t index_base, uint64_t* out_indices, void* scratch,
+                               size_t scratch_bytes);
+/* Sample-sort building blocks for the multi-GPU path.  sort_keys writes the
+ * order-preserving 64-bit radix key of every row (the same transform the local sort uses;
+ * NaN -> 2^64-2, null -> 2^64-1) so that ranks can exchange (key, global row) pairs;
+ * sort_pairs stably sorts such pairs by key, ties by their input order. */
+B200_API int b200_sort_keys(b200_ctx* ctx, const b200_col* values, int order, uint64_t* out_keys);
+B200_API int b200_sort_pairs_scratch_bytes(int64_t length, size_t* out_bytes);
+B200_API int b200_sort_pairs(b200_ctx* ctx, const uint64_t* keys, const uint64_t* payload,
+                             int64_t length, uint64_t* out_keys /* nullable */,
+                             uint64_t* out_payload, void* scratch, size_t scratch_bytes);
+
+/* ---- Grouper + hash aggregates ------------------------------------------------------------
+ * b200_agg_kind: the registered hash aggregate functions (kernels/hash_aggregate.cc:1039-1062)
+ * plus hash_mean, which the reference lacks and is defined as MeanImpl::Finalize
+ * (kernels/aggregate_basic_internal.h:99-109) over GroupedSumImpl's sums/counts. */
+typedef enum b200_agg_kind {
+  B200_HASH_COUNT = 0,   /* GroupedCountImpl   hash_aggregate.cc:466-517 */
+  B200_HASH_SUM = 1,     /* GroupedSumImpl     hash_aggregate.cc:522-622 */
+  B200_HASH_MIN_MAX = 2, /* GroupedMinMaxImpl  hash_aggregate.cc:627-768 */
+  B200_HASH_MEAN = 3
+} b200_agg_kind;
+
+typedef struct b200_agg_spec {
+  int32_t kind;     /* b200_agg_kind */
+  int32_t arg_type; /* b200_type of the argument column */
+  /* hash_count: CountOptions::count_mode (0 COUNT_NON_NULL, 1 COUNT_NULL; api_aggregate.h:47-58)
+   * hash_min_max: MinMaxOptions::null_handling (0 SKIP, 1 EMIT_NULL; api_aggregate.h:65-76) */
+  int32_t option;
+  int32_t reserved;
+} b200_agg_spec;
+
+typedef struct b200_groupby b200_groupby;
+
+/* == Grouper::Make + GetKernels/InitKernels (hash_aggregate.cc:314-356, 809-859).
+ * Keys: 1..4 fixed-width columns (B200_BOOL..B200_DOUBLE) whose packed width is <= 64 bits;
+ * otherwise B200_NOT_IMPLEMENTED, as GrouperImpl::Make does for unsupported key types.
+ * expected_groups: sizing hint for the open-addressing table (0 = unknown, the table grows). */
+B200_API int b200_groupby_create(b200_ctx* ctx, int n_keys, const int32_t* key_types, int n_aggs,
+                                 const b200_agg_spec* aggs, int64_t expected_groups,
+                                 b200_groupby** out);
+B200_API int b200_groupby_destroy(b200_groupby* gb);
+/* == one iteration of GroupBy's batch loop (hash_aggregate.cc:928-943): Grouper::Consume
+ * (:358-408) fused with every aggregate's Consume.  args[i] feeds aggs[i].  row_base is the
+ * global index of the batch's first row: group order is first-occurrence order of
+ * (row_base + i), which makes range-sharded partial tables mergeable in reference order. */
+B200_API int b200_groupby_consume(b200_groupby* gb, const b200_col* keys, const b200_col* args,
+                                  uint64_t row_base);
+/* == Grouper::Consume proper (hash_aggregate.cc:358-408): writes the uint32 group id of every
+ * row, ids handed out in first-occurrence order across calls. */
+B200_API int b200_grouper_consume(b200_groupby* gb, const b200_col* keys, uint32_t* out_ids);
+/* == HashAggregateKernel::consume with the reference signature (arg, uint32 ids, num_groups)
+ * (hash_aggregate.cc:783-789): accumulates aggregate `agg_index` of `gb` by dense group id. */
+B200_API int b200_hash_agg_consume(b200_groupby* gb, int agg_index, const b200_col* arg,
+                                   const uint32_t* ids, uint32_t num_groups);
+/* == Grouper::num_groups (hash_aggregate.cc:410); synchronises. */
+B200_API int b200_groupby_num_groups(b200_groupby* gb, uint32_t* out /* host */);
+/* == HashAggregateKernel::merge, which the reference leaves NotImplemented
+ * (hash_aggregate.cc:795-798): folds every group of `src` into `dst` (same key/agg schema). */
+B200_API int b200_groupby_merge(b200_groupby* dst, b200_groupby* src);
+/* Export / import of the occupied slots as a flat device buffer, the unit the multi-GPU
+ * all-gather exchanges.  state_bytes = num_groups * slot_bytes. */
+B200_API int b200_groupby_state_layout(b200_groupby* gb, size_t* slot_bytes);
+B200_API int b200_groupby_export(b200_groupby* gb, void* out_state, uint32_t* out_groups /* host */);
+B200_API int b200_groupby_import(b200_groupby* gb, const void* state, uint32_t n_slots);
+/* == finalize of every kernel + Grouper::GetUniques (hash_aggregate.cc:946-960, 412-429).
+ * Call num_groups first, allocate, then finalize.  Layout of the outputs (all of length G):
+ *   out_keys[k]           data = G elements of key type k; validity = G bits or NULL
+ *                         (library reports null_count; validity may be NULL only if the key
+ *                         column never carried a validity bitmap)
+ *   out_aggs[j], by kind  COUNT:   data int64[G], validity ignored (never null)
+ *                         SUM:     data {int64|uint64|double}[G], validity G bits (required)
+ *                         MEAN:    data double[G], validity G bits (required)
+ *                         MIN_MAX: TWO consecutive entries: mins then maxes, of the argument
+ *                                  type, sharing one validity (the first's; the second's is
+ *                                  ignored), like struct<min,max> (hash_aggregate.cc:741-757)
+ * so out_aggs has n_aggs + (number of MIN_MAX aggs) entries. */
+B200_API int b200_groupby_finalize(b200_groupby* gb, b200_out_col* out_aggs, b200_out_col* out_keys);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ARROW1_B200_H */
