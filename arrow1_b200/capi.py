@@ -1,0 +1,348 @@
+"""ctypes binding of the C ABI (include/arrow1_b200.h) over torch-owned device memory.
+
+PyTorch is used here for device buffers and streams only; every computation goes through
+libarrow1_b200.so.  There is no fallback: a missing library or GPU raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from .columns import (BITS, BOOL, DOUBLE, HASH_MIN_MAX, INT64, NP_OF, UINT64, AggSpec, Column, agg_out_types,
+                      b200_agg_spec, b200_col, b200_out_col, col_array)
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libarrow1_b200.so")
+_lib = None
+
+STATUS_NAMES = {0: "OK", 1: "OutOfMemory", 2: "KeyError", 3: "TypeError", 4: "Invalid", 5: "IOError",
+                6: "CapacityError", 7: "IndexError", 9: "UnknownError", 10: "NotImplemented"}
+
+
+class B200Error(RuntimeError):
+    """Carries the arrow::StatusCode-valued status of a failed C-ABI call."""
+
+    def __init__(self, code: int, msg: str):
+        super().__init__("%s: %s" % (STATUS_NAMES.get(code, str(code)), msg))
+        self.code = code
+        self.message = msg
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise RuntimeError("libarrow1_b200.so is not built: run `python -m arrow1_b200.build` "
+                               "(there is no CPU fallback)")
+        L = C.CDLL(_LIB_PATH)
+        L.b200_last_error.restype = C.c_char_p
+        L.b200_version.restype = C.c_char_p
+        L.b200_ctx_launch_count.restype = C.c_int64
+        L.b200_filter_plan_length_ptr.restype = C.c_void_p
+        L.b200_filter_plan_length_ptr.argtypes = [C.c_void_p]
+        _lib = L
+    return _lib
+
+
+class Context:
+    """One device + one stream (b200_ctx)."""
+
+    def __init__(self, device: int = 0, stream: Optional[torch.cuda.Stream] = None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("arrow1_b200 needs a CUDA device (sm_100a); no CPU fallback exists")
+        self.device = device
+        torch.cuda.set_device(device)
+        self.stream = stream if stream is not None else torch.cuda.current_stream(device)
+        self._h = C.c_void_p()
+        code = lib().b200_ctx_create(C.c_int(device), C.c_void_p(self.stream.cuda_stream), C.byref(self._h))
+        if code != 0:
+            raise B200Error(code, "b200_ctx_create failed")
+
+    def close(self):
+        if self._h:
+            lib().b200_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def check(self, code: int):
+        if code != 0:
+            raise B200Error(code, lib().b200_last_error(self._h).decode())
+
+    def synchronize(self):
+        self.check(lib().b200_ctx_synchronize(self._h))
+
+    @property
+    def launches(self) -> int:
+        return int(lib().b200_ctx_launch_count(self._h))
+
+    def empty(self, nbytes: int) -> torch.Tensor:
+        # rounded up so bitmap tails and vector stores stay inside the allocation
+        return torch.empty(max((nbytes + 63) // 64 * 64, 64), dtype=torch.uint8, device="cuda:%d" % self.device)
+
+
+# ---------------------------------------------------------------------------------------------
+# Filter
+
+
+class FilterOutput:
+    def __init__(self, col: Column, has_validity: bool):
+        self.col = col
+        self.has_validity = has_validity
+
+    @property
+    def length(self):
+        return self.col.length
+
+    @property
+    def null_count(self):
+        return self.col.null_count
+
+    def data_bytes(self) -> bytes:
+        bits = BITS[self.col.type]
+        n = (self.col.length + 7) // 8 if bits == 1 else self.col.length * (bits // 8)
+        return self.col.data[:n].cpu().numpy().tobytes()
+
+    def validity_bytes(self) -> Optional[bytes]:
+        if not self.has_validity:
+            return None
+        return self.col.validity[: (self.col.length + 7) // 8].cpu().numpy().tobytes()
+
+
+def filter_out_spec(values: Column, mask: Column, null_selection: int):
+    av, nc = C.c_int(0), C.c_int64(0)
+    v, m = values.desc(), mask.desc()
+    lib().b200_filter_out_spec(C.byref(v), C.byref(m), C.c_int(null_selection), C.byref(av), C.byref(nc))
+    return bool(av.value), int(nc.value)
+
+
+class FilterPlan:
+    """Device-side scan of one mask, reusable for several value columns (b200_filter_plan)."""
+
+    def __init__(self, ctx: Context, mask: Column, null_selection: int = 0, sync: bool = True):
+        self.ctx, self.mask, self.null_selection = ctx, mask, null_selection
+        nbytes = C.c_size_t(0)
+        ctx.check(lib().b200_filter_plan_bytes(C.c_int64(mask.length), C.byref(nbytes)))
+        self.buf = ctx.empty(nbytes.value)
+        m = mask.desc()
+        out_len = C.c_int64(-1)
+        ctx.check(lib().b200_filter_plan(ctx._h, C.byref(m), C.c_int(null_selection), C.c_void_p(self.buf.data_ptr()),
+                                         C.byref(out_len) if sync else None))
+        self.out_length = int(out_len.value) if sync else None
+
+    def length_tensor(self) -> torch.Tensor:
+        return self.buf[:8].view(torch.int64)
+
+    def apply(self, values: Column, out_data: Optional[torch.Tensor] = None,
+              out_validity: Optional[torch.Tensor] = None) -> FilterOutput:
+        ctx = self.ctx
+        cap = self.out_length if self.out_length is not None else self.mask.length
+        has_validity, null_count = filter_out_spec(values, self.mask, self.null_selection)
+        bits = BITS[values.type]
+        if out_data is None:
+            out_data = ctx.empty((cap + 7) // 8 if bits == 1 else cap * (bits // 8))
+        if has_validity and out_validity is None:
+            out_validity = ctx.empty((cap + 7) // 8)
+        v, m = values.desc(), self.mask.desc()
+        ctx.check(lib().b200_filter_apply(ctx._h, C.byref(v), C.byref(m), C.c_int(self.null_selection),
+                                          C.c_void_p(self.buf.data_ptr()), C.c_void_p(out_data.data_ptr()),
+                                          C.c_void_p(out_validity.data_ptr()) if has_validity else None,
+                                          C.c_int64(cap)))
+        col = Column(values.type, out_data, out_validity if has_validity else None,
+                     self.out_length if self.out_length is not None else -1, 0, null_count)
+        return FilterOutput(col, has_validity)
+
+
+def filter_count(ctx: Context, mask: Column, null_selection: int = 0) -> int:
+    m = mask.desc()
+    n = C.c_int64(0)
+    ctx.check(lib().b200_filter_count(ctx._h, C.byref(m), C.c_int(null_selection), C.byref(n)))
+    return int(n.value)
+
+
+def filter(ctx: Context, values: Column, mask: Column, null_selection: int = 0) -> FilterOutput:
+    """== compute::Filter(values, mask, FilterOptions(null_selection)) on device columns."""
+    if values.length != mask.length:
+        # ExecBatchIterator::Make (compute/exec.cc:186-189)
+        raise B200Error(4, "Array arguments must all be the same length")
+    return FilterPlan(ctx, mask, null_selection, sync=True).apply(values)
+
+
+# ---------------------------------------------------------------------------------------------
+# SortIndices
+
+
+def sort_scratch_bytes(ctx: Context, length: int) -> int:
+    n = C.c_size_t(0)
+    ctx.check(lib().b200_sort_indices_scratch_bytes(C.c_int64(length), C.byref(n)))
+    return int(n.value)
+
+
+def sort_indices(ctx: Context, values: Column, order: int = 0, index_base: int = 0,
+                 out: Optional[torch.Tensor] = None, scratch: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """== compute::SortIndices(values, order): int64-typed tensor holding the uint64 indices."""
+    n = values.length
+    if out is None:
+        out = torch.empty(max(n, 1), dtype=torch.int64, device="cuda:%d" % ctx.device)
+    if scratch is None:
+        scratch = ctx.empty(sort_scratch_bytes(ctx, n))
+    v = values.desc()
+    ctx.check(lib().b200_sort_indices(ctx._h, C.byref(v), C.c_int(order), C.c_uint64(index_base),
+                                      C.c_void_p(out.data_ptr()), C.c_void_p(scratch.data_ptr()),
+                                      C.c_size_t(scratch.numel())))
+    return out[:n]
+
+
+def sort_keys(ctx: Context, values: Column, order: int = 0) -> torch.Tensor:
+    out = torch.empty(max(values.length, 1), dtype=torch.int64, device="cuda:%d" % ctx.device)
+    v = values.desc()
+    ctx.check(lib().b200_sort_keys(ctx._h, C.byref(v), C.c_int(order), C.c_void_p(out.data_ptr())))
+    return out[: values.length]
+
+
+def sort_pairs(ctx: Context, keys: torch.Tensor, payload: torch.Tensor, want_keys: bool = False):
+    n = keys.numel()
+    nb = C.c_size_t(0)
+    ctx.check(lib().b200_sort_pairs_scratch_bytes(C.c_int64(n), C.byref(nb)))
+    scratch = ctx.empty(nb.value)
+    out_p = torch.empty(max(n, 1), dtype=torch.int64, device=keys.device)
+    out_k = torch.empty(max(n, 1), dtype=torch.int64, device=keys.device) if want_keys else None
+    ctx.check(lib().b200_sort_pairs(ctx._h, C.c_void_p(keys.data_ptr()), C.c_void_p(payload.data_ptr()), C.c_int64(n),
+                                    C.c_void_p(out_k.data_ptr()) if want_keys else None,
+                                    C.c_void_p(out_p.data_ptr()), C.c_void_p(scratch.data_ptr()),
+                                    C.c_size_t(scratch.numel())))
+    return (out_k[:n] if want_keys else None), out_p[:n]
+
+
+# ---------------------------------------------------------------------------------------------
+# Grouper + hash aggregates
+
+
+class GroupByOutput:
+    """aggs[j] = list of Columns (one, or [mins, maxes] for hash_min_max); keys[k] = Column."""
+
+    def __init__(self, num_groups: int, aggs: List[List[Column]], keys: List[Column]):
+        self.num_groups, self.aggs, self.keys = num_groups, aggs, keys
+
+
+class GroupBy:
+    """== the streaming state of compute::internal::GroupBy (hash_aggregate.cc:890-966)."""
+
+    def __init__(self, ctx: Context, key_types: Sequence[int], aggs: Sequence[AggSpec], arg_types: Sequence[int],
+                 expected_groups: int = 0):
+        self.ctx = ctx
+        self.key_types = list(key_types)
+        self.aggs = list(aggs)
+        self.arg_types = list(arg_types)
+        kt = (C.c_int32 * max(len(key_types), 1))(*key_types)
+        specs = (b200_agg_spec * max(len(aggs), 1))()
+        for j, a in enumerate(aggs):
+            specs[j] = b200_agg_spec(a.kind, arg_types[j], a.option, 0)
+        self._h = C.c_void_p()
+        ctx.check(lib().b200_groupby_create(ctx._h, C.c_int(len(key_types)), kt, C.c_int(len(aggs)), specs,
+                                            C.c_int64(expected_groups), C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().b200_groupby_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def consume(self, keys: Sequence[Column], args: Sequence[Column], row_base: int = 0):
+        self.ctx.check(lib().b200_groupby_consume(self._h, col_array(keys), col_array(args), C.c_uint64(row_base)))
+
+    def grouper_consume(self, keys: Sequence[Column]) -> torch.Tensor:
+        n = keys[0].length
+        ids = torch.empty(max(n, 1), dtype=torch.int32, device="cuda:%d" % self.ctx.device)
+        self.ctx.check(lib().b200_grouper_consume(self._h, col_array(keys), C.c_void_p(ids.data_ptr())))
+        return ids[:n]
+
+    def agg_consume(self, agg_index: int, arg: Column, ids: torch.Tensor, num_groups: int):
+        a = arg.desc()
+        self.ctx.check(lib().b200_hash_agg_consume(self._h, C.c_int(agg_index), C.byref(a),
+                                                   C.c_void_p(ids.data_ptr()), C.c_uint32(num_groups)))
+
+    def num_groups(self) -> int:
+        g = C.c_uint32(0)
+        self.ctx.check(lib().b200_groupby_num_groups(self._h, C.byref(g)))
+        return int(g.value)
+
+    def merge(self, other: "GroupBy"):
+        self.ctx.check(lib().b200_groupby_merge(self._h, other._h))
+
+    def slot_bytes(self) -> int:
+        n = C.c_size_t(0)
+        self.ctx.check(lib().b200_groupby_state_layout(self._h, C.byref(n)))
+        return int(n.value)
+
+    def export_state(self) -> torch.Tensor:
+        g = self.num_groups()
+        sb = self.slot_bytes()
+        buf = self.ctx.empty(max(g, 1) * sb)
+        ng = C.c_uint32(0)
+        self.ctx.check(lib().b200_groupby_export(self._h, C.c_void_p(buf.data_ptr()), C.byref(ng)))
+        return buf[: ng.value * sb]
+
+    def import_state(self, state: torch.Tensor):
+        sb = self.slot_bytes()
+        n = state.numel() // sb
+        self.ctx.check(lib().b200_groupby_import(self._h, C.c_void_p(state.data_ptr()), C.c_uint32(n)))
+
+    def finalize(self) -> GroupByOutput:
+        ctx = self.ctx
+        G = self.num_groups()
+        out_types = [agg_out_types(a.kind, t) for a, t in zip(self.aggs, self.arg_types)]
+        flat = [t for ts in out_types for t in ts]
+        out_aggs = (b200_out_col * max(len(flat), 1))()
+        bufs = []
+        for i, t in enumerate(flat):
+            bits = BITS[t]
+            d = ctx.empty(max(G, 1) * max(bits // 8, 1))
+            v = ctx.empty((G + 7) // 8 + 8)
+            out_aggs[i] = b200_out_col(v.data_ptr(), d.data_ptr(), t, 0, 0, 0)
+            bufs.append((t, d, v))
+        out_keys = (b200_out_col * max(len(self.key_types), 1))()
+        kbufs = []
+        for i, t in enumerate(self.key_types):
+            bits = BITS[t]
+            d = ctx.empty((G + 7) // 8 + 8 if bits == 1 else max(G, 1) * (bits // 8))
+            v = ctx.empty((G + 7) // 8 + 8)
+            out_keys[i] = b200_out_col(v.data_ptr(), d.data_ptr(), t, 0, 0, 0)
+            kbufs.append((t, d, v))
+        ctx.check(lib().b200_groupby_finalize(self._h, out_aggs, out_keys))
+        ctx.synchronize()
+        aggs, i = [], 0
+        for ts in out_types:
+            cols = []
+            for _ in ts:
+                t, d, v = bufs[i]
+                cols.append(Column(t, d, v, G, 0, int(out_aggs[i].null_count)))
+                i += 1
+            if len(cols) == 2:
+                cols[1] = Column(cols[1].type, cols[1].data, cols[0].validity, G, 0, cols[0].null_count)
+            aggs.append(cols)
+        keys = [Column(t, d, v, G, 0, int(out_keys[k].null_count)) for k, (t, d, v) in enumerate(kbufs)]
+        return GroupByOutput(G, aggs, keys)
+
+
+def group_by(ctx: Context, keys: Sequence[Column], aggs: Sequence[AggSpec], args: Sequence[Column],
+             expected_groups: int = 0, row_base: int = 0) -> GroupByOutput:
+    """== compute::internal::GroupBy(arguments, keys, aggregates) in one batch."""
+    gb = GroupBy(ctx, [k.type for k in keys], aggs, [a.type for a in args], expected_groups)
+    try:
+        gb.consume(keys, args, row_base)
+        return gb.finalize()
+    finally:
+        gb.close()

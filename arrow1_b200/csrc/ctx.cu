@@ -50,7 +50,7 @@ int b200_ctx_create(int device, void* cu_stream, b200_ctx** out) {
     delete ctx;
     return B200_UNKNOWN_ERROR;
   }
-  cudaDeviceProp prop;
+  cudaDeviceProp prop = {};
   if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) ctx->num_sms = prop.multiProcessorCount;
   if (prop.major < 10) {
     fprintf(stderr, "arrow1_b200: device %d is sm_%d%d; this library is built for sm_100a only\n",

@@ -1,0 +1,77 @@
+"""The C-ABI library loads and exports every symbol include/arrow1_b200.h declares (no compute
+calls: this runs without a GPU), and the pure-host helpers behave."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from arrow1_b200 import columns as cols
+from arrow1_b200.columns import Column
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "arrow1_b200.h")).read()
+    return sorted(set(re.findall(r"B200_API\s+[\w\s\*]+?\b(b200_\w+)\s*\(", text)))
+
+
+def _lib():
+    from arrow1_b200 import build
+    path = build.build()
+    return C.CDLL(path)
+
+
+def test_header_declares_expected_surface():
+    syms = _declared_symbols()
+    for s in ("b200_ctx_create", "b200_filter_plan", "b200_filter_apply", "b200_sort_indices",
+              "b200_groupby_create", "b200_groupby_consume", "b200_groupby_finalize", "b200_grouper_consume",
+              "b200_hash_agg_consume", "b200_groupby_merge"):
+        assert s in syms
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib()
+    missing = [s for s in _declared_symbols() if not hasattr(lib, s)]
+    assert not missing, missing
+
+
+def test_filter_out_spec_rules():
+    # PrimitiveFilter null_count / allocate_validity rules (vector_selection.cc:799-812)
+    import numpy as np
+    lib = _lib()
+    v_nonull = Column.from_numpy(np.arange(4, dtype=np.int32))
+    v_nulls = Column.from_numpy(np.arange(4, dtype=np.int32), np.array([1, 0, 1, 1], dtype=bool))
+    m_nonull = Column.from_numpy(np.array([1, 0, 1, 1], dtype=bool))
+    m_nulls = Column.from_numpy(np.array([1, 0, 1, 1], dtype=bool), np.array([1, 1, 0, 1], dtype=bool))
+    cases = [  # values, mask, null_sel -> (allocate_validity, null_count)
+        (v_nonull, m_nonull, 0, (0, 0)), (v_nonull, m_nonull, 1, (0, 0)),
+        (v_nonull, m_nulls, 0, (1, 0)), (v_nonull, m_nulls, 1, (1, -1)),
+        (v_nulls, m_nonull, 0, (1, -1)), (v_nulls, m_nulls, 1, (1, -1)),
+    ]
+    for v, m, ns, exp in cases:
+        av, nc = C.c_int(-5), C.c_int64(-5)
+        vd, md = v.desc(), m.desc()
+        assert lib.b200_filter_out_spec(C.byref(vd), C.byref(md), C.c_int(ns), C.byref(av), C.byref(nc)) == 0
+        assert (av.value, nc.value) == exp
+
+
+def test_plan_and_scratch_sizes():
+    lib = _lib()
+    n = C.c_size_t(0)
+    assert lib.b200_filter_plan_bytes(C.c_int64(10_000_000), C.byref(n)) == 0 and n.value > 0
+    assert lib.b200_sort_indices_scratch_bytes(C.c_int64(1000), C.byref(n)) == 0 and n.value > 24 * 1000
+    assert lib.b200_filter_plan_bytes(C.c_int64(-1), C.byref(n)) == 4  # Invalid
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    lib = _lib()
+    h = C.c_void_p()
+    assert lib.b200_ctx_create(C.c_int(0), None, C.byref(h)) != 0
+    from arrow1_b200 import capi
+    with pytest.raises(RuntimeError):
+        capi.Context(0)

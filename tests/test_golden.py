@@ -1,0 +1,165 @@
+"""Golden vectors transcribed from the reference's own tests (tests/golden/*.json), pushed through
+the oracle port, the unmodified reference (when oracle/_ref is built) and — marked gpu — the CUDA
+path through the C ABI."""
+import numpy as np
+import pytest
+
+import oracle
+from arrow1_b200 import columns as cols
+from arrow1_b200.columns import AggSpec, Column
+from conftest import TYPE_BY_NAME, column_from_json, expected_from_json, load_golden
+from helpers import run_filter, run_groupby, run_sort
+
+IMPLS = [
+    pytest.param("port"),
+    pytest.param("reference", marks=pytest.mark.skipif(not oracle.have_reference(), reason="oracle/_ref not built")),
+    pytest.param("gpu", marks=pytest.mark.gpu),
+]
+
+
+def _ctx(impl, request):
+    return request.getfixturevalue("ctx") if impl == "gpu" else None
+
+
+def _coalesce_null_to_false(mask: Column) -> Column:
+    v = mask.values() & mask.valid()
+    return Column.from_numpy(v)
+
+
+def _check_filter_case(impl, ctx, type_name, case):
+    values = column_from_json(case["values"], type_name)
+    mask = column_from_json(case["mask"], "bool")
+    if "mask_slice" in case:
+        off, ln = case["mask_slice"]
+        parent = mask
+        mask = Column(parent.type, parent.data, parent.validity, ln, off, -1 if parent.validity is not None else 0)
+    exp_vals, exp_valid = expected_from_json(case["expected"], type_name)
+    # EMIT_NULL against the literal expectation (vector_selection_test.cc:184-187)
+    r = run_filter(impl, values, mask, 1, ctx)
+    assert r.length == len(exp_vals)
+    np.testing.assert_array_equal(r.valid, exp_valid)
+    np.testing.assert_array_equal(r.values[exp_valid], exp_vals[exp_valid])
+    # DROP == EMIT_NULL on the null-coalesced mask (vector_selection_test.cc:189-196)
+    r_drop = run_filter(impl, values, mask, 0, ctx)
+    r_ref = run_filter(impl, values, _coalesce_null_to_false(mask), 1, ctx)
+    assert r_drop.length == r_ref.length
+    np.testing.assert_array_equal(r_drop.valid, r_ref.valid)
+    np.testing.assert_array_equal(r_drop.values[r_drop.valid], r_ref.values[r_ref.valid])
+
+
+@pytest.mark.parametrize("impl", IMPLS)
+def test_filter_numeric_golden(impl, request):
+    g = load_golden("filter.json")
+    ctx = _ctx(impl, request)
+    for type_name in g["numeric_types"]:
+        for case in g["numeric"]:
+            _check_filter_case(impl, ctx, type_name, case)
+
+
+@pytest.mark.parametrize("impl", IMPLS)
+def test_filter_boolean_golden(impl, request):
+    g = load_golden("filter.json")
+    ctx = _ctx(impl, request)
+    for case in g["boolean"]:
+        _check_filter_case(impl, ctx, "bool", case)
+
+
+@pytest.mark.parametrize("impl", IMPLS)
+def test_filter_length_mismatch_is_invalid(impl, request):
+    g = load_golden("filter.json")["length_mismatch"]
+    ctx = _ctx(impl, request)
+    values = column_from_json(g["values"], "int32")
+    mask = column_from_json(g["mask"], "bool")
+    for null_sel in (0, 1):
+        with pytest.raises(Exception) as ei:
+            run_filter(impl, values, mask, null_sel, ctx)
+        assert getattr(ei.value, "code", None) == 4  # StatusCode::Invalid
+
+
+@pytest.mark.parametrize("impl", IMPLS)
+def test_sort_indices_golden(impl, request):
+    g = load_golden("sort_indices.json")
+    ctx = _ctx(impl, request)
+    groups = [(g["real_types"], g["real"]), (g["integral_types"], g["integral"]), (["uint8"], g["uint8"]),
+              (["int8"], g["int8"])]
+    for types, cases in groups:
+        for type_name in types:
+            for case in cases:
+                col = column_from_json(case["values"], type_name)
+                out = run_sort(impl, col, case["order"], 0, ctx)
+                np.testing.assert_array_equal(out, np.array(case["expected"], dtype=np.uint64),
+                                              err_msg="%s %s" % (type_name, case))
+
+
+def _batch(g):
+    arg = column_from_json(g["batch"]["argument"], "double")
+    key = column_from_json(g["batch"]["key"], "int64")
+    return arg, key
+
+
+def _cmp(col, expected, type_name):
+    vals, valid = col
+    ev, evalid = expected_from_json(expected, type_name)
+    np.testing.assert_array_equal(valid, evalid)
+    np.testing.assert_array_equal(vals[valid], ev[evalid])
+
+
+@pytest.mark.parametrize("impl", IMPLS)
+def test_group_by_golden(impl, request):
+    g = load_golden("group_by.json")
+    ctx = _ctx(impl, request)
+    arg, key = _batch(g)
+    r = run_groupby(impl, [key], [AggSpec(cols.HASH_SUM)], [arg], ctx)
+    assert r.num_groups == 4
+    _cmp(r.aggs[0][0], g["sum_only"]["hash_sum"], "double")
+    _cmp(r.keys[0], g["sum_only"]["key_0"], "int64")
+
+    r = run_groupby(impl, [key], [AggSpec(cols.HASH_MIN_MAX)], [arg], ctx)
+    _cmp(r.aggs[0][0], g["min_max_only"]["min"], "double")
+    _cmp(r.aggs[0][1], g["min_max_only"]["max"], "double")
+    _cmp(r.keys[0], g["min_max_only"]["key_0"], "int64")
+
+    # "passing an argument twice or also using it as a key is legal" (hash_aggregate_test.cc:575)
+    aggs = [AggSpec(cols.HASH_COUNT), AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_SUM)]
+    r = run_groupby(impl, [key], aggs, [arg, arg, key], ctx)
+    e = g["count_and_sum"]
+    _cmp(r.aggs[0][0], e["hash_count"], "int64")
+    _cmp(r.aggs[1][0], e["hash_sum_f64"], "double")
+    _cmp(r.aggs[2][0], e["hash_sum_key_i64"], "int64")
+    _cmp(r.keys[0], e["key_0"], "int64")
+
+
+def _grouper_sequence(impl, ctx, key_types, batches):
+    """Successive Consume calls keep handing out ids in first-occurrence order."""
+    if impl == "gpu":
+        from arrow1_b200 import capi
+        gb = capi.GroupBy(ctx, [TYPE_BY_NAME[t] for t in key_types], [], [])
+        for b in batches:
+            keys = [column_from_json(v, t).to_device() for v, t in zip(b["keys"], key_types)]
+            ids = gb.grouper_consume(keys).cpu().numpy().view(np.uint32)
+            np.testing.assert_array_equal(ids, np.array(b["ids"], dtype=np.uint32), err_msg=str((key_types, b)))
+        gb.close()
+        return
+    # the CPU oracles are single-shot: replay the concatenation and compare the tail
+    acc = [[] for _ in key_types]
+    expected = []
+    for b in batches:
+        for i, v in enumerate(b["keys"]):
+            acc[i] += v
+        expected += b["ids"]
+        keys = [column_from_json(v, t) for v, t in zip(acc, key_types)]
+        r = oracle.groupby(keys, [], [], want_ids=True, kind=impl)
+        np.testing.assert_array_equal(r.ids, np.array(expected, dtype=np.uint32), err_msg=str((key_types, b)))
+
+
+@pytest.mark.parametrize("impl", IMPLS)
+def test_grouper_golden(impl, request):
+    g = load_golden("group_by.json")
+    ctx = _ctx(impl, request)
+    numeric = ["uint8", "int8", "uint16", "int16", "uint32", "int32", "uint64", "int64", "float", "double"]
+    for seq in g["grouper_sequences"]:
+        if seq["key_types"] == ["NUMERIC"]:
+            for t in numeric:
+                _grouper_sequence(impl, ctx, [t], seq["batches"])
+        else:
+            _grouper_sequence(impl, ctx, seq["key_types"], seq["batches"])

@@ -1,0 +1,95 @@
+"""Pins oracle/oracle.cc (the restated algorithm) against the UNMODIFIED reference built from
+/root/reference (oracle/_ref) on randomised inputs shaped like the reference's own property
+tests.  CPU only."""
+import numpy as np
+import pytest
+
+import oracle
+from arrow1_b200 import columns as cols
+from arrow1_b200.columns import AggSpec
+from gen import ALL_NUMERIC, rand_column, rand_mask
+from helpers import assert_filter_equal, assert_group_equal, run_filter, run_groupby, run_sort
+
+needs_ref = pytest.mark.skipif(not oracle.have_reference(), reason="oracle/_ref not built")
+
+
+@needs_ref
+@pytest.mark.parametrize("t", [cols.BOOL] + ALL_NUMERIC)
+def test_filter_port_matches_reference(t):
+    rng = np.random.default_rng(1234 + t)
+    # vector_selection_test.cc:1618-1636: null_prob x true_prob matrix, length 1024, mis-aligned slices
+    for null_prob in (0.0, 0.01, 0.1, 0.999, 1.0):
+        for true_prob in (0.0, 0.1, 0.999, 1.0):
+            for (voff, moff) in ((0, 0), (3, 4)):
+                for mask_null in (0.0, 0.05):
+                    values = rand_column(rng, t, 1024, null_prob, offset=voff)
+                    mask = rand_mask(rng, 1024, true_prob, mask_null, offset=moff)
+                    for null_sel in (0, 1):
+                        a = run_filter("port", values, mask, null_sel)
+                        b = run_filter("reference", values, mask, null_sel)
+                        assert_filter_equal(a, b, bit_exact=True)
+
+
+@needs_ref
+def test_filter_unknown_null_count_port_matches_reference():
+    # vector_selection_test.cc:445-455: null_count unknown (-1) on both sides
+    rng = np.random.default_rng(7)
+    values = rand_column(rng, cols.INT32, 500, 0.2)
+    mask = rand_mask(rng, 500, 0.5, 0.1)
+    values.null_count = -1
+    mask.null_count = -1
+    for null_sel in (0, 1):
+        assert_filter_equal(run_filter("port", values, mask, null_sel), run_filter("reference", values, mask, null_sel))
+
+
+@needs_ref
+@pytest.mark.parametrize("t", ALL_NUMERIC)
+def test_sort_port_matches_reference(t):
+    rng = np.random.default_rng(99 + t)
+    for n in (0, 1, 100, 5000):
+        for null_prob in (0.0, 0.1, 0.5, 1.0):
+            for kw in (dict(), dict(lo=-100 if np.dtype(cols.NP_OF[t]).kind in "if" else 0, hi=100), dict(special=True)):
+                col = rand_column(rng, t, n, null_prob, offset=3, **kw)
+                for order in (0, 1):
+                    a = run_sort("port", col, order)
+                    b = run_sort("reference", col, order)
+                    np.testing.assert_array_equal(a, b)
+
+
+@needs_ref
+@pytest.mark.parametrize("kt", [cols.BOOL, cols.UINT8, cols.INT32, cols.INT64, cols.FLOAT, cols.DOUBLE])
+@pytest.mark.parametrize("at", [cols.INT8, cols.UINT16, cols.INT32, cols.UINT64, cols.INT64, cols.FLOAT, cols.DOUBLE])
+def test_groupby_port_matches_reference(kt, at):
+    rng = np.random.default_rng(5 + 31 * kt + at)
+    for n in (0, 1, 1 << 10, 1 << 12):
+        for null_prob in (0.0, 0.01, 0.5, 1.0):
+            key = rand_column(rng, kt, n, 0.05, lo=0, hi=100, special=(kt in (cols.FLOAT, cols.DOUBLE)))
+            arg = rand_column(rng, at, n, null_prob, special=True)
+            aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT), AggSpec(cols.HASH_COUNT, 1),
+                    AggSpec(cols.HASH_MIN_MAX), AggSpec(cols.HASH_MIN_MAX, 1), AggSpec(cols.HASH_MEAN)]
+            args = [arg] * len(aggs)
+            a = run_groupby("port", [key], aggs, args, want_ids=True)
+            b = run_groupby("reference", [key], aggs, args, want_ids=True)
+            # both are sequential in row order: even float sums must be bit-identical
+            assert_group_equal(a, b, aggs, rtol=0)
+
+
+@needs_ref
+def test_groupby_multi_key_port_matches_reference():
+    rng = np.random.default_rng(11)
+    n = 4096
+    k0 = rand_column(rng, cols.UINT8, n, 0.1, lo=0, hi=3)
+    k1 = rand_column(rng, cols.INT16, n, 0.1, lo=-2, hi=2)
+    k2 = rand_column(rng, cols.BOOL, n, 0.1)
+    arg = rand_column(rng, cols.DOUBLE, n, 0.2)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MIN_MAX), AggSpec(cols.HASH_COUNT)]
+    a = run_groupby("port", [k0, k1, k2], aggs, [arg] * 3, want_ids=True)
+    b = run_groupby("reference", [k0, k1, k2], aggs, [arg] * 3, want_ids=True)
+    assert_group_equal(a, b, aggs, rtol=0)
+
+
+def test_oracle_builds_and_exports():
+    oracle.build()
+    lib, _ = oracle._lib("port")
+    for name in ("oracle_filter", "oracle_filter_count", "oracle_sort_indices", "oracle_groupby", "oracle_version"):
+        assert hasattr(lib, name)
