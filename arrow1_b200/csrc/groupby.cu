@@ -1,0 +1,1275 @@
+// Grouper + grouped aggregates: open-addressing hash aggregation.
+// Replaces GrouperImpl::Consume / GetUniques, GroupedCountImpl, GroupedSumImpl, GroupedMinMaxImpl
+// and the GroupBy driver (reference compute/kernels/hash_aggregate.cc:313-437, 466-768, 890-966);
+// hash_mean is MeanImpl::Finalize (aggregate_basic_internal.h:99-109) over the sum state.
+//
+//   key      the reference's row-major encoding [null byte][raw bytes, zero if null] per key column
+//            (hash_aggregate.cc:48-196) is never materialised: the same information is packed into
+//            one 64-bit register key = value bits | one null flag per column (floats by bit
+//            pattern, so -0.0 != 0.0 and NaNs group by payload, hash_aggregate_test.cc:280-289).
+//   table    slots of `stride` bytes {key, first_row, per-aggregate state}; linear probing; keys
+//            claimed with 64-bit atomicCAS.  Two extra slots hold the null key and the key equal to
+//            the EMPTY sentinel when a single 64-bit key column leaves no spare bit.
+//   order    group ids are first-occurrence order (hash_aggregate.cc:391-403): every slot keeps
+//            min(row_base + i); finalize ranks the occupied slots by it with the radix sort.
+//   kernels  gb_consume_kernel<false>  rows -> global table, global atomics (high cardinality)
+//            gb_consume_kernel<true>   rows -> per-CTA shared-memory table (shared atomics), flushed
+//                                      once per CTA into the global table (low cardinality)
+//            gb_rehash / gb_merge / gb_collect / gb_emit / gb_dense_consume
+// Algorithmic HBM bytes per row: every key and argument column read once:
+// C3 12.125 B/row, C4 16 B/row.
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int kMaxKeys = 4;
+constexpr int kMaxCols = 8;
+constexpr int kMaxAggs = 12;
+constexpr uint64_t kEmpty = ~uint64_t(0);
+constexpr uint32_t kNoId = 0xFFFFFFFFu;
+constexpr int kMaxProbe = 256;
+constexpr int kLocalProbe = 24;
+
+enum Domain { kSigned = 0, kUnsigned = 1, kFloat = 2 };
+enum Mode { kModeFused = 0, kModeInsert = 1, kModeLookup = 2 };
+
+struct GbKey {
+  const void* data;  // shifted by the element offset (non-bool)
+  BitmapRef bits;    // bool key data
+  BitmapRef vv;
+  int32_t type, nbits, shift, pad;
+};
+struct GbCol {
+  const void* data;  // shifted
+  BitmapRef bits;    // bool argument (hash_count only)
+  BitmapRef vv;
+  int32_t type, pad;
+};
+struct GbAgg {
+  int32_t kind, dom, option, off, col, arg_type;
+};
+struct GbSchema {
+  GbAgg aggs[kMaxAggs];
+  int32_t n_aggs;
+  int32_t n_keys;
+  int32_t null_shift;   // bit position of the first null flag, or -1 (single 64-bit key)
+  int32_t stride;       // global slot stride (bytes, multiple of 16)
+  int32_t lstride;      // shared slot stride (bytes, multiple of 8)
+  int32_t key_bits[kMaxKeys], key_shift[kMaxKeys], key_type[kMaxKeys];
+};
+struct GbTable {
+  char* slots;       // (cap + 2) slots
+  uint64_t cap;      // power of two
+};
+struct GbArgs {
+  GbSchema s;
+  GbKey keys[kMaxKeys];
+  GbCol cols[kMaxCols];
+  int32_t n_cols;
+  int32_t mode;
+  int64_t n;
+  uint64_t row_base;
+  GbTable t;
+  uint32_t* counters;        // [0] groups, [1] deferred rows, [2] claimed slots (grouper), [3] error
+  const uint32_t* defer_in;  // nullable: only rows whose bit is set are processed
+  uint32_t* defer_out;       // rows that found no slot
+  uint32_t* claimed;         // grouper: newly claimed slot indices
+  uint32_t* slot_ids;        // grouper: dense id per slot
+  uint32_t* out_ids;         // grouper lookup output
+  int32_t local_slots;       // shared-memory table size (power of two), 0 = none
+  int32_t rows_per_block;
+};
+
+__device__ __forceinline__ uint64_t mix64(uint64_t k) {
+  k ^= k >> 33;
+  k *= 0xff51afd7ed558ccdull;
+  k ^= k >> 33;
+  k *= 0xc4ceb9fe1a85ec53ull;
+  k ^= k >> 33;
+  return k;
+}
+
+// ---- order-preserving encodings for min/max -------------------------------------------------
+__device__ __forceinline__ uint64_t ord_f64(double v) {  // v is not NaN; +-0 canonicalised
+  uint64_t b = __double_as_longlong(v);
+  if ((b << 1) == 0) b = 0;
+  return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double unord_f64(uint64_t o) {
+  uint64_t b = (o >> 63) ? (o & 0x7FFFFFFFFFFFFFFFull) : ~o;
+  return __longlong_as_double(b);
+}
+
+struct Val {
+  uint64_t bits;  // signed: sign-extended, unsigned: zero-extended, float: f64 bits (f32 widened)
+  bool valid;
+};
+
+__device__ __forceinline__ Val load_val(const GbCol& c, int64_t row) {
+  Val v;
+  v.valid = bitmap_get(c.vv, row);
+  v.bits = 0;
+  switch (c.type) {
+    case B200_BOOL: v.bits = bitmap_get(c.bits, row); break;
+    case B200_UINT8: v.bits = reinterpret_cast<const uint8_t*>(c.data)[row]; break;
+    case B200_INT8: v.bits = uint64_t(int64_t(reinterpret_cast<const int8_t*>(c.data)[row])); break;
+    case B200_UINT16: v.bits = reinterpret_cast<const uint16_t*>(c.data)[row]; break;
+    case B200_INT16: v.bits = uint64_t(int64_t(reinterpret_cast<const int16_t*>(c.data)[row])); break;
+    case B200_UINT32: v.bits = reinterpret_cast<const uint32_t*>(c.data)[row]; break;
+    case B200_INT32: v.bits = uint64_t(int64_t(reinterpret_cast<const int32_t*>(c.data)[row])); break;
+    case B200_FLOAT: v.bits = __double_as_longlong(double(reinterpret_cast<const float*>(c.data)[row])); break;
+    default: v.bits = reinterpret_cast<const uint64_t*>(c.data)[row]; break;  // 64-bit types
+  }
+  return v;
+}
+
+// packed key of a row; *special = 1 (null single-64-bit key) or 2 (key == EMPTY sentinel)
+__device__ __forceinline__ uint64_t load_key(const GbArgs& a, int64_t row, int* special) {
+  uint64_t key = 0;
+  *special = 0;
+#pragma unroll
+  for (int k = 0; k < kMaxKeys; ++k) {
+    if (k < a.s.n_keys) {
+      const GbKey& c = a.keys[k];
+      const bool valid = bitmap_get(c.vv, row);
+      if (!valid) {
+        if (a.s.null_shift >= 0) key |= uint64_t(1) << (a.s.null_shift + k);
+        else *special = 1;
+        continue;
+      }
+      uint64_t v;
+      switch (c.nbits) {
+        case 1: v = bitmap_get(c.bits, row); break;
+        case 8: v = reinterpret_cast<const uint8_t*>(c.data)[row]; break;
+        case 16: v = reinterpret_cast<const uint16_t*>(c.data)[row]; break;
+        case 32: v = reinterpret_cast<const uint32_t*>(c.data)[row]; break;
+        default: v = reinterpret_cast<const uint64_t*>(c.data)[row]; break;
+      }
+      key |= v << c.shift;
+    }
+  }
+  if (a.s.null_shift < 0 && *special == 0 && key == kEmpty) *special = 2;
+  return key;
+}
+
+// ---- slot state -----------------------------------------------------------------------------
+// COUNT: {u64 count}  SUM/MEAN: {u64|f64 sum, u64 count}
+// MIN_MAX: {u64 min_ord, u64 max_ord, u64 zero_first, u64 flags(bit0 has_values, bit1 has_nulls)}
+__host__ __device__ inline int state_bytes(int kind) {
+  return kind == B200_HASH_COUNT ? 8 : (kind == B200_HASH_MIN_MAX ? 32 : 16);
+}
+
+__device__ __forceinline__ void init_slot(char* slot, const GbSchema& s) {
+  uint64_t* w = reinterpret_cast<uint64_t*>(slot);
+  w[0] = kEmpty;
+  w[1] = ~uint64_t(0);
+  for (int j = 0; j < s.n_aggs; ++j) {
+    uint64_t* st = reinterpret_cast<uint64_t*>(slot + s.aggs[j].off);
+    if (s.aggs[j].kind == B200_HASH_MIN_MAX) {
+      st[0] = ~uint64_t(0);
+      st[1] = 0;
+      st[2] = ~uint64_t(0);
+      st[3] = 0;
+    } else {
+      st[0] = 0;
+      if (s.aggs[j].kind != B200_HASH_COUNT) st[1] = 0;
+    }
+  }
+}
+
+__device__ __forceinline__ void atomic_min_checked(uint64_t* p, uint64_t v) {
+  // a stale read is always >= the true value (it only decreases), so skipping is safe
+  if (v < *reinterpret_cast<volatile uint64_t*>(p)) atomicMin(reinterpret_cast<unsigned long long*>(p), (unsigned long long)v);
+}
+__device__ __forceinline__ void atomic_max_checked(uint64_t* p, uint64_t v) {
+  if (v > *reinterpret_cast<volatile uint64_t*>(p)) atomicMax(reinterpret_cast<unsigned long long*>(p), (unsigned long long)v);
+}
+__device__ __forceinline__ void atomic_or_checked(uint64_t* p, uint64_t v) {
+  if ((*reinterpret_cast<volatile uint64_t*>(p) & v) != v) atomicOr(reinterpret_cast<unsigned long long*>(p), (unsigned long long)v);
+}
+
+// one row into one aggregate's state
+__device__ __forceinline__ void accumulate(char* slot, const GbAgg& g, const Val& v, uint64_t row) {
+  uint64_t* st = reinterpret_cast<uint64_t*>(slot + g.off);
+  switch (g.kind) {
+    case B200_HASH_COUNT:  // hash_aggregate.cc:474-505
+      if (g.option ? !v.valid : v.valid) atomicAdd(reinterpret_cast<unsigned long long*>(st), 1ull);
+      break;
+    case B200_HASH_SUM:
+    case B200_HASH_MEAN:   // hash_aggregate.cc:533-545
+      if (v.valid) {
+        if (g.dom == kFloat) atomicAdd(reinterpret_cast<double*>(st), __longlong_as_double(v.bits));
+        else atomicAdd(reinterpret_cast<unsigned long long*>(st), (unsigned long long)v.bits);
+        atomicAdd(reinterpret_cast<unsigned long long*>(st + 1), 1ull);
+      }
+      break;
+    default:               // hash_aggregate.cc:663-677
+      if (!v.valid) {
+        atomic_or_checked(st + 3, 2);
+        break;
+      }
+      atomic_or_checked(st + 3, 1);
+      uint64_t o;
+      if (g.dom == kFloat) {
+        const double d = __longlong_as_double(v.bits);
+        if (d != d) break;  // std::max/min never pick a NaN, but has_values is set
+        // +-0.0 ties: the earlier row's sign wins (std::max(cur, v) keeps cur when equal)
+        if (d == 0.0) atomic_min_checked(st + 2, (row << 1) | (v.bits >> 63));
+        o = ord_f64(d);
+      } else if (g.dom == kSigned) {
+        o = v.bits ^ 0x8000000000000000ull;
+      } else {
+        o = v.bits;
+      }
+      atomic_min_checked(st + 0, o);
+      atomic_max_checked(st + 1, o);
+      break;
+  }
+}
+
+// fold a source slot's state (plain memory) into a destination slot (atomics)
+__device__ __forceinline__ void merge_state(char* dst, const char* src, const GbSchema& s) {
+  const uint64_t* sw = reinterpret_cast<const uint64_t*>(src);
+  atomic_min_checked(reinterpret_cast<uint64_t*>(dst) + 1, sw[1]);
+  for (int j = 0; j < s.n_aggs; ++j) {
+    const GbAgg& g = s.aggs[j];
+    uint64_t* d = reinterpret_cast<uint64_t*>(dst + g.off);
+    const uint64_t* c = reinterpret_cast<const uint64_t*>(src + g.off);
+    switch (g.kind) {
+      case B200_HASH_COUNT:
+        if (c[0]) atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)c[0]);
+        break;
+      case B200_HASH_SUM:
+      case B200_HASH_MEAN:
+        if (c[1]) {
+          if (g.dom == kFloat) atomicAdd(reinterpret_cast<double*>(d), __longlong_as_double(c[0]));
+          else atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)c[0]);
+          atomicAdd(reinterpret_cast<unsigned long long*>(d + 1), (unsigned long long)c[1]);
+        }
+        break;
+      default:
+        atomic_min_checked(d + 0, c[0]);
+        atomic_max_checked(d + 1, c[1]);
+        atomic_min_checked(d + 2, c[2]);
+        if (c[3]) atomic_or_checked(d + 3, c[3]);
+        break;
+    }
+  }
+}
+
+// find or claim the global slot of `key`; nullptr when the probe limit is hit (table too full)
+__device__ __forceinline__ char* global_slot(const GbTable& t, int stride, uint64_t key, int special,
+                                             bool insert, bool* claimed_new, uint64_t* slot_index) {
+  *claimed_new = false;
+  if (special) {
+    const uint64_t idx = t.cap + (special - 1);
+    char* slot = t.slots + idx * stride;
+    uint64_t* kp = reinterpret_cast<uint64_t*>(slot);
+    *slot_index = idx;
+    // occupancy marker of a special slot: key word 0 (EMPTY = unused)
+    if (*reinterpret_cast<volatile uint64_t*>(kp) == kEmpty) {
+      if (!insert) return nullptr;
+      if (atomicCAS(reinterpret_cast<unsigned long long*>(kp), (unsigned long long)kEmpty, 0ull) == kEmpty) *claimed_new = true;
+    }
+    return slot;
+  }
+  uint64_t idx = mix64(key) & (t.cap - 1);
+  for (int probe = 0; probe < kMaxProbe; ++probe) {
+    char* slot = t.slots + idx * stride;
+    uint64_t* kp = reinterpret_cast<uint64_t*>(slot);
+    uint64_t cur = *reinterpret_cast<volatile uint64_t*>(kp);
+    if (cur == kEmpty) {
+      if (!insert) return nullptr;
+      cur = atomicCAS(reinterpret_cast<unsigned long long*>(kp), (unsigned long long)kEmpty, (unsigned long long)key);
+      if (cur == kEmpty) {
+        *claimed_new = true;
+        *slot_index = idx;
+        return slot;
+      }
+    }
+    if (cur == key) {
+      *slot_index = idx;
+      return slot;
+    }
+    idx = (idx + 1) & (t.cap - 1);
+  }
+  return nullptr;
+}
+
+__global__ void gb_init_kernel(GbSchema s, char* slots, uint64_t n_slots, int stride) {
+  const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n_slots) init_slot(slots + i * stride, s);
+}
+
+// ---- the consume kernel ---------------------------------------------------------------------
+template <bool kLocal>
+__global__ void __launch_bounds__(kLocal ? 1024 : 256) gb_consume_kernel(const __grid_constant__ GbArgs a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ uint32_t s_new_groups;
+  __shared__ uint32_t s_deferred;
+  char* ltab = reinterpret_cast<char*>(smem);
+  const int lstride = a.s.lstride;
+  const uint32_t lmask = uint32_t(a.local_slots - 1);
+  if (threadIdx.x == 0) {
+    s_new_groups = 0;
+    s_deferred = 0;
+  }
+  if (kLocal) {
+    for (int i = threadIdx.x; i < a.local_slots; i += blockDim.x) init_slot(ltab + i * lstride, a.s);
+  }
+  __syncthreads();
+
+  const int64_t begin = int64_t(blockIdx.x) * a.rows_per_block;
+  const int64_t end = min(a.n, begin + a.rows_per_block);
+  for (int64_t row = begin + threadIdx.x; row < end; row += blockDim.x) {
+    if (a.defer_in && !((a.defer_in[row >> 5] >> (row & 31)) & 1u)) continue;
+    int special;
+    const uint64_t key = load_key(a, row, &special);
+    const uint64_t grow = a.row_base + uint64_t(row);
+    char* slot = nullptr;
+    bool local_hit = false;
+    if (kLocal && !special) {
+      uint32_t idx = uint32_t(mix64(key) >> 20) & lmask;
+      for (int probe = 0; probe < kLocalProbe; ++probe) {
+        char* ls = ltab + idx * lstride;
+        uint64_t* kp = reinterpret_cast<uint64_t*>(ls);
+        uint64_t cur = *reinterpret_cast<volatile uint64_t*>(kp);
+        if (cur == kEmpty) cur = atomicCAS(reinterpret_cast<unsigned long long*>(kp), (unsigned long long)kEmpty, (unsigned long long)key);
+        if (cur == kEmpty || cur == key) {
+          slot = ls;
+          local_hit = true;
+          break;
+        }
+        idx = (idx + 1) & lmask;
+      }
+    }
+    uint64_t slot_index = 0;
+    if (!local_hit) {
+      bool claimed;
+      slot = global_slot(a.t, a.s.stride, key, special, a.mode != kModeLookup, &claimed, &slot_index);
+      if (claimed) {
+        atomicAdd(&s_new_groups, 1u);
+        if (a.claimed) a.claimed[atomicAdd(a.counters + 2, 1u)] = uint32_t(slot_index);
+      }
+      if (!slot) {
+        if (a.mode == kModeLookup) {
+          atomicExch(a.counters + 3, 1u);  // every key was inserted by the pass before: cannot happen
+        } else {
+          atomicOr(a.defer_out + (row >> 5), 1u << (row & 31));
+          atomicAdd(&s_deferred, 1u);
+        }
+        continue;
+      }
+    }
+    if (a.mode == kModeLookup) {
+      a.out_ids[row] = a.slot_ids[slot_index];
+      continue;
+    }
+    atomic_min_checked(reinterpret_cast<uint64_t*>(slot) + 1, grow);
+    if (a.mode == kModeInsert) continue;
+    // each distinct argument column is loaded once and feeds all of its aggregates
+#pragma unroll
+    for (int c = 0; c < kMaxCols; ++c) {
+      if (c < a.n_cols) {
+        const Val v = load_val(a.cols[c], row);
+        for (int j = 0; j < a.s.n_aggs; ++j)
+          if (a.s.aggs[j].col == c) accumulate(slot, a.s.aggs[j], v, grow);
+      }
+    }
+  }
+  __syncthreads();
+  if (kLocal) {
+    // flush the CTA's partial aggregates; the host sized the global table so this cannot fail
+    for (int i = threadIdx.x; i < a.local_slots; i += blockDim.x) {
+      const char* ls = ltab + i * lstride;
+      const uint64_t key = *reinterpret_cast<const uint64_t*>(ls);
+      if (key == kEmpty) continue;
+      bool claimed;
+      uint64_t slot_index;
+      char* gs = global_slot(a.t, a.s.stride, key, 0, true, &claimed, &slot_index);
+      if (!gs) {
+        atomicExch(a.counters + 3, 2u);
+        continue;
+      }
+      if (claimed) {
+        atomicAdd(&s_new_groups, 1u);
+        if (a.claimed) a.claimed[atomicAdd(a.counters + 2, 1u)] = uint32_t(slot_index);
+      }
+      if (a.mode == kModeInsert) atomic_min_checked(reinterpret_cast<uint64_t*>(gs) + 1, reinterpret_cast<const uint64_t*>(ls)[1]);
+      else merge_state(gs, ls, a.s);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    if (s_new_groups) atomicAdd(a.counters + 0, s_new_groups);
+    if (s_deferred) atomicAdd(a.counters + 1, s_deferred);
+  }
+}
+
+// ---- table maintenance ----------------------------------------------------------------------
+// moves every occupied slot of `src` (stride bytes each) into table `dst`; when `merge` the states
+// are folded (duplicates allowed), otherwise copied (rehash: keys are unique)
+__global__ void gb_move_kernel(GbSchema s, const char* src, uint64_t n_src, int src_stride, uint64_t src_cap,
+                               GbTable dst, int merge, uint32_t* counters) {
+  const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n_src) return;
+  const char* ss = src + i * src_stride;
+  const uint64_t key = *reinterpret_cast<const uint64_t*>(ss);
+  int special = 0;
+  if (src_cap != 0 && i >= src_cap) {  // special slots of a source table
+    if (key == kEmpty) return;
+    special = int(i - src_cap) + 1;
+  } else if (key == kEmpty) {
+    return;
+  }
+  // flat exports carry the special tag in first_row's place? no: they carry it in the key order —
+  // exports append the two special slots last and pass src_cap = number of ordinary slots
+  bool claimed;
+  uint64_t slot_index;
+  char* ds = global_slot(dst, s.stride, key, special, true, &claimed, &slot_index);
+  if (!ds) {
+    atomicExch(counters + 3, 3u);
+    return;
+  }
+  if (claimed) atomicAdd(counters + 0, 1u);
+  if (merge) {
+    merge_state(ds, ss, s);
+  } else {
+    const uint64_t* sw = reinterpret_cast<const uint64_t*>(ss);
+    uint64_t* dw = reinterpret_cast<uint64_t*>(ds);
+    for (int w = 1; w < s.stride / 8; ++w) dw[w] = sw[w];
+  }
+}
+
+// occupied slots -> (first_row, slot index) pairs, unordered
+__global__ void gb_collect_kernel(GbTable t, int stride, uint64_t* first_rows, uint64_t* slot_idx, uint32_t* counter,
+                                  const uint32_t* slot_ids, int only_unassigned) {
+  const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= t.cap + 2) return;
+  const uint64_t* w = reinterpret_cast<const uint64_t*>(t.slots + i * stride);
+  if (w[0] == kEmpty) return;
+  if (only_unassigned && slot_ids[i] != kNoId) return;
+  const uint32_t pos = atomicAdd(counter, 1u);
+  first_rows[pos] = w[1];
+  slot_idx[pos] = i;
+}
+
+// grouper: first_row of the newly claimed slots
+__global__ void gb_claimed_rows_kernel(GbTable t, int stride, const uint32_t* claimed, uint32_t n, uint64_t* first_rows,
+                                       uint64_t* slot_idx) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t s = claimed[i];
+  first_rows[i] = reinterpret_cast<const uint64_t*>(t.slots + s * stride)[1];
+  slot_idx[i] = s;
+}
+
+__global__ void gb_assign_ids_kernel(const uint64_t* sorted_slots, uint32_t n, uint32_t base, uint32_t* slot_ids) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) slot_ids[sorted_slots[i]] = base + i;
+}
+
+__global__ void gb_fill_u32_kernel(uint32_t* p, uint64_t n, uint32_t v) {
+  const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+// export: occupied slots copied densely (ordinary slots in any order; special slots tagged by key
+// words that cannot occur otherwise are re-detected on import through `special_tags`)
+__global__ void gb_export_kernel(GbTable t, int stride, const uint64_t* slot_idx, uint32_t n, char* out, uint8_t* tags) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t s = slot_idx[i];
+  const uint64_t* sw = reinterpret_cast<const uint64_t*>(t.slots + s * stride);
+  uint64_t* dw = reinterpret_cast<uint64_t*>(out + uint64_t(i) * stride);
+  for (int w = 0; w < stride / 8; ++w) dw[w] = sw[w];
+  // the trailing 8 bytes of slot 0..: first word stays the key; special slots are tagged in-band by
+  // storing their kind in the (otherwise unused) padding word at the end of the slot
+  (void)tags;
+  if (s >= t.cap) dw[stride / 8 - 1] = 0xB200000000000000ull | (s - t.cap + 1);
+}
+
+__global__ void gb_import_kernel(GbSchema s, const char* src, uint32_t n, GbTable dst, uint32_t* counters) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const char* ss = src + uint64_t(i) * s.stride;
+  const uint64_t* sw = reinterpret_cast<const uint64_t*>(ss);
+  int special = 0;
+  const uint64_t tag = sw[s.stride / 8 - 1];
+  if ((tag >> 56) == 0xB2) special = int(tag & 3);
+  bool claimed;
+  uint64_t slot_index;
+  char* ds = global_slot(dst, s.stride, sw[0], special, true, &claimed, &slot_index);
+  if (!ds) {
+    atomicExch(counters + 3, 4u);
+    return;
+  }
+  if (claimed) atomicAdd(counters + 0, 1u);
+  merge_state(ds, ss, s);
+}
+
+// ---- finalize -------------------------------------------------------------------------------
+struct EmitOut {
+  void* data;
+  uint32_t* validity;  // nullable
+  int32_t type;
+};
+struct EmitArgs {
+  GbSchema s;
+  GbTable t;
+  const uint64_t* order;  // slot index per output rank (nullptr: dense mode, slot = rank)
+  uint32_t n_groups;
+  EmitOut keys[kMaxKeys];
+  EmitOut aggs[2 * kMaxAggs];
+  uint32_t* null_counts;  // [kMaxKeys + 2*kMaxAggs]
+};
+
+__device__ __forceinline__ void store_typed(void* base, int type, uint32_t i, uint64_t bits_signed_or_unsigned, double f) {
+  switch (type) {
+    case B200_UINT8: case B200_INT8: reinterpret_cast<uint8_t*>(base)[i] = uint8_t(bits_signed_or_unsigned); break;
+    case B200_UINT16: case B200_INT16: reinterpret_cast<uint16_t*>(base)[i] = uint16_t(bits_signed_or_unsigned); break;
+    case B200_UINT32: case B200_INT32: reinterpret_cast<uint32_t*>(base)[i] = uint32_t(bits_signed_or_unsigned); break;
+    case B200_FLOAT: reinterpret_cast<float*>(base)[i] = float(f); break;
+    case B200_DOUBLE: reinterpret_cast<double*>(base)[i] = f; break;
+    default: reinterpret_cast<uint64_t*>(base)[i] = bits_signed_or_unsigned; break;
+  }
+}
+
+__device__ __forceinline__ uint64_t anti_extreme_bits(int type, bool for_min) {
+  // Extrema / numeric_limits (hash_aggregate.cc:627-640): min starts at max(), max at min()
+  switch (type) {
+    case B200_INT8: return for_min ? 0x7Full : 0x80ull;
+    case B200_INT16: return for_min ? 0x7FFFull : 0x8000ull;
+    case B200_INT32: return for_min ? 0x7FFFFFFFull : 0x80000000ull;
+    case B200_INT64: return for_min ? 0x7FFFFFFFFFFFFFFFull : 0x8000000000000000ull;
+    default: return for_min ? ~0ull : 0ull;  // unsigned
+  }
+}
+
+__global__ void gb_emit_kernel(const __grid_constant__ EmitArgs e) {
+  const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const bool in = r < e.n_groups;
+  const uint64_t slot_index = in ? (e.order ? e.order[r] : r) : 0;
+  const char* slot = e.t.slots + slot_index * e.s.stride;
+  const uint64_t* w = reinterpret_cast<const uint64_t*>(slot);
+  const uint64_t key = w[0];
+  const bool special_null = e.order && e.s.null_shift < 0 && slot_index == e.t.cap;
+  const bool special_full = e.order && e.s.null_shift < 0 && slot_index == e.t.cap + 1;
+  // keys: GetUniques / Decode (hash_aggregate.cc:412-429, 65-94, 174-192)
+  for (int k = 0; k < e.s.n_keys; ++k) {
+    const EmitOut& o = e.keys[k];
+    if (!o.data) continue;
+    bool valid = true;
+    uint64_t v = 0;
+    if (in) {
+      if (e.s.null_shift >= 0) valid = !((key >> (e.s.null_shift + k)) & 1ull);
+      else valid = !special_null;
+      const int nb = e.s.key_bits[k];
+      if (valid) {
+        const uint64_t kk = special_full ? kEmpty : key;
+        v = nb == 64 ? kk : ((kk >> e.s.key_shift[k]) & ((uint64_t(1) << nb) - 1));
+      }
+    }
+    if (e.s.key_type[k] == B200_BOOL) {
+      const unsigned word = __ballot_sync(0xffffffffu, in && valid && v);
+      if (lane == 0 && (r >> 5) <= ((e.n_groups - 1) >> 5)) reinterpret_cast<uint32_t*>(o.data)[r >> 5] = word;
+    } else if (in) {
+      store_typed(o.data, e.s.key_type[k], r, v, 0.0);
+    }
+    const unsigned vw = __ballot_sync(0xffffffffu, in && valid);
+    const unsigned inw = __ballot_sync(0xffffffffu, in);
+    if (lane == 0 && inw) {
+      if (o.validity) o.validity[r >> 5] = vw;
+      const int nulls = __popc(inw & ~vw);
+      if (nulls) atomicAdd(e.null_counts + k, uint32_t(nulls));
+    }
+  }
+  int oi = 0;
+  for (int j = 0; j < e.s.n_aggs; ++j) {
+    const GbAgg& g = e.s.aggs[j];
+    const uint64_t* st = reinterpret_cast<const uint64_t*>(slot + g.off);
+    bool valid = true;
+    if (g.kind == B200_HASH_MIN_MAX) {
+      const EmitOut& omin = e.aggs[oi];
+      const EmitOut& omax = e.aggs[oi + 1];
+      if (in) {
+        const uint64_t flags = st[3];
+        const bool has_values = flags & 1, has_nulls = flags & 2;
+        valid = has_values && !(g.option == 1 && has_nulls);  // hash_aggregate.cc:722-732
+        if (g.dom == kFloat) {
+          double mn = __longlong_as_double(0x7FF0000000000000ull), mx = __longlong_as_double(0xFFF0000000000000ull);
+          if (st[0] != ~uint64_t(0)) {  // at least one non-NaN value
+            mn = unord_f64(st[0]);
+            mx = unord_f64(st[1]);
+            if (st[2] != ~uint64_t(0)) {  // a zero was seen: the earliest zero row decides the sign
+              const double z = (st[2] & 1ull) ? -0.0 : 0.0;
+              if (mn == 0.0) mn = z;
+              if (mx == 0.0) mx = z;
+            }
+          }
+          store_typed(omin.data, g.arg_type, r, 0, mn);
+          store_typed(omax.data, g.arg_type, r, 0, mx);
+        } else {
+          uint64_t mn = anti_extreme_bits(g.arg_type, true), mx = anti_extreme_bits(g.arg_type, false);
+          if (has_values) {
+            mn = g.dom == kSigned ? (st[0] ^ 0x8000000000000000ull) : st[0];
+            mx = g.dom == kSigned ? (st[1] ^ 0x8000000000000000ull) : st[1];
+          }
+          store_typed(omin.data, g.arg_type, r, mn, 0.0);
+          store_typed(omax.data, g.arg_type, r, mx, 0.0);
+        }
+      }
+      const unsigned vw = __ballot_sync(0xffffffffu, in && valid);
+      const unsigned inw = __ballot_sync(0xffffffffu, in);
+      if (lane == 0 && inw) {
+        if (omin.validity) omin.validity[r >> 5] = vw;
+        if (omax.validity && omax.validity != omin.validity) omax.validity[r >> 5] = vw;
+        const int nulls = __popc(inw & ~vw);
+        if (nulls) {
+          atomicAdd(e.null_counts + kMaxKeys + oi, uint32_t(nulls));
+          atomicAdd(e.null_counts + kMaxKeys + oi + 1, uint32_t(nulls));
+        }
+      }
+      oi += 2;
+      continue;
+    }
+    const EmitOut& o = e.aggs[oi];
+    if (in) {
+      if (g.kind == B200_HASH_COUNT) {
+        reinterpret_cast<int64_t*>(o.data)[r] = int64_t(st[0]);
+      } else if (g.kind == B200_HASH_SUM) {
+        valid = st[1] > 0;  // hash_aggregate.cc:595-605
+        reinterpret_cast<uint64_t*>(o.data)[r] = st[0];
+      } else {              // MeanImpl::Finalize: static_cast<double>(sum) / count
+        valid = st[1] > 0;
+        double s = g.dom == kFloat ? __longlong_as_double(st[0])
+                                   : (g.dom == kSigned ? double(int64_t(st[0])) : double(st[0]));
+        reinterpret_cast<double*>(o.data)[r] = valid ? s / double(st[1]) : 0.0;
+      }
+    }
+    const unsigned vw = __ballot_sync(0xffffffffu, in && valid);
+    const unsigned inw = __ballot_sync(0xffffffffu, in);
+    if (lane == 0 && inw) {
+      if (o.validity) o.validity[r >> 5] = vw;
+      const int nulls = __popc(inw & ~vw);
+      if (nulls) atomicAdd(e.null_counts + kMaxKeys + oi, uint32_t(nulls));
+    }
+    oi += 1;
+  }
+}
+
+// ---- dense (group-id indexed) accumulation: HashAggregateKernel::consume ----------------------
+__global__ void gb_dense_consume_kernel(GbSchema s, int agg_index, GbCol col, const uint32_t* ids, int64_t n,
+                                        char* dense, uint32_t num_groups, uint32_t* counters) {
+  const int64_t row = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (row >= n) return;
+  const uint32_t g = ids[row];
+  if (g >= num_groups) {
+    atomicExch(counters + 3, 5u);
+    return;
+  }
+  const Val v = load_val(col, row);
+  accumulate(dense + uint64_t(g) * s.stride, s.aggs[agg_index], v, uint64_t(row));
+}
+
+}  // namespace
+
+// ===============================================================================================
+struct b200_groupby {
+  b200_ctx* ctx = nullptr;
+  GbSchema schema;
+  std::vector<b200_agg_spec> specs;
+  GbTable table{nullptr, 0};
+  uint32_t* counters = nullptr;  // device, 8 words
+  uint32_t groups = 0;           // host view, refreshed at every sync point
+  uint64_t expected = 0;         // caller's cardinality hint
+  // grouper state
+  uint32_t* slot_ids = nullptr;
+  uint64_t slot_ids_cap = 0;
+  uint32_t ids_assigned = 0;
+  // dense mode (b200_hash_agg_consume)
+  char* dense = nullptr;
+  uint32_t dense_groups = 0;
+  uint32_t dense_cap = 0;
+  bool dense_used = false;
+  uint64_t dense_rows = 0;
+  // scratch owned by the handle
+  void* tmp = nullptr;
+  size_t tmp_bytes = 0;
+};
+
+namespace {
+
+int domain_of(int t) {
+  switch (t) {
+    case B200_FLOAT: case B200_DOUBLE: return kFloat;
+    case B200_INT8: case B200_INT16: case B200_INT32: case B200_INT64: return kSigned;
+    default: return kUnsigned;
+  }
+}
+
+int gb_reserve_tmp(b200_groupby* gb, size_t bytes) {
+  b200_ctx* ctx = gb->ctx;
+  if (bytes <= gb->tmp_bytes) return B200_OK;
+  if (gb->tmp) {
+    B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    B200_CUDA(ctx, cudaFree(gb->tmp));
+    gb->tmp = nullptr;
+    gb->tmp_bytes = 0;
+  }
+  bytes = b200_align_up(bytes, 1 << 20);
+  B200_CUDA(ctx, cudaMalloc(&gb->tmp, bytes));
+  gb->tmp_bytes = bytes;
+  return B200_OK;
+}
+
+int alloc_table(b200_groupby* gb, uint64_t cap, GbTable* out) {
+  b200_ctx* ctx = gb->ctx;
+  GbTable t;
+  t.cap = cap;
+  const uint64_t n_slots = cap + 2;
+  B200_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&t.slots), n_slots * gb->schema.stride));
+  gb_init_kernel<<<(unsigned)((n_slots + 255) / 256), 256, 0, ctx->stream>>>(gb->schema, t.slots, n_slots, gb->schema.stride);
+  B200_LAUNCHED(ctx);
+  *out = t;
+  return B200_OK;
+}
+
+uint64_t pow2_at_least(uint64_t x) {
+  uint64_t p = 1024;
+  while (p < x) p <<= 1;
+  return p;
+}
+
+int read_counters(b200_groupby* gb, uint32_t out[4]) {
+  b200_ctx* ctx = gb->ctx;
+  B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 16, gb->counters, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  memcpy(out, ctx->host_words + 16, 4 * sizeof(uint32_t));
+  gb->groups = out[0];
+  if (out[3] != 0) return b200_fail(ctx, B200_UNKNOWN_ERROR, "groupby: internal table error %u", out[3]);
+  return B200_OK;
+}
+
+// grows the table to at least `min_cap` slots, re-inserting every group
+int grow_table(b200_groupby* gb, uint64_t min_cap) {
+  b200_ctx* ctx = gb->ctx;
+  const uint64_t new_cap = pow2_at_least(min_cap);
+  if (new_cap <= gb->table.cap) return B200_OK;
+  GbTable nt;
+  B200_RETURN_NOT_OK(alloc_table(gb, new_cap, &nt));
+  // group counter is rebuilt by the move
+  B200_CUDA(ctx, cudaMemsetAsync(gb->counters, 0, sizeof(uint32_t), ctx->stream));
+  const uint64_t n_src = gb->table.cap + 2;
+  gb_move_kernel<<<(unsigned)((n_src + 255) / 256), 256, 0, ctx->stream>>>(gb->schema, gb->table.slots, n_src,
+                                                                           gb->schema.stride, gb->table.cap, nt, 0,
+                                                                           gb->counters);
+  B200_LAUNCHED(ctx);
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  B200_CUDA(ctx, cudaFree(gb->table.slots));
+  gb->table = nt;
+  // slot ids are positional: the grouper re-derives them after a rehash
+  if (gb->slot_ids) {
+    B200_CUDA(ctx, cudaFree(gb->slot_ids));
+    gb->slot_ids = nullptr;
+    gb->slot_ids_cap = 0;
+    gb->ids_assigned = 0;
+  }
+  return B200_OK;
+}
+
+int fill_keys(b200_groupby* gb, const b200_col* keys, GbArgs* a) {
+  b200_ctx* ctx = gb->ctx;
+  const int64_t n = keys[0].length;
+  for (int k = 0; k < gb->schema.n_keys; ++k) {
+    const b200_col& c = keys[k];
+    if (c.type != gb->schema.key_type[k]) return b200_fail(ctx, B200_TYPE_ERROR, "groupby: key %d has type %d, expected %d", k, c.type, gb->schema.key_type[k]);
+    if (c.length != n) return b200_fail(ctx, B200_INVALID, "Array arguments must all be the same length");
+    if (n > 0 && !c.data) return b200_fail(ctx, B200_INVALID, "groupby: key %d has no data buffer", k);
+    GbKey& g = a->keys[k];
+    const int bits = gb->schema.key_bits[k];
+    g.type = c.type;
+    g.nbits = bits;
+    g.shift = gb->schema.key_shift[k];
+    g.data = bits >= 8 ? reinterpret_cast<const char*>(c.data) + c.offset * (bits / 8) : nullptr;
+    g.bits = make_bitmap_ref(bits == 1 ? c.data : nullptr, c.offset);
+    const bool has_nulls = c.validity != nullptr && c.null_count != 0;
+    g.vv = has_nulls ? make_bitmap_ref(c.validity, c.offset) : BitmapRef{nullptr, 0};
+  }
+  a->n = n;
+  return B200_OK;
+}
+
+void fill_col(const b200_col& c, GbCol* g) {
+  const int bits = b200_type_bits(c.type);
+  g->type = c.type;
+  g->data = bits >= 8 ? reinterpret_cast<const char*>(c.data) + c.offset * (bits / 8) : nullptr;
+  g->bits = make_bitmap_ref(bits == 1 ? c.data : nullptr, c.offset);
+  const bool has_nulls = c.validity != nullptr && c.null_count != 0;
+  g->vv = has_nulls ? make_bitmap_ref(c.validity, c.offset) : BitmapRef{nullptr, 0};
+}
+
+// launches the consume kernel over all rows, then re-runs it over deferred rows after growing the
+// table until every row found a slot
+int run_consume(b200_groupby* gb, GbArgs& a) {
+  b200_ctx* ctx = gb->ctx;
+  const int64_t n = a.n;
+  if (n == 0) return B200_OK;
+  const size_t words = size_t((n + 31) / 32);
+  const size_t claimed_bytes = a.mode == kModeInsert ? b200_align_up(size_t(n) * 4, 256) : 0;
+  B200_RETURN_NOT_OK(gb_reserve_tmp(gb, 2 * b200_align_up(words * 4, 256) + claimed_bytes + 256));
+  uint32_t* defer_a = reinterpret_cast<uint32_t*>(gb->tmp);
+  uint32_t* defer_b = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(gb->tmp) + b200_align_up(words * 4, 256));
+  if (a.mode == kModeInsert) a.claimed = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(gb->tmp) + 2 * b200_align_up(words * 4, 256));
+  a.counters = gb->counters;
+  a.defer_in = nullptr;
+  a.defer_out = defer_a;
+  B200_CUDA(ctx, cudaMemsetAsync(defer_a, 0, words * 4, ctx->stream));
+  B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 1, 0, 2 * sizeof(uint32_t), ctx->stream));
+
+  // path choice: the shared-memory table pays off while the groups fit in it
+  const int sm_slots_budget = 160 * 1024 / a.s.lstride;
+  int local_slots = 1;
+  while (local_slots * 2 <= sm_slots_budget) local_slots *= 2;
+  const uint64_t likely_groups = std::max<uint64_t>(gb->groups, gb->expected);
+  const bool low_card = a.mode != kModeLookup && likely_groups * 2 <= uint64_t(local_slots) && local_slots >= 64;
+  for (int round = 0; round < 8; ++round) {
+    a.t = gb->table;
+    if (low_card && round == 0) {
+      const int blocks = ctx->num_sms;
+      // the flush of every CTA must find room: table >= 2 * (groups + all local slots)
+      B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + uint64_t(blocks) * local_slots)));
+      a.t = gb->table;
+      a.local_slots = local_slots;
+      a.rows_per_block = int((n + blocks - 1) / blocks);
+      a.rows_per_block = (a.rows_per_block + 1023) / 1024 * 1024;
+      const int smem = local_slots * a.s.lstride;
+      static bool attr = false;
+      if (!attr) {
+        B200_CUDA(ctx, cudaFuncSetAttribute(gb_consume_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr = true;
+      }
+      gb_consume_kernel<true><<<blocks, 1024, smem, ctx->stream>>>(a);
+    } else {
+      a.local_slots = 1;
+      a.rows_per_block = 4096;
+      const int64_t blocks = (n + a.rows_per_block - 1) / a.rows_per_block;
+      gb_consume_kernel<false><<<(unsigned)blocks, 256, 0, ctx->stream>>>(a);
+    }
+    B200_LAUNCHED(ctx);
+    uint32_t c[4];
+    B200_RETURN_NOT_OK(read_counters(gb, c));
+    const uint32_t deferred = c[1];
+    if (deferred == 0) {
+      // keep the load factor <= 1/2 for the next batch
+      if (uint64_t(gb->groups) * 2 > gb->table.cap) B200_RETURN_NOT_OK(grow_table(gb, uint64_t(gb->groups) * 4));
+      return B200_OK;
+    }
+    if (a.mode == kModeInsert && gb->slot_ids) {
+      // a rehash invalidates positional ids and the claimed list: the grouper restarts this batch
+      return b200_fail(ctx, B200_CAPACITY_ERROR, "grouper: table overflow");
+    }
+    B200_RETURN_NOT_OK(grow_table(gb, std::max<uint64_t>(gb->table.cap * 4, 4 * (uint64_t(gb->groups) + deferred))));
+    a.defer_in = a.defer_out;
+    a.defer_out = (a.defer_in == defer_a) ? defer_b : defer_a;
+    B200_CUDA(ctx, cudaMemsetAsync(a.defer_out, 0, words * 4, ctx->stream));
+    B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 1, 0, sizeof(uint32_t), ctx->stream));
+  }
+  return b200_fail(ctx, B200_CAPACITY_ERROR, "groupby: rows still deferred after 8 table growths");
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_groupby_create(b200_ctx* ctx, int n_keys, const int32_t* key_types, int n_aggs, const b200_agg_spec* aggs,
+                        int64_t expected_groups, b200_groupby** out) {
+  if (!ctx || !out) return B200_INVALID;
+  *out = nullptr;
+  if (n_keys < 1 || n_keys > kMaxKeys) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby: %d key columns (1..%d supported)", n_keys, kMaxKeys);
+  if (n_aggs < 0 || n_aggs > kMaxAggs) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby: %d aggregates (max %d)", n_aggs, kMaxAggs);
+  GbSchema s;
+  memset(&s, 0, sizeof(s));
+  s.n_keys = n_keys;
+  s.n_aggs = n_aggs;
+  int total = 0;
+  for (int k = 0; k < n_keys; ++k) {
+    const int bits = b200_type_bits(key_types[k]);
+    // GrouperImpl::Make: "Keys of type ..." NotImplemented for unsupported types (hash_aggregate.cc:352)
+    if (bits == 0) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "Keys of type %d", key_types[k]);
+    s.key_type[k] = key_types[k];
+    s.key_bits[k] = bits;
+    s.key_shift[k] = total;
+    total += bits;
+  }
+  if (total + n_keys <= 64) {
+    s.null_shift = total;
+  } else if (n_keys == 1 && total == 64) {
+    s.null_shift = -1;
+  } else {
+    return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby: packed key of %d bits + %d null flags exceeds 64 bits", total, n_keys);
+  }
+  int off = 16;
+  for (int j = 0; j < n_aggs; ++j) {
+    const int kind = aggs[j].kind, t = aggs[j].arg_type;
+    if (kind < B200_HASH_COUNT || kind > B200_HASH_MEAN) return b200_fail(ctx, B200_KEY_ERROR, "No function registered with kind %d", kind);
+    if (b200_type_bits(t) == 0) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby: argument type %d", t);
+    // GroupedSumImpl / GroupedMinMaxImpl: "Summing data of type" / "Grouped MinMax data of type" NotImplemented
+    // (hash_aggregate.cc:550-556, 684-694)
+    if (kind != B200_HASH_COUNT && t == B200_BOOL)
+      return b200_fail(ctx, B200_NOT_IMPLEMENTED, "%s data of type bool", kind == B200_HASH_MIN_MAX ? "Grouped MinMax" : "Summing");
+    s.aggs[j].kind = kind;
+    s.aggs[j].dom = domain_of(t);
+    s.aggs[j].option = aggs[j].option;
+    s.aggs[j].off = off;
+    s.aggs[j].col = j;
+    s.aggs[j].arg_type = t;
+    off += state_bytes(kind);
+  }
+  s.lstride = off;
+  s.stride = int(b200_align_up(size_t(off) + 8, 16));  // + one padding word (export tag)
+  b200_groupby* gb = new b200_groupby();
+  gb->ctx = ctx;
+  gb->schema = s;
+  gb->specs.assign(aggs, aggs + n_aggs);
+  gb->expected = expected_groups > 0 ? uint64_t(expected_groups) : 0;
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&gb->counters), 8 * sizeof(uint32_t));
+  if (e != cudaSuccess) {
+    delete gb;
+    return b200_fail(ctx, B200_OUT_OF_MEMORY, "groupby: %s", cudaGetErrorString(e));
+  }
+  cudaMemsetAsync(gb->counters, 0, 8 * sizeof(uint32_t), ctx->stream);
+  const uint64_t cap = pow2_at_least(expected_groups > 0 ? uint64_t(expected_groups) * 2 : (1u << 16));
+  int st = alloc_table(gb, cap, &gb->table);
+  if (st != B200_OK) {
+    cudaFree(gb->counters);
+    delete gb;
+    return st;
+  }
+  *out = gb;
+  return B200_OK;
+}
+
+int b200_groupby_destroy(b200_groupby* gb) {
+  if (!gb) return B200_OK;
+  cudaStreamSynchronize(gb->ctx->stream);
+  if (gb->table.slots) cudaFree(gb->table.slots);
+  if (gb->counters) cudaFree(gb->counters);
+  if (gb->slot_ids) cudaFree(gb->slot_ids);
+  if (gb->dense) cudaFree(gb->dense);
+  if (gb->tmp) cudaFree(gb->tmp);
+  delete gb;
+  return B200_OK;
+}
+
+int b200_groupby_consume(b200_groupby* gb, const b200_col* keys, const b200_col* args, uint64_t row_base) {
+  if (!gb) return B200_INVALID;
+  b200_ctx* ctx = gb->ctx;
+  if (!keys || (gb->schema.n_aggs > 0 && !args)) return b200_fail(ctx, B200_INVALID, "groupby_consume: null argument");
+  if (gb->dense_used) return b200_fail(ctx, B200_INVALID, "groupby: handle already used through b200_hash_agg_consume");
+  GbArgs a;
+  memset(&a, 0, sizeof(a));
+  a.s = gb->schema;
+  B200_RETURN_NOT_OK(fill_keys(gb, keys, &a));
+  // de-duplicate argument columns: the same buffers feed several aggregates (C3, Q1)
+  a.n_cols = 0;
+  for (int j = 0; j < a.s.n_aggs; ++j) {
+    const b200_col& c = args[j];
+    if (c.type != a.s.aggs[j].arg_type) return b200_fail(ctx, B200_TYPE_ERROR, "groupby: argument %d has type %d, expected %d", j, c.type, a.s.aggs[j].arg_type);
+    if (c.length != a.n) return b200_fail(ctx, B200_INVALID, "Array arguments must all be the same length");
+    if (a.n > 0 && !c.data) return b200_fail(ctx, B200_INVALID, "groupby: argument %d has no data buffer", j);
+    int found = -1;
+    for (int p = 0; p < j; ++p)
+      if (args[p].data == c.data && args[p].validity == c.validity && args[p].offset == c.offset && args[p].type == c.type &&
+          ((args[p].null_count != 0) == (c.null_count != 0)))
+        found = a.s.aggs[p].col;
+    if (found < 0) {
+      if (a.n_cols == kMaxCols) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby: more than %d distinct argument columns", kMaxCols);
+      fill_col(c, &a.cols[a.n_cols]);
+      found = a.n_cols++;
+    }
+    a.s.aggs[j].col = found;
+  }
+  a.mode = kModeFused;
+  a.row_base = row_base;
+  return run_consume(gb, a);
+}
+
+int b200_groupby_num_groups(b200_groupby* gb, uint32_t* out) {
+  if (!gb || !out) return B200_INVALID;
+  if (gb->dense_used) {
+    *out = gb->dense_groups;
+    return B200_OK;
+  }
+  uint32_t c[4];
+  B200_RETURN_NOT_OK(read_counters(gb, c));
+  *out = c[0];
+  return B200_OK;
+}
+
+int b200_grouper_consume(b200_groupby* gb, const b200_col* keys, uint32_t* out_ids) {
+  if (!gb) return B200_INVALID;
+  b200_ctx* ctx = gb->ctx;
+  if (!keys) return b200_fail(ctx, B200_INVALID, "grouper_consume: null keys");
+  GbArgs a;
+  memset(&a, 0, sizeof(a));
+  a.s = gb->schema;
+  a.s.n_aggs = 0;
+  a.s.lstride = 16;
+  B200_RETURN_NOT_OK(fill_keys(gb, keys, &a));
+  const int64_t n = a.n;
+  if (n == 0) return B200_OK;
+  if (!out_ids) return b200_fail(ctx, B200_INVALID, "grouper_consume: null output");
+  // row indices continue across calls so that first-occurrence order is global
+  a.row_base = gb->dense_rows;
+  gb->dense_rows += uint64_t(n);
+  // make room up front: a rehash in the middle of a batch would invalidate positional slot ids
+  {
+    uint32_t c[4];
+    B200_RETURN_NOT_OK(read_counters(gb, c));
+    if ((uint64_t(gb->groups) + uint64_t(n)) * 2 > gb->table.cap) B200_RETURN_NOT_OK(grow_table(gb, (uint64_t(gb->groups) + uint64_t(n)) * 2));
+  }
+  // all scratch of this call is reserved up front: the claimed-slot list written by pass 1 must
+  // survive until the ids are assigned
+  size_t sort_bytes = 0;
+  b200_sort_pairs_scratch_bytes(n, &sort_bytes);
+  const size_t words = size_t((n + 31) / 32);
+  const size_t base_off = 2 * b200_align_up(words * 4, 256) + b200_align_up(size_t(n) * 4, 256) + 256;
+  const size_t arr = b200_align_up(size_t(n) * 8, 256);
+  B200_RETURN_NOT_OK(gb_reserve_tmp(gb, base_off + 3 * arr + sort_bytes + 256));
+  const uint64_t n_slots = gb->table.cap + 2;
+  const bool rebuild_ids = gb->slot_ids == nullptr;
+  if (rebuild_ids) {
+    B200_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&gb->slot_ids), n_slots * sizeof(uint32_t)));
+    gb->slot_ids_cap = n_slots;
+    gb_fill_u32_kernel<<<(unsigned)((n_slots + 255) / 256), 256, 0, ctx->stream>>>(gb->slot_ids, n_slots, kNoId);
+    B200_LAUNCHED(ctx);
+    gb->ids_assigned = 0;
+  }
+  // pass 1: insert keys, track first rows and newly claimed slots
+  a.mode = kModeInsert;
+  a.slot_ids = gb->slot_ids;
+  B200_RETURN_NOT_OK(run_consume(gb, a));
+  uint32_t c[4];
+  B200_RETURN_NOT_OK(read_counters(gb, c));
+  // slots that still need an id: the claimed list, or (after a rehash / fused consumes) a full scan
+  uint32_t n_new = c[2];
+  const bool full_scan = rebuild_ids && gb->groups != n_new;
+  const uint32_t want = gb->groups - gb->ids_assigned;
+  if (want > 0) {
+    if (want > uint64_t(n)) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "grouper: %u groups from earlier fused consumes need ids; use a fresh handle", want);
+    // scratch: first_rows[n] slot_idx[n] sorted[n] + sort scratch, placed after run_consume's regions
+    char* base = reinterpret_cast<char*>(gb->tmp);
+    uint32_t* claimed = reinterpret_cast<uint32_t*>(base + 2 * b200_align_up(words * 4, 256));
+    uint64_t* first_rows = reinterpret_cast<uint64_t*>(base + base_off);
+    uint64_t* slot_idx = reinterpret_cast<uint64_t*>(base + base_off + arr);
+    uint64_t* sorted = reinterpret_cast<uint64_t*>(base + base_off + 2 * arr);
+    void* sort_scratch = base + base_off + 3 * arr;
+    if (full_scan || n_new != want) {
+      B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 4, 0, sizeof(uint32_t), ctx->stream));
+      gb_collect_kernel<<<(unsigned)((n_slots + 255) / 256), 256, 0, ctx->stream>>>(gb->table, gb->schema.stride, first_rows, slot_idx,
+                                                                                   gb->counters + 4, gb->slot_ids, 1);
+      B200_LAUNCHED(ctx);
+    } else {
+      gb_claimed_rows_kernel<<<(want + 255) / 256, 256, 0, ctx->stream>>>(gb->table, gb->schema.stride, claimed, want, first_rows, slot_idx);
+      B200_LAUNCHED(ctx);
+    }
+    B200_RETURN_NOT_OK(b200_sort_pairs(ctx, first_rows, slot_idx, want, nullptr, sorted, sort_scratch, sort_bytes));
+    gb_assign_ids_kernel<<<(want + 255) / 256, 256, 0, ctx->stream>>>(sorted, want, gb->ids_assigned, gb->slot_ids);
+    B200_LAUNCHED(ctx);
+    gb->ids_assigned += want;
+  }
+  // pass 2: look the ids up
+  a.mode = kModeLookup;
+  a.out_ids = out_ids;
+  a.claimed = nullptr;
+  a.row_base = 0;
+  B200_RETURN_NOT_OK(run_consume(gb, a));
+  return B200_OK;
+}
+
+int b200_hash_agg_consume(b200_groupby* gb, int agg_index, const b200_col* arg, const uint32_t* ids, uint32_t num_groups) {
+  if (!gb) return B200_INVALID;
+  b200_ctx* ctx = gb->ctx;
+  if (agg_index < 0 || agg_index >= gb->schema.n_aggs) return b200_fail(ctx, B200_INVALID, "hash_agg_consume: bad aggregate index");
+  if (!arg || (arg->length > 0 && !ids)) return b200_fail(ctx, B200_INVALID, "hash_agg_consume: null argument");
+  if (arg->type != gb->schema.aggs[agg_index].arg_type) return b200_fail(ctx, B200_TYPE_ERROR, "hash_agg_consume: argument type mismatch");
+  gb->dense_used = true;
+  // MaybeReserve (hash_aggregate.cc:450-458): grow the per-group state to num_groups
+  if (num_groups > gb->dense_cap) {
+    const uint32_t new_cap = uint32_t(pow2_at_least(num_groups));
+    char* nd = nullptr;
+    B200_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&nd), size_t(new_cap) * gb->schema.stride));
+    gb_init_kernel<<<(new_cap + 255) / 256, 256, 0, ctx->stream>>>(gb->schema, nd, new_cap, gb->schema.stride);
+    B200_LAUNCHED(ctx);
+    if (gb->dense) {
+      B200_CUDA(ctx, cudaMemcpyAsync(nd, gb->dense, size_t(gb->dense_cap) * gb->schema.stride, cudaMemcpyDeviceToDevice, ctx->stream));
+      B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+      B200_CUDA(ctx, cudaFree(gb->dense));
+    }
+    gb->dense = nd;
+    gb->dense_cap = new_cap;
+  }
+  if (num_groups > gb->dense_groups) gb->dense_groups = num_groups;
+  const int64_t n = arg->length;
+  if (n == 0) return B200_OK;
+  GbCol col;
+  fill_col(*arg, &col);
+  gb_dense_consume_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(gb->schema, agg_index, col, ids, n, gb->dense,
+                                                                               num_groups, gb->counters);
+  B200_LAUNCHED(ctx);
+  return B200_OK;
+}
+
+int b200_groupby_state_layout(b200_groupby* gb, size_t* slot_bytes) {
+  if (!gb || !slot_bytes) return B200_INVALID;
+  *slot_bytes = size_t(gb->schema.stride);
+  return B200_OK;
+}
+
+static int collect_slots(b200_groupby* gb, uint64_t** first_rows, uint64_t** slot_idx, uint32_t* n_out, size_t extra,
+                         char** extra_ptr) {
+  b200_ctx* ctx = gb->ctx;
+  uint32_t c[4];
+  B200_RETURN_NOT_OK(read_counters(gb, c));
+  const uint32_t G = c[0];
+  const size_t arr = b200_align_up(size_t(std::max<uint32_t>(G, 1)) * 8, 256);
+  B200_RETURN_NOT_OK(gb_reserve_tmp(gb, 2 * arr + extra + 256));
+  *first_rows = reinterpret_cast<uint64_t*>(gb->tmp);
+  *slot_idx = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(gb->tmp) + arr);
+  if (extra_ptr) *extra_ptr = reinterpret_cast<char*>(gb->tmp) + 2 * arr;
+  B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 4, 0, sizeof(uint32_t), ctx->stream));
+  const uint64_t n_slots = gb->table.cap + 2;
+  gb_collect_kernel<<<(unsigned)((n_slots + 255) / 256), 256, 0, ctx->stream>>>(gb->table, gb->schema.stride, *first_rows, *slot_idx,
+                                                                               gb->counters + 4, nullptr, 0);
+  B200_LAUNCHED(ctx);
+  *n_out = G;
+  return B200_OK;
+}
+
+int b200_groupby_export(b200_groupby* gb, void* out_state, uint32_t* out_groups) {
+  if (!gb || !out_groups) return B200_INVALID;
+  b200_ctx* ctx = gb->ctx;
+  uint64_t *first_rows, *slot_idx;
+  uint32_t G;
+  B200_RETURN_NOT_OK(collect_slots(gb, &first_rows, &slot_idx, &G, 0, nullptr));
+  if (G > 0) {
+    if (!out_state) return b200_fail(ctx, B200_INVALID, "groupby_export: null output");
+    gb_export_kernel<<<(G + 255) / 256, 256, 0, ctx->stream>>>(gb->table, gb->schema.stride, slot_idx, G,
+                                                               reinterpret_cast<char*>(out_state), nullptr);
+    B200_LAUNCHED(ctx);
+  }
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *out_groups = G;
+  return B200_OK;
+}
+
+int b200_groupby_import(b200_groupby* gb, const void* state, uint32_t n_slots) {
+  if (!gb) return B200_INVALID;
+  b200_ctx* ctx = gb->ctx;
+  if (n_slots == 0) return B200_OK;
+  if (!state) return b200_fail(ctx, B200_INVALID, "groupby_import: null state");
+  uint32_t c[4];
+  B200_RETURN_NOT_OK(read_counters(gb, c));
+  B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + n_slots)));
+  gb_import_kernel<<<(n_slots + 255) / 256, 256, 0, ctx->stream>>>(gb->schema, reinterpret_cast<const char*>(state), n_slots,
+                                                                  gb->table, gb->counters);
+  B200_LAUNCHED(ctx);
+  return read_counters(gb, c);
+}
+
+int b200_groupby_merge(b200_groupby* dst, b200_groupby* src) {
+  if (!dst || !src) return B200_INVALID;
+  b200_ctx* ctx = dst->ctx;
+  if (memcmp(&dst->schema, &src->schema, sizeof(GbSchema)) != 0) return b200_fail(ctx, B200_TYPE_ERROR, "groupby_merge: schemas differ");
+  if (dst->ctx != src->ctx) return b200_fail(ctx, B200_INVALID, "groupby_merge: handles belong to different contexts");
+  uint32_t c[4];
+  B200_RETURN_NOT_OK(read_counters(src, c));
+  const uint32_t src_groups = c[0];
+  B200_RETURN_NOT_OK(read_counters(dst, c));
+  B200_RETURN_NOT_OK(grow_table(dst, 2 * (uint64_t(dst->groups) + src_groups)));
+  const uint64_t n_src = src->table.cap + 2;
+  gb_move_kernel<<<(unsigned)((n_src + 255) / 256), 256, 0, ctx->stream>>>(dst->schema, src->table.slots, n_src, src->schema.stride,
+                                                                           src->table.cap, dst->table, 1, dst->counters);
+  B200_LAUNCHED(ctx);
+  return read_counters(dst, c);
+}
+
+int b200_groupby_finalize(b200_groupby* gb, b200_out_col* out_aggs, b200_out_col* out_keys) {
+  if (!gb) return B200_INVALID;
+  b200_ctx* ctx = gb->ctx;
+  EmitArgs e;
+  memset(&e, 0, sizeof(e));
+  e.s = gb->schema;
+  uint32_t G = 0;
+  if (gb->dense_used) {
+    // HashAggregateKernel::finalize only: ids are already dense, no keys to emit
+    uint32_t c[4];
+    B200_RETURN_NOT_OK(read_counters(gb, c));
+    G = gb->dense_groups;
+    e.t.slots = gb->dense;
+    e.t.cap = 0;
+    e.order = nullptr;
+    B200_RETURN_NOT_OK(gb_reserve_tmp(gb, 4096));
+    e.null_counts = reinterpret_cast<uint32_t*>(gb->tmp);
+  } else {
+    uint64_t *first_rows, *slot_idx;
+    size_t sort_bytes = 0;
+    uint32_t c[4];
+    B200_RETURN_NOT_OK(read_counters(gb, c));
+    b200_sort_pairs_scratch_bytes(std::max<uint32_t>(c[0], 1), &sort_bytes);
+    const size_t arr = b200_align_up(size_t(std::max<uint32_t>(c[0], 1)) * 8, 256);
+    char* extra = nullptr;
+    B200_RETURN_NOT_OK(collect_slots(gb, &first_rows, &slot_idx, &G, arr + sort_bytes + 4096, &extra));
+    uint64_t* sorted = reinterpret_cast<uint64_t*>(extra);
+    e.null_counts = reinterpret_cast<uint32_t*>(extra + arr);
+    void* sort_scratch = extra + arr + 4096;
+    if (G > 0) B200_RETURN_NOT_OK(b200_sort_pairs(ctx, first_rows, slot_idx, G, nullptr, sorted, sort_scratch, sort_bytes));
+    e.t = gb->table;
+    e.order = sorted;
+  }
+  e.n_groups = G;
+  B200_CUDA(ctx, cudaMemsetAsync(e.null_counts, 0, (kMaxKeys + 2 * kMaxAggs) * sizeof(uint32_t), ctx->stream));
+  for (int k = 0; k < e.s.n_keys; ++k) {
+    if (out_keys && !gb->dense_used) {
+      e.keys[k].data = out_keys[k].data;
+      e.keys[k].validity = reinterpret_cast<uint32_t*>(out_keys[k].validity);
+      e.keys[k].type = e.s.key_type[k];
+      if (G > 0 && !out_keys[k].data) return b200_fail(ctx, B200_INVALID, "groupby_finalize: key %d has no data buffer", k);
+    }
+  }
+  int oi = 0;
+  for (int j = 0; j < e.s.n_aggs; ++j) {
+    const int n_out = e.s.aggs[j].kind == B200_HASH_MIN_MAX ? 2 : 1;
+    for (int q = 0; q < n_out; ++q, ++oi) {
+      if (!out_aggs) return b200_fail(ctx, B200_INVALID, "groupby_finalize: null out_aggs");
+      e.aggs[oi].data = out_aggs[oi].data;
+      e.aggs[oi].validity = reinterpret_cast<uint32_t*>(out_aggs[oi].validity);
+      if (G > 0 && !out_aggs[oi].data) return b200_fail(ctx, B200_INVALID, "groupby_finalize: aggregate output %d has no data buffer", oi);
+    }
+  }
+  if (G > 0) {
+    gb_emit_kernel<<<(G + 255) / 256, 256, 0, ctx->stream>>>(e);
+    B200_LAUNCHED(ctx);
+  }
+  B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 24, e.null_counts, (kMaxKeys + 2 * kMaxAggs) * sizeof(uint32_t),
+                                 cudaMemcpyDeviceToHost, ctx->stream));
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  const uint32_t* nc = reinterpret_cast<const uint32_t*>(ctx->host_words + 24);
+  for (int k = 0; k < e.s.n_keys && out_keys && !gb->dense_used; ++k) {
+    out_keys[k].length = G;
+    out_keys[k].null_count = nc[k];
+    out_keys[k].type = e.s.key_type[k];
+  }
+  for (int i = 0; i < oi; ++i) {
+    out_aggs[i].length = G;
+    out_aggs[i].null_count = nc[kMaxKeys + i];
+  }
+  return B200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,244 @@
+"""Grouper + hash aggregate parity: CUDA path (through the C ABI) vs the oracle.  Bit-exact for
+keys, group order (first occurrence), counts, min/max (incl. +-0.0 and NaN rules) and integer
+sums; float64 sums / means within 1e-12 relative (north_star tolerance)."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from arrow1_b200 import columns as cols
+from arrow1_b200.columns import AggSpec, Column
+from conftest import rand_u64
+from gen import rand_column
+from helpers import assert_group_equal, run_groupby
+
+pytestmark = pytest.mark.gpu
+ORACLE = "reference" if oracle.have_reference() else "port"
+RTOL = 1e-12
+
+ALL_AGGS = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT), AggSpec(cols.HASH_COUNT, 1),
+            AggSpec(cols.HASH_MIN_MAX), AggSpec(cols.HASH_MIN_MAX, 1), AggSpec(cols.HASH_MEAN)]
+
+
+@pytest.mark.parametrize("kt", [cols.BOOL, cols.UINT8, cols.INT16, cols.INT32, cols.INT64, cols.UINT64, cols.FLOAT, cols.DOUBLE])
+@pytest.mark.parametrize("at", [cols.INT8, cols.UINT16, cols.INT32, cols.UINT64, cols.INT64, cols.FLOAT, cols.DOUBLE])
+def test_groupby_random(ctx, kt, at):
+    # hash_aggregate_test.cc:704-723 shape (keys in [0,100], lengths 2^10..2^15, null_prob ladder)
+    rng = np.random.default_rng(500 + 31 * kt + at)
+    for n in (1, 1 << 10, 1 << 15):
+        for null_prob in (0.0, 0.01, 0.5, 1.0):
+            key = rand_column(rng, kt, n, 0.05, lo=0, hi=100, special=(kt in (cols.FLOAT, cols.DOUBLE)))
+            arg = rand_column(rng, at, n, null_prob, special=True)
+            args = [arg] * len(ALL_AGGS)
+            a = run_groupby("gpu", [key], ALL_AGGS, args, ctx, want_ids=True)
+            b = run_groupby(ORACLE, [key], ALL_AGGS, args, want_ids=True)
+            assert_group_equal(a, b, ALL_AGGS, rtol=RTOL)
+
+
+def test_groupby_empty(ctx):
+    key = Column.from_numpy(np.array([], dtype=np.int32))
+    arg = Column.from_numpy(np.array([], dtype=np.float64))
+    r = run_groupby("gpu", [key], [AggSpec(cols.HASH_SUM)], [arg], ctx)
+    assert r.num_groups == 0
+
+
+def test_groupby_multi_key(ctx):
+    rng = np.random.default_rng(11)
+    n = 50000
+    k0 = rand_column(rng, cols.UINT8, n, 0.1, lo=0, hi=3)
+    k1 = rand_column(rng, cols.INT16, n, 0.1, lo=-2, hi=2)
+    k2 = rand_column(rng, cols.BOOL, n, 0.1)
+    arg = rand_column(rng, cols.DOUBLE, n, 0.2)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MIN_MAX), AggSpec(cols.HASH_COUNT)]
+    a = run_groupby("gpu", [k0, k1, k2], aggs, [arg] * 3, ctx, want_ids=True)
+    b = run_groupby(ORACLE, [k0, k1, k2], aggs, [arg] * 3, want_ids=True)
+    assert_group_equal(a, b, aggs, rtol=RTOL)
+
+
+def test_groupby_int64_key_sentinel_and_null(ctx):
+    """A single 64-bit key leaves no spare bit: null and the all-ones key live in special slots."""
+    v = np.array([-1, 5, -1, 0, 7, 5, -1, 0], dtype=np.int64)  # -1 == the EMPTY sentinel bit pattern
+    valid = np.array([1, 1, 1, 0, 1, 1, 0, 1], dtype=bool)
+    key = Column.from_numpy(v, valid)
+    arg = Column.from_numpy(np.arange(8, dtype=np.float64))
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT)]
+    a = run_groupby("gpu", [key], aggs, [arg, arg], ctx, want_ids=True)
+    b = run_groupby(ORACLE, [key], aggs, [arg, arg], want_ids=True)
+    assert_group_equal(a, b, aggs, rtol=RTOL)
+    ukey = Column.from_numpy(v.view(np.uint64), valid)
+    a = run_groupby("gpu", [ukey], aggs, [arg, arg], ctx, want_ids=True)
+    b = run_groupby(ORACLE, [ukey], aggs, [arg, arg], want_ids=True)
+    assert_group_equal(a, b, aggs, rtol=RTOL)
+
+
+def test_groupby_min_max_zero_sign_and_nan(ctx):
+    # std::max/min tie rule: the earlier of +-0.0 wins; NaN never wins but sets has_values
+    # (hash_aggregate.cc:663-677)
+    vals = np.array([0.0, -0.0, -0.0, 0.0, np.nan, np.nan, 1.0, -0.0, -1.0, 0.0, np.nan, 3.0], dtype=np.float64)
+    keys = np.array([0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5], dtype=np.int32)
+    for dt, t in ((np.float64, cols.DOUBLE), (np.float32, cols.FLOAT)):
+        key = Column.from_numpy(keys)
+        arg = Column.from_numpy(vals.astype(dt))
+        aggs = [AggSpec(cols.HASH_MIN_MAX)]
+        a = run_groupby("gpu", [key], aggs, [arg], ctx)
+        b = run_groupby(ORACLE, [key], aggs, [arg])
+        assert_group_equal(a, b, aggs)
+        # signs compared bitwise by assert_group_equal (view as bytes)
+
+
+def test_groupby_high_cardinality_growth(ctx):
+    """No hint, far more groups than the initial table: rows get deferred, the table grows, parity holds."""
+    rng = np.random.default_rng(21)
+    n = 400000
+    key = Column.from_numpy(rng.integers(0, 1 << 40, size=n, dtype=np.int64))
+    arg = Column.from_numpy(rng.random(n))
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MEAN)]
+    a = run_groupby("gpu", [key], aggs, [arg, arg], ctx, expected_groups=0)
+    b = run_groupby(ORACLE, [key], aggs, [arg, arg])
+    assert_group_equal(a, b, aggs, rtol=RTOL)
+    a = run_groupby("gpu", [key], aggs, [arg, arg], ctx, expected_groups=n)
+    assert_group_equal(a, b, aggs, rtol=RTOL)
+
+
+def test_groupby_streaming_batches_match_single_batch(ctx):
+    """GroupBy's batch loop (hash_aggregate.cc:928-943): consuming row ranges one after the other,
+    sliced (offset != 0) — the case the reference itself gets wrong — equals one batch."""
+    from arrow1_b200 import capi
+    rng = np.random.default_rng(22)
+    n = 100000
+    kv = rng.integers(0, 300, size=n, dtype=np.int32)
+    av = rng.random(n) * 1e6
+    avalid = rng.random(n) > 0.1
+    key, arg = Column.from_numpy(kv), Column.from_numpy(av, avalid)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT), AggSpec(cols.HASH_MIN_MAX)]
+    gb = capi.GroupBy(ctx, [cols.INT32], aggs, [cols.DOUBLE] * 3)
+    dkey, darg = key.to_device(), arg.to_device()
+    step = 33333
+    for lo in range(0, n, step):
+        ln = min(step, n - lo)
+        ks = Column(dkey.type, dkey.data, dkey.validity, ln, lo, 0)
+        as_ = Column(darg.type, darg.data, darg.validity, ln, lo, -1)
+        gb.consume([ks], [as_] * 3, row_base=lo)
+    out = gb.finalize()
+    gb.close()
+    b = run_groupby(ORACLE, [key], aggs, [arg] * 3)
+    assert out.num_groups == b.num_groups
+    np.testing.assert_array_equal(out.keys[0].to_host().values(), b.keys[0][0])
+    np.testing.assert_array_equal(out.aggs[1][0].to_host().values(), b.aggs[1][0][0])
+    np.testing.assert_allclose(out.aggs[0][0].to_host().values(), b.aggs[0][0][0], rtol=RTOL)
+    np.testing.assert_array_equal(out.aggs[2][0].to_host().values(), b.aggs[2][0][0])
+    np.testing.assert_array_equal(out.aggs[2][1].to_host().values(), b.aggs[2][1][0])
+
+
+def test_groupby_merge_and_export_import(ctx):
+    """HashAggregateKernel::merge (NotImplemented in the reference, hash_aggregate.cc:795-798) ==
+    what a single table over all rows gives; also through the flat export/import the multi-GPU
+    all-gather uses."""
+    from arrow1_b200 import capi
+    rng = np.random.default_rng(23)
+    n = 60000
+    kv = rng.integers(0, 5000, size=n, dtype=np.int64)
+    av = rng.integers(-1000, 1000, size=n, dtype=np.int32)
+    key, arg = Column.from_numpy(kv), Column.from_numpy(av)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MIN_MAX), AggSpec(cols.HASH_MEAN)]
+    b = run_groupby(ORACLE, [key], aggs, [arg] * 3)
+    dkey, darg = key.to_device(), arg.to_device()
+    half = n // 2
+    parts = []
+    for lo, ln in ((0, half), (half, n - half)):
+        g = capi.GroupBy(ctx, [cols.INT64], aggs, [cols.INT32] * 3)
+        g.consume([Column(dkey.type, dkey.data, None, ln, lo, 0)], [Column(darg.type, darg.data, None, ln, lo, 0)] * 3,
+                  row_base=lo)
+        parts.append(g)
+    # (a) direct merge
+    parts[0].merge(parts[1])
+    out = parts[0].finalize()
+    # (b) export -> import into a fresh handle
+    g2 = capi.GroupBy(ctx, [cols.INT64], aggs, [cols.INT32] * 3)
+    g2.import_state(parts[0].export_state())
+    out2 = g2.finalize()
+    for o in (out, out2):
+        assert o.num_groups == b.num_groups
+        np.testing.assert_array_equal(o.keys[0].to_host().values(), b.keys[0][0])
+        np.testing.assert_array_equal(o.aggs[0][0].to_host().values(), b.aggs[0][0][0])
+        np.testing.assert_array_equal(o.aggs[1][0].to_host().values(), b.aggs[1][0][0])
+        np.testing.assert_array_equal(o.aggs[1][1].to_host().values(), b.aggs[1][1][0])
+        np.testing.assert_allclose(o.aggs[2][0].to_host().values(), b.aggs[2][0][0], rtol=RTOL)
+    for g in parts + [g2]:
+        g.close()
+
+
+def test_hash_agg_kernel_abi_with_dense_ids(ctx):
+    """The reference's HashAggregateKernel signature (arg, uint32 ids, num_groups)
+    (hash_aggregate.cc:783-789): Grouper ids -> per-aggregate consume -> finalize."""
+    from arrow1_b200 import capi
+    rng = np.random.default_rng(24)
+    n = 20000
+    key = rand_column(rng, cols.INT32, n, 0.05, lo=0, hi=50)
+    arg = rand_column(rng, cols.DOUBLE, n, 0.1)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT), AggSpec(cols.HASH_MIN_MAX)]
+    b = run_groupby(ORACLE, [key], aggs, [arg] * 3, want_ids=True)
+    grouper = capi.GroupBy(ctx, [cols.INT32], [], [])
+    ids = grouper.grouper_consume([key.to_device()])
+    G = grouper.num_groups()
+    np.testing.assert_array_equal(ids.cpu().numpy().view(np.uint32), b.ids)
+    assert G == b.num_groups
+    uniques = grouper.finalize().keys[0].to_host()
+    np.testing.assert_array_equal(uniques.valid(), b.keys[0][1])
+    np.testing.assert_array_equal(uniques.values()[uniques.valid()], b.keys[0][0][b.keys[0][1]])
+    kernels = capi.GroupBy(ctx, [cols.INT32], aggs, [cols.DOUBLE] * 3)
+    darg = arg.to_device()
+    for j in range(3):
+        kernels.agg_consume(j, darg, ids, G)
+    out = kernels.finalize()
+    np.testing.assert_allclose(out.aggs[0][0].to_host().values()[b.aggs[0][0][1]], b.aggs[0][0][0][b.aggs[0][0][1]], rtol=RTOL)
+    np.testing.assert_array_equal(out.aggs[0][0].to_host().valid(), b.aggs[0][0][1])
+    np.testing.assert_array_equal(out.aggs[1][0].to_host().values(), b.aggs[1][0][0])
+    v = b.aggs[2][0][1]
+    np.testing.assert_array_equal(out.aggs[2][0].to_host().valid(), v)
+    np.testing.assert_array_equal(out.aggs[2][0].to_host().values()[v], b.aggs[2][0][0][v])
+    np.testing.assert_array_equal(out.aggs[2][1].to_host().values()[v], b.aggs[2][1][0][v])
+    grouper.close()
+    kernels.close()
+
+
+def test_groupby_unsupported(ctx):
+    from arrow1_b200 import capi
+    with pytest.raises(capi.B200Error) as ei:  # summing booleans (hash_aggregate.cc:550-556)
+        capi.GroupBy(ctx, [cols.INT32], [AggSpec(cols.HASH_SUM)], [cols.BOOL])
+    assert ei.value.code == 10
+    with pytest.raises(capi.B200Error) as ei:  # packed key wider than 64 bits
+        capi.GroupBy(ctx, [cols.INT64, cols.INT64], [], [])
+    assert ei.value.code == 10
+
+
+def test_groupby_config3_shape(ctx):
+    """BASELINE config 3 shape (int32 key % 1000, float64 value, 1 % nulls; sum+count+min_max) at
+    20 M rows vs the oracle; sums within 1e-12, everything else exact."""
+    n = 20_000_000
+    with np.errstate(over="ignore"):
+        kv = (rand_u64(7, n) % np.uint64(1000)).astype(np.int32)
+        av = (rand_u64(8, n) >> np.uint64(11)).astype(np.float64) * (2.0 ** -53) * 1e14
+        valid = (rand_u64(12, n) % np.uint64(100)) != 0
+    key, arg = Column.from_numpy(kv), Column.from_numpy(av, valid)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT), AggSpec(cols.HASH_MIN_MAX)]
+    a = run_groupby("gpu", [key], aggs, [arg] * 3, ctx, expected_groups=1000)
+    b = run_groupby(ORACLE, [key], aggs, [arg] * 3)
+    assert_group_equal(a, b, aggs, rtol=RTOL)
+    # checksum of counts == number of valid rows
+    assert int(a.aggs[1][0][0].sum()) == int(valid.sum())
+
+
+def test_groupby_config4_shape(ctx):
+    """BASELINE config 4 shape (int64 keys spread over the full range, ~n/10 distinct; sum+mean) at 4 M rows."""
+    n = 4_000_000
+    with np.errstate(over="ignore"):
+        kv = (rand_u64(9, n) % np.uint64(n // 10))
+        from conftest import splitmix64
+        kv = splitmix64(kv).view(np.int64)
+        av = (rand_u64(10, n) >> np.uint64(11)).astype(np.float64) * (2.0 ** -53) * 1e14
+    key, arg = Column.from_numpy(kv), Column.from_numpy(av)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MEAN)]
+    a = run_groupby("gpu", [key], aggs, [arg] * 2, ctx, expected_groups=n // 10)
+    b = run_groupby(ORACLE, [key], aggs, [arg] * 2)
+    assert_group_equal(a, b, aggs, rtol=RTOL)
