@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include <string>
+#include <vector>
 
 #include "arrow1_b200.h"
 
@@ -20,7 +21,26 @@ struct b200_ctx {
   size_t scratch_bytes = 0;
   // pinned host word block for scalar read-backs
   int64_t* host_words = nullptr;
+  // optional per-kernel CUDA-event timing (bench.py's roofline leg)
+  bool timing = false;
+  struct TimedLaunch {
+    const char* name;
+    cudaEvent_t start, stop;
+  };
+  std::vector<TimedLaunch> timed;
 };
+
+void b200_time_begin(b200_ctx* ctx, const char* name);
+void b200_time_end(b200_ctx* ctx);
+
+// a kernel launch bracketed by CUDA events on the launching stream when timing is enabled
+#define B200_TIMED(ctx, name, launch)   \
+  do {                                  \
+    b200_time_begin((ctx), (name));     \
+    launch;                             \
+    b200_time_end((ctx));               \
+    B200_LAUNCHED(ctx);                 \
+  } while (0)
 
 int b200_fail(b200_ctx* ctx, int code, const char* fmt, ...);
 int b200_ctx_reserve_scratch(b200_ctx* ctx, size_t bytes);

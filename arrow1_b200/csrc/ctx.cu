@@ -27,7 +27,56 @@ int b200_ctx_reserve_scratch(b200_ctx* ctx, size_t bytes) {
   return B200_OK;
 }
 
+void b200_time_begin(b200_ctx* ctx, const char* name) {
+  if (!ctx->timing) return;
+  b200_ctx::TimedLaunch t;
+  t.name = name;
+  cudaEventCreate(&t.start);
+  cudaEventCreate(&t.stop);
+  cudaEventRecord(t.start, ctx->stream);
+  ctx->timed.push_back(t);
+}
+
+void b200_time_end(b200_ctx* ctx) {
+  if (!ctx->timing || ctx->timed.empty()) return;
+  cudaEventRecord(ctx->timed.back().stop, ctx->stream);
+}
+
+static void clear_timed(b200_ctx* ctx) {
+  for (auto& t : ctx->timed) {
+    cudaEventDestroy(t.start);
+    cudaEventDestroy(t.stop);
+  }
+  ctx->timed.clear();
+}
+
 extern "C" {
+
+int b200_ctx_set_kernel_timing(b200_ctx* ctx, int enabled) {
+  if (!ctx) return B200_INVALID;
+  cudaStreamSynchronize(ctx->stream);
+  clear_timed(ctx);
+  ctx->timing = enabled != 0;
+  return B200_OK;
+}
+
+int b200_ctx_kernel_time(b200_ctx* ctx, const char* name, double* total_ms, int64_t* launches) {
+  if (!ctx || !name) return B200_INVALID;
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  double total = 0;
+  int64_t n = 0;
+  for (auto& t : ctx->timed) {
+    if (strcmp(t.name, name) != 0) continue;
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, t.start, t.stop) == cudaSuccess) {
+      total += ms;
+      ++n;
+    }
+  }
+  if (total_ms) *total_ms = total;
+  if (launches) *launches = n;
+  return B200_OK;
+}
 
 const char* b200_version(void) { return "arrow1_b200 0.1 (sm_100a)"; }
 
@@ -70,6 +119,7 @@ int b200_ctx_destroy(b200_ctx* ctx) {
   if (!ctx) return B200_OK;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  clear_timed(ctx);
   if (ctx->scratch) cudaFree(ctx->scratch);
   if (ctx->host_words) cudaFreeHost(ctx->host_words);
   delete ctx;

@@ -297,10 +297,9 @@ template <typename T, bool kBool>
 int launch_apply(b200_ctx* ctx, const ApplyArgs& a, int64_t n_tiles) {
   dim3 grid((unsigned)n_tiles), block(kThreads);
   if (a.out_valid)
-    filter_apply_kernel<T, kBool, true><<<grid, block, 0, ctx->stream>>>(a);
+    B200_TIMED(ctx, "filter_apply", (filter_apply_kernel<T, kBool, true><<<grid, block, 0, ctx->stream>>>(a)));
   else
-    filter_apply_kernel<T, kBool, false><<<grid, block, 0, ctx->stream>>>(a);
-  B200_LAUNCHED(ctx);
+    B200_TIMED(ctx, "filter_apply", (filter_apply_kernel<T, kBool, false><<<grid, block, 0, ctx->stream>>>(a)));
   return B200_OK;
 }
 
@@ -330,9 +329,9 @@ int b200_filter_plan(b200_ctx* ctx, const b200_col* mask, int null_selection, vo
   if (length > 0) {
     BitmapRef f = make_bitmap_ref(mask->data, mask->offset);
     BitmapRef fv = make_bitmap_ref(mask->validity, mask->offset);
-    filter_plan_kernel<<<(unsigned)n_super_for(length), kThreads, 0, ctx->stream>>>(
-        f, fv, length, null_selection, n_tiles_for(length), pv);
-    B200_LAUNCHED(ctx);
+    B200_TIMED(ctx, "filter_plan",
+               (filter_plan_kernel<<<(unsigned)n_super_for(length), kThreads, 0, ctx->stream>>>(
+                   f, fv, length, null_selection, n_tiles_for(length), pv)));
   }
   if (out_len) {
     B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words, &pv.header->out_length, sizeof(int64_t),

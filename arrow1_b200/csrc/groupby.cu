@@ -578,7 +578,13 @@ __global__ void gb_emit_kernel(const __grid_constant__ EmitArgs e) {
       const unsigned word = __ballot_sync(0xffffffffu, in && valid && v);
       if (lane == 0 && (r >> 5) <= ((e.n_groups - 1) >> 5)) reinterpret_cast<uint32_t*>(o.data)[r >> 5] = word;
     } else if (in) {
-      store_typed(o.data, e.s.key_type[k], r, v, 0.0);
+      // raw key bits (floats group by bit pattern)
+      switch (e.s.key_bits[k]) {
+        case 8: reinterpret_cast<uint8_t*>(o.data)[r] = uint8_t(v); break;
+        case 16: reinterpret_cast<uint16_t*>(o.data)[r] = uint16_t(v); break;
+        case 32: reinterpret_cast<uint32_t*>(o.data)[r] = uint32_t(v); break;
+        default: reinterpret_cast<uint64_t*>(o.data)[r] = v; break;
+      }
     }
     const unsigned vw = __ballot_sync(0xffffffffu, in && valid);
     const unsigned inw = __ballot_sync(0xffffffffu, in);
@@ -836,7 +842,9 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
   int local_slots = 1;
   while (local_slots * 2 <= sm_slots_budget) local_slots *= 2;
   const uint64_t likely_groups = std::max<uint64_t>(gb->groups, gb->expected);
-  const bool low_card = a.mode != kModeLookup && likely_groups * 2 <= uint64_t(local_slots) && local_slots >= 64;
+  // (the grouper's insert/lookup passes stay on the global table: a growth here would move slots
+  // whose positional ids are live)
+  const bool low_card = a.mode == kModeFused && likely_groups * 2 <= uint64_t(local_slots) && local_slots >= 64;
   for (int round = 0; round < 8; ++round) {
     a.t = gb->table;
     if (low_card && round == 0) {
@@ -853,14 +861,13 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
         B200_CUDA(ctx, cudaFuncSetAttribute(gb_consume_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr = true;
       }
-      gb_consume_kernel<true><<<blocks, 1024, smem, ctx->stream>>>(a);
+      B200_TIMED(ctx, "groupby_consume", (gb_consume_kernel<true><<<blocks, 1024, smem, ctx->stream>>>(a)));
     } else {
       a.local_slots = 1;
       a.rows_per_block = 4096;
       const int64_t blocks = (n + a.rows_per_block - 1) / a.rows_per_block;
-      gb_consume_kernel<false><<<(unsigned)blocks, 256, 0, ctx->stream>>>(a);
+      B200_TIMED(ctx, "groupby_consume", (gb_consume_kernel<false><<<(unsigned)blocks, 256, 0, ctx->stream>>>(a)));
     }
-    B200_LAUNCHED(ctx);
     uint32_t c[4];
     B200_RETURN_NOT_OK(read_counters(gb, c));
     const uint32_t deferred = c[1];

@@ -102,6 +102,12 @@ B200_API const char* b200_last_error(b200_ctx* ctx);
 /* number of kernels this context has launched since creation (bench.py's gpu_launches) */
 B200_API int64_t b200_ctx_launch_count(b200_ctx* ctx);
 B200_API const char* b200_version(void);
+/* Optional measurement hook: when enabled every hot kernel launch is bracketed by CUDA events on
+ * the context's stream; b200_ctx_kernel_time sums the device time of the launches of one kernel
+ * ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume") since timing was
+ * (re)enabled.  Synchronises. */
+B200_API int b200_ctx_set_kernel_timing(b200_ctx* ctx, int enabled);
+B200_API int b200_ctx_kernel_time(b200_ctx* ctx, const char* name, double* total_ms, int64_t* launches);
 
 /* ---- Filter -------------------------------------------------------------------------------
  * null_selection: 0 = FilterOptions::DROP, 1 = FilterOptions::EMIT_NULL (api_vector.h:37-49).
