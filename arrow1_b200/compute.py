@@ -1,0 +1,181 @@
+"""Host-side mirror of the reference's public entry points for the hot path.
+
+    Filter(values, mask, null_selection)      == compute::Filter        (compute/api_vector.cc:94-99)
+    SortIndices(values, order)                == compute::SortIndices   (compute/api_vector.cc:48-53)
+    GroupBy(arguments, keys, aggregates)      == compute::internal::GroupBy
+                                                 (compute/kernels/hash_aggregate.cc:890-966)
+
+Same argument meaning and error behaviour (status codes of arrow::StatusCode carried by B200Error).
+Inputs are `Column`s; when they live in host memory (numpy buffers) they are staged to the GPU,
+the C-ABI kernels run there, and the result comes back to host memory: that round trip is what
+bench.py's `e2e` leg times.  Device-resident Columns (torch buffers, the analogue of
+arrow_cuda CudaBuffer-backed ArrayData) stay on the device.  Nothing here computes on the CPU.
+"""
+from __future__ import annotations
+
+import weakref
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import capi
+from .columns import BITS, AggSpec, Column
+
+DROP, EMIT_NULL = 0, 1          # FilterOptions::NullSelectionBehavior (api_vector.h:37-49)
+ASCENDING, DESCENDING = 0, 1    # SortOrder (api_vector.h:61-66)
+
+_contexts: Dict[int, capi.Context] = {}
+
+
+def default_context(device: Optional[int] = None) -> capi.Context:
+    """One shared context per device, the role default_exec_context() plays (compute/exec.cc:61-64)."""
+    if device is None:
+        device = torch.cuda.current_device() if torch.cuda.is_available() else 0
+    ctx = _contexts.get(device)
+    if ctx is None:
+        ctx = capi.Context(device)
+        _contexts[device] = ctx
+    return ctx
+
+
+class PinnedPool:
+    """Page-locked host staging buffers, reused across calls (cudaHostAlloc is slow)."""
+
+    def __init__(self):
+        self._free: Dict[int, List[torch.Tensor]] = {}
+
+    def get(self, nbytes: int) -> torch.Tensor:
+        size = 1 << max(int(nbytes - 1).bit_length(), 12)
+        lst = self._free.get(size)
+        if lst:
+            return lst.pop()
+        return torch.empty(size, dtype=torch.uint8, pin_memory=True)
+
+    def put(self, t: torch.Tensor) -> None:
+        self._free.setdefault(t.numel(), []).append(t)
+
+
+_pool = PinnedPool()
+
+
+def pinned_column(col: Column) -> Column:
+    """Copy of a host column whose buffers are page-locked (so H2D copies run at PCIe speed)."""
+    assert not col.on_device
+    d = _pool.get(col.data.nbytes)
+    d[: col.data.nbytes].numpy()[:] = col.data
+    v = None
+    if col.validity is not None:
+        v = _pool.get(col.validity.nbytes)
+        v[: col.validity.nbytes].numpy()[:] = col.validity
+    return Column(col.type, d[: col.data.nbytes].numpy(), None if v is None else v[: col.validity.nbytes].numpy(),
+                  col.length, col.offset, col.null_count)
+
+
+def _h2d(col: Column, ctx: capi.Context) -> Tuple[Column, int]:
+    if col.on_device:
+        return col, 0
+    dev = "cuda:%d" % ctx.device
+    d = torch.from_numpy(col.data).to(dev, non_blocking=True)
+    v = None
+    n = col.data.nbytes
+    if col.validity is not None:
+        v = torch.from_numpy(col.validity).to(dev, non_blocking=True)
+        n += col.validity.nbytes
+    return Column(col.type, d, v, col.length, col.offset, col.null_count), n
+
+
+def _d2h(t: torch.Tensor, nbytes: int) -> np.ndarray:
+    """Device bytes -> page-locked host buffer (returned as a numpy view; the caller owns it)."""
+    h = _pool.get(max(nbytes, 1))
+    h[:nbytes].copy_(t.view(torch.uint8).reshape(-1)[:nbytes], non_blocking=True)
+    arr = h[:nbytes].numpy()
+    weakref.finalize(arr, _pool.put, h)  # the staging buffer is recycled when the result dies
+    return arr
+
+
+class Transfer:
+    """Byte counts of the last call's staging copies (bench.py's h2d/d2h_bytes_per_step)."""
+    h2d = 0
+    d2h = 0
+
+
+def Filter(values: Column, mask: Column, null_selection: int = DROP, ctx: Optional[capi.Context] = None) -> Column:
+    ctx = ctx or default_context()
+    host = not values.on_device
+    dv, b0 = _h2d(values, ctx)
+    dm, b1 = _h2d(mask, ctx)
+    out = capi.filter(ctx, dv, dm, null_selection)
+    Transfer.h2d, Transfer.d2h = b0 + b1, 0
+    if not host:
+        return out.col
+    col = out.col
+    bits = BITS[col.type]
+    nd = (col.length + 7) // 8 if bits == 1 else col.length * (bits // 8)
+    data = _d2h(col.data, nd)
+    validity = None
+    nv = 0
+    if out.has_validity:
+        nv = (col.length + 7) // 8
+        validity = _d2h(col.validity, nv)
+    torch.cuda.current_stream(ctx.device).synchronize()
+    Transfer.d2h = nd + nv + 8
+    return Column(col.type, data, validity, col.length, 0, col.null_count)
+
+
+def SortIndices(values: Column, order: int = ASCENDING, ctx: Optional[capi.Context] = None):
+    """uint64 indices: numpy array for host input, int64-typed torch tensor for device input."""
+    ctx = ctx or default_context()
+    host = not values.on_device
+    dv, b0 = _h2d(values, ctx)
+    out = capi.sort_indices(ctx, dv, order)
+    Transfer.h2d, Transfer.d2h = b0, 0
+    if not host:
+        return out
+    h = _d2h(out, values.length * 8)
+    torch.cuda.current_stream(ctx.device).synchronize()
+    Transfer.d2h = values.length * 8
+    return h.view(np.uint64)
+
+
+class GroupByResult:
+    """Image of GroupBy's StructArray (hash_aggregate.cc:962-965): one entry per aggregate (a list
+    of (values, valid) pairs: two for hash_min_max) then the key columns, `num_groups` long."""
+
+    def __init__(self, num_groups, aggs, keys):
+        self.num_groups, self.aggs, self.keys = num_groups, aggs, keys
+
+
+def GroupBy(arguments: Sequence[Column], keys: Sequence[Column], aggregates: Sequence[AggSpec],
+            ctx: Optional[capi.Context] = None, expected_groups: int = 0):
+    ctx = ctx or default_context()
+    host = not keys[0].on_device
+    nbytes = 0
+    dkeys, dargs, seen = [], [], {}
+    for c in list(keys) + list(arguments):
+        key = (id(c.data), id(c.validity), c.offset)
+        if key not in seen:
+            seen[key], b = _h2d(c, ctx)
+            nbytes += b
+    dkeys = [seen[(id(c.data), id(c.validity), c.offset)] for c in keys]
+    dargs = [seen[(id(c.data), id(c.validity), c.offset)] for c in arguments]
+    out = capi.group_by(ctx, dkeys, aggregates, dargs, expected_groups=expected_groups)
+    Transfer.h2d, Transfer.d2h = nbytes, 0
+    if not host:
+        return out
+    d2h = 0
+    res_aggs = []
+    for cols_ in out.aggs:
+        lst = []
+        for c in cols_:
+            h = c.to_host()
+            d2h += h.nbytes()
+            lst.append((h.values().copy(), h.valid()))
+        res_aggs.append(lst)
+    res_keys = []
+    for c in out.keys:
+        h = c.to_host()
+        d2h += h.nbytes()
+        res_keys.append((h.values().copy(), h.valid()))
+    Transfer.d2h = d2h
+    return GroupByResult(out.num_groups, res_aggs, res_keys)

@@ -1,0 +1,584 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the Filter / SortIndices / grouped-aggregate hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+One JSON line on stdout (rank 0).  A "step" is one pass of the workload's operation over one
+batch of synthetic columns (arrow1_b200/synth.py, counter-based).  Workloads:
+
+    sort_i64    SortIndices ascending, 100 M int64 rows, 1 % nulls          (BASELINE configs[1], default)
+    sort_f64    SortIndices ascending, 100 M float64 rows, 1 % nulls        (BASELINE configs[1])
+    filter      Filter, 100 M int64 rows, 50 % mask, 1 % nulls              (configs[0] shape at the timed size)
+    filter_10m  Filter, 10 M rows                                           (configs[0] as written)
+    groupby_c3  hash_sum+hash_count+hash_min_max, (int32 key, float64), 1 K keys, 1 B rows   (configs[2])
+    groupby_c4  hash_sum+hash_mean, int64 keys, 100 M distinct, 1 B rows                     (configs[3])
+
+`value` = rows/s of the whole job with inputs resident in HBM; `e2e` = the same through
+arrow1_b200.compute (the reference-facing API) from pinned HOST buffers, copies inside the timed
+region.  `roofline` describes the workload's dominant kernel (per-launch CUDA events from the
+library's timing hook, taken over the timed steps); `cpu_baseline` is the reference's own CPU
+kernels (oracle/_ref) timed on this box's host cores on a bounded sample.  The default run adds a
+`workloads` object with the device-resident numbers of the other configs.
+
+`--impl reference` times the reference's CPU implementation (oracle/_ref, else the oracle port)
+of the same workload on the host cores and prints the same line with "impl": "reference".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+from concurrent.futures import ThreadPoolExecutor
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "rows/s & input GB/s (filter, sort_indices, hash_sum) at 1-8 B200; % HBM peak"
+L2_BYTES = 126 * 1024 * 1024
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------
+# workload definitions
+
+AGG_C3 = ("hash_sum", "hash_count", "hash_min_max")
+AGG_C4 = ("hash_sum", "hash_mean")
+
+
+class Workload:
+    name = ""
+    default_rows = 0
+    kernel = ""          # dominant kernel (name in the library's timing hook)
+    dtype = ""
+    description = ""
+
+    def __init__(self, rows):
+        self.n = rows
+
+    # generated columns (host when gen.device is None)
+    def make(self, gen, start=0, n=None):
+        raise NotImplementedError
+
+    def input_bytes(self):      # the reference benchmarks' convention
+        raise NotImplementedError
+
+    def alg_bytes_per_launch(self, launches_per_step):   # dominant kernel, per launch
+        raise NotImplementedError
+
+    def prepare(self, ctx, cols_):   # device buffers reused across steps
+        return None
+
+    def step(self, ctx, cols_, bufs):
+        raise NotImplementedError
+
+    def e2e_step(self, host_cols):
+        raise NotImplementedError
+
+    def cpu_step(self, oracle, kind, host_cols):
+        raise NotImplementedError
+
+
+class SortWL(Workload):
+    kernel = "sort_pass"
+
+    def __init__(self, rows, dtype):
+        super().__init__(rows)
+        self.dt = dtype
+        self.name = "sort_i64" if dtype == "int64" else "sort_f64"
+        self.dtype = "u64 radix keys (%s column)" % dtype
+        self.description = "SortIndices ascending, %d %s rows, 1%% nulls (at end), stable" % (rows, dtype)
+
+    def make(self, gen, start=0, n=None):
+        return (gen.sort_c2(n or self.n, self.dt, start),)
+
+    def input_bytes(self):
+        return self.n * 8
+
+    def alg_bytes_per_launch(self, launches_per_step):
+        # 8 live digit passes of a 64-bit column (DESIGN.md "Sort"): first reads 8.125 B/row and
+        # writes key+row number (12), six middle passes read 12 write 12, the last reads 12 writes 8
+        total = self.n * (8.125 + 12 + 6 * 24 + 12 + 8)
+        return total / max(launches_per_step, 1)
+
+    def prepare(self, ctx, cols_):
+        import torch
+        from arrow1_b200 import capi
+        return {"out": torch.empty(self.n, dtype=torch.int64, device="cuda:%d" % ctx.device),
+                "scratch": ctx.empty(capi.sort_scratch_bytes(ctx, self.n))}
+
+    def step(self, ctx, cols_, bufs):
+        from arrow1_b200 import capi
+        return capi.sort_indices(ctx, cols_[0], 0, 0, bufs["out"], bufs["scratch"])
+
+    def e2e_step(self, host_cols):
+        from arrow1_b200 import compute
+        return compute.SortIndices(host_cols[0], compute.ASCENDING)
+
+    def cpu_step(self, oracle, kind, host_cols):
+        return oracle.sort_indices(host_cols[0], 0, 0, kind=kind)
+
+
+class FilterWL(Workload):
+    kernel = "filter_apply"
+    dtype = "u64 (bit copy of int64) + bitmaps"
+
+    def __init__(self, rows, name):
+        super().__init__(rows)
+        self.name = name
+        self.description = "Filter, %d int64 rows, 50%% boolean mask, 1%% value nulls, DROP" % rows
+        self.out_len = None
+
+    def make(self, gen, start=0, n=None):
+        return gen.filter_c1(n or self.n, start)
+
+    def input_bytes(self):
+        return self.n * 8   # values buffer only (vector_selection_benchmark.cc:92-97)
+
+    def alg_bytes_per_launch(self, launches_per_step):
+        sel = (self.out_len or self.n // 2)
+        return self.n * (8 + 1 / 8 + 1 / 8) + sel * (8 + 1 / 8)
+
+    def prepare(self, ctx, cols_):
+        return {"data": ctx.empty(self.n * 8), "validity": ctx.empty((self.n + 7) // 8)}
+
+    def step(self, ctx, cols_, bufs):
+        from arrow1_b200 import capi
+        plan = capi.FilterPlan(ctx, cols_[1], 0, sync=True)   # GetFilterOutputSize -> host (vector_selection.cc:61-88)
+        self.out_len = plan.out_length
+        return plan.apply(cols_[0], bufs["data"], bufs["validity"])
+
+    def e2e_step(self, host_cols):
+        from arrow1_b200 import compute
+        return compute.Filter(host_cols[0], host_cols[1], compute.DROP)
+
+    def cpu_step(self, oracle, kind, host_cols):
+        return oracle.filter(host_cols[0], host_cols[1], 0, kind=kind)
+
+
+class GroupByWL(Workload):
+    kernel = "groupby_consume"
+
+    def __init__(self, rows, which):
+        super().__init__(rows)
+        self.which = which
+        self.name = "groupby_" + which
+        if which == "c3":
+            self.n_keys, self.agg_names = 1000, AGG_C3
+            self.dtype = "f64 sums / u64 counts, int32 keys"
+            self.description = "hash_sum+hash_count+hash_min_max over %d rows of (int32 key, float64 value), 1K keys, 1%% nulls" % rows
+        else:
+            self.n_keys, self.agg_names = min(100_000_000, max(rows // 10, 1)), AGG_C4
+            self.dtype = "f64 sums / u64 counts, int64 keys"
+            self.description = "hash_sum+hash_mean over %d rows of (int64 key, float64 value), %d distinct keys" % (rows, self.n_keys)
+
+    def _specs(self):
+        from arrow1_b200 import columns as cols
+        kind = {"hash_sum": cols.HASH_SUM, "hash_count": cols.HASH_COUNT, "hash_min_max": cols.HASH_MIN_MAX,
+                "hash_mean": cols.HASH_MEAN}
+        return [cols.AggSpec(kind[a]) for a in self.agg_names]
+
+    def make(self, gen, start=0, n=None):
+        if self.which == "c3":
+            return gen.groupby_c3(n or self.n, self.n_keys, start)
+        return gen.groupby_c4(n or self.n, self.n_keys, start)
+
+    def input_bytes(self):
+        return self.n * (12 if self.which == "c3" else 16)
+
+    def alg_bytes_per_launch(self, launches_per_step):
+        per_row = 4 + 8 + 1 / 8 if self.which == "c3" else 16
+        return self.n * per_row / max(launches_per_step, 1)
+
+    def step(self, ctx, cols_, bufs):
+        from arrow1_b200 import capi
+        k, v = cols_
+        return capi.group_by(ctx, [k], self._specs(), [v] * len(self.agg_names), expected_groups=self.n_keys)
+
+    def e2e_step(self, host_cols):
+        from arrow1_b200 import compute
+        k, v = host_cols
+        return compute.GroupBy([v] * len(self.agg_names), [k], self._specs(), expected_groups=self.n_keys)
+
+    def cpu_step(self, oracle, kind, host_cols):
+        k, v = host_cols
+        return oracle.groupby([k], self._specs(), [v] * len(self.agg_names), kind=kind, max_groups=self.n_keys + 2)
+
+
+def make_workload(name, rows=None):
+    if name == "sort_i64":
+        return SortWL(rows or 100_000_000, "int64")
+    if name == "sort_f64":
+        return SortWL(rows or 100_000_000, "float64")
+    if name == "filter":
+        return FilterWL(rows or 100_000_000, "filter")
+    if name == "filter_10m":
+        return FilterWL(rows or 10_000_000, "filter_10m")
+    if name == "groupby_c3":
+        return GroupByWL(rows or 1_000_000_000, "c3")
+    if name == "groupby_c4":
+        return GroupByWL(rows or 1_000_000_000, "c4")
+    raise SystemExit("unknown workload %s" % name)
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return None
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 7:
+                    continue
+                try:
+                    sm.append(float(f[0]))
+                    mx.append(float(f[1]))
+                except ValueError:
+                    continue
+                for nm, val in zip(names, f[3:7]):
+                    if val.lower().startswith("active"):
+                        reasons.add(nm)
+        finally:
+            try:
+                os.unlink(self.path)
+            except OSError:
+                pass
+        if not sm:
+            return None
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# reference / cpu baseline
+
+def host_threads():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def cpu_sample_rows(wl, threads):
+    per_thread = {"sort_i64": 2_000_000, "sort_f64": 2_000_000, "filter": 16_000_000, "filter_10m": 10_000_000,
+                  "groupby_c3": 8_000_000, "groupby_c4": 4_000_000}[wl.name]
+    return per_thread
+
+
+def run_cpu(wl, steps, warmup, threads):
+    """Times the reference's CPU kernels on `threads` independent row-range shards (the kernels
+    are single-threaded by construction, compute/exec.h:86-92): rows/s = rows of all shards / time.
+    Sort and group-by shards are not merged, i.e. an upper bound for the CPU."""
+    import oracle
+    from arrow1_b200 import synth
+    kind = "reference" if oracle.have_reference() else "port"
+    if kind == "port":
+        oracle.build()
+    per = cpu_sample_rows(wl, threads)
+    gen = synth.Gen(None)
+    shards = [wl.make(gen, start=i * per, n=per) for i in range(threads)]
+    sub = make_workload(wl.name, per)
+    pool = ThreadPoolExecutor(max_workers=threads)
+
+    def one():
+        t0 = time.perf_counter()
+        list(pool.map(lambda cols_: sub.cpu_step(oracle, kind, cols_), shards))
+        return time.perf_counter() - t0
+
+    for _ in range(warmup):
+        one()
+    times = [one() for _ in range(steps)]
+    pool.shutdown()
+    total = sum(times)
+    rows = per * threads
+    return {"rows_per_s": rows * steps / total, "ms_per_step": 1e3 * total / steps, "kind": kind, "cores": threads,
+            "sample": "%d independent shards x %d rows of the %s columns (same generator), one reference call per shard "
+                      "per step, %d steps; shards not merged" % (threads, per, wl.name, steps)}
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    wl = make_workload(args.workload, args.rows)
+    threads = host_threads()
+    r = run_cpu(wl, max(args.steps, 1), min(args.warmup, 1) if args.warmup else 0, threads)
+    line = {
+        "metric": METRIC, "impl": "reference", "value": r["rows_per_s"], "unit": "rows/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": wl.dtype, "data": "synthetic",
+        "config": {"workload": wl.name, "description": wl.description, "rows_full_config": wl.n,
+                   "note": "CPU reference on a bounded sample of the workload"},
+        "cpu_baseline": {"value": r["rows_per_s"], "unit": "rows/s", "cores": r["cores"], "kind": r["kind"],
+                         "sample": r["sample"]},
+        "e2e": {"value": r["rows_per_s"], "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "input_gbs": r["rows_per_s"] * wl.input_bytes() / wl.n / 1e9,
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+
+def kernel_times(ctx, names):
+    import ctypes as C
+    from arrow1_b200 import capi
+    out = {}
+    for nm in names:
+        ms, n = C.c_double(0), C.c_int64(0)
+        capi.lib().b200_ctx_kernel_time(ctx._h, nm.encode(), C.byref(ms), C.byref(n))
+        out[nm] = (ms.value, n.value)
+    return out
+
+
+ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume")
+
+
+def time_device(ctx, wl, cols_, steps, warmup, world, dist_step=None):
+    """W warm-up + K timed steps with per-launch kernel events; returns per-step ms (max over
+    ranks when world > 1), kernel times, launch count."""
+    import torch
+    from arrow1_b200 import capi
+    bufs = wl.prepare(ctx, cols_)
+    fn = (lambda: dist_step(ctx, wl, cols_, bufs)) if dist_step else (lambda: wl.step(ctx, cols_, bufs))
+    for _ in range(warmup):
+        fn()
+    capi.lib().b200_ctx_set_kernel_timing(ctx._h, 1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+    l0 = ctx.launches
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    launches = ctx.launches - l0
+    kt = kernel_times(ctx, ALL_KERNELS)
+    capi.lib().b200_ctx_set_kernel_timing(ctx._h, 0)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms / steps, kt, launches, bufs
+
+
+def roofline_of(wl, kt, steps, peak, peak_src):
+    total_ms, n = kt.get(wl.kernel, (0.0, 0))
+    if n == 0:
+        return None
+    per_launch_ms = total_ms / n
+    alg = wl.alg_bytes_per_launch(n / steps)
+    achieved = alg / (per_launch_ms * 1e-3) / 1e9
+    return {"bound": "hbm", "kernel": wl.kernel, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "frac_of_8TBs": achieved / 8000.0, "traffic": None, "peak_source": peak_src,
+            "launches_per_step": n / steps, "avg_launch_ms": per_launch_ms, "algorithmic_bytes_per_launch": alg,
+            "kernel_share_of_step_events": None}
+
+
+def gpu_arm(args):
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        log("bench: --gpus %d but WORLD_SIZE %d; using WORLD_SIZE" % (args.gpus, world))
+    torch.cuda.set_device(local)
+    dist_step = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda:%d" % local))
+        from arrow1_b200 import dist as b200_dist
+        dist_step = b200_dist.bench_step
+    from arrow1_b200 import capi, compute, synth
+    ctx = compute.default_context(local)
+    peak, peak_src = measured_peak()
+    wl = make_workload(args.workload, args.rows)
+    gen = synth.Gen("cuda:%d" % local)
+    t0 = time.time()
+    cols_ = wl.make(gen, start=rank * wl.n)
+    torch.cuda.synchronize()
+    log("[rank %d] generated %s in %.1f s" % (rank, wl.name, time.time() - t0))
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms_step, kt, launches, bufs = time_device(ctx, wl, cols_, args.steps, args.warmup, world, dist_step)
+    clocks = sampler.stop()
+    rows_total = wl.n * world
+    value = rows_total / (ms_step * 1e-3)
+    roof = roofline_of(wl, kt, args.steps, peak, peak_src)
+    if roof:
+        roof["kernel_share_of_step_events"] = (kt[wl.kernel][0] / args.steps) / ms_step
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if roof and os.path.exists(traffic_file):
+        try:
+            roof["traffic"] = json.load(open(traffic_file)).get(wl.name, {}).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+
+    # ---- e2e: host (pinned) -> device -> op -> host, through arrow1_b200.compute
+    e2e = None
+    if not args.no_e2e:
+        e2e_rows = wl.n if wl.n <= 200_000_000 else 200_000_000
+        sub = make_workload(wl.name, e2e_rows)
+        hgen = synth.Gen(None)
+        t0 = time.time()
+        host_cols = tuple(compute.pinned_column(c) for c in sub.make(hgen, start=rank * wl.n, n=e2e_rows))
+        log("[rank %d] host columns for e2e (%d rows) in %.1f s" % (rank, e2e_rows, time.time() - t0))
+        if world > 1:
+            from arrow1_b200 import dist as b200_dist
+            e2e_fn = lambda: b200_dist.bench_e2e_step(ctx, sub, host_cols)  # noqa: E731
+        else:
+            e2e_fn = lambda: sub.e2e_step(host_cols)  # noqa: E731
+        for _ in range(2):
+            r = e2e_fn()
+            del r
+        e2e_steps = max(3, min(args.steps, 10))
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(e2e_steps):
+            r = e2e_fn()
+            del r
+        e1.record()
+        torch.cuda.synchronize()
+        ems = e0.elapsed_time(e1) / e2e_steps
+        if world > 1:
+            t = torch.tensor([ems], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ems = float(t.item())
+        e2e = {"value": e2e_rows * world / (ems * 1e-3), "unit": "rows/s", "h2d_bytes_per_step": compute.Transfer.h2d,
+               "d2h_bytes_per_step": compute.Transfer.d2h, "ms_per_step": ems, "rows_per_step_per_gpu": e2e_rows,
+               "api": "arrow1_b200.compute (mirror of compute::Filter / SortIndices / internal::GroupBy)"}
+        del host_cols
+
+    # ---- the other configs, device-resident numbers only
+    extras = {}
+    if rank == 0 and world == 1 and not args.no_extras:
+        del cols_, bufs
+        torch.cuda.empty_cache()
+        for name in ("filter", "filter_10m", "sort_i64", "sort_f64", "groupby_c3"):
+            if name == wl.name:
+                continue
+            try:
+                w2 = make_workload(name, None)
+                c2 = w2.make(gen)
+                k2 = max(3, min(args.steps, 10))
+                ms2, kt2, l2, b2 = time_device(ctx, w2, c2, k2, 3, 1)
+                r2 = roofline_of(w2, kt2, k2, peak, peak_src)
+                extras[name] = {"rows": w2.n, "ms_per_step": ms2, "rows_per_s": w2.n / (ms2 * 1e-3),
+                                "input_gbs": w2.input_bytes() / (ms2 * 1e-3) / 1e9, "gpu_launches": l2,
+                                "roofline": r2, "description": w2.description}
+                del c2, b2
+                torch.cuda.empty_cache()
+            except Exception as ex:  # an extra must never take the main line down
+                extras[name] = {"error": repr(ex)[:300]}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        try:
+            r = run_cpu(wl, 2, 1, host_threads())
+            cpu = {"value": r["rows_per_s"], "unit": "rows/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]}
+        except Exception as ex:
+            cpu = {"value": None, "unit": "rows/s", "cores": 0, "kind": "port", "sample": "failed: %r" % (ex,)}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": wl.dtype,
+            "data": "synthetic",
+            "config": {"workload": wl.name, "description": wl.description, "rows_per_gpu": wl.n, "rows_total": rows_total,
+                       "l2": "inputs (%.0f MB per step) larger than the 126 MB L2; no explicit flush" % (wl.input_bytes() / 1e6)
+                       if wl.input_bytes() > 2 * L2_BYTES else "inputs fit in L2: numbers are L2-warm",
+                       "parallelism": "row-range shards, one process per GPU" if world > 1 else "single GPU"},
+            "input_gbs": value * wl.input_bytes() / wl.n / 1e9,
+            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "kernel_ms_per_step": {k: v[0] / args.steps for k, v in kt.items() if v[1]},
+        }
+        if extras:
+            line["workloads"] = extras
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="sort_i64")
+    ap.add_argument("--rows", type=int, default=None, help="rows per GPU (default: the config's size)")
+    ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        log("bench: warmup raised to 3 (timing rules)")
+        args.warmup = 3
+    if args.impl == "reference":
+        return reference_arm(args)
+    return gpu_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

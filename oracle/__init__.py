@@ -169,9 +169,10 @@ class GroupByResult:
 
 
 def groupby(keys: Sequence[Column], aggs: Sequence[AggSpec], args: Sequence[Column], want_ids: bool = False,
-            kind: str = "port") -> GroupByResult:
+            kind: str = "port", max_groups: Optional[int] = None) -> GroupByResult:
+    """`max_groups` bounds the output buffers when the caller knows the cardinality (default: n)."""
     n = keys[0].length
-    cap = max(n, 1)
+    cap = max(n if max_groups is None else min(n, max_groups), 1)
     specs = (b200_agg_spec * max(len(aggs), 1))()
     out_types = []
     for j, a in enumerate(aggs):
@@ -190,7 +191,7 @@ def groupby(keys: Sequence[Column], aggs: Sequence[AggSpec], args: Sequence[Colu
         oc, d, v = _out_col(k.type, cap)
         out_keys[i] = oc
         key_holders.append((k.type, d, v))
-    ids = np.zeros(cap, dtype=np.uint32) if want_ids else None
+    ids = np.zeros(max(n, 1), dtype=np.uint32) if want_ids else None
     num_groups = C.c_uint32(0)
     _check(kind, _fn(kind, "groupby")(C.c_int(len(keys)), col_array(keys), C.c_int(len(aggs)), specs, col_array(args),
                                       out_aggs, out_keys, C.byref(num_groups),
