@@ -207,6 +207,17 @@ def sort_keys(ctx: Context, values: Column, order: int = 0) -> torch.Tensor:
     return out[: values.length]
 
 
+def sort_keys_rows(ctx: Context, values: Column, order: int = 0, index_base: int = 0):
+    """(radix keys, (index_base + row) | class << 62) as two int64-typed tensors."""
+    n = values.length
+    keys = torch.empty(max(n, 1), dtype=torch.int64, device="cuda:%d" % ctx.device)
+    rows = torch.empty(max(n, 1), dtype=torch.int64, device="cuda:%d" % ctx.device)
+    v = values.desc()
+    ctx.check(lib().b200_sort_keys_rows(ctx._h, C.byref(v), C.c_int(order), C.c_uint64(index_base),
+                                        C.c_void_p(keys.data_ptr()), C.c_void_p(rows.data_ptr())))
+    return keys[:n], rows[:n]
+
+
 def sort_pairs(ctx: Context, keys: torch.Tensor, payload: torch.Tensor, want_keys: bool = False):
     n = keys.numel()
     nb = C.c_size_t(0)

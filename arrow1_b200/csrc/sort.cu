@@ -460,12 +460,13 @@ __global__ void __launch_bounds__(kThreads, 3) sort_pass_kernel(SortParams p, in
   else sort_pass_body<kClass, false>(p, d, info, s, tile, tile_items);
 }
 
-__global__ void sort_keys_kernel(SortParams p, uint64_t* out) {
+__global__ void sort_keys_kernel(SortParams p, uint64_t* out, uint64_t* out_rows) {
   const int64_t row = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
   if (row < p.n) {
     uint32_t cls;
     const uint64_t k = source_key(p, row, &cls);
     out[row] = cls == 2 ? kNullKeyOut : (cls == 1 ? kNanKeyOut : k);
+    if (out_rows) out_rows[row] = (p.index_base + uint64_t(row)) | (uint64_t(cls) << 62);
   }
 }
 
@@ -586,16 +587,24 @@ int b200_sort_indices(b200_ctx* ctx, const b200_col* values, int order, uint64_t
   return run_sort(ctx, p, scratch, scratch_bytes);
 }
 
-int b200_sort_keys(b200_ctx* ctx, const b200_col* values, int order, uint64_t* out_keys) {
+int b200_sort_keys_rows(b200_ctx* ctx, const b200_col* values, int order, uint64_t index_base, uint64_t* out_keys,
+                        uint64_t* out_rows) {
   if (!ctx) return B200_INVALID;
   SortParams p;
   memset(&p, 0, sizeof(p));
   B200_RETURN_NOT_OK(fill_column_source(ctx, values, order, &p));
   if (p.n == 0) return B200_OK;
   if (!out_keys) return b200_fail(ctx, B200_INVALID, "sort_keys: null output");
-  sort_keys_kernel<<<(unsigned)((p.n + 255) / 256), 256, 0, ctx->stream>>>(p, out_keys);
+  if (out_rows && index_base + uint64_t(p.n) > (uint64_t(1) << 62))
+    return b200_fail(ctx, B200_INDEX_ERROR, "sort_keys: row numbers beyond 2^62");
+  p.index_base = index_base;
+  sort_keys_kernel<<<(unsigned)((p.n + 255) / 256), 256, 0, ctx->stream>>>(p, out_keys, out_rows);
   B200_LAUNCHED(ctx);
   return B200_OK;
+}
+
+int b200_sort_keys(b200_ctx* ctx, const b200_col* values, int order, uint64_t* out_keys) {
+  return b200_sort_keys_rows(ctx, values, order, 0, out_keys, nullptr);
 }
 
 int b200_sort_pairs(b200_ctx* ctx, const uint64_t* keys, const uint64_t* payload, int64_t length,

@@ -1,0 +1,246 @@
+"""Multi-GPU forms of the hot path: one process per GPU, rows range-sharded.
+
+    dist_filter        no collective: every rank compacts its own row range; the result stays
+                       sharded, rank order == row order (a ChunkedArray with one chunk per rank).
+    dist_sort_indices  sample sort: local stable radix sort of (key, global row) pairs, splitters
+                       from an all-gathered regular sample, one all-to-all of contiguous runs over
+                       NVLink, local stable radix sort of the received runs.  Reproduces
+                       ChunkedArraySorter's global stable order with NaNs then nulls last
+                       (compute/kernels/vector_sort.cc:657-832).
+    dist_group_by      low cardinality: every rank aggregates its rows into a partial table (first
+                       rows are GLOBAL row numbers), the occupied slots are all-gathered and merged
+                       in rank order on every rank (== HashAggregateKernel::merge, which the
+                       reference leaves unimplemented, hash_aggregate.cc:795-798).
+                       high cardinality: rows are hash-partitioned by key, exchanged with one
+                       all-to-all, and each rank aggregates a disjoint key set.
+
+torch.distributed (NCCL on GPUs, gloo in the CPU tests) is the plumbing; all computation goes
+through a `LocalOps` object — `CudaOps` (the C ABI) in the product; the tests substitute a numpy
+stand-in to exercise the exchange logic with gloo on CPU.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from .columns import AggSpec, Column
+
+_I64_MIN = -(1 << 63)
+_ROW_MASK = (1 << 62) - 1
+_TAIL_KEY_BIASED = ((1 << 64) - 2) ^ (1 << 63)   # biased image of the NaN key 2^64-2 (== INT64_MAX - 1)
+OVERSAMPLE = 256
+
+
+def _bias(keys: torch.Tensor) -> torch.Tensor:
+    """uint64 keys held in int64 -> int64 whose signed order is the unsigned key order."""
+    return keys ^ _I64_MIN
+
+
+class CudaOps:
+    """LocalOps over the C ABI (arrow1_b200.capi)."""
+
+    def __init__(self, ctx):
+        from . import capi
+        self.capi, self.ctx = capi, ctx
+        self.device = torch.device("cuda:%d" % ctx.device)
+
+    def sort_keys_rows(self, col: Column, order: int, index_base: int):
+        return self.capi.sort_keys_rows(self.ctx, col, order, index_base)
+
+    def sort_pairs(self, keys: torch.Tensor, rows: torch.Tensor):
+        if keys.numel() == 0:
+            return keys, rows
+        return self.capi.sort_pairs(self.ctx, keys, rows, want_keys=True)
+
+    def filter(self, values: Column, mask: Column, null_selection: int):
+        return self.capi.filter(self.ctx, values, mask, null_selection)
+
+    def groupby(self, key_types, aggs, arg_types, expected_groups):
+        return self.capi.GroupBy(self.ctx, key_types, aggs, arg_types, expected_groups)
+
+
+# ------------------------------------------------------------------------------------------------
+def dist_filter(ops, values: Column, mask: Column, null_selection: int = 0):
+    """Filter of a row-range shard.  No collective: shard boundaries are arbitrary
+    because every bitmap is addressed by (buffer, bit offset)."""
+    return ops.filter(values, mask, null_selection)
+
+
+# ------------------------------------------------------------------------------------------------
+def choose_splitters(samples: torch.Tensor, world: int) -> torch.Tensor:
+    """`samples`: the biased keys every rank sampled from its sorted run, concatenated (empty
+    ranks contribute none).  Returns world-1 splitters; rank j owns biased keys in
+    [splitter[j-1], splitter[j]).  Keys >= the NaN key (NaN / null / genuine maxima) all belong to
+    the last rank so that one rank can order the three classes (see dist_sort_indices)."""
+    if samples.numel() == 0:
+        return torch.full((world - 1,), _TAIL_KEY_BIASED, dtype=torch.int64, device=samples.device)
+    s, _ = torch.sort(samples)
+    pos = (torch.arange(1, world, device=samples.device, dtype=torch.int64) * s.numel()) // world
+    spl = s[pos.clamp(max=s.numel() - 1)]
+    return torch.clamp(spl, max=_TAIL_KEY_BIASED)
+
+
+def sample_sorted(biased_sorted: torch.Tensor, count: int) -> torch.Tensor:
+    n = biased_sorted.numel()
+    if n == 0:
+        return biased_sorted[:0]
+    m = min(count, n)
+    pos = ((torch.arange(m, device=biased_sorted.device, dtype=torch.int64) * 2 + 1) * n) // (2 * m)
+    return biased_sorted[pos]
+
+
+def class_fixup(keys_sorted: torch.Tensor, rows_sorted: torch.Tensor) -> torch.Tensor:
+    """Rows whose key is >= the NaN key: genuine values first (already in key, row order), then
+    NaNs, then nulls, each in global row order (vector_sort.cc:269-302).  Returns row numbers
+    with the class bits stripped."""
+    biased = _bias(keys_sorted)
+    start = int(torch.searchsorted(biased, torch.tensor([_TAIL_KEY_BIASED], dtype=torch.int64, device=biased.device)).item())
+    tail = rows_sorted[start:]
+    if tail.numel():
+        cls = (tail >> 62) & 3
+        if bool((cls != 0).any()):
+            tail = torch.cat([tail[cls == 0], tail[cls == 1], tail[cls == 2]])
+            rows_sorted = torch.cat([rows_sorted[:start], tail])
+    return rows_sorted & _ROW_MASK
+
+
+def dist_sort_indices(ops, col: Column, order: int, row_base: int, group=None):
+    """Global SortIndices over the concatenation of every rank's shard (rank order == row order).
+    Returns (indices, global_offset): this rank's contiguous slice of the global uint64 index
+    array (int64-typed tensor) and where it starts."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    keys, rows = ops.sort_keys_rows(col, order, row_base)
+    ks, rs = ops.sort_pairs(keys, rows)
+    if world == 1:
+        return class_fixup(ks, rs), 0
+    dev = ks.device
+    biased = _bias(ks)
+    # ---- splitters from a regular sample of every rank's sorted run
+    smp = torch.full((OVERSAMPLE,), 0, dtype=torch.int64, device=dev)
+    got = sample_sorted(biased, OVERSAMPLE)
+    smp[: got.numel()] = got
+    meta = torch.tensor([got.numel()], dtype=torch.int64, device=dev)
+    all_smp = torch.empty(world * OVERSAMPLE, dtype=torch.int64, device=dev)
+    all_meta = torch.empty(world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(all_smp, smp, group=group)
+    dist.all_gather_into_tensor(all_meta, meta, group=group)
+    counts = all_meta.tolist()
+    valid = torch.cat([all_smp[r * OVERSAMPLE: r * OVERSAMPLE + counts[r]] for r in range(world)])
+    splitters = choose_splitters(valid, world)
+    # ---- contiguous runs of the sorted local data go to each rank
+    cuts = torch.searchsorted(biased, splitters).tolist() if biased.numel() else [0] * (world - 1)
+    bounds = [0] + cuts + [biased.numel()]
+    send_counts = [bounds[j + 1] - bounds[j] for j in range(world)]
+    sc = torch.tensor(send_counts, dtype=torch.int64, device=dev)
+    rc = torch.empty(world, dtype=torch.int64, device=dev)
+    dist.all_to_all_single(rc, sc, group=group)
+    recv_counts = rc.tolist()
+    total = sum(recv_counts)
+    rk = torch.empty(total, dtype=torch.int64, device=dev)
+    rr = torch.empty(total, dtype=torch.int64, device=dev)
+    dist.all_to_all_single(rk, ks.contiguous(), recv_counts, send_counts, group=group)
+    dist.all_to_all_single(rr, rs.contiguous(), recv_counts, send_counts, group=group)
+    # ---- runs arrive in source-rank order == global row order, so a stable sort by key yields
+    # the (key, global row) order
+    ks2, rs2 = ops.sort_pairs(rk, rr)
+    out = class_fixup(ks2, rs2) if rank == world - 1 else (rs2 & _ROW_MASK)
+    # where this rank's slice starts in the global result
+    tot = torch.tensor([total], dtype=torch.int64, device=dev)
+    all_tot = torch.empty(world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(all_tot, tot, group=group)
+    offset = int(all_tot[:rank].sum().item())
+    return out, offset
+
+
+# ------------------------------------------------------------------------------------------------
+def dist_group_by(ops, keys: Sequence[Column], aggs: Sequence[AggSpec], args: Sequence[Column], row_base: int,
+                  expected_groups: int = 0, group=None):
+    """Low-cardinality grouped aggregation: local partial table -> all-gather of the occupied
+    slots -> merge in rank order on every rank (bitwise identical results on all ranks; float
+    sums within the stated tolerance of the single-pass result).  Returns the finalized output of
+    the merged table (every rank holds the full result, in the reference's first-occurrence
+    order because first rows are global)."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    key_types = [k.type for k in keys]
+    arg_types = [a.type for a in args]
+    part = ops.groupby(key_types, aggs, arg_types, expected_groups)
+    try:
+        part.consume(keys, args, row_base)
+        if world == 1:
+            return part.finalize()
+        state = part.export_state()
+        sb = part.slot_bytes()
+        dev = state.device
+        n = torch.tensor([state.numel()], dtype=torch.int64, device=dev)
+        all_n = torch.empty(world, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(all_n, n, group=group)
+        sizes = all_n.tolist()
+        cap = max(max(sizes), sb)
+        padded = torch.zeros(cap, dtype=torch.uint8, device=dev)
+        padded[: state.numel()] = state
+        gathered = torch.empty(world * cap, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(gathered, padded, group=group)
+        merged = ops.groupby(key_types, aggs, arg_types, max(expected_groups, max(sizes) // sb))
+        try:
+            for r in range(world):
+                if sizes[r]:
+                    merged.import_state(gathered[r * cap: r * cap + sizes[r]])
+            return merged.finalize()
+        finally:
+            merged.close()
+    finally:
+        part.close()
+
+
+# ------------------------------------------------------------------------------------------------
+# bench.py hooks: one step of a workload over this rank's shard
+
+def _rank_world():
+    return (dist.get_rank(), dist.get_world_size()) if dist.is_initialized() else (0, 1)
+
+
+def bench_step(ctx, wl, cols_, bufs):
+    ops = CudaOps(ctx)
+    rank, _ = _rank_world()
+    if wl.name.startswith("sort"):
+        return dist_sort_indices(ops, cols_[0], 0, rank * wl.n)
+    if wl.name.startswith("filter"):
+        return wl.step(ctx, cols_, bufs)
+    if wl.name == "groupby_c3":
+        k, v = cols_
+        return dist_group_by(ops, [k], wl._specs(), [v] * len(wl.agg_names), rank * wl.n, wl.n_keys)
+    raise SystemExit("bench: workload %s has no multi-GPU form yet" % wl.name)
+
+
+def bench_e2e_step(ctx, wl, host_cols):
+    """Host shard -> device -> multi-GPU op -> host (the result slice / merged groups)."""
+    from . import compute
+    ops = CudaOps(ctx)
+    rank, _ = _rank_world()
+    dev_cols, nbytes = [], 0
+    for c in host_cols:
+        d, b = compute._h2d(c, ctx)
+        dev_cols.append(d)
+        nbytes += b
+    compute.Transfer.h2d = nbytes
+    if wl.name.startswith("sort"):
+        out, _ = dist_sort_indices(ops, dev_cols[0], 0, rank * wl.n)
+        h = compute._d2h(out, out.numel() * 8)
+        torch.cuda.current_stream().synchronize()
+        compute.Transfer.d2h = out.numel() * 8
+        return h
+    if wl.name.startswith("filter"):
+        return wl.e2e_step(host_cols)
+    if wl.name == "groupby_c3":
+        k, v = dev_cols
+        res = dist_group_by(ops, [k], wl._specs(), [v] * len(wl.agg_names), rank * wl.n, wl.n_keys)
+        d2h = 0
+        for cols__ in res.aggs:
+            for c in cols__:
+                d2h += c.to_host().nbytes()
+        compute.Transfer.d2h = d2h
+        return res
+    raise SystemExit("bench: workload %s has no multi-GPU form yet" % wl.name)

@@ -161,6 +161,11 @@ B200_API int b200_sort_indices(b200_ctx* ctx, const b200_col* values, int order,
  * NaN -> 2^64-2, null -> 2^64-1) so that ranks can exchange (key, global row) pairs;
  * sort_pairs stably sorts such pairs by key, ties by their input order. */
 B200_API int b200_sort_keys(b200_ctx* ctx, const b200_col* values, int order, uint64_t* out_keys);
+/* As b200_sort_keys, and also writes out_rows[i] = (index_base + i) | class << 62 with class
+ * 0 = value, 1 = NaN, 2 = null: the (key, global row) pairs a rank sends in the sample sort, the
+ * class letting the receiver tell a null from a genuine maximum key. */
+B200_API int b200_sort_keys_rows(b200_ctx* ctx, const b200_col* values, int order, uint64_t index_base,
+                                 uint64_t* out_keys, uint64_t* out_rows /* nullable */);
 B200_API int b200_sort_pairs_scratch_bytes(int64_t length, size_t* out_bytes);
 B200_API int b200_sort_pairs(b200_ctx* ctx, const uint64_t* keys, const uint64_t* payload,
                              int64_t length, uint64_t* out_keys /* nullable */,
