@@ -79,6 +79,7 @@ struct GbArgs {
   uint32_t* claimed;         // grouper: newly claimed slot indices
   uint32_t* slot_ids;        // grouper: dense id per slot
   uint32_t* out_ids;         // grouper lookup output
+  uint64_t* zf_scratch;      // fast path: per-CTA earliest-zero-row words [grid][kFastGroups]
   int32_t local_slots;       // shared-memory table size (power of two), 0 = none
   int32_t rows_per_block;
 };
@@ -324,7 +325,12 @@ __global__ void __launch_bounds__(kLocal ? 1024 : 256) gb_consume_kernel(const _
 
   const int64_t begin = int64_t(blockIdx.x) * a.rows_per_block;
   const int64_t end = min(a.n, begin + a.rows_per_block);
-  for (int64_t row = begin + threadIdx.x; row < end; row += blockDim.x) {
+  // trip count made warp-uniform so that the warp can be re-converged every iteration (lanes that
+  // diverge in probe / CAS loops otherwise keep running apart: 2-3 active lanes per instruction)
+  for (int64_t row0 = begin + (threadIdx.x & ~31); row0 < end; row0 += blockDim.x) {
+    __syncwarp();
+    const int64_t row = row0 + (threadIdx.x & 31);
+    if (row >= end) continue;
     if (a.defer_in && !((a.defer_in[row >> 5] >> (row & 31)) & 1u)) continue;
     int special;
     const uint64_t key = load_key(a, row, &special);
@@ -406,6 +412,423 @@ __global__ void __launch_bounds__(kLocal ? 1024 : 256) gb_consume_kernel(const _
   if (threadIdx.x == 0) {
     if (s_new_groups) atomicAdd(a.counters + 0, s_new_groups);
     if (s_deferred) atomicAdd(a.counters + 1, s_deferred);
+  }
+}
+
+// ---- fast low-cardinality path ----------------------------------------------------------------
+// One value column feeding any mix of hash_sum / hash_mean / hash_count / hash_min_max (C3: 12.125
+// algorithmic B/row), up to 1024 groups per CTA.  Shared-memory atomics on sm_100a are native only
+// for 32-bit integers (measured 6.5 updates/cycle/SM; 64-bit and floating-point ones are CAS loops
+// at 0.07-1.3, and their retry loops split the warp), so nothing is accumulated with atomics:
+// every 4096-row tile is counting-sorted by group in shared memory and reduced per group.
+//   P1  128-bit loads (4 consecutive rows per thread, two sub-tiles); key -> dense group id through
+//       a shared hash table (new keys are inserted in a separate, rarely taken step); the row's rank
+//       inside its group = native ATOMS.ADD on the group's tile counter
+//   P2  exclusive scan of the 1024 tile counters
+//   P3  values scattered to sorted[offset[group] + rank]
+//   P4  each thread owns two groups: walks their segments with plain adds / min / max in registers
+//       and updates the CTA's per-group accumulators without any conflict
+// Rows that cannot be placed (special keys, more than 1024 groups in a CTA) are flagged in the
+// deferred-row bitmap and taken by the generic kernel afterwards.  At the end every CTA folds its
+// groups into the global table.
+constexpr int kFastThreads = 512;
+constexpr int kFastSub = 4;                              // consecutive rows per thread per sub-tile
+constexpr int kFastSubs = 2;                             // sub-tiles per tile
+constexpr int kFastRows = kFastSub * kFastSubs;          // rows per thread per tile
+constexpr int kFastSubRows = kFastThreads * kFastSub;    // 2048
+constexpr int kFastTile = kFastThreads * kFastRows;      // 4096
+constexpr int kFastGroups = 1024;                        // dense group ids per CTA
+constexpr int kFastMaxGroupsHint = 1008;                 // cardinality hint up to which the path is chosen
+constexpr uint32_t kGidUnset = 0xFFFFu, kGidOverflow = 0xFFFEu;
+constexpr uint32_t kNoRank = 0xFFFFFFFFu;
+
+// Hash table of a CTA: 16 KB of keys in 16-byte buckets read with one LDS.128 — four 32-bit keys
+// (KEY32: a single key column of at most 32 bits without nulls; 4096 slots) or two 64-bit packed
+// keys (2048 slots) — plus a 16-bit dense group id per slot.  With <= 1024 groups a key sits in its
+// home bucket with probability > 0.99 (four-key buckets), so a warp rarely probes twice.
+constexpr int kFastKeyBytes = 16 * 1024;
+constexpr int kFastSlots32 = kFastKeyBytes / 4;   // 4096
+constexpr int kFastSlots64 = kFastKeyBytes / 8;   // 2048
+constexpr int kFastBuckets = kFastKeyBytes / 16;  // 1024
+constexpr uint32_t kEmpty32 = 0xFFFFFFFFu;
+
+struct FastSmem {
+  uint4 hbuckets[kFastBuckets];
+  uint64_t sorted[kFastTile];
+  uint64_t sum[kFastGroups];
+  uint64_t mn[kFastGroups];
+  uint64_t mx[kFastGroups];
+  uint32_t tcnt[kFastGroups];
+  uint32_t toff[kFastGroups];
+  uint32_t cnt[kFastGroups];
+  uint32_t nulls[kFastGroups];
+  uint32_t first[kFastGroups];
+  uint16_t hgid[kFastSlots32];
+  uint32_t warp_tot[kFastThreads / 32];
+  uint32_t n_groups, need_insert, new_groups, deferred;
+};
+
+__device__ __forceinline__ uint32_t fast_hash(uint64_t key) {
+  uint32_t x = uint32_t(key) ^ (uint32_t(key >> 32) * 0x9E3779B9u);
+  x *= 0x85EBCA6Bu;
+  x ^= x >> 15;
+  x *= 0xC2B2AE35u;
+  return x >> (32 - 10);   // bucket index
+}
+static_assert(kFastBuckets == 1024, "fast_hash yields 10 bits");
+
+// slot of `key` in bucket b: KEY32 -> 4 candidates, else 2; -1 if absent; *has_empty = bucket has room
+template <bool KEY32>
+__device__ __forceinline__ int fast_match(const FastSmem& S, uint32_t b, uint64_t key, bool* has_empty) {
+  uint4 w;
+  asm volatile("ld.volatile.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(w.x), "=r"(w.y), "=r"(w.z), "=r"(w.w)
+               : "r"(uint32_t(__cvta_generic_to_shared(&S.hbuckets[b]))));
+  if (KEY32) {
+    const uint32_t k = uint32_t(key);
+    *has_empty = w.w == kEmpty32;   // slots of a bucket fill in order
+    const uint32_t m = (w.x == k ? 1u : 0u) | (w.y == k ? 2u : 0u) | (w.z == k ? 4u : 0u) | (w.w == k ? 8u : 0u);
+    return m ? int(4 * b) + (__ffs(m) - 1) : -1;
+  } else {
+    const uint64_t k0 = (uint64_t(w.y) << 32) | w.x, k1 = (uint64_t(w.w) << 32) | w.z;
+    *has_empty = k1 == kEmpty;
+    const uint32_t m = (k0 == key ? 1u : 0u) | (k1 == key ? 2u : 0u);
+    return m ? int(2 * b) + (__ffs(m) - 1) : -1;
+  }
+}
+
+__device__ __forceinline__ int fast_gid_of_slot(const FastSmem& S, int slot) {
+  const uint32_t g = *reinterpret_cast<const volatile uint16_t*>(&S.hgid[slot]);
+  return g < uint32_t(kFastGroups) ? int(g) : (g == kGidUnset ? -1 : -2);
+}
+
+// the rare continuation of a lookup whose home bucket neither holds the key nor has room
+template <bool KEY32>
+__device__ __noinline__ int fast_lookup_far(const FastSmem& S, uint64_t key, uint32_t b) {
+#pragma unroll 1
+  for (int probe = 1; probe < kLocalProbe; ++probe) {
+    b = (b + 1) & (kFastBuckets - 1);
+    bool has_empty;
+    const int slot = fast_match<KEY32>(S, b, key, &has_empty);
+    if (slot >= 0) return fast_gid_of_slot(S, slot);
+    if (has_empty) return -1;
+  }
+  return -2;
+}
+
+// group id of `key`, -1 = not (yet) in the table, -2 = cannot be placed
+template <bool KEY32>
+__device__ __forceinline__ int fast_lookup(const FastSmem& S, uint64_t key) {
+  const uint32_t b = fast_hash(key);
+  bool has_empty;
+  const int slot = fast_match<KEY32>(S, b, key, &has_empty);
+  if (slot >= 0) return fast_gid_of_slot(S, slot);
+  if (has_empty) return -1;
+  return fast_lookup_far<KEY32>(S, key, b);
+}
+
+template <bool KEY32>
+__device__ __forceinline__ void fast_insert(FastSmem& S, uint64_t key) {
+  uint32_t b = fast_hash(key);
+#pragma unroll 1
+  for (int probe = 0; probe < kLocalProbe; ++probe) {
+    bool has_empty;
+    if (fast_match<KEY32>(S, b, key, &has_empty) >= 0) return;
+    if (has_empty) {
+      if (*reinterpret_cast<const volatile uint32_t*>(&S.n_groups) >= uint32_t(kFastGroups)) return;
+      // claim the first free slot of the bucket; a lost race re-examines the same bucket
+      const int per = KEY32 ? 4 : 2;
+      bool mine = false, same = false;
+      int slot = -1;
+      for (int i = 0; i < per && !mine && !same; ++i) {
+        slot = int(per * b) + i;
+        if (KEY32) {
+          uint32_t* kp = reinterpret_cast<uint32_t*>(S.hbuckets) + slot;
+          const uint32_t old = atomicCAS(kp, kEmpty32, uint32_t(key));
+          mine = old == kEmpty32;
+          same = old == uint32_t(key);
+        } else {
+          unsigned long long* kp = reinterpret_cast<unsigned long long*>(S.hbuckets) + slot;
+          const unsigned long long old = atomicCAS(kp, (unsigned long long)kEmpty, (unsigned long long)key);
+          mine = old == kEmpty;
+          same = old == key;
+        }
+      }
+      if (same) return;
+      if (mine) {
+        const uint32_t g = atomicAdd(&S.n_groups, 1u);
+        S.hgid[slot] = uint16_t(g < uint32_t(kFastGroups) ? g : kGidOverflow);
+        return;
+      }
+      // the bucket filled up under us: fall through to the next one
+    }
+    b = (b + 1) & (kFastBuckets - 1);
+  }
+}
+
+template <int KMODE, bool VFAST>
+__global__ void __launch_bounds__(kFastThreads, 2) gb_fast_kernel(const __grid_constant__ GbArgs a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  FastSmem& S = *reinterpret_cast<FastSmem*>(smem);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  for (int i = t; i < kFastBuckets; i += kFastThreads) S.hbuckets[i] = make_uint4(kEmpty32, kEmpty32, kEmpty32, kEmpty32);
+  for (int i = t; i < kFastSlots32; i += kFastThreads) S.hgid[i] = uint16_t(kGidUnset);
+  for (int i = t; i < kFastGroups; i += kFastThreads) {
+    S.sum[i] = 0;
+    S.mn[i] = ~uint64_t(0);
+    S.mx[i] = 0;
+    S.tcnt[i] = 0;
+    S.cnt[i] = 0;
+    S.nulls[i] = 0;
+    S.first[i] = 0xFFFFFFFFu;
+  }
+  if (t == 0) {
+    S.n_groups = 0;
+    S.need_insert = 0;
+    S.new_groups = 0;
+    S.deferred = 0;
+  }
+  __syncthreads();
+  const int dom = a.s.aggs[0].dom;
+  bool want_minmax = false;
+  for (int j = 0; j < a.s.n_aggs; ++j)
+    if (a.s.aggs[j].kind == B200_HASH_MIN_MAX) want_minmax = true;
+  const int64_t begin = int64_t(blockIdx.x) * a.rows_per_block;
+  const int64_t end = min(a.n, begin + a.rows_per_block);   // a.n is a multiple of kFastTile here
+  uint64_t* zf = a.zf_scratch + size_t(blockIdx.x) * kFastGroups;
+
+#pragma unroll 1
+  for (int64_t base = begin; base < end; base += kFastTile) {
+    uint64_t vbits[kFastRows];
+    int gid[kFastRows];
+    uint32_t vmask = 0;   // validity of the values
+    uint32_t newkey = 0;  // rows whose key was not in the table when the tile started
+    // ---- P1a: loads and group lookup
+    {
+      uint64_t key[kFastRows];
+      uint32_t special = 0;
+#pragma unroll
+      for (int s = 0; s < kFastSubs; ++s) {
+        const int64_t r0 = base + s * kFastSubRows + t * kFastSub;
+        if (KMODE == 1) {
+          const uint4 k4 = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(a.keys[0].data) + r0);
+          key[4 * s + 0] = k4.x; key[4 * s + 1] = k4.y; key[4 * s + 2] = k4.z; key[4 * s + 3] = k4.w;
+#pragma unroll
+          for (int i = 0; i < kFastSub; ++i)
+            if (uint32_t(key[4 * s + i]) == kEmpty32) special |= 1u << (4 * s + i);
+        } else if (KMODE == 2) {
+          const ulonglong2* kp = reinterpret_cast<const ulonglong2*>(reinterpret_cast<const uint64_t*>(a.keys[0].data) + r0);
+          const ulonglong2 ka = kp[0], kb = kp[1];
+          key[4 * s + 0] = ka.x; key[4 * s + 1] = ka.y; key[4 * s + 2] = kb.x; key[4 * s + 3] = kb.y;
+#pragma unroll
+          for (int i = 0; i < kFastSub; ++i)
+            if (key[4 * s + i] == kEmpty) special |= 1u << (4 * s + i);
+        } else {
+#pragma unroll
+          for (int i = 0; i < kFastSub; ++i) {
+            int sp;
+            key[4 * s + i] = load_key(a, r0 + i, &sp);
+            if (sp) special |= 1u << (4 * s + i);
+          }
+        }
+        if (VFAST) {
+          const ulonglong2* vp = reinterpret_cast<const ulonglong2*>(reinterpret_cast<const uint64_t*>(a.cols[0].data) + r0);
+          const ulonglong2 va = vp[0], vb = vp[1];
+          vbits[4 * s + 0] = va.x; vbits[4 * s + 1] = va.y; vbits[4 * s + 2] = vb.x; vbits[4 * s + 3] = vb.y;
+          uint32_t m = 0xFu;
+          if (a.cols[0].vv.words) {
+            const int64_t bit = a.cols[0].vv.bit_offset + r0;
+            const uint8_t* bytes = reinterpret_cast<const uint8_t*>(a.cols[0].vv.words);
+            const int sh = int(bit & 7);
+            m = uint32_t(__ldg(bytes + (bit >> 3))) >> sh;
+            if (sh > 4) m |= uint32_t(__ldg(bytes + (bit >> 3) + 1)) << (8 - sh);
+          }
+          vmask |= (m & 0xFu) << (4 * s);
+        } else {
+#pragma unroll
+          for (int i = 0; i < kFastSub; ++i) {
+            const Val v = load_val(a.cols[0], r0 + i);
+            vbits[4 * s + i] = v.bits;
+            vmask |= (v.valid ? 1u : 0u) << (4 * s + i);
+          }
+        }
+      }
+      uint32_t pending = 0;
+#pragma unroll
+      for (int i = 0; i < kFastRows; ++i) {
+        gid[i] = ((special >> i) & 1u) ? -2 : fast_lookup<KMODE == 1>(S, key[i]);
+        if (gid[i] == -1) pending |= 1u << i;
+      }
+      newkey = pending;
+      if (__any_sync(0xffffffffu, pending != 0) && lane == 0) S.need_insert = 1;
+      __syncthreads();
+      if (S.need_insert) {   // CTA-uniform; taken for the first tile(s) only
+#pragma unroll
+        for (int i = 0; i < kFastRows; ++i)
+          if ((pending >> i) & 1u) fast_insert<KMODE == 1>(S, key[i]);
+        __syncthreads();
+        if (t == 0) S.need_insert = 0;
+#pragma unroll
+        for (int i = 0; i < kFastRows; ++i)
+          if ((pending >> i) & 1u) {
+            gid[i] = fast_lookup<KMODE == 1>(S, key[i]);
+            if (gid[i] == -1) gid[i] = -2;
+          }
+        __syncwarp();
+      }
+    }
+    // ---- P1b: rank inside the group (native shared atomics), null counts, first rows, deferred rows
+    uint32_t rank[kFastRows];
+    uint32_t defer = 0;
+#pragma unroll
+    for (int i = 0; i < kFastRows; ++i) {
+      rank[i] = kNoRank;
+      const int64_t row = base + (i / kFastSub) * kFastSubRows + t * kFastSub + (i % kFastSub);
+      if (gid[i] < 0) {
+        defer |= 1u << i;
+        continue;
+      }
+      // first rows: a key is inserted in the tile where the CTA first meets it, and every row of
+      // that key in that tile was pending, so only those rows can lower the group's first row
+      if ((newkey >> i) & 1u) atomicMin(&S.first[gid[i]], uint32_t(row - begin));
+      if ((vmask >> i) & 1u) {
+        rank[i] = atomicAdd(&S.tcnt[gid[i]], 1u);
+        // +-0.0 ties in hash_min_max: the earliest zero row decides the sign (see accumulate())
+        if (want_minmax && dom == kFloat && (vbits[i] << 1) == 0)
+          atomic_min_checked(zf + gid[i], ((a.row_base + uint64_t(row)) << 1) | (vbits[i] >> 63));
+      } else {
+        atomicAdd(&S.nulls[gid[i]], 1u);
+      }
+    }
+    if (defer) {
+#pragma unroll
+      for (int i = 0; i < kFastRows; ++i)
+        if ((defer >> i) & 1u) {
+          const int64_t row = base + (i / kFastSub) * kFastSubRows + t * kFastSub + (i % kFastSub);
+          atomicOr(a.defer_out + (row >> 5), 1u << (row & 31));
+        }
+      atomicAdd(&S.deferred, uint32_t(__popc(defer)));
+    }
+    __syncthreads();
+    // ---- P2: exclusive scan of the tile counters (two per thread)
+    {
+      const uint32_t c0 = S.tcnt[2 * t], c1 = S.tcnt[2 * t + 1];
+      uint32_t incl = c0 + c1;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+      }
+      if (lane == 31) S.warp_tot[warp] = incl;
+      __syncthreads();
+      uint32_t wpre = 0;
+#pragma unroll
+      for (int w = 0; w < kFastThreads / 32; ++w)
+        if (w < warp) wpre += S.warp_tot[w];
+      const uint32_t excl = wpre + incl - (c0 + c1);
+      S.toff[2 * t] = excl;
+      S.toff[2 * t + 1] = excl + c0;
+    }
+    __syncthreads();
+    // ---- P3: scatter the values into group order
+#pragma unroll
+    for (int i = 0; i < kFastRows; ++i)
+      if (rank[i] != kNoRank) S.sorted[S.toff[gid[i]] + rank[i]] = vbits[i];
+    __syncthreads();
+    // ---- P4: per-group reduction by the owning thread
+#pragma unroll
+    for (int q = 0; q < kFastGroups / kFastThreads; ++q) {
+      const int g = t + q * kFastThreads;
+      const uint32_t c = S.tcnt[g];
+      if (c == 0) continue;
+      const uint32_t o = S.toff[g];
+      S.tcnt[g] = 0;
+      S.cnt[g] += c;
+      if (dom == kFloat) {
+        double s = 0.0, lo = __longlong_as_double(0x7FF0000000000000ull), hi = __longlong_as_double(0xFFF0000000000000ull);
+        // fmin / fmax return the non-NaN operand: NaNs never win (hash_aggregate.cc:672-673)
+        const uint64_t* seg = S.sorted + o;
+        uint32_t j = 0;
+#pragma unroll 1
+        for (; j + 2 <= c; j += 2) {
+          const double v0 = __longlong_as_double(seg[j]), v1 = __longlong_as_double(seg[j + 1]);
+          s += v0;
+          s += v1;
+          lo = fmin(lo, fmin(v0, v1));
+          hi = fmax(hi, fmax(v0, v1));
+        }
+        if (j < c) {
+          const double v = __longlong_as_double(seg[j]);
+          s += v;
+          lo = fmin(lo, v);
+          hi = fmax(hi, v);
+        }
+        S.sum[g] = __double_as_longlong(__longlong_as_double(S.sum[g]) + s);
+        const uint64_t olo = ord_f64(lo), ohi = ord_f64(hi);
+        if (olo < S.mn[g]) S.mn[g] = olo;
+        if (ohi > S.mx[g]) S.mx[g] = ohi;
+      } else {
+        const uint64_t flip = dom == kSigned ? 0x8000000000000000ull : 0ull;
+        uint64_t s = 0, lo = ~uint64_t(0), hi = 0;
+#pragma unroll 1
+        for (uint32_t j = 0; j < c; ++j) {
+          const uint64_t v = S.sorted[o + j];
+          s += v;
+          const uint64_t ov = v ^ flip;
+          lo = ov < lo ? ov : lo;
+          hi = ov > hi ? ov : hi;
+        }
+        S.sum[g] += s;
+        if (lo < S.mn[g]) S.mn[g] = lo;
+        if (hi > S.mx[g]) S.mx[g] = hi;
+      }
+    }
+    // no barrier here: the next tile's P1a touches neither tcnt nor sorted, and its own barrier
+    // orders this P4 before the next P1b
+  }
+  __syncthreads();
+  // ---- flush: every group of this CTA is folded into the global table
+  constexpr bool KEY32 = KMODE == 1;
+  for (int slot = t; slot < (KEY32 ? kFastSlots32 : kFastSlots64); slot += kFastThreads) {
+    const uint32_t g = S.hgid[slot];
+    if (g >= uint32_t(kFastGroups)) continue;   // unset or overflow
+    const uint64_t key = KEY32 ? uint64_t(reinterpret_cast<const uint32_t*>(S.hbuckets)[slot])
+                               : reinterpret_cast<const uint64_t*>(S.hbuckets)[slot];
+    bool claimed;
+    uint64_t slot_index;
+    char* gs = global_slot(a.t, a.s.stride, key, 0, true, &claimed, &slot_index);
+    if (!gs) {
+      atomicExch(a.counters + 3, 2u);
+      continue;
+    }
+    if (claimed) atomicAdd(&S.new_groups, 1u);
+    const uint64_t cnt = S.cnt[g], nulls = S.nulls[g];
+    if (S.first[g] != 0xFFFFFFFFu) atomic_min_checked(reinterpret_cast<uint64_t*>(gs) + 1, a.row_base + uint64_t(begin) + S.first[g]);
+    for (int j = 0; j < a.s.n_aggs; ++j) {
+      const GbAgg& ag = a.s.aggs[j];
+      uint64_t* d = reinterpret_cast<uint64_t*>(gs + ag.off);
+      if (ag.kind == B200_HASH_COUNT) {
+        const uint64_t c = ag.option ? nulls : cnt;
+        if (c) atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)c);
+      } else if (ag.kind == B200_HASH_MIN_MAX) {
+        if (cnt) {
+          atomic_min_checked(d + 0, S.mn[g]);
+          atomic_max_checked(d + 1, S.mx[g]);
+          atomic_min_checked(d + 2, zf[g]);
+        }
+        const uint64_t flags = (cnt ? 1ull : 0ull) | (nulls ? 2ull : 0ull);
+        if (flags) atomic_or_checked(d + 3, flags);
+      } else if (cnt) {
+        if (ag.dom == kFloat) atomicAdd(reinterpret_cast<double*>(d), __longlong_as_double(S.sum[g]));
+        else atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)S.sum[g]);
+        atomicAdd(reinterpret_cast<unsigned long long*>(d + 1), (unsigned long long)cnt);
+      }
+    }
+  }
+  __syncthreads();
+  if (t == 0) {
+    if (S.new_groups) atomicAdd(a.counters + 0, S.new_groups);
+    if (S.deferred) atomicAdd(a.counters + 1, S.deferred);
   }
 }
 
@@ -693,6 +1116,7 @@ struct b200_groupby {
   uint32_t* counters = nullptr;  // device, 8 words
   uint32_t groups = 0;           // host view, refreshed at every sync point
   uint64_t expected = 0;         // caller's cardinality hint
+  bool fast_disabled = false;    // observed cardinality exceeds the shared-memory table
   // grouper state
   uint32_t* slot_ids = nullptr;
   uint64_t slot_ids_cap = 0;
@@ -827,7 +1251,8 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
   if (n == 0) return B200_OK;
   const size_t words = size_t((n + 31) / 32);
   const size_t claimed_bytes = a.mode == kModeInsert ? b200_align_up(size_t(n) * 4, 256) : 0;
-  B200_RETURN_NOT_OK(gb_reserve_tmp(gb, 2 * b200_align_up(words * 4, 256) + claimed_bytes + 256));
+  const size_t zf_bytes = size_t(ctx->num_sms) * 2 * kFastGroups * sizeof(uint64_t);
+  B200_RETURN_NOT_OK(gb_reserve_tmp(gb, 2 * b200_align_up(words * 4, 256) + claimed_bytes + zf_bytes + 512));
   uint32_t* defer_a = reinterpret_cast<uint32_t*>(gb->tmp);
   uint32_t* defer_b = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(gb->tmp) + b200_align_up(words * 4, 256));
   if (a.mode == kModeInsert) a.claimed = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(gb->tmp) + 2 * b200_align_up(words * 4, 256));
@@ -845,9 +1270,69 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
   // (the grouper's insert/lookup passes stay on the global table: a growth here would move slots
   // whose positional ids are live)
   const bool low_card = a.mode == kModeFused && likely_groups * 2 <= uint64_t(local_slots) && local_slots >= 64;
+  // one value column (or none) and a cardinality hint (or history) that fits the shared table: the fast kernel.
+  // With no hint at all the fast kernel is tried too: a CTA whose table fills up bypasses it.
+  const bool fast = a.mode == kModeFused && a.n_cols == 1 && likely_groups <= uint64_t(kFastMaxGroupsHint) && !gb->fast_disabled;
   for (int round = 0; round < 8; ++round) {
     a.t = gb->table;
-    if (low_card && round == 0) {
+    if (fast && round == 0) {
+      // full 2048-row tiles go through the fast kernel; the ragged tail and every row it defers
+      // (special keys, keys that found no room in a CTA's table) are taken by the generic kernel
+      const int64_t n_full = n / kFastTile * kFastTile;
+      if (n_full < n) B200_CUDA(ctx, cudaMemsetAsync(defer_a + n_full / 32, 0xFF, (words - size_t(n_full / 32)) * 4, ctx->stream));
+      uint32_t fast_deferred = 0;
+      if (n_full > 0) {
+        const int max_blocks = ctx->num_sms * 2;
+        int64_t rpb = (n_full + max_blocks - 1) / max_blocks;
+        rpb = (rpb + kFastTile - 1) / kFastTile * kFastTile;
+        const int grid = int((n_full + rpb - 1) / rpb);
+        B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + uint64_t(grid) * kFastGroups)));
+        a.t = gb->table;
+        a.local_slots = kFastSlots32;
+        a.rows_per_block = int(rpb);
+        a.n = n_full;
+        a.zf_scratch = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(gb->tmp) + 2 * b200_align_up(words * 4, 256) + claimed_bytes + 256);
+        B200_CUDA(ctx, cudaMemsetAsync(a.zf_scratch, 0xFF, size_t(grid) * kFastGroups * sizeof(uint64_t), ctx->stream));
+        const int smem = int(sizeof(FastSmem));
+        const bool k32 = a.s.n_keys == 1 && a.keys[0].nbits == 32 && !a.keys[0].vv.words && (reinterpret_cast<uintptr_t>(a.keys[0].data) & 15) == 0;
+        const bool k64 = a.s.n_keys == 1 && a.keys[0].nbits == 64 && !a.keys[0].vv.words && (reinterpret_cast<uintptr_t>(a.keys[0].data) & 15) == 0;
+        const bool vfast = a.n_cols == 1 && b200_type_bits(a.cols[0].type) == 64 && (reinterpret_cast<uintptr_t>(a.cols[0].data) & 15) == 0;
+        static bool fattr = false;
+        if (!fattr) {
+          const int mx = int(sizeof(FastSmem));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          fattr = true;
+        }
+#define B200_FAST_LAUNCH(KM, VF) \
+  B200_TIMED(ctx, "groupby_consume", (gb_fast_kernel<KM, VF><<<grid, kFastThreads, smem, ctx->stream>>>(a)))
+        if (k32) { if (vfast) B200_FAST_LAUNCH(1, true); else B200_FAST_LAUNCH(1, false); }
+        else if (k64) { if (vfast) B200_FAST_LAUNCH(2, true); else B200_FAST_LAUNCH(2, false); }
+        else { if (vfast) B200_FAST_LAUNCH(0, true); else B200_FAST_LAUNCH(0, false); }
+#undef B200_FAST_LAUNCH
+        a.n = n;
+        uint32_t c[4];
+        B200_RETURN_NOT_OK(read_counters(gb, c));
+        fast_deferred = c[1];
+        if (uint64_t(gb->groups) > uint64_t(kFastMaxGroupsHint)) gb->fast_disabled = true;
+      }
+      if (fast_deferred == 0 && n_full == n) {
+        if (uint64_t(gb->groups) * 2 > gb->table.cap) B200_RETURN_NOT_OK(grow_table(gb, uint64_t(gb->groups) * 4));
+        return B200_OK;
+      }
+      // the generic kernel below picks up exactly the flagged rows
+      if (uint64_t(gb->groups) + fast_deferred + uint64_t(n - n_full) > gb->table.cap / 2)
+        B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + fast_deferred + uint64_t(n - n_full))));
+      a.defer_in = defer_a;
+      a.defer_out = defer_b;
+      B200_CUDA(ctx, cudaMemsetAsync(defer_b, 0, words * 4, ctx->stream));
+      B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 1, 0, sizeof(uint32_t), ctx->stream));
+      continue;
+    } else if (low_card && round == 0) {
       const int blocks = ctx->num_sms;
       // the flush of every CTA must find room: table >= 2 * (groups + all local slots)
       B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + uint64_t(blocks) * local_slots)));
@@ -871,6 +1356,8 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
     uint32_t c[4];
     B200_RETURN_NOT_OK(read_counters(gb, c));
     const uint32_t deferred = c[1];
+    // cardinality beyond the shared table: later batches go straight to the global table
+    if (uint64_t(gb->groups) > uint64_t(kFastMaxGroupsHint)) gb->fast_disabled = true;
     if (deferred == 0) {
       // keep the load factor <= 1/2 for the next batch
       if (uint64_t(gb->groups) * 2 > gb->table.cap) B200_RETURN_NOT_OK(grow_table(gb, uint64_t(gb->groups) * 4));
