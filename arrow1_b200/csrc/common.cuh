@@ -28,7 +28,19 @@ struct b200_ctx {
     cudaEvent_t start, stop;
   };
   std::vector<TimedLaunch> timed;
+  // device blocks handed back by b200_dev_free, reused by b200_dev_alloc (all work of a context is
+  // ordered on its one stream, so reuse needs no synchronisation)
+  struct Block {
+    void* ptr;
+    size_t bytes;
+    bool in_use;
+  };
+  std::vector<Block> blocks;
 };
+
+// caching device allocator of a context: cudaMalloc / cudaFree stay out of the steady state
+int b200_dev_alloc(b200_ctx* ctx, void** out, size_t bytes);
+void b200_dev_free(b200_ctx* ctx, void* ptr);
 
 void b200_time_begin(b200_ctx* ctx, const char* name);
 void b200_time_end(b200_ctx* ctx);

@@ -27,6 +27,62 @@ int b200_ctx_reserve_scratch(b200_ctx* ctx, size_t bytes) {
   return B200_OK;
 }
 
+int b200_dev_alloc(b200_ctx* ctx, void** out, size_t bytes) {
+  bytes = b200_align_up(bytes ? bytes : 1, 512);
+  int best = -1;
+  for (size_t i = 0; i < ctx->blocks.size(); ++i) {
+    const b200_ctx::Block& b = ctx->blocks[i];
+    if (!b.in_use && b.bytes >= bytes && b.bytes <= 2 * bytes + (1 << 20) && (best < 0 || b.bytes < ctx->blocks[best].bytes)) best = int(i);
+  }
+  if (best >= 0) {
+    ctx->blocks[best].in_use = true;
+    *out = ctx->blocks[best].ptr;
+    return B200_OK;
+  }
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, bytes);
+  if (e != cudaSuccess) {
+    // give cached blocks back and retry once
+    cudaGetLastError();
+    cudaStreamSynchronize(ctx->stream);
+    for (size_t i = 0; i < ctx->blocks.size();) {
+      if (!ctx->blocks[i].in_use) {
+        cudaFree(ctx->blocks[i].ptr);
+        ctx->blocks.erase(ctx->blocks.begin() + i);
+      } else {
+        ++i;
+      }
+    }
+    e = cudaMalloc(&p, bytes);
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return b200_fail(ctx, B200_OUT_OF_MEMORY, "device allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+  }
+  ctx->blocks.push_back({p, bytes, true});
+  *out = p;
+  return B200_OK;
+}
+
+void b200_dev_free(b200_ctx* ctx, void* ptr) {
+  if (!ptr) return;
+  size_t idle = 0;
+  for (auto& b : ctx->blocks) {
+    if (b.ptr == ptr) b.in_use = false;
+    if (!b.in_use) ++idle;
+  }
+  if (idle > 24) {  // bound the cache: drop the largest idle block
+    int big = -1;
+    for (size_t i = 0; i < ctx->blocks.size(); ++i)
+      if (!ctx->blocks[i].in_use && (big < 0 || ctx->blocks[i].bytes > ctx->blocks[big].bytes)) big = int(i);
+    if (big >= 0) {
+      cudaStreamSynchronize(ctx->stream);
+      cudaFree(ctx->blocks[big].ptr);
+      ctx->blocks.erase(ctx->blocks.begin() + big);
+    }
+  }
+}
+
 void b200_time_begin(b200_ctx* ctx, const char* name) {
   if (!ctx->timing) return;
   b200_ctx::TimedLaunch t;
@@ -121,6 +177,8 @@ int b200_ctx_destroy(b200_ctx* ctx) {
   cudaStreamSynchronize(ctx->stream);
   clear_timed(ctx);
   if (ctx->scratch) cudaFree(ctx->scratch);
+  for (auto& b : ctx->blocks) cudaFree(b.ptr);
+  ctx->blocks.clear();
   if (ctx->host_words) cudaFreeHost(ctx->host_words);
   delete ctx;
   return B200_OK;
@@ -128,6 +186,7 @@ int b200_ctx_destroy(b200_ctx* ctx) {
 
 int b200_ctx_set_stream(b200_ctx* ctx, void* cu_stream) {
   if (!ctx) return B200_INVALID;
+  cudaStreamSynchronize(ctx->stream);  // cached device blocks are reused in stream order
   ctx->stream = reinterpret_cast<cudaStream_t>(cu_stream);
   return B200_OK;
 }

@@ -79,6 +79,7 @@ struct GbArgs {
   uint32_t* claimed;         // grouper: newly claimed slot indices
   uint32_t* slot_ids;        // grouper: dense id per slot
   uint32_t* out_ids;         // grouper lookup output
+  char* spill;               // fast path: slot images of groups the global table had no room for (counters[5])
   uint64_t* zf_scratch;      // fast path: per-CTA earliest-zero-row words [grid][kFastGroups]
   int32_t local_slots;       // shared-memory table size (power of two), 0 = none
   int32_t rows_per_block;
@@ -566,7 +567,7 @@ __device__ __forceinline__ void fast_insert(FastSmem& S, uint64_t key) {
   }
 }
 
-template <int KMODE, bool VFAST>
+template <int KMODE, bool VFAST, bool DIRECT>
 __global__ void __launch_bounds__(kFastThreads, 2) gb_fast_kernel(const __grid_constant__ GbArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
   FastSmem& S = *reinterpret_cast<FastSmem*>(smem);
@@ -677,6 +678,101 @@ __global__ void __launch_bounds__(kFastThreads, 2) gb_fast_kernel(const __grid_c
         __syncwarp();
       }
     }
+    if (DIRECT) {
+      // ---- direct accumulation: native 32-bit atomics for counts, warp-converged CAS retries for
+      // float sums (two rows in flight), read-then-rarely-CAS for the extremes
+      uint32_t ok = 0;
+#pragma unroll
+      for (int i = 0; i < kFastRows; ++i)
+        if (gid[i] >= 0) ok |= 1u << i;
+      const uint32_t live = vmask & ok, nullm = ok & ~vmask, nk = newkey & ok, defer = ~ok & ((1u << kFastRows) - 1);
+#pragma unroll
+      for (int i = 0; i < kFastRows; ++i)
+        if ((live >> i) & 1u) atomicAdd(&S.cnt[gid[i]], 1u);
+      if (nullm) {
+#pragma unroll
+        for (int i = 0; i < kFastRows; ++i)
+          if ((nullm >> i) & 1u) atomicAdd(&S.nulls[gid[i]], 1u);
+      }
+      if (nk) {
+#pragma unroll
+        for (int i = 0; i < kFastRows; ++i)
+          if ((nk >> i) & 1u) {
+            const int64_t row = base + (i / kFastSub) * kFastSubRows + t * kFastSub + (i % kFastSub);
+            atomicMin(&S.first[gid[i]], uint32_t(row - begin));
+          }
+      }
+      if (defer) {
+#pragma unroll
+        for (int i = 0; i < kFastRows; ++i)
+          if ((defer >> i) & 1u) {
+            const int64_t row = base + (i / kFastSub) * kFastSubRows + t * kFastSub + (i % kFastSub);
+            atomicOr(a.defer_out + (row >> 5), 1u << (row & 31));
+          }
+        atomicAdd(&S.deferred, uint32_t(__popc(defer)));
+      }
+      __syncwarp();
+      if (dom == kFloat) {
+#pragma unroll
+        for (int i = 0; i < kFastRows; i += 2) {
+          uint32_t pend = (live >> i) & 3u;
+          while (__any_sync(0xffffffffu, pend != 0)) {
+            uint64_t o0 = 0, o1 = 0;
+            if (pend & 1u) o0 = *reinterpret_cast<const volatile uint64_t*>(&S.sum[gid[i]]);
+            if (pend & 2u) o1 = *reinterpret_cast<const volatile uint64_t*>(&S.sum[gid[i + 1]]);
+            if (pend & 1u) {
+              const uint64_t nw = __double_as_longlong(__longlong_as_double(o0) + __longlong_as_double(vbits[i]));
+              if (atomicCAS(reinterpret_cast<unsigned long long*>(&S.sum[gid[i]]), (unsigned long long)o0, (unsigned long long)nw) == o0) pend &= ~1u;
+            }
+            if (pend & 2u) {
+              const uint64_t nw = __double_as_longlong(__longlong_as_double(o1) + __longlong_as_double(vbits[i + 1]));
+              if (atomicCAS(reinterpret_cast<unsigned long long*>(&S.sum[gid[i + 1]]), (unsigned long long)o1, (unsigned long long)nw) == o1) pend &= ~2u;
+            }
+          }
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < kFastRows; ++i) {
+          if (!((live >> i) & 1u)) continue;
+          uint32_t* w = reinterpret_cast<uint32_t*>(&S.sum[gid[i]]);
+          const uint32_t lo = uint32_t(vbits[i]), hi = uint32_t(vbits[i] >> 32);
+          const uint32_t old_lo = atomicAdd(w, lo);
+          const uint32_t carry = (old_lo + lo) < old_lo ? 1u : 0u;
+          if (hi + carry) atomicAdd(w + 1, hi + carry);
+        }
+      }
+      if (want_minmax) {
+#pragma unroll
+        for (int i = 0; i < kFastRows; ++i) {
+          bool lt = false, gt = false;
+          uint64_t o = 0;
+          if ((live >> i) & 1u) {
+            bool use = true;
+            if (dom == kFloat) {
+              const double dv = __longlong_as_double(vbits[i]);
+              use = dv == dv;
+              o = ord_f64(dv);
+              if ((vbits[i] << 1) == 0) {
+                const int64_t row = base + (i / kFastSub) * kFastSubRows + t * kFastSub + (i % kFastSub);
+                atomic_min_checked(zf + gid[i], ((a.row_base + uint64_t(row)) << 1) | (vbits[i] >> 63));
+              }
+            } else {
+              o = dom == kSigned ? (vbits[i] ^ 0x8000000000000000ull) : vbits[i];
+            }
+            if (use) {
+              lt = o < *reinterpret_cast<const volatile uint64_t*>(&S.mn[gid[i]]);
+              gt = o > *reinterpret_cast<const volatile uint64_t*>(&S.mx[gid[i]]);
+            }
+          }
+          if (__any_sync(0xffffffffu, lt || gt)) {
+            if (lt) atomicMin(reinterpret_cast<unsigned long long*>(&S.mn[gid[i]]), (unsigned long long)o);
+            if (gt) atomicMax(reinterpret_cast<unsigned long long*>(&S.mx[gid[i]]), (unsigned long long)o);
+            __syncwarp();
+          }
+        }
+      }
+      continue;
+    }
     // ---- P1b: rank inside the group (native shared atomics), null counts, first rows, deferred rows
     uint32_t rank[kFastRows];
     uint32_t defer = 0;
@@ -746,7 +842,6 @@ __global__ void __launch_bounds__(kFastThreads, 2) gb_fast_kernel(const __grid_c
       S.cnt[g] += c;
       if (dom == kFloat) {
         double s = 0.0, lo = __longlong_as_double(0x7FF0000000000000ull), hi = __longlong_as_double(0xFFF0000000000000ull);
-        // fmin / fmax return the non-NaN operand: NaNs never win (hash_aggregate.cc:672-673)
         const uint64_t* seg = S.sorted + o;
         uint32_t j = 0;
 #pragma unroll 1
@@ -754,14 +849,16 @@ __global__ void __launch_bounds__(kFastThreads, 2) gb_fast_kernel(const __grid_c
           const double v0 = __longlong_as_double(seg[j]), v1 = __longlong_as_double(seg[j + 1]);
           s += v0;
           s += v1;
-          lo = fmin(lo, fmin(v0, v1));
-          hi = fmax(hi, fmax(v0, v1));
+          lo = v0 < lo ? v0 : lo;   // a NaN never compares true: it never wins (hash_aggregate.cc:672-673)
+          hi = v0 > hi ? v0 : hi;
+          lo = v1 < lo ? v1 : lo;
+          hi = v1 > hi ? v1 : hi;
         }
         if (j < c) {
           const double v = __longlong_as_double(seg[j]);
           s += v;
-          lo = fmin(lo, v);
-          hi = fmax(hi, v);
+          lo = v < lo ? v : lo;
+          hi = v > hi ? v : hi;
         }
         S.sum[g] = __double_as_longlong(__longlong_as_double(S.sum[g]) + s);
         const uint64_t olo = ord_f64(lo), ohi = ord_f64(hi);
@@ -798,8 +895,13 @@ __global__ void __launch_bounds__(kFastThreads, 2) gb_fast_kernel(const __grid_c
     uint64_t slot_index;
     char* gs = global_slot(a.t, a.s.stride, key, 0, true, &claimed, &slot_index);
     if (!gs) {
-      atomicExch(a.counters + 3, 2u);
-      continue;
+      // no room (the table is sized from the cardinality hint, not for the worst case): the group
+      // goes to the spill list as a fresh slot image; the host grows the table and imports it
+      gs = a.spill + size_t(atomicAdd(a.counters + 5, 1u)) * a.s.stride;
+      init_slot(gs, a.s);
+      reinterpret_cast<uint64_t*>(gs)[0] = key;
+      reinterpret_cast<uint64_t*>(gs)[a.s.stride / 8 - 1] = 0;
+      claimed = false;
     }
     if (claimed) atomicAdd(&S.new_groups, 1u);
     const uint64_t cnt = S.cnt[g], nulls = S.nulls[g];
@@ -1117,6 +1219,7 @@ struct b200_groupby {
   uint32_t groups = 0;           // host view, refreshed at every sync point
   uint64_t expected = 0;         // caller's cardinality hint
   bool fast_disabled = false;    // observed cardinality exceeds the shared-memory table
+  uint32_t spilled = 0;          // fast path: groups waiting in the spill list
   // grouper state
   uint32_t* slot_ids = nullptr;
   uint64_t slot_ids_cap = 0;
@@ -1146,13 +1249,12 @@ int gb_reserve_tmp(b200_groupby* gb, size_t bytes) {
   b200_ctx* ctx = gb->ctx;
   if (bytes <= gb->tmp_bytes) return B200_OK;
   if (gb->tmp) {
-    B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    B200_CUDA(ctx, cudaFree(gb->tmp));
+    b200_dev_free(ctx, gb->tmp);
     gb->tmp = nullptr;
     gb->tmp_bytes = 0;
   }
   bytes = b200_align_up(bytes, 1 << 20);
-  B200_CUDA(ctx, cudaMalloc(&gb->tmp, bytes));
+  B200_RETURN_NOT_OK(b200_dev_alloc(ctx, &gb->tmp, bytes));
   gb->tmp_bytes = bytes;
   return B200_OK;
 }
@@ -1162,7 +1264,7 @@ int alloc_table(b200_groupby* gb, uint64_t cap, GbTable* out) {
   GbTable t;
   t.cap = cap;
   const uint64_t n_slots = cap + 2;
-  B200_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&t.slots), n_slots * gb->schema.stride));
+  B200_RETURN_NOT_OK(b200_dev_alloc(ctx, reinterpret_cast<void**>(&t.slots), n_slots * gb->schema.stride));
   gb_init_kernel<<<(unsigned)((n_slots + 255) / 256), 256, 0, ctx->stream>>>(gb->schema, t.slots, n_slots, gb->schema.stride);
   B200_LAUNCHED(ctx);
   *out = t;
@@ -1177,10 +1279,11 @@ uint64_t pow2_at_least(uint64_t x) {
 
 int read_counters(b200_groupby* gb, uint32_t out[4]) {
   b200_ctx* ctx = gb->ctx;
-  B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 16, gb->counters, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 16, gb->counters, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
   B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   memcpy(out, ctx->host_words + 16, 4 * sizeof(uint32_t));
   gb->groups = out[0];
+  gb->spilled = reinterpret_cast<const uint32_t*>(ctx->host_words + 16)[5];
   if (out[3] != 0) return b200_fail(ctx, B200_UNKNOWN_ERROR, "groupby: internal table error %u", out[3]);
   return B200_OK;
 }
@@ -1200,11 +1303,11 @@ int grow_table(b200_groupby* gb, uint64_t min_cap) {
                                                                            gb->counters);
   B200_LAUNCHED(ctx);
   B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  B200_CUDA(ctx, cudaFree(gb->table.slots));
+  b200_dev_free(ctx, gb->table.slots);
   gb->table = nt;
   // slot ids are positional: the grouper re-derives them after a rehash
   if (gb->slot_ids) {
-    B200_CUDA(ctx, cudaFree(gb->slot_ids));
+    b200_dev_free(ctx, gb->slot_ids);
     gb->slot_ids = nullptr;
     gb->slot_ids_cap = 0;
     gb->ids_assigned = 0;
@@ -1252,7 +1355,8 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
   const size_t words = size_t((n + 31) / 32);
   const size_t claimed_bytes = a.mode == kModeInsert ? b200_align_up(size_t(n) * 4, 256) : 0;
   const size_t zf_bytes = size_t(ctx->num_sms) * 2 * kFastGroups * sizeof(uint64_t);
-  B200_RETURN_NOT_OK(gb_reserve_tmp(gb, 2 * b200_align_up(words * 4, 256) + claimed_bytes + zf_bytes + 512));
+  const size_t spill_bytes = a.mode == kModeFused ? size_t(ctx->num_sms) * 2 * kFastGroups * size_t(a.s.stride) : 0;
+  B200_RETURN_NOT_OK(gb_reserve_tmp(gb, 2 * b200_align_up(words * 4, 256) + claimed_bytes + zf_bytes + spill_bytes + 512));
   uint32_t* defer_a = reinterpret_cast<uint32_t*>(gb->tmp);
   uint32_t* defer_b = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(gb->tmp) + b200_align_up(words * 4, 256));
   if (a.mode == kModeInsert) a.claimed = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(gb->tmp) + 2 * b200_align_up(words * 4, 256));
@@ -1286,8 +1390,10 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
         int64_t rpb = (n_full + max_blocks - 1) / max_blocks;
         rpb = (rpb + kFastTile - 1) / kFastTile * kFastTile;
         const int grid = int((n_full + rpb - 1) / rpb);
-        B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + uint64_t(grid) * kFastGroups)));
+        B200_RETURN_NOT_OK(grow_table(gb, 2 * std::max<uint64_t>(likely_groups, 32 * 1024)));
         a.t = gb->table;
+        a.spill = reinterpret_cast<char*>(gb->tmp) + 2 * b200_align_up(words * 4, 256) + claimed_bytes + 256 + zf_bytes;
+        B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 5, 0, sizeof(uint32_t), ctx->stream));
         a.local_slots = kFastSlots32;
         a.rows_per_block = int(rpb);
         a.n = n_full;
@@ -1300,16 +1406,26 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
         static bool fattr = false;
         if (!fattr) {
           const int mx = int(sizeof(FastSmem));
-          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<0, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<0, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<0, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<0, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<1, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<1, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<1, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<2, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<2, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<2, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
           fattr = true;
         }
+        static const bool direct = getenv("B200_GB_DIRECT") != nullptr;
 #define B200_FAST_LAUNCH(KM, VF) \
-  B200_TIMED(ctx, "groupby_consume", (gb_fast_kernel<KM, VF><<<grid, kFastThreads, smem, ctx->stream>>>(a)))
+  do {                                                                                                              \
+    if (direct) B200_TIMED(ctx, "groupby_consume", (gb_fast_kernel<KM, VF, true><<<grid, kFastThreads, smem, ctx->stream>>>(a)));  \
+    else B200_TIMED(ctx, "groupby_consume", (gb_fast_kernel<KM, VF, false><<<grid, kFastThreads, smem, ctx->stream>>>(a)));        \
+  } while (0)
         if (k32) { if (vfast) B200_FAST_LAUNCH(1, true); else B200_FAST_LAUNCH(1, false); }
         else if (k64) { if (vfast) B200_FAST_LAUNCH(2, true); else B200_FAST_LAUNCH(2, false); }
         else { if (vfast) B200_FAST_LAUNCH(0, true); else B200_FAST_LAUNCH(0, false); }
@@ -1318,6 +1434,14 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
         uint32_t c[4];
         B200_RETURN_NOT_OK(read_counters(gb, c));
         fast_deferred = c[1];
+        if (gb->spilled) {
+          const uint32_t n_spill = gb->spilled;
+          B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + n_spill)));
+          gb_import_kernel<<<(n_spill + 255) / 256, 256, 0, ctx->stream>>>(gb->schema, a.spill, n_spill, gb->table, gb->counters);
+          B200_LAUNCHED(ctx);
+          B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 5, 0, sizeof(uint32_t), ctx->stream));
+          B200_RETURN_NOT_OK(read_counters(gb, c));
+        }
         if (uint64_t(gb->groups) > uint64_t(kFastMaxGroupsHint)) gb->fast_disabled = true;
       }
       if (fast_deferred == 0 && n_full == n) {
@@ -1431,16 +1555,15 @@ int b200_groupby_create(b200_ctx* ctx, int n_keys, const int32_t* key_types, int
   gb->schema = s;
   gb->specs.assign(aggs, aggs + n_aggs);
   gb->expected = expected_groups > 0 ? uint64_t(expected_groups) : 0;
-  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&gb->counters), 8 * sizeof(uint32_t));
-  if (e != cudaSuccess) {
+  if (b200_dev_alloc(ctx, reinterpret_cast<void**>(&gb->counters), 8 * sizeof(uint32_t)) != B200_OK) {
     delete gb;
-    return b200_fail(ctx, B200_OUT_OF_MEMORY, "groupby: %s", cudaGetErrorString(e));
+    return B200_OUT_OF_MEMORY;
   }
   cudaMemsetAsync(gb->counters, 0, 8 * sizeof(uint32_t), ctx->stream);
   const uint64_t cap = pow2_at_least(expected_groups > 0 ? uint64_t(expected_groups) * 2 : (1u << 16));
   int st = alloc_table(gb, cap, &gb->table);
   if (st != B200_OK) {
-    cudaFree(gb->counters);
+    b200_dev_free(ctx, gb->counters);
     delete gb;
     return st;
   }
@@ -1451,11 +1574,11 @@ int b200_groupby_create(b200_ctx* ctx, int n_keys, const int32_t* key_types, int
 int b200_groupby_destroy(b200_groupby* gb) {
   if (!gb) return B200_OK;
   cudaStreamSynchronize(gb->ctx->stream);
-  if (gb->table.slots) cudaFree(gb->table.slots);
-  if (gb->counters) cudaFree(gb->counters);
-  if (gb->slot_ids) cudaFree(gb->slot_ids);
-  if (gb->dense) cudaFree(gb->dense);
-  if (gb->tmp) cudaFree(gb->tmp);
+  b200_dev_free(gb->ctx, gb->table.slots);
+  b200_dev_free(gb->ctx, gb->counters);
+  b200_dev_free(gb->ctx, gb->slot_ids);
+  b200_dev_free(gb->ctx, gb->dense);
+  b200_dev_free(gb->ctx, gb->tmp);
   delete gb;
   return B200_OK;
 }
@@ -1538,7 +1661,7 @@ int b200_grouper_consume(b200_groupby* gb, const b200_col* keys, uint32_t* out_i
   const uint64_t n_slots = gb->table.cap + 2;
   const bool rebuild_ids = gb->slot_ids == nullptr;
   if (rebuild_ids) {
-    B200_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&gb->slot_ids), n_slots * sizeof(uint32_t)));
+    B200_RETURN_NOT_OK(b200_dev_alloc(ctx, reinterpret_cast<void**>(&gb->slot_ids), n_slots * sizeof(uint32_t)));
     gb->slot_ids_cap = n_slots;
     gb_fill_u32_kernel<<<(unsigned)((n_slots + 255) / 256), 256, 0, ctx->stream>>>(gb->slot_ids, n_slots, kNoId);
     B200_LAUNCHED(ctx);
@@ -1597,13 +1720,13 @@ int b200_hash_agg_consume(b200_groupby* gb, int agg_index, const b200_col* arg, 
   if (num_groups > gb->dense_cap) {
     const uint32_t new_cap = uint32_t(pow2_at_least(num_groups));
     char* nd = nullptr;
-    B200_CUDA(ctx, cudaMalloc(reinterpret_cast<void**>(&nd), size_t(new_cap) * gb->schema.stride));
+    B200_RETURN_NOT_OK(b200_dev_alloc(ctx, reinterpret_cast<void**>(&nd), size_t(new_cap) * gb->schema.stride));
     gb_init_kernel<<<(new_cap + 255) / 256, 256, 0, ctx->stream>>>(gb->schema, nd, new_cap, gb->schema.stride);
     B200_LAUNCHED(ctx);
     if (gb->dense) {
       B200_CUDA(ctx, cudaMemcpyAsync(nd, gb->dense, size_t(gb->dense_cap) * gb->schema.stride, cudaMemcpyDeviceToDevice, ctx->stream));
       B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-      B200_CUDA(ctx, cudaFree(gb->dense));
+      b200_dev_free(ctx, gb->dense);
     }
     gb->dense = nd;
     gb->dense_cap = new_cap;

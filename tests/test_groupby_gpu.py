@@ -100,6 +100,20 @@ def test_groupby_high_cardinality_growth(ctx):
     assert_group_equal(a, b, aggs, rtol=RTOL)
 
 
+def test_groupby_fast_path_spill_and_deferral(ctx):
+    """One value column, no hint, ~1 M distinct keys over 2 M rows: every CTA of the fast kernel fills
+    its 1024-group table (rows beyond are deferred to the generic kernel) and the CTAs' flushes
+    overflow the hint-sized global table (groups go through the spill list and are imported)."""
+    rng = np.random.default_rng(77)
+    n = 2_000_000
+    key = Column.from_numpy(rng.integers(0, 1_000_000, size=n).astype(np.int32))
+    arg = Column.from_numpy(rng.integers(-1000, 1000, size=n).astype(np.int64), rng.random(n) > 0.01)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT), AggSpec(cols.HASH_MIN_MAX)]
+    a = run_groupby("gpu", [key], aggs, [arg] * 3, ctx, expected_groups=0)
+    b = run_groupby(ORACLE, [key], aggs, [arg] * 3)
+    assert_group_equal(a, b, aggs, rtol=RTOL)
+
+
 def test_groupby_streaming_batches_match_single_batch(ctx):
     """GroupBy's batch loop (hash_aggregate.cc:928-943): consuming row ranges one after the other,
     sliced (offset != 0) — the case the reference itself gets wrong — equals one batch."""
