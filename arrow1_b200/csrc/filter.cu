@@ -253,6 +253,17 @@ filter_apply_kernel(ApplyArgs a) {
   T* out = reinterpret_cast<T*>(a.out_data);
   const unsigned lt = lanemask_lt();
 
+  // every value load of the warp's 512 rows is issued before the first store (16 independent
+  // 256-byte requests in flight per warp); rows that are not emitted are not requested
+  T vreg[16];
+  if (!kBool) {
+#pragma unroll
+    for (int s = 0; s < 16; ++s) {
+      const uint32_t ivs = __shfl_sync(0xffffffffu, iv, s);
+      vreg[s] = T(0);  // an emitted filter-null writes zero (vector_selection.cc:743-746)
+      if ((ivs >> lane) & 1u) vreg[s] = __ldg(vals + wrow0 + s * 32 + lane);
+    }
+  }
 #pragma unroll
   for (int s = 0; s < 16; ++s) {
     const uint32_t es = __shfl_sync(0xffffffffu, e, s);
@@ -263,9 +274,7 @@ filter_apply_kernel(ApplyArgs a) {
     const bool isv = (ivs >> lane) & 1u;
     const uint32_t rank = __popc(es & lt);
     if (!kBool) {
-      T v = T(0);  // an emitted filter-null writes zero (vector_selection.cc:743-746)
-      if (isv) v = vals[wrow0 + s * 32 + lane];
-      if (emit) out[wout + ps + rank] = v;
+      if (emit) out[wout + ps + rank] = vreg[s];
     } else {
       const uint32_t ds = __shfl_sync(0xffffffffu, dbw, s);
       const uint32_t bit = (isv && ((ds >> lane) & 1u)) ? (1u << rank) : 0u;

@@ -398,7 +398,16 @@ __global__ void __launch_bounds__(kLocal ? 1024 : 256) gb_consume_kernel(const _
       uint64_t slot_index;
       char* gs = global_slot(a.t, a.s.stride, key, 0, true, &claimed, &slot_index);
       if (!gs) {
-        atomicExch(a.counters + 3, 2u);
+        // no room left in the global table: the group goes to the spill list as a slot image;
+        // the host grows the table and imports the list
+        if (a.mode == kModeInsert) {
+          atomicExch(a.counters + 3, 2u);
+          continue;
+        }
+        uint64_t* img = reinterpret_cast<uint64_t*>(a.spill + size_t(atomicAdd(a.counters + 5, 1u)) * a.s.stride);
+        const uint64_t* lw = reinterpret_cast<const uint64_t*>(ls);
+        for (int w = 0; w < lstride / 8; ++w) img[w] = lw[w];
+        img[a.s.stride / 8 - 1] = 0;
         continue;
       }
       if (claimed) {
@@ -1346,6 +1355,19 @@ void fill_col(const b200_col& c, GbCol* g) {
   g->vv = has_nulls ? make_bitmap_ref(c.validity, c.offset) : BitmapRef{nullptr, 0};
 }
 
+// groups a CTA could not place in the global table wait as slot images in the spill list
+int import_spilled(b200_groupby* gb, const char* spill) {
+  b200_ctx* ctx = gb->ctx;
+  if (!gb->spilled) return B200_OK;
+  const uint32_t n_spill = gb->spilled;
+  B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + n_spill)));
+  gb_import_kernel<<<(n_spill + 255) / 256, 256, 0, ctx->stream>>>(gb->schema, spill, n_spill, gb->table, gb->counters);
+  B200_LAUNCHED(ctx);
+  B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 5, 0, sizeof(uint32_t), ctx->stream));
+  uint32_t c[4];
+  return read_counters(gb, c);
+}
+
 // launches the consume kernel over all rows, then re-runs it over deferred rows after growing the
 // table until every row found a slot
 int run_consume(b200_groupby* gb, GbArgs& a) {
@@ -1355,7 +1377,8 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
   const size_t words = size_t((n + 31) / 32);
   const size_t claimed_bytes = a.mode == kModeInsert ? b200_align_up(size_t(n) * 4, 256) : 0;
   const size_t zf_bytes = size_t(ctx->num_sms) * 2 * kFastGroups * sizeof(uint64_t);
-  const size_t spill_bytes = a.mode == kModeFused ? size_t(ctx->num_sms) * 2 * kFastGroups * size_t(a.s.stride) : 0;
+  const size_t spill_slots = std::max<size_t>(size_t(ctx->num_sms) * 2 * kFastGroups, size_t(ctx->num_sms) * (160 * 1024 / a.s.lstride));
+  const size_t spill_bytes = a.mode == kModeFused ? spill_slots * size_t(a.s.stride) : 0;
   B200_RETURN_NOT_OK(gb_reserve_tmp(gb, 2 * b200_align_up(words * 4, 256) + claimed_bytes + zf_bytes + spill_bytes + 512));
   uint32_t* defer_a = reinterpret_cast<uint32_t*>(gb->tmp);
   uint32_t* defer_b = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(gb->tmp) + b200_align_up(words * 4, 256));
@@ -1365,6 +1388,8 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
   a.defer_out = defer_a;
   B200_CUDA(ctx, cudaMemsetAsync(defer_a, 0, words * 4, ctx->stream));
   B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 1, 0, 2 * sizeof(uint32_t), ctx->stream));
+  a.spill = reinterpret_cast<char*>(gb->tmp) + 2 * b200_align_up(words * 4, 256) + claimed_bytes + 256 + zf_bytes;
+  B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 5, 0, sizeof(uint32_t), ctx->stream));
 
   // path choice: the shared-memory table pays off while the groups fit in it
   const int sm_slots_budget = 160 * 1024 / a.s.lstride;
@@ -1392,8 +1417,7 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
         const int grid = int((n_full + rpb - 1) / rpb);
         B200_RETURN_NOT_OK(grow_table(gb, 2 * std::max<uint64_t>(likely_groups, 32 * 1024)));
         a.t = gb->table;
-        a.spill = reinterpret_cast<char*>(gb->tmp) + 2 * b200_align_up(words * 4, 256) + claimed_bytes + 256 + zf_bytes;
-        B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 5, 0, sizeof(uint32_t), ctx->stream));
+
         a.local_slots = kFastSlots32;
         a.rows_per_block = int(rpb);
         a.n = n_full;
@@ -1434,14 +1458,7 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
         uint32_t c[4];
         B200_RETURN_NOT_OK(read_counters(gb, c));
         fast_deferred = c[1];
-        if (gb->spilled) {
-          const uint32_t n_spill = gb->spilled;
-          B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + n_spill)));
-          gb_import_kernel<<<(n_spill + 255) / 256, 256, 0, ctx->stream>>>(gb->schema, a.spill, n_spill, gb->table, gb->counters);
-          B200_LAUNCHED(ctx);
-          B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 5, 0, sizeof(uint32_t), ctx->stream));
-          B200_RETURN_NOT_OK(read_counters(gb, c));
-        }
+        B200_RETURN_NOT_OK(import_spilled(gb, a.spill));
         if (uint64_t(gb->groups) > uint64_t(kFastMaxGroupsHint)) gb->fast_disabled = true;
       }
       if (fast_deferred == 0 && n_full == n) {
@@ -1458,8 +1475,8 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
       continue;
     } else if (low_card && round == 0) {
       const int blocks = ctx->num_sms;
-      // the flush of every CTA must find room: table >= 2 * (groups + all local slots)
-      B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + uint64_t(blocks) * local_slots)));
+      // sized from the hint; a flush that finds no room spills (see import_spilled)
+      B200_RETURN_NOT_OK(grow_table(gb, 2 * std::max<uint64_t>(likely_groups, 32 * 1024)));
       a.t = gb->table;
       a.local_slots = local_slots;
       a.rows_per_block = int((n + blocks - 1) / blocks);
@@ -1480,6 +1497,7 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
     uint32_t c[4];
     B200_RETURN_NOT_OK(read_counters(gb, c));
     const uint32_t deferred = c[1];
+    B200_RETURN_NOT_OK(import_spilled(gb, a.spill));
     // cardinality beyond the shared table: later batches go straight to the global table
     if (uint64_t(gb->groups) > uint64_t(kFastMaxGroupsHint)) gb->fast_disabled = true;
     if (deferred == 0) {

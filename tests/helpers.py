@@ -61,8 +61,12 @@ def run_groupby(impl, keys, aggs, args, ctx=None, want_ids=False, expected_group
         r = oracle.groupby(keys, aggs, args, want_ids=want_ids, kind=impl)
         return GroupRes(r.num_groups, r.aggs, r.keys, r.ids)
     from arrow1_b200 import capi
-    dkeys = [k.to_device() for k in keys]
-    dargs = [a.to_device() for a in args]
+    dev = {}   # one device copy per distinct host column (aggregates sharing a column share its buffers)
+    for c in list(keys) + list(args):
+        if id(c) not in dev:
+            dev[id(c)] = c.to_device()
+    dkeys = [dev[id(k)] for k in keys]
+    dargs = [dev[id(a)] for a in args]
     out = capi.group_by(ctx, dkeys, aggs, dargs, expected_groups=expected_groups)
     res_aggs = [[(c.to_host().values().copy(), c.to_host().valid()) for c in a] for a in out.aggs]
     res_keys = [(c.to_host().values().copy(), c.to_host().valid()) for c in out.keys]

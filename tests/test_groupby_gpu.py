@@ -258,3 +258,17 @@ def test_groupby_config4_shape(ctx):
     a = run_groupby("gpu", [key], aggs, [arg] * 2, ctx, expected_groups=n // 10)
     b = run_groupby(ORACLE, [key], aggs, [arg] * 2)
     assert_group_equal(a, b, aggs, rtol=RTOL)
+
+
+def test_groupby_low_card_kernel_spill_without_hint(ctx):
+    """Several value columns and no hint take the shared-table kernel; with ~1 M distinct keys its
+    CTAs overflow into the global table and their final flush spills: parity must hold."""
+    rng = np.random.default_rng(78)
+    n = 1_500_000
+    key = Column.from_numpy(rng.integers(0, 1_000_000, size=n).astype(np.int32))
+    a1 = Column.from_numpy(rng.integers(-1000, 1000, size=n).astype(np.int64))
+    a2 = Column.from_numpy(rng.integers(0, 1000, size=n).astype(np.int32), rng.random(n) > 0.1)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MIN_MAX), AggSpec(cols.HASH_COUNT)]
+    a = run_groupby("gpu", [key], aggs, [a1, a2, a2], ctx, expected_groups=0)
+    b = run_groupby(ORACLE, [key], aggs, [a1, a2, a2])
+    assert_group_equal(a, b, aggs, rtol=RTOL)
