@@ -1216,6 +1216,12 @@ __global__ void gb_dense_consume_kernel(GbSchema s, int agg_index, GbCol col, co
   accumulate(dense + uint64_t(g) * s.stride, s.aggs[agg_index], v, uint64_t(row));
 }
 
+// dense states over one id space folded slot by slot: HashAggregateKernel::merge
+__global__ void gb_dense_merge_kernel(GbSchema s, const char* src, char* dst, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) merge_state(dst + uint64_t(i) * s.stride, src + uint64_t(i) * s.stride, s);
+}
+
 }  // namespace
 
 // ===============================================================================================
@@ -1756,6 +1762,34 @@ int b200_hash_agg_consume(b200_groupby* gb, int agg_index, const b200_col* arg, 
   fill_col(*arg, &col);
   gb_dense_consume_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(gb->schema, agg_index, col, ids, n, gb->dense,
                                                                                num_groups, gb->counters);
+  B200_LAUNCHED(ctx);
+  return B200_OK;
+}
+
+int b200_hash_agg_merge(b200_groupby* dst, b200_groupby* src) {
+  if (!dst || !src) return B200_INVALID;
+  b200_ctx* ctx = dst->ctx;
+  if (dst->ctx != src->ctx) return b200_fail(ctx, B200_INVALID, "hash_agg_merge: handles belong to different contexts");
+  if (memcmp(&dst->schema, &src->schema, sizeof(GbSchema)) != 0) return b200_fail(ctx, B200_TYPE_ERROR, "hash_agg_merge: schemas differ");
+  if (!src->dense_used || src->dense_groups == 0) return B200_OK;
+  dst->dense_used = true;
+  const uint32_t n = src->dense_groups;
+  if (n > dst->dense_cap) {  // MaybeReserve, as in b200_hash_agg_consume
+    const uint32_t new_cap = uint32_t(pow2_at_least(n));
+    char* nd = nullptr;
+    B200_RETURN_NOT_OK(b200_dev_alloc(ctx, reinterpret_cast<void**>(&nd), size_t(new_cap) * dst->schema.stride));
+    gb_init_kernel<<<(new_cap + 255) / 256, 256, 0, ctx->stream>>>(dst->schema, nd, new_cap, dst->schema.stride);
+    B200_LAUNCHED(ctx);
+    if (dst->dense) {
+      B200_CUDA(ctx, cudaMemcpyAsync(nd, dst->dense, size_t(dst->dense_cap) * dst->schema.stride, cudaMemcpyDeviceToDevice, ctx->stream));
+      B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+      b200_dev_free(ctx, dst->dense);
+    }
+    dst->dense = nd;
+    dst->dense_cap = new_cap;
+  }
+  if (n > dst->dense_groups) dst->dense_groups = n;
+  gb_dense_merge_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(dst->schema, src->dense, dst->dense, n);
   B200_LAUNCHED(ctx);
   return B200_OK;
 }

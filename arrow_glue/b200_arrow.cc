@@ -1,0 +1,778 @@
+// b200_arrow.cc — Arrow FunctionRegistry glue over libarrow1_b200.so.  See b200_arrow.h.
+//
+// Host code only: unwraps device addresses out of CudaBuffer-resident ArrayData into b200_col
+// descriptors, sizes and allocates outputs through CudaContext::Allocate, maps b200_status onto
+// arrow::Status (the codes are equal by construction, include/arrow1_b200.h), and reproduces the
+// reference's host-side rules (argument checks, output schema, error messages) for the path.
+#include "b200_arrow.h"
+
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <utility>
+
+#include "arrow/array.h"
+#include "arrow/array/data.h"
+#include "arrow/buffer.h"
+#include "arrow/chunked_array.h"
+#include "arrow/compute/api_vector.h"
+#include "arrow/compute/function.h"
+#include "arrow/compute/kernel.h"
+#include "arrow/gpu/cuda_context.h"
+#include "arrow/gpu/cuda_memory.h"
+#include "arrow/record_batch.h"
+#include "arrow/scalar.h"
+#include "arrow/table.h"
+#include "arrow/type.h"
+#include "arrow/util/checked_cast.h"
+#include "arrow/util/make_unique.h"
+
+#include "arrow1_b200.h"
+
+namespace arrow {
+namespace compute {
+namespace cuda {
+
+using ::arrow::internal::checked_cast;
+
+namespace {
+
+// ---- device context ---------------------------------------------------------------------------
+// One b200_ctx per device, created on first use, living for the process.  It runs on the legacy
+// default stream so that it is ordered with CudaContext's synchronous cuMemcpy calls
+// (gpu/cuda_context.cc CopyHostToDevice / CopyDeviceToHost).  A b200_ctx is single-stream and
+// not re-entrant, so calls are serialised per device.
+struct DeviceState {
+  b200_ctx* ctx = nullptr;
+  std::shared_ptr<::arrow::cuda::CudaContext> arrow_ctx;
+  std::mutex mutex;
+};
+
+Status FromB200(b200_ctx* ctx, int code) {
+  if (code == B200_OK) return Status::OK();
+  const char* msg = ctx ? b200_last_error(ctx) : "";
+  return Status(static_cast<StatusCode>(code), msg && *msg ? msg : "arrow1_b200 call failed");
+}
+
+Result<DeviceState*> GetDevice(int device) {
+  static std::mutex registry_mutex;
+  static std::map<int, std::unique_ptr<DeviceState>> devices;
+  std::lock_guard<std::mutex> lock(registry_mutex);
+  auto it = devices.find(device);
+  if (it != devices.end()) return it->second.get();
+  auto st = ::arrow::internal::make_unique<DeviceState>();
+  ARROW_ASSIGN_OR_RAISE(auto manager, ::arrow::cuda::CudaDeviceManager::Instance());
+  ARROW_ASSIGN_OR_RAISE(st->arrow_ctx, manager->GetContext(device));
+  const int code = b200_ctx_create(device, /*cu_stream=*/nullptr, &st->ctx);
+  if (code != B200_OK) {
+    return Status(static_cast<StatusCode>(code), "b200_ctx_create failed for device " + std::to_string(device) +
+                                                     " (no CPU fallback exists)");
+  }
+  DeviceState* raw = st.get();
+  devices.emplace(device, std::move(st));
+  return raw;
+}
+
+#define B200_OK_OR_RAISE(dev, expr)                          \
+  do {                                                       \
+    const int _code = (expr);                                \
+    if (_code != B200_OK) return FromB200((dev)->ctx, _code); \
+  } while (0)
+
+// Device allocation through the reference's own allocator; zero-filled when asked (bitmaps must
+// come back zero-padded, compute/kernel.cc:51-59).  cuMemAlloc rejects 0 bytes, and the C ABI
+// wants 8-byte multiples, so sizes are rounded up to 64 like Arrow's host buffers.
+Result<std::shared_ptr<Buffer>> AllocateDevice(DeviceState* dev, int64_t nbytes) {
+  const int64_t padded = ((nbytes < 1 ? 1 : nbytes) + 63) / 64 * 64;
+  ARROW_ASSIGN_OR_RAISE(auto buf, dev->arrow_ctx->Allocate(padded));
+  return std::static_pointer_cast<Buffer>(buf);
+}
+
+int64_t BitmapBytes(int64_t bits) { return (bits + 7) / 8; }
+
+// ---- ArrayData -> b200_col ----------------------------------------------------------------------
+Status CheckOnDevice(const std::shared_ptr<Buffer>& buf, const char* what) {
+  if (buf && buf->is_cpu()) {
+    return Status::Invalid("CUDA-backed kernel got a host-resident ", what,
+                           " buffer; inputs must be CudaBuffer-resident ArrayData");
+  }
+  return Status::OK();
+}
+
+// physical b200_type of a fixed-width column: filter and group keys only move bits
+// (PrimitiveFilter dispatches on bit_width, vector_selection.cc:813-832)
+Result<int32_t> PhysicalType(const DataType& type) {
+  if (type.id() == Type::BOOL) return B200_BOOL;
+  if (!is_primitive(type.id())) {
+    return Status::NotImplemented("CUDA-backed kernels handle fixed-width primitive columns, got ",
+                                  type.ToString());
+  }
+  switch (checked_cast<const FixedWidthType&>(type).bit_width()) {
+    case 8: return B200_UINT8;
+    case 16: return B200_UINT16;
+    case 32: return B200_UINT32;
+    case 64: return B200_UINT64;
+    default: break;
+  }
+  return Status::NotImplemented("bit width of ", type.ToString());
+}
+
+// logical b200_type: ordering and arithmetic depend on signedness / floating point
+Result<int32_t> NumericType(const DataType& type) {
+  switch (type.id()) {
+    case Type::UINT8: return B200_UINT8;
+    case Type::INT8: return B200_INT8;
+    case Type::UINT16: return B200_UINT16;
+    case Type::INT16: return B200_INT16;
+    case Type::UINT32: return B200_UINT32;
+    case Type::INT32: case Type::DATE32: case Type::TIME32: return B200_INT32;
+    case Type::UINT64: return B200_UINT64;
+    case Type::INT64: case Type::DATE64: case Type::TIME64: case Type::TIMESTAMP:
+    case Type::DURATION: return B200_INT64;
+    case Type::FLOAT: return B200_FLOAT;
+    case Type::DOUBLE: return B200_DOUBLE;
+    default: break;
+  }
+  return Status::NotImplemented("no CUDA-backed kernel for type ", type.ToString());
+}
+
+Status ToCol(const ArrayData& a, int32_t type, b200_col* c) {
+  if (a.buffers.size() < 2) return Status::Invalid("expected a primitive array layout");
+  RETURN_NOT_OK(CheckOnDevice(a.buffers[0], "validity"));
+  RETURN_NOT_OK(CheckOnDevice(a.buffers[1], "data"));
+  std::memset(c, 0, sizeof(*c));
+  c->validity = a.buffers[0] ? reinterpret_cast<const void*>(a.buffers[0]->address()) : nullptr;
+  c->data = a.buffers[1] ? reinterpret_cast<const void*>(a.buffers[1]->address()) : nullptr;
+  c->type = type;
+  c->length = a.length;
+  c->offset = a.offset;
+  // may be kUnknownNullCount, like PrimitiveArg (util_internal.cc:45-58); never computed on the host
+  c->null_count = a.buffers[0] ? a.null_count.load() : 0;
+  return Status::OK();
+}
+
+// ---- Filter --------------------------------------------------------------------------------------
+// == PrimitiveFilter (vector_selection.cc:786-835): GetFilterOutputSize -> PreallocateData -> Exec
+Result<std::shared_ptr<ArrayData>> FilterArray(DeviceState* dev, const ArrayData& values,
+                                               const ArrayData& mask, int null_selection) {
+  if (mask.type->id() != Type::BOOL) {
+    return Status::NotImplemented("Filter argument must be boolean type");
+  }
+  if (values.length != mask.length) {
+    // exec.cc:186-189 (ExecBatchIterator) — the code the reference's tests assert
+    return Status::Invalid("Array arguments must all be the same length");
+  }
+  ARROW_ASSIGN_OR_RAISE(const int32_t vtype, PhysicalType(*values.type));
+  b200_col v, m;
+  RETURN_NOT_OK(ToCol(values, vtype, &v));
+  RETURN_NOT_OK(ToCol(mask, B200_BOOL, &m));
+
+  std::lock_guard<std::mutex> lock(dev->mutex);
+  size_t plan_bytes = 0;
+  B200_OK_OR_RAISE(dev, b200_filter_plan_bytes(m.length, &plan_bytes));
+  ARROW_ASSIGN_OR_RAISE(auto plan, AllocateDevice(dev, static_cast<int64_t>(plan_bytes)));
+  void* plan_ptr = reinterpret_cast<void*>(plan->address());
+  int64_t out_len = 0;
+  B200_OK_OR_RAISE(dev, b200_filter_plan(dev->ctx, &m, null_selection, plan_ptr, &out_len));
+
+  int allocate_validity = 0;
+  int64_t out_null_count = 0;
+  B200_OK_OR_RAISE(dev, b200_filter_out_spec(&v, &m, null_selection, &allocate_validity, &out_null_count));
+
+  const int bits = vtype == B200_BOOL ? 1 : checked_cast<const FixedWidthType&>(*values.type).bit_width();
+  const int64_t data_bytes = bits == 1 ? BitmapBytes(out_len) : out_len * (bits / 8);
+  ARROW_ASSIGN_OR_RAISE(auto out_data, AllocateDevice(dev, data_bytes));
+  std::shared_ptr<Buffer> out_validity;
+  if (allocate_validity) {
+    ARROW_ASSIGN_OR_RAISE(out_validity, AllocateDevice(dev, BitmapBytes(out_len)));
+  }
+  B200_OK_OR_RAISE(dev, b200_filter_apply(dev->ctx, &v, &m, null_selection, plan_ptr,
+                                          reinterpret_cast<void*>(out_data->address()),
+                                          out_validity ? reinterpret_cast<void*>(out_validity->address()) : nullptr,
+                                          out_len));
+  // the plan buffer is released when this returns: its last reader must have finished
+  B200_OK_OR_RAISE(dev, b200_ctx_synchronize(dev->ctx));
+  return ArrayData::Make(values.type, out_len, {std::move(out_validity), std::move(out_data)}, out_null_count);
+}
+
+int NullSelectionOf(const FunctionOptions* options) {
+  if (!options) return 0;
+  return static_cast<const FilterOptions*>(options)->null_selection_behavior == FilterOptions::EMIT_NULL ? 1 : 0;
+}
+
+const FilterOptions kDefaultFilterOptions = FilterOptions::Defaults();
+const ArraySortOptions kDefaultArraySortOptions = ArraySortOptions::Defaults();
+const SortOptions kDefaultSortOptions = SortOptions::Defaults();
+
+const FunctionDoc array_filter_doc(
+    "Filter with a boolean selection filter (CUDA, sm_100a)",
+    "Same contract as the CPU array_filter; inputs and output are CudaBuffer-resident.",
+    {"array", "selection_filter"}, "FilterOptions");
+const FunctionDoc filter_doc(
+    "Filter with a boolean selection filter (CUDA, sm_100a)",
+    "Same contract as the CPU filter; inputs and output are CudaBuffer-resident.",
+    {"input", "selection_filter"}, "FilterOptions");
+const FunctionDoc array_sort_indices_doc(
+    "Return the indices that would sort an array (CUDA, sm_100a)",
+    "Stable; nulls last, NaNs before nulls; input and output are CudaBuffer-resident.",
+    {"array"}, "ArraySortOptions");
+const FunctionDoc sort_indices_doc(
+    "Return the indices that would sort an array (CUDA, sm_100a)",
+    "Array and single-chunk ChunkedArray inputs; see array_sort_indices.", {"input"}, "SortOptions");
+const FunctionDoc hash_count_doc("Count the number of null / non-null values per group (CUDA)", "", {"array", "group_id_array", "group_count"}, "CountOptions");
+const FunctionDoc hash_sum_doc("Sum values per group (CUDA)", "", {"array", "group_id_array", "group_count"});
+const FunctionDoc hash_min_max_doc("Min and max per group (CUDA)", "", {"array", "group_id_array", "group_count"}, "MinMaxOptions");
+const FunctionDoc hash_mean_doc("Mean per group (CUDA); MeanImpl::Finalize over the grouped sum state", "", {"array", "group_id_array", "group_count"});
+
+struct FilterState : public KernelState {
+  explicit FilterState(int null_selection) : null_selection(null_selection) {}
+  int null_selection;
+};
+struct SortState : public KernelState {
+  explicit SortState(SortOrder order) : order(order) {}
+  SortOrder order;
+};
+
+// Datum of chunks -> list of ArrayData
+Result<ArrayVector> ChunksOf(const Datum& d) {
+  if (d.kind() == Datum::ARRAY) return ArrayVector{d.make_array()};
+  if (d.kind() == Datum::CHUNKED_ARRAY) return d.chunked_array()->chunks();
+  return Status::NotImplemented("CUDA-backed kernels take Array or ChunkedArray, got ", d.ToString());
+}
+
+// == FilterMetaFunction (vector_selection.cc:1877-1903) + FilterRecordBatch / FilterTable (:1776-1866):
+// the table forms are the same mask applied column by column (pinned by vector_selection_test.cc:208-236)
+class CudaFilterMetaFunction : public MetaFunction {
+ public:
+  explicit CudaFilterMetaFunction(int device)
+      : MetaFunction("filter", Arity::Binary(), &filter_doc, &kDefaultFilterOptions), device_(device) {}
+
+  Result<Datum> ExecuteImpl(const std::vector<Datum>& args, const FunctionOptions* options,
+                            ExecContext* ctx) const override {
+    if (args[1].type()->id() != Type::BOOL) {
+      return Status::NotImplemented("Filter argument must be boolean type");
+    }
+    ARROW_ASSIGN_OR_RAISE(DeviceState * dev, GetDevice(device_));
+    const int null_selection = NullSelectionOf(options);
+    if (args[0].kind() == Datum::RECORD_BATCH) {
+      if (args[1].kind() != Datum::ARRAY) return Status::NotImplemented("filter(RecordBatch, non-Array)");
+      const auto& batch = *args[0].record_batch();
+      std::vector<std::shared_ptr<ArrayData>> columns(batch.num_columns());
+      int64_t out_len = 0;
+      for (int i = 0; i < batch.num_columns(); ++i) {
+        ARROW_ASSIGN_OR_RAISE(columns[i], FilterArray(dev, *batch.column_data(i), *args[1].array(), null_selection));
+        out_len = columns[i]->length;
+      }
+      return Datum(RecordBatch::Make(batch.schema(), out_len, std::move(columns)));
+    }
+    if (args[0].kind() == Datum::TABLE) {
+      return Status::NotImplemented("filter(Table): filter each RecordBatch");
+    }
+    if (args[0].kind() == Datum::CHUNKED_ARRAY || args[1].kind() == Datum::CHUNKED_ARRAY) {
+      // chunk pairs must line up (the reference re-chunks on the host; device chunks are not re-sliced here)
+      ARROW_ASSIGN_OR_RAISE(auto vchunks, ChunksOf(args[0]));
+      ARROW_ASSIGN_OR_RAISE(auto mchunks, ChunksOf(args[1]));
+      if (args[0].length() != args[1].length()) return Status::Invalid("Array arguments must all be the same length");
+      if (vchunks.size() != mchunks.size()) return Status::NotImplemented("filter: values and mask chunk layouts differ");
+      ArrayVector out;
+      for (size_t i = 0; i < vchunks.size(); ++i) {
+        if (vchunks[i]->length() != mchunks[i]->length()) return Status::NotImplemented("filter: values and mask chunk layouts differ");
+        ARROW_ASSIGN_OR_RAISE(auto piece, FilterArray(dev, *vchunks[i]->data(), *mchunks[i]->data(), null_selection));
+        out.push_back(MakeArray(piece));
+      }
+      return Datum(std::make_shared<ChunkedArray>(std::move(out), args[0].type()));
+    }
+    return CallFunction("array_filter", args, options, ctx);
+  }
+
+ private:
+  int device_;
+};
+
+// ---- SortIndices ---------------------------------------------------------------------------------
+// == ArraySortIndices::Exec (vector_sort.cc:559-575); output uint64, never null (:1747)
+Result<std::shared_ptr<ArrayData>> SortIndicesArray(DeviceState* dev, const ArrayData& values, SortOrder order) {
+  ARROW_ASSIGN_OR_RAISE(const int32_t vtype, NumericType(*values.type));
+  b200_col v;
+  RETURN_NOT_OK(ToCol(values, vtype, &v));
+  std::lock_guard<std::mutex> lock(dev->mutex);
+  size_t scratch_bytes = 0;
+  B200_OK_OR_RAISE(dev, b200_sort_indices_scratch_bytes(v.length, &scratch_bytes));
+  ARROW_ASSIGN_OR_RAISE(auto scratch, AllocateDevice(dev, static_cast<int64_t>(scratch_bytes)));
+  ARROW_ASSIGN_OR_RAISE(auto out, AllocateDevice(dev, v.length * 8));
+  B200_OK_OR_RAISE(dev, b200_sort_indices(dev->ctx, &v, order == SortOrder::Descending ? 1 : 0, /*index_base=*/0,
+                                          reinterpret_cast<uint64_t*>(out->address()),
+                                          reinterpret_cast<void*>(scratch->address()), scratch_bytes));
+  B200_OK_OR_RAISE(dev, b200_ctx_synchronize(dev->ctx));  // scratch is released on return
+  return ArrayData::Make(uint64(), v.length, {nullptr, std::move(out)}, 0);
+}
+
+// == SortIndicesMetaFunction (vector_sort.cc:1565-1711), Array / single-chunk ChunkedArray routes
+class CudaSortIndicesMetaFunction : public MetaFunction {
+ public:
+  explicit CudaSortIndicesMetaFunction(int device)
+      : MetaFunction("sort_indices", Arity::Unary(), &sort_indices_doc, &kDefaultSortOptions), device_(device) {}
+
+  Result<Datum> ExecuteImpl(const std::vector<Datum>& args, const FunctionOptions* options,
+                            ExecContext* ctx) const override {
+    const SortOptions& sort_options = static_cast<const SortOptions&>(*options);
+    SortOrder order = SortOrder::Ascending;  // vector_sort.cc:1600-1606
+    if (!sort_options.sort_keys.empty()) order = sort_options.sort_keys[0].order;
+    ArraySortOptions array_options(order);
+    switch (args[0].kind()) {
+      case Datum::ARRAY:
+        return CallFunction("array_sort_indices", {args[0]}, &array_options, ctx);
+      case Datum::CHUNKED_ARRAY: {
+        const auto& chunked = *args[0].chunked_array();
+        if (chunked.num_chunks() == 1) {
+          return CallFunction("array_sort_indices", {Datum(chunked.chunk(0))}, &array_options, ctx);
+        }
+        if (chunked.num_chunks() == 0) {
+          ARROW_ASSIGN_OR_RAISE(DeviceState * dev, GetDevice(device_));
+          ARROW_ASSIGN_OR_RAISE(auto out, AllocateDevice(dev, 0));
+          return Datum(ArrayData::Make(uint64(), 0, {nullptr, std::move(out)}, 0));
+        }
+        return Status::NotImplemented("sort_indices over a multi-chunk device ChunkedArray: concatenate on the device first");
+      }
+      default:
+        break;
+    }
+    return Status::NotImplemented("Unsupported types for sort_indices operation: values=", args[0].ToString());
+  }
+
+ private:
+  int device_;
+};
+
+// ---- grouped aggregation -------------------------------------------------------------------------
+struct AggInfo {
+  int32_t kind;
+  std::shared_ptr<DataType> out_type;
+};
+
+// accumulator / output types: GroupedCountImpl -> int64 (hash_aggregate.cc:507-509), GroupedSumImpl
+// -> int64 / uint64 / double (aggregate_internal.h:30-50), GroupedMinMaxImpl -> struct<min,max> (:759-761)
+Result<AggInfo> ResolveAggregate(const std::string& function, const std::shared_ptr<DataType>& arg_type_ptr) {
+  const DataType& arg_type = *arg_type_ptr;
+  AggInfo info;
+  if (function == "hash_count") {
+    info.kind = B200_HASH_COUNT;
+    info.out_type = int64();
+    return info;
+  }
+  if (function == "hash_sum" || function == "hash_mean") {
+    info.kind = function == "hash_sum" ? B200_HASH_SUM : B200_HASH_MEAN;
+    if (!is_integer(arg_type.id()) && !is_floating(arg_type.id()) ) {
+      return Status::NotImplemented("Summing data of type ", arg_type.ToString());
+    }
+    if (arg_type.id() == Type::HALF_FLOAT) return Status::NotImplemented("Summing data of type ", arg_type.ToString());
+    if (function == "hash_mean") info.out_type = float64();
+    else if (is_floating(arg_type.id())) info.out_type = float64();
+    else if (is_signed_integer(arg_type.id())) info.out_type = int64();
+    else info.out_type = uint64();
+    return info;
+  }
+  if (function == "hash_min_max") {
+    info.kind = B200_HASH_MIN_MAX;
+    if ((!is_integer(arg_type.id()) && !is_floating(arg_type.id())) || arg_type.id() == Type::HALF_FLOAT) {
+      return Status::NotImplemented("Grouped MinMax data of type ", arg_type.ToString());
+    }
+    info.out_type = struct_({field("min", arg_type_ptr), field("max", arg_type_ptr)});
+    return info;
+  }
+  return Status::KeyError("No function registered with name: ", function);
+}
+
+int32_t OptionOf(int32_t kind, const FunctionOptions* options) {
+  if (!options) return 0;
+  if (kind == B200_HASH_COUNT) return static_cast<const CountOptions*>(options)->count_mode == CountOptions::COUNT_NULL ? 1 : 0;
+  if (kind == B200_HASH_MIN_MAX) return static_cast<const MinMaxOptions*>(options)->null_handling == MinMaxOptions::EMIT_NULL ? 1 : 0;
+  return 0;
+}
+
+Result<int32_t> AggArgType(int32_t kind, const DataType& type) {
+  if (kind == B200_HASH_COUNT) {
+    if (type.id() == Type::BOOL) return B200_BOOL;
+    return PhysicalType(type);  // only validity is read
+  }
+  return NumericType(type);
+}
+
+struct GroupByHandle {
+  DeviceState* dev = nullptr;
+  b200_groupby* gb = nullptr;
+  ~GroupByHandle() {
+    if (gb) {
+      std::lock_guard<std::mutex> lock(dev->mutex);
+      b200_groupby_destroy(gb);
+    }
+  }
+};
+
+// allocates and fills the aggregate outputs of a handle; returns one ArrayData per aggregate
+Result<ArrayDataVector> FinalizeAggregates(GroupByHandle* h, const std::vector<AggInfo>& infos,
+                                           const std::vector<std::shared_ptr<DataType>>& arg_types, uint32_t num_groups,
+                                           std::vector<b200_out_col>* out_keys) {
+  DeviceState* dev = h->dev;
+  std::vector<b200_out_col> outs;
+  std::vector<std::shared_ptr<Buffer>> data_bufs, validity_bufs;
+  for (size_t j = 0; j < infos.size(); ++j) {
+    const int n_out = infos[j].kind == B200_HASH_MIN_MAX ? 2 : 1;
+    int width = 8;
+    if (infos[j].kind == B200_HASH_MIN_MAX) width = checked_cast<const FixedWidthType&>(*arg_types[j]).bit_width() / 8;
+    std::shared_ptr<Buffer> validity;
+    ARROW_ASSIGN_OR_RAISE(validity, AllocateDevice(dev, BitmapBytes(num_groups)));
+    for (int q = 0; q < n_out; ++q) {
+      ARROW_ASSIGN_OR_RAISE(auto data, AllocateDevice(dev, int64_t(num_groups) * width));
+      b200_out_col o;
+      std::memset(&o, 0, sizeof(o));
+      o.data = reinterpret_cast<void*>(data->address());
+      o.validity = reinterpret_cast<void*>(validity->address());
+      outs.push_back(o);
+      data_bufs.push_back(std::move(data));
+      validity_bufs.push_back(validity);
+    }
+  }
+  B200_OK_OR_RAISE(dev, b200_groupby_finalize(h->gb, outs.data(), out_keys ? out_keys->data() : nullptr));
+  ArrayDataVector result;
+  size_t oi = 0;
+  for (size_t j = 0; j < infos.size(); ++j) {
+    if (infos[j].kind == B200_HASH_MIN_MAX) {
+      // struct<min,max>, children share one validity (hash_aggregate.cc:741-757)
+      auto mins = ArrayData::Make(arg_types[j], num_groups, {validity_bufs[oi], data_bufs[oi]}, outs[oi].null_count);
+      auto maxes = ArrayData::Make(arg_types[j], num_groups, {validity_bufs[oi], data_bufs[oi + 1]}, outs[oi].null_count);
+      result.push_back(ArrayData::Make(infos[j].out_type, num_groups, {nullptr}, {std::move(mins), std::move(maxes)}, 0));
+      oi += 2;
+    } else if (infos[j].kind == B200_HASH_COUNT) {
+      result.push_back(ArrayData::Make(infos[j].out_type, num_groups, {nullptr, data_bufs[oi]}, 0));  // never null
+      oi += 1;
+    } else {
+      // validity only if some group is empty (hash_aggregate.cc:595-605)
+      const int64_t nulls = outs[oi].null_count;
+      result.push_back(ArrayData::Make(infos[j].out_type, num_groups,
+                                       {nulls ? validity_bufs[oi] : nullptr, data_bufs[oi]}, nulls));
+      oi += 1;
+    }
+  }
+  return result;
+}
+
+// ---- HashAggregateKernel{init, consume, merge, finalize} (kernel.h:681-721) over dense group ids
+struct CudaGroupedAggregator : public KernelState {
+  GroupByHandle handle;
+  AggInfo info;
+  std::shared_ptr<DataType> arg_type;
+  uint32_t num_groups = 0;
+};
+
+HashAggregateKernel MakeHashKernel(const std::string& function, int device) {
+  HashAggregateKernel kernel;
+  kernel.init = [function, device](KernelContext*, const KernelInitArgs& args) -> Result<std::unique_ptr<KernelState>> {
+    auto state = ::arrow::internal::make_unique<CudaGroupedAggregator>();
+    state->arg_type = args.inputs[0].type;
+    ARROW_ASSIGN_OR_RAISE(state->info, ResolveAggregate(function, state->arg_type));
+    ARROW_ASSIGN_OR_RAISE(state->handle.dev, GetDevice(device));
+    b200_agg_spec spec;
+    std::memset(&spec, 0, sizeof(spec));
+    spec.kind = state->info.kind;
+    ARROW_ASSIGN_OR_RAISE(spec.arg_type, AggArgType(spec.kind, *state->arg_type));
+    spec.option = OptionOf(spec.kind, args.options);
+    const int32_t dummy_key = B200_UINT32;  // ids arrive dense: the key side of the handle is unused
+    std::lock_guard<std::mutex> lock(state->handle.dev->mutex);
+    B200_OK_OR_RAISE(state->handle.dev, b200_groupby_create(state->handle.dev->ctx, 1, &dummy_key, 1, &spec, 1024, &state->handle.gb));
+    return std::move(state);
+  };
+  kernel.signature = KernelSignature::Make(
+      {InputType(ValueDescr::ARRAY), InputType::Array(Type::UINT32), InputType::Scalar(Type::UINT32)},
+      OutputType([](KernelContext* ctx, const std::vector<ValueDescr>&) -> Result<ValueDescr> {
+        return ValueDescr::Array(checked_cast<CudaGroupedAggregator*>(ctx->state())->info.out_type);
+      }));
+  kernel.consume = [](KernelContext* ctx, const ExecBatch& batch) -> Status {
+    auto* state = checked_cast<CudaGroupedAggregator*>(ctx->state());
+    DeviceState* dev = state->handle.dev;
+    const ArrayData& arg = *batch[0].array();
+    const ArrayData& ids = *batch[1].array();
+    const uint32_t num_groups = checked_cast<const UInt32Scalar&>(*batch[2].scalar()).value;
+    b200_col c;
+    ARROW_ASSIGN_OR_RAISE(const int32_t t, AggArgType(state->info.kind, *arg.type));
+    RETURN_NOT_OK(ToCol(arg, t, &c));
+    RETURN_NOT_OK(CheckOnDevice(ids.buffers[1], "group id"));
+    const uint32_t* id_ptr = reinterpret_cast<const uint32_t*>(ids.buffers[1]->address()) + ids.offset;
+    std::lock_guard<std::mutex> lock(dev->mutex);
+    B200_OK_OR_RAISE(dev, b200_hash_agg_consume(state->handle.gb, 0, &c, id_ptr, num_groups));
+    state->num_groups = std::max(state->num_groups, num_groups);
+    return Status::OK();
+  };
+  kernel.merge = [](KernelContext* ctx, KernelState&& src, KernelState* dst) -> Status {
+    // the reference leaves this NotImplemented (hash_aggregate.cc:795-798); here two dense states over the
+    // same id space fold slot by slot
+    auto* d = checked_cast<CudaGroupedAggregator*>(dst);
+    auto& s = checked_cast<CudaGroupedAggregator&>(src);
+    std::lock_guard<std::mutex> lock(d->handle.dev->mutex);
+    B200_OK_OR_RAISE(d->handle.dev, b200_hash_agg_merge(d->handle.gb, s.handle.gb));
+    d->num_groups = std::max(d->num_groups, s.num_groups);
+    return Status::OK();
+  };
+  kernel.finalize = [](KernelContext* ctx, Datum* out) -> Status {
+    auto* state = checked_cast<CudaGroupedAggregator*>(ctx->state());
+    std::lock_guard<std::mutex> lock(state->handle.dev->mutex);
+    ARROW_ASSIGN_OR_RAISE(auto arrays, FinalizeAggregates(&state->handle, {state->info}, {state->arg_type}, state->num_groups, nullptr));
+    *out = Datum(arrays[0]);
+    return Status::OK();
+  };
+  return kernel;
+}
+
+// ---- Grouper twin ----------------------------------------------------------------------------
+class CudaGrouper : public internal::Grouper {
+ public:
+  static Result<std::unique_ptr<internal::Grouper>> Make(const std::vector<ValueDescr>& descrs, int device) {
+    auto g = ::arrow::internal::make_unique<CudaGrouper>();
+    ARROW_ASSIGN_OR_RAISE(g->handle_.dev, GetDevice(device));
+    for (const auto& d : descrs) {
+      // GrouperImpl::Make: "Keys of type ..." (hash_aggregate.cc:325-352)
+      if (d.type->id() != Type::BOOL && !is_primitive(d.type->id())) return Status::NotImplemented("Keys of type ", d.type->ToString());
+      ARROW_ASSIGN_OR_RAISE(const int32_t t, PhysicalType(*d.type));
+      g->key_types_.push_back(t);
+      g->types_.push_back(d.type);
+    }
+    std::lock_guard<std::mutex> lock(g->handle_.dev->mutex);
+    B200_OK_OR_RAISE(g->handle_.dev, b200_groupby_create(g->handle_.dev->ctx, int(g->key_types_.size()), g->key_types_.data(), 0, nullptr, 0, &g->handle_.gb));
+    return std::unique_ptr<internal::Grouper>(std::move(g));
+  }
+
+  Result<Datum> Consume(const ExecBatch& batch) override {
+    DeviceState* dev = handle_.dev;
+    std::vector<b200_col> keys(batch.num_values());
+    if (size_t(batch.num_values()) != key_types_.size()) return Status::Invalid("expected ", key_types_.size(), " key columns");
+    for (int k = 0; k < batch.num_values(); ++k) RETURN_NOT_OK(ToCol(*batch[k].array(), key_types_[k], &keys[k]));
+    std::lock_guard<std::mutex> lock(dev->mutex);
+    ARROW_ASSIGN_OR_RAISE(auto ids, AllocateDevice(dev, batch.length * 4));
+    B200_OK_OR_RAISE(dev, b200_grouper_consume(handle_.gb, keys.data(), reinterpret_cast<uint32_t*>(ids->address())));
+    B200_OK_OR_RAISE(dev, b200_groupby_num_groups(handle_.gb, &num_groups_));
+    return Datum(ArrayData::Make(uint32(), batch.length, {nullptr, std::move(ids)}, 0));
+  }
+
+  Result<ExecBatch> GetUniques() override {
+    DeviceState* dev = handle_.dev;
+    std::lock_guard<std::mutex> lock(dev->mutex);
+    ARROW_ASSIGN_OR_RAISE(auto keys, EmitKeys(&handle_, types_, key_types_, num_groups_));
+    ExecBatch out({}, num_groups_);
+    for (auto& k : keys) out.values.emplace_back(std::move(k));
+    return out;
+  }
+
+  uint32_t num_groups() const override { return num_groups_; }
+
+  // key columns of a handle in group order: GetUniques (hash_aggregate.cc:412-429); validity only if a key is null
+  static Result<ArrayDataVector> EmitKeys(GroupByHandle* h, const std::vector<std::shared_ptr<DataType>>& types,
+                                          const std::vector<int32_t>& key_types, uint32_t num_groups) {
+    DeviceState* dev = h->dev;
+    std::vector<b200_out_col> outs(types.size());
+    std::vector<std::shared_ptr<Buffer>> data(types.size()), validity(types.size());
+    for (size_t k = 0; k < types.size(); ++k) {
+      const int bits = key_types[k] == B200_BOOL ? 1 : checked_cast<const FixedWidthType&>(*types[k]).bit_width();
+      ARROW_ASSIGN_OR_RAISE(data[k], AllocateDevice(dev, bits == 1 ? BitmapBytes(num_groups) : int64_t(num_groups) * (bits / 8)));
+      ARROW_ASSIGN_OR_RAISE(validity[k], AllocateDevice(dev, BitmapBytes(num_groups)));
+      std::memset(&outs[k], 0, sizeof(b200_out_col));
+      outs[k].data = reinterpret_cast<void*>(data[k]->address());
+      outs[k].validity = reinterpret_cast<void*>(validity[k]->address());
+    }
+    B200_OK_OR_RAISE(dev, b200_groupby_finalize(h->gb, nullptr, outs.data()));
+    ArrayDataVector result;
+    for (size_t k = 0; k < types.size(); ++k) {
+      const int64_t nulls = outs[k].null_count;
+      result.push_back(ArrayData::Make(types[k], num_groups, {nulls ? validity[k] : nullptr, data[k]}, nulls));
+    }
+    return result;
+  }
+
+ private:
+  GroupByHandle handle_;
+  std::vector<int32_t> key_types_;
+  std::vector<std::shared_ptr<DataType>> types_;
+  uint32_t num_groups_ = 0;
+};
+
+}  // namespace
+
+// ==================================================================================================
+Status RegisterCudaKernels(FunctionRegistry* registry, int device) {
+  if (!registry) return Status::Invalid("null registry");
+  // array_filter: VectorFunction, one kernel over every primitive type (vector_selection.cc:2133)
+  {
+    auto func = std::make_shared<VectorFunction>("array_filter", Arity::Binary(), &array_filter_doc, &kDefaultFilterOptions);
+    VectorKernel kernel;
+    // outputs are device buffers the executor cannot allocate or pre-fill
+    kernel.mem_allocation = MemAllocation::NO_PREALLOCATE;
+    kernel.null_handling = NullHandling::COMPUTED_NO_PREALLOCATE;
+    kernel.can_execute_chunkwise = false;  // never re-slice device arrays on the host
+    kernel.init = [](KernelContext*, const KernelInitArgs& args) -> Result<std::unique_ptr<KernelState>> {
+      return std::unique_ptr<KernelState>(new FilterState(NullSelectionOf(args.options)));
+    };
+    kernel.signature = KernelSignature::Make(
+        {InputType(match::Primitive(), ValueDescr::ARRAY), InputType::Array(boolean())},
+        OutputType([](KernelContext*, const std::vector<ValueDescr>& descrs) -> Result<ValueDescr> { return descrs[0]; }));
+    kernel.exec = [device](KernelContext* ctx, const ExecBatch& batch, Datum* out) -> Status {
+      ARROW_ASSIGN_OR_RAISE(DeviceState * dev, GetDevice(device));
+      const int null_selection = checked_cast<const FilterState*>(ctx->state())->null_selection;
+      ARROW_ASSIGN_OR_RAISE(auto result, FilterArray(dev, *batch[0].array(), *batch[1].array(), null_selection));
+      out->value = std::move(result);
+      return Status::OK();
+    };
+    RETURN_NOT_OK(func->AddKernel(std::move(kernel)));
+    RETURN_NOT_OK(registry->AddFunction(std::move(func)));
+  }
+  RETURN_NOT_OK(registry->AddFunction(std::make_shared<CudaFilterMetaFunction>(device)));
+  // array_sort_indices: one kernel per numeric / temporal type (vector_sort.cc:582-595)
+  {
+    auto func = std::make_shared<VectorFunction>("array_sort_indices", Arity::Unary(), &array_sort_indices_doc, &kDefaultArraySortOptions);
+    VectorKernel base;
+    base.mem_allocation = MemAllocation::NO_PREALLOCATE;
+    base.null_handling = NullHandling::OUTPUT_NOT_NULL;
+    base.can_execute_chunkwise = false;
+    base.init = [](KernelContext*, const KernelInitArgs& args) -> Result<std::unique_ptr<KernelState>> {
+      const auto* options = static_cast<const ArraySortOptions*>(args.options);
+      return std::unique_ptr<KernelState>(new SortState(options ? options->order : SortOrder::Ascending));
+    };
+    base.exec = [device](KernelContext* ctx, const ExecBatch& batch, Datum* out) -> Status {
+      ARROW_ASSIGN_OR_RAISE(DeviceState * dev, GetDevice(device));
+      ARROW_ASSIGN_OR_RAISE(auto result, SortIndicesArray(dev, *batch[0].array(), checked_cast<const SortState*>(ctx->state())->order));
+      out->value = std::move(result);
+      return Status::OK();
+    };
+    std::vector<std::shared_ptr<DataType>> types = {uint8(), int8(), uint16(), int16(), uint32(), int32(), uint64(), int64(), float32(), float64(), date32(), date64()};
+    for (const auto& ty : types) {
+      base.signature = KernelSignature::Make({InputType::Array(ty)}, uint64());
+      RETURN_NOT_OK(func->AddKernel(base));
+    }
+    for (auto id : {Type::TIMESTAMP, Type::TIME32, Type::TIME64, Type::DURATION}) {
+      base.signature = KernelSignature::Make({InputType::Array(id)}, uint64());
+      RETURN_NOT_OK(func->AddKernel(base));
+    }
+    RETURN_NOT_OK(registry->AddFunction(std::move(func)));
+  }
+  RETURN_NOT_OK(registry->AddFunction(std::make_shared<CudaSortIndicesMetaFunction>(device)));
+  // hash aggregates (hash_aggregate.cc:1039-1062) + hash_mean
+  {
+    static auto default_count_options = CountOptions::Defaults();
+    static auto default_minmax_options = MinMaxOptions::Defaults();
+    struct Entry { const char* name; const FunctionDoc* doc; const FunctionOptions* defaults; };
+    const Entry entries[] = {{"hash_count", &hash_count_doc, &default_count_options},
+                             {"hash_sum", &hash_sum_doc, nullptr},
+                             {"hash_min_max", &hash_min_max_doc, &default_minmax_options},
+                             {"hash_mean", &hash_mean_doc, nullptr}};
+    for (const auto& e : entries) {
+      auto func = std::make_shared<HashAggregateFunction>(e.name, Arity::Ternary(), e.doc, e.defaults);
+      RETURN_NOT_OK(func->AddKernel(MakeHashKernel(e.name, device)));
+      RETURN_NOT_OK(registry->AddFunction(std::move(func)));
+    }
+  }
+  return Status::OK();
+}
+
+Result<std::unique_ptr<FunctionRegistry>> MakeCudaRegistry(int device) {
+  auto registry = FunctionRegistry::Make();
+  RETURN_NOT_OK(RegisterCudaKernels(registry.get(), device));
+  return std::move(registry);
+}
+
+Result<std::unique_ptr<internal::Grouper>> MakeGrouper(const std::vector<ValueDescr>& descrs, ExecContext*, int device) {
+  return CudaGrouper::Make(descrs, device);
+}
+
+Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Datum>& keys,
+                      const std::vector<internal::Aggregate>& aggregates, ExecContext* ctx) {
+  if (!ctx) return Status::Invalid("cuda::GroupBy needs an ExecContext carrying the CUDA registry");
+  // GetKernels (hash_aggregate.cc:809-830)
+  if (aggregates.size() != arguments.size()) {
+    return Status::Invalid(aggregates.size(), " aggregate functions were specified but ", arguments.size(), " arguments were provided.");
+  }
+  if (keys.empty()) return Status::Invalid("GroupBy needs at least one key");
+  std::vector<AggInfo> infos(aggregates.size());
+  std::vector<b200_agg_spec> specs(aggregates.size());
+  std::vector<std::shared_ptr<DataType>> arg_types(aggregates.size());
+  for (size_t i = 0; i < aggregates.size(); ++i) {
+    ARROW_ASSIGN_OR_RAISE(auto function, ctx->func_registry()->GetFunction(aggregates[i].function));  // KeyError if absent
+    if (function->kind() != Function::HASH_AGGREGATE) return Status::Invalid(aggregates[i].function, " is not a hash aggregate function");
+    arg_types[i] = arguments[i].type();
+    ARROW_ASSIGN_OR_RAISE(infos[i], ResolveAggregate(aggregates[i].function, arg_types[i]));
+    const FunctionOptions* options = aggregates[i].options ? aggregates[i].options : function->default_options();
+    std::memset(&specs[i], 0, sizeof(b200_agg_spec));
+    specs[i].kind = infos[i].kind;
+    ARROW_ASSIGN_OR_RAISE(specs[i].arg_type, AggArgType(infos[i].kind, *arg_types[i]));
+    specs[i].option = OptionOf(infos[i].kind, options);
+  }
+  std::vector<int32_t> key_types;
+  std::vector<std::shared_ptr<DataType>> key_dtypes;
+  for (const auto& k : keys) {
+    if (k.type()->id() != Type::BOOL && !is_primitive(k.type()->id())) return Status::NotImplemented("Keys of type ", k.type()->ToString());
+    ARROW_ASSIGN_OR_RAISE(const int32_t t, PhysicalType(*k.type()));
+    key_types.push_back(t);
+    key_dtypes.push_back(k.type());
+  }
+  // every argument and key shares one chunk layout (the reference re-chunks on the host with
+  // ExecBatchIterator; device chunks are consumed as they are, batch by batch)
+  std::vector<ArrayVector> arg_chunks(arguments.size()), key_chunks(keys.size());
+  for (size_t i = 0; i < arguments.size(); ++i) { ARROW_ASSIGN_OR_RAISE(arg_chunks[i], ChunksOf(arguments[i])); }
+  for (size_t i = 0; i < keys.size(); ++i) { ARROW_ASSIGN_OR_RAISE(key_chunks[i], ChunksOf(keys[i])); }
+  const size_t n_batches = key_chunks[0].size();
+  const int64_t total = keys[0].length();
+  for (size_t i = 0; i < arguments.size(); ++i)
+    if (arguments[i].length() != total) return Status::Invalid("Array arguments must all be the same length");
+  for (size_t i = 0; i < keys.size(); ++i)
+    if (keys[i].length() != total) return Status::Invalid("Array arguments must all be the same length");
+  for (const auto& c : arg_chunks) if (c.size() != n_batches) return Status::NotImplemented("GroupBy: arguments and keys must share one chunk layout");
+  for (const auto& c : key_chunks) if (c.size() != n_batches) return Status::NotImplemented("GroupBy: arguments and keys must share one chunk layout");
+
+  GroupByHandle handle;
+  ARROW_ASSIGN_OR_RAISE(handle.dev, GetDevice(0));
+  DeviceState* dev = handle.dev;
+  std::unique_lock<std::mutex> lock(dev->mutex);
+  B200_OK_OR_RAISE(dev, b200_groupby_create(dev->ctx, int(key_types.size()), key_types.data(), int(specs.size()), specs.data(), 0, &handle.gb));
+  uint64_t row_base = 0;
+  for (size_t b = 0; b < n_batches; ++b) {
+    const int64_t len = key_chunks[0][b]->length();
+    if (len == 0) continue;
+    std::vector<b200_col> kcols(keys.size()), acols(arguments.size());
+    for (size_t k = 0; k < keys.size(); ++k) {
+      if (key_chunks[k][b]->length() != len) return Status::NotImplemented("GroupBy: arguments and keys must share one chunk layout");
+      RETURN_NOT_OK(ToCol(*key_chunks[k][b]->data(), key_types[k], &kcols[k]));
+    }
+    for (size_t i = 0; i < arguments.size(); ++i) {
+      if (arg_chunks[i][b]->length() != len) return Status::NotImplemented("GroupBy: arguments and keys must share one chunk layout");
+      RETURN_NOT_OK(ToCol(*arg_chunks[i][b]->data(), specs[i].arg_type, &acols[i]));
+    }
+    B200_OK_OR_RAISE(dev, b200_groupby_consume(handle.gb, kcols.data(), acols.data(), row_base));
+    row_base += uint64_t(len);
+  }
+  uint32_t num_groups = 0;
+  B200_OK_OR_RAISE(dev, b200_groupby_num_groups(handle.gb, &num_groups));
+
+  // outputs: aggregates then keys (hash_aggregate.cc:946-965)
+  std::vector<b200_out_col> key_outs(keys.size());
+  std::vector<std::shared_ptr<Buffer>> key_data(keys.size()), key_validity(keys.size());
+  for (size_t k = 0; k < keys.size(); ++k) {
+    const int bits = key_types[k] == B200_BOOL ? 1 : checked_cast<const FixedWidthType&>(*key_dtypes[k]).bit_width();
+    ARROW_ASSIGN_OR_RAISE(key_data[k], AllocateDevice(dev, bits == 1 ? BitmapBytes(num_groups) : int64_t(num_groups) * (bits / 8)));
+    ARROW_ASSIGN_OR_RAISE(key_validity[k], AllocateDevice(dev, BitmapBytes(num_groups)));
+    std::memset(&key_outs[k], 0, sizeof(b200_out_col));
+    key_outs[k].data = reinterpret_cast<void*>(key_data[k]->address());
+    key_outs[k].validity = reinterpret_cast<void*>(key_validity[k]->address());
+  }
+  ARROW_ASSIGN_OR_RAISE(auto out_data, FinalizeAggregates(&handle, infos, arg_types, num_groups, &key_outs));
+  FieldVector out_fields;
+  for (size_t i = 0; i < aggregates.size(); ++i) out_fields.push_back(field(aggregates[i].function, infos[i].out_type));
+  for (size_t k = 0; k < keys.size(); ++k) {
+    const int64_t nulls = key_outs[k].null_count;
+    out_data.push_back(ArrayData::Make(key_dtypes[k], num_groups, {nulls ? key_validity[k] : nullptr, key_data[k]}, nulls));
+    out_fields.push_back(field("key_" + std::to_string(k), key_dtypes[k]));
+  }
+  lock.unlock();  // ~GroupByHandle takes the device mutex again
+  return Datum(ArrayData::Make(struct_(std::move(out_fields)), num_groups, {nullptr}, std::move(out_data), 0));
+}
+
+}  // namespace cuda
+}  // namespace compute
+}  // namespace arrow

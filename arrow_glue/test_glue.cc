@@ -1,0 +1,365 @@
+// test_glue.cc — GPU parity driver for the Arrow glue: every check runs the SAME call twice through
+// the reference's public API — once with the reference's default (CPU) registry on host arrays,
+// once with the CUDA registry on CudaBuffer-resident copies — and compares the results on the host
+// with the reference's own Array::Equals.  Cases follow the reference's tests
+// (vector_selection_test.cc:296-321, vector_sort_test.cc:423-464, hash_aggregate_test.cc:480-605).
+// Test infrastructure: run by tests/test_glue_gpu.py on the GPU box; exits non-zero on any mismatch.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <iostream>
+#include <random>
+#include <string>
+#include <vector>
+
+#include "arrow/api.h"
+#include "arrow/compute/api.h"
+#include "arrow/compute/exec.h"
+#include "arrow/compute/kernel.h"
+#include "arrow/gpu/cuda_api.h"
+#include "arrow/util/checked_cast.h"
+
+#include "b200_arrow.h"
+
+using namespace arrow;  // NOLINT
+namespace cp = arrow::compute;
+
+static int g_failures = 0, g_checks = 0;
+#define CHECK_TRUE(cond, what)                                         \
+  do {                                                                 \
+    ++g_checks;                                                        \
+    if (!(cond)) {                                                     \
+      ++g_failures;                                                    \
+      std::cout << "FAIL " << what << " (" #cond ")" << std::endl;     \
+    } else {                                                           \
+      std::cout << "ok   " << what << std::endl;                       \
+    }                                                                  \
+  } while (0)
+#define ABORT_NOT_OK(expr)                                                         \
+  do {                                                                             \
+    ::arrow::Status _st = (expr);                                                  \
+    if (!_st.ok()) {                                                               \
+      std::cout << "ABORT " #expr ": " << _st.ToString() << std::endl;             \
+      std::exit(2);                                                                \
+    }                                                                              \
+  } while (0)
+template <typename T>
+T Unwrap(Result<T> r, const char* what) {
+  if (!r.ok()) {
+    std::cout << "ABORT " << what << ": " << r.status().ToString() << std::endl;
+    std::exit(2);
+  }
+  return r.MoveValueUnsafe();
+}
+#define GET(expr) Unwrap((expr), #expr)
+
+static std::shared_ptr<cuda::CudaContext> g_cuda;
+
+// ---- host <-> device copies of ArrayData (buffers copied whole; offsets / null counts kept)
+std::shared_ptr<ArrayData> ToDevice(const ArrayData& a) {
+  auto out = a.Copy();
+  for (auto& buf : out->buffers) {
+    if (!buf) continue;
+    auto dbuf = GET(g_cuda->Allocate(std::max<int64_t>(buf->size(), 64)));
+    if (buf->size() > 0) ABORT_NOT_OK(dbuf->CopyFromHost(0, buf->data(), buf->size()));
+    buf = dbuf;
+  }
+  for (auto& child : out->child_data) child = ToDevice(*child);
+  return out;
+}
+std::shared_ptr<ArrayData> ToHost(const ArrayData& a) {
+  auto out = a.Copy();
+  for (auto& buf : out->buffers) {
+    if (!buf) continue;
+    auto hbuf = GET(AllocateBuffer(buf->size()));
+    if (buf->size() > 0) {
+      auto cbuf = GET(cuda::CudaBuffer::FromBuffer(buf));
+      ABORT_NOT_OK(cbuf->CopyToHost(0, buf->size(), hbuf->mutable_data()));
+    }
+    buf = std::move(hbuf);
+  }
+  for (auto& child : out->child_data) child = ToHost(*child);
+  return out;
+}
+Datum DeviceDatum(const std::shared_ptr<Array>& a) { return Datum(ToDevice(*a->data())); }
+std::shared_ptr<Array> HostArray(const Datum& d) { return MakeArray(ToHost(*d.array())); }
+
+// ---- builders
+template <typename BuilderT, typename V>
+std::shared_ptr<Array> Make(const std::vector<V>& values, const std::vector<bool>& valid = {}) {
+  BuilderT b;
+  for (size_t i = 0; i < values.size(); ++i) {
+    if (!valid.empty() && !valid[i]) ABORT_NOT_OK(b.AppendNull());
+    else ABORT_NOT_OK(b.Append(static_cast<typename BuilderT::value_type>(values[i])));
+  }
+  return GET(b.Finish());
+}
+template <typename BuilderT, typename V>
+std::shared_ptr<Array> MakeRandom(int64_t n, std::mt19937_64& rng, double null_p, V lo, V hi, bool floating) {
+  BuilderT b;
+  std::uniform_real_distribution<double> u(0, 1);
+  for (int64_t i = 0; i < n; ++i) {
+    if (u(rng) < null_p) { ABORT_NOT_OK(b.AppendNull()); continue; }
+    const double x = u(rng);
+    V v = floating ? static_cast<V>(lo + (hi - lo) * x) : static_cast<V>(lo + static_cast<V>(x * (double(hi) - double(lo))));
+    ABORT_NOT_OK(b.Append(static_cast<typename BuilderT::value_type>(v)));
+  }
+  return GET(b.Finish());
+}
+
+void ExpectEqual(const std::shared_ptr<Array>& got, const std::shared_ptr<Array>& want, const std::string& what) {
+  const bool same = got->type()->Equals(want->type()) && got->Equals(want);
+  CHECK_TRUE(same, what);
+  if (!same && want->length() < 40) std::cout << "  want " << want->ToString() << "\n  got  " << got->ToString() << std::endl;
+  auto st = got->ValidateFull();
+  CHECK_TRUE(st.ok(), what + " ValidateFull");
+}
+
+// sums / means: |gpu - ref| <= 1e-12 * |ref| (north_star's float64 tolerance); everything else exact
+void ExpectStructClose(const std::shared_ptr<Array>& got, const std::shared_ptr<Array>& want, const std::string& what) {
+  bool ok = got->type()->Equals(want->type()) && got->length() == want->length();
+  if (ok) {
+    const auto& g = internal::checked_cast<const StructArray&>(*got);
+    const auto& w = internal::checked_cast<const StructArray&>(*want);
+    for (int f = 0; f < g.num_fields() && ok; ++f) {
+      auto gf = g.field(f), wf = w.field(f);
+      if (gf->type_id() == Type::DOUBLE) {
+        const auto& gd = internal::checked_cast<const DoubleArray&>(*gf);
+        const auto& wd = internal::checked_cast<const DoubleArray&>(*wf);
+        for (int64_t i = 0; i < gd.length() && ok; ++i) {
+          if (gd.IsNull(i) != wd.IsNull(i)) ok = false;
+          else if (gd.IsValid(i)) {
+            const double a = gd.Value(i), b = wd.Value(i);
+            if (!(a == b || std::fabs(a - b) <= 1e-12 * std::fabs(b) || (std::isnan(a) && std::isnan(b)))) ok = false;
+          }
+        }
+      } else {
+        ok = gf->Equals(wf);
+      }
+      if (!ok) std::cout << "  field " << f << " (" << got->type()->field(f)->name() << ") differs" << std::endl;
+    }
+  }
+  CHECK_TRUE(ok, what);
+  if (!ok && want->length() < 40) std::cout << "  want " << want->ToString() << "\n  got  " << got->ToString() << std::endl;
+}
+
+int main() {
+  auto manager = GET(cuda::CudaDeviceManager::Instance());
+  g_cuda = GET(manager->GetContext(0));
+  auto registry = GET(cp::cuda::MakeCudaRegistry(0));
+  cp::ExecContext gpu_ctx(default_memory_pool(), registry.get());
+  cp::ExecContext cpu_ctx;  // the reference's own registry and kernels
+  std::mt19937_64 rng(42);
+
+  {  // the registry holds exactly the reference's names for the path
+    for (const char* name : {"filter", "array_filter", "sort_indices", "array_sort_indices", "hash_count", "hash_sum", "hash_min_max", "hash_mean"})
+      CHECK_TRUE(registry->GetFunction(name).ok(), std::string("registered: ") + name);
+    CHECK_TRUE(registry->GetFunction("take").status().IsKeyError(), "unknown function -> KeyError (registry.cc:62-64)");
+  }
+
+  // ---------------- Filter ----------------
+  {
+    auto values = Make<Int32Builder, int32_t>({7, 8, 9});
+    auto mask = Make<BooleanBuilder, bool>({false, true, false}, {false, true, true});
+    for (auto ns : {cp::FilterOptions::DROP, cp::FilterOptions::EMIT_NULL}) {
+      cp::FilterOptions opts(ns);
+      auto want = GET(cp::Filter(values, mask, opts, &cpu_ctx)).make_array();
+      auto got = HostArray(GET(cp::Filter(DeviceDatum(values), DeviceDatum(mask), opts, &gpu_ctx)));
+      ExpectEqual(got, want, std::string("filter [7,8,9]x[null,1,0] ") + (ns ? "EMIT_NULL" : "DROP"));
+    }
+    // sliced mask / values (vector_selection_test.cc:312-315)
+    auto v2 = Make<Int64Builder, int64_t>({1, 2, 3, 4, 5, 6, 7, 8, 9, 10}, {true, true, false, true, true, true, true, false, true, true});
+    auto m2 = Make<BooleanBuilder, bool>({true, false, true, true, false, true, false, true, true, true, false, true});
+    auto vs = v2->Slice(3, 6), ms = m2->Slice(5, 6);
+    auto want = GET(cp::Filter(vs, ms, cp::FilterOptions::Defaults(), &cpu_ctx)).make_array();
+    auto got = HostArray(GET(cp::Filter(DeviceDatum(vs), DeviceDatum(ms), cp::FilterOptions::Defaults(), &gpu_ctx)));
+    ExpectEqual(got, want, "filter sliced values + sliced mask");
+    // length mismatch: the reference's test asserts Invalid (vector_selection_test.cc:317-320)
+    auto bad = cp::Filter(DeviceDatum(values), DeviceDatum(m2), cp::FilterOptions::Defaults(), &gpu_ctx);
+    CHECK_TRUE(bad.status().IsInvalid(), "filter length mismatch -> Invalid");
+    auto notbool = cp::Filter(DeviceDatum(values), DeviceDatum(values), cp::FilterOptions::Defaults(), &gpu_ctx);
+    CHECK_TRUE(notbool.status().IsNotImplemented(), "filter non-boolean mask -> NotImplemented (vector_selection.cc:1885-1887)");
+    auto hostin = cp::Filter(Datum(values), Datum(mask), cp::FilterOptions::Defaults(), &gpu_ctx);
+    CHECK_TRUE(hostin.status().IsInvalid(), "filter on host-resident input -> Invalid (no CPU fallback)");
+  }
+  {
+    const int64_t n = 200003;
+    std::vector<std::shared_ptr<Array>> columns = {
+        MakeRandom<Int64Builder, int64_t>(n, rng, 0.01, -(1LL << 60), 1LL << 60, false),
+        MakeRandom<Int8Builder, int8_t>(n, rng, 0.05, -100, 100, false),
+        MakeRandom<UInt16Builder, uint16_t>(n, rng, 0.0, 0, 60000, false),
+        MakeRandom<FloatBuilder, float>(n, rng, 0.1, -1e3f, 1e3f, true),
+        MakeRandom<DoubleBuilder, double>(n, rng, 0.5, -1e9, 1e9, true),
+        MakeRandom<BooleanBuilder, int>(n, rng, 0.02, 0, 2, false),
+        MakeRandom<Date32Builder, int32_t>(n, rng, 0.02, 8000, 11000, false)};
+    auto mask_nonull = MakeRandom<BooleanBuilder, int>(n, rng, 0.0, 0, 2, false);
+    auto mask_nulls = MakeRandom<BooleanBuilder, int>(n, rng, 0.05, 0, 2, false);
+    for (auto& col : columns) {
+      for (auto& mask : {mask_nonull, mask_nulls}) {
+        for (auto ns : {cp::FilterOptions::DROP, cp::FilterOptions::EMIT_NULL}) {
+          cp::FilterOptions opts(ns);
+          auto want = GET(cp::CallFunction("filter", {col, mask}, &opts, &cpu_ctx)).make_array();
+          auto got = HostArray(GET(cp::CallFunction("filter", {DeviceDatum(col), DeviceDatum(mask)}, &opts, &gpu_ctx)));
+          ExpectEqual(got, want, "filter random " + col->type()->ToString() + (mask.get() == mask_nulls.get() ? " mask+nulls " : " mask ") + (ns ? "EMIT_NULL" : "DROP"));
+        }
+      }
+    }
+    // RecordBatch form == per-column array_filter (vector_selection_test.cc:208-236)
+    auto schema_ = schema({field("a", columns[0]->type()), field("b", columns[4]->type())});
+    auto batch = RecordBatch::Make(schema_, n, {columns[0], columns[4]});
+    auto dbatch = RecordBatch::Make(schema_, n, {ToDevice(*columns[0]->data()), ToDevice(*columns[4]->data())});
+    cp::FilterOptions opts(cp::FilterOptions::EMIT_NULL);
+    auto want = GET(cp::CallFunction("filter", {Datum(batch), Datum(mask_nulls)}, &opts, &cpu_ctx)).record_batch();
+    auto got = GET(cp::CallFunction("filter", {Datum(dbatch), DeviceDatum(mask_nulls)}, &opts, &gpu_ctx)).record_batch();
+    for (int c = 0; c < 2; ++c) ExpectEqual(MakeArray(ToHost(*got->column_data(c))), want->column(c), "filter RecordBatch column " + std::to_string(c));
+  }
+
+  // ---------------- SortIndices ----------------
+  {
+    auto values = Make<Int64Builder, int64_t>({10, 12, 4, 50, 50, 32, 11});
+    for (auto order : {cp::SortOrder::Ascending, cp::SortOrder::Descending}) {
+      auto want = GET(cp::SortIndices(*values, order, &cpu_ctx));
+      auto dvalues = MakeArray(ToDevice(*values->data()));
+      auto got = GET(cp::SortIndices(*dvalues, order, &gpu_ctx));
+      ExpectEqual(MakeArray(ToHost(*got->data())), want, std::string("sort_indices ties ") + (order == cp::SortOrder::Ascending ? "asc" : "desc"));
+    }
+    const int64_t n = 300007;
+    DoubleBuilder fb;
+    std::uniform_real_distribution<double> u(0, 1);
+    for (int64_t i = 0; i < n; ++i) {
+      const double x = u(rng);
+      if (x < 0.02) ABORT_NOT_OK(fb.AppendNull());
+      else if (x < 0.04) ABORT_NOT_OK(fb.Append(std::nan("")));
+      else if (x < 0.05) ABORT_NOT_OK(fb.Append(-0.0));
+      else if (x < 0.06) ABORT_NOT_OK(fb.Append(0.0));
+      else if (x < 0.07) ABORT_NOT_OK(fb.Append(x < 0.065 ? INFINITY : -INFINITY));
+      else ABORT_NOT_OK(fb.Append(std::floor((u(rng) - 0.5) * 2000.0)));  // heavy duplicates
+    }
+    std::vector<std::shared_ptr<Array>> columns = {
+        GET(fb.Finish()),
+        MakeRandom<Int64Builder, int64_t>(n, rng, 0.01, -(1LL << 62), 1LL << 62, false),
+        MakeRandom<Int32Builder, int32_t>(n, rng, 0.01, -1000, 1000, false),
+        MakeRandom<UInt8Builder, uint8_t>(n, rng, 0.1, 0, 255, false),
+        MakeRandom<FloatBuilder, float>(n, rng, 0.0, -5.f, 5.f, true),
+        MakeRandom<UInt64Builder, uint64_t>(n, rng, 0.0, 0, ~0ull >> 1, false)};
+    for (auto& col : columns) {
+      for (auto order : {cp::SortOrder::Ascending, cp::SortOrder::Descending}) {
+        cp::ArraySortOptions opts(order);
+        auto want = GET(cp::CallFunction("array_sort_indices", {col}, &opts, &cpu_ctx)).make_array();
+        auto got = HostArray(GET(cp::CallFunction("array_sort_indices", {DeviceDatum(col)}, &opts, &gpu_ctx)));
+        ExpectEqual(got, want, "array_sort_indices random " + col->type()->ToString() + (order == cp::SortOrder::Ascending ? " asc" : " desc"));
+      }
+    }
+    // sliced input, through the meta function with SortOptions
+    auto sl = columns[0]->Slice(1001, 50000);
+    cp::SortOptions sopts({cp::SortKey("", cp::SortOrder::Descending)});
+    auto want = GET(cp::CallFunction("sort_indices", {sl}, &sopts, &cpu_ctx)).make_array();
+    auto got = HostArray(GET(cp::CallFunction("sort_indices", {DeviceDatum(sl)}, &sopts, &gpu_ctx)));
+    ExpectEqual(got, want, "sort_indices sliced float64 desc (meta function)");
+  }
+
+  // ---------------- GroupBy ----------------
+  {
+    // hash_aggregate_test.cc:555-605 (CountAndSum shape): null key group sits at its first-occurrence position
+    auto arg = Make<DoubleBuilder, double>({1.0, 0.0, 0.0, 3.25, 0.125, -0.25, 0.75, 0.0}, {true, false, true, true, true, true, true, false});
+    auto key = Make<Int64Builder, int64_t>({1, 1, 2, 3, 0, 2, 0, 3}, {true, true, true, true, false, true, false, true});
+    cp::CountOptions count_nulls(cp::CountOptions::COUNT_NULL);
+    cp::MinMaxOptions emit_null(cp::MinMaxOptions::EMIT_NULL);
+    std::vector<cp::internal::Aggregate> aggs = {{"hash_count", nullptr}, {"hash_sum", nullptr}, {"hash_min_max", nullptr},
+                                                 {"hash_count", &count_nulls}, {"hash_min_max", &emit_null}};
+    std::vector<Datum> host_args(aggs.size(), Datum(arg)), dev_args;
+    for (size_t i = 0; i < aggs.size(); ++i) dev_args.push_back(DeviceDatum(arg));
+    auto want = GET(cp::internal::GroupBy(host_args, {Datum(key)}, aggs, &cpu_ctx)).make_array();
+    auto got = HostArray(GET(cp::cuda::GroupBy(dev_args, {DeviceDatum(key)}, aggs, &gpu_ctx)));
+    ExpectStructClose(got, want, "GroupBy count/sum/min_max, null key, options (golden shape)");
+
+    auto bad = cp::cuda::GroupBy({DeviceDatum(arg)}, {DeviceDatum(key)}, {{"hash_sum", nullptr}, {"hash_count", nullptr}}, &gpu_ctx);
+    CHECK_TRUE(bad.status().IsInvalid(), "GroupBy aggregates/arguments count mismatch -> Invalid (hash_aggregate.cc:812-815)");
+    auto unknown = cp::cuda::GroupBy({DeviceDatum(arg)}, {DeviceDatum(key)}, {{"hash_nope", nullptr}}, &gpu_ctx);
+    CHECK_TRUE(unknown.status().IsKeyError(), "GroupBy unknown aggregate -> KeyError");
+    // direct execution of a hash aggregate: code + message substring (hash_aggregate_test.cc:474-477)
+    auto gid = Make<UInt32Builder, uint32_t>({0, 0, 1, 2, 3, 1, 3, 2});
+    auto direct = cp::CallFunction("hash_sum", {DeviceDatum(arg), DeviceDatum(gid), Datum(uint32_t(4))}, &gpu_ctx);
+    CHECK_TRUE(direct.status().IsNotImplemented() && direct.status().message().find("Direct execution of HASH_AGGREGATE functions") != std::string::npos,
+               "direct hash_sum execution -> NotImplemented");
+  }
+  {
+    const int64_t n = 400000;
+    auto keys32 = MakeRandom<Int32Builder, int32_t>(n, rng, 0.01, 0, 1000, false);
+    auto keys8 = MakeRandom<UInt8Builder, uint8_t>(n, rng, 0.0, 0, 3, false);
+    auto keysb = MakeRandom<BooleanBuilder, int>(n, rng, 0.1, 0, 2, false);
+    auto keys64 = MakeRandom<Int64Builder, int64_t>(n, rng, 0.0, -50000, 50000, false);
+    auto vals = MakeRandom<DoubleBuilder, double>(n, rng, 0.01, 0.0, 1e14, true);
+    auto ivals = MakeRandom<Int64Builder, int64_t>(n, rng, 0.02, -(1LL << 40), 1LL << 40, false);
+    auto i32vals = MakeRandom<Int32Builder, int32_t>(n, rng, 0.02, -100000, 100000, false);
+    std::vector<cp::internal::Aggregate> aggs = {{"hash_sum", nullptr}, {"hash_count", nullptr}, {"hash_min_max", nullptr}};
+    struct Case { std::string name; std::vector<std::shared_ptr<Array>> keys; std::shared_ptr<Array> arg; };
+    std::vector<Case> cases = {{"int32 key (1K groups, C3 shape) x float64", {keys32}, vals},
+                               {"int64 key (100K groups) x int64", {keys64}, ivals},
+                               {"(uint8, bool) keys (Q1 shape) x float64", {keys8, keysb}, vals},
+                               {"(int32, uint8) keys x int32", {keys32, keys8}, i32vals}};
+    for (auto& c : cases) {
+      std::vector<Datum> hk, dk, ha, da;
+      for (auto& k : c.keys) { hk.push_back(k); dk.push_back(DeviceDatum(k)); }
+      for (size_t i = 0; i < aggs.size(); ++i) { ha.push_back(c.arg); da.push_back(DeviceDatum(c.arg)); }
+      auto want = GET(cp::internal::GroupBy(ha, hk, aggs, &cpu_ctx)).make_array();
+      auto got = HostArray(GET(cp::cuda::GroupBy(da, dk, aggs, &gpu_ctx)));
+      ExpectStructClose(got, want, "GroupBy random " + c.name);
+    }
+    // hash_mean == MeanImpl::Finalize over hash_sum / hash_count of the reference
+    {
+      auto want = GET(cp::internal::GroupBy({vals, vals}, {keys32}, {{"hash_sum", nullptr}, {"hash_count", nullptr}}, &cpu_ctx)).make_array();
+      auto got = HostArray(GET(cp::cuda::GroupBy({DeviceDatum(vals)}, {DeviceDatum(keys32)}, {{"hash_mean", nullptr}}, &gpu_ctx)));
+      const auto& w = internal::checked_cast<const StructArray&>(*want);
+      const auto& g = internal::checked_cast<const StructArray&>(*got);
+      const auto& sums = internal::checked_cast<const DoubleArray&>(*w.field(0));
+      const auto& counts = internal::checked_cast<const Int64Array&>(*w.field(1));
+      const auto& means = internal::checked_cast<const DoubleArray&>(*g.field(0));
+      bool ok = g.length() == w.length() && g.type()->field(0)->name() == "hash_mean" && g.field(1)->Equals(w.field(2));
+      for (int64_t i = 0; ok && i < g.length(); ++i) {
+        if (counts.Value(i) == 0) ok = means.IsNull(i);
+        else ok = means.IsValid(i) && std::fabs(means.Value(i) - sums.Value(i) / double(counts.Value(i))) <= 1e-12 * std::fabs(sums.Value(i) / double(counts.Value(i)));
+      }
+      CHECK_TRUE(ok, "GroupBy hash_mean == sum / count of the reference (1e-12)");
+    }
+
+    // Grouper twin: ids and uniques over two batches
+    {
+      auto k1 = keys64->Slice(0, n / 2), k2 = keys64->Slice(n / 2);
+      auto cpu_grouper = GET(cp::internal::Grouper::Make({ValueDescr::Array(int64())}, &cpu_ctx));
+      auto gpu_grouper = GET(cp::cuda::MakeGrouper({ValueDescr::Array(int64())}, &gpu_ctx));
+      for (auto& k : {k1, k2}) {
+        auto want = GET(cpu_grouper->Consume(GET(cp::ExecBatch::Make({Datum(k)})))).make_array();
+        auto got = HostArray(GET(gpu_grouper->Consume(GET(cp::ExecBatch::Make({DeviceDatum(k)})))));
+        ExpectEqual(got, want, "Grouper::Consume ids, batch of " + std::to_string(k->length()));
+      }
+      CHECK_TRUE(cpu_grouper->num_groups() == gpu_grouper->num_groups(), "Grouper::num_groups");
+      auto want = GET(cpu_grouper->GetUniques());
+      auto got = GET(gpu_grouper->GetUniques());
+      ExpectEqual(HostArray(got[0]), want[0].make_array(), "Grouper::GetUniques");
+
+      // the reference's GroupBy loop (hash_aggregate.cc:928-960) driven by hand over the CUDA registry's
+      // HashAggregateKernels: ids -> consume -> finalize
+      auto ids_want_grouper = GET(cp::internal::Grouper::Make({ValueDescr::Array(int64())}, &cpu_ctx));
+      auto gpu_grouper2 = GET(cp::cuda::MakeGrouper({ValueDescr::Array(int64())}, &gpu_ctx));
+      auto dkeys = DeviceDatum(keys64);
+      auto dvals = DeviceDatum(ivals);
+      auto ids = GET(gpu_grouper2->Consume(GET(cp::ExecBatch::Make({dkeys}))));
+      for (const char* fname : {"hash_sum", "hash_count", "hash_min_max"}) {
+        auto function = GET(registry->GetFunction(fname));
+        auto kernel = static_cast<const cp::HashAggregateKernel*>(GET(function->DispatchExact({ValueDescr::Array(int64()), ValueDescr::Array(uint32()), ValueDescr::Scalar(uint32())})));
+        cp::KernelContext kctx(&gpu_ctx);
+        auto state = GET(kernel->init(&kctx, cp::KernelInitArgs{kernel, {int64(), uint32(), uint32()}, function->default_options()}));
+        kctx.SetState(state.get());
+        ABORT_NOT_OK(kernel->consume(&kctx, GET(cp::ExecBatch::Make({dvals, ids, Datum(gpu_grouper2->num_groups())}))));
+        Datum out;
+        ABORT_NOT_OK(kernel->finalize(&kctx, &out));
+        auto want_all = GET(cp::internal::GroupBy({ivals}, {keys64}, {{fname, nullptr}}, &cpu_ctx)).make_array();
+        ExpectEqual(HostArray(out), internal::checked_cast<const StructArray&>(*want_all).field(0), std::string("HashAggregateKernel consume/finalize over device ids: ") + fname);
+      }
+    }
+  }
+
+  std::cout << (g_failures ? "GLUE FAILED: " : "GLUE OK: ") << g_checks - g_failures << "/" << g_checks << " checks passed" << std::endl;
+  return g_failures ? 1 : 0;
+}

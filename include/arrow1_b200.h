@@ -214,6 +214,10 @@ B200_API int b200_grouper_consume(b200_groupby* gb, const b200_col* keys, uint32
  * (hash_aggregate.cc:783-789): accumulates aggregate `agg_index` of `gb` by dense group id. */
 B200_API int b200_hash_agg_consume(b200_groupby* gb, int agg_index, const b200_col* arg,
                                    const uint32_t* ids, uint32_t num_groups);
+/* == HashAggregateKernel::merge (kernel.h:688-690; NotImplemented upstream, hash_aggregate.cc:795-798)
+ * for two handles driven through b200_hash_agg_consume over the same dense id space: folds every
+ * group state of `src` into `dst` slot by slot (same aggregate schema). */
+B200_API int b200_hash_agg_merge(b200_groupby* dst, b200_groupby* src);
 /* == Grouper::num_groups (hash_aggregate.cc:410); synchronises. */
 B200_API int b200_groupby_num_groups(b200_groupby* gb, uint32_t* out /* host */);
 /* == HashAggregateKernel::merge, which the reference leaves NotImplemented
