@@ -34,10 +34,11 @@ class B200Error(RuntimeError):
 def lib() -> C.CDLL:
     global _lib
     if _lib is None:
-        if not os.path.exists(_LIB_PATH):
+        path = os.environ.get("B200_LIB", _LIB_PATH)   # tuning sweeps load alternative builds
+        if not os.path.exists(path):
             raise RuntimeError("libarrow1_b200.so is not built: run `python -m arrow1_b200.build` "
                                "(there is no CPU fallback)")
-        L = C.CDLL(_LIB_PATH)
+        L = C.CDLL(path)
         L.b200_last_error.restype = C.c_char_p
         L.b200_version.restype = C.c_char_p
         L.b200_ctx_launch_count.restype = C.c_int64
@@ -274,6 +275,31 @@ class GroupBy:
     def consume(self, keys: Sequence[Column], args: Sequence[Column], row_base: int = 0):
         self.ctx.check(lib().b200_groupby_consume(self._h, col_array(keys), col_array(args), C.c_uint64(row_base)))
 
+    def consume_rows(self, keys: Sequence[Column], args: Sequence[Column], row_ids: torch.Tensor):
+        """b200_groupby_consume_rows: explicit global row numbers (int64-typed tensor of uint64)."""
+        self.ctx.check(lib().b200_groupby_consume_rows(self._h, col_array(keys), col_array(args),
+                                                       C.c_void_p(row_ids.data_ptr())))
+
+    def first_rows(self) -> torch.Tensor:
+        """Global first-occurrence row of every group, in group order (int64-typed uint64)."""
+        g = self.num_groups()
+        out = torch.empty(max(g, 1), dtype=torch.int64, device="cuda:%d" % self.ctx.device)
+        self.ctx.check(lib().b200_groupby_first_rows(self._h, C.c_void_p(out.data_ptr())))
+        return out[:g]
+
+    def partition_plan(self, keys: Sequence[Column], n_parts: int):
+        """b200_groupby_partition_plan -> (pos uint32-as-int32 tensor [n], counts list[n_parts])."""
+        n = keys[0].length
+        dev = "cuda:%d" % self.ctx.device
+        nbytes = C.c_size_t(0)
+        self.ctx.check(lib().b200_partition_scratch_bytes(C.c_int64(n), C.byref(nbytes)))
+        scratch = self.ctx.empty(nbytes.value)
+        pos = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+        counts = (C.c_int64 * 16)()
+        self.ctx.check(lib().b200_groupby_partition_plan(self._h, col_array(keys), C.c_int(n_parts), C.c_void_p(pos.data_ptr()),
+                                                         counts, C.c_void_p(scratch.data_ptr()), C.c_size_t(nbytes.value)))
+        return pos[:n], [int(counts[p]) for p in range(n_parts)]
+
     def grouper_consume(self, keys: Sequence[Column]) -> torch.Tensor:
         n = keys[0].length
         ids = torch.empty(max(n, 1), dtype=torch.int32, device="cuda:%d" % self.ctx.device)
@@ -346,6 +372,35 @@ class GroupBy:
             aggs.append(cols)
         keys = [Column(t, d, v, G, 0, int(out_keys[k].null_count)) for k, (t, d, v) in enumerate(kbufs)]
         return GroupByOutput(G, aggs, keys)
+
+
+def partition_scatter(ctx: Context, col: Column, pos: torch.Tensor, want_valid: bool):
+    """b200_partition_scatter -> (data bytes tensor, validity bytes tensor or None), partitioned layout."""
+    n = col.length
+    width = BITS[col.type] // 8
+    out = ctx.empty(max(n, 1) * width)
+    valid = ctx.empty(max(n, 1)) if want_valid else None
+    d = col.desc()
+    ctx.check(lib().b200_partition_scatter(ctx._h, C.byref(d), C.c_void_p(pos.data_ptr()), C.c_void_p(out.data_ptr()),
+                                           C.c_void_p(valid.data_ptr()) if want_valid else None))
+    return out[: n * width], (valid[:n] if want_valid else None)
+
+
+def partition_rows(ctx: Context, n: int, row_base: int, pos: torch.Tensor) -> torch.Tensor:
+    out = torch.empty(max(n, 1), dtype=torch.int64, device="cuda:%d" % ctx.device)
+    ctx.check(lib().b200_partition_rows(ctx._h, C.c_int64(n), C.c_uint64(row_base), C.c_void_p(pos.data_ptr()),
+                                        C.c_void_p(out.data_ptr())))
+    return out[:n]
+
+
+def pack_validity(ctx: Context, valid_bytes: torch.Tensor):
+    """b200_pack_validity -> (bitmap bytes tensor, null_count)."""
+    n = valid_bytes.numel()
+    bitmap = ctx.empty((n + 31) // 32 * 4 + 8)
+    nulls = C.c_int64(0)
+    ctx.check(lib().b200_pack_validity(ctx._h, C.c_void_p(valid_bytes.data_ptr()), C.c_int64(n), C.c_void_p(bitmap.data_ptr()),
+                                       C.byref(nulls)))
+    return bitmap, int(nulls.value)
 
 
 def group_by(ctx: Context, keys: Sequence[Column], aggs: Sequence[AggSpec], args: Sequence[Column],

@@ -72,6 +72,7 @@ struct GbArgs {
   int32_t mode;
   int64_t n;
   uint64_t row_base;
+  const uint64_t* row_ids;   // nullable: explicit global row number of every row (repartitioned input)
   GbTable t;
   uint32_t* counters;        // [0] groups, [1] deferred rows, [2] claimed slots (grouper), [3] error
   const uint32_t* defer_in;  // nullable: only rows whose bit is set are processed
@@ -335,7 +336,7 @@ __global__ void __launch_bounds__(kLocal ? 1024 : 256) gb_consume_kernel(const _
     if (a.defer_in && !((a.defer_in[row >> 5] >> (row & 31)) & 1u)) continue;
     int special;
     const uint64_t key = load_key(a, row, &special);
-    const uint64_t grow = a.row_base + uint64_t(row);
+    const uint64_t grow = a.row_ids ? a.row_ids[row] : a.row_base + uint64_t(row);
     char* slot = nullptr;
     bool local_hit = false;
     if (kLocal && !special) {
@@ -1216,6 +1217,123 @@ __global__ void gb_dense_consume_kernel(GbSchema s, int agg_index, GbCol col, co
   accumulate(dense + uint64_t(g) * s.stride, s.aggs[agg_index], v, uint64_t(row));
 }
 
+// ---- hash repartitioning (multi-GPU, high cardinality: SURVEY §8e) ---------------------------------
+// dest(row) = (mix64(packed key) >> 40) % n_parts — bits disjoint from the table's slot index, so the
+// keys one rank receives still spread over its table.  Rows of one destination end up contiguous.
+constexpr int kPartMax = 16;
+constexpr int kPartThreads = 256;
+constexpr int kPartItems = 16;
+constexpr int kPartTile = kPartThreads * kPartItems;
+
+__device__ __forceinline__ uint32_t part_of(const GbArgs& a, int64_t row, uint32_t n_parts) {
+  int special;
+  const uint64_t key = load_key(a, row, &special);
+  if (special) return 0;   // the null key / the EMPTY-valued key: one fixed owner
+  return uint32_t((mix64(key) >> 40) % n_parts);
+}
+
+// pass 1: per-tile destination counts
+__global__ void __launch_bounds__(kPartThreads) gb_part_count_kernel(const __grid_constant__ GbArgs a, uint32_t n_parts,
+                                                                     uint32_t* tile_counts) {
+  __shared__ uint32_t cnt[kPartMax];
+  if (threadIdx.x < kPartMax) cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const int64_t base = int64_t(blockIdx.x) * kPartTile;
+#pragma unroll 4
+  for (int i = 0; i < kPartItems; ++i) {
+    const int64_t row = base + i * kPartThreads + threadIdx.x;
+    if (row < a.n) atomicAdd(&cnt[part_of(a, row, n_parts)], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x < n_parts) tile_counts[size_t(blockIdx.x) * kPartMax + threadIdx.x] = cnt[threadIdx.x];
+}
+
+// pass 2 (one CTA): per destination, exclusive scan over tiles; totals and destination bases
+__global__ void __launch_bounds__(1024) gb_part_scan_kernel(uint32_t* tile_counts, int64_t n_tiles, uint32_t n_parts,
+                                                            int64_t* totals /* [n_parts] counts, [kPartMax + p] bases */) {
+  __shared__ uint32_t warp_sums[32];
+  __shared__ uint32_t carry_s;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  for (uint32_t p = 0; p < n_parts; ++p) {
+    if (t == 0) carry_s = 0;
+    __syncthreads();
+    for (int64_t base = 0; base < n_tiles; base += 1024) {
+      const int64_t tile = base + t;
+      const uint32_t c = tile < n_tiles ? tile_counts[size_t(tile) * kPartMax + p] : 0;
+      uint32_t incl = c;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+      }
+      if (lane == 31) warp_sums[warp] = incl;
+      __syncthreads();
+      uint32_t wpre = 0;
+      for (int w = 0; w < warp; ++w) wpre += warp_sums[w];
+      const uint32_t carry = carry_s;
+      if (tile < n_tiles) tile_counts[size_t(tile) * kPartMax + p] = carry + wpre + incl - c;
+      __syncthreads();
+      if (t == 1023) carry_s = carry + wpre + incl;
+      __syncthreads();
+    }
+    if (t == 0) totals[p] = carry_s;
+    __syncthreads();
+  }
+  if (t == 0) {
+    int64_t acc = 0;
+    for (uint32_t p = 0; p < n_parts; ++p) {
+      totals[kPartMax + p] = acc;
+      acc += totals[p];
+    }
+  }
+}
+
+// pass 3: position of every row in the partitioned layout
+__global__ void __launch_bounds__(kPartThreads) gb_part_pos_kernel(const __grid_constant__ GbArgs a, uint32_t n_parts,
+                                                                   const uint32_t* tile_offsets, const int64_t* totals,
+                                                                   uint32_t* pos) {
+  __shared__ uint32_t cur[kPartMax];
+  if (threadIdx.x < kPartMax)
+    cur[threadIdx.x] = threadIdx.x < n_parts ? uint32_t(totals[kPartMax + threadIdx.x]) + tile_offsets[size_t(blockIdx.x) * kPartMax + threadIdx.x] : 0;
+  __syncthreads();
+  const int64_t base = int64_t(blockIdx.x) * kPartTile;
+#pragma unroll 4
+  for (int i = 0; i < kPartItems; ++i) {
+    const int64_t row = base + i * kPartThreads + threadIdx.x;
+    if (row < a.n) pos[row] = atomicAdd(&cur[part_of(a, row, n_parts)], 1u);
+  }
+}
+
+template <typename T>
+__global__ void gb_part_scatter_kernel(const T* __restrict__ in, BitmapRef vv, const uint32_t* __restrict__ pos, int64_t n,
+                                       T* __restrict__ out, uint8_t* __restrict__ out_valid) {
+  const int64_t row = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (row >= n) return;
+  const uint32_t p = pos[row];
+  out[p] = in[row];
+  if (out_valid) out_valid[p] = bitmap_get(vv, row) ? 1 : 0;
+}
+
+__global__ void gb_part_rows_kernel(int64_t n, uint64_t row_base, const uint32_t* __restrict__ pos, uint64_t* __restrict__ out) {
+  const int64_t row = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (row < n) out[pos[row]] = row_base + uint64_t(row);
+}
+
+// validity bytes (0/1 per row) -> LSB-first bitmap, whole 32-bit words; counts nulls
+__global__ void gb_pack_validity_kernel(const uint8_t* __restrict__ bytes, int64_t n, uint32_t* __restrict__ bitmap,
+                                        unsigned long long* null_count) {
+  const int64_t row = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  const bool in = row < n;
+  const bool v = in && bytes[row] != 0;
+  const unsigned word = __ballot_sync(0xffffffffu, v);
+  const unsigned inw = __ballot_sync(0xffffffffu, in);
+  if ((threadIdx.x & 31) == 0 && inw) {
+    bitmap[row >> 5] = word;
+    const int nulls = __popc(inw & ~word);
+    if (nulls) atomicAdd(null_count, (unsigned long long)nulls);
+  }
+}
+
 // dense states over one id space folded slot by slot: HashAggregateKernel::merge
 __global__ void gb_dense_merge_kernel(GbSchema s, const char* src, char* dst, uint32_t n) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1404,10 +1522,10 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
   const uint64_t likely_groups = std::max<uint64_t>(gb->groups, gb->expected);
   // (the grouper's insert/lookup passes stay on the global table: a growth here would move slots
   // whose positional ids are live)
-  const bool low_card = a.mode == kModeFused && likely_groups * 2 <= uint64_t(local_slots) && local_slots >= 64;
+  const bool low_card = a.mode == kModeFused && likely_groups * 2 <= uint64_t(local_slots) && local_slots >= 64 && !a.row_ids;
   // one value column (or none) and a cardinality hint (or history) that fits the shared table: the fast kernel.
   // With no hint at all the fast kernel is tried too: a CTA whose table fills up bypasses it.
-  const bool fast = a.mode == kModeFused && a.n_cols == 1 && likely_groups <= uint64_t(kFastMaxGroupsHint) && !gb->fast_disabled;
+  const bool fast = a.mode == kModeFused && a.n_cols == 1 && likely_groups <= uint64_t(kFastMaxGroupsHint) && !gb->fast_disabled && !a.row_ids;
   for (int round = 0; round < 8; ++round) {
     a.t = gb->table;
     if (fast && round == 0) {
@@ -1607,7 +1725,20 @@ int b200_groupby_destroy(b200_groupby* gb) {
   return B200_OK;
 }
 
+static int groupby_consume_impl(b200_groupby* gb, const b200_col* keys, const b200_col* args, uint64_t row_base,
+                                const uint64_t* row_ids);
+
 int b200_groupby_consume(b200_groupby* gb, const b200_col* keys, const b200_col* args, uint64_t row_base) {
+  return groupby_consume_impl(gb, keys, args, row_base, nullptr);
+}
+
+int b200_groupby_consume_rows(b200_groupby* gb, const b200_col* keys, const b200_col* args, const uint64_t* row_ids) {
+  if (gb && !row_ids && keys && keys[0].length > 0) return b200_fail(gb->ctx, B200_INVALID, "groupby_consume_rows: null row_ids");
+  return groupby_consume_impl(gb, keys, args, 0, row_ids);
+}
+
+static int groupby_consume_impl(b200_groupby* gb, const b200_col* keys, const b200_col* args, uint64_t row_base,
+                                const uint64_t* row_ids) {
   if (!gb) return B200_INVALID;
   b200_ctx* ctx = gb->ctx;
   if (!keys || (gb->schema.n_aggs > 0 && !args)) return b200_fail(ctx, B200_INVALID, "groupby_consume: null argument");
@@ -1637,7 +1768,96 @@ int b200_groupby_consume(b200_groupby* gb, const b200_col* keys, const b200_col*
   }
   a.mode = kModeFused;
   a.row_base = row_base;
+  a.row_ids = row_ids;
   return run_consume(gb, a);
+}
+
+// ---- hash repartitioning -------------------------------------------------------------------------
+int b200_partition_scratch_bytes(int64_t length, size_t* out_bytes) {
+  if (!out_bytes || length < 0) return B200_INVALID;
+  const size_t n_tiles = size_t((length + kPartTile - 1) / kPartTile);
+  *out_bytes = b200_align_up(n_tiles * kPartMax * sizeof(uint32_t), 256) + 2 * kPartMax * sizeof(int64_t) + 512;
+  return B200_OK;
+}
+
+int b200_groupby_partition_plan(b200_groupby* gb, const b200_col* keys, int n_parts, uint32_t* out_pos, int64_t* out_counts,
+                                void* scratch, size_t scratch_bytes) {
+  if (!gb) return B200_INVALID;
+  b200_ctx* ctx = gb->ctx;
+  if (!keys || !out_counts) return b200_fail(ctx, B200_INVALID, "partition_plan: null argument");
+  if (n_parts < 1 || n_parts > kPartMax) return b200_fail(ctx, B200_INVALID, "partition_plan: 1..%d partitions", kPartMax);
+  GbArgs a;
+  memset(&a, 0, sizeof(a));
+  a.s = gb->schema;
+  B200_RETURN_NOT_OK(fill_keys(gb, keys, &a));
+  for (int p = 0; p < n_parts; ++p) out_counts[p] = 0;
+  if (a.n == 0) return B200_OK;
+  if (a.n >= (int64_t(1) << 32)) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "partition_plan: more than 2^32-1 rows per call");
+  size_t need = 0;
+  b200_partition_scratch_bytes(a.n, &need);
+  if (!out_pos || !scratch || scratch_bytes < need) return b200_fail(ctx, B200_INVALID, "partition_plan: scratch too small (%zu < %zu)", scratch_bytes, need);
+  const int64_t n_tiles = (a.n + kPartTile - 1) / kPartTile;
+  char* base = reinterpret_cast<char*>(b200_align_up(reinterpret_cast<uintptr_t>(scratch), 256));
+  uint32_t* tile_counts = reinterpret_cast<uint32_t*>(base);
+  int64_t* totals = reinterpret_cast<int64_t*>(base + b200_align_up(size_t(n_tiles) * kPartMax * sizeof(uint32_t), 256));
+  B200_TIMED(ctx, "partition_plan", (gb_part_count_kernel<<<(unsigned)n_tiles, kPartThreads, 0, ctx->stream>>>(a, uint32_t(n_parts), tile_counts)));
+  gb_part_scan_kernel<<<1, 1024, 0, ctx->stream>>>(tile_counts, n_tiles, uint32_t(n_parts), totals);
+  B200_LAUNCHED(ctx);
+  B200_TIMED(ctx, "partition_plan", (gb_part_pos_kernel<<<(unsigned)n_tiles, kPartThreads, 0, ctx->stream>>>(a, uint32_t(n_parts), tile_counts, totals, out_pos)));
+  B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 32, totals, kPartMax * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  for (int p = 0; p < n_parts; ++p) out_counts[p] = ctx->host_words[32 + p];
+  return B200_OK;
+}
+
+int b200_partition_scatter(b200_ctx* ctx, const b200_col* col, const uint32_t* pos, void* out_data, uint8_t* out_valid) {
+  if (!ctx) return B200_INVALID;
+  if (!col) return b200_fail(ctx, B200_INVALID, "partition_scatter: null column");
+  const int64_t n = col->length;
+  if (n == 0) return B200_OK;
+  if (!pos || !out_data || !col->data) return b200_fail(ctx, B200_INVALID, "partition_scatter: null argument");
+  const int bits = b200_type_bits(col->type);
+  if (bits < 8) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "partition_scatter: type %d", col->type);
+  const bool has_nulls = col->validity != nullptr && col->null_count != 0;
+  const BitmapRef vv = has_nulls ? make_bitmap_ref(col->validity, col->offset) : BitmapRef{nullptr, 0};
+  const char* data = reinterpret_cast<const char*>(col->data) + col->offset * (bits / 8);
+  const unsigned grid = unsigned((n + 255) / 256);
+  switch (bits) {
+    case 8: B200_TIMED(ctx, "partition_scatter", (gb_part_scatter_kernel<uint8_t><<<grid, 256, 0, ctx->stream>>>(reinterpret_cast<const uint8_t*>(data), vv, pos, n, reinterpret_cast<uint8_t*>(out_data), out_valid))); break;
+    case 16: B200_TIMED(ctx, "partition_scatter", (gb_part_scatter_kernel<uint16_t><<<grid, 256, 0, ctx->stream>>>(reinterpret_cast<const uint16_t*>(data), vv, pos, n, reinterpret_cast<uint16_t*>(out_data), out_valid))); break;
+    case 32: B200_TIMED(ctx, "partition_scatter", (gb_part_scatter_kernel<uint32_t><<<grid, 256, 0, ctx->stream>>>(reinterpret_cast<const uint32_t*>(data), vv, pos, n, reinterpret_cast<uint32_t*>(out_data), out_valid))); break;
+    default: B200_TIMED(ctx, "partition_scatter", (gb_part_scatter_kernel<uint64_t><<<grid, 256, 0, ctx->stream>>>(reinterpret_cast<const uint64_t*>(data), vv, pos, n, reinterpret_cast<uint64_t*>(out_data), out_valid))); break;
+  }
+  return B200_OK;
+}
+
+int b200_partition_rows(b200_ctx* ctx, int64_t length, uint64_t row_base, const uint32_t* pos, uint64_t* out_rows) {
+  if (!ctx) return B200_INVALID;
+  if (length < 0) return b200_fail(ctx, B200_INVALID, "partition_rows: negative length");
+  if (length == 0) return B200_OK;
+  if (!pos || !out_rows) return b200_fail(ctx, B200_INVALID, "partition_rows: null argument");
+  gb_part_rows_kernel<<<unsigned((length + 255) / 256), 256, 0, ctx->stream>>>(length, row_base, pos, out_rows);
+  B200_LAUNCHED(ctx);
+  return B200_OK;
+}
+
+int b200_pack_validity(b200_ctx* ctx, const uint8_t* valid_bytes, int64_t length, void* out_bitmap, int64_t* out_null_count) {
+  if (!ctx) return B200_INVALID;
+  if (length < 0) return b200_fail(ctx, B200_INVALID, "pack_validity: negative length");
+  if (out_null_count) *out_null_count = 0;
+  if (length == 0) return B200_OK;
+  if (!valid_bytes || !out_bitmap) return b200_fail(ctx, B200_INVALID, "pack_validity: null argument");
+  B200_RETURN_NOT_OK(b200_ctx_reserve_scratch(ctx, 256));
+  unsigned long long* counter = reinterpret_cast<unsigned long long*>(ctx->scratch);
+  B200_CUDA(ctx, cudaMemsetAsync(counter, 0, sizeof(unsigned long long), ctx->stream));
+  gb_pack_validity_kernel<<<unsigned((length + 255) / 256), 256, 0, ctx->stream>>>(valid_bytes, length, reinterpret_cast<uint32_t*>(out_bitmap), counter);
+  B200_LAUNCHED(ctx);
+  if (out_null_count) {
+    B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 48, counter, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *out_null_count = ctx->host_words[48];
+  }
+  return B200_OK;
 }
 
 int b200_groupby_num_groups(b200_groupby* gb, uint32_t* out) {
@@ -1818,6 +2038,24 @@ static int collect_slots(b200_groupby* gb, uint64_t** first_rows, uint64_t** slo
   B200_LAUNCHED(ctx);
   *n_out = G;
   return B200_OK;
+}
+
+int b200_groupby_first_rows(b200_groupby* gb, uint64_t* out_first_rows) {
+  if (!gb) return B200_INVALID;
+  b200_ctx* ctx = gb->ctx;
+  if (gb->dense_used) return b200_fail(ctx, B200_INVALID, "groupby_first_rows: dense handle has no row order");
+  uint64_t *first_rows, *slot_idx;
+  size_t sort_bytes = 0;
+  uint32_t c[4];
+  B200_RETURN_NOT_OK(read_counters(gb, c));
+  b200_sort_pairs_scratch_bytes(std::max<uint32_t>(c[0], 1), &sort_bytes);
+  const size_t arr = b200_align_up(size_t(std::max<uint32_t>(c[0], 1)) * 8, 256);
+  char* extra = nullptr;
+  uint32_t G = 0;
+  B200_RETURN_NOT_OK(collect_slots(gb, &first_rows, &slot_idx, &G, arr + sort_bytes + 256, &extra));
+  if (G == 0) return B200_OK;
+  if (!out_first_rows) return b200_fail(ctx, B200_INVALID, "groupby_first_rows: null output");
+  return b200_sort_pairs(ctx, first_rows, slot_idx, G, out_first_rows, reinterpret_cast<uint64_t*>(extra), extra + arr, sort_bytes);
 }
 
 int b200_groupby_export(b200_groupby* gb, void* out_state, uint32_t* out_groups) {

@@ -16,8 +16,9 @@
 //                                skipped (generalises the reference's narrow-range counting sort,
 //                                vector_sort.cc:484-525; also makes int32 a 4-pass sort)
 //             sort_pass_kernel   onesweep pass: 4096-key tile per CTA; lanes with equal digits are
-//                                matched through an atomicOr bitmask in shared memory (MATCH.ANY
-//                                measured ~60 cycles/warp-instruction on B200); per-digit decoupled
+//                                matched with one warp ballot per digit bit (MATCH.ANY measured ~60
+//                                cycles/warp-instruction on B200; an atomicOr bitmask in shared memory
+//                                cost three dependent shared round trips per item); per-digit decoupled
 //                                look-back across tiles; keys + 32-bit row numbers staged through
 //                                shared memory so global stores are digit-contiguous.  The first
 //                                live pass reads the raw column (row number = position, no iota
@@ -33,10 +34,20 @@
 namespace {
 
 constexpr int kDigits = 8;
-constexpr int kThreads = 256;
-constexpr int kItems = 16;
-constexpr int kTile = kThreads * kItems;  // 4096
+constexpr int kHistThreads = 256;          // histogram / scan kernels (the scan wants one warp per digit)
+constexpr int kHistItems = 16;
+constexpr int kHistTile = kHistThreads * kHistItems;
+#ifndef B200_SORT_THREADS
+#define B200_SORT_THREADS 256
+#define B200_SORT_ITEMS 16
+#define B200_SORT_MINBLOCKS 3
+#endif
+constexpr int kThreads = B200_SORT_THREADS;   // pass kernel: threads x keys per thread (tuned on B200, see
+constexpr int kItems = B200_SORT_ITEMS;       // profiles/r01_sort_tile_sweep.txt)
+constexpr int kTile = kThreads * kItems;
 constexpr int kWarps = kThreads / 32;
+constexpr int kMinBlocks = B200_SORT_MINBLOCKS;
+static_assert(kThreads >= 256 && kItems <= 32, "one thread per digit bin; validity words come from lanes < kItems");
 constexpr int kBinStride = 264;           // >= 258, keeps rows 32-byte aligned
 constexpr int kLook = 8;                  // predecessor states requested per look-back round trip
 constexpr uint32_t kStatusPartial = 1u << 30;
@@ -125,15 +136,15 @@ __device__ __forceinline__ uint64_t source_key(const SortParams& p, int64_t row,
 // All digit histograms in one read of the column: shared-memory atomics, flushed once per CTA.
 // (Measured on B200 at 100 M 64-bit keys: 0.4 ms this way vs 5.3 ms with MATCH.ANY-aggregated
 // warp-private counters.)
-__global__ void __launch_bounds__(kThreads) sort_hist_kernel(SortParams p) {
+__global__ void __launch_bounds__(kHistThreads) sort_hist_kernel(SortParams p) {
   __shared__ uint32_t h[kDigits][kBinStride];
   const int t = threadIdx.x;
-  for (int i = t; i < kDigits * kBinStride; i += kThreads) (&h[0][0])[i] = 0;
+  for (int i = t; i < kDigits * kBinStride; i += kHistThreads) (&h[0][0])[i] = 0;
   __syncthreads();
-  for (int64_t base = int64_t(blockIdx.x) * kTile; base < p.n; base += int64_t(gridDim.x) * kTile) {
+  for (int64_t base = int64_t(blockIdx.x) * kHistTile; base < p.n; base += int64_t(gridDim.x) * kHistTile) {
 #pragma unroll 4
-    for (int k = 0; k < kItems; ++k) {
-      const int64_t row = base + k * kThreads + t;
+    for (int k = 0; k < kHistItems; ++k) {
+      const int64_t row = base + k * kHistThreads + t;
       if (row < p.n) {
         uint32_t cls;
         const uint64_t key = source_key(p, row, &cls);
@@ -149,14 +160,14 @@ __global__ void __launch_bounds__(kThreads) sort_hist_kernel(SortParams p) {
     }
   }
   __syncthreads();
-  for (int i = t; i < kDigits * kBinStride; i += kThreads) {
+  for (int i = t; i < kDigits * kBinStride; i += kHistThreads) {
     const uint32_t c = (&h[0][0])[i];
     if (c) atomicAdd(p.hist + i, c);
   }
 }
 
 // one warp per digit: exclusive scan of its 258 bins; then thread 0 plans the passes
-__global__ void __launch_bounds__(kThreads) sort_scan_kernel(SortParams p) {
+__global__ void __launch_bounds__(kHistThreads) sort_scan_kernel(SortParams p) {
   __shared__ int skip_s[kDigits];
   const int lane = threadIdx.x & 31, d = threadIdx.x >> 5;
   uint32_t* h = p.hist + d * kBinStride;
@@ -215,7 +226,6 @@ struct PassSmem {
   uint64_t keys[kTile];
   uint32_t pay[kTile];
   uint32_t whist[kWarps][kBinStride];
-  uint32_t match[kWarps][kBinStride];
   uint32_t tile_count[kBinStride];
   uint32_t tile_prefix[kBinStride];
   uint32_t bin_delta[kBinStride];
@@ -239,7 +249,7 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
 
   // ---- load: all global loads are issued back to back, transforms follow
   uint64_t key[kItems];
-  uint32_t cls_bits = 0;  // 2 bits per item: 1 NaN, 2 null (only in the class pass)
+  uint64_t cls_bits = 0;  // 2 bits per item: 1 NaN, 2 null (only in the class pass)
   if (info.first && !p.keys_in) {
     uint32_t vword = 0xffffffffu;  // validity word of step `lane` (lanes 0..15)
     if (p.vv.words && lane < kItems) vword = bitmap_load32(p.vv, tile_row0 + warp * (kItems * 32) + lane * 32, p.n);
@@ -276,7 +286,7 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
         k = p.wmask;
       }
       key[i] = k;
-      if (kClass) cls_bits |= cls << (2 * i);
+      if (kClass) cls_bits |= uint64_t(cls) << (2 * i);
     }
   } else {
     const uint64_t* src = info.first ? p.keys_in : keys_src;
@@ -290,40 +300,57 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
           uint32_t cls = 0;
           if (p.vv.words && !bitmap_get(p.vv, pays_src[tile_row0 + wbase + 32 * i])) cls = 2;
           else if (p.tkind == kFloatKey && key[i] == p.wmask) cls = 1;
-          cls_bits |= cls << (2 * i);
+          cls_bits |= uint64_t(cls) << (2 * i);
         }
       }
     }
   }
 
-  // ---- rank inside the warp (stable: items visited in index order, lanes in lane order)
+  // ---- rank inside the warp (stable: items visited in index order, lanes in lane order).
+  // Lanes holding the same digit are matched with one ballot per digit bit (no shared-memory round
+  // trip); the lowest matched lane bumps the warp's digit counter with one native ATOMS.ADD and its
+  // return value is the group's base rank.  Items go in groups of kRankGroup: all atomics of a group
+  // are issued before the first return value is consumed, so their latencies overlap instead of
+  // forming a 16-deep dependency chain (the short-scoreboard stall that dominated v2's profile).
+  constexpr int NB = kClass ? 9 : 8;
+  constexpr int kRankGroup = kItems < 8 ? kItems : 8;
   uint32_t rank2[kItems / 2];  // two 16-bit ranks per register
   uint32_t* myhist = s.whist[warp];
-  uint32_t* mymatch = s.match[warp];
 #pragma unroll
-  for (int i = 0; i < kItems; ++i) {
-    const bool in = kFull || wbase + 32 * i < tile_items;
-    uint32_t bin = uint32_t(key[i] >> shift) & 255u;
-    if (kClass) {
-      const uint32_t cls = (cls_bits >> (2 * i)) & 3u;
-      if (cls) bin = 255u + cls;
+  for (int g0 = 0; g0 < kItems; g0 += kRankGroup) {
+    unsigned peers[kRankGroup];
+    uint32_t base[kRankGroup];
+#pragma unroll
+    for (int q = 0; q < kRankGroup; ++q) {
+      const int i = g0 + q;
+      const bool in = kFull || wbase + 32 * i < tile_items;
+      uint32_t bin = uint32_t(key[i] >> shift) & 255u;
+      if (kClass) {
+        const uint32_t cls = uint32_t(cls_bits >> (2 * i)) & 3u;
+        if (cls) bin = 255u + cls;
+      }
+      unsigned m = kFull ? 0xffffffffu : __ballot_sync(0xffffffffu, in);
+#pragma unroll
+      for (int b = 0; b < NB; ++b) {
+        const bool bit = (bin >> b) & 1u;
+        const unsigned bal = __ballot_sync(0xffffffffu, bit);
+        m &= bit ? bal : ~bal;
+      }
+      peers[q] = m;
+      base[q] = 0;
+      // same-warp shared atomics issue in program order: item i's bump precedes item i+1's
+      if (in && (m & lt) == 0) base[q] = atomicAdd(myhist + bin, uint32_t(__popc(m)));
+      __syncwarp();
     }
-    if (in) atomicOr(mymatch + bin, 1u << lane);
-    __syncwarp();
-    const unsigned m = in ? mymatch[bin] : 0u;
-    __syncwarp();
-    const int leader = __ffs(m) - 1;
-    uint32_t old = 0;
-    if (in && lane == leader) {
-      mymatch[bin] = 0;
-      old = myhist[bin];
-      myhist[bin] = old + __popc(m);
+#pragma unroll
+    for (int q = 0; q < kRankGroup; ++q) {
+      const int i = g0 + q;
+      const unsigned m = peers[q];
+      const uint32_t b0 = __shfl_sync(0xffffffffu, base[q], (__ffs(m) - 1) & 31);
+      const uint32_t r = b0 + __popc(m & lt);
+      if (i & 1) rank2[i >> 1] |= r << 16;
+      else rank2[i >> 1] = r;
     }
-    old = __shfl_sync(0xffffffffu, old, in ? leader : 0);
-    const uint32_t r = old + __popc(m & lt);
-    if (i & 1) rank2[i >> 1] |= r << 16;
-    else rank2[i >> 1] = r;
-    __syncwarp();
   }
   // ---- row numbers: issued now, consumed after the look-back
   uint32_t pay[kItems];
@@ -348,25 +375,41 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
     st_volatile_u32(state + b, (tile == 0 ? kStatusInclusive : kStatusPartial) | acc);
   }
   __syncthreads();
-  // ---- exclusive prefix over bins (tile-local layout)
+  // ---- exclusive prefix over bins (tile-local layout): threads 0..255 own one bin each
   {
-    const uint32_t c = s.tile_count[t];  // bins 0..255
-    uint32_t incl = c;
+    uint32_t c = 0, incl = 0;
+    if (t < 256) {
+      c = s.tile_count[t];
+      incl = c;
 #pragma unroll
-    for (int sft = 1; sft < 32; sft <<= 1) {
-      uint32_t o = __shfl_up_sync(0xffffffffu, incl, sft);
-      if (lane >= sft) incl += o;
+      for (int sft = 1; sft < 32; sft <<= 1) {
+        uint32_t o = __shfl_up_sync(0xffffffffu, incl, sft);
+        if (lane >= sft) incl += o;
+      }
+      if (lane == 31) s.warp_sums[warp] = incl;
     }
-    if (lane == 31) s.warp_sums[warp] = incl;
     __syncthreads();
-    uint32_t wpre = 0;
+    if (t < 256) {
+      uint32_t wpre = 0;
 #pragma unroll
-    for (int w = 0; w < kWarps; ++w)
-      if (w < warp) wpre += s.warp_sums[w];
-    s.tile_prefix[t] = wpre + incl - c;
-    if (kClass && t == kThreads - 1) {
-      s.tile_prefix[256] = wpre + incl;
-      s.tile_prefix[257] = wpre + incl + s.tile_count[256];
+      for (int w = 0; w < 8; ++w)
+        if (w < warp) wpre += s.warp_sums[w];
+      const uint32_t pre = wpre + incl - c;
+      s.tile_prefix[t] = pre;
+      // fold the bin's tile offset into every warp's offset (conflict-free: one bin per thread), so the
+      // scatter below needs one random shared load per key instead of two — the pass is bound by
+      // shared-memory wavefronts (57 % of them bank conflicts from digit-random addresses)
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) s.whist[w][t] += pre;
+      if (kClass && t == 255) {
+        const uint32_t p256 = wpre + incl, p257 = wpre + incl + s.tile_count[256];
+        s.tile_prefix[256] = p256;
+        s.tile_prefix[257] = p257;
+        for (int w = 0; w < kWarps; ++w) {
+          s.whist[w][256] += p256;
+          s.whist[w][257] += p257;
+        }
+      }
     }
   }
   __syncthreads();
@@ -375,7 +418,7 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
   // of the kernel's stall samples) and before the shared-memory scatter, which hides the first trip.
   const uint32_t* base_hist = p.hist + d * kBinStride;
   uint32_t look[kLook];
-  if (tile > 0) {
+  if (tile > 0 && t < 256) {
 #pragma unroll
     for (int j = 0; j < kLook; ++j)
       look[j] = tile - 1 - j >= 0 ? ld_volatile_u32(state + t - (j + 1) * kBinStride) : kStatusInclusive;
@@ -389,18 +432,18 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
       uint32_t bin = uint32_t(key[i] >> shift) & 255u;
       uint32_t pv = pay[i];
       if (kClass) {
-        const uint32_t cls = (cls_bits >> (2 * i)) & 3u;
+        const uint32_t cls = uint32_t(cls_bits >> (2 * i)) & 3u;
         if (cls) bin = 255u + cls;
         pv |= cls << 30;
       }
       const uint32_t r = (i & 1) ? (rank2[i >> 1] >> 16) : (rank2[i >> 1] & 0xFFFFu);
-      const uint32_t pos = s.tile_prefix[bin] + myhist[bin] + r;
+      const uint32_t pos = myhist[bin] + r;
       s.keys[pos] = key[i];
       s.pay[pos] = pv;
     }
   }
   // ---- resolve the look-back
-  {
+  if (t < 256) {
     uint32_t excl = 0;
     if (tile > 0) {
       int64_t back = tile - 1;  // tile look[0] belongs to
@@ -421,10 +464,11 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
         }
         if (done) break;
         back -= j;
-        if (++spins > (1u << 24)) {  // never hang the GPU: flag and bail out
+        if (++spins > (1u << 22)) {  // never hang the GPU: flag and bail out
           atomicExch(p.err, 1u);
           break;
         }
+        if (j == 0) __nanosleep(40);  // the predecessor has not published yet: do not burn issue slots
 #pragma unroll
         for (int jj = 0; jj < kLook; ++jj)
           look[jj] = back - jj >= 0 ? ld_volatile_u32(state + t - (tile - back + jj) * kBinStride) : kStatusInclusive;
@@ -489,14 +533,14 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
 }
 
 template <bool kClass>
-__global__ void __launch_bounds__(kThreads, 3) sort_pass_kernel(SortParams p, int d) {
+__global__ void __launch_bounds__(kThreads, kMinBlocks) sort_pass_kernel(SortParams p, int d) {
   const PassInfo info = p.info[d];
   if (info.skip) return;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   PassSmem& s = *reinterpret_cast<PassSmem*>(smem_raw);
   const int t = threadIdx.x;
   if (t == 0) s.tile = atomicAdd(p.counters + d, 1u);
-  for (int i = t; i < 2 * kWarps * kBinStride; i += kThreads) (&s.whist[0][0])[i] = 0;  // whist + match
+  for (int i = t; i < kWarps * kBinStride / 4; i += kThreads) reinterpret_cast<uint4*>(&s.whist[0][0])[i] = make_uint4(0, 0, 0, 0);
   __syncthreads();
   const int64_t tile = s.tile;
   const int tile_items = int(min(int64_t(kTile), p.n - tile * kTile));
@@ -585,7 +629,7 @@ int run_sort(b200_ctx* ctx, SortParams p, void* scratch, size_t scratch_bytes) {
   // only the digits that can vary need look-back state
   const size_t zero_bytes = L.state + b200_align_up(size_t(p.n_digits) * size_t(p.n_tiles) * kBinStride * 4, 256);
   B200_CUDA(ctx, cudaMemsetAsync(base, 0, std::min(zero_bytes, L.zero_bytes), ctx->stream));
-  const int hist_blocks = int(std::min<int64_t>(p.n_tiles, int64_t(ctx->num_sms) * 8));
+  const int hist_blocks = int(std::min<int64_t>((p.n + kHistTile - 1) / kHistTile, int64_t(ctx->num_sms) * 8));
   static bool attr_set = false;
   const int smem = int(sizeof(PassSmem));
   if (!attr_set) {
@@ -593,8 +637,8 @@ int run_sort(b200_ctx* ctx, SortParams p, void* scratch, size_t scratch_bytes) {
     B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;
   }
-  B200_TIMED(ctx, "sort_hist", (sort_hist_kernel<<<hist_blocks, kThreads, 0, ctx->stream>>>(p)));
-  sort_scan_kernel<<<1, kThreads, 0, ctx->stream>>>(p);
+  B200_TIMED(ctx, "sort_hist", (sort_hist_kernel<<<hist_blocks, kHistThreads, 0, ctx->stream>>>(p)));
+  sort_scan_kernel<<<1, kHistThreads, 0, ctx->stream>>>(p);
   B200_LAUNCHED(ctx);
   for (int d = 0; d < p.n_digits; ++d) {
     if (d == p.cls_digit)

@@ -60,6 +60,25 @@ class CudaOps:
     def groupby(self, key_types, aggs, arg_types, expected_groups):
         return self.capi.GroupBy(self.ctx, key_types, aggs, arg_types, expected_groups)
 
+    # ---- hash repartitioning (high-cardinality group-by)
+    def partition(self, gb, keys: Sequence[Column], cols: Sequence[Column], n_parts: int, row_base: int):
+        """-> (counts[n_parts], [data bytes tensor per col], [validity bytes tensor or None per col], rows)
+        in the partitioned layout (destination p contiguous, starting at sum(counts[:p]))."""
+        pos, counts = gb.partition_plan(keys, n_parts)
+        datas, valids = [], []
+        for c in cols:
+            d, v = self.capi.partition_scatter(self.ctx, c, pos, c.validity is not None and c.null_count != 0)
+            datas.append(d)
+            valids.append(v)
+        rows = self.capi.partition_rows(self.ctx, keys[0].length, row_base, pos)
+        return counts, datas, valids, rows
+
+    def column_from_exchange(self, type_: int, data: torch.Tensor, valid_bytes: Optional[torch.Tensor], n: int) -> Column:
+        if valid_bytes is None:
+            return Column(type_, data, None, n, 0, 0)
+        bitmap, nulls = self.capi.pack_validity(self.ctx, valid_bytes)
+        return Column(type_, data, bitmap, n, 0, nulls)
+
 
 # ------------------------------------------------------------------------------------------------
 def dist_filter(ops, values: Column, mask: Column, null_selection: int = 0):
@@ -196,6 +215,87 @@ def dist_group_by(ops, keys: Sequence[Column], aggs: Sequence[AggSpec], args: Se
 
 
 # ------------------------------------------------------------------------------------------------
+class ShardedGroups:
+    """Result of the repartitioned group-by on one rank: this rank's DISJOINT set of groups (finalized
+    output in local first-occurrence order) plus each group's global first row, which ranks the groups
+    of all ranks into the reference's order (hash_aggregate.cc:391-403)."""
+
+    def __init__(self, out, first_rows):
+        self.out, self.first_rows = out, first_rows
+
+    @property
+    def num_groups(self):
+        return self.out.num_groups
+
+
+def _all_to_all_bytes(t: torch.Tensor, width: int, send_counts, recv_counts, group):
+    """all-to-all of a byte tensor holding `width`-byte elements, counts in elements."""
+    total = sum(recv_counts)
+    out = torch.empty(max(total, 1) * width, dtype=torch.uint8, device=t.device)[: total * width]
+    dist.all_to_all_single(out, t.contiguous(), [c * width for c in recv_counts], [c * width for c in send_counts], group=group)
+    return out
+
+
+def dist_group_by_repartition(ops, keys: Sequence[Column], aggs: Sequence[AggSpec], args: Sequence[Column], row_base: int,
+                              expected_groups: int = 0, group=None) -> ShardedGroups:
+    """High-cardinality grouped aggregation: rows are hash-partitioned by key
+    on every rank, exchanged with one all-to-all per column (+ the global row numbers) over NVLink, and
+    each rank aggregates the DISJOINT key set it owns.  Every key's rows meet on one rank, so counts,
+    min/max and integer sums are exact and a float sum sees all of its addends on one GPU.  Results stay
+    sharded; `first_rows` restores the reference's global group order when gathered."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    key_types = [k.type for k in keys]
+    arg_types = [a.type for a in args]
+    n = keys[0].length
+    # distinct columns are exchanged once
+    cols, index = [], {}
+    for c in list(keys) + list(args):
+        ident = (id(c.data), id(c.validity), c.offset)
+        if ident not in index:
+            index[ident] = len(cols)
+            cols.append(c)
+    gb = ops.groupby(key_types, aggs, arg_types, max(expected_groups // world, 1) if expected_groups else 0)
+    try:
+        if world == 1:
+            gb.consume(keys, args, row_base)
+            return ShardedGroups(gb.finalize(), gb.first_rows())
+        counts, datas, valids, rows = ops.partition(gb, keys, cols, world, row_base)
+        dev = rows.device
+        sc = torch.tensor(counts, dtype=torch.int64, device=dev)
+        rc = torch.empty(world, dtype=torch.int64, device=dev)
+        dist.all_to_all_single(rc, sc, group=group)
+        recv_counts = rc.tolist()
+        total = sum(recv_counts)
+        # whether a column carries validity must agree on every rank
+        has_valid = torch.tensor([1 if v is not None else 0 for v in valids], dtype=torch.int64, device=dev)
+        dist.all_reduce(has_valid, op=dist.ReduceOp.MAX, group=group)
+        has_valid = has_valid.tolist()
+        recv_cols = []
+        for c, d, v, hv in zip(cols, datas, valids, has_valid):
+            width = _WIDTH_OF(c)
+            rd = _all_to_all_bytes(d, width, counts, recv_counts, group)
+            rv = None
+            if hv:
+                if v is None:
+                    v = torch.ones(n, dtype=torch.uint8, device=dev)
+                rv = _all_to_all_bytes(v, 1, counts, recv_counts, group)
+            recv_cols.append(ops.column_from_exchange(c.type, rd, rv, total))
+        rrows = _all_to_all_bytes(rows.view(torch.uint8), 8, counts, recv_counts, group).view(torch.int64)
+        rkeys = [recv_cols[index[(id(c.data), id(c.validity), c.offset)]] for c in keys]
+        rargs = [recv_cols[index[(id(c.data), id(c.validity), c.offset)]] for c in args]
+        if total:
+            gb.consume_rows(rkeys, rargs, rrows)
+        return ShardedGroups(gb.finalize(), gb.first_rows())
+    finally:
+        gb.close()
+
+
+def _WIDTH_OF(c: Column) -> int:
+    from .columns import BITS
+    return max(BITS[c.type] // 8, 1)
+
+
+# ------------------------------------------------------------------------------------------------
 # bench.py hooks: one step of a workload over this rank's shard
 
 def _rank_world():
@@ -212,6 +312,9 @@ def bench_step(ctx, wl, cols_, bufs):
     if wl.name == "groupby_c3":
         k, v = cols_
         return dist_group_by(ops, [k], wl._specs(), [v] * len(wl.agg_names), rank * wl.n, wl.n_keys)
+    if wl.name == "groupby_c4":
+        k, v = cols_
+        return dist_group_by_repartition(ops, [k], wl._specs(), [v] * len(wl.agg_names), rank * wl.n, wl.n_keys)
     raise SystemExit("bench: workload %s has no multi-GPU form yet" % wl.name)
 
 
@@ -239,6 +342,15 @@ def bench_e2e_step(ctx, wl, host_cols):
         res = dist_group_by(ops, [k], wl._specs(), [v] * len(wl.agg_names), rank * wl.n, wl.n_keys)
         d2h = 0
         for cols__ in res.aggs:
+            for c in cols__:
+                d2h += c.to_host().nbytes()
+        compute.Transfer.d2h = d2h
+        return res
+    if wl.name == "groupby_c4":
+        k, v = dev_cols
+        res = dist_group_by_repartition(ops, [k], wl._specs(), [v] * len(wl.agg_names), rank * wl.n, wl.n_keys)
+        d2h = 0
+        for cols__ in res.out.aggs + [res.out.keys]:
             for c in cols__:
                 d2h += c.to_host().nbytes()
         compute.Transfer.d2h = d2h

@@ -207,6 +207,15 @@ B200_API int b200_groupby_destroy(b200_groupby* gb);
  * (row_base + i), which makes range-sharded partial tables mergeable in reference order. */
 B200_API int b200_groupby_consume(b200_groupby* gb, const b200_col* keys, const b200_col* args,
                                   uint64_t row_base);
+/* As b200_groupby_consume with an explicit global row number per row (row_ids: device uint64[length])
+ * instead of row_base + i: the form the hash-repartitioned multi-GPU path uses, where a rank
+ * aggregates rows that arrived from every shard (SURVEY §8e, high cardinality). */
+B200_API int b200_groupby_consume_rows(b200_groupby* gb, const b200_col* keys, const b200_col* args,
+                                       const uint64_t* row_ids);
+/* global first-occurrence row of every group, in output (group id) order: device uint64[num_groups].
+ * Lets ranks holding disjoint key sets restore the reference's global group order
+ * (hash_aggregate.cc:391-403) by ranking their groups on it. */
+B200_API int b200_groupby_first_rows(b200_groupby* gb, uint64_t* out_first_rows);
 /* == Grouper::Consume proper (hash_aggregate.cc:358-408): writes the uint32 group id of every
  * row, ids handed out in first-occurrence order across calls. */
 B200_API int b200_grouper_consume(b200_groupby* gb, const b200_col* keys, uint32_t* out_ids);
@@ -241,6 +250,27 @@ B200_API int b200_groupby_import(b200_groupby* gb, const void* state, uint32_t n
  *                                  ignored), like struct<min,max> (hash_aggregate.cc:741-757)
  * so out_aggs has n_aggs + (number of MIN_MAX aggs) entries. */
 B200_API int b200_groupby_finalize(b200_groupby* gb, b200_out_col* out_aggs, b200_out_col* out_keys);
+
+
+/* ---- hash repartitioning (multi-GPU grouped aggregation at high cardinality) -----
+ * No reference counterpart: upstream has no distributed execution; this realises north_star's
+ * "hash-repartitioning alltoall".  dest(row) = hash(packed key of gb's key schema) % n_parts;
+ * out_pos[row] = position of the row in a layout where the rows of destination p are contiguous
+ * and destination p starts at sum(out_counts[0..p)).  n_parts <= 16; length < 2^32.
+ *   plan     -> out_pos (device uint32[length]), out_counts (host int64[n_parts]); synchronises
+ *   scatter  -> out_data[out_pos[i]] = column[i]; out_valid (nullable) gets one 0/1 byte per row
+ *   rows     -> out_rows[out_pos[i]] = row_base + i
+ *   pack     -> validity bytes (as received from the exchange) to an Arrow bitmap + null count */
+B200_API int b200_partition_scratch_bytes(int64_t length, size_t* out_bytes);
+B200_API int b200_groupby_partition_plan(b200_groupby* gb, const b200_col* keys, int n_parts,
+                                         uint32_t* out_pos, int64_t* out_counts /* host */,
+                                         void* scratch, size_t scratch_bytes);
+B200_API int b200_partition_scatter(b200_ctx* ctx, const b200_col* col, const uint32_t* pos,
+                                    void* out_data, uint8_t* out_valid /* nullable */);
+B200_API int b200_partition_rows(b200_ctx* ctx, int64_t length, uint64_t row_base,
+                                 const uint32_t* pos, uint64_t* out_rows);
+B200_API int b200_pack_validity(b200_ctx* ctx, const uint8_t* valid_bytes, int64_t length,
+                                void* out_bitmap, int64_t* out_null_count /* host, nullable */);
 
 #ifdef __cplusplus
 }

@@ -79,6 +79,36 @@ class NumpyGroupBy:
                 s[3] = min(s[3], v[i])
                 s[4] = max(s[4], v[i])
 
+    def consume_rows(self, keys, args, row_ids):
+        rows = row_ids.numpy()
+        k = keys[0].values()
+        kv = keys[0].valid()
+        v = args[0].values().astype(np.float64)
+        vv = args[0].valid()
+        for i in range(len(k)):
+            key = (int(k[i]) if kv[i] else 0, bool(kv[i]))
+            s = self.t.setdefault(key, [int(rows[i]), 0.0, 0, np.inf, -np.inf])
+            s[0] = min(s[0], int(rows[i]))
+            if vv[i]:
+                s[1] += v[i]
+                s[2] += 1
+                s[3] = min(s[3], v[i])
+                s[4] = max(s[4], v[i])
+
+    def first_rows(self):
+        return torch.tensor(sorted(s[0] for s in self.t.values()), dtype=torch.int64)
+
+    def partition_plan(self, keys, n_parts):
+        """numpy image of b200_groupby_partition_plan: any deterministic key hash will do here (what is
+        under test is the exchange logic); rows of one destination contiguous."""
+        k = keys[0].values().astype(np.int64)
+        kv = keys[0].valid()
+        dest = np.where(kv, (k * 2654435761 >> 7) % n_parts, 0).astype(np.int64)
+        order = np.argsort(dest, kind="stable")
+        pos = np.empty(len(k), dtype=np.int64)
+        pos[order] = np.arange(len(k))
+        return torch.from_numpy(pos), [int((dest == p).sum()) for p in range(n_parts)]
+
     def slot_bytes(self):
         return self.SLOT
 
@@ -126,6 +156,30 @@ class NumpyOps:
     def groupby(self, key_types, aggs, arg_types, expected_groups):
         return NumpyGroupBy()
 
+    def partition(self, gb, keys, cols_, n_parts, row_base):
+        pos, counts = gb.partition_plan(keys, n_parts)
+        p = pos.numpy()
+        datas, valids = [], []
+        for c in cols_:
+            v = c.values()
+            out = np.empty_like(v)
+            out[p] = v
+            datas.append(torch.from_numpy(out.view(np.uint8).reshape(-1).copy()))
+            if c.validity is not None and c.null_count != 0:
+                vb = np.empty(len(v), dtype=np.uint8)
+                vb[p] = c.valid().astype(np.uint8)
+                valids.append(torch.from_numpy(vb))
+            else:
+                valids.append(None)
+        rows = np.empty(len(p), dtype=np.int64)
+        rows[p] = np.arange(len(p), dtype=np.int64) + row_base
+        return counts, datas, valids, torch.from_numpy(rows)
+
+    def column_from_exchange(self, type_, data, valid_bytes, n):
+        from arrow1_b200.columns import NP_OF
+        v = data.numpy().view(NP_OF[type_])[:n].copy()
+        return Column.from_numpy(v, None if valid_bytes is None else valid_bytes.numpy().astype(bool), type=type_)
+
 
 def shard(col: Column, world: int):
     """Row-range shards (uneven on purpose); returns [(column, row_base)]."""
@@ -165,6 +219,10 @@ def _worker(rank, world, port, job, path):
         elif kind == "groupby":
             (k, v), base = case["shards"][rank]
             res.append(bd.dist_group_by(ops, [k], [AggSpec(cols.HASH_SUM)], [v], base))
+        elif kind == "groupby_repart":
+            (k, v), base = case["shards"][rank]
+            sg = bd.dist_group_by_repartition(ops, [k], [AggSpec(cols.HASH_SUM)], [v], base)
+            res.append((sg.out, sg.first_rows.numpy().copy()))
         elif kind == "filter":
             (v, m), base = case["shards"][rank]
             r = bd.dist_filter(ops, v, m, case["null_selection"])
@@ -254,6 +312,39 @@ def test_dist_group_by_and_filter_world2():
     assert sum(results[r][1][2] for r in range(world)) == wf.length
     np.testing.assert_array_equal(gvalid, wf.valid())
     np.testing.assert_array_equal(gv[gvalid], wf.values()[wf.valid()])
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_dist_group_by_repartition_matches_oracle(world):
+    """High-cardinality form: hash partition -> all-to-all of (key, value, validity, global row) ->
+    disjoint local aggregation.  Gathering every rank's groups and ranking them by global first row
+    must give the oracle's output exactly (group order, null-key group, counts, sums)."""
+    rng = np.random.default_rng(40 + world)
+    n = 4000
+    keys = Column.from_numpy(rng.integers(-2000, 2000, size=n).astype(np.int64), rng.random(n) > 0.01)
+    vals = Column.from_numpy(rng.integers(0, 1000, size=n).astype(np.float64), rng.random(n) > 0.1)
+    ks, vs = shard(keys, world), shard(vals, world)
+    gshards = [((ks[r][0], vs[r][0]), ks[r][1]) for r in range(world)]
+    results = run_world(world, [{"kind": "groupby_repart", "shards": gshards}])
+    want = oracle.groupby([keys], [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT)], [vals, vals], kind="port")
+    merged, seen = [], set()
+    for r in range(world):
+        groups, first_rows = results[r][0]
+        assert len(groups) == len(first_rows)
+        for (key, s, c, mn, mx), fr in zip(groups, first_rows):
+            assert key not in seen, "key sets of the ranks must be disjoint"
+            seen.add(key)
+            merged.append((int(fr), key, s, c))
+    merged.sort()
+    assert len(merged) == want.num_groups
+    wk, wkv = want.keys[0]
+    for g, (fr, key, s, c) in enumerate(merged):
+        assert key[1] == bool(wkv[g])
+        if key[1]:
+            assert key[0] == int(wk[g]), "ranking by global first row restores the reference's group order"
+        assert c == int(want.aggs[1][0][0][g])
+        if c:
+            assert s == want.aggs[0][0][0][g]
 
 
 def test_choose_splitters_clamps_tail_keys():
