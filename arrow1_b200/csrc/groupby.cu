@@ -82,6 +82,7 @@ struct GbArgs {
   uint32_t* out_ids;         // grouper lookup output
   char* spill;               // fast path: slot images of groups the global table had no room for (counters[5])
   uint64_t* zf_scratch;      // fast path: per-CTA earliest-zero-row words [grid][kFastGroups]
+  int32_t dbg;               // B200_GB_DBG: phase-skipping bits for timing experiments (results are wrong)
   int32_t local_slots;       // shared-memory table size (power of two), 0 = none
   int32_t rows_per_block;
 };
@@ -489,8 +490,8 @@ __device__ __forceinline__ uint32_t fast_hash(uint64_t key) {
 static_assert(kFastBuckets == 1024, "fast_hash yields 10 bits");
 
 // slot of `key` in bucket b: KEY32 -> 4 candidates, else 2; -1 if absent; *has_empty = bucket has room
-template <bool KEY32>
-__device__ __forceinline__ int fast_match(const FastSmem& S, uint32_t b, uint64_t key, bool* has_empty) {
+template <bool KEY32, class SM>
+__device__ __forceinline__ int fast_match(const SM& S, uint32_t b, uint64_t key, bool* has_empty) {
   uint4 w;
   asm volatile("ld.volatile.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
                : "=r"(w.x), "=r"(w.y), "=r"(w.z), "=r"(w.w)
@@ -508,14 +509,15 @@ __device__ __forceinline__ int fast_match(const FastSmem& S, uint32_t b, uint64_
   }
 }
 
-__device__ __forceinline__ int fast_gid_of_slot(const FastSmem& S, int slot) {
+template <class SM>
+__device__ __forceinline__ int fast_gid_of_slot(const SM& S, int slot) {
   const uint32_t g = *reinterpret_cast<const volatile uint16_t*>(&S.hgid[slot]);
   return g < uint32_t(kFastGroups) ? int(g) : (g == kGidUnset ? -1 : -2);
 }
 
 // the rare continuation of a lookup whose home bucket neither holds the key nor has room
-template <bool KEY32>
-__device__ __noinline__ int fast_lookup_far(const FastSmem& S, uint64_t key, uint32_t b) {
+template <bool KEY32, class SM>
+__device__ __noinline__ int fast_lookup_far(const SM& S, uint64_t key, uint32_t b) {
 #pragma unroll 1
   for (int probe = 1; probe < kLocalProbe; ++probe) {
     b = (b + 1) & (kFastBuckets - 1);
@@ -528,8 +530,8 @@ __device__ __noinline__ int fast_lookup_far(const FastSmem& S, uint64_t key, uin
 }
 
 // group id of `key`, -1 = not (yet) in the table, -2 = cannot be placed
-template <bool KEY32>
-__device__ __forceinline__ int fast_lookup(const FastSmem& S, uint64_t key) {
+template <bool KEY32, class SM>
+__device__ __forceinline__ int fast_lookup(const SM& S, uint64_t key) {
   const uint32_t b = fast_hash(key);
   bool has_empty;
   const int slot = fast_match<KEY32>(S, b, key, &has_empty);
@@ -538,8 +540,8 @@ __device__ __forceinline__ int fast_lookup(const FastSmem& S, uint64_t key) {
   return fast_lookup_far<KEY32>(S, key, b);
 }
 
-template <bool KEY32>
-__device__ __forceinline__ void fast_insert(FastSmem& S, uint64_t key) {
+template <bool KEY32, class SM>
+__device__ __forceinline__ void fast_insert(SM& S, uint64_t key) {
   uint32_t b = fast_hash(key);
 #pragma unroll 1
   for (int probe = 0; probe < kLocalProbe; ++probe) {
@@ -907,6 +909,777 @@ __global__ void __launch_bounds__(kFastThreads, 2) gb_fast_kernel(const __grid_c
     if (!gs) {
       // no room (the table is sized from the cardinality hint, not for the worst case): the group
       // goes to the spill list as a fresh slot image; the host grows the table and imports it
+      gs = a.spill + size_t(atomicAdd(a.counters + 5, 1u)) * a.s.stride;
+      init_slot(gs, a.s);
+      reinterpret_cast<uint64_t*>(gs)[0] = key;
+      reinterpret_cast<uint64_t*>(gs)[a.s.stride / 8 - 1] = 0;
+      claimed = false;
+    }
+    if (claimed) atomicAdd(&S.new_groups, 1u);
+    const uint64_t cnt = S.cnt[g], nulls = S.nulls[g];
+    if (S.first[g] != 0xFFFFFFFFu) atomic_min_checked(reinterpret_cast<uint64_t*>(gs) + 1, a.row_base + uint64_t(begin) + S.first[g]);
+    for (int j = 0; j < a.s.n_aggs; ++j) {
+      const GbAgg& ag = a.s.aggs[j];
+      uint64_t* d = reinterpret_cast<uint64_t*>(gs + ag.off);
+      if (ag.kind == B200_HASH_COUNT) {
+        const uint64_t c = ag.option ? nulls : cnt;
+        if (c) atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)c);
+      } else if (ag.kind == B200_HASH_MIN_MAX) {
+        if (cnt) {
+          atomic_min_checked(d + 0, S.mn[g]);
+          atomic_max_checked(d + 1, S.mx[g]);
+          atomic_min_checked(d + 2, zf[g]);
+        }
+        const uint64_t flags = (cnt ? 1ull : 0ull) | (nulls ? 2ull : 0ull);
+        if (flags) atomic_or_checked(d + 3, flags);
+      } else if (cnt) {
+        if (ag.dom == kFloat) atomicAdd(reinterpret_cast<double*>(d), __longlong_as_double(S.sum[g]));
+        else atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)S.sum[g]);
+        atomicAdd(reinterpret_cast<unsigned long long*>(d + 1), (unsigned long long)cnt);
+      }
+    }
+  }
+  __syncthreads();
+  if (t == 0) {
+    if (S.new_groups) atomicAdd(a.counters + 0, S.new_groups);
+    if (S.deferred) atomicAdd(a.counters + 1, S.deferred);
+  }
+}
+
+// ---- binned low-cardinality path (v2 of the fast path) -------------------------------------------
+// Same contract as gb_fast_kernel.  What changed, and why (profiles/r01_gb_v2_ncu_summary.txt: 4.9 warp
+// instructions and 1.36 shared-memory wavefronts per row, both at their limit):
+//   * one CTA of 1024 threads per SM and 8192-row tiles: a group sees ~8 rows per tile instead of ~4, so
+//     the per-group bookkeeping of the reduction step is amortised over twice the rows
+//   * every group owns a fixed-capacity bin of kBinCap values, laid out value-slot-major
+//     (bins[j * 1024 + g]): a row's slot is known as soon as its rank comes back from the native
+//     ATOMS.ADD, so the tile-wide scan of the counters, the per-row offset lookup and the registers that
+//     held keys / values / ranks across two barriers are gone; and the owner threads of a warp read
+//     consecutive addresses (conflict-free LDS.64) instead of 32 unrelated segments
+//   * rows that find their bin full (skewed keys) are accumulated on the spot with the warp-converged
+//     shared-memory CAS path, so skew costs speed but never defers rows
+constexpr int kBinThreads = 1024;
+constexpr int kBinRows = kFastSub * kFastSubs;          // rows per thread per tile (8)
+constexpr int kBinSubRows = kBinThreads * kFastSub;     // 4096
+constexpr int kBinTile = kBinThreads * kBinRows;        // 8192
+constexpr int kBinCap = 16;                             // values per group per tile before the overflow path
+constexpr int kBinSlots = 4096;                         // KEY32 table: {key, group id} pairs, load <= 1/4
+constexpr uint32_t kBinGidOverflow = 0xFFFFFFFEu;     // == -2 as int: "cannot be placed"
+
+struct BinSmem {
+  // key -> dense group id.  KEY32 (one <= 32-bit key column without nulls): 4096 {key, gid} pairs probed
+  // with ONE LDS.64 — the profile of the bucketed table (LDS.128 + four compares + a second load for
+  // the id) showed 37 % of the kernel's instructions in the lookup.  Other key shapes keep the
+  // bucketed table of gb_fast_kernel.
+  union {
+    struct {
+      uint4 hbuckets[kFastBuckets];
+      uint16_t hgid[kFastSlots32];
+    };
+    uint2 ktab[kBinSlots];
+  };
+  uint64_t bins[kBinCap * kFastGroups];
+  uint64_t sum[kFastGroups];
+  uint64_t mn[kFastGroups];
+  uint64_t mx[kFastGroups];
+  uint32_t tcnt[kFastGroups];
+  uint32_t cnt[kFastGroups];
+  uint32_t nulls[kFastGroups];
+  uint32_t first[kFastGroups];
+  uint32_t n_groups, need_insert, new_groups, deferred;
+};
+static_assert(kBinThreads == kFastGroups, "the reduction step gives every thread one group");
+static_assert(sizeof(BinSmem) <= 227 * 1024, "BinSmem must fit the 227 KB a CTA can opt into");
+
+// dense small keys (0..4095) map to themselves: no collisions at all for C3-like dictionaries; wider keys
+// fold their upper bits in
+__device__ __forceinline__ uint32_t bin_hash32(uint32_t k) { return (k ^ (k >> 12)) & uint32_t(kBinSlots - 1); }
+
+__device__ __noinline__ int bin_lookup_far(const BinSmem& S, uint32_t k, uint32_t h) {
+#pragma unroll 1
+  for (int probe = 1; probe < 4 * kLocalProbe; ++probe) {
+    h = (h + 1) & uint32_t(kBinSlots - 1);
+    const uint2 e = S.ktab[h];
+    if (e.x == k) return int(e.y);
+    if (e.x == kEmpty32) return -1;
+  }
+  return -2;
+}
+
+// group id of a 32-bit key: -1 = not (yet) in the table, -2 = cannot be placed
+__device__ __forceinline__ int bin_lookup32(const BinSmem& S, uint32_t k) {
+  const uint32_t h = bin_hash32(k);
+  const uint2 e = S.ktab[h];
+  if (e.x == k) return int(e.y);   // the id, or kBinGidOverflow == -2
+  if (e.x == kEmpty32) return -1;
+  return bin_lookup_far(S, k, h);
+}
+
+// runs only between the two barriers of the insert phase; lookups resume after the second one
+__device__ __forceinline__ void bin_insert32(BinSmem& S, uint32_t k) {
+  uint32_t h = bin_hash32(k);
+#pragma unroll 1
+  for (int probe = 0; probe < 4 * kLocalProbe; ++probe) {
+    uint32_t* kp = &S.ktab[h].x;
+    uint32_t cur = *reinterpret_cast<volatile uint32_t*>(kp);
+    if (cur == kEmpty32) {
+      if (*reinterpret_cast<const volatile uint32_t*>(&S.n_groups) >= uint32_t(kFastGroups)) return;
+      cur = atomicCAS(kp, kEmpty32, k);
+      if (cur == kEmpty32) {
+        const uint32_t g = atomicAdd(&S.n_groups, 1u);
+        S.ktab[h].y = g < uint32_t(kFastGroups) ? g : kBinGidOverflow;
+        return;
+      }
+    }
+    if (cur == k) return;
+    h = (h + 1) & uint32_t(kBinSlots - 1);
+  }
+}
+
+template <int KMODE, bool VFAST>
+__global__ void __launch_bounds__(kBinThreads, 1) gb_bin_kernel(const __grid_constant__ GbArgs a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  BinSmem& S = *reinterpret_cast<BinSmem*>(smem);
+  const int t = threadIdx.x, lane = t & 31;
+  constexpr bool KEY32 = KMODE == 1;
+  // the raw columns of the NEXT tile are requested before this tile's barrier + reduction and decoded
+  // after it: their latency hides behind work that needs few registers
+  constexpr bool PREFETCH = KEY32 && VFAST;
+  if (KEY32) {
+    for (int i = t; i < kBinSlots; i += kBinThreads) S.ktab[i] = make_uint2(kEmpty32, 0xFFFFFFFFu);
+  } else {
+    for (int i = t; i < kFastBuckets; i += kBinThreads) S.hbuckets[i] = make_uint4(kEmpty32, kEmpty32, kEmpty32, kEmpty32);
+    for (int i = t; i < kFastSlots32; i += kBinThreads) S.hgid[i] = uint16_t(kGidUnset);
+  }
+  {
+    S.sum[t] = 0;
+    S.mn[t] = ~uint64_t(0);
+    S.mx[t] = 0;
+    S.tcnt[t] = 0;
+    S.cnt[t] = 0;
+    S.nulls[t] = 0;
+    S.first[t] = 0xFFFFFFFFu;
+  }
+  if (t == 0) {
+    S.n_groups = 0;
+    S.need_insert = 0;
+    S.new_groups = 0;
+    S.deferred = 0;
+  }
+  __syncthreads();
+  const int dom = a.s.aggs[0].dom;
+  bool want_minmax = false;
+  for (int j = 0; j < a.s.n_aggs; ++j)
+    if (a.s.aggs[j].kind == B200_HASH_MIN_MAX) want_minmax = true;
+  const int64_t begin = int64_t(blockIdx.x) * a.rows_per_block;
+  const int64_t end = min(a.n, begin + a.rows_per_block);   // a.n is a multiple of kBinTile here
+  uint64_t* zf = a.zf_scratch + size_t(blockIdx.x) * kFastGroups;
+
+  // raw image of a tile's rows of this thread (PREFETCH only)
+  uint4 rk[kFastSubs];
+  ulonglong2 rva[kFastSubs], rvb[kFastSubs];
+  uint32_t rvm[kFastSubs];
+  auto request = [&](int64_t base) {
+#pragma unroll
+    for (int s = 0; s < kFastSubs; ++s) {
+      const int64_t r0 = base + s * kBinSubRows + t * kFastSub;
+      rk[s] = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(a.keys[0].data) + r0);
+      const ulonglong2* vp = reinterpret_cast<const ulonglong2*>(reinterpret_cast<const uint64_t*>(a.cols[0].data) + r0);
+      rva[s] = vp[0];
+      rvb[s] = vp[1];
+      rvm[s] = 0xFFu;
+      if (a.cols[0].vv.words) {
+        // r0 is a multiple of 4: its 4 validity bits never straddle more than two bytes
+        const int64_t bit = a.cols[0].vv.bit_offset + r0;
+        const uint8_t* bytes = reinterpret_cast<const uint8_t*>(a.cols[0].vv.words);
+        rvm[s] = uint32_t(__ldg(reinterpret_cast<const uint16_t*>(bytes + ((bit >> 3) & ~int64_t(1))))) |
+                 (uint32_t(__ldg(bytes + ((bit >> 3) & ~int64_t(1)) + 2)) << 16);
+      }
+    }
+  };
+  if (PREFETCH && begin < end) request(begin);
+
+#pragma unroll 1
+  for (int64_t base = begin; base < end; base += kBinTile) {
+    uint64_t vbits[kBinRows];
+    int gid[kBinRows];
+    uint32_t vmask = 0;   // validity of the values
+    uint32_t newkey = 0;  // rows whose key was not in the table when the tile started
+    // ---- P1a: loads and group lookup
+    {
+      uint64_t key[kBinRows];
+      uint32_t special = 0;
+#pragma unroll
+      for (int s = 0; s < kFastSubs; ++s) {
+        const int64_t r0 = base + s * kBinSubRows + t * kFastSub;
+        if (PREFETCH) {
+          key[4 * s + 0] = rk[s].x; key[4 * s + 1] = rk[s].y; key[4 * s + 2] = rk[s].z; key[4 * s + 3] = rk[s].w;
+          vbits[4 * s + 0] = rva[s].x; vbits[4 * s + 1] = rva[s].y; vbits[4 * s + 2] = rvb[s].x; vbits[4 * s + 3] = rvb[s].y;
+          uint32_t m = 0xFu;
+          if (a.cols[0].vv.words) {
+            const int64_t bit = a.cols[0].vv.bit_offset + r0;
+            m = rvm[s] >> (int(bit & 7) + 8 * int((bit >> 3) & 1));
+          }
+          vmask |= (m & 0xFu) << (4 * s);
+#pragma unroll
+          for (int i = 0; i < kFastSub; ++i)
+            if (uint32_t(key[4 * s + i]) == kEmpty32) special |= 1u << (4 * s + i);
+          continue;
+        }
+        if (KMODE == 1) {
+          const uint4 k4 = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(a.keys[0].data) + r0);
+          key[4 * s + 0] = k4.x; key[4 * s + 1] = k4.y; key[4 * s + 2] = k4.z; key[4 * s + 3] = k4.w;
+#pragma unroll
+          for (int i = 0; i < kFastSub; ++i)
+            if (uint32_t(key[4 * s + i]) == kEmpty32) special |= 1u << (4 * s + i);
+        } else if (KMODE == 2) {
+          const ulonglong2* kp = reinterpret_cast<const ulonglong2*>(reinterpret_cast<const uint64_t*>(a.keys[0].data) + r0);
+          const ulonglong2 ka = kp[0], kb = kp[1];
+          key[4 * s + 0] = ka.x; key[4 * s + 1] = ka.y; key[4 * s + 2] = kb.x; key[4 * s + 3] = kb.y;
+#pragma unroll
+          for (int i = 0; i < kFastSub; ++i)
+            if (key[4 * s + i] == kEmpty) special |= 1u << (4 * s + i);
+        } else {
+#pragma unroll
+          for (int i = 0; i < kFastSub; ++i) {
+            int sp;
+            key[4 * s + i] = load_key(a, r0 + i, &sp);
+            if (sp) special |= 1u << (4 * s + i);
+          }
+        }
+        if (VFAST) {
+          const ulonglong2* vp = reinterpret_cast<const ulonglong2*>(reinterpret_cast<const uint64_t*>(a.cols[0].data) + r0);
+          const ulonglong2 va = vp[0], vb = vp[1];
+          vbits[4 * s + 0] = va.x; vbits[4 * s + 1] = va.y; vbits[4 * s + 2] = vb.x; vbits[4 * s + 3] = vb.y;
+          uint32_t m = 0xFu;
+          if (a.cols[0].vv.words) {
+            const int64_t bit = a.cols[0].vv.bit_offset + r0;
+            const uint8_t* bytes = reinterpret_cast<const uint8_t*>(a.cols[0].vv.words);
+            const int sh = int(bit & 7);
+            m = uint32_t(__ldg(bytes + (bit >> 3))) >> sh;
+            if (sh > 4) m |= uint32_t(__ldg(bytes + (bit >> 3) + 1)) << (8 - sh);
+          }
+          vmask |= (m & 0xFu) << (4 * s);
+        } else {
+#pragma unroll
+          for (int i = 0; i < kFastSub; ++i) {
+            const Val v = load_val(a.cols[0], r0 + i);
+            vbits[4 * s + i] = v.bits;
+            vmask |= (v.valid ? 1u : 0u) << (4 * s + i);
+          }
+        }
+      }
+      uint32_t pending = 0;
+#pragma unroll
+      for (int i = 0; i < kBinRows; ++i) {
+        if (a.dbg & 4) gid[i] = int(key[i] & 1023);
+        else if (KEY32) gid[i] = bin_lookup32(S, uint32_t(key[i]));
+        else gid[i] = fast_lookup<false>(S, key[i]);
+        if (gid[i] == -1) pending |= 1u << i;
+      }
+      if (special) {   // the EMPTY-valued key cannot live in the table: its rows go to the generic kernel
+#pragma unroll
+        for (int i = 0; i < kBinRows; ++i)
+          if ((special >> i) & 1u) gid[i] = -2;
+        pending &= ~special;
+      }
+      newkey = pending;
+      if (__any_sync(0xffffffffu, pending != 0) && lane == 0) S.need_insert = 1;
+      __syncthreads();   // also orders the previous tile's reduction before this tile's bin writes
+      if (S.need_insert) {   // CTA-uniform; taken for the first tile(s) only
+#pragma unroll
+        for (int i = 0; i < kBinRows; ++i)
+          if ((pending >> i) & 1u) {
+            if (KEY32) bin_insert32(S, uint32_t(key[i]));
+            else fast_insert<false>(S, key[i]);
+          }
+        __syncthreads();
+        if (t == 0) S.need_insert = 0;
+#pragma unroll
+        for (int i = 0; i < kBinRows; ++i)
+          if ((pending >> i) & 1u) {
+            gid[i] = KEY32 ? bin_lookup32(S, uint32_t(key[i])) : fast_lookup<false>(S, key[i]);
+            if (gid[i] == -1) gid[i] = -2;
+          }
+        __syncwarp();
+      }
+    }
+    // ---- P1b: slot in the group's bin (native shared atomic), straight into the bin
+    uint32_t defer = 0, over = 0, zeros = 0;
+#pragma unroll
+    for (int i = 0; i < kBinRows; ++i) {
+      const int g = gid[i];
+      if (g < 0) {
+        defer |= 1u << i;
+        continue;
+      }
+      if (a.dbg & 2) continue;
+      if ((vmask >> i) & 1u) {
+        const uint32_t r = atomicAdd(&S.tcnt[g], 1u);
+        if (r < uint32_t(kBinCap)) S.bins[r * kFastGroups + g] = vbits[i];
+        else over |= 1u << i;
+        if ((uint32_t(vbits[i] >> 32) & 0x7FFFFFFFu) == 0) zeros |= 1u << i;   // candidate +-0.0 (exact test below)
+      } else {
+        atomicAdd(&S.nulls[g], 1u);
+      }
+    }
+    newkey &= ~defer;
+    if (newkey) {   // first rows: only rows whose key entered the table in this tile can lower them
+#pragma unroll
+      for (int i = 0; i < kBinRows; ++i)
+        if ((newkey >> i) & 1u) {
+          const int64_t row = base + (i / kFastSub) * kBinSubRows + t * kFastSub + (i % kFastSub);
+          atomicMin(&S.first[gid[i]], uint32_t(row - begin));
+        }
+    }
+    if (zeros && want_minmax && dom == kFloat) {
+      // +-0.0 ties in hash_min_max: the earliest zero row decides the sign (see accumulate())
+#pragma unroll
+      for (int i = 0; i < kBinRows; ++i)
+        if (((zeros >> i) & 1u) && (vbits[i] << 1) == 0) {
+          const int64_t row = base + (i / kFastSub) * kBinSubRows + t * kFastSub + (i % kFastSub);
+          atomic_min_checked(zf + gid[i], ((a.row_base + uint64_t(row)) << 1) | (vbits[i] >> 63));
+        }
+    }
+    if (defer) {
+#pragma unroll
+      for (int i = 0; i < kBinRows; ++i)
+        if ((defer >> i) & 1u) {
+          const int64_t row = base + (i / kFastSub) * kBinSubRows + t * kFastSub + (i % kFastSub);
+          atomicOr(a.defer_out + (row >> 5), 1u << (row & 31));
+        }
+      atomicAdd(&S.deferred, uint32_t(__popc(defer)));
+    }
+    __syncwarp();
+    if (__any_sync(0xffffffffu, over != 0)) {
+      // ---- bin overflow (skewed keys): accumulate these rows directly.  Counts use the native 32-bit
+      // atomic; float sums a CAS loop the whole warp stays converged in; extremes read-then-rarely-CAS.
+#pragma unroll
+      for (int i = 0; i < kBinRows; ++i) {
+        const bool mine = (over >> i) & 1u;
+        const int g = mine ? gid[i] : 0;
+        if (mine) atomicAdd(&S.cnt[g], 1u);
+        if (dom == kFloat) {
+          bool pend = mine;
+          while (__any_sync(0xffffffffu, pend)) {
+            if (pend) {
+              const uint64_t o = *reinterpret_cast<const volatile uint64_t*>(&S.sum[g]);
+              const uint64_t nw = __double_as_longlong(__longlong_as_double(o) + __longlong_as_double(vbits[i]));
+              if (atomicCAS(reinterpret_cast<unsigned long long*>(&S.sum[g]), (unsigned long long)o, (unsigned long long)nw) == o) pend = false;
+            }
+          }
+        } else if (mine) {
+          uint32_t* w = reinterpret_cast<uint32_t*>(&S.sum[g]);
+          const uint32_t lo = uint32_t(vbits[i]), hi = uint32_t(vbits[i] >> 32);
+          const uint32_t old_lo = atomicAdd(w, lo);
+          const uint32_t carry = (old_lo + lo) < old_lo ? 1u : 0u;
+          if (hi + carry) atomicAdd(w + 1, hi + carry);
+        }
+        if (want_minmax) {
+          bool lt = false, gt = false;
+          uint64_t o = 0;
+          if (mine) {
+            bool use = true;
+            if (dom == kFloat) {
+              const double dv = __longlong_as_double(vbits[i]);
+              use = dv == dv;
+              o = ord_f64(dv);
+            } else {
+              o = dom == kSigned ? (vbits[i] ^ 0x8000000000000000ull) : vbits[i];
+            }
+            if (use) {
+              lt = o < *reinterpret_cast<const volatile uint64_t*>(&S.mn[g]);
+              gt = o > *reinterpret_cast<const volatile uint64_t*>(&S.mx[g]);
+            }
+          }
+          if (__any_sync(0xffffffffu, lt || gt)) {
+            if (lt) atomicMin(reinterpret_cast<unsigned long long*>(&S.mn[g]), (unsigned long long)o);
+            if (gt) atomicMax(reinterpret_cast<unsigned long long*>(&S.mx[g]), (unsigned long long)o);
+            __syncwarp();
+          }
+        }
+      }
+    }
+    if (PREFETCH && base + kBinTile < end) request(base + kBinTile);
+    __syncthreads();
+    // ---- P4: every thread reduces the bin of its own group with plain adds / compares
+    {
+      const int g = t;
+      const uint32_t c_all = (a.dbg & 1) ? 0u : S.tcnt[g];
+      if (c_all != 0) {
+        const uint32_t c = min(c_all, uint32_t(kBinCap));
+        S.tcnt[g] = 0;
+        S.cnt[g] += c;
+        const uint64_t* bin = S.bins + g;
+        if (dom == kFloat) {
+          // the group's running extremes ride along, so an update is the rare case and a value costs one
+          // add and two compares (a NaN never compares true: it never wins, hash_aggregate.cc:672-673)
+          const uint64_t omn = S.mn[g], omx = S.mx[g];
+          double s = 0.0;
+          double lo = omn == ~uint64_t(0) ? __longlong_as_double(0x7FF0000000000000ull) : unord_f64(omn);
+          double hi = omx == 0 ? __longlong_as_double(0xFFF0000000000000ull) : unord_f64(omx);
+#pragma unroll 4
+          for (uint32_t j = 0; j < c; ++j) {
+            const double v = __longlong_as_double(bin[j * kFastGroups]);
+            s += v;
+            if (v < lo || v > hi) {
+              if (v < lo) lo = v;
+              if (v > hi) hi = v;
+            }
+          }
+          S.sum[g] = __double_as_longlong(__longlong_as_double(S.sum[g]) + s);
+          const uint64_t olo = ord_f64(lo), ohi = ord_f64(hi);
+          if (olo < omn) S.mn[g] = olo;
+          if (ohi > omx) S.mx[g] = ohi;
+        } else {
+          const uint64_t flip = dom == kSigned ? 0x8000000000000000ull : 0ull;
+          uint64_t s = 0, lo = ~uint64_t(0), hi = 0;
+#pragma unroll 2
+          for (uint32_t j = 0; j < c; ++j) {
+            const uint64_t v = bin[j * kFastGroups];
+            s += v;
+            const uint64_t ov = v ^ flip;
+            lo = ov < lo ? ov : lo;
+            hi = ov > hi ? ov : hi;
+          }
+          S.sum[g] += s;
+          if (lo < S.mn[g]) S.mn[g] = lo;
+          if (hi > S.mx[g]) S.mx[g] = hi;
+        }
+      }
+    }
+    // no barrier here: the next tile's P1a touches neither tcnt nor the bins, and its own barrier
+    // orders this reduction before the next tile's bin writes
+  }
+  __syncthreads();
+  // ---- flush: every group of this CTA is folded into the global table
+  for (int slot = t; slot < (KEY32 ? kBinSlots : kFastSlots64); slot += kBinThreads) {
+    uint32_t g;
+    uint64_t key;
+    if (KEY32) {
+      const uint2 e = S.ktab[slot];
+      if (e.x == kEmpty32) continue;
+      g = e.y;
+      key = e.x;
+    } else {
+      g = S.hgid[slot];
+      key = reinterpret_cast<const uint64_t*>(S.hbuckets)[slot];
+    }
+    if (g >= uint32_t(kFastGroups)) continue;   // unset or overflow
+    bool claimed;
+    uint64_t slot_index;
+    char* gs = global_slot(a.t, a.s.stride, key, 0, true, &claimed, &slot_index);
+    if (!gs) {
+      gs = a.spill + size_t(atomicAdd(a.counters + 5, 1u)) * a.s.stride;
+      init_slot(gs, a.s);
+      reinterpret_cast<uint64_t*>(gs)[0] = key;
+      reinterpret_cast<uint64_t*>(gs)[a.s.stride / 8 - 1] = 0;
+      claimed = false;
+    }
+    if (claimed) atomicAdd(&S.new_groups, 1u);
+    const uint64_t cnt = S.cnt[g], nulls = S.nulls[g];
+    if (S.first[g] != 0xFFFFFFFFu) atomic_min_checked(reinterpret_cast<uint64_t*>(gs) + 1, a.row_base + uint64_t(begin) + S.first[g]);
+    for (int j = 0; j < a.s.n_aggs; ++j) {
+      const GbAgg& ag = a.s.aggs[j];
+      uint64_t* d = reinterpret_cast<uint64_t*>(gs + ag.off);
+      if (ag.kind == B200_HASH_COUNT) {
+        const uint64_t c = ag.option ? nulls : cnt;
+        if (c) atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)c);
+      } else if (ag.kind == B200_HASH_MIN_MAX) {
+        if (cnt) {
+          atomic_min_checked(d + 0, S.mn[g]);
+          atomic_max_checked(d + 1, S.mx[g]);
+          atomic_min_checked(d + 2, zf[g]);
+        }
+        const uint64_t flags = (cnt ? 1ull : 0ull) | (nulls ? 2ull : 0ull);
+        if (flags) atomic_or_checked(d + 3, flags);
+      } else if (cnt) {
+        if (ag.dom == kFloat) atomicAdd(reinterpret_cast<double*>(d), __longlong_as_double(S.sum[g]));
+        else atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)S.sum[g]);
+        atomicAdd(reinterpret_cast<unsigned long long*>(d + 1), (unsigned long long)cnt);
+      }
+    }
+  }
+  __syncthreads();
+  if (t == 0) {
+    if (S.new_groups) atomicAdd(a.counters + 0, S.new_groups);
+    if (S.deferred) atomicAdd(a.counters + 1, S.deferred);
+  }
+}
+
+// ---- binned path, pipelined form for the C3 shape (one <= 32-bit key column without nulls, one 64-bit
+// value column).  gb_bin_kernel with no work at all in its row loop still needed 4.1 ms per 1 B rows
+// (2.9 TB/s): with one bulk-synchronous CTA per SM the column loads of a tile were requested only after
+// the previous tile's loads had been consumed.  Here the loads run TWO half-tiles (2 x 4096 rows, 2 x 12
+// registers per thread) ahead of the work and flow across the barriers, and the per-tile consensus barrier
+// for new keys is gone: a row whose key is not in the table yet inserts it on the spot (CAS on the key
+// word, then the dense id is published in the same 8-byte slot; concurrent lookups of that key spin for
+// the few cycles until it is).  Every slot remembers the tile it was born in, because a row that HITS a
+// key born in the current tile may still be the group's first row (warps are not ordered inside a tile).
+constexpr uint32_t kB32Unset = 0xFFFFu, kB32Overflow = 0xFFFEu;
+
+struct Raw32 {
+  uint4 k;
+  ulonglong2 va, vb;
+  uint16_t vm0;   // validity bytes, kept as loaded: combining them at request time would wait for the loads
+  uint8_t vm1;
+};
+
+// key -> dense group id (>= 0), or -2 when the CTA's table is full.  *fresh = the group was born in `tile`.
+__device__ __forceinline__ int b32_find_or_insert(BinSmem& S, uint32_t k, uint32_t tile, bool* fresh) {
+  uint32_t h = bin_hash32(k);
+  uint2 e = S.ktab[h];
+  if (e.x != k || (e.y & 0xFFFFu) >= kB32Overflow) {
+    // slow path: probe, insert, or wait for the inserting thread to publish the id
+#pragma unroll 1
+    for (int probe = 0; probe < 4 * kLocalProbe; ++probe) {
+      uint32_t cur = *reinterpret_cast<volatile uint32_t*>(&S.ktab[h].x);
+      if (cur == kEmpty32) {
+        if (*reinterpret_cast<const volatile uint32_t*>(&S.n_groups) >= uint32_t(kFastGroups)) return -2;
+        cur = atomicCAS(&S.ktab[h].x, kEmpty32, k);
+        if (cur == kEmpty32) {
+          const uint32_t g = atomicAdd(&S.n_groups, 1u);
+          const uint32_t y = (g < uint32_t(kFastGroups) ? g : kB32Overflow) | (tile << 16);
+          *reinterpret_cast<volatile uint32_t*>(&S.ktab[h].y) = y;
+          *fresh = true;
+          return g < uint32_t(kFastGroups) ? int(g) : -2;
+        }
+      }
+      if (cur == k) {
+        uint32_t y;
+        do {
+          y = *reinterpret_cast<volatile uint32_t*>(&S.ktab[h].y);
+        } while ((y & 0xFFFFu) == kB32Unset);
+        e.y = y;
+        break;
+      }
+      h = (h + 1) & uint32_t(kBinSlots - 1);
+      e.y = kB32Overflow;   // probe limit reached without finding the key: cannot be placed
+    }
+  }
+  const uint32_t g = e.y & 0xFFFFu;
+  *fresh = (e.y >> 16) == tile;
+  return g < uint32_t(kFastGroups) ? int(g) : -2;
+}
+
+__global__ void __launch_bounds__(kBinThreads, 1) gb_bin32_kernel(const __grid_constant__ GbArgs a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  BinSmem& S = *reinterpret_cast<BinSmem*>(smem);
+  const int t = threadIdx.x;
+  for (int i = t; i < kBinSlots; i += kBinThreads) S.ktab[i] = make_uint2(kEmpty32, kB32Unset);
+  S.sum[t] = 0;
+  S.mn[t] = ~uint64_t(0);
+  S.mx[t] = 0;
+  S.tcnt[t] = 0;
+  S.cnt[t] = 0;
+  S.nulls[t] = 0;
+  S.first[t] = 0xFFFFFFFFu;
+  if (t == 0) {
+    S.n_groups = 0;
+    S.new_groups = 0;
+    S.deferred = 0;
+  }
+  __syncthreads();
+  const int dom = a.s.aggs[0].dom;
+  bool want_minmax = false;
+  for (int j = 0; j < a.s.n_aggs; ++j)
+    if (a.s.aggs[j].kind == B200_HASH_MIN_MAX) want_minmax = true;
+  const int64_t begin = int64_t(blockIdx.x) * a.rows_per_block;
+  const int64_t end = min(a.n, begin + a.rows_per_block);   // a.n is a multiple of kBinTile here
+  uint64_t* zf = a.zf_scratch + size_t(blockIdx.x) * kFastGroups;
+  const uint32_t* kcol = reinterpret_cast<const uint32_t*>(a.keys[0].data);
+  const uint64_t* vcol = reinterpret_cast<const uint64_t*>(a.cols[0].data);
+  const uint8_t* vbytes = reinterpret_cast<const uint8_t*>(a.cols[0].vv.words);
+  const int64_t voff = a.cols[0].vv.bit_offset;
+
+  // half-tile h (4096 rows) of this CTA starts at row begin + h * kBinSubRows; this thread owns 4 rows of it
+  auto request = [&](Raw32& r, int64_t r0) {
+    if (r0 < end) {
+      r.k = *reinterpret_cast<const uint4*>(kcol + r0);
+      const ulonglong2* vp = reinterpret_cast<const ulonglong2*>(vcol + r0);
+      r.va = vp[0];
+      r.vb = vp[1];
+      if (vbytes) {
+        // r0 is a multiple of 4: its 4 validity bits never straddle more than two bytes
+        const int64_t byte = ((voff + r0) >> 3) & ~int64_t(1);
+        r.vm0 = __ldg(reinterpret_cast<const uint16_t*>(vbytes + byte));
+        r.vm1 = __ldg(vbytes + byte + 2);
+      }
+    }
+  };
+  // one half-tile of this thread's rows: lookup / insert, slot in the bin, rare side paths
+  auto work = [&](const Raw32& r, int64_t r0, uint32_t tile) {
+    if (a.dbg & 8) {   // timing experiment: loads only
+      if ((r.k.x ^ r.k.y ^ r.k.z ^ r.k.w ^ uint32_t(r.va.x ^ r.va.y ^ r.vb.x ^ r.vb.y) ^ r.vm0 ^ r.vm1) == 0x12345678u) S.deferred = 1;
+      return;
+    }
+    const uint32_t key[4] = {r.k.x, r.k.y, r.k.z, r.k.w};
+    const uint64_t vbits[4] = {r.va.x, r.va.y, r.vb.x, r.vb.y};
+    uint32_t vmask = 0xFu;
+    if (vbytes) {
+      const int64_t bit = voff + r0;
+      vmask = ((uint32_t(r.vm0) | (uint32_t(r.vm1) << 16)) >> (int(bit & 7) + 8 * int((bit >> 3) & 1))) & 0xFu;
+    }
+    int gid[4];
+    uint32_t fresh = 0, defer = 0, over = 0, zeros = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      bool f = false;
+      gid[i] = key[i] == kEmpty32 ? -2 : b32_find_or_insert(S, key[i], tile, &f);
+      if (f) fresh |= 1u << i;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int g = gid[i];
+      if (g < 0) {
+        defer |= 1u << i;
+        continue;
+      }
+      if ((vmask >> i) & 1u) {
+        const uint32_t rk = atomicAdd(&S.tcnt[g], 1u);
+        if (rk < uint32_t(kBinCap)) S.bins[rk * kFastGroups + g] = vbits[i];
+        else over |= 1u << i;
+        if ((uint32_t(vbits[i] >> 32) & 0x7FFFFFFFu) == 0) zeros |= 1u << i;   // candidate +-0.0
+      } else {
+        atomicAdd(&S.nulls[g], 1u);
+      }
+    }
+    fresh &= ~defer;
+    if (fresh) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if ((fresh >> i) & 1u) atomicMin(&S.first[gid[i]], uint32_t(r0 + i - begin));
+    }
+    if (zeros && want_minmax && dom == kFloat) {
+      // +-0.0 ties in hash_min_max: the earliest zero row decides the sign (see accumulate())
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if (((zeros >> i) & 1u) && (vbits[i] << 1) == 0)
+          atomic_min_checked(zf + gid[i], ((a.row_base + uint64_t(r0 + i)) << 1) | (vbits[i] >> 63));
+    }
+    if (defer) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if ((defer >> i) & 1u) atomicOr(a.defer_out + ((r0 + i) >> 5), 1u << ((r0 + i) & 31));
+      atomicAdd(&S.deferred, uint32_t(__popc(defer)));
+    }
+    if (over) {
+      // bin overflow (skewed keys): accumulate directly.  Counts: native 32-bit atomic; float sums: CAS loop
+      // (lanes may retry independently here: this path is already the slow one); extremes: checked atomics
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (!((over >> i) & 1u)) continue;
+        const int g = gid[i];
+        atomicAdd(&S.cnt[g], 1u);
+        if (dom == kFloat) {
+          unsigned long long* sp = reinterpret_cast<unsigned long long*>(&S.sum[g]);
+          unsigned long long o = *reinterpret_cast<volatile unsigned long long*>(sp), seen;
+          do {
+            seen = o;
+            o = atomicCAS(sp, seen, (unsigned long long)__double_as_longlong(__longlong_as_double(seen) + __longlong_as_double(vbits[i])));
+          } while (o != seen);
+        } else {
+          uint32_t* w = reinterpret_cast<uint32_t*>(&S.sum[g]);
+          const uint32_t lo = uint32_t(vbits[i]), hi = uint32_t(vbits[i] >> 32);
+          const uint32_t old_lo = atomicAdd(w, lo);
+          const uint32_t carry = (old_lo + lo) < old_lo ? 1u : 0u;
+          if (hi + carry) atomicAdd(w + 1, hi + carry);
+        }
+        if (want_minmax) {
+          uint64_t o;
+          bool use = true;
+          if (dom == kFloat) {
+            const double dv = __longlong_as_double(vbits[i]);
+            use = dv == dv;
+            o = ord_f64(dv);
+          } else {
+            o = dom == kSigned ? (vbits[i] ^ 0x8000000000000000ull) : vbits[i];
+          }
+          if (use) {
+            atomic_min_checked(&S.mn[g], o);
+            atomic_max_checked(&S.mx[g], o);
+          }
+        }
+      }
+    }
+  };
+
+  Raw32 ra, rb;
+  const int64_t mine = begin + int64_t(t) * kFastSub;
+  request(ra, mine);
+  request(rb, mine + kBinSubRows);
+  uint32_t tile = 0;
+#pragma unroll 1
+  for (int64_t base = begin; base < end; base += kBinTile, ++tile) {
+    const int64_t r0 = base + int64_t(t) * kFastSub;
+    {
+      const Raw32 cur = ra;
+      request(ra, r0 + 2 * kBinSubRows);
+      work(cur, r0, tile & 0xFFFFu);
+    }
+    {
+      const Raw32 cur = rb;
+      request(rb, r0 + 3 * kBinSubRows);
+      work(cur, r0 + kBinSubRows, tile & 0xFFFFu);
+    }
+    __syncthreads();
+    // ---- every thread reduces the bin of its own group with plain adds / compares
+    {
+      const int g = t;
+      const uint32_t c_all = S.tcnt[g];
+      if (c_all != 0) {
+        const uint32_t c = min(c_all, uint32_t(kBinCap));
+        S.tcnt[g] = 0;
+        S.cnt[g] += c;
+        const uint64_t* bin = S.bins + g;
+        if (dom == kFloat) {
+          const uint64_t omn = S.mn[g], omx = S.mx[g];
+          double s = 0.0;
+          double lo = omn == ~uint64_t(0) ? __longlong_as_double(0x7FF0000000000000ull) : unord_f64(omn);
+          double hi = omx == 0 ? __longlong_as_double(0xFFF0000000000000ull) : unord_f64(omx);
+#pragma unroll 4
+          for (uint32_t j = 0; j < c; ++j) {
+            const double v = __longlong_as_double(bin[j * kFastGroups]);
+            s += v;
+            if (v < lo || v > hi) {   // a NaN never compares true: it never wins (hash_aggregate.cc:672-673)
+              if (v < lo) lo = v;
+              if (v > hi) hi = v;
+            }
+          }
+          S.sum[g] = __double_as_longlong(__longlong_as_double(S.sum[g]) + s);
+          const uint64_t olo = ord_f64(lo), ohi = ord_f64(hi);
+          if (olo < omn) S.mn[g] = olo;
+          if (ohi > omx) S.mx[g] = ohi;
+        } else {
+          const uint64_t flip = dom == kSigned ? 0x8000000000000000ull : 0ull;
+          uint64_t s = 0, lo = ~uint64_t(0), hi = 0;
+#pragma unroll 2
+          for (uint32_t j = 0; j < c; ++j) {
+            const uint64_t v = bin[j * kFastGroups];
+            s += v;
+            const uint64_t ov = v ^ flip;
+            lo = ov < lo ? ov : lo;
+            hi = ov > hi ? ov : hi;
+          }
+          S.sum[g] += s;
+          if (lo < S.mn[g]) S.mn[g] = lo;
+          if (hi > S.mx[g]) S.mx[g] = hi;
+        }
+      }
+    }
+    __syncthreads();   // the bins and their counters are free again
+  }
+  // ---- flush: every group of this CTA is folded into the global table
+  for (int slot = t; slot < kBinSlots; slot += kBinThreads) {
+    const uint2 e = S.ktab[slot];
+    if (e.x == kEmpty32) continue;
+    const uint32_t g = e.y & 0xFFFFu;
+    if (g >= uint32_t(kFastGroups)) continue;   // overflow marker
+    const uint64_t key = e.x;
+    bool claimed;
+    uint64_t slot_index;
+    char* gs = global_slot(a.t, a.s.stride, key, 0, true, &claimed, &slot_index);
+    if (!gs) {
       gs = a.spill + size_t(atomicAdd(a.counters + 5, 1u)) * a.s.stride;
       init_slot(gs, a.s);
       reinterpret_cast<uint64_t*>(gs)[0] = key;
@@ -1531,23 +2304,28 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
     if (fast && round == 0) {
       // full 2048-row tiles go through the fast kernel; the ragged tail and every row it defers
       // (special keys, keys that found no room in a CTA's table) are taken by the generic kernel
-      const int64_t n_full = n / kFastTile * kFastTile;
+      // v2 (binned, one 1024-thread CTA per SM) unless B200_GB_V1 / B200_GB_DIRECT ask for the earlier kernels
+      static const bool binned = getenv("B200_GB_V1") == nullptr && getenv("B200_GB_DIRECT") == nullptr;
+      const int64_t tile_rows = binned ? kBinTile : kFastTile;
+      const int64_t n_full = n / tile_rows * tile_rows;
       if (n_full < n) B200_CUDA(ctx, cudaMemsetAsync(defer_a + n_full / 32, 0xFF, (words - size_t(n_full / 32)) * 4, ctx->stream));
       uint32_t fast_deferred = 0;
       if (n_full > 0) {
-        const int max_blocks = ctx->num_sms * 2;
+        const int max_blocks = binned ? ctx->num_sms : ctx->num_sms * 2;
         int64_t rpb = (n_full + max_blocks - 1) / max_blocks;
-        rpb = (rpb + kFastTile - 1) / kFastTile * kFastTile;
+        rpb = (rpb + tile_rows - 1) / tile_rows * tile_rows;
         const int grid = int((n_full + rpb - 1) / rpb);
         B200_RETURN_NOT_OK(grow_table(gb, 2 * std::max<uint64_t>(likely_groups, 32 * 1024)));
         a.t = gb->table;
 
         a.local_slots = kFastSlots32;
+        static const int dbg = getenv("B200_GB_DBG") ? atoi(getenv("B200_GB_DBG")) : 0;
+        a.dbg = dbg;
         a.rows_per_block = int(rpb);
         a.n = n_full;
         a.zf_scratch = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(gb->tmp) + 2 * b200_align_up(words * 4, 256) + claimed_bytes + 256);
         B200_CUDA(ctx, cudaMemsetAsync(a.zf_scratch, 0xFF, size_t(grid) * kFastGroups * sizeof(uint64_t), ctx->stream));
-        const int smem = int(sizeof(FastSmem));
+        const int smem = binned ? int(sizeof(BinSmem)) : int(sizeof(FastSmem));
         const bool k32 = a.s.n_keys == 1 && a.keys[0].nbits == 32 && !a.keys[0].vv.words && (reinterpret_cast<uintptr_t>(a.keys[0].data) & 15) == 0;
         const bool k64 = a.s.n_keys == 1 && a.keys[0].nbits == 64 && !a.keys[0].vv.words && (reinterpret_cast<uintptr_t>(a.keys[0].data) & 15) == 0;
         const bool vfast = a.n_cols == 1 && b200_type_bits(a.cols[0].type) == 64 && (reinterpret_cast<uintptr_t>(a.cols[0].data) & 15) == 0;
@@ -1566,15 +2344,27 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
           B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
           B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<2, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
           B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<2, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+          const int bx = int(sizeof(BinSmem));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_bin_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_bin_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_bin_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_bin_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_bin_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_bin_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bx));
+          B200_CUDA(ctx, cudaFuncSetAttribute(gb_bin32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bx));
           fattr = true;
         }
         static const bool direct = getenv("B200_GB_DIRECT") != nullptr;
 #define B200_FAST_LAUNCH(KM, VF) \
   do {                                                                                                              \
-    if (direct) B200_TIMED(ctx, "groupby_consume", (gb_fast_kernel<KM, VF, true><<<grid, kFastThreads, smem, ctx->stream>>>(a)));  \
+    if (binned) B200_TIMED(ctx, "groupby_consume", (gb_bin_kernel<KM, VF><<<grid, kBinThreads, smem, ctx->stream>>>(a)));          \
+    else if (direct) B200_TIMED(ctx, "groupby_consume", (gb_fast_kernel<KM, VF, true><<<grid, kFastThreads, smem, ctx->stream>>>(a)));  \
     else B200_TIMED(ctx, "groupby_consume", (gb_fast_kernel<KM, VF, false><<<grid, kFastThreads, smem, ctx->stream>>>(a)));        \
   } while (0)
-        if (k32) { if (vfast) B200_FAST_LAUNCH(1, true); else B200_FAST_LAUNCH(1, false); }
+        static const bool pipelined = getenv("B200_GB_V2") == nullptr;
+        if (binned && pipelined && k32 && vfast && a.keys[0].nbits == 32) {
+          B200_TIMED(ctx, "groupby_consume", (gb_bin32_kernel<<<grid, kBinThreads, smem, ctx->stream>>>(a)));
+        } else if (k32) { if (vfast) B200_FAST_LAUNCH(1, true); else B200_FAST_LAUNCH(1, false); }
         else if (k64) { if (vfast) B200_FAST_LAUNCH(2, true); else B200_FAST_LAUNCH(2, false); }
         else { if (vfast) B200_FAST_LAUNCH(0, true); else B200_FAST_LAUNCH(0, false); }
 #undef B200_FAST_LAUNCH
