@@ -161,6 +161,23 @@ class FilterPlan:
         return FilterOutput(col, has_validity)
 
 
+CMP_OPS = {"equal": 0, "not_equal": 1, "greater": 2, "greater_equal": 3, "less": 4, "less_equal": 5}
+
+
+def compare_scalar(ctx: Context, values: Column, op: str, scalar) -> Column:
+    """== CallFunction(op, {values, scalar}) of compute/kernels/scalar_compare.cc on a device column:
+    boolean Column whose validity is the input's (shared buffer)."""
+    n = values.length
+    out = ctx.empty((n + 31) // 32 * 4 + 8)
+    sc = np.array([scalar], dtype=NP_OF[values.type])
+    v = values.desc()
+    ctx.check(lib().b200_compare_scalar(ctx._h, C.byref(v), C.c_int(CMP_OPS[op]), C.c_void_p(sc.ctypes.data),
+                                        C.c_void_p(out.data_ptr())))
+    if values.validity is not None and values.offset != 0:
+        raise B200Error(10, "compare_scalar: sliced nullable input (validity cannot be shared at offset 0)")
+    return Column(BOOL, out, values.validity, n, 0, values.null_count if values.validity is not None else 0)
+
+
 def filter_count(ctx: Context, mask: Column, null_selection: int = 0) -> int:
     m = mask.desc()
     n = C.c_int64(0)

@@ -138,6 +138,34 @@ def SortIndices(values: Column, order: int = ASCENDING, ctx: Optional[capi.Conte
     return h.view(np.uint64)
 
 
+Q1_SHIPDATE_CUTOFF = 10471   # 1998-09-02 as date32 (TPC-H Q1: l_shipdate <= date '1998-12-01' - 90 days)
+
+
+def q1_aggregates():
+    """The Q1 outputs that need no arithmetic: argument index into
+    (quantity, extendedprice, discount) and the aggregate applied to it."""
+    from . import columns as cols
+    return [(0, AggSpec(cols.HASH_SUM)), (1, AggSpec(cols.HASH_SUM)), (0, AggSpec(cols.HASH_MEAN)),
+            (1, AggSpec(cols.HASH_MEAN)), (2, AggSpec(cols.HASH_MEAN)), (0, AggSpec(cols.HASH_COUNT))]
+
+
+def Q1Pipeline(shipdate: Column, returnflag: Column, linestatus: Column, measures: Sequence[Column],
+               ctx: Optional[capi.Context] = None):
+    """TPC-H Q1-shaped pipeline through the public operations, unfused (config C5):
+        mask = less_equal(shipdate, cutoff)                   scalar_compare.cc
+        c'   = Filter(c, mask) for every used column          one plan shared by all columns
+                                                              (FilterRecordBatch, vector_selection.cc:1776-1866)
+        GroupBy(measures', keys = (returnflag', linestatus'), q1_aggregates())
+    Device columns in, device GroupByOutput out."""
+    ctx = ctx or default_context()
+    mask = capi.compare_scalar(ctx, shipdate, "less_equal", Q1_SHIPDATE_CUTOFF)
+    plan = capi.FilterPlan(ctx, mask, DROP, sync=True)
+    rf, ls = plan.apply(returnflag).col, plan.apply(linestatus).col
+    ms = [plan.apply(m).col for m in measures]
+    specs = q1_aggregates()
+    return capi.group_by(ctx, [rf, ls], [a for _, a in specs], [ms[i] for i, _ in specs], expected_groups=8)
+
+
 class GroupByResult:
     """Image of GroupBy's StructArray (hash_aggregate.cc:962-965): one entry per aggregate (a list
     of (values, valid) pairs: two for hash_min_max) then the key columns, `num_groups` long."""

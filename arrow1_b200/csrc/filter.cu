@@ -312,6 +312,58 @@ int launch_apply(b200_ctx* ctx, const ApplyArgs& a, int64_t n_tiles) {
   return B200_OK;
 }
 
+// ---- mask producer: values[i] OP scalar -> boolean bitmap (compute/kernels/scalar_compare.cc) -----------
+// One row per thread; the warp's 32 predicate bits are one ballot = one bitmap word (no atomics, no
+// shared memory).  Arrow semantics: C++ comparison operators on the physical values (a NaN compares
+// false except under not_equal); null-ness is not computed here: the output shares the input's validity.
+enum { kCmpEq = 0, kCmpNe = 1, kCmpGt = 2, kCmpGe = 3, kCmpLt = 4, kCmpLe = 5 };
+
+template <typename T>
+__device__ __forceinline__ bool cmp_apply(T v, T s, int op) {
+  switch (op) {
+    case kCmpEq: return v == s;
+    case kCmpNe: return v != s;
+    case kCmpGt: return v > s;
+    case kCmpGe: return v >= s;
+    case kCmpLt: return v < s;
+    default: return v <= s;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) compare_scalar_kernel(const T* __restrict__ values, int64_t n, T scalar, int op,
+                                                            uint32_t* __restrict__ out) {
+  // 4 words (128 rows) per warp iteration keeps enough loads in flight for narrow types
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t base = warp * 128;
+  if (base >= n) return;
+  T v[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int64_t row = base + k * 32 + lane;
+    v[k] = row < n ? values[row] : T(0);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int64_t row = base + k * 32 + lane;
+    const unsigned word = __ballot_sync(0xffffffffu, row < n && cmp_apply<T>(v[k], scalar, op));
+    if (lane == 0 && base + k * 32 < n) out[(base >> 5) + k] = word;
+  }
+}
+
+template <typename T>
+int launch_compare(b200_ctx* ctx, const b200_col* values, const void* scalar, int op, void* out) {
+  T s;
+  memcpy(&s, scalar, sizeof(T));
+  const int64_t n = values->length;
+  const T* data = reinterpret_cast<const T*>(values->data) + values->offset;
+  const int64_t warps = (n + 127) / 128;
+  const unsigned grid = unsigned((warps * 32 + 255) / 256);
+  B200_TIMED(ctx, "compare_scalar", (compare_scalar_kernel<T><<<grid, 256, 0, ctx->stream>>>(data, n, s, op, reinterpret_cast<uint32_t*>(out))));
+  return B200_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -349,6 +401,30 @@ int b200_filter_plan(b200_ctx* ctx, const b200_col* mask, int null_selection, vo
     *out_len = ctx->host_words[0];
   }
   return B200_OK;
+}
+
+int b200_compare_scalar(b200_ctx* ctx, const b200_col* values, int op, const void* scalar, void* out_bitmap) {
+  if (!ctx) return B200_INVALID;
+  if (!values || !scalar) return b200_fail(ctx, B200_INVALID, "compare_scalar: null argument");
+  if (op < kCmpEq || op > kCmpLe) return b200_fail(ctx, B200_INVALID, "compare_scalar: bad operator %d", op);
+  if (values->length < 0 || values->offset < 0) return b200_fail(ctx, B200_INVALID, "compare_scalar: negative length/offset");
+  if (values->length == 0) return B200_OK;
+  if (!values->data || !out_bitmap) return b200_fail(ctx, B200_INVALID, "compare_scalar: null buffer");
+  switch (values->type) {
+    case B200_UINT8: return launch_compare<uint8_t>(ctx, values, scalar, op, out_bitmap);
+    case B200_INT8: return launch_compare<int8_t>(ctx, values, scalar, op, out_bitmap);
+    case B200_UINT16: return launch_compare<uint16_t>(ctx, values, scalar, op, out_bitmap);
+    case B200_INT16: return launch_compare<int16_t>(ctx, values, scalar, op, out_bitmap);
+    case B200_UINT32: return launch_compare<uint32_t>(ctx, values, scalar, op, out_bitmap);
+    case B200_INT32: return launch_compare<int32_t>(ctx, values, scalar, op, out_bitmap);
+    case B200_UINT64: return launch_compare<uint64_t>(ctx, values, scalar, op, out_bitmap);
+    case B200_INT64: return launch_compare<int64_t>(ctx, values, scalar, op, out_bitmap);
+    case B200_FLOAT: return launch_compare<float>(ctx, values, scalar, op, out_bitmap);
+    case B200_DOUBLE: return launch_compare<double>(ctx, values, scalar, op, out_bitmap);
+    default: break;
+  }
+  // the reference has boolean comparisons too (scalar_compare.cc); not on the Q1 path
+  return b200_fail(ctx, B200_NOT_IMPLEMENTED, "compare_scalar: no kernel for type %d", values->type);
 }
 
 int b200_filter_count(b200_ctx* ctx, const b200_col* mask, int null_selection, int64_t* out_len) {

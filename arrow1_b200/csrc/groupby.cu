@@ -602,10 +602,15 @@ __global__ void __launch_bounds__(kFastThreads, 2) gb_fast_kernel(const __grid_c
     S.deferred = 0;
   }
   __syncthreads();
-  const int dom = a.s.aggs[0].dom;
+  // this launch serves the aggregates whose argument is column 0 (col == 0); a multi-column group-by runs
+  // the kernel once per distinct argument column, the others carry col == -1
+  int dom = kSigned;
   bool want_minmax = false;
-  for (int j = 0; j < a.s.n_aggs; ++j)
-    if (a.s.aggs[j].kind == B200_HASH_MIN_MAX) want_minmax = true;
+  for (int j = a.s.n_aggs - 1; j >= 0; --j)
+    if (a.s.aggs[j].col == 0) {
+      dom = a.s.aggs[j].dom;
+      if (a.s.aggs[j].kind == B200_HASH_MIN_MAX) want_minmax = true;
+    }
   const int64_t begin = int64_t(blockIdx.x) * a.rows_per_block;
   const int64_t end = min(a.n, begin + a.rows_per_block);   // a.n is a multiple of kFastTile here
   uint64_t* zf = a.zf_scratch + size_t(blockIdx.x) * kFastGroups;
@@ -920,6 +925,7 @@ __global__ void __launch_bounds__(kFastThreads, 2) gb_fast_kernel(const __grid_c
     if (S.first[g] != 0xFFFFFFFFu) atomic_min_checked(reinterpret_cast<uint64_t*>(gs) + 1, a.row_base + uint64_t(begin) + S.first[g]);
     for (int j = 0; j < a.s.n_aggs; ++j) {
       const GbAgg& ag = a.s.aggs[j];
+      if (ag.col != 0) continue;
       uint64_t* d = reinterpret_cast<uint64_t*>(gs + ag.off);
       if (ag.kind == B200_HASH_COUNT) {
         const uint64_t c = ag.option ? nulls : cnt;
@@ -1067,10 +1073,15 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin_kernel(const __grid_con
     S.deferred = 0;
   }
   __syncthreads();
-  const int dom = a.s.aggs[0].dom;
+  // this launch serves the aggregates whose argument is column 0 (col == 0); a multi-column group-by runs
+  // the kernel once per distinct argument column, the others carry col == -1
+  int dom = kSigned;
   bool want_minmax = false;
-  for (int j = 0; j < a.s.n_aggs; ++j)
-    if (a.s.aggs[j].kind == B200_HASH_MIN_MAX) want_minmax = true;
+  for (int j = a.s.n_aggs - 1; j >= 0; --j)
+    if (a.s.aggs[j].col == 0) {
+      dom = a.s.aggs[j].dom;
+      if (a.s.aggs[j].kind == B200_HASH_MIN_MAX) want_minmax = true;
+    }
   const int64_t begin = int64_t(blockIdx.x) * a.rows_per_block;
   const int64_t end = min(a.n, begin + a.rows_per_block);   // a.n is a multiple of kBinTile here
   uint64_t* zf = a.zf_scratch + size_t(blockIdx.x) * kFastGroups;
@@ -1381,6 +1392,7 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin_kernel(const __grid_con
     if (S.first[g] != 0xFFFFFFFFu) atomic_min_checked(reinterpret_cast<uint64_t*>(gs) + 1, a.row_base + uint64_t(begin) + S.first[g]);
     for (int j = 0; j < a.s.n_aggs; ++j) {
       const GbAgg& ag = a.s.aggs[j];
+      if (ag.col != 0) continue;
       uint64_t* d = reinterpret_cast<uint64_t*>(gs + ag.off);
       if (ag.kind == B200_HASH_COUNT) {
         const uint64_t c = ag.option ? nulls : cnt;
@@ -1480,10 +1492,15 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin32_kernel(const __grid_c
     S.deferred = 0;
   }
   __syncthreads();
-  const int dom = a.s.aggs[0].dom;
+  // this launch serves the aggregates whose argument is column 0 (col == 0); a multi-column group-by runs
+  // the kernel once per distinct argument column, the others carry col == -1
+  int dom = kSigned;
   bool want_minmax = false;
-  for (int j = 0; j < a.s.n_aggs; ++j)
-    if (a.s.aggs[j].kind == B200_HASH_MIN_MAX) want_minmax = true;
+  for (int j = a.s.n_aggs - 1; j >= 0; --j)
+    if (a.s.aggs[j].col == 0) {
+      dom = a.s.aggs[j].dom;
+      if (a.s.aggs[j].kind == B200_HASH_MIN_MAX) want_minmax = true;
+    }
   const int64_t begin = int64_t(blockIdx.x) * a.rows_per_block;
   const int64_t end = min(a.n, begin + a.rows_per_block);   // a.n is a multiple of kBinTile here
   uint64_t* zf = a.zf_scratch + size_t(blockIdx.x) * kFastGroups;
@@ -1691,6 +1708,7 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin32_kernel(const __grid_c
     if (S.first[g] != 0xFFFFFFFFu) atomic_min_checked(reinterpret_cast<uint64_t*>(gs) + 1, a.row_base + uint64_t(begin) + S.first[g]);
     for (int j = 0; j < a.s.n_aggs; ++j) {
       const GbAgg& ag = a.s.aggs[j];
+      if (ag.col != 0) continue;
       uint64_t* d = reinterpret_cast<uint64_t*>(gs + ag.off);
       if (ag.kind == B200_HASH_COUNT) {
         const uint64_t c = ag.option ? nulls : cnt;
@@ -1711,6 +1729,176 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin32_kernel(const __grid_c
     }
   }
   __syncthreads();
+  if (t == 0) {
+    if (S.new_groups) atomicAdd(a.counters + 0, S.new_groups);
+    if (S.deferred) atomicAdd(a.counters + 1, S.deferred);
+  }
+}
+
+// ---- tiny-cardinality path (<= 8 groups: the Q1 shape) ------------------------------------------
+// With a handful of groups every shared-memory counter or bin is hammered by the whole CTA (measured on
+// Q1's 4 groups: 24 ms per column with the counting-sort kernel, 180 ms with the binned one).  Here nothing
+// is shared while rows stream: every thread owns a private (sum, count) accumulator per group in shared
+// memory, laid out [group][thread] so a warp's accesses are conflict-free, and updates them with plain
+// loads / adds / stores.  Keys are matched against a <= 8-entry CTA table (linear scan, all lanes read the
+// same word: a broadcast; the table is re-read into registers once per 4 rows), new keys are claimed with one CAS.  Rare events (null value, first row of a
+// group in a thread) use shared atomics.  At the end the thread-private partials are tree-reduced per
+// group and folded into the global table.  hash_sum / hash_mean / hash_count only (no min_max state).
+constexpr int kTinyGroups = 8;
+constexpr int kTinyThreads = 256;
+
+struct TinySmem {
+  uint64_t sum[kTinyGroups][kTinyThreads];
+  uint32_t cnt[kTinyGroups][kTinyThreads];
+  uint64_t keys[kTinyGroups];
+  uint32_t nulls[kTinyGroups];
+  uint32_t first[kTinyGroups];
+  uint64_t red_sum[kTinyThreads / 32];
+  uint32_t red_cnt[kTinyThreads / 32];
+  uint32_t new_groups, deferred;
+};
+
+__global__ void __launch_bounds__(kTinyThreads, 4) gb_tiny_kernel(const __grid_constant__ GbArgs a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  TinySmem& S = *reinterpret_cast<TinySmem*>(smem);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+#pragma unroll
+  for (int g = 0; g < kTinyGroups; ++g) {
+    S.sum[g][t] = 0;
+    S.cnt[g][t] = 0;
+  }
+  if (t < kTinyGroups) {
+    S.keys[t] = kEmpty;
+    S.nulls[t] = 0;
+    S.first[t] = 0xFFFFFFFFu;
+  }
+  if (t == 0) {
+    S.new_groups = 0;
+    S.deferred = 0;
+  }
+  __syncthreads();
+  int dom = kSigned;
+  for (int j = a.s.n_aggs - 1; j >= 0; --j)
+    if (a.s.aggs[j].col == 0) dom = a.s.aggs[j].dom;
+  const int64_t begin = int64_t(blockIdx.x) * a.rows_per_block;
+  const int64_t end = min(a.n, begin + a.rows_per_block);
+  uint32_t seen = 0;   // groups this thread has met (their first row in this thread is already recorded)
+  constexpr int kTinyUnroll = 4;   // rows in flight per thread: all loads of an iteration are issued first
+#pragma unroll 1
+  for (int64_t row0 = begin + t; row0 < end; row0 += kTinyUnroll * kTinyThreads) {
+    uint64_t keyv[kTinyUnroll];
+    Val val[kTinyUnroll];
+    int spec[kTinyUnroll];
+#pragma unroll
+    for (int u = 0; u < kTinyUnroll; ++u) {
+      const int64_t row = row0 + u * kTinyThreads;
+      spec[u] = 1;
+      keyv[u] = 0;
+      val[u].bits = 0;
+      val[u].valid = false;
+      if (row < end) {
+        keyv[u] = load_key(a, row, &spec[u]);
+        val[u] = load_val(a.cols[0], row);
+      }
+    }
+    uint64_t tk[kTinyGroups];   // the CTA's key table, as of now (entries only ever go from EMPTY to a key)
+#pragma unroll
+    for (int q = 0; q < kTinyGroups; ++q) tk[q] = *reinterpret_cast<const volatile uint64_t*>(&S.keys[q]);
+#pragma unroll
+    for (int u = 0; u < kTinyUnroll; ++u) {
+      const int64_t row = row0 + u * kTinyThreads;
+      if (row >= end) break;
+      const uint64_t key = keyv[u];
+      int g = -1;
+      if (!spec[u]) {
+#pragma unroll
+        for (int q = 0; q < kTinyGroups; ++q)
+          if (tk[q] == key) g = q;
+        if (g < 0) {   // not in the snapshot: claim the first free entry, or find the key claimed meanwhile
+#pragma unroll 1
+          for (int q = 0; q < kTinyGroups && g < 0; ++q) {
+            const unsigned long long old = atomicCAS(reinterpret_cast<unsigned long long*>(&S.keys[q]), (unsigned long long)kEmpty, (unsigned long long)key);
+            if (old == kEmpty || old == key) g = q;
+          }
+#pragma unroll
+          for (int q = 0; q < kTinyGroups; ++q) tk[q] = *reinterpret_cast<const volatile uint64_t*>(&S.keys[q]);
+        }
+      }
+      if (g < 0) {   // special key or more than 8 groups in this CTA: the generic kernel takes the row
+        atomicOr(a.defer_out + (row >> 5), 1u << (row & 31));
+        atomicAdd(&S.deferred, 1u);
+        continue;
+      }
+      if (!((seen >> g) & 1u)) {
+        seen |= 1u << g;
+        atomicMin(&S.first[g], uint32_t(row - begin));   // rows of a thread come in increasing order
+      }
+      if (val[u].valid) {
+        if (dom == kFloat) S.sum[g][t] = __double_as_longlong(__longlong_as_double(S.sum[g][t]) + __longlong_as_double(val[u].bits));
+        else S.sum[g][t] += val[u].bits;
+        S.cnt[g][t] += 1;
+      } else {
+        atomicAdd(&S.nulls[g], 1u);
+      }
+    }
+  }
+  __syncthreads();
+  // ---- per group: tree reduction of the thread-private partials, then one thread folds it into the table
+  for (int g = 0; g < kTinyGroups; ++g) {
+    const uint64_t key = S.keys[g];
+    if (key == kEmpty) break;   // entries fill in order
+    uint64_t sv = S.sum[g][t];
+    uint32_t cv = S.cnt[g][t];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      const uint64_t os = __shfl_down_sync(0xffffffffu, sv, d);
+      const uint32_t oc = __shfl_down_sync(0xffffffffu, cv, d);
+      if (dom == kFloat) sv = __double_as_longlong(__longlong_as_double(sv) + __longlong_as_double(os));
+      else sv += os;
+      cv += oc;
+    }
+    if (lane == 0) {
+      S.red_sum[warp] = sv;
+      S.red_cnt[warp] = cv;
+    }
+    __syncthreads();
+    if (t == 0) {
+      uint64_t ts = S.red_sum[0];
+      uint64_t tc = S.red_cnt[0];
+      for (int w = 1; w < kTinyThreads / 32; ++w) {
+        if (dom == kFloat) ts = __double_as_longlong(__longlong_as_double(ts) + __longlong_as_double(S.red_sum[w]));
+        else ts += S.red_sum[w];
+        tc += S.red_cnt[w];
+      }
+      bool claimed;
+      uint64_t slot_index;
+      char* gs = global_slot(a.t, a.s.stride, key, 0, true, &claimed, &slot_index);
+      if (!gs) {
+        gs = a.spill + size_t(atomicAdd(a.counters + 5, 1u)) * a.s.stride;
+        init_slot(gs, a.s);
+        reinterpret_cast<uint64_t*>(gs)[0] = key;
+        reinterpret_cast<uint64_t*>(gs)[a.s.stride / 8 - 1] = 0;
+        claimed = false;
+      }
+      if (claimed) S.new_groups += 1;
+      const uint64_t nulls = S.nulls[g];
+      if (S.first[g] != 0xFFFFFFFFu) atomic_min_checked(reinterpret_cast<uint64_t*>(gs) + 1, a.row_base + uint64_t(begin) + S.first[g]);
+      for (int j = 0; j < a.s.n_aggs; ++j) {
+        const GbAgg& ag = a.s.aggs[j];
+        if (ag.col != 0) continue;
+        uint64_t* d = reinterpret_cast<uint64_t*>(gs + ag.off);
+        if (ag.kind == B200_HASH_COUNT) {
+          const uint64_t c = ag.option ? nulls : tc;
+          if (c) atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)c);
+        } else if (tc) {   // hash_sum / hash_mean (this path is not chosen for hash_min_max)
+          if (ag.dom == kFloat) atomicAdd(reinterpret_cast<double*>(d), __longlong_as_double(ts));
+          else atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)ts);
+          atomicAdd(reinterpret_cast<unsigned long long*>(d + 1), (unsigned long long)tc);
+        }
+      }
+    }
+    __syncthreads();
+  }
   if (t == 0) {
     if (S.new_groups) atomicAdd(a.counters + 0, S.new_groups);
     if (S.deferred) atomicAdd(a.counters + 1, S.deferred);
@@ -2301,11 +2489,52 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
   const bool fast = a.mode == kModeFused && a.n_cols == 1 && likely_groups <= uint64_t(kFastMaxGroupsHint) && !gb->fast_disabled && !a.row_ids;
   for (int round = 0; round < 8; ++round) {
     a.t = gb->table;
+    bool tiny = false;
+    if (fast && round == 0 && likely_groups > 0 && likely_groups <= uint64_t(kTinyGroups)) {
+      tiny = true;
+      for (int j = 0; j < a.s.n_aggs; ++j)
+        if (a.s.aggs[j].col == 0 && a.s.aggs[j].kind == B200_HASH_MIN_MAX) tiny = false;
+    }
+    if (tiny) {
+      // <= 8 groups, sums / means / counts: thread-private accumulators (gb_tiny_kernel); rows it defers
+      // (special keys, a 9th group) are picked up by the generic kernel below
+      const int grid = int(std::min<int64_t>(int64_t(ctx->num_sms) * 4, (n + 4095) / 4096));
+      int64_t rpb = (n + grid - 1) / grid;
+      rpb = (rpb + 31) / 32 * 32;
+      B200_RETURN_NOT_OK(grow_table(gb, 2 * std::max<uint64_t>(likely_groups, 32 * 1024)));
+      a.t = gb->table;
+      a.rows_per_block = int(rpb);
+      static bool tattr = false;
+      if (!tattr) {
+        B200_CUDA(ctx, cudaFuncSetAttribute(gb_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(TinySmem))));
+        tattr = true;
+      }
+      B200_TIMED(ctx, "groupby_consume", (gb_tiny_kernel<<<grid, kTinyThreads, int(sizeof(TinySmem)), ctx->stream>>>(a)));
+      uint32_t c[4];
+      B200_RETURN_NOT_OK(read_counters(gb, c));
+      const uint32_t tiny_deferred = c[1];
+      B200_RETURN_NOT_OK(import_spilled(gb, a.spill));
+      if (uint64_t(gb->groups) > uint64_t(kFastMaxGroupsHint)) gb->fast_disabled = true;
+      if (tiny_deferred == 0) {
+        if (uint64_t(gb->groups) * 2 > gb->table.cap) B200_RETURN_NOT_OK(grow_table(gb, uint64_t(gb->groups) * 4));
+        return B200_OK;
+      }
+      if (uint64_t(gb->groups) + tiny_deferred > gb->table.cap / 2) B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + tiny_deferred)));
+      a.defer_in = defer_a;
+      a.defer_out = defer_b;
+      B200_CUDA(ctx, cudaMemsetAsync(defer_b, 0, words * 4, ctx->stream));
+      B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 1, 0, sizeof(uint32_t), ctx->stream));
+      continue;
+    }
     if (fast && round == 0) {
       // full 2048-row tiles go through the fast kernel; the ragged tail and every row it defers
       // (special keys, keys that found no room in a CTA's table) are taken by the generic kernel
       // v2 (binned, one 1024-thread CTA per SM) unless B200_GB_V1 / B200_GB_DIRECT ask for the earlier kernels
-      static const bool binned = getenv("B200_GB_V1") == nullptr && getenv("B200_GB_DIRECT") == nullptr;
+      // The binned kernels want many groups: a group may hold kBinCap values per 8192-row tile before rows
+      // take the slow overflow path, so below ~512 expected groups (>= 16 rows per group per tile) the
+      // counting-sort kernel, whose bins are sized exactly by a scan, is the right one.
+      static const bool binned_ok = getenv("B200_GB_V1") == nullptr && getenv("B200_GB_DIRECT") == nullptr;
+      const bool binned = binned_ok && likely_groups * kBinCap >= uint64_t(kBinTile);
       const int64_t tile_rows = binned ? kBinTile : kFastTile;
       const int64_t n_full = n / tile_rows * tile_rows;
       if (n_full < n) B200_CUDA(ctx, cudaMemsetAsync(defer_a + n_full / 32, 0xFF, (words - size_t(n_full / 32)) * 4, ctx->stream));
@@ -2559,6 +2788,21 @@ static int groupby_consume_impl(b200_groupby* gb, const b200_col* keys, const b2
   a.mode = kModeFused;
   a.row_base = row_base;
   a.row_ids = row_ids;
+  // Several distinct argument columns at low cardinality (the Q1 shape): aggregates over different columns
+  // are independent, so the batch is consumed once per column with the binned single-column kernel — the
+  // key columns are re-read (2 B/row for Q1) instead of funnelling every column's float sums through CAS
+  // loops on a handful of shared-memory slots (measured 92 ms vs 3 x ~5 ms at 600 M rows, 4 groups).
+  const uint64_t likely = std::max<uint64_t>(gb->groups, gb->expected);
+  if (a.n_cols > 1 && !row_ids && likely > 0 && likely <= uint64_t(kFastMaxGroupsHint) && !gb->fast_disabled && a.n >= kBinTile) {
+    for (int c = 0; c < a.n_cols; ++c) {
+      GbArgs b = a;
+      b.n_cols = 1;
+      b.cols[0] = a.cols[c];
+      for (int j = 0; j < b.s.n_aggs; ++j) b.s.aggs[j].col = a.s.aggs[j].col == c ? 0 : -1;
+      B200_RETURN_NOT_OK(run_consume(gb, b));
+    }
+    return B200_OK;
+  }
   return run_consume(gb, a);
 }
 

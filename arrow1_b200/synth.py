@@ -184,3 +184,44 @@ class Gen:
         vals = self._chunks(start, n, lambda s, m: u_np(10, s, m) * 1e14, lambda s, m: u_t(10, s, m, self.device) * 1e14,
                             np.float64, None if self.device is None else torch.float64)
         return self._wrap(cols.INT64, keys, None, n, 0), self._wrap(cols.DOUBLE, vals, None, n, 0)
+
+    # ---- C5: Q1-shaped lineitem: shipdate date32 in [8036, 10561] seed 12; returnflag /
+    # linestatus as uint8 derived from it (seed 13 picks 'A' or 'R'); quantity seed 14, extendedprice seed 15,
+    # discount seed 16; all float64, no nulls
+    def q1_lineitem(self, n, start=0):
+        import torch
+        dev = self.device
+        i32 = None if dev is None else torch.int32
+        u8 = None if dev is None else torch.uint8
+        f64 = None if dev is None else torch.float64
+
+        def ship_np(s, m):
+            return (8036 + ((r_np(12, s, m) >> np.uint64(20)) % np.uint64(2526))).astype(np.int32)
+
+        def ship_t(s, m):
+            return (8036 + _lsr(r_t(12, s, m, dev), 20) % 2526).to(torch.int32)
+
+        ship = self._chunks(start, n, ship_np, ship_t, np.int32, i32)
+
+        def rf_np(s, m):
+            sd = ship_np(s, m)
+            ar = np.where((r_np(13, s, m) & np.uint64(1)) != 0, 65, 82)
+            return np.where(sd > 9268, 78, ar).astype(np.uint8)
+
+        def rf_t(s, m):
+            sd = ship_t(s, m)
+            ar = torch.where((r_t(13, s, m, dev) & 1) != 0, 65, 82)
+            return torch.where(sd > 9268, 78, ar).to(torch.uint8)
+
+        rflag = self._chunks(start, n, rf_np, rf_t, np.uint8, u8)
+        lstat = self._chunks(start, n, lambda s, m: np.where(ship_np(s, m) <= 9298, 70, 79).astype(np.uint8),
+                             lambda s, m: torch.where(ship_t(s, m) <= 9298, 70, 79).to(torch.uint8), np.uint8, u8)
+        qty = self._chunks(start, n, lambda s, m: (1 + (r_np(14, s, m) >> np.uint64(20)) % np.uint64(50)).astype(np.float64),
+                           lambda s, m: (1 + _lsr(r_t(14, s, m, dev), 20) % 50).to(torch.float64), np.float64, f64)
+        price = self._chunks(start, n, lambda s, m: u_np(15, s, m) * 104100.0 + 900.0,
+                             lambda s, m: u_t(15, s, m, dev) * 104100.0 + 900.0, np.float64, f64)
+        disc = self._chunks(start, n, lambda s, m: ((r_np(16, s, m) >> np.uint64(20)) % np.uint64(11)).astype(np.float64) / 100.0,
+                            lambda s, m: (_lsr(r_t(16, s, m, dev), 20) % 11).to(torch.float64) / 100.0, np.float64, f64)
+        return (self._wrap(cols.INT32, ship, None, n, 0), self._wrap(cols.UINT8, rflag, None, n, 0),
+                self._wrap(cols.UINT8, lstat, None, n, 0), self._wrap(cols.DOUBLE, qty, None, n, 0),
+                self._wrap(cols.DOUBLE, price, None, n, 0), self._wrap(cols.DOUBLE, disc, None, n, 0))

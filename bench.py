@@ -225,7 +225,64 @@ class GroupByWL(Workload):
         return oracle.groupby([k], self._specs(), [v] * len(self.agg_names), kind=kind, max_groups=self.n_keys + 2)
 
 
+class Q1WL(Workload):
+    """Config C5: TPC-H Q1-shaped pipeline on synthetic lineitem, UNFUSED through the public operations:
+    less_equal(shipdate) -> Filter of the 5 used columns (one shared plan) -> GroupBy(returnflag, linestatus)."""
+    kernel = "groupby_consume"
+    name = "q1"
+    dtype = "f64 sums / means, u8 keys, date32 predicate"
+
+    def __init__(self, rows):
+        super().__init__(rows)
+        self.description = ("Q1-shaped pipeline over %d synthetic lineitem rows: shipdate <= 1998-09-02 (~96%% selective), Filter of "
+                            "returnflag/linestatus/quantity/extendedprice/discount, GroupBy(returnflag, linestatus) "
+                            "sum x2, mean x3, count; unfused (each operation reads and writes HBM)" % rows)
+
+    def make(self, gen, start=0, n=None):
+        return gen.q1_lineitem(n or self.n, start)
+
+    def input_bytes(self):
+        return self.n * 30          # 4 (date) + 2 (keys) + 3 x 8 (measures)
+
+    def alg_bytes_per_launch(self, launches_per_step):
+        # group-by consume reads the two filtered key columns and the three filtered measures once
+        return 0.964 * self.n * 26 / max(launches_per_step, 1)
+
+    def step(self, ctx, cols_, bufs):
+        from arrow1_b200 import compute
+        ship, rf, ls, qty, price, disc = cols_
+        return compute.Q1Pipeline(ship, rf, ls, [qty, price, disc], ctx)
+
+    def e2e_step(self, host_cols):
+        from arrow1_b200 import compute
+        ctx = compute.default_context()
+        dev, nbytes = [], 0
+        for c in host_cols:
+            d, b = compute._h2d(c, ctx)
+            dev.append(d)
+            nbytes += b
+        out = compute.Q1Pipeline(dev[0], dev[1], dev[2], dev[3:], ctx)
+        d2h = 0
+        for cols__ in out.aggs + [out.keys]:
+            for c in cols__:
+                d2h += c.to_host().nbytes()
+        compute.Transfer.h2d, compute.Transfer.d2h = nbytes, d2h
+        return out
+
+    def cpu_step(self, oracle, kind, host_cols):
+        import numpy as np
+        from arrow1_b200 import compute
+        from arrow1_b200.columns import Column
+        ship, rf, ls, qty, price, disc = host_cols
+        mask = Column.from_numpy(ship.values() <= compute.Q1_SHIPDATE_CUTOFF)
+        f = [Column.from_numpy(oracle.filter(c, mask, 0, kind=kind).values().copy()) for c in (rf, ls, qty, price, disc)]
+        specs = compute.q1_aggregates()
+        return oracle.groupby([f[0], f[1]], [a for _, a in specs], [f[2 + i] for i, _ in specs], kind=kind, max_groups=8)
+
+
 def make_workload(name, rows=None):
+    if name == "q1":
+        return Q1WL(rows or 600_000_000)
     if name == "sort_i64":
         return SortWL(rows or 100_000_000, "int64")
     if name == "sort_f64":
@@ -379,7 +436,7 @@ def kernel_times(ctx, names):
     return out
 
 
-ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume")
+ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume", "compare_scalar", "partition_plan", "partition_scatter")
 
 
 def time_device(ctx, wl, cols_, steps, warmup, world, dist_step=None):
@@ -514,7 +571,7 @@ def gpu_arm(args):
     if rank == 0 and world == 1 and not args.no_extras:
         del cols_, bufs
         torch.cuda.empty_cache()
-        for name in ("filter", "filter_10m", "sort_i64", "sort_f64", "groupby_c3"):
+        for name in ("filter", "filter_10m", "sort_i64", "sort_f64", "groupby_c3", "groupby_c4", "q1"):
             if name == wl.name:
                 continue
             try:

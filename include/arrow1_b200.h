@@ -144,6 +144,17 @@ B200_API int b200_filter_out_spec(const b200_col* values, const b200_col* mask, 
 /* device address of the int64 output length inside a plan (for fully asynchronous callers) */
 B200_API const int64_t* b200_filter_plan_length_ptr(const void* plan);
 
+/* ---- mask producer -------------------------------------------------------
+ * == the array-vs-scalar form of the comparison functions "equal", "not_equal", "greater",
+ * "greater_equal", "less", "less_equal" (compute/kernels/scalar_compare.cc; op = 0..5 in that order) on a
+ * numeric column: out bit i = values[i] OP *scalar, with the C++ operators of the physical type (a NaN
+ * compares false except under not_equal).  `scalar` is a HOST pointer to one value of the column's type.
+ * out_bitmap: device, ceil(length / 32) whole 32-bit words, bit offset 0.  Null-ness is not touched: like
+ * the reference's null propagation (exec.cc PropagateNulls) the result's validity is the input's, and the
+ * binding shares that buffer.  This is what feeds Filter in the Q1-shaped pipeline (config C5). */
+B200_API int b200_compare_scalar(b200_ctx* ctx, const b200_col* values, int op,
+                                 const void* scalar /* host */, void* out_bitmap);
+
 /* ---- SortIndices --------------------------------------------------------------------------
  * order: 0 = SortOrder::Ascending, 1 = SortOrder::Descending (api_vector.h:61-66).
  * == ArraySortIndices<UInt64Type, T>::Exec with ArrayCompareSorter / ArrayCountOrCompareSorter
