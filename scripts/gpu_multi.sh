@@ -5,7 +5,7 @@ N=${1:-2}
 mkdir -p gpurun_out
 for wl in sort_i64 filter groupby_c3 groupby_c4; do
   rows=""
-  if [ "$wl" = "groupby_c4" ]; then rows="--rows 250000000"; fi
+  if [ "$wl" = "groupby_c4" ]; then rows="--rows $((1000000000 / N))"; fi
   ( timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
       bench.py --gpus $N --workload $wl $rows --steps 5 --warmup 3 --no-extras --no-cpu ) > gpurun_out/multi_${N}_$wl.json 2> gpurun_out/multi_${N}_$wl.err
   python - "$wl" "$N" <<'PY'
