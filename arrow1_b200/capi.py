@@ -236,6 +236,25 @@ def sort_keys_rows(ctx: Context, values: Column, order: int = 0, index_base: int
     return keys[:n], rows[:n]
 
 
+def sort_range_partition(ctx: Context, values: Column, order: int, index_base: int, splitters: Sequence[int], n_parts: int):
+    """b200_sort_range_partition -> (keys, rows, counts): the (radix key, global row | class << 62) pairs of
+    the column grouped by destination (stable), int64-typed tensors; `splitters` are unsigned radix keys."""
+    n = values.length
+    dev = "cuda:%d" % ctx.device
+    keys = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+    rows = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+    nb = C.c_size_t(0)
+    ctx.check(lib().b200_sort_partition_scratch_bytes(C.c_int64(n), C.byref(nb)))
+    scratch = ctx.empty(nb.value)
+    spl = (C.c_uint64 * max(n_parts - 1, 1))(*[int(x) & ((1 << 64) - 1) for x in splitters])
+    counts = (C.c_int64 * 16)()
+    v = values.desc()
+    ctx.check(lib().b200_sort_range_partition(ctx._h, C.byref(v), C.c_int(order), C.c_uint64(index_base), spl, C.c_int(n_parts),
+                                              C.c_void_p(keys.data_ptr()), C.c_void_p(rows.data_ptr()), counts,
+                                              C.c_void_p(scratch.data_ptr()), C.c_size_t(nb.value)))
+    return keys[:n], rows[:n], [int(counts[q]) for q in range(n_parts)]
+
+
 def sort_pairs(ctx: Context, keys: torch.Tensor, payload: torch.Tensor, want_keys: bool = False):
     n = keys.numel()
     nb = C.c_size_t(0)

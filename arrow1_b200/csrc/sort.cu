@@ -558,6 +558,145 @@ __global__ void sort_keys_kernel(SortParams p, uint64_t* out, uint64_t* out_rows
   }
 }
 
+// ---- stable range partition (multi-GPU sample sort) ----------------------------------
+// dest(row) = number of splitters <= key(row) (unsigned radix keys; NaN -> 2^64-2, null -> 2^64-1 as in
+// sort_keys_kernel).  Rows of one destination come out contiguous AND in row order, so that after the
+// all-to-all the concatenation of the runs a rank receives (source ranks in rank order) is in global row
+// order and ONE stable sort by key finishes the job — the first version sorted locally before the exchange
+// and again after it.  256 threads x 16 rows; every warp owns 512 consecutive rows.
+constexpr int kSpMax = 16;
+constexpr int kSpThreads = 256;
+constexpr int kSpItems = 16;
+constexpr int kSpTile = kSpThreads * kSpItems;
+
+struct Splitters {
+  uint64_t s[kSpMax - 1];
+  int32_t n_parts;
+};
+
+__device__ __forceinline__ uint32_t sp_dest(const Splitters& sp, uint64_t key) {
+  uint32_t d = 0;
+#pragma unroll
+  for (int j = 0; j < kSpMax - 1; ++j)
+    if (j < sp.n_parts - 1 && sp.s[j] <= key) ++d;
+  return d;
+}
+
+__device__ __forceinline__ uint64_t sp_out_key(const SortParams& p, int64_t row, uint32_t* cls) {
+  const uint64_t k = source_key(p, row, cls);
+  return *cls == 2 ? kNullKeyOut : (*cls == 1 ? kNanKeyOut : k);
+}
+
+__global__ void __launch_bounds__(kSpThreads) sp_count_kernel(SortParams p, const __grid_constant__ Splitters sp, uint32_t* tile_counts) {
+  __shared__ uint32_t cnt[kSpMax];
+  if (threadIdx.x < kSpMax) cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const int64_t base = int64_t(blockIdx.x) * kSpTile;
+#pragma unroll 4
+  for (int i = 0; i < kSpItems; ++i) {
+    const int64_t row = base + i * kSpThreads + threadIdx.x;
+    if (row < p.n) {
+      uint32_t cls;
+      atomicAdd(&cnt[sp_dest(sp, sp_out_key(p, row, &cls))], 1u);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < kSpMax) tile_counts[size_t(blockIdx.x) * kSpMax + threadIdx.x] = cnt[threadIdx.x];
+}
+
+// one CTA: per destination, exclusive scan over tiles; totals[p] = count, totals[kSpMax + p] = base
+__global__ void __launch_bounds__(1024) sp_scan_kernel(uint32_t* tile_counts, int64_t n_tiles, int n_parts, int64_t* totals) {
+  __shared__ uint32_t warp_sums[32];
+  __shared__ uint32_t carry_s;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  for (int q = 0; q < n_parts; ++q) {
+    if (t == 0) carry_s = 0;
+    __syncthreads();
+    for (int64_t base = 0; base < n_tiles; base += 1024) {
+      const int64_t tile = base + t;
+      const uint32_t c = tile < n_tiles ? tile_counts[size_t(tile) * kSpMax + q] : 0;
+      uint32_t incl = c;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+      }
+      if (lane == 31) warp_sums[warp] = incl;
+      __syncthreads();
+      uint32_t wpre = 0;
+      for (int w = 0; w < warp; ++w) wpre += warp_sums[w];
+      const uint32_t carry = carry_s;
+      if (tile < n_tiles) tile_counts[size_t(tile) * kSpMax + q] = carry + wpre + incl - c;
+      __syncthreads();
+      if (t == 1023) carry_s = carry + wpre + incl;
+      __syncthreads();
+    }
+    if (t == 0) totals[q] = carry_s;
+    __syncthreads();
+  }
+  if (t == 0) {
+    int64_t acc = 0;
+    for (int q = 0; q < n_parts; ++q) {
+      totals[kSpMax + q] = acc;
+      acc += totals[q];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kSpThreads) sp_scatter_kernel(SortParams p, const __grid_constant__ Splitters sp,
+                                                                const uint32_t* tile_offsets, const int64_t* totals,
+                                                                uint64_t* out_keys, uint64_t* out_rows) {
+  __shared__ uint32_t wtot[kSpThreads / 32][kSpMax];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const unsigned lt = lanemask_lt();
+  const int64_t wrow0 = int64_t(blockIdx.x) * kSpTile + warp * (kSpItems * 32);
+  uint64_t key[kSpItems];
+  uint32_t meta[kSpItems];   // dest | class << 4 | local rank << 8
+  uint32_t cnt = 0;          // lane q (< 16): rows of this warp seen so far for destination q
+#pragma unroll
+  for (int i = 0; i < kSpItems; ++i) {
+    const int64_t row = wrow0 + i * 32 + lane;
+    const bool in = row < p.n;
+    uint32_t cls = 0, d = 0;
+    key[i] = 0;
+    if (in) {
+      key[i] = sp_out_key(p, row, &cls);
+      d = sp_dest(sp, key[i]);
+    }
+    const unsigned inmask = __ballot_sync(0xffffffffu, in);
+    unsigned m = inmask, mq = inmask;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const unsigned bal = __ballot_sync(0xffffffffu, in && ((d >> b) & 1u));
+      m &= ((d >> b) & 1u) ? bal : ~bal;
+      mq &= ((lane >> b) & 1u) ? bal : ~bal;
+    }
+    const uint32_t before = __shfl_sync(0xffffffffu, cnt, int(d));
+    meta[i] = d | (cls << 4) | ((before + __popc(m & lt)) << 8);
+    cnt += __popc(mq);
+  }
+  if (lane < kSpMax) wtot[warp][lane] = cnt;
+  __syncthreads();
+  // lane q: where this warp's rows for destination q start
+  uint64_t off = 0;
+  if (lane < sp.n_parts) {
+    uint32_t wpre = 0;
+    for (int w = 0; w < warp; ++w) wpre += wtot[w][lane];
+    off = uint64_t(totals[kSpMax + lane]) + tile_offsets[size_t(blockIdx.x) * kSpMax + lane] + wpre;
+  }
+#pragma unroll
+  for (int i = 0; i < kSpItems; ++i) {
+    const int64_t row = wrow0 + i * 32 + lane;
+    const uint32_t d = meta[i] & 15u;
+    const uint64_t base = __shfl_sync(0xffffffffu, off, int(d));
+    if (row < p.n) {
+      const uint64_t pos = base + (meta[i] >> 8);
+      out_keys[pos] = key[i];
+      out_rows[pos] = (p.index_base + uint64_t(row)) | (uint64_t((meta[i] >> 4) & 3u) << 62);
+    }
+  }
+}
+
 struct Layout {
   size_t hist, info, counters, err, state, zero_bytes, keys0, keys1, pays0, pays1, total;
 };
@@ -688,6 +827,51 @@ int b200_sort_keys_rows(b200_ctx* ctx, const b200_col* values, int order, uint64
   p.index_base = index_base;
   sort_keys_kernel<<<(unsigned)((p.n + 255) / 256), 256, 0, ctx->stream>>>(p, out_keys, out_rows);
   B200_LAUNCHED(ctx);
+  return B200_OK;
+}
+
+int b200_sort_partition_scratch_bytes(int64_t length, size_t* out_bytes) {
+  if (!out_bytes || length < 0) return B200_INVALID;
+  const size_t n_tiles = size_t((length + kSpTile - 1) / kSpTile);
+  *out_bytes = b200_align_up(n_tiles * kSpMax * sizeof(uint32_t), 256) + 2 * kSpMax * sizeof(int64_t) + 512;
+  return B200_OK;
+}
+
+int b200_sort_range_partition(b200_ctx* ctx, const b200_col* values, int order, uint64_t index_base,
+                              const uint64_t* splitters, int n_parts, uint64_t* out_keys, uint64_t* out_rows,
+                              int64_t* out_counts, void* scratch, size_t scratch_bytes) {
+  if (!ctx) return B200_INVALID;
+  if (!out_counts || n_parts < 1 || n_parts > kSpMax || (n_parts > 1 && !splitters))
+    return b200_fail(ctx, B200_INVALID, "sort_range_partition: bad arguments (1..%d partitions)", kSpMax);
+  SortParams p;
+  memset(&p, 0, sizeof(p));
+  B200_RETURN_NOT_OK(fill_column_source(ctx, values, order, &p));
+  for (int q = 0; q < n_parts; ++q) out_counts[q] = 0;
+  if (p.n == 0) return B200_OK;
+  if (index_base + uint64_t(p.n) > (uint64_t(1) << 62)) return b200_fail(ctx, B200_INDEX_ERROR, "sort_range_partition: row numbers beyond 2^62");
+  if (p.n >= (int64_t(1) << 32)) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "sort_range_partition: more than 2^32-1 rows per call");
+  size_t need = 0;
+  b200_sort_partition_scratch_bytes(p.n, &need);
+  if (!out_keys || !out_rows || !scratch || scratch_bytes < need) return b200_fail(ctx, B200_INVALID, "sort_range_partition: null output or scratch too small");
+  Splitters sp;
+  memset(&sp, 0, sizeof(sp));
+  sp.n_parts = n_parts;
+  for (int j = 0; j + 1 < n_parts; ++j) {
+    sp.s[j] = splitters[j];
+    if (j > 0 && sp.s[j] < sp.s[j - 1]) return b200_fail(ctx, B200_INVALID, "sort_range_partition: splitters must ascend");
+  }
+  p.index_base = index_base;
+  const int64_t n_tiles = (p.n + kSpTile - 1) / kSpTile;
+  char* base = reinterpret_cast<char*>(b200_align_up(reinterpret_cast<uintptr_t>(scratch), 256));
+  uint32_t* tile_counts = reinterpret_cast<uint32_t*>(base);
+  int64_t* totals = reinterpret_cast<int64_t*>(base + b200_align_up(size_t(n_tiles) * kSpMax * sizeof(uint32_t), 256));
+  B200_TIMED(ctx, "sort_partition", (sp_count_kernel<<<(unsigned)n_tiles, kSpThreads, 0, ctx->stream>>>(p, sp, tile_counts)));
+  sp_scan_kernel<<<1, 1024, 0, ctx->stream>>>(tile_counts, n_tiles, n_parts, totals);
+  B200_LAUNCHED(ctx);
+  B200_TIMED(ctx, "sort_partition", (sp_scatter_kernel<<<(unsigned)n_tiles, kSpThreads, 0, ctx->stream>>>(p, sp, tile_counts, totals, out_keys, out_rows)));
+  B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 32, totals, kSpMax * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  for (int q = 0; q < n_parts; ++q) out_counts[q] = ctx->host_words[32 + q];
   return B200_OK;
 }
 

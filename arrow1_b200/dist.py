@@ -60,6 +60,34 @@ class CudaOps:
     def groupby(self, key_types, aggs, arg_types, expected_groups):
         return self.capi.GroupBy(self.ctx, key_types, aggs, arg_types, expected_groups)
 
+    def range_partition(self, col: Column, order: int, index_base: int, splitters, n_parts: int):
+        return self.capi.sort_range_partition(self.ctx, col, order, index_base, splitters, n_parts)
+
+    def sample_keys(self, col: Column, order: int, count: int) -> torch.Tensor:
+        """Radix keys of `count` regularly spaced rows (plumbing: a gathered mini-column through b200_sort_keys)."""
+        from .columns import BITS
+        n = col.length
+        if n == 0:
+            return torch.empty(0, dtype=torch.int64, device=self.device)
+        m = min(count, n)
+        pos = ((torch.arange(m, device=self.device, dtype=torch.int64) * 2 + 1) * n) // (2 * m) + col.offset
+        width = BITS[col.type] // 8
+        vals = col.data[: (col.offset + n) * width].view(-1, width)[pos].contiguous().view(-1)
+        validity = None
+        nulls = 0
+        if col.validity is not None and col.null_count != 0:
+            bits = (col.validity[pos >> 3].to(torch.int32) >> (pos & 7).to(torch.int32)) & 1
+            nulls = int(m - int(bits.sum().item()))
+            padded = torch.zeros(((m + 7) // 8 + 64) * 8, dtype=torch.uint8, device=self.device)
+            padded[:m] = bits.to(torch.uint8)
+            w = torch.tensor([1, 2, 4, 8, 16, 32, 64, 128], dtype=torch.uint8, device=self.device)
+            validity = (padded.view(-1, 8) * w).sum(dim=1, dtype=torch.uint8)
+        buf = torch.zeros(vals.numel() + 64, dtype=torch.uint8, device=self.device)
+        buf[: vals.numel()] = vals
+        mini = Column(col.type, buf, validity, m, 0, nulls)
+        keys, _ = self.capi.sort_keys_rows(self.ctx, mini, order, 0)
+        return keys
+
     # ---- hash repartitioning (high-cardinality group-by)
     def partition(self, gb, keys: Sequence[Column], cols: Sequence[Column], n_parts: int, row_base: int):
         """-> (counts[n_parts], [data bytes tensor per col], [validity bytes tensor or None per col], rows)
@@ -128,18 +156,24 @@ def class_fixup(keys_sorted: torch.Tensor, rows_sorted: torch.Tensor) -> torch.T
 def dist_sort_indices(ops, col: Column, order: int, row_base: int, group=None):
     """Global SortIndices over the concatenation of every rank's shard (rank order == row order).
     Returns (indices, global_offset): this rank's contiguous slice of the global uint64 index
-    array (int64-typed tensor) and where it starts."""
+    array (int64-typed tensor) and where it starts.
+
+    Sample sort with ONE local radix sort per rank: splitters come from a regular sample of every rank's
+    (unsorted) keys; each rank range-partitions its (key, global row) pairs by the splitters with a STABLE
+    partition kernel (b200_sort_range_partition), the runs are exchanged with one all-to-all, and since
+    the runs a rank receives are in global row order when concatenated in source-rank order, one stable
+    sort by key yields the (key, row) order.  Keys >= the NaN key all go to the last rank, which orders
+    values / NaNs / nulls (class_fixup)."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
-    keys, rows = ops.sort_keys_rows(col, order, row_base)
-    ks, rs = ops.sort_pairs(keys, rows)
     if world == 1:
+        keys, rows = ops.sort_keys_rows(col, order, row_base)
+        ks, rs = ops.sort_pairs(keys, rows)
         return class_fixup(ks, rs), 0
-    dev = ks.device
-    biased = _bias(ks)
-    # ---- splitters from a regular sample of every rank's sorted run
-    smp = torch.full((OVERSAMPLE,), 0, dtype=torch.int64, device=dev)
-    got = sample_sorted(biased, OVERSAMPLE)
+    dev = ops.device
+    # ---- splitters from a regular sample of every rank's keys
+    got = _bias(ops.sample_keys(col, order, OVERSAMPLE))
+    smp = torch.zeros(OVERSAMPLE, dtype=torch.int64, device=dev)
     smp[: got.numel()] = got
     meta = torch.tensor([got.numel()], dtype=torch.int64, device=dev)
     all_smp = torch.empty(world * OVERSAMPLE, dtype=torch.int64, device=dev)
@@ -149,10 +183,9 @@ def dist_sort_indices(ops, col: Column, order: int, row_base: int, group=None):
     counts = all_meta.tolist()
     valid = torch.cat([all_smp[r * OVERSAMPLE: r * OVERSAMPLE + counts[r]] for r in range(world)])
     splitters = choose_splitters(valid, world)
-    # ---- contiguous runs of the sorted local data go to each rank
-    cuts = torch.searchsorted(biased, splitters).tolist() if biased.numel() else [0] * (world - 1)
-    bounds = [0] + cuts + [biased.numel()]
-    send_counts = [bounds[j + 1] - bounds[j] for j in range(world)]
+    spl_unsigned = [(int(x) ^ _I64_MIN) & ((1 << 64) - 1) for x in splitters.tolist()]
+    # ---- stable range partition, then one all-to-all of keys and one of rows
+    ks, rs, send_counts = ops.range_partition(col, order, row_base, spl_unsigned, world)
     sc = torch.tensor(send_counts, dtype=torch.int64, device=dev)
     rc = torch.empty(world, dtype=torch.int64, device=dev)
     dist.all_to_all_single(rc, sc, group=group)
@@ -162,11 +195,9 @@ def dist_sort_indices(ops, col: Column, order: int, row_base: int, group=None):
     rr = torch.empty(total, dtype=torch.int64, device=dev)
     dist.all_to_all_single(rk, ks.contiguous(), recv_counts, send_counts, group=group)
     dist.all_to_all_single(rr, rs.contiguous(), recv_counts, send_counts, group=group)
-    # ---- runs arrive in source-rank order == global row order, so a stable sort by key yields
-    # the (key, global row) order
+    # ---- received runs, concatenated in source-rank order, are in global row order: a stable sort by key
     ks2, rs2 = ops.sort_pairs(rk, rr)
     out = class_fixup(ks2, rs2) if rank == world - 1 else (rs2 & _ROW_MASK)
-    # where this rank's slice starts in the global result
     tot = torch.tensor([total], dtype=torch.int64, device=dev)
     all_tot = torch.empty(world, dtype=torch.int64, device=dev)
     dist.all_gather_into_tensor(all_tot, tot, group=group)

@@ -436,7 +436,7 @@ def kernel_times(ctx, names):
     return out
 
 
-ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume", "compare_scalar", "partition_plan", "partition_scatter")
+ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume", "compare_scalar", "partition_plan", "partition_scatter", "sort_partition")
 
 
 def time_device(ctx, wl, cols_, steps, warmup, world, dist_step=None):

@@ -177,6 +177,16 @@ B200_API int b200_sort_keys(b200_ctx* ctx, const b200_col* values, int order, ui
  * class letting the receiver tell a null from a genuine maximum key. */
 B200_API int b200_sort_keys_rows(b200_ctx* ctx, const b200_col* values, int order, uint64_t index_base,
                                  uint64_t* out_keys, uint64_t* out_rows /* nullable */);
+/* Stable range partition for the sample sort: dest(row) = number of splitters <= key(row), with the keys /
+ * rows of b200_sort_keys_rows (so NaN and null keys go to the last destination when the splitters are
+ * clamped to 2^64-2).  Destination q's (key, row) pairs are written contiguously from sum(out_counts[0..q))
+ * IN ROW ORDER, which is what lets the receiving rank finish with one stable b200_sort_pairs.
+ * splitters: HOST, n_parts-1 ascending radix keys; n_parts <= 16; out_counts: HOST int64[n_parts]. */
+B200_API int b200_sort_partition_scratch_bytes(int64_t length, size_t* out_bytes);
+B200_API int b200_sort_range_partition(b200_ctx* ctx, const b200_col* values, int order,
+                                       uint64_t index_base, const uint64_t* splitters /* host */,
+                                       int n_parts, uint64_t* out_keys, uint64_t* out_rows,
+                                       int64_t* out_counts /* host */, void* scratch, size_t scratch_bytes);
 B200_API int b200_sort_pairs_scratch_bytes(int64_t length, size_t* out_bytes);
 B200_API int b200_sort_pairs(b200_ctx* ctx, const uint64_t* keys, const uint64_t* payload,
                              int64_t length, uint64_t* out_keys /* nullable */,

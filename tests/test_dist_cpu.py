@@ -153,6 +153,25 @@ class NumpyOps:
     def filter(self, values, mask, null_selection):
         return oracle.filter(values, mask, null_selection, kind="port")
 
+    def sample_keys(self, col, order, count):
+        k, _ = radix_keys(col, order)
+        n = len(k)
+        if n == 0:
+            return torch.empty(0, dtype=torch.int64)
+        m = min(count, n)
+        pos = ((np.arange(m, dtype=np.int64) * 2 + 1) * n) // (2 * m)
+        return torch.from_numpy(k[pos].view(np.int64).copy())
+
+    def range_partition(self, col, order, index_base, splitters, n_parts):
+        """numpy image of b200_sort_range_partition: dest = number of splitters <= key, stable."""
+        k, cls = radix_keys(col, order)
+        rows = (np.arange(len(k), dtype=U64) + U64(index_base)) | (cls.astype(U64) << U64(62))
+        spl = np.array(splitters, dtype=U64)
+        dest = np.searchsorted(spl, k, side="right") if len(spl) else np.zeros(len(k), dtype=np.int64)
+        p = np.argsort(dest, kind="stable")
+        return (torch.from_numpy(k[p].view(np.int64).copy()), torch.from_numpy(rows[p].view(np.int64).copy()),
+                [int((dest == q).sum()) for q in range(n_parts)])
+
     def groupby(self, key_types, aggs, arg_types, expected_groups):
         return NumpyGroupBy()
 

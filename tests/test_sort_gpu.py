@@ -119,3 +119,28 @@ def test_sort_keys_transform_is_order_preserving(ctx):
     keys = capi.sort_keys(ctx, col.to_device(), 0).cpu().numpy().view(np.uint64)
     idx = run_sort(ORACLE, col, 0)
     assert (np.diff(keys[idx].astype(np.float64)) >= 0).all() or (keys[idx][:-1] <= keys[idx][1:]).all()
+
+
+@pytest.mark.parametrize("n_parts", [1, 2, 3, 8, 16])
+def test_range_partition_is_stable_and_matches_numpy_image(ctx, n_parts):
+    """b200_sort_range_partition (the multi-GPU sample sort's local step): dest = number of splitters <=
+    radix key; every destination's (key, row) pairs contiguous and in row order."""
+    from arrow1_b200 import capi
+    from test_dist_cpu import radix_keys
+    rng = np.random.default_rng(70 + n_parts)
+    for n in (1, 33, 4095, 4096, 4097, 100_003):
+        f = rng.integers(-50, 50, size=n).astype(np.float64)
+        f[rng.integers(0, n, max(n // 50, 1))] = np.nan
+        for col in (Column.from_numpy(f, rng.random(n) > 0.05),
+                    Column.from_numpy(rng.integers(-2**63, 2**63 - 1, size=n, dtype=np.int64), rng.random(n) > 0.05)):
+            for order in (0, 1):
+                k, cls = radix_keys(col, order)
+                spl = np.sort(rng.choice(k, size=n_parts - 1)) if n_parts > 1 else np.zeros(0, dtype=np.uint64)
+                spl = np.minimum(spl, np.uint64(2**64 - 2))
+                keys, rows, counts = capi.sort_range_partition(ctx, col.to_device(), order, 1000, [int(x) for x in spl], n_parts)
+                dest = np.searchsorted(spl, k, side="right")
+                p = np.argsort(dest, kind="stable")
+                want_rows = (np.arange(n, dtype=np.uint64) + np.uint64(1000)) | (cls.astype(np.uint64) << np.uint64(62))
+                assert counts == [int((dest == q).sum()) for q in range(n_parts)]
+                np.testing.assert_array_equal(keys.cpu().numpy().view(np.uint64), k[p])
+                np.testing.assert_array_equal(rows.cpu().numpy().view(np.uint64), want_rows[p])
