@@ -236,6 +236,18 @@ def sort_keys_rows(ctx: Context, values: Column, order: int = 0, index_base: int
     return keys[:n], rows[:n]
 
 
+def sort_indices_chunked(ctx: Context, chunks: Sequence[Column], order: int = 0) -> torch.Tensor:
+    """== compute::SortIndices(ChunkedArray, order): indices into the logical concatenation."""
+    total = sum(c.length for c in chunks)
+    out = torch.empty(max(total, 1), dtype=torch.int64, device="cuda:%d" % ctx.device)
+    nb = C.c_size_t(0)
+    ctx.check(lib().b200_sort_indices_chunked_scratch_bytes(C.c_int64(total), C.byref(nb)))
+    scratch = ctx.empty(nb.value)
+    ctx.check(lib().b200_sort_indices_chunked(ctx._h, col_array(chunks), C.c_int(len(chunks)), C.c_int(order),
+                                              C.c_void_p(out.data_ptr()), C.c_void_p(scratch.data_ptr()), C.c_size_t(nb.value)))
+    return out[:total]
+
+
 def sort_range_partition(ctx: Context, values: Column, order: int, index_base: int, splitters: Sequence[int], n_parts: int):
     """b200_sort_range_partition -> (keys, rows, counts): the (radix key, global row | class << 62) pairs of
     the column grouped by destination (stable), int64-typed tensors; `splitters` are unsigned radix keys."""

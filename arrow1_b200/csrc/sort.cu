@@ -697,6 +697,18 @@ __global__ void __launch_bounds__(kSpThreads) sp_scatter_kernel(SortParams p, co
   }
 }
 
+// ---- chunked input: class keys for the final stable 3-way split, and the class-bit strip
+// sorted (key, row | class << 62) pairs -> 0 for keys below the NaN key, else 1 + class: one more stable
+// pass on this 2-bit key puts [values | genuine maxima | NaNs | nulls] in place (vector_sort.cc:269-302)
+__global__ void chunk_class_keys_kernel(const uint64_t* keys, const uint64_t* rows, int64_t n, uint64_t* out) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = keys[i] >= kNanKeyOut ? 1 + (rows[i] >> 62) : 0;
+}
+__global__ void chunk_strip_kernel(uint64_t* rows, int64_t n) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) rows[i] &= (uint64_t(1) << 62) - 1;
+}
+
 struct Layout {
   size_t hist, info, counters, err, state, zero_bytes, keys0, keys1, pays0, pays1, total;
 };
@@ -826,6 +838,52 @@ int b200_sort_keys_rows(b200_ctx* ctx, const b200_col* values, int order, uint64
     return b200_fail(ctx, B200_INDEX_ERROR, "sort_keys: row numbers beyond 2^62");
   p.index_base = index_base;
   sort_keys_kernel<<<(unsigned)((p.n + 255) / 256), 256, 0, ctx->stream>>>(p, out_keys, out_rows);
+  B200_LAUNCHED(ctx);
+  return B200_OK;
+}
+
+int b200_sort_indices_chunked_scratch_bytes(int64_t total_length, size_t* out_bytes) {
+  if (!out_bytes || total_length < 0) return B200_INVALID;
+  // keys, rows, sorted keys, sorted rows (8 B each) + the pair sort's own scratch
+  *out_bytes = 4 * b200_align_up(size_t(total_length) * 8, 256) + layout_for(total_length).total + 1024;
+  return B200_OK;
+}
+
+int b200_sort_indices_chunked(b200_ctx* ctx, const b200_col* chunks, int n_chunks, int order, uint64_t* out_indices,
+                              void* scratch, size_t scratch_bytes) {
+  if (!ctx) return B200_INVALID;
+  if (n_chunks < 0 || (n_chunks > 0 && !chunks)) return b200_fail(ctx, B200_INVALID, "sort_indices_chunked: bad chunk list");
+  int64_t total = 0;
+  for (int c = 0; c < n_chunks; ++c) {
+    if (chunks[c].length < 0) return b200_fail(ctx, B200_INVALID, "sort_indices_chunked: negative length");
+    if (chunks[c].type != chunks[0].type) return b200_fail(ctx, B200_TYPE_ERROR, "sort_indices_chunked: chunk types differ");
+    total += chunks[c].length;
+  }
+  if (total == 0) return B200_OK;
+  size_t need = 0;
+  b200_sort_indices_chunked_scratch_bytes(total, &need);
+  if (!out_indices || !scratch || scratch_bytes < need) return b200_fail(ctx, B200_INVALID, "sort_indices_chunked: null output or scratch too small");
+  char* base = reinterpret_cast<char*>(b200_align_up(reinterpret_cast<uintptr_t>(scratch), 256));
+  const size_t arr = b200_align_up(size_t(total) * 8, 256);
+  uint64_t* keys = reinterpret_cast<uint64_t*>(base);
+  uint64_t* rows = reinterpret_cast<uint64_t*>(base + arr);
+  uint64_t* skeys = reinterpret_cast<uint64_t*>(base + 2 * arr);
+  uint64_t* srows = reinterpret_cast<uint64_t*>(base + 3 * arr);
+  void* pair_scratch = base + 4 * arr;
+  const size_t pair_bytes = scratch_bytes - (size_t(base - reinterpret_cast<char*>(scratch)) + 4 * arr);
+  // the logical concatenation (ChunkedArraySorter's global indices, vector_sort.cc:657-832)
+  int64_t off = 0;
+  for (int c = 0; c < n_chunks; ++c) {
+    if (chunks[c].length == 0) continue;
+    B200_RETURN_NOT_OK(b200_sort_keys_rows(ctx, &chunks[c], order, uint64_t(off), keys + off, rows + off));
+    off += chunks[c].length;
+  }
+  B200_RETURN_NOT_OK(b200_sort_pairs(ctx, keys, rows, total, skeys, srows, pair_scratch, pair_bytes));
+  const unsigned grid = unsigned((total + 255) / 256);
+  chunk_class_keys_kernel<<<grid, 256, 0, ctx->stream>>>(skeys, srows, total, keys);
+  B200_LAUNCHED(ctx);
+  B200_RETURN_NOT_OK(b200_sort_pairs(ctx, keys, srows, total, nullptr, out_indices, pair_scratch, pair_bytes));
+  chunk_strip_kernel<<<grid, 256, 0, ctx->stream>>>(out_indices, total);
   B200_LAUNCHED(ctx);
   return B200_OK;
 }

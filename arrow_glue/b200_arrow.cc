@@ -333,7 +333,21 @@ class CudaSortIndicesMetaFunction : public MetaFunction {
           ARROW_ASSIGN_OR_RAISE(auto out, AllocateDevice(dev, 0));
           return Datum(ArrayData::Make(uint64(), 0, {nullptr, std::move(out)}, 0));
         }
-        return Status::NotImplemented("sort_indices over a multi-chunk device ChunkedArray: concatenate on the device first");
+        // ChunkedArraySorter semantics (vector_sort.cc:657-832): global indices over the logical concatenation
+        ARROW_ASSIGN_OR_RAISE(DeviceState * dev, GetDevice(device_));
+        ARROW_ASSIGN_OR_RAISE(const int32_t vtype, NumericType(*chunked.type()));
+        std::vector<b200_col> cols(chunked.num_chunks());
+        for (int c = 0; c < chunked.num_chunks(); ++c) RETURN_NOT_OK(ToCol(*chunked.chunk(c)->data(), vtype, &cols[c]));
+        std::lock_guard<std::mutex> lock(dev->mutex);
+        size_t scratch_bytes = 0;
+        B200_OK_OR_RAISE(dev, b200_sort_indices_chunked_scratch_bytes(chunked.length(), &scratch_bytes));
+        ARROW_ASSIGN_OR_RAISE(auto scratch, AllocateDevice(dev, static_cast<int64_t>(scratch_bytes)));
+        ARROW_ASSIGN_OR_RAISE(auto out, AllocateDevice(dev, chunked.length() * 8));
+        B200_OK_OR_RAISE(dev, b200_sort_indices_chunked(dev->ctx, cols.data(), int(cols.size()), order == SortOrder::Descending ? 1 : 0,
+                                                        reinterpret_cast<uint64_t*>(out->address()),
+                                                        reinterpret_cast<void*>(scratch->address()), scratch_bytes));
+        B200_OK_OR_RAISE(dev, b200_ctx_synchronize(dev->ctx));
+        return Datum(ArrayData::Make(uint64(), chunked.length(), {nullptr, std::move(out)}, 0));
       }
       default:
         break;

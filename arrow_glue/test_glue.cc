@@ -256,6 +256,23 @@ int main() {
     auto want = GET(cp::CallFunction("sort_indices", {sl}, &sopts, &cpu_ctx)).make_array();
     auto got = HostArray(GET(cp::CallFunction("sort_indices", {DeviceDatum(sl)}, &sopts, &gpu_ctx)));
     ExpectEqual(got, want, "sort_indices sliced float64 desc (meta function)");
+    // ChunkedArray: indices over the logical concatenation, NaNs / nulls of every chunk last (vector_sort_test.cc:629-647)
+    for (auto& col : {columns[0], columns[1]}) {
+      ArrayVector hchunks = {col->Slice(0, 70001), col->Slice(70001, 0), col->Slice(70001, 130000), col->Slice(200001)};
+      ArrayVector dchunks;
+      // ChunkedArray's constructor sums chunk->null_count() (chunked_array.cc:46-63); for a slice that is
+      // kUnknownNullCount, i.e. a host scan of the bitmap, so the count has to be settled before the buffers
+      // are device pointers
+      for (auto& c : hchunks) { (void)c->null_count(); dchunks.push_back(MakeArray(ToDevice(*c->data()))); }
+      auto hca = std::make_shared<ChunkedArray>(hchunks, col->type());
+      auto dca = std::make_shared<ChunkedArray>(dchunks, col->type());
+      for (auto order : {cp::SortOrder::Ascending, cp::SortOrder::Descending}) {
+        cp::SortOptions o({cp::SortKey("", order)});
+        auto want_c = GET(cp::CallFunction("sort_indices", {Datum(hca)}, &o, &cpu_ctx)).make_array();
+        auto got_c = HostArray(GET(cp::CallFunction("sort_indices", {Datum(dca)}, &o, &gpu_ctx)));
+        ExpectEqual(got_c, want_c, "sort_indices ChunkedArray (4 chunks) " + col->type()->ToString() + (order == cp::SortOrder::Ascending ? " asc" : " desc"));
+      }
+    }
   }
 
   // ---------------- GroupBy ----------------

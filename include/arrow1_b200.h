@@ -167,6 +167,13 @@ B200_API int b200_sort_indices_scratch_bytes(int64_t length, size_t* out_bytes);
 B200_API int b200_sort_indices(b200_ctx* ctx, const b200_col* values, int order,
                                uint64_t index_base, uint64_t* out_indices, void* scratch,
                                size_t scratch_bytes);
+/* ChunkedArray input (ChunkedArraySorter, vector_sort.cc:657-832): the stable sort of the LOGICAL
+ * CONCATENATION of the chunks — indices are global, nulls / NaNs of every chunk come last.  Each chunk's
+ * radix keys and global row numbers are written side by side, pair-sorted by key, and one more stable pass
+ * on a 2-bit class key separates genuine maxima from NaNs from nulls.  out_indices: uint64[sum of lengths]. */
+B200_API int b200_sort_indices_chunked_scratch_bytes(int64_t total_length, size_t* out_bytes);
+B200_API int b200_sort_indices_chunked(b200_ctx* ctx, const b200_col* chunks, int n_chunks, int order,
+                                       uint64_t* out_indices, void* scratch, size_t scratch_bytes);
 /* Sample-sort building blocks for the multi-GPU path.  sort_keys writes the
  * order-preserving 64-bit radix key of every row (the same transform the local sort uses;
  * NaN -> 2^64-2, null -> 2^64-1) so that ranks can exchange (key, global row) pairs;

@@ -144,3 +144,25 @@ def test_range_partition_is_stable_and_matches_numpy_image(ctx, n_parts):
                 assert counts == [int((dest == q).sum()) for q in range(n_parts)]
                 np.testing.assert_array_equal(keys.cpu().numpy().view(np.uint64), k[p])
                 np.testing.assert_array_equal(rows.cpu().numpy().view(np.uint64), want_rows[p])
+
+
+def test_sort_indices_chunked_equals_sort_of_concatenation(ctx):
+    """ChunkedArraySorter semantics (vector_sort.cc:657-832): global stable order over the logical
+    concatenation, NaNs then nulls of every chunk last; genuine maxima stay ahead of them."""
+    from arrow1_b200 import capi
+    rng = np.random.default_rng(321)
+    n = 50_000
+    f = rng.integers(-20, 20, size=n).astype(np.float64)
+    f[rng.integers(0, n, 900)] = np.nan
+    f[rng.integers(0, n, 200)] = np.inf
+    u = rng.integers(0, 2**64 - 1, size=n, dtype=np.uint64)
+    u[rng.integers(0, n, 300)] = np.uint64(2**64 - 1)
+    u[rng.integers(0, n, 300)] = np.uint64(2**64 - 2)
+    for vals in (f, u):
+        valid = rng.random(n) > 0.05
+        whole = Column.from_numpy(vals, valid)
+        cuts = [0, 1, 17000, 17000, 42000, n]
+        chunks = [Column.from_numpy(vals[a:b].copy(), valid[a:b].copy()).to_device() for a, b in zip(cuts[:-1], cuts[1:])]
+        for order in (0, 1):
+            got = capi.sort_indices_chunked(ctx, chunks, order).cpu().numpy().view(np.uint64)
+            np.testing.assert_array_equal(got, run_sort(ORACLE, whole, order))
