@@ -100,7 +100,8 @@ class Transfer:
     d2h = 0
 
 
-def Filter(values: Column, mask: Column, null_selection: int = DROP, ctx: Optional[capi.Context] = None) -> Column:
+def Filter(values: Column, mask: Column, null_selection: int = DROP, ctx: Optional[capi.Context] = None,
+           _wait: bool = True) -> Column:
     ctx = ctx or default_context()
     host = not values.on_device
     dv, b0 = _h2d(values, ctx)
@@ -118,12 +119,13 @@ def Filter(values: Column, mask: Column, null_selection: int = DROP, ctx: Option
     if out.has_validity:
         nv = (col.length + 7) // 8
         validity = _d2h(col.validity, nv)
-    torch.cuda.current_stream(ctx.device).synchronize()
+    if _wait:
+        ctx.stream.synchronize()
     Transfer.d2h = nd + nv + 8
     return Column(col.type, data, validity, col.length, 0, col.null_count)
 
 
-def SortIndices(values: Column, order: int = ASCENDING, ctx: Optional[capi.Context] = None):
+def SortIndices(values: Column, order: int = ASCENDING, ctx: Optional[capi.Context] = None, _wait: bool = True):
     """uint64 indices: numpy array for host input, int64-typed torch tensor for device input."""
     ctx = ctx or default_context()
     host = not values.on_device
@@ -133,9 +135,83 @@ def SortIndices(values: Column, order: int = ASCENDING, ctx: Optional[capi.Conte
     if not host:
         return out
     h = _d2h(out, values.length * 8)
-    torch.cuda.current_stream(ctx.device).synchronize()
+    if _wait:
+        ctx.stream.synchronize()
     Transfer.d2h = values.length * 8
     return h.view(np.uint64)
+
+
+class Pending:
+    """Result of Pipeline.submit: `result()` blocks until the lane's copies and kernels are done."""
+
+    def __init__(self, event: torch.cuda.Event, value):
+        self._event, self._value = event, value
+
+    def done(self) -> bool:
+        return self._event.query()
+
+    def result(self):
+        self._event.synchronize()
+        return self._value
+
+
+class Pipeline:
+    """Several calls in flight on one GPU: `depth` lanes, each one b200_ctx on its own CUDA stream
+    ("callers wanting concurrency create one b200_ctx per stream").  A call submitted
+    to a lane stages its host inputs, runs and reads its result back on that lane's stream only, so the
+    H2D copy of call i+1, the kernels of call i and the D2H copy of call i-1 overlap: both PCIe
+    directions and the SMs are busy at once, which is what bounds an ingest loop over host batches.
+    The reference's counterpart is calling compute::Filter / SortIndices from several CPU threads
+    (its kernels run on the calling thread, compute/exec.cc:972-986).
+
+        pipe = Pipeline(depth=3)
+        pending = [pipe.submit(SortIndices, batch, ASCENDING) for batch in batches]
+        for p in pending: indices = p.result()
+    """
+
+    def __init__(self, depth: int = 3, device: Optional[int] = None):
+        if device is None:
+            device = torch.cuda.current_device()
+        self.device = device
+        self.lanes = []
+        for _ in range(max(depth, 1)):
+            stream = torch.cuda.Stream(device)
+            self.lanes.append((capi.Context(device, stream), stream))
+        self._next = 0
+        self._last: List[Optional[torch.cuda.Event]] = [None] * len(self.lanes)
+
+    @property
+    def launches(self) -> int:
+        return sum(ctx.launches for ctx, _ in self.lanes)
+
+    def submit(self, fn, *args, **kwargs) -> Pending:
+        """fn is Filter or SortIndices (calls that need a host-visible size mid-way, GroupBy's group count
+        or Filter's output length, block the submitting thread for that long but still overlap with the
+        other lanes' copies)."""
+        i = self._next % len(self.lanes)
+        self._next += 1
+        ctx, stream = self.lanes[i]
+        with torch.cuda.stream(stream):
+            if fn in (Filter, SortIndices):
+                kwargs["_wait"] = False
+            value = fn(*args, ctx=ctx, **kwargs)
+            ev = torch.cuda.Event()
+            ev.record(stream)
+        self._last[i] = ev
+        return Pending(ev, value)
+
+    def join(self, stream: Optional[torch.cuda.Stream] = None) -> None:
+        """Make `stream` (default: the current one) wait for everything submitted so far."""
+        stream = stream or torch.cuda.current_stream(self.device)
+        for ev in self._last:
+            if ev is not None:
+                stream.wait_event(ev)
+
+    def close(self):
+        for ctx, stream in self.lanes:
+            stream.synchronize()
+            ctx.close()
+        self.lanes = []
 
 
 Q1_SHIPDATE_CUTOFF = 10471   # 1998-09-02 as date32 (TPC-H Q1: l_shipdate <= date '1998-12-01' - 90 days)
