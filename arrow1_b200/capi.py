@@ -281,6 +281,97 @@ def sort_pairs(ctx: Context, keys: torch.Tensor, payload: torch.Tensor, want_key
     return (out_k[:n] if want_keys else None), out_p[:n]
 
 
+def sort_pairs32(ctx: Context, keys: torch.Tensor, payload32: torch.Tensor, want_keys: bool = False):
+    """b200_sort_pairs32: stable sort of (uint64 key, uint32 payload) pairs; the payload travels through the
+    passes and comes out widened to uint64 (int64-typed tensor)."""
+    n = keys.numel()
+    nb = C.c_size_t(0)
+    ctx.check(lib().b200_sort_pairs_scratch_bytes(C.c_int64(n), C.byref(nb)))
+    scratch = ctx.empty(nb.value)
+    out_p = torch.empty(max(n, 1), dtype=torch.int64, device=keys.device)
+    out_k = torch.empty(max(n, 1), dtype=torch.int64, device=keys.device) if want_keys else None
+    ctx.check(lib().b200_sort_pairs32(ctx._h, C.c_void_p(keys.data_ptr()), C.c_void_p(payload32.data_ptr()), C.c_int64(n),
+                                      C.c_void_p(out_k.data_ptr()) if want_keys else None,
+                                      C.c_void_p(out_p.data_ptr()), C.c_void_p(scratch.data_ptr()),
+                                      C.c_size_t(scratch.numel())))
+    return (out_k[:n] if want_keys else None), out_p[:n]
+
+
+class RangePartitionPush:
+    """The two phases of the range partition fused with the exchange (b200_sort_range_partition_count / _push)."""
+
+    def __init__(self, ctx: Context, values: Column, order: int, splitters: Sequence[int], n_parts: int):
+        self.ctx, self.values, self.order, self.n_parts = ctx, values, order, n_parts
+        nb = C.c_size_t(0)
+        ctx.check(lib().b200_sort_partition_scratch_bytes(C.c_int64(values.length), C.byref(nb)))
+        self.scratch = ctx.empty(nb.value)
+        self.spl = (C.c_uint64 * max(n_parts - 1, 1))(*[int(x) & ((1 << 64) - 1) for x in splitters])
+        counts = (C.c_int64 * 16)()
+        v = values.desc()
+        ctx.check(lib().b200_sort_range_partition_count(ctx._h, C.byref(v), C.c_int(order), self.spl, C.c_int(n_parts), counts,
+                                                        C.c_void_p(self.scratch.data_ptr()), C.c_size_t(self.scratch.numel())))
+        self.counts = [int(counts[q]) for q in range(n_parts)]
+
+    def push(self, index_base: int, dst_keys: Sequence[int], dst_rows: Sequence[int], dst_offsets: Sequence[int], rows32: bool):
+        """dst_keys / dst_rows: device addresses (possibly peer mappings), one per destination."""
+        n = self.n_parts
+        kp = (C.c_void_p * n)(*[int(x) for x in dst_keys])
+        rp = (C.c_void_p * n)(*[int(x) for x in dst_rows])
+        off = (C.c_int64 * n)(*[int(x) for x in dst_offsets])
+        v = self.values.desc()
+        self.ctx.check(lib().b200_sort_range_partition_push(
+            self.ctx._h, C.byref(v), C.c_int(self.order), C.c_uint64(index_base), self.spl, C.c_int(n), kp, rp, off,
+            C.c_int(1 if rows32 else 0), C.c_void_p(self.scratch.data_ptr()), C.c_size_t(self.scratch.numel())))
+
+
+class _RawCuda:
+    """Borrowed device memory as a __cuda_array_interface__ provider (zero-copy torch view)."""
+
+    def __init__(self, ptr: int, nbytes: int, owner):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+        self._owner = owner
+
+
+class PeerBuffer:
+    """A device allocation other processes of the node can map (b200_peer_alloc / _export / _open)."""
+
+    def __init__(self, ctx: Context, nbytes: int):
+        self.ctx, self.nbytes = ctx, int(nbytes)
+        p = C.c_void_p()
+        ctx.check(lib().b200_peer_alloc(ctx._h, C.c_size_t(self.nbytes), C.byref(p)))
+        self.ptr = int(p.value)
+        self.peers: List[int] = []     # mappings of the other ranks' buffers opened here
+
+    def handle(self) -> bytes:
+        h = (C.c_ubyte * 64)()
+        self.ctx.check(lib().b200_peer_export(self.ctx._h, C.c_void_p(self.ptr), h))
+        return bytes(h)
+
+    def open(self, handle: bytes) -> int:
+        h = (C.c_ubyte * 64)(*handle)
+        p = C.c_void_p()
+        self.ctx.check(lib().b200_peer_open(self.ctx._h, h, C.byref(p)))
+        self.peers.append(int(p.value))
+        return int(p.value)
+
+    def tensor(self, dtype: torch.dtype, count: int, byte_offset: int = 0) -> torch.Tensor:
+        item = torch.empty(0, dtype=dtype).element_size()
+        assert byte_offset + count * item <= self.nbytes
+        raw = torch.as_tensor(_RawCuda(self.ptr + byte_offset, max(count * item, 1), self), device="cuda:%d" % self.ctx.device)
+        return raw[: count * item].view(dtype)
+
+    def close_peers(self):
+        for p in self.peers:
+            lib().b200_peer_close(self.ctx._h, C.c_void_p(p))
+        self.peers = []
+
+    def close(self):
+        self.close_peers()
+        if self.ptr:
+            lib().b200_peer_free(self.ctx._h, C.c_void_p(self.ptr))
+            self.ptr = 0
+
+
 # ---------------------------------------------------------------------------------------------
 # Grouper + hash aggregates
 

@@ -83,6 +83,7 @@ struct SortParams {
   int64_t n_tiles;
   uint64_t index_base;
   const uint64_t* gather;  // optional: out_idx[pos] = gather[row]
+  const uint32_t* pay_in;  // optional (with keys_in): 32-bit payload carried through the passes instead of the row number
   uint64_t* out_idx;
   uint64_t* out_keys;      // optional
   uint32_t* hist;          // [8][kBinStride] counts, then exclusive bases
@@ -357,8 +358,8 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
 #pragma unroll
   for (int i = 0; i < kItems; ++i) {
     const int local = wbase + 32 * i;
-    if (info.first) pay[i] = uint32_t(tile_row0 + local);
-    else pay[i] = (kFull || local < tile_items) ? pays_src[tile_row0 + local] : 0u;
+    if (info.first && !p.pay_in) pay[i] = uint32_t(tile_row0 + local);
+    else pay[i] = (kFull || local < tile_items) ? (info.first ? p.pay_in : pays_src)[tile_row0 + local] : 0u;
   }
   __syncthreads();
 
@@ -574,11 +575,15 @@ struct Splitters {
   int32_t n_parts;
 };
 
+// number of splitters <= key: the splitters ascend, so four halving steps replace the 15 compares
 __device__ __forceinline__ uint32_t sp_dest(const Splitters& sp, uint64_t key) {
+  const uint32_t ns = uint32_t(sp.n_parts - 1);
   uint32_t d = 0;
 #pragma unroll
-  for (int j = 0; j < kSpMax - 1; ++j)
-    if (j < sp.n_parts - 1 && sp.s[j] <= key) ++d;
+  for (uint32_t step = 8; step > 0; step >>= 1) {
+    const uint32_t j = d + step;   // candidate count: valid if splitter j-1 exists and is <= key
+    if (j <= ns && sp.s[j - 1] <= key) d = j;
+  }
   return d;
 }
 
@@ -589,17 +594,31 @@ __device__ __forceinline__ uint64_t sp_out_key(const SortParams& p, int64_t row,
 
 __global__ void __launch_bounds__(kSpThreads) sp_count_kernel(SortParams p, const __grid_constant__ Splitters sp, uint32_t* tile_counts) {
   __shared__ uint32_t cnt[kSpMax];
+  const int lane = threadIdx.x & 31;
   if (threadIdx.x < kSpMax) cnt[threadIdx.x] = 0;
   __syncthreads();
   const int64_t base = int64_t(blockIdx.x) * kSpTile;
+  // lane q (< 16) counts the warp's rows for destination q from four ballots per step: with 2..16 destinations
+  // per-row shared atomics would all land on a handful of addresses and serialise
+  uint32_t mine = 0;
 #pragma unroll 4
   for (int i = 0; i < kSpItems; ++i) {
     const int64_t row = base + i * kSpThreads + threadIdx.x;
-    if (row < p.n) {
+    const bool in = row < p.n;
+    uint32_t d = 0;
+    if (in) {
       uint32_t cls;
-      atomicAdd(&cnt[sp_dest(sp, sp_out_key(p, row, &cls))], 1u);
+      d = sp_dest(sp, sp_out_key(p, row, &cls));
     }
+    unsigned mq = __ballot_sync(0xffffffffu, in);
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const unsigned bal = __ballot_sync(0xffffffffu, in && ((d >> b) & 1u));
+      mq &= ((lane >> b) & 1u) ? bal : ~bal;
+    }
+    mine += __popc(mq);
   }
+  if (lane < kSpMax && mine) atomicAdd(&cnt[lane], mine);
   __syncthreads();
   if (threadIdx.x < kSpMax) tile_counts[size_t(blockIdx.x) * kSpMax + threadIdx.x] = cnt[threadIdx.x];
 }
@@ -643,9 +662,20 @@ __global__ void __launch_bounds__(1024) sp_scan_kernel(uint32_t* tile_counts, in
   }
 }
 
+// Where the scatter writes.  Local partition: every destination shares one buffer, run q starts at the
+// device-side totals[kSpMax + q].  Fused exchange: keys[q] / rows[q] are rank q's receive buffers (peer
+// mappings over NVLink; this rank's own for q == rank) and base[q] where this rank's run starts in them.
+struct PushDst {
+  uint64_t* keys[kSpMax];
+  void* rows[kSpMax];
+  int64_t base[kSpMax];
+  const int64_t* totals;  // nullable
+  int32_t rows32;
+};
+
 __global__ void __launch_bounds__(kSpThreads) sp_scatter_kernel(SortParams p, const __grid_constant__ Splitters sp,
-                                                                const uint32_t* tile_offsets, const int64_t* totals,
-                                                                uint64_t* out_keys, uint64_t* out_rows) {
+                                                                const uint32_t* tile_offsets,
+                                                                const __grid_constant__ PushDst dst) {
   __shared__ uint32_t wtot[kSpThreads / 32][kSpMax];
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const unsigned lt = lanemask_lt();
@@ -682,7 +712,8 @@ __global__ void __launch_bounds__(kSpThreads) sp_scatter_kernel(SortParams p, co
   if (lane < sp.n_parts) {
     uint32_t wpre = 0;
     for (int w = 0; w < warp; ++w) wpre += wtot[w][lane];
-    off = uint64_t(totals[kSpMax + lane]) + tile_offsets[size_t(blockIdx.x) * kSpMax + lane] + wpre;
+    off = uint64_t(dst.base[lane]) + (dst.totals ? uint64_t(dst.totals[kSpMax + lane]) : 0) +
+          tile_offsets[size_t(blockIdx.x) * kSpMax + lane] + wpre;
   }
 #pragma unroll
   for (int i = 0; i < kSpItems; ++i) {
@@ -691,8 +722,10 @@ __global__ void __launch_bounds__(kSpThreads) sp_scatter_kernel(SortParams p, co
     const uint64_t base = __shfl_sync(0xffffffffu, off, int(d));
     if (row < p.n) {
       const uint64_t pos = base + (meta[i] >> 8);
-      out_keys[pos] = key[i];
-      out_rows[pos] = (p.index_base + uint64_t(row)) | (uint64_t((meta[i] >> 4) & 3u) << 62);
+      const uint32_t cls = (meta[i] >> 4) & 3u;
+      dst.keys[d][pos] = key[i];
+      if (dst.rows32) reinterpret_cast<uint32_t*>(dst.rows[d])[pos] = uint32_t(p.index_base + uint64_t(row)) | (cls << 30);
+      else reinterpret_cast<uint64_t*>(dst.rows[d])[pos] = (p.index_base + uint64_t(row)) | (uint64_t(cls) << 62);
     }
   }
 }
@@ -895,41 +928,146 @@ int b200_sort_partition_scratch_bytes(int64_t length, size_t* out_bytes) {
   return B200_OK;
 }
 
+namespace {
+struct PartitionPlan {
+  SortParams p;
+  Splitters sp;
+  int64_t n_tiles;
+  uint32_t* tile_counts;
+  int64_t* totals;
+};
+
+int make_partition_plan(b200_ctx* ctx, const char* who, const b200_col* values, int order, const uint64_t* splitters,
+                        int n_parts, void* scratch, size_t scratch_bytes, PartitionPlan* pl) {
+  if (n_parts < 1 || n_parts > kSpMax || (n_parts > 1 && !splitters))
+    return b200_fail(ctx, B200_INVALID, "%s: bad arguments (1..%d partitions)", who, kSpMax);
+  memset(pl, 0, sizeof(*pl));
+  B200_RETURN_NOT_OK(fill_column_source(ctx, values, order, &pl->p));
+  if (pl->p.n >= (int64_t(1) << 32)) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "%s: more than 2^32-1 rows per call", who);
+  size_t need = 0;
+  b200_sort_partition_scratch_bytes(pl->p.n, &need);
+  if (pl->p.n > 0 && (!scratch || scratch_bytes < need)) return b200_fail(ctx, B200_INVALID, "%s: scratch too small", who);
+  pl->sp.n_parts = n_parts;
+  for (int j = 0; j + 1 < n_parts; ++j) {
+    pl->sp.s[j] = splitters[j];
+    if (j > 0 && pl->sp.s[j] < pl->sp.s[j - 1]) return b200_fail(ctx, B200_INVALID, "%s: splitters must ascend", who);
+  }
+  pl->n_tiles = (pl->p.n + kSpTile - 1) / kSpTile;
+  char* base = reinterpret_cast<char*>(b200_align_up(reinterpret_cast<uintptr_t>(scratch), 256));
+  pl->tile_counts = reinterpret_cast<uint32_t*>(base);
+  pl->totals = reinterpret_cast<int64_t*>(base + b200_align_up(size_t(pl->n_tiles) * kSpMax * sizeof(uint32_t), 256));
+  return B200_OK;
+}
+
+int partition_count(b200_ctx* ctx, const PartitionPlan& pl) {
+  B200_TIMED(ctx, "sort_partition", (sp_count_kernel<<<(unsigned)pl.n_tiles, kSpThreads, 0, ctx->stream>>>(pl.p, pl.sp, pl.tile_counts)));
+  sp_scan_kernel<<<1, 1024, 0, ctx->stream>>>(pl.tile_counts, pl.n_tiles, pl.sp.n_parts, pl.totals);
+  B200_LAUNCHED(ctx);
+  return B200_OK;
+}
+
+int partition_counts_to_host(b200_ctx* ctx, const PartitionPlan& pl, int64_t* out_counts) {
+  B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 32, pl.totals, kSpMax * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  for (int q = 0; q < pl.sp.n_parts; ++q) out_counts[q] = ctx->host_words[32 + q];
+  return B200_OK;
+}
+}  // namespace
+
 int b200_sort_range_partition(b200_ctx* ctx, const b200_col* values, int order, uint64_t index_base,
                               const uint64_t* splitters, int n_parts, uint64_t* out_keys, uint64_t* out_rows,
                               int64_t* out_counts, void* scratch, size_t scratch_bytes) {
   if (!ctx) return B200_INVALID;
-  if (!out_counts || n_parts < 1 || n_parts > kSpMax || (n_parts > 1 && !splitters))
-    return b200_fail(ctx, B200_INVALID, "sort_range_partition: bad arguments (1..%d partitions)", kSpMax);
-  SortParams p;
-  memset(&p, 0, sizeof(p));
-  B200_RETURN_NOT_OK(fill_column_source(ctx, values, order, &p));
+  if (!out_counts) return b200_fail(ctx, B200_INVALID, "sort_range_partition: null out_counts");
+  PartitionPlan pl;
+  B200_RETURN_NOT_OK(make_partition_plan(ctx, "sort_range_partition", values, order, splitters, n_parts, scratch, scratch_bytes, &pl));
   for (int q = 0; q < n_parts; ++q) out_counts[q] = 0;
-  if (p.n == 0) return B200_OK;
-  if (index_base + uint64_t(p.n) > (uint64_t(1) << 62)) return b200_fail(ctx, B200_INDEX_ERROR, "sort_range_partition: row numbers beyond 2^62");
-  if (p.n >= (int64_t(1) << 32)) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "sort_range_partition: more than 2^32-1 rows per call");
-  size_t need = 0;
-  b200_sort_partition_scratch_bytes(p.n, &need);
-  if (!out_keys || !out_rows || !scratch || scratch_bytes < need) return b200_fail(ctx, B200_INVALID, "sort_range_partition: null output or scratch too small");
-  Splitters sp;
-  memset(&sp, 0, sizeof(sp));
-  sp.n_parts = n_parts;
-  for (int j = 0; j + 1 < n_parts; ++j) {
-    sp.s[j] = splitters[j];
-    if (j > 0 && sp.s[j] < sp.s[j - 1]) return b200_fail(ctx, B200_INVALID, "sort_range_partition: splitters must ascend");
+  if (pl.p.n == 0) return B200_OK;
+  if (index_base + uint64_t(pl.p.n) > (uint64_t(1) << 62)) return b200_fail(ctx, B200_INDEX_ERROR, "sort_range_partition: row numbers beyond 2^62");
+  if (!out_keys || !out_rows) return b200_fail(ctx, B200_INVALID, "sort_range_partition: null output");
+  pl.p.index_base = index_base;
+  B200_RETURN_NOT_OK(partition_count(ctx, pl));
+  PushDst dst;
+  memset(&dst, 0, sizeof(dst));
+  for (int q = 0; q < n_parts; ++q) {
+    dst.keys[q] = out_keys;
+    dst.rows[q] = out_rows;
   }
-  p.index_base = index_base;
-  const int64_t n_tiles = (p.n + kSpTile - 1) / kSpTile;
-  char* base = reinterpret_cast<char*>(b200_align_up(reinterpret_cast<uintptr_t>(scratch), 256));
-  uint32_t* tile_counts = reinterpret_cast<uint32_t*>(base);
-  int64_t* totals = reinterpret_cast<int64_t*>(base + b200_align_up(size_t(n_tiles) * kSpMax * sizeof(uint32_t), 256));
-  B200_TIMED(ctx, "sort_partition", (sp_count_kernel<<<(unsigned)n_tiles, kSpThreads, 0, ctx->stream>>>(p, sp, tile_counts)));
-  sp_scan_kernel<<<1, 1024, 0, ctx->stream>>>(tile_counts, n_tiles, n_parts, totals);
-  B200_LAUNCHED(ctx);
-  B200_TIMED(ctx, "sort_partition", (sp_scatter_kernel<<<(unsigned)n_tiles, kSpThreads, 0, ctx->stream>>>(p, sp, tile_counts, totals, out_keys, out_rows)));
-  B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 32, totals, kSpMax * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  for (int q = 0; q < n_parts; ++q) out_counts[q] = ctx->host_words[32 + q];
+  dst.totals = pl.totals;
+  B200_TIMED(ctx, "sort_partition", (sp_scatter_kernel<<<(unsigned)pl.n_tiles, kSpThreads, 0, ctx->stream>>>(pl.p, pl.sp, pl.tile_counts, dst)));
+  return partition_counts_to_host(ctx, pl, out_counts);
+}
+
+int b200_sort_range_partition_count(b200_ctx* ctx, const b200_col* values, int order, const uint64_t* splitters,
+                                    int n_parts, int64_t* out_counts, void* scratch, size_t scratch_bytes) {
+  if (!ctx) return B200_INVALID;
+  if (!out_counts) return b200_fail(ctx, B200_INVALID, "sort_range_partition_count: null out_counts");
+  PartitionPlan pl;
+  B200_RETURN_NOT_OK(make_partition_plan(ctx, "sort_range_partition_count", values, order, splitters, n_parts, scratch, scratch_bytes, &pl));
+  for (int q = 0; q < n_parts; ++q) out_counts[q] = 0;
+  if (pl.p.n == 0) return B200_OK;
+  B200_RETURN_NOT_OK(partition_count(ctx, pl));
+  return partition_counts_to_host(ctx, pl, out_counts);
+}
+
+int b200_sort_range_partition_push(b200_ctx* ctx, const b200_col* values, int order, uint64_t index_base,
+                                   const uint64_t* splitters, int n_parts, uint64_t* const* dst_keys,
+                                   void* const* dst_rows, const int64_t* dst_offsets, int rows32, void* scratch,
+                                   size_t scratch_bytes) {
+  if (!ctx) return B200_INVALID;
+  if (!dst_keys || !dst_rows || !dst_offsets) return b200_fail(ctx, B200_INVALID, "sort_range_partition_push: null destination table");
+  PartitionPlan pl;
+  B200_RETURN_NOT_OK(make_partition_plan(ctx, "sort_range_partition_push", values, order, splitters, n_parts, scratch, scratch_bytes, &pl));
+  if (pl.p.n == 0) return B200_OK;
+  const uint64_t row_limit = rows32 ? (uint64_t(1) << 30) : (uint64_t(1) << 62);
+  if (index_base + uint64_t(pl.p.n) > row_limit)
+    return b200_fail(ctx, B200_INDEX_ERROR, "sort_range_partition_push: row numbers beyond 2^%d", rows32 ? 30 : 62);
+  pl.p.index_base = index_base;
+  PushDst dst;
+  memset(&dst, 0, sizeof(dst));
+  for (int q = 0; q < n_parts; ++q) {
+    if (!dst_keys[q] || !dst_rows[q] || dst_offsets[q] < 0) return b200_fail(ctx, B200_INVALID, "sort_range_partition_push: bad destination %d", q);
+    dst.keys[q] = dst_keys[q];
+    dst.rows[q] = dst_rows[q];
+    dst.base[q] = dst_offsets[q];
+  }
+  dst.rows32 = rows32 ? 1 : 0;
+  B200_TIMED(ctx, "sort_partition", (sp_scatter_kernel<<<(unsigned)pl.n_tiles, kSpThreads, 0, ctx->stream>>>(pl.p, pl.sp, pl.tile_counts, dst)));
+  return B200_OK;
+}
+
+int b200_peer_alloc(b200_ctx* ctx, size_t bytes, void** out_ptr) {
+  if (!ctx || !out_ptr) return B200_INVALID;
+  *out_ptr = nullptr;
+  B200_CUDA(ctx, cudaSetDevice(ctx->device));
+  B200_CUDA(ctx, cudaMalloc(out_ptr, bytes ? bytes : 256));
+  return B200_OK;
+}
+int b200_peer_free(b200_ctx* ctx, void* ptr) {
+  if (!ctx) return B200_INVALID;
+  if (ptr) B200_CUDA(ctx, cudaFree(ptr));
+  return B200_OK;
+}
+int b200_peer_export(b200_ctx* ctx, void* ptr, unsigned char* out_handle) {
+  if (!ctx || !ptr || !out_handle) return B200_INVALID;
+  static_assert(sizeof(cudaIpcMemHandle_t) == B200_PEER_HANDLE_BYTES, "IPC handle size");
+  cudaIpcMemHandle_t h;
+  B200_CUDA(ctx, cudaIpcGetMemHandle(&h, ptr));
+  memcpy(out_handle, &h, sizeof(h));
+  return B200_OK;
+}
+int b200_peer_open(b200_ctx* ctx, const unsigned char* handle, void** out_ptr) {
+  if (!ctx || !handle || !out_ptr) return B200_INVALID;
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  *out_ptr = nullptr;
+  B200_CUDA(ctx, cudaSetDevice(ctx->device));
+  B200_CUDA(ctx, cudaIpcOpenMemHandle(out_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return B200_OK;
+}
+int b200_peer_close(b200_ctx* ctx, void* ptr) {
+  if (!ctx) return B200_INVALID;
+  if (ptr) B200_CUDA(ctx, cudaIpcCloseMemHandle(ptr));
   return B200_OK;
 }
 
@@ -951,6 +1089,25 @@ int b200_sort_pairs(b200_ctx* ctx, const uint64_t* keys, const uint64_t* payload
   p.cls_digit = -1;
   p.wmask = ~uint64_t(0);
   p.gather = payload;  // NULL => emits the permutation itself
+  p.out_idx = out_payload;
+  p.out_keys = out_keys;
+  return run_sort(ctx, p, scratch, scratch_bytes);
+}
+
+int b200_sort_pairs32(b200_ctx* ctx, const uint64_t* keys, const uint32_t* payload32, int64_t length,
+                      uint64_t* out_keys, uint64_t* out_payload, void* scratch, size_t scratch_bytes) {
+  if (!ctx) return B200_INVALID;
+  if (length < 0) return b200_fail(ctx, B200_INVALID, "sort_pairs32: negative length");
+  if (length == 0) return B200_OK;
+  if (!keys || !payload32 || !out_payload) return b200_fail(ctx, B200_INVALID, "sort_pairs32: null argument");
+  SortParams p;
+  memset(&p, 0, sizeof(p));
+  p.keys_in = keys;
+  p.pay_in = payload32;
+  p.n = length;
+  p.n_digits = kDigits;
+  p.cls_digit = -1;
+  p.wmask = ~uint64_t(0);
   p.out_idx = out_payload;
   p.out_keys = out_keys;
   return run_sort(ctx, p, scratch, scratch_bytes);

@@ -63,6 +63,26 @@ class CudaOps:
     def range_partition(self, col: Column, order: int, index_base: int, splitters, n_parts: int):
         return self.capi.sort_range_partition(self.ctx, col, order, index_base, splitters, n_parts)
 
+    # ---- range partition fused with the exchange (peer memory over NVLink)
+    def peer_sort_exchange(self, capacity: int, group=None) -> "PeerSortExchange":
+        """This rank's receive buffers (>= capacity rows), mapped into every rank; collective (every rank calls
+        it with the same capacity)."""
+        ex = getattr(self.ctx, "_peer_sort", None)   # lives with the context: CudaOps objects are throw-away
+        if ex is None or ex.capacity < capacity:
+            if ex is not None:
+                ex.close(group)
+            ex = PeerSortExchange(self, int(capacity * 1.25) + 4096, group)
+            self.ctx._peer_sort = ex
+        return ex
+
+    def range_partition_count(self, col: Column, order: int, splitters, n_parts: int):
+        return self.capi.RangePartitionPush(self.ctx, col, order, splitters, n_parts)
+
+    def sort_pairs32(self, keys: torch.Tensor, rows32: torch.Tensor, want_keys: bool):
+        if keys.numel() == 0:
+            return keys, torch.empty(0, dtype=torch.int64, device=self.device)
+        return self.capi.sort_pairs32(self.ctx, keys, rows32, want_keys=want_keys)
+
     def sample_keys(self, col: Column, order: int, count: int) -> torch.Tensor:
         """Radix keys of `count` regularly spaced rows (plumbing: a gathered mini-column through b200_sort_keys)."""
         from .columns import BITS
@@ -108,6 +128,47 @@ class CudaOps:
         return Column(type_, data, bitmap, n, 0, nulls)
 
 
+class PeerSortExchange:
+    """Receive buffers of the fused range partition + exchange: `capacity` uint64 keys and uint32 rows on
+    every rank (b200_peer_alloc), each mapped into every other rank through CUDA IPC so that a rank's scatter
+    kernel stores rank q's run directly into rank q's buffers over NVLink."""
+
+    def __init__(self, ops: CudaOps, capacity: int, group=None):
+        capi = ops.capi
+        self.capacity = capacity
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.keys = capi.PeerBuffer(ops.ctx, capacity * 8)
+        self.rows = capi.PeerBuffer(ops.ctx, capacity * 4)
+        mine = torch.tensor(list(self.keys.handle() + self.rows.handle()), dtype=torch.uint8, device=ops.device)
+        every = torch.empty(self.world * mine.numel(), dtype=torch.uint8, device=ops.device)
+        dist.all_gather_into_tensor(every, mine, group=group)
+        blob = every.cpu().numpy().tobytes()
+        self.key_ptrs, self.row_ptrs = [], []
+        for r in range(self.world):
+            h = blob[r * 128: (r + 1) * 128]
+            if r == self.rank:
+                self.key_ptrs.append(self.keys.ptr)
+                self.row_ptrs.append(self.rows.ptr)
+            else:
+                self.key_ptrs.append(self.keys.open(h[:64]))
+                self.row_ptrs.append(self.rows.open(h[64:]))
+        self.flag = torch.zeros(1, dtype=torch.int32, device=ops.device)
+
+    def fence(self, group=None) -> None:
+        """Stream-ordered barrier: returns (on the stream) once every rank's earlier work has completed."""
+        dist.all_reduce(self.flag, group=group)
+
+    def close(self, group=None) -> None:
+        torch.cuda.synchronize()
+        dist.barrier(group=group)       # nobody is still writing into a peer
+        self.keys.close_peers()
+        self.rows.close_peers()
+        dist.barrier(group=group)       # every mapping of this rank's buffers is gone
+        self.keys.close()
+        self.rows.close()
+
+
 # ------------------------------------------------------------------------------------------------
 def dist_filter(ops, values: Column, mask: Column, null_selection: int = 0):
     """Filter of a row-range shard.  No collective: shard boundaries are arbitrary
@@ -138,19 +199,35 @@ def sample_sorted(biased_sorted: torch.Tensor, count: int) -> torch.Tensor:
     return biased_sorted[pos]
 
 
-def class_fixup(keys_sorted: torch.Tensor, rows_sorted: torch.Tensor) -> torch.Tensor:
+def class_fixup(keys_sorted: torch.Tensor, rows_sorted: torch.Tensor, class_shift: int = 62) -> torch.Tensor:
     """Rows whose key is >= the NaN key: genuine values first (already in key, row order), then
     NaNs, then nulls, each in global row order (vector_sort.cc:269-302).  Returns row numbers
-    with the class bits stripped."""
+    with the class bits (at `class_shift`) stripped."""
+    mask = (1 << class_shift) - 1
+    if keys_sorted.numel() == 0:
+        return rows_sorted
+    # keys are in unsigned order: such rows sit at the very end, so the last key tells whether there are any
+    if int(keys_sorted[-1].item()) not in (-1, -2):
+        return rows_sorted if class_shift == 30 else rows_sorted & mask   # 32-bit rows: no class bit can be set
     biased = _bias(keys_sorted)
     start = int(torch.searchsorted(biased, torch.tensor([_TAIL_KEY_BIASED], dtype=torch.int64, device=biased.device)).item())
     tail = rows_sorted[start:]
     if tail.numel():
-        cls = (tail >> 62) & 3
+        cls = (tail >> class_shift) & 3
         if bool((cls != 0).any()):
             tail = torch.cat([tail[cls == 0], tail[cls == 1], tail[cls == 2]])
             rows_sorted = torch.cat([rows_sorted[:start], tail])
-    return rows_sorted & _ROW_MASK
+    return rows_sorted & mask
+
+
+TRACE: Optional[list] = None   # set to [] to collect (phase name, CUDA event) marks (scripts/dist_sort_breakdown.py)
+
+
+def _mark(name: str) -> None:
+    if TRACE is not None and torch.cuda.is_available():
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        TRACE.append((name, ev))
 
 
 def dist_sort_indices(ops, col: Column, order: int, row_base: int, group=None):
@@ -160,10 +237,13 @@ def dist_sort_indices(ops, col: Column, order: int, row_base: int, group=None):
 
     Sample sort with ONE local radix sort per rank: splitters come from a regular sample of every rank's
     (unsorted) keys; each rank range-partitions its (key, global row) pairs by the splitters with a STABLE
-    partition kernel (b200_sort_range_partition), the runs are exchanged with one all-to-all, and since
-    the runs a rank receives are in global row order when concatenated in source-rank order, one stable
-    sort by key yields the (key, row) order.  Keys >= the NaN key all go to the last rank, which orders
-    values / NaNs / nulls (class_fixup)."""
+    partition kernel, the runs reach their destination rank, and since the runs a rank receives are in
+    global row order when concatenated in source-rank order, one stable sort by key yields the (key, row)
+    order.  Keys >= the NaN key all go to the last rank, which orders values / NaNs / nulls (class_fixup).
+
+    On GPUs the partition's scatter IS the exchange (`_exchange_fused`): it stores every run straight into
+    the destination rank's receive buffer through NVLink peer mappings.  The NCCL all-to-all form
+    (`_exchange_all_to_all`) remains for row numbers beyond 2^30 and for the gloo tests."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     if world == 1:
@@ -171,21 +251,78 @@ def dist_sort_indices(ops, col: Column, order: int, row_base: int, group=None):
         ks, rs = ops.sort_pairs(keys, rows)
         return class_fixup(ks, rs), 0
     dev = ops.device
+    _mark("start")
     # ---- splitters from a regular sample of every rank's keys
     got = _bias(ops.sample_keys(col, order, OVERSAMPLE))
     smp = torch.zeros(OVERSAMPLE, dtype=torch.int64, device=dev)
     smp[: got.numel()] = got
-    meta = torch.tensor([got.numel()], dtype=torch.int64, device=dev)
+    meta = torch.tensor([got.numel(), col.length, row_base], dtype=torch.int64, device=dev)
     all_smp = torch.empty(world * OVERSAMPLE, dtype=torch.int64, device=dev)
-    all_meta = torch.empty(world, dtype=torch.int64, device=dev)
+    all_meta = torch.empty(world * 3, dtype=torch.int64, device=dev)
     dist.all_gather_into_tensor(all_smp, smp, group=group)
     dist.all_gather_into_tensor(all_meta, meta, group=group)
-    counts = all_meta.tolist()
-    valid = torch.cat([all_smp[r * OVERSAMPLE: r * OVERSAMPLE + counts[r]] for r in range(world)])
+    metas = all_meta.view(world, 3).tolist()
+    valid = torch.cat([all_smp[r * OVERSAMPLE: r * OVERSAMPLE + metas[r][0]] for r in range(world)])
     splitters = choose_splitters(valid, world)
     spl_unsigned = [(int(x) ^ _I64_MIN) & ((1 << 64) - 1) for x in splitters.tolist()]
+    _mark("splitters")
+    fused = (hasattr(ops, "peer_sort_exchange") and FUSED_EXCHANGE and world < 16
+             and max(m[2] + m[1] for m in metas) <= (1 << 30))
+    if fused:
+        return _exchange_fused(ops, col, order, row_base, spl_unsigned, max(m[1] for m in metas), world, rank, group)
+    return _exchange_all_to_all(ops, col, order, row_base, spl_unsigned, world, rank, group)
+
+
+FUSED_EXCHANGE = True   # tests flip this to run the NCCL all-to-all form on GPUs too
+
+
+_NAN_KEY = (1 << 64) - 2
+
+
+def _exchange_fused(ops, col, order, row_base, spl_unsigned, max_rows, world, rank, group):
+    """count -> all-gather of the count matrix -> scatter into the peers' receive buffers -> fence -> one sort.
+    The rows whose key is >= the NaN key (NaN, null, genuine maxima) form one extra partition that also
+    goes to the last rank, behind its other runs, so that their number is known from the counts alone."""
+    dev = ops.device
+    parts = world + 1
+    plan = ops.range_partition_count(col, order, list(spl_unsigned) + [_NAN_KEY], parts)
+    mine = torch.tensor(plan.counts, dtype=torch.int64, device=dev)
+    matrix = torch.empty(world * parts, dtype=torch.int64, device=dev)
+    # also orders the exchange: it completes here only after every rank has finished the sort that read its
+    # receive buffer in the previous call (their all-gather is enqueued behind it)
+    dist.all_gather_into_tensor(matrix, mine, group=group)
+    m = matrix.view(world, parts).tolist()                     # m[src][partition]
+    body = [sum(m[src][q] for src in range(world)) for q in range(world)]
+    tail = sum(m[src][world] for src in range(world))
+    incoming = body[:-1] + [body[-1] + tail]
+    _mark("count")
+    ex = ops.peer_sort_exchange(max(max(incoming), max_rows), group)
+    offsets = [sum(m[src][q] for src in range(rank)) for q in range(world)]
+    offsets.append(body[-1] + sum(m[src][world] for src in range(rank)))
+    plan.push(row_base, ex.key_ptrs + [ex.key_ptrs[-1]], ex.row_ptrs + [ex.row_ptrs[-1]], offsets, rows32=True)
+    ex.fence(group)                                            # every run addressed to this rank has landed
+    _mark("push")
+    total = incoming[rank]
+    rk = ex.keys.tensor(torch.int64, total)
+    rr = ex.rows.tensor(torch.int32, total)
+    _, out = ops.sort_pairs32(rk, rr, want_keys=False)
+    _mark("sort_pairs")
+    if rank == world - 1 and tail:
+        # rows arrive as global row | class << 30; the stable sort left the tail partition at the end in
+        # (key, row) order: genuine maxima, then NaNs, then nulls (vector_sort.cc:269-302)
+        t = out[total - tail:]
+        cls = (t >> 30) & 3
+        if bool((cls != 0).any()):
+            out[total - tail:] = torch.cat([t[cls == 0], t[cls == 1], t[cls == 2]]) & ((1 << 30) - 1)
+    _mark("class_fixup")
+    return out, sum(incoming[:rank])
+
+
+def _exchange_all_to_all(ops, col, order, row_base, spl_unsigned, world, rank, group):
+    dev = ops.device
     # ---- stable range partition, then one all-to-all of keys and one of rows
     ks, rs, send_counts = ops.range_partition(col, order, row_base, spl_unsigned, world)
+    _mark("range_partition")
     sc = torch.tensor(send_counts, dtype=torch.int64, device=dev)
     rc = torch.empty(world, dtype=torch.int64, device=dev)
     dist.all_to_all_single(rc, sc, group=group)
@@ -195,13 +332,17 @@ def dist_sort_indices(ops, col: Column, order: int, row_base: int, group=None):
     rr = torch.empty(total, dtype=torch.int64, device=dev)
     dist.all_to_all_single(rk, ks.contiguous(), recv_counts, send_counts, group=group)
     dist.all_to_all_single(rr, rs.contiguous(), recv_counts, send_counts, group=group)
+    _mark("all_to_all")
     # ---- received runs, concatenated in source-rank order, are in global row order: a stable sort by key
     ks2, rs2 = ops.sort_pairs(rk, rr)
+    _mark("sort_pairs")
     out = class_fixup(ks2, rs2) if rank == world - 1 else (rs2 & _ROW_MASK)
+    _mark("class_fixup")
     tot = torch.tensor([total], dtype=torch.int64, device=dev)
     all_tot = torch.empty(world, dtype=torch.int64, device=dev)
     dist.all_gather_into_tensor(all_tot, tot, group=group)
     offset = int(all_tot[:rank].sum().item())
+    _mark("offsets")
     return out, offset
 
 

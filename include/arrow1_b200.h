@@ -198,6 +198,44 @@ B200_API int b200_sort_pairs_scratch_bytes(int64_t length, size_t* out_bytes);
 B200_API int b200_sort_pairs(b200_ctx* ctx, const uint64_t* keys, const uint64_t* payload,
                              int64_t length, uint64_t* out_keys /* nullable */,
                              uint64_t* out_payload, void* scratch, size_t scratch_bytes);
+/* As b200_sort_pairs with a 32-bit payload that travels through the passes (no gather at the end):
+ * out_payload[i] = (uint64_t)payload32[perm[i]].  Scratch: b200_sort_pairs_scratch_bytes. */
+B200_API int b200_sort_pairs32(b200_ctx* ctx, const uint64_t* keys, const uint32_t* payload32,
+                               int64_t length, uint64_t* out_keys /* nullable */,
+                               uint64_t* out_payload, void* scratch, size_t scratch_bytes);
+
+/* ---- Range partition fused with the exchange (multi-GPU sample sort over NVLink peer memory) ----
+ * The partition's scatter kernel stores every destination's (key, row) run straight into THAT rank's receive
+ * buffer through a peer mapping, so the all-to-all is the scatter itself: no staging copy, no separate
+ * collective pass.  Two phases, like the sizing calls elsewhere in this header:
+ *   count : per-destination row counts of this rank's column (HOST int64[n_parts]); ranks exchange them,
+ *           each rank derives where its run starts inside every destination buffer (sum of the counts of
+ *           lower ranks for that destination);
+ *   push  : the stable scatter, destination q's run written at dst_keys[q] + dst_offsets[q] (and the same
+ *           element offset in dst_rows[q]).  rows32 != 0 stores rows as uint32 = (index_base + i) | class << 30
+ *           (requires index_base + length <= 2^30), else uint64 with the class at bit 62.
+ * push must follow count with the same column, order, splitters and scratch.  The caller orders the
+ * exchange: no rank may push before every destination has finished reading its buffer's previous
+ * contents, and no rank may read its buffer before every rank's push has completed (stream-ordered
+ * collectives on either side do both; see arrow1_b200/dist.py). */
+B200_API int b200_sort_range_partition_count(b200_ctx* ctx, const b200_col* values, int order,
+                                             const uint64_t* splitters /* host */, int n_parts,
+                                             int64_t* out_counts /* host */, void* scratch, size_t scratch_bytes);
+B200_API int b200_sort_range_partition_push(b200_ctx* ctx, const b200_col* values, int order,
+                                            uint64_t index_base, const uint64_t* splitters /* host */, int n_parts,
+                                            uint64_t* const* dst_keys /* host array of device pointers */,
+                                            void* const* dst_rows /* host array of device pointers */,
+                                            const int64_t* dst_offsets /* host, elements */, int rows32,
+                                            void* scratch, size_t scratch_bytes);
+/* Exchange buffers other processes of this node can map: plain device allocations exported as CUDA IPC
+ * handles (64 opaque bytes, exchanged by the caller, e.g. with an all-gather) and opened by the peers.
+ * The one place this library allocates device memory, because an IPC handle names a whole allocation. */
+#define B200_PEER_HANDLE_BYTES 64
+B200_API int b200_peer_alloc(b200_ctx* ctx, size_t bytes, void** out_ptr);
+B200_API int b200_peer_free(b200_ctx* ctx, void* ptr);
+B200_API int b200_peer_export(b200_ctx* ctx, void* ptr, unsigned char* out_handle /* 64 bytes */);
+B200_API int b200_peer_open(b200_ctx* ctx, const unsigned char* handle /* 64 bytes */, void** out_ptr);
+B200_API int b200_peer_close(b200_ctx* ctx, void* ptr);
 
 /* ---- Grouper + hash aggregates ------------------------------------------------------------
  * b200_agg_kind: the registered hash aggregate functions (kernels/hash_aggregate.cc:1039-1062)

@@ -166,3 +166,44 @@ def test_sort_indices_chunked_equals_sort_of_concatenation(ctx):
         for order in (0, 1):
             got = capi.sort_indices_chunked(ctx, chunks, order).cpu().numpy().view(np.uint64)
             np.testing.assert_array_equal(got, run_sort(ORACLE, whole, order))
+
+
+def test_range_partition_push_and_sort_pairs32_match_the_unfused_forms(ctx):
+    """b200_sort_range_partition_count/_push into per-destination buffers at arbitrary offsets == the runs of
+    b200_sort_range_partition; b200_sort_pairs32 == b200_sort_pairs with the payload widened."""
+    import torch
+    from arrow1_b200 import capi
+    rng = np.random.default_rng(99)
+    n = 123_457
+    f = np.floor(rng.random(n) * 3000.0) - 1500.0
+    f[rng.integers(0, n, 700)] = np.nan
+    col = Column.from_numpy(f, rng.random(n) > 0.03).to_device()
+    keys_all = capi.sort_keys(ctx, col, 0).cpu().numpy().view(np.uint64)
+    spl = [int(x) for x in np.quantile(keys_all[keys_all < np.uint64(2**63)], [0.3, 0.8]).astype(np.uint64)]
+    base = 1000
+    ks, rs, counts = capi.sort_range_partition(ctx, col, 0, base, spl, 3)
+    plan = capi.RangePartitionPush(ctx, col, 0, spl, 3)
+    assert plan.counts == counts
+    offs = [5, 0, 7]
+    kb = [capi.PeerBuffer(ctx, (c + o) * 8 + 64) for c, o in zip(counts, offs)]
+    rb = [capi.PeerBuffer(ctx, (c + o) * 4 + 64) for c, o in zip(counts, offs)]
+    try:
+        plan.push(base, [b.ptr for b in kb], [b.ptr for b in rb], offs, rows32=True)
+        start = 0
+        for q in range(3):
+            k = kb[q].tensor(torch.int64, counts[q], offs[q] * 8)
+            r = rb[q].tensor(torch.int32, counts[q], offs[q] * 4)
+            want_k, want_r = ks[start:start + counts[q]], rs[start:start + counts[q]]
+            assert torch.equal(k, want_k)
+            want32 = (want_r & ((1 << 30) - 1)) | (((want_r >> 62) & 3) << 30)
+            assert torch.equal(r.to(torch.int64) & 0xFFFFFFFF, want32)
+            start += counts[q]
+        # pairs with a 32-bit payload
+        k = kb[2].tensor(torch.int64, counts[2], offs[2] * 8)
+        r = rb[2].tensor(torch.int32, counts[2], offs[2] * 4)
+        sk32, sp32 = capi.sort_pairs32(ctx, k, r, want_keys=True)
+        sk, sp = capi.sort_pairs(ctx, k.clone(), (r.to(torch.int64) & 0xFFFFFFFF).contiguous(), want_keys=True)
+        assert torch.equal(sk32, sk) and torch.equal(sp32, sp)
+    finally:
+        for b in kb + rb:
+            b.close()
