@@ -223,6 +223,30 @@ __device__ __forceinline__ void st_volatile_u32(uint32_t* p, uint32_t v) {
   asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// byte `d` of a 64-bit key: word select + one PRMT (the runtime 64-bit shift costs a funnel shift and a mask)
+__device__ __forceinline__ uint32_t key_digit(uint64_t key, int d) {
+  const uint32_t w = d >= 4 ? uint32_t(key >> 32) : uint32_t(key);
+  return __byte_perm(w, 0u, 0x4440u | uint32_t(d & 3));
+}
+
+// m &= lanes whose bit `b` of `bin` equals this lane's: predicate, ballot, conditional complement, and
+__device__ __forceinline__ unsigned match_bit(unsigned m, uint32_t bin, uint32_t bitmask) {
+  unsigned r;
+  asm volatile(
+      "{\n"
+      "  .reg .pred p;\n"
+      "  .reg .b32 t;\n"
+      "  and.b32 t, %2, %3;\n"
+      "  setp.ne.u32 p, t, 0;\n"
+      "  vote.sync.ballot.b32 t, p, 0xffffffff;\n"
+      "  @!p not.b32 t, t;\n"
+      "  and.b32 %0, %1, t;\n"
+      "}\n"
+      : "=r"(r)
+      : "r"(m), "r"(bin), "r"(bitmask));
+  return r;
+}
+
 struct PassSmem {
   uint64_t keys[kTile];
   uint32_t pay[kTile];
@@ -325,18 +349,14 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
     for (int q = 0; q < kRankGroup; ++q) {
       const int i = g0 + q;
       const bool in = kFull || wbase + 32 * i < tile_items;
-      uint32_t bin = uint32_t(key[i] >> shift) & 255u;
+      uint32_t bin = key_digit(key[i], d);
       if (kClass) {
         const uint32_t cls = uint32_t(cls_bits >> (2 * i)) & 3u;
         if (cls) bin = 255u + cls;
       }
       unsigned m = kFull ? 0xffffffffu : __ballot_sync(0xffffffffu, in);
 #pragma unroll
-      for (int b = 0; b < NB; ++b) {
-        const bool bit = (bin >> b) & 1u;
-        const unsigned bal = __ballot_sync(0xffffffffu, bit);
-        m &= bit ? bal : ~bal;
-      }
+      for (int b = 0; b < NB; ++b) m = match_bit(m, bin, 1u << b);
       peers[q] = m;
       base[q] = 0;
       // same-warp shared atomics issue in program order: item i's bump precedes item i+1's
@@ -430,7 +450,7 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
   for (int i = 0; i < kItems; ++i) {
     const int local = wbase + 32 * i;
     if (kFull || local < tile_items) {
-      uint32_t bin = uint32_t(key[i] >> shift) & 255u;
+      uint32_t bin = key_digit(key[i], d);
       uint32_t pv = pay[i];
       if (kClass) {
         const uint32_t cls = uint32_t(cls_bits >> (2 * i)) & 3u;
@@ -515,7 +535,7 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
     if (kFull || j < tile_items) {
       const uint64_t kk = s.keys[j];
       uint32_t pv = s.pay[j];
-      uint32_t bin = uint32_t(kk >> shift) & 255u;
+      uint32_t bin = key_digit(kk, d);
       if (kClass) {
         const uint32_t cls = pv >> 30;
         if (cls) bin = 255u + cls;
@@ -623,42 +643,50 @@ __global__ void __launch_bounds__(kSpThreads) sp_count_kernel(SortParams p, cons
   if (threadIdx.x < kSpMax) tile_counts[size_t(blockIdx.x) * kSpMax + threadIdx.x] = cnt[threadIdx.x];
 }
 
-// one CTA: per destination, exclusive scan over tiles; totals[p] = count, totals[kSpMax + p] = base
-__global__ void __launch_bounds__(1024) sp_scan_kernel(uint32_t* tile_counts, int64_t n_tiles, int n_parts, int64_t* totals) {
+// one CTA per destination: exclusive scan of its per-tile counts; totals[q] = count.  The exclusive bases
+// over destinations (totals[kSpMax + q]) are written by the last CTA to finish.
+__global__ void __launch_bounds__(1024) sp_scan_kernel(uint32_t* tile_counts, int64_t n_tiles, int n_parts, int64_t* totals,
+                                                       uint32_t* done_counter) {
   __shared__ uint32_t warp_sums[32];
   __shared__ uint32_t carry_s;
+  __shared__ bool last_s;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  for (int q = 0; q < n_parts; ++q) {
-    if (t == 0) carry_s = 0;
-    __syncthreads();
-    for (int64_t base = 0; base < n_tiles; base += 1024) {
-      const int64_t tile = base + t;
-      const uint32_t c = tile < n_tiles ? tile_counts[size_t(tile) * kSpMax + q] : 0;
-      uint32_t incl = c;
+  const int q = blockIdx.x;
+  if (t == 0) carry_s = 0;
+  __syncthreads();
+  for (int64_t base = 0; base < n_tiles; base += 1024) {
+    const int64_t tile = base + t;
+    const uint32_t c = tile < n_tiles ? tile_counts[size_t(tile) * kSpMax + q] : 0;
+    uint32_t incl = c;
 #pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d) incl += o;
-      }
-      if (lane == 31) warp_sums[warp] = incl;
-      __syncthreads();
-      uint32_t wpre = 0;
-      for (int w = 0; w < warp; ++w) wpre += warp_sums[w];
-      const uint32_t carry = carry_s;
-      if (tile < n_tiles) tile_counts[size_t(tile) * kSpMax + q] = carry + wpre + incl - c;
-      __syncthreads();
-      if (t == 1023) carry_s = carry + wpre + incl;
-      __syncthreads();
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += o;
     }
-    if (t == 0) totals[q] = carry_s;
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    uint32_t wpre = 0;
+    for (int w = 0; w < warp; ++w) wpre += warp_sums[w];
+    const uint32_t carry = carry_s;
+    if (tile < n_tiles) tile_counts[size_t(tile) * kSpMax + q] = carry + wpre + incl - c;
+    __syncthreads();
+    if (t == 1023) carry_s = carry + wpre + incl;
     __syncthreads();
   }
   if (t == 0) {
+    totals[q] = carry_s;
+    __threadfence();
+    last_s = atomicAdd(done_counter, 1u) == uint32_t(n_parts - 1);
+  }
+  __syncthreads();
+  if (last_s && t == 0) {
+    __threadfence();
     int64_t acc = 0;
-    for (int q = 0; q < n_parts; ++q) {
-      totals[kSpMax + q] = acc;
-      acc += totals[q];
+    for (int j = 0; j < n_parts; ++j) {
+      totals[kSpMax + j] = acc;
+      acc += reinterpret_cast<volatile int64_t*>(totals)[j];
     }
+    *done_counter = 0;   // ready for the next call (stream-ordered)
   }
 }
 
@@ -935,6 +963,7 @@ struct PartitionPlan {
   int64_t n_tiles;
   uint32_t* tile_counts;
   int64_t* totals;
+  uint32_t* done;
 };
 
 int make_partition_plan(b200_ctx* ctx, const char* who, const b200_col* values, int order, const uint64_t* splitters,
@@ -956,12 +985,14 @@ int make_partition_plan(b200_ctx* ctx, const char* who, const b200_col* values, 
   char* base = reinterpret_cast<char*>(b200_align_up(reinterpret_cast<uintptr_t>(scratch), 256));
   pl->tile_counts = reinterpret_cast<uint32_t*>(base);
   pl->totals = reinterpret_cast<int64_t*>(base + b200_align_up(size_t(pl->n_tiles) * kSpMax * sizeof(uint32_t), 256));
+  pl->done = reinterpret_cast<uint32_t*>(pl->totals + 2 * kSpMax);
   return B200_OK;
 }
 
 int partition_count(b200_ctx* ctx, const PartitionPlan& pl) {
   B200_TIMED(ctx, "sort_partition", (sp_count_kernel<<<(unsigned)pl.n_tiles, kSpThreads, 0, ctx->stream>>>(pl.p, pl.sp, pl.tile_counts)));
-  sp_scan_kernel<<<1, 1024, 0, ctx->stream>>>(pl.tile_counts, pl.n_tiles, pl.sp.n_parts, pl.totals);
+  B200_CUDA(ctx, cudaMemsetAsync(pl.done, 0, sizeof(uint32_t), ctx->stream));
+  sp_scan_kernel<<<pl.sp.n_parts, 1024, 0, ctx->stream>>>(pl.tile_counts, pl.n_tiles, pl.sp.n_parts, pl.totals, pl.done);
   B200_LAUNCHED(ctx);
   return B200_OK;
 }

@@ -254,15 +254,15 @@ def dist_sort_indices(ops, col: Column, order: int, row_base: int, group=None):
     _mark("start")
     # ---- splitters from a regular sample of every rank's keys
     got = _bias(ops.sample_keys(col, order, OVERSAMPLE))
-    smp = torch.zeros(OVERSAMPLE, dtype=torch.int64, device=dev)
+    W = OVERSAMPLE + 3                      # the sample, then (sample count, rows, row base): one all-gather
+    smp = torch.zeros(W, dtype=torch.int64, device=dev)
     smp[: got.numel()] = got
-    meta = torch.tensor([got.numel(), col.length, row_base], dtype=torch.int64, device=dev)
-    all_smp = torch.empty(world * OVERSAMPLE, dtype=torch.int64, device=dev)
-    all_meta = torch.empty(world * 3, dtype=torch.int64, device=dev)
+    smp[OVERSAMPLE:] = torch.tensor([got.numel(), col.length, row_base], dtype=torch.int64)
+    all_smp = torch.empty(world * W, dtype=torch.int64, device=dev)
     dist.all_gather_into_tensor(all_smp, smp, group=group)
-    dist.all_gather_into_tensor(all_meta, meta, group=group)
-    metas = all_meta.view(world, 3).tolist()
-    valid = torch.cat([all_smp[r * OVERSAMPLE: r * OVERSAMPLE + metas[r][0]] for r in range(world)])
+    all_smp = all_smp.view(world, W)
+    metas = all_smp[:, OVERSAMPLE:].tolist()
+    valid = torch.cat([all_smp[r, : metas[r][0]] for r in range(world)])
     splitters = choose_splitters(valid, world)
     spl_unsigned = [(int(x) ^ _I64_MIN) & ((1 << 64) - 1) for x in splitters.tolist()]
     _mark("splitters")
