@@ -178,6 +178,34 @@ def compare_scalar(ctx: Context, values: Column, op: str, scalar) -> Column:
     return Column(BOOL, out, values.validity, n, 0, values.null_count if values.validity is not None else 0)
 
 
+ARITH_OPS = {"add": 0, "subtract": 1, "multiply": 2}
+
+
+def arithmetic(ctx: Context, op: str, a, b) -> Column:
+    """== CallFunction(op, {a, b}) for "add" / "subtract" / "multiply" (compute/kernels/scalar_arithmetic.cc) where
+    a and b are device Columns of one numeric type or Python / numpy scalars (at least one Column).  The result's
+    validity is the AND of the operands' (null_count -1 = unknown when any operand may hold nulls)."""
+    ca = a if isinstance(a, Column) else None
+    cb = b if isinstance(b, Column) else None
+    c = ca if ca is not None else cb
+    if c is None:
+        raise B200Error(4, "arithmetic: at least one operand must be a column")
+    n = c.length
+    width = BITS[c.type] // 8
+    out = ctx.empty(max(n, 1) * max(width, 1))
+    nullable = any(x is not None and x.validity is not None and x.null_count != 0 for x in (ca, cb))
+    out_v = ctx.empty((n + 31) // 32 * 4 + 8) if nullable else None
+    sa = None if ca is not None else np.array([a], dtype=NP_OF[c.type])
+    sb = None if cb is not None else np.array([b], dtype=NP_OF[c.type])
+    da = ca.desc() if ca is not None else None
+    db = cb.desc() if cb is not None else None
+    ctx.check(lib().b200_arithmetic(ctx._h, C.c_int(ARITH_OPS[op]),
+                                    C.byref(da) if da is not None else None, C.c_void_p(sa.ctypes.data) if sa is not None else None,
+                                    C.byref(db) if db is not None else None, C.c_void_p(sb.ctypes.data) if sb is not None else None,
+                                    C.c_void_p(out.data_ptr()), C.c_void_p(out_v.data_ptr()) if nullable else None))
+    return Column(c.type, out, out_v, n, 0, -1 if nullable else 0)
+
+
 def filter_count(ctx: Context, mask: Column, null_selection: int = 0) -> int:
     m = mask.desc()
     n = C.c_int64(0)

@@ -218,11 +218,12 @@ Q1_SHIPDATE_CUTOFF = 10471   # 1998-09-02 as date32 (TPC-H Q1: l_shipdate <= dat
 
 
 def q1_aggregates():
-    """The Q1 outputs that need no arithmetic: argument index into
-    (quantity, extendedprice, discount) and the aggregate applied to it."""
+    """The Q1 outputs: argument index into (quantity, extendedprice, discount,
+    disc_price = extendedprice * (1 - discount)) and the aggregate applied to it."""
     from . import columns as cols
-    return [(0, AggSpec(cols.HASH_SUM)), (1, AggSpec(cols.HASH_SUM)), (0, AggSpec(cols.HASH_MEAN)),
-            (1, AggSpec(cols.HASH_MEAN)), (2, AggSpec(cols.HASH_MEAN)), (0, AggSpec(cols.HASH_COUNT))]
+    return [(0, AggSpec(cols.HASH_SUM)), (1, AggSpec(cols.HASH_SUM)), (3, AggSpec(cols.HASH_SUM)),
+            (0, AggSpec(cols.HASH_MEAN)), (1, AggSpec(cols.HASH_MEAN)), (2, AggSpec(cols.HASH_MEAN)),
+            (0, AggSpec(cols.HASH_COUNT))]
 
 
 def Q1Pipeline(shipdate: Column, returnflag: Column, linestatus: Column, measures: Sequence[Column],
@@ -231,13 +232,15 @@ def Q1Pipeline(shipdate: Column, returnflag: Column, linestatus: Column, measure
         mask = less_equal(shipdate, cutoff)                   scalar_compare.cc
         c'   = Filter(c, mask) for every used column          one plan shared by all columns
                                                               (FilterRecordBatch, vector_selection.cc:1776-1866)
-        GroupBy(measures', keys = (returnflag', linestatus'), q1_aggregates())
+        disc_price' = multiply(extendedprice', subtract(1.0, discount'))      scalar_arithmetic.cc
+        GroupBy(measures' + [disc_price'], keys = (returnflag', linestatus'), q1_aggregates())
     Device columns in, device GroupByOutput out."""
     ctx = ctx or default_context()
     mask = capi.compare_scalar(ctx, shipdate, "less_equal", Q1_SHIPDATE_CUTOFF)
     plan = capi.FilterPlan(ctx, mask, DROP, sync=True)
     rf, ls = plan.apply(returnflag).col, plan.apply(linestatus).col
     ms = [plan.apply(m).col for m in measures]
+    ms.append(capi.arithmetic(ctx, "multiply", ms[1], capi.arithmetic(ctx, "subtract", 1.0, ms[2])))
     specs = q1_aggregates()
     return capi.group_by(ctx, [rf, ls], [a for _, a in specs], [ms[i] for i, _ in specs], expected_groups=8)
 

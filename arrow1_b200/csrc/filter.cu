@@ -12,6 +12,8 @@
 //                        consecutive output slots; validity bits (and boolean values) are
 //                        compacted with REDUX.OR and appended as whole 32-bit words.
 // HBM roofline: 8 B/row values + 3/8 B/row bitmaps read, s*(8+1/8) B/row written.
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace {
@@ -364,9 +366,112 @@ int launch_compare(b200_ctx* ctx, const b200_col* values, const void* scalar, in
   return B200_OK;
 }
 
+// ---- add / subtract / multiply (scalar_arithmetic.cc, unchecked forms)
+template <typename T>
+struct ArithTraits {
+  // integers: computed in the unsigned type of the same width so that overflow wraps (and 16-bit products do
+  // not promote to a signed int that could overflow), like the reference's SafeSigned* / to_unsigned forms
+  using U = typename std::make_unsigned<T>::type;
+  static __device__ __forceinline__ T apply(int op, T x, T y) {
+    const U ux = U(x), uy = U(y);
+    return T(op == 0 ? U(ux + uy) : (op == 1 ? U(ux - uy) : U(ux * uy)));
+  }
+};
+template <>
+struct ArithTraits<float> {
+  static __device__ __forceinline__ float apply(int op, float x, float y) {
+    return op == 0 ? __fadd_rn(x, y) : (op == 1 ? __fsub_rn(x, y) : __fmul_rn(x, y));   // never contracted
+  }
+};
+template <>
+struct ArithTraits<double> {
+  static __device__ __forceinline__ double apply(int op, double x, double y) {
+    return op == 0 ? __dadd_rn(x, y) : (op == 1 ? __dsub_rn(x, y) : __dmul_rn(x, y));
+  }
+};
+
+constexpr int kArithItems = 4;
+
+template <typename T>
+__global__ void __launch_bounds__(256) arith_kernel(const T* __restrict__ a, const T* __restrict__ b, T sa, T sb, int op,
+                                                    int64_t n, T* __restrict__ out) {
+  const int64_t base = (int64_t(blockIdx.x) * 256) * kArithItems + threadIdx.x;
+  T x[kArithItems], y[kArithItems];
+#pragma unroll
+  for (int k = 0; k < kArithItems; ++k) {
+    const int64_t i = base + k * 256;
+    x[k] = (a && i < n) ? a[i] : sa;
+    y[k] = (b && i < n) ? b[i] : sb;
+  }
+#pragma unroll
+  for (int k = 0; k < kArithItems; ++k) {
+    const int64_t i = base + k * 256;
+    if (i < n) out[i] = ArithTraits<T>::apply(op, x[k], y[k]);
+  }
+}
+
+// out word w = validity bits [32w, 32w+32) of a AND of b (a missing bitmap reads as all ones)
+__global__ void __launch_bounds__(256) bitmap_and_kernel(BitmapRef a, BitmapRef b, int64_t n, uint32_t* __restrict__ out) {
+  const int64_t w = int64_t(blockIdx.x) * 256 + threadIdx.x;
+  if (w * 32 < n) out[w] = bitmap_load32(a, w * 32, n) & bitmap_load32(b, w * 32, n);
+}
+
+template <typename T>
+int launch_arith(b200_ctx* ctx, int op, const b200_col* a, const void* a_scalar, const b200_col* b, const void* b_scalar,
+                 int64_t n, void* out) {
+  T sa = T(0), sb = T(0);
+  if (!a) memcpy(&sa, a_scalar, sizeof(T));
+  if (!b) memcpy(&sb, b_scalar, sizeof(T));
+  const T* pa = a ? reinterpret_cast<const T*>(a->data) + a->offset : nullptr;
+  const T* pb = b ? reinterpret_cast<const T*>(b->data) + b->offset : nullptr;
+  const unsigned grid = unsigned((n + 256 * kArithItems - 1) / (256 * kArithItems));
+  B200_TIMED(ctx, "arithmetic", (arith_kernel<T><<<grid, 256, 0, ctx->stream>>>(pa, pb, sa, sb, op, n, reinterpret_cast<T*>(out))));
+  return B200_OK;
+}
+
 }  // namespace
 
 extern "C" {
+
+int b200_arithmetic(b200_ctx* ctx, int op, const b200_col* a, const void* a_scalar, const b200_col* b, const void* b_scalar,
+                    void* out_data, void* out_validity) {
+  if (!ctx) return B200_INVALID;
+  if (op < 0 || op > 2) return b200_fail(ctx, B200_INVALID, "arithmetic: bad operator %d", op);
+  if (!a && !b) return b200_fail(ctx, B200_INVALID, "arithmetic: at least one operand must be a column");
+  if ((!a && !a_scalar) || (!b && !b_scalar)) return b200_fail(ctx, B200_INVALID, "arithmetic: missing operand");
+  const b200_col* c = a ? a : b;
+  if (a && b) {
+    // ExecBatchIterator: "Array arguments must all be the same length" (compute/exec.cc:186-189)
+    if (a->length != b->length) return b200_fail(ctx, B200_INVALID, "Array arguments must all be the same length");
+    // the reference casts to a common type first (DispatchBest); that cast is not part of this path
+    if (a->type != b->type) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "arithmetic: operand types differ (%d, %d)", a->type, b->type);
+  }
+  const int64_t n = c->length;
+  if (n < 0 || c->offset < 0 || (a && b && b->offset < 0)) return b200_fail(ctx, B200_INVALID, "arithmetic: negative length/offset");
+  if (n == 0) return B200_OK;
+  if (!c->data || (a && b && !b->data) || !out_data) return b200_fail(ctx, B200_INVALID, "arithmetic: null buffer");
+  if (out_validity) {
+    const BitmapRef va = a ? make_bitmap_ref(a->validity, a->offset) : BitmapRef{nullptr, 0};
+    const BitmapRef vb = b ? make_bitmap_ref(b->validity, b->offset) : BitmapRef{nullptr, 0};
+    const int64_t words = (n + 31) / 32;
+    bitmap_and_kernel<<<unsigned((words + 255) / 256), 256, 0, ctx->stream>>>(va, vb, n, reinterpret_cast<uint32_t*>(out_validity));
+    B200_LAUNCHED(ctx);
+  }
+  switch (c->type) {
+    case B200_UINT8: return launch_arith<uint8_t>(ctx, op, a, a_scalar, b, b_scalar, n, out_data);
+    case B200_INT8: return launch_arith<int8_t>(ctx, op, a, a_scalar, b, b_scalar, n, out_data);
+    case B200_UINT16: return launch_arith<uint16_t>(ctx, op, a, a_scalar, b, b_scalar, n, out_data);
+    case B200_INT16: return launch_arith<int16_t>(ctx, op, a, a_scalar, b, b_scalar, n, out_data);
+    case B200_UINT32: return launch_arith<uint32_t>(ctx, op, a, a_scalar, b, b_scalar, n, out_data);
+    case B200_INT32: return launch_arith<int32_t>(ctx, op, a, a_scalar, b, b_scalar, n, out_data);
+    case B200_UINT64: return launch_arith<uint64_t>(ctx, op, a, a_scalar, b, b_scalar, n, out_data);
+    case B200_INT64: return launch_arith<int64_t>(ctx, op, a, a_scalar, b, b_scalar, n, out_data);
+    case B200_FLOAT: return launch_arith<float>(ctx, op, a, a_scalar, b, b_scalar, n, out_data);
+    case B200_DOUBLE: return launch_arith<double>(ctx, op, a, a_scalar, b, b_scalar, n, out_data);
+    default: break;
+  }
+  return b200_fail(ctx, B200_NOT_IMPLEMENTED, "arithmetic: no kernel for type %d", c->type);
+}
 
 int b200_filter_plan_bytes(int64_t mask_length, size_t* out_bytes) {
   if (!out_bytes || mask_length < 0) return B200_INVALID;

@@ -49,6 +49,28 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+_JSON_FD = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on
+    rank 0), so fd 1 is pointed at stderr for the whole run and the JSON line goes to the original stdout."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _JSON_FD is None:
+        os.write(1, data)
+    else:
+        os.write(_JSON_FD, data)
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -426,7 +448,7 @@ def reference_arm(args):
         "input_gbs": r["rows_per_s"] * wl.input_bytes() / wl.n / 1e9,
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -444,7 +466,7 @@ def kernel_times(ctx, names):
     return out
 
 
-ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume", "compare_scalar", "partition_plan", "partition_scatter", "sort_partition")
+ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume", "compare_scalar", "arithmetic", "partition_plan", "partition_scatter", "sort_partition")
 
 
 def time_device(ctx, wl, cols_, steps, warmup, world, dist_step=None):
@@ -653,7 +675,7 @@ def gpu_arm(args):
         }
         if extras:
             line["workloads"] = extras
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -671,6 +693,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    claim_stdout()
     if args.warmup < 3 and args.impl == "b200":
         log("bench: warmup raised to 3 (timing rules)")
         args.warmup = 3

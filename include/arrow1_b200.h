@@ -155,6 +155,22 @@ B200_API const int64_t* b200_filter_plan_length_ptr(const void* plan);
 B200_API int b200_compare_scalar(b200_ctx* ctx, const b200_col* values, int op,
                                  const void* scalar /* host */, void* out_bitmap);
 
+/* ---- derived-column producers ------------------------------------------------
+ * == "add", "subtract", "multiply" of compute/kernels/scalar_arithmetic.cc (the unchecked forms: integers
+ * wrap like the reference's unsigned-cast arithmetic, :75-121, floats are plain IEEE operations, never
+ * contracted into an FMA; a NaN result carries the GPU's canonical NaN payload) on numeric columns of ONE type.  Either side may be a scalar (a HOST pointer to one
+ * value of that type, with that side's column pointer NULL); at least one side is a column.
+ *   op: 0 add, 1 subtract, 2 multiply.
+ *   a / b: column, or NULL when that operand is the scalar a_scalar / b_scalar.
+ *   out_data: device, length * width bytes, every slot computed (also under nulls, like ScalarBinary).
+ *   out_validity: device bitmap at bit offset 0, ceil(length / 32) whole words — the AND of the operands'
+ *     validity (NullHandling::INTERSECTION, exec.cc PropagateNulls); pass NULL when neither operand has
+ *     nulls.  The result's null_count is left to the caller (-1 = unknown, as the reference leaves it). */
+typedef enum b200_arith_op { B200_ADD = 0, B200_SUBTRACT = 1, B200_MULTIPLY = 2 } b200_arith_op;
+B200_API int b200_arithmetic(b200_ctx* ctx, int op, const b200_col* a, const void* a_scalar /* host */,
+                             const b200_col* b, const void* b_scalar /* host */, void* out_data,
+                             void* out_validity /* nullable */);
+
 /* ---- SortIndices --------------------------------------------------------------------------
  * order: 0 = SortOrder::Ascending, 1 = SortOrder::Descending (api_vector.h:61-66).
  * == ArraySortIndices<UInt64Type, T>::Exec with ArrayCompareSorter / ArrayCountOrCompareSorter

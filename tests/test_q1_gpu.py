@@ -65,6 +65,7 @@ def test_q1_pipeline_matches_oracle(ctx, n):
     mask = Column.from_numpy(hship.values() <= compute.Q1_SHIPDATE_CUTOFF)
     filt = [oracle.filter(c, mask, 0, kind=ORACLE) for c in (hrf, hls, hqty, hprice, hdisc)]
     fcols = [Column.from_numpy(f.values().copy()) for f in filt]
+    fcols.append(Column.from_numpy(fcols[3].values() * (1.0 - fcols[4].values())))   # disc_price, IEEE double ops
     specs = compute.q1_aggregates()
     want = oracle.groupby([fcols[0], fcols[1]], [a for _, a in specs], [fcols[2 + i] for i, _ in specs], kind=ORACLE)
 
@@ -72,3 +73,50 @@ def test_q1_pipeline_matches_oracle(ctx, n):
     b = GroupRes(want.num_groups, want.aggs, want.keys)
     assert a.num_groups == b.num_groups and a.num_groups <= 4   # A/F, N/F, N/O, R/F
     assert_group_equal(a, b, [s for _, s in specs], rtol=1e-12)
+
+
+NP_ARITH = {"add": np.add, "subtract": np.subtract, "multiply": np.multiply}
+
+
+@pytest.mark.parametrize("t", [cols.INT8, cols.UINT8, cols.INT16, cols.UINT16, cols.INT32, cols.UINT32, cols.INT64,
+                               cols.UINT64, cols.FLOAT, cols.DOUBLE])
+def test_arithmetic_matches_wrapping_and_ieee_semantics(ctx, t):
+    """add / subtract / multiply (scalar_arithmetic.cc:69-190, unchecked): integers wrap, floats are single IEEE
+    operations; validity = AND of the operands'; array-array, array-scalar and scalar-array forms; sliced inputs."""
+    rng = np.random.default_rng(500 + t)
+    for n in (1, 33, 1024, 100_003):
+        a = rand_column(rng, t, n, 0.1, offset=3, special=(t in (cols.FLOAT, cols.DOUBLE)))
+        b = rand_column(rng, t, n, 0.0 if n == 33 else 0.2, offset=5, special=(t in (cols.FLOAT, cols.DOUBLE)))
+        va, vb = a.values(), b.values()
+        s = va[n // 2]
+        if va.dtype.kind == "f" and not np.isfinite(s):
+            s = va.dtype.type(1.5)
+        da, db = a.to_device(), b.to_device()
+        for op, fn in NP_ARITH.items():
+            with np.errstate(all="ignore"):
+                for got, want, valid in (
+                        (capi.arithmetic(ctx, op, da, db), fn(va, vb), a.valid() & b.valid()),
+                        (capi.arithmetic(ctx, op, da, s), fn(va, s), a.valid()),
+                        (capi.arithmetic(ctx, op, s, db), fn(s, vb), b.valid())):
+                    h = got.to_host()
+                    want = want.astype(va.dtype)
+                    gv = h.values()
+                    if va.dtype.kind == "f":   # a NaN result carries the GPU's canonical payload, not the x86 one
+                        nan = np.isnan(want)
+                        np.testing.assert_array_equal(np.isnan(gv), nan)
+                        gv, want = gv[~nan], want[~nan]
+                    assert gv.tobytes() == want.tobytes(), "%s type %d n %d" % (op, t, n)
+                    np.testing.assert_array_equal(h.valid(), valid)
+
+
+def test_arithmetic_errors(ctx):
+    from arrow1_b200.capi import B200Error
+    a = Column.from_numpy(np.arange(10, dtype=np.int32)).to_device()
+    b = Column.from_numpy(np.arange(11, dtype=np.int32)).to_device()
+    c = Column.from_numpy(np.arange(10, dtype=np.int64)).to_device()
+    with pytest.raises(B200Error) as e:
+        capi.arithmetic(ctx, "add", a, b)
+    assert e.value.code == 4 and "same length" in str(e.value)
+    with pytest.raises(B200Error) as e:
+        capi.arithmetic(ctx, "add", a, c)
+    assert e.value.code == 10
