@@ -439,10 +439,16 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
   // of the kernel's stall samples) and before the shared-memory scatter, which hides the first trip.
   const uint32_t* base_hist = p.hist + d * kBinStride;
   uint32_t look[kLook];
+  uint32_t look2[kLook];   // class pass: threads 0 / 1 also own the NaN / null bins (256 / 257)
   if (tile > 0 && t < 256) {
 #pragma unroll
     for (int j = 0; j < kLook; ++j)
       look[j] = tile - 1 - j >= 0 ? ld_volatile_u32(state + t - (j + 1) * kBinStride) : kStatusInclusive;
+    if (kClass && t < 2) {
+#pragma unroll
+      for (int j = 0; j < kLook; ++j)
+        look2[j] = tile - 1 - j >= 0 ? ld_volatile_u32(state + 256 + t - (j + 1) * kBinStride) : kStatusInclusive;
+    }
   }
 
   // ---- scatter into shared memory in tile-sorted order (needs tile_prefix + warp offsets only)
@@ -464,17 +470,17 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
     }
   }
   // ---- resolve the look-back
-  if (t < 256) {
+  auto resolve = [&](const int b, uint32_t (&lk)[kLook]) {
     uint32_t excl = 0;
     if (tile > 0) {
-      int64_t back = tile - 1;  // tile look[0] belongs to
+      int64_t back = tile - 1;  // tile lk[0] belongs to
       uint32_t spins = 0;
       bool done = false;
       while (!done) {
         int j = 0;
 #pragma unroll
         for (; j < kLook; ++j) {
-          const uint32_t v = look[j];
+          const uint32_t v = lk[j];
           const uint32_t status = v & ~kValueMask;
           if (status == 0) break;
           excl += v & kValueMask;
@@ -492,37 +498,15 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
         if (j == 0) __nanosleep(40);  // the predecessor has not published yet: do not burn issue slots
 #pragma unroll
         for (int jj = 0; jj < kLook; ++jj)
-          look[jj] = back - jj >= 0 ? ld_volatile_u32(state + t - (tile - back + jj) * kBinStride) : kStatusInclusive;
+          lk[jj] = back - jj >= 0 ? ld_volatile_u32(state + b - (tile - back + jj) * kBinStride) : kStatusInclusive;
       }
-      st_volatile_u32(state + t, kStatusInclusive | ((excl + s.tile_count[t]) & kValueMask));
+      st_volatile_u32(state + b, kStatusInclusive | ((excl + s.tile_count[b]) & kValueMask));
     }
-    s.bin_delta[t] = base_hist[t] + excl - s.tile_prefix[t];
-    if (kClass && t < 2) {  // the NaN / null bins: plain serial walk (only the class pass has them)
-      const int b = 256 + t;
-      uint32_t e2 = 0;
-      if (tile > 0) {
-        const uint32_t* st = state + b - kBinStride;
-        int64_t back = tile - 1;
-        uint32_t spins = 0;
-        while (true) {
-          const uint32_t v = ld_volatile_u32(st);
-          const uint32_t status = v & ~kValueMask;
-          if (status == 0) {
-            if (++spins > (1u << 26)) {
-              atomicExch(p.err, 1u);
-              break;
-            }
-            continue;
-          }
-          e2 += v & kValueMask;
-          if (status == kStatusInclusive || back == 0) break;
-          --back;
-          st -= kBinStride;
-        }
-        st_volatile_u32(state + b, kStatusInclusive | ((e2 + s.tile_count[b]) & kValueMask));
-      }
-      s.bin_delta[b] = base_hist[b] + e2 - s.tile_prefix[b];
-    }
+    s.bin_delta[b] = base_hist[b] + excl - s.tile_prefix[b];
+  };
+  if (t < 256) {
+    resolve(t, look);
+    if (kClass && t < 2) resolve(256 + t, look2);
   }
   __syncthreads();
 
