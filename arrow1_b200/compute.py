@@ -1,6 +1,7 @@
 """Host-side mirror of the reference's public entry points for the hot path.
 
     Filter(values, mask, null_selection)      == compute::Filter        (compute/api_vector.cc:94-99)
+    Take(values, indices, boundscheck)        == compute::Take          (compute/api_vector.cc:101-105)
     SortIndices(values, order)                == compute::SortIndices   (compute/api_vector.cc:48-53)
     GroupBy(arguments, keys, aggregates)      == compute::internal::GroupBy
                                                  (compute/kernels/hash_aggregate.cc:890-966)
@@ -139,6 +140,26 @@ def SortIndices(values: Column, order: int = ASCENDING, ctx: Optional[capi.Conte
         ctx.stream.synchronize()
     Transfer.d2h = values.length * 8
     return h.view(np.uint64)
+
+
+def Take(values: Column, indices, boundscheck: bool = True, ctx: Optional[capi.Context] = None) -> Column:
+    """== compute::Take (compute/api_vector.cc:101-105) for fixed-width values.  Host columns are staged to the
+    device and the result comes back to the host; device columns (or a device index tensor from SortIndices) stay."""
+    ctx = ctx or default_context()
+    host = not values.on_device
+    dv, b0 = _h2d(values, ctx)
+    di, b1 = (indices, 0) if isinstance(indices, torch.Tensor) else _h2d(indices, ctx)
+    out = capi.take(ctx, dv, di, boundscheck)
+    Transfer.h2d, Transfer.d2h = b0 + b1, 0
+    if not host:
+        return out
+    bits = BITS[out.type]
+    nd = (out.length + 7) // 8 if bits == 1 else out.length * (bits // 8)
+    nv = (out.length + 7) // 8
+    data, validity = _d2h(out.data, nd), _d2h(out.validity, nv)
+    ctx.stream.synchronize()
+    Transfer.d2h = nd + nv
+    return Column(out.type, data, validity, out.length, 0, out.null_count)
 
 
 class Pending:

@@ -366,6 +366,90 @@ int launch_compare(b200_ctx* ctx, const b200_col* values, const void* scalar, in
   return B200_OK;
 }
 
+// ---- Take: out[i] = values[indices[i]] (vector_selection.cc:273-469)
+struct TakeArgs {
+  const void* vdata;       // values, shifted by the element offset (not for bool)
+  BitmapRef vbits;         // bool values
+  BitmapRef vv;            // values validity
+  int64_t vlen;
+  const void* idata;       // indices, shifted by the element offset
+  BitmapRef iv;            // indices validity
+  int32_t itype;
+  int64_t n;
+  void* out;
+  uint32_t* out_valid;
+  unsigned long long* counters;   // [0] valid rows, [1] first row with an out-of-bounds index (or ~0)
+};
+
+__device__ __forceinline__ bool take_index(const TakeArgs& a, int64_t row, uint64_t* ix) {
+  // -> false if the index is negative (signed types); *ix is the index as an unsigned number otherwise
+  switch (a.itype) {
+    case B200_INT8: { const int8_t v = reinterpret_cast<const int8_t*>(a.idata)[row]; *ix = uint64_t(int64_t(v)); return v >= 0; }
+    case B200_UINT8: *ix = reinterpret_cast<const uint8_t*>(a.idata)[row]; return true;
+    case B200_INT16: { const int16_t v = reinterpret_cast<const int16_t*>(a.idata)[row]; *ix = uint64_t(int64_t(v)); return v >= 0; }
+    case B200_UINT16: *ix = reinterpret_cast<const uint16_t*>(a.idata)[row]; return true;
+    case B200_INT32: { const int32_t v = reinterpret_cast<const int32_t*>(a.idata)[row]; *ix = uint64_t(int64_t(v)); return v >= 0; }
+    case B200_UINT32: *ix = reinterpret_cast<const uint32_t*>(a.idata)[row]; return true;
+    case B200_INT64: { const int64_t v = reinterpret_cast<const int64_t*>(a.idata)[row]; *ix = uint64_t(v); return v >= 0; }
+    default: *ix = reinterpret_cast<const uint64_t*>(a.idata)[row]; return true;
+  }
+}
+
+constexpr int kTakeItems = 4;   // gathers in flight per thread
+
+template <typename V, bool kBool>
+__global__ void __launch_bounds__(256) take_kernel(const __grid_constant__ TakeArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t base = warp * (32 * kTakeItems);
+  if (base >= a.n) return;
+  uint64_t ix[kTakeItems];
+  bool ok[kTakeItems];
+#pragma unroll
+  for (int k = 0; k < kTakeItems; ++k) {
+    const int64_t row = base + k * 32 + lane;
+    ix[k] = 0;
+    ok[k] = false;
+    if (row < a.n && bitmap_get(a.iv, row)) {
+      const bool nonneg = take_index(a, row, &ix[k]);
+      if (nonneg && ix[k] < uint64_t(a.vlen)) ok[k] = true;
+      else atomicMin(a.counters + 1, (unsigned long long)row);
+    }
+  }
+  V val[kTakeItems];
+#pragma unroll
+  for (int k = 0; k < kTakeItems; ++k) {
+    val[k] = V(0);
+    if (ok[k]) {
+      ok[k] = bitmap_get(a.vv, int64_t(ix[k]));
+      if (ok[k]) val[k] = kBool ? V(bitmap_get(a.vbits, int64_t(ix[k]))) : reinterpret_cast<const V*>(a.vdata)[ix[k]];
+    }
+  }
+  uint32_t valid_rows = 0;
+#pragma unroll
+  for (int k = 0; k < kTakeItems; ++k) {
+    const int64_t row = base + k * 32 + lane;
+    const unsigned word = __ballot_sync(0xffffffffu, ok[k]);
+    if (kBool) {
+      const unsigned bits = __ballot_sync(0xffffffffu, ok[k] && val[k] != V(0));
+      if (lane == 0 && base + k * 32 < a.n) reinterpret_cast<uint32_t*>(a.out)[(base >> 5) + k] = bits;
+    } else if (row < a.n) {
+      reinterpret_cast<V*>(a.out)[row] = val[k];
+    }
+    if (lane == 0 && base + k * 32 < a.n) a.out_valid[(base >> 5) + k] = word;
+    valid_rows += __popc(word);
+  }
+  if (lane == 0 && valid_rows) atomicAdd(a.counters, (unsigned long long)valid_rows);
+}
+
+template <typename V, bool kBool>
+int launch_take(b200_ctx* ctx, const TakeArgs& a) {
+  const int64_t warps = (a.n + 32 * kTakeItems - 1) / (32 * kTakeItems);
+  const unsigned grid = unsigned((warps * 32 + 255) / 256);
+  B200_TIMED(ctx, "take", (take_kernel<V, kBool><<<grid, 256, 0, ctx->stream>>>(a)));
+  return B200_OK;
+}
+
 // ---- add / subtract / multiply (scalar_arithmetic.cc, unchecked forms)
 template <typename T>
 struct ArithTraits {
@@ -432,6 +516,70 @@ int launch_arith(b200_ctx* ctx, int op, const b200_col* a, const void* a_scalar,
 }  // namespace
 
 extern "C" {
+
+int b200_take(b200_ctx* ctx, const b200_col* values, const b200_col* indices, int boundscheck, void* out_data,
+              void* out_validity, int64_t* out_null_count) {
+  if (!ctx) return B200_INVALID;
+  if (!values || !indices) return b200_fail(ctx, B200_INVALID, "take: null argument");
+  const int vbits = b200_type_bits(values->type);
+  if (vbits == 0) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "take: unsupported values type %d", values->type);
+  const int ibits = b200_type_bits(indices->type);
+  if (ibits < 8 || indices->type == B200_FLOAT || indices->type == B200_DOUBLE)
+    return b200_fail(ctx, B200_TYPE_ERROR, "take: indices must be an integer column, got type %d", indices->type);
+  if (values->length < 0 || values->offset < 0 || indices->length < 0 || indices->offset < 0)
+    return b200_fail(ctx, B200_INVALID, "take: negative length/offset");
+  const int64_t n = indices->length;
+  if (out_null_count) *out_null_count = 0;
+  if (n == 0) return B200_OK;
+  if (!indices->data || !out_data || !out_validity || (values->length > 0 && !values->data))
+    return b200_fail(ctx, B200_INVALID, "take: null buffer (the output validity bitmap is always produced)");
+  B200_RETURN_NOT_OK(b200_ctx_reserve_scratch(ctx, 256));
+  unsigned long long* counters = reinterpret_cast<unsigned long long*>(ctx->scratch);
+  const unsigned long long init[2] = {0ull, ~0ull};
+  ctx->host_words[8] = int64_t(init[0]);
+  ctx->host_words[9] = int64_t(init[1]);
+  B200_CUDA(ctx, cudaMemcpyAsync(counters, ctx->host_words + 8, 16, cudaMemcpyHostToDevice, ctx->stream));
+  TakeArgs a;
+  a.vdata = vbits >= 8 ? reinterpret_cast<const char*>(values->data) + values->offset * (vbits / 8) : nullptr;
+  a.vbits = make_bitmap_ref(values->data, values->offset);
+  a.vv = (values->validity && values->null_count != 0) ? make_bitmap_ref(values->validity, values->offset) : BitmapRef{nullptr, 0};
+  a.vlen = values->length;
+  a.idata = reinterpret_cast<const char*>(indices->data) + indices->offset * (ibits / 8);
+  a.iv = (indices->validity && indices->null_count != 0) ? make_bitmap_ref(indices->validity, indices->offset) : BitmapRef{nullptr, 0};
+  a.itype = indices->type;
+  a.n = n;
+  a.out = out_data;
+  a.out_valid = reinterpret_cast<uint32_t*>(out_validity);
+  a.counters = counters;
+  switch (vbits) {
+    case 1: B200_RETURN_NOT_OK((launch_take<uint8_t, true>(ctx, a))); break;
+    case 8: B200_RETURN_NOT_OK((launch_take<uint8_t, false>(ctx, a))); break;
+    case 16: B200_RETURN_NOT_OK((launch_take<uint16_t, false>(ctx, a))); break;
+    case 32: B200_RETURN_NOT_OK((launch_take<uint32_t, false>(ctx, a))); break;
+    default: B200_RETURN_NOT_OK((launch_take<uint64_t, false>(ctx, a))); break;
+  }
+  if (boundscheck || out_null_count) {
+    B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 8, counters, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const uint64_t bad_row = uint64_t(ctx->host_words[9]);
+    if (boundscheck && bad_row != ~uint64_t(0)) {
+      // the offending value, for the reference's message (error path only)
+      int64_t raw = 0;
+      B200_CUDA(ctx, cudaMemcpy(&raw, reinterpret_cast<const char*>(a.idata) + bad_row * (ibits / 8), ibits / 8, cudaMemcpyDeviceToHost));
+      long long shown;
+      switch (indices->type) {
+        case B200_INT8: shown = (long long)(int8_t)raw; break;
+        case B200_INT16: shown = (long long)(int16_t)raw; break;
+        case B200_INT32: shown = (long long)(int32_t)raw; break;
+        default: shown = (long long)raw; break;   // little-endian: narrower unsigned values are zero-extended
+      }
+      if (indices->type == B200_UINT64) return b200_fail(ctx, B200_INDEX_ERROR, "Index %llu out of bounds", (unsigned long long)raw);
+      return b200_fail(ctx, B200_INDEX_ERROR, "Index %lld out of bounds", shown);
+    }
+    if (out_null_count) *out_null_count = n - ctx->host_words[8];
+  }
+  return B200_OK;
+}
 
 int b200_arithmetic(b200_ctx* ctx, int op, const b200_col* a, const void* a_scalar, const b200_col* b, const void* b_scalar,
                     void* out_data, void* out_validity) {

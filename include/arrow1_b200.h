@@ -220,6 +220,22 @@ B200_API int b200_sort_pairs32(b200_ctx* ctx, const uint64_t* keys, const uint32
                                int64_t length, uint64_t* out_keys /* nullable */,
                                uint64_t* out_payload, void* scratch, size_t scratch_bytes);
 
+/* ---- Take (the gather that follows SortIndices) -----------------------------------
+ * == compute::Take(values, indices, TakeOptions(boundscheck)) on a fixed-width column: PrimitiveTake /
+ * PrimitiveTakeImpl / BooleanTakeImpl (kernels/vector_selection.cc:273-469, 493-526).
+ *   out[i] = values[indices[i]]; a null index or a null value gives a null whose data is zero.
+ *   indices: any integer type (the uint64 output of b200_sort_indices included), optional validity.
+ *   out_data: indices->length elements of the value width (ceil(length / 32) whole words for B200_BOOL).
+ *   out_validity: REQUIRED, ceil(length / 32) whole 32-bit words: like the reference, the bitmap is always
+ *     produced.
+ *   boundscheck != 0: a valid index that is negative or >= values->length fails with B200_INDEX_ERROR
+ *     "Index N out of bounds" (CheckIndexBounds, util/int_util.cc) — this reads a flag back and synchronises.
+ *     boundscheck == 0 matches TakeOptions::NoBoundsCheck(): such an index is undefined behaviour upstream;
+ *     here the row comes out null.
+ *   out_null_count (host, nullable): exact null count of the result (synchronises). */
+B200_API int b200_take(b200_ctx* ctx, const b200_col* values, const b200_col* indices, int boundscheck,
+                       void* out_data, void* out_validity, int64_t* out_null_count /* host, nullable */);
+
 /* ---- Range partition fused with the exchange (multi-GPU sample sort over NVLink peer memory) ----
  * The partition's scatter kernel stores every destination's (key, row) run straight into THAT rank's receive
  * buffer through a peer mapping, so the all-to-all is the scatter itself: no staging copy, no separate

@@ -152,6 +152,14 @@ def filter(values: Column, mask: Column, null_selection: int = 0, kind: str = "p
     return FilterResult(values.type, oc.length, oc.null_count, bool(has_validity.value), data, validity)
 
 
+def take(values: Column, indices: Column, boundscheck: bool = True, kind: str = "port") -> FilterResult:
+    """compute::Take(values, indices): FilterResult-shaped (the validity bitmap is always present)."""
+    oc, data, validity = _out_col(values.type, indices.length)
+    v, i = values.desc(), indices.desc()
+    _check(kind, _fn(kind, "take")(C.byref(v), C.byref(i), C.c_int(1 if boundscheck else 0), C.byref(oc)))
+    return FilterResult(values.type, oc.length, oc.null_count, True, data, validity)
+
+
 def sort_indices(values: Column, order: int = 0, index_base: int = 0, kind: str = "port") -> np.ndarray:
     out = np.zeros(max(values.length, 1), dtype=np.uint64)
     v = values.desc()

@@ -190,6 +190,73 @@ B200_API int oracle_filter(const b200_col* values, const b200_col* mask, int nul
   return FilterImpl(values, mask, null_selection, out, has_validity);
 }
 
+// PrimitiveTake / PrimitiveTakeImpl / BooleanTakeImpl (vector_selection.cc:273-469, 493-526) with CheckIndexBounds
+// (util/int_util.cc): out[i] = values[indices[i]]; a null index or a null value gives a null with zero data; the
+// validity bitmap is always produced; null_count exact.  Returns 7 (IndexError) on an out-of-bounds index.
+B200_API int oracle_take(const b200_col* values, const b200_col* indices, int boundscheck, b200_out_col* out) {
+  const int vbits = BitsOf(values->type);
+  const int ibits = BitsOf(indices->type);
+  const bool isigned = indices->type == B200_INT8 || indices->type == B200_INT16 || indices->type == B200_INT32 ||
+                       indices->type == B200_INT64;
+  if (ibits < 8 || indices->type == B200_FLOAT || indices->type == B200_DOUBLE) return 3;   // TypeError
+  const uint8_t* ivalid = static_cast<const uint8_t*>(indices->validity);
+  const uint8_t* vvalid = static_cast<const uint8_t*>(values->validity);
+  const int64_t n = indices->length;
+  auto get_bit = [](const uint8_t* b, int64_t i) { return (b[i >> 3] >> (i & 7)) & 1; };
+  auto index_at = [&](int64_t i, bool* negative) -> uint64_t {
+    const int64_t p = indices->offset + i;
+    *negative = false;
+    switch (indices->type) {
+      case B200_INT8: { int8_t v = static_cast<const int8_t*>(indices->data)[p]; *negative = v < 0; return uint64_t(int64_t(v)); }
+      case B200_UINT8: return static_cast<const uint8_t*>(indices->data)[p];
+      case B200_INT16: { int16_t v = static_cast<const int16_t*>(indices->data)[p]; *negative = v < 0; return uint64_t(int64_t(v)); }
+      case B200_UINT16: return static_cast<const uint16_t*>(indices->data)[p];
+      case B200_INT32: { int32_t v = static_cast<const int32_t*>(indices->data)[p]; *negative = v < 0; return uint64_t(int64_t(v)); }
+      case B200_UINT32: return static_cast<const uint32_t*>(indices->data)[p];
+      case B200_INT64: { int64_t v = static_cast<const int64_t*>(indices->data)[p]; *negative = v < 0; return uint64_t(v); }
+      default: return static_cast<const uint64_t*>(indices->data)[p];
+    }
+  };
+  (void)isigned;
+  if (boundscheck) {
+    for (int64_t i = 0; i < n; ++i) {
+      if (ivalid && !get_bit(ivalid, indices->offset + i)) continue;
+      bool neg;
+      const uint64_t ix = index_at(i, &neg);
+      if (neg || ix >= uint64_t(values->length)) return 7;
+    }
+  }
+  uint8_t* od = static_cast<uint8_t*>(out->data);
+  uint8_t* ov = static_cast<uint8_t*>(out->validity);
+  std::memset(ov, 0, size_t((n + 7) / 8));
+  if (vbits == 1) std::memset(od, 0, size_t((n + 7) / 8));
+  int64_t valid_count = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    bool ok = !ivalid || get_bit(ivalid, indices->offset + i);
+    uint64_t ix = 0;
+    if (ok) {
+      bool neg;
+      ix = index_at(i, &neg);
+      ok = !vvalid || get_bit(vvalid, values->offset + int64_t(ix));
+    }
+    if (ok) {
+      ++valid_count;
+      ov[i >> 3] |= uint8_t(1u << (i & 7));
+      const int64_t src = values->offset + int64_t(ix);
+      if (vbits == 1) {
+        if (get_bit(static_cast<const uint8_t*>(values->data), src)) od[i >> 3] |= uint8_t(1u << (i & 7));
+      } else {
+        std::memcpy(od + i * (vbits / 8), static_cast<const uint8_t*>(values->data) + src * (vbits / 8), size_t(vbits / 8));
+      }
+    } else if (vbits != 1) {
+      std::memset(od + i * (vbits / 8), 0, size_t(vbits / 8));
+    }
+  }
+  out->length = n;
+  out->null_count = n - valid_count;
+  return 0;
+}
+
 B200_API int oracle_filter_count(const b200_col* mask, int null_sel, int64_t* out_len) {
   // GetFilterOutputSize (vector_selection.cc:61-88)
   int64_t n = 0;

@@ -127,6 +127,17 @@ B200_API int ref_filter_timed(const b200_col* values, const b200_col* mask, int 
   return 0;
 }
 
+// compute::Take(values, indices, TakeOptions(boundscheck)).  out buffers sized for indices->length elements; the
+// reference always allocates the validity bitmap (PrimitiveTake, vector_selection.cc:493-506).
+B200_API int ref_take(const b200_col* values, const b200_col* indices, int boundscheck, b200_out_col* out) {
+  compute::TakeOptions opts(boundscheck != 0);
+  compute::ExecContext ctx;
+  auto res = compute::Take(Datum(Wrap(*values)), Datum(Wrap(*indices)), opts, &ctx);
+  if (!res.ok()) return Fail(res.status());
+  CopyOut(*res.ValueOrDie().array(), out);
+  return 0;
+}
+
 // compute::SortIndices(Array, order); index_base is added afterwards (ChunkedArraySorter offset)
 B200_API int ref_sort_indices(const b200_col* values, int order, uint64_t index_base, uint64_t* out) {
   compute::ExecContext ctx;

@@ -93,3 +93,31 @@ def test_oracle_builds_and_exports():
     lib, _ = oracle._lib("port")
     for name in ("oracle_filter", "oracle_filter_count", "oracle_sort_indices", "oracle_groupby", "oracle_version"):
         assert hasattr(lib, name)
+
+
+@needs_ref
+@pytest.mark.parametrize("t", ALL_NUMERIC + [cols.BOOL])
+def test_take_port_matches_reference(t):
+    """oracle_take (the restatement of PrimitiveTake, vector_selection.cc:273-526) against compute::Take itself."""
+    from arrow1_b200.columns import Column
+    rng = np.random.default_rng(1200 + t)
+    for nv, ni in ((1, 4), (50, 500), (1000, 5000)):
+        for vnull, inull in ((0.0, 0.0), (0.2, 0.0), (0.0, 0.3), (0.4, 0.4)):
+            if t == cols.BOOL:
+                values = Column.from_numpy(rng.random(nv + 2) < 0.5, (rng.random(nv + 2) >= vnull) if vnull else None, offset=2)
+            else:
+                values = rand_column(rng, t, nv, vnull, offset=2, special=True)
+            for dt in (np.int8, np.uint16, np.int32, np.uint64):
+                hi = min(nv, int(np.iinfo(dt).max))
+                ix = rng.integers(0, hi, size=ni + 5).astype(dt)
+                indices = Column.from_numpy(ix, (rng.random(ni + 5) >= inull) if inull else None, offset=5)
+                a = oracle.take(values, indices, True, kind="port")
+                b = oracle.take(values, indices, True, kind="reference")
+                assert a.length == b.length and a.null_count == b.null_count
+                assert a.data_bytes() == b.data_bytes() and a.validity_bytes() == b.validity_bytes()
+    values = rand_column(rng, t, 20, 0.0) if t != cols.BOOL else Column.from_numpy(rng.random(20) < 0.5)
+    for bad in ([0, 1, 50], [-1]):
+        for kind in ("port", "reference"):
+            with pytest.raises(oracle.OracleError) as e:
+                oracle.take(values, Column.from_numpy(np.array(bad, dtype=np.int64)), True, kind=kind)
+            assert e.value.code == 7
