@@ -196,6 +196,56 @@ Result<std::shared_ptr<ArrayData>> FilterArray(DeviceState* dev, const ArrayData
   return ArrayData::Make(values.type, out_len, {std::move(out_validity), std::move(out_data)}, out_null_count);
 }
 
+// ---- Take ----------------------------------------------------------------------------------------
+// == PrimitiveTake (vector_selection.cc:493-526): boundscheck -> PreallocateData (validity always) -> Exec
+Result<std::shared_ptr<ArrayData>> TakeArray(DeviceState* dev, const ArrayData& values, const ArrayData& indices,
+                                             bool boundscheck) {
+  ARROW_ASSIGN_OR_RAISE(const int32_t vtype, PhysicalType(*values.type));
+  if (!is_integer(indices.type->id())) return Status::NotImplemented("Take indices must be integer type");
+  ARROW_ASSIGN_OR_RAISE(const int32_t itype, NumericType(*indices.type));
+  b200_col v, i;
+  RETURN_NOT_OK(ToCol(values, vtype, &v));
+  RETURN_NOT_OK(ToCol(indices, itype, &i));
+  std::lock_guard<std::mutex> lock(dev->mutex);
+  const int bits = vtype == B200_BOOL ? 1 : checked_cast<const FixedWidthType&>(*values.type).bit_width();
+  const int64_t n = indices.length;
+  // bitmaps are written as whole 32-bit words
+  const int64_t bitmap_bytes = (n + 31) / 32 * 4;
+  ARROW_ASSIGN_OR_RAISE(auto out_data, AllocateDevice(dev, bits == 1 ? bitmap_bytes : n * (bits / 8)));
+  ARROW_ASSIGN_OR_RAISE(auto out_validity, AllocateDevice(dev, bitmap_bytes));
+  int64_t null_count = 0;
+  B200_OK_OR_RAISE(dev, b200_take(dev->ctx, &v, &i, boundscheck ? 1 : 0, reinterpret_cast<void*>(out_data->address()),
+                                  reinterpret_cast<void*>(out_validity->address()), &null_count));
+  return ArrayData::Make(values.type, n, {std::move(out_validity), std::move(out_data)}, null_count);
+}
+
+struct TakeStateB200 : public KernelState {
+  explicit TakeStateB200(bool boundscheck) : boundscheck(boundscheck) {}
+  bool boundscheck;
+};
+
+const FunctionDoc array_take_doc(
+    "Select values from an array by integer indices (CUDA)",
+    "Same contract as the CPU array_take; inputs and output are CudaBuffer-resident.", {"values", "indices"},
+    "TakeOptions");
+const FunctionDoc take_doc("Select values by integer indices (CUDA)", "Array x Array inputs; see array_take.",
+                           {"input", "indices"}, "TakeOptions");
+const TakeOptions kDefaultTakeOptions = TakeOptions::Defaults();
+
+// == TakeMetaFunction (vector_selection.cc:2028-2081), Array x Array route
+class CudaTakeMetaFunction : public MetaFunction {
+ public:
+  CudaTakeMetaFunction() : MetaFunction("take", Arity::Binary(), &take_doc, &kDefaultTakeOptions) {}
+  Result<Datum> ExecuteImpl(const std::vector<Datum>& args, const FunctionOptions* options,
+                            ExecContext* ctx) const override {
+    if (args[0].kind() == Datum::ARRAY && args[1].kind() == Datum::ARRAY) {
+      return CallFunction("array_take", args, options, ctx);
+    }
+    return Status::NotImplemented("Unsupported types for take operation: values=", args[0].ToString(),
+                                  "indices=", args[1].ToString());
+  }
+};
+
 int NullSelectionOf(const FunctionOptions* options) {
   if (!options) return 0;
   return static_cast<const FilterOptions*>(options)->null_selection_behavior == FilterOptions::EMIT_NULL ? 1 : 0;
@@ -639,6 +689,31 @@ Status RegisterCudaKernels(FunctionRegistry* registry, int device) {
     RETURN_NOT_OK(registry->AddFunction(std::move(func)));
   }
   RETURN_NOT_OK(registry->AddFunction(std::make_shared<CudaFilterMetaFunction>(device)));
+  // array_take: VectorFunction over (primitive array, integer array) (vector_selection.cc:2154-2176)
+  {
+    auto func = std::make_shared<VectorFunction>("array_take", Arity::Binary(), &array_take_doc, &kDefaultTakeOptions);
+    VectorKernel kernel;
+    kernel.mem_allocation = MemAllocation::NO_PREALLOCATE;
+    kernel.null_handling = NullHandling::COMPUTED_NO_PREALLOCATE;
+    kernel.can_execute_chunkwise = false;
+    kernel.init = [](KernelContext*, const KernelInitArgs& args) -> Result<std::unique_ptr<KernelState>> {
+      const bool boundscheck = args.options ? static_cast<const TakeOptions*>(args.options)->boundscheck : true;
+      return std::unique_ptr<KernelState>(new TakeStateB200(boundscheck));
+    };
+    kernel.signature = KernelSignature::Make(
+        {InputType(match::Primitive(), ValueDescr::ARRAY), InputType(match::Integer(), ValueDescr::ARRAY)},
+        OutputType([](KernelContext*, const std::vector<ValueDescr>& descrs) -> Result<ValueDescr> { return descrs[0]; }));
+    kernel.exec = [device](KernelContext* ctx, const ExecBatch& batch, Datum* out) -> Status {
+      ARROW_ASSIGN_OR_RAISE(DeviceState * dev, GetDevice(device));
+      const bool boundscheck = checked_cast<const TakeStateB200*>(ctx->state())->boundscheck;
+      ARROW_ASSIGN_OR_RAISE(auto result, TakeArray(dev, *batch[0].array(), *batch[1].array(), boundscheck));
+      out->value = std::move(result);
+      return Status::OK();
+    };
+    RETURN_NOT_OK(func->AddKernel(std::move(kernel)));
+    RETURN_NOT_OK(registry->AddFunction(std::move(func)));
+  }
+  RETURN_NOT_OK(registry->AddFunction(std::make_shared<CudaTakeMetaFunction>()));
   // array_sort_indices: one kernel per numeric / temporal type (vector_sort.cc:582-595)
   {
     auto func = std::make_shared<VectorFunction>("array_sort_indices", Arity::Unary(), &array_sort_indices_doc, &kDefaultArraySortOptions);

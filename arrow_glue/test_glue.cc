@@ -152,9 +152,9 @@ int main() {
   std::mt19937_64 rng(42);
 
   {  // the registry holds exactly the reference's names for the path
-    for (const char* name : {"filter", "array_filter", "sort_indices", "array_sort_indices", "hash_count", "hash_sum", "hash_min_max", "hash_mean"})
+    for (const char* name : {"filter", "array_filter", "sort_indices", "array_sort_indices", "take", "array_take", "hash_count", "hash_sum", "hash_min_max", "hash_mean"})
       CHECK_TRUE(registry->GetFunction(name).ok(), std::string("registered: ") + name);
-    CHECK_TRUE(registry->GetFunction("take").status().IsKeyError(), "unknown function -> KeyError (registry.cc:62-64)");
+    CHECK_TRUE(registry->GetFunction("unique").status().IsKeyError(), "unknown function -> KeyError (registry.cc:62-64)");
   }
 
   // ---------------- Filter ----------------
@@ -273,6 +273,48 @@ int main() {
         ExpectEqual(got_c, want_c, "sort_indices ChunkedArray (4 chunks) " + col->type()->ToString() + (order == cp::SortOrder::Ascending ? " asc" : " desc"));
       }
     }
+  }
+
+  // ---------------- Take ----------------
+  {
+    const int64_t n = 60000;
+    auto values = MakeRandom<DoubleBuilder, double>(n, rng, 0.1, -1e6, 1e6, true);
+    auto small = MakeRandom<Int16Builder, int16_t>(200, rng, 0.2, -300, 300, false);
+    auto ix32 = MakeRandom<Int32Builder, int32_t>(100000, rng, 0.05, 0, int32_t(n - 1), false);
+    auto ix8 = MakeRandom<UInt8Builder, uint8_t>(5000, rng, 0.0, 0, 199, false);
+    struct Case { std::shared_ptr<Array> v, i; const char* what; };
+    for (const Case& c : {Case{values, ix32, "take double by nullable int32"}, Case{small, ix8, "take int16 by uint8"},
+                          Case{values->Slice(100, 50000), ix32->Slice(7, 9000)->View(int32()).ValueOrDie(), "take sliced values"}}) {
+      // the sliced case needs in-range indices: reduce them on the host first
+      std::shared_ptr<Array> idx = c.i;
+      if (std::string(c.what) == "take sliced values") {
+        Int32Builder b;
+        const auto& src = internal::checked_cast<const Int32Array&>(*c.i);
+        for (int64_t k = 0; k < src.length(); ++k) {
+          if (src.IsNull(k)) ABORT_NOT_OK(b.AppendNull());
+          else ABORT_NOT_OK(b.Append(src.Value(k) % 50000));
+        }
+        idx = GET(b.Finish());
+      }
+      auto want = GET(cp::CallFunction("take", {c.v, idx}, &cpu_ctx)).make_array();
+      auto got = HostArray(GET(cp::CallFunction("take", {DeviceDatum(c.v), DeviceDatum(idx)}, &gpu_ctx)));
+      ExpectEqual(got, want, c.what);
+      CHECK_TRUE(got->null_count() == want->null_count(), std::string(c.what) + " null_count");
+    }
+    // SortIndices -> Take through both registries: the sorted column itself
+    cp::ArraySortOptions asc(cp::SortOrder::Ascending);
+    auto widx = GET(cp::CallFunction("array_sort_indices", {values}, &asc, &cpu_ctx));
+    auto wsorted = GET(cp::CallFunction("take", {Datum(values), widx}, &cpu_ctx)).make_array();
+    auto dvalues = DeviceDatum(values);
+    auto gidx = GET(cp::CallFunction("array_sort_indices", {dvalues}, &asc, &gpu_ctx));
+    auto gsorted = HostArray(GET(cp::CallFunction("take", {dvalues, gidx}, &gpu_ctx)));
+    ExpectEqual(gsorted, wsorted, "take(values, sort_indices(values)) on the device");
+    // out of bounds -> IndexError from both (vector_selection_test.cc: TakeTest index errors)
+    auto bad = Make<Int32Builder, int32_t>({0, 200, 1});
+    auto st_cpu = cp::CallFunction("take", {small, bad}, &cpu_ctx).status();
+    auto st_gpu = cp::CallFunction("take", {DeviceDatum(small), DeviceDatum(bad)}, &gpu_ctx).status();
+    CHECK_TRUE(st_cpu.IsIndexError() && st_gpu.IsIndexError(), "take out of bounds -> IndexError");
+    CHECK_TRUE(st_gpu.message().find("Index 200 out of bounds") != std::string::npos, "take IndexError message names the index");
   }
 
   // ---------------- GroupBy ----------------
