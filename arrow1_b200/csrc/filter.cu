@@ -381,49 +381,55 @@ struct TakeArgs {
   unsigned long long* counters;   // [0] valid rows, [1] first row with an out-of-bounds index (or ~0)
 };
 
+// the index as an unsigned number, and whether it is non-negative (I is the index C type: no per-row dispatch,
+// so the compiler can batch the loads of a thread's rows)
+template <typename I>
 __device__ __forceinline__ bool take_index(const TakeArgs& a, int64_t row, uint64_t* ix) {
-  // -> false if the index is negative (signed types); *ix is the index as an unsigned number otherwise
-  switch (a.itype) {
-    case B200_INT8: { const int8_t v = reinterpret_cast<const int8_t*>(a.idata)[row]; *ix = uint64_t(int64_t(v)); return v >= 0; }
-    case B200_UINT8: *ix = reinterpret_cast<const uint8_t*>(a.idata)[row]; return true;
-    case B200_INT16: { const int16_t v = reinterpret_cast<const int16_t*>(a.idata)[row]; *ix = uint64_t(int64_t(v)); return v >= 0; }
-    case B200_UINT16: *ix = reinterpret_cast<const uint16_t*>(a.idata)[row]; return true;
-    case B200_INT32: { const int32_t v = reinterpret_cast<const int32_t*>(a.idata)[row]; *ix = uint64_t(int64_t(v)); return v >= 0; }
-    case B200_UINT32: *ix = reinterpret_cast<const uint32_t*>(a.idata)[row]; return true;
-    case B200_INT64: { const int64_t v = reinterpret_cast<const int64_t*>(a.idata)[row]; *ix = uint64_t(v); return v >= 0; }
-    default: *ix = reinterpret_cast<const uint64_t*>(a.idata)[row]; return true;
-  }
+  const I v = reinterpret_cast<const I*>(a.idata)[row];
+  *ix = std::is_signed<I>::value ? uint64_t(int64_t(v)) : uint64_t(v);
+  return !std::is_signed<I>::value || v >= I(0);
 }
 
-constexpr int kTakeItems = 4;   // gathers in flight per thread
+constexpr int kTakeItems = 8;   // gathers in flight per thread
 
-template <typename V, bool kBool>
+template <typename V, bool kBool, typename I>
 __global__ void __launch_bounds__(256) take_kernel(const __grid_constant__ TakeArgs a) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const int64_t base = warp * (32 * kTakeItems);
   if (base >= a.n) return;
+  // three batches of independent loads, no branch between the loads of a batch: index validity words and
+  // indices; then value validity bytes and values (addresses clamped to row 0 where the index is unusable)
   uint64_t ix[kTakeItems];
   bool ok[kTakeItems];
+  uint32_t ivw[kTakeItems];
+#pragma unroll
+  for (int k = 0; k < kTakeItems; ++k) ivw[k] = bitmap_load32(a.iv, base + k * 32, a.n);
+  bool nonneg[kTakeItems];
+#pragma unroll
+  for (int k = 0; k < kTakeItems; ++k) {
+    const int64_t row = min(base + k * 32 + lane, a.n - 1);
+    nonneg[k] = take_index<I>(a, row, &ix[k]);
+  }
 #pragma unroll
   for (int k = 0; k < kTakeItems; ++k) {
     const int64_t row = base + k * 32 + lane;
-    ix[k] = 0;
-    ok[k] = false;
-    if (row < a.n && bitmap_get(a.iv, row)) {
-      const bool nonneg = take_index(a, row, &ix[k]);
-      if (nonneg && ix[k] < uint64_t(a.vlen)) ok[k] = true;
-      else atomicMin(a.counters + 1, (unsigned long long)row);
-    }
+    const bool present = row < a.n && ((ivw[k] >> lane) & 1u);
+    ok[k] = present && nonneg[k] && ix[k] < uint64_t(a.vlen);
+    if (present && !ok[k]) atomicMin(a.counters + 1, (unsigned long long)row);
+    if (!ok[k]) ix[k] = 0;
   }
   V val[kTakeItems];
+  bool vvalid[kTakeItems];
 #pragma unroll
   for (int k = 0; k < kTakeItems; ++k) {
-    val[k] = V(0);
-    if (ok[k]) {
-      ok[k] = bitmap_get(a.vv, int64_t(ix[k]));
-      if (ok[k]) val[k] = kBool ? V(bitmap_get(a.vbits, int64_t(ix[k]))) : reinterpret_cast<const V*>(a.vdata)[ix[k]];
-    }
+    vvalid[k] = bitmap_get(a.vv, int64_t(ix[k]));
+    val[k] = kBool ? V(bitmap_get(a.vbits, int64_t(ix[k]))) : reinterpret_cast<const V*>(a.vdata)[ix[k]];
+  }
+#pragma unroll
+  for (int k = 0; k < kTakeItems; ++k) {
+    ok[k] = ok[k] && vvalid[k];
+    if (!ok[k]) val[k] = V(0);
   }
   uint32_t valid_rows = 0;
 #pragma unroll
@@ -442,12 +448,26 @@ __global__ void __launch_bounds__(256) take_kernel(const __grid_constant__ TakeA
   if (lane == 0 && valid_rows) atomicAdd(a.counters, (unsigned long long)valid_rows);
 }
 
-template <typename V, bool kBool>
-int launch_take(b200_ctx* ctx, const TakeArgs& a) {
+template <typename V, bool kBool, typename I>
+int launch_take_i(b200_ctx* ctx, const TakeArgs& a) {
   const int64_t warps = (a.n + 32 * kTakeItems - 1) / (32 * kTakeItems);
   const unsigned grid = unsigned((warps * 32 + 255) / 256);
-  B200_TIMED(ctx, "take", (take_kernel<V, kBool><<<grid, 256, 0, ctx->stream>>>(a)));
+  B200_TIMED(ctx, "take", (take_kernel<V, kBool, I><<<grid, 256, 0, ctx->stream>>>(a)));
   return B200_OK;
+}
+
+template <typename V, bool kBool>
+int launch_take(b200_ctx* ctx, const TakeArgs& a) {
+  switch (a.itype) {
+    case B200_INT8: return launch_take_i<V, kBool, int8_t>(ctx, a);
+    case B200_UINT8: return launch_take_i<V, kBool, uint8_t>(ctx, a);
+    case B200_INT16: return launch_take_i<V, kBool, int16_t>(ctx, a);
+    case B200_UINT16: return launch_take_i<V, kBool, uint16_t>(ctx, a);
+    case B200_INT32: return launch_take_i<V, kBool, int32_t>(ctx, a);
+    case B200_UINT32: return launch_take_i<V, kBool, uint32_t>(ctx, a);
+    case B200_INT64: return launch_take_i<V, kBool, int64_t>(ctx, a);
+    default: return launch_take_i<V, kBool, uint64_t>(ctx, a);
+  }
 }
 
 // ---- add / subtract / multiply (scalar_arithmetic.cc, unchecked forms)
@@ -544,6 +564,11 @@ int b200_take(b200_ctx* ctx, const b200_col* values, const b200_col* indices, in
   a.vbits = make_bitmap_ref(values->data, values->offset);
   a.vv = (values->validity && values->null_count != 0) ? make_bitmap_ref(values->validity, values->offset) : BitmapRef{nullptr, 0};
   a.vlen = values->length;
+  if (values->length == 0) {   // every index is out of range; the clamped gathers read row 0 of the scratch block
+    a.vdata = counters;
+    a.vbits = make_bitmap_ref(counters, 0);
+    a.vv = BitmapRef{nullptr, 0};
+  }
   a.idata = reinterpret_cast<const char*>(indices->data) + indices->offset * (ibits / 8);
   a.iv = (indices->validity && indices->null_count != 0) ? make_bitmap_ref(indices->validity, indices->offset) : BitmapRef{nullptr, 0};
   a.itype = indices->type;

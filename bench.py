@@ -165,6 +165,51 @@ class SortWL(Workload):
         return oracle.sort_indices(host_cols[0], 0, 0, kind=kind)
 
 
+class TakeWL(Workload):
+    """the gather that follows SortIndices — Take(values, SortIndices(values)), i.e. the sorted
+    column itself; the indices are a random permutation of the rows."""
+    kernel = "take"
+    name = "take_sorted"
+    dtype = "u64 (bit copy of int64) + bitmaps, uint64 indices"
+
+    def __init__(self, rows):
+        super().__init__(rows)
+        self.description = "Take(values, SortIndices(values)): %d int64 rows gathered by a random permutation, 1%% nulls" % rows
+
+    def make(self, gen, start=0, n=None):
+        return (gen.sort_c2(n or self.n, "int64", start),)
+
+    def input_bytes(self):
+        return self.n * 16
+
+    def alg_bytes_per_launch(self, launches_per_step):
+        return self.n * (8 + 8 + 8 + 0.25)   # index + value in (plus its validity bit), value + validity bit out
+
+    def prepare(self, ctx, cols_):
+        from arrow1_b200 import capi
+        return {"indices": capi.sort_indices(ctx, cols_[0], 0)}
+
+    def step(self, ctx, cols_, bufs):
+        from arrow1_b200 import capi
+        return capi.take(ctx, cols_[0], bufs["indices"], True, want_null_count=True)
+
+    def e2e_step(self, host_cols):
+        from arrow1_b200 import compute
+        from arrow1_b200.columns import Column
+        idx = getattr(self, "_e2e_idx", None)
+        if idx is None or idx[0] is not host_cols[0]:   # the permutation is an input of Take: made once, untimed
+            perm = compute.SortIndices(host_cols[0], compute.ASCENDING)
+            self._e2e_idx = idx = (host_cols[0], compute.pinned_column(Column.from_numpy(perm)))
+        return compute.Take(host_cols[0], idx[1], True)
+
+    def cpu_step(self, oracle, kind, host_cols):
+        from arrow1_b200.columns import Column
+        idx = getattr(self, "_cpu_idx", None)
+        if idx is None or idx[0] is not host_cols[0]:
+            self._cpu_idx = idx = (host_cols[0], Column.from_numpy(oracle.sort_indices(host_cols[0], 0, 0, kind=kind)))
+        return oracle.take(host_cols[0], idx[1], True, kind=kind)
+
+
 class FilterWL(Workload):
     kernel = "filter_apply"
     dtype = "u64 (bit copy of int64) + bitmaps"
@@ -317,6 +362,8 @@ def make_workload(name, rows=None):
         return SortWL(rows or 100_000_000, "int64")
     if name == "sort_f64":
         return SortWL(rows or 100_000_000, "float64")
+    if name == "take_sorted":
+        return TakeWL(rows or 100_000_000)
     if name == "filter":
         return FilterWL(rows or 100_000_000, "filter")
     if name == "filter_10m":
@@ -466,7 +513,7 @@ def kernel_times(ctx, names):
     return out
 
 
-ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume", "compare_scalar", "arithmetic", "partition_plan", "partition_scatter", "sort_partition")
+ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume", "compare_scalar", "arithmetic", "take", "partition_plan", "partition_scatter", "sort_partition")
 
 
 def time_device(ctx, wl, cols_, steps, warmup, world, dist_step=None):
@@ -635,7 +682,7 @@ def gpu_arm(args):
     if rank == 0 and world == 1 and not args.no_extras:
         del cols_, bufs
         torch.cuda.empty_cache()
-        for name in ("filter", "filter_10m", "sort_i64", "sort_f64", "groupby_c3", "groupby_c4", "q1"):
+        for name in ("filter", "filter_10m", "sort_i64", "sort_f64", "take_sorted", "groupby_c3", "groupby_c4", "q1"):
             if name == wl.name:
                 continue
             try:
