@@ -204,9 +204,10 @@ class TakeWL(Workload):
 
     def cpu_step(self, oracle, kind, host_cols):
         from arrow1_b200.columns import Column
-        idx = getattr(self, "_cpu_idx", None)
-        if idx is None or idx[0] is not host_cols[0]:
-            self._cpu_idx = idx = (host_cols[0], Column.from_numpy(oracle.sort_indices(host_cols[0], 0, 0, kind=kind)))
+        cache = self.__dict__.setdefault("_cpu_idx", {})   # one permutation per shard, made once (an input of Take)
+        idx = cache.get(id(host_cols[0]))
+        if idx is None:
+            idx = cache[id(host_cols[0])] = (host_cols[0], Column.from_numpy(oracle.sort_indices(host_cols[0], 0, 0, kind=kind)))
         return oracle.take(host_cols[0], idx[1], True, kind=kind)
 
 
@@ -441,8 +442,8 @@ def host_threads():
 
 def cpu_sample_rows(wl, threads):
     per_thread = {"sort_i64": 2_000_000, "sort_f64": 2_000_000, "filter": 16_000_000, "filter_10m": 10_000_000,
-                  "groupby_c3": 8_000_000, "groupby_c4": 4_000_000}[wl.name]
-    return per_thread
+                  "groupby_c3": 8_000_000, "groupby_c4": 4_000_000, "take_sorted": 2_000_000, "q1": 4_000_000}[wl.name]
+    return min(per_thread, wl.n)
 
 
 def run_cpu(wl, steps, warmup, threads):
