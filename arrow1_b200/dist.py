@@ -20,6 +20,7 @@ stand-in to exercise the exchange logic with gloo on CPU.
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional, Sequence
 
 import torch
@@ -73,6 +74,8 @@ class CudaOps:
                 ex.close(group)
             ex = PeerSortExchange(self, int(capacity * 1.25) + 4096, group)
             self.ctx._peer_sort = ex
+            if not ex.ok:   # no peer mappings on this node (same outcome on every rank): NCCL all-to-all from now on
+                self.ctx._peer_sort_failed = True
         return ex
 
     def range_partition_count(self, col: Column, order: int, splitters, n_parts: int):
@@ -138,22 +141,59 @@ class PeerSortExchange:
         self.capacity = capacity
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
-        self.keys = capi.PeerBuffer(ops.ctx, capacity * 8)
-        self.rows = capi.PeerBuffer(ops.ctx, capacity * 4)
-        mine = torch.tensor(list(self.keys.handle() + self.rows.handle()), dtype=torch.uint8, device=ops.device)
+        self.keys = self.rows = None
+        self.key_ptrs, self.row_ptrs = [], []
+        self.ok = False
+        self.flag = torch.zeros(1, dtype=torch.int32, device=ops.device)
+
+        def agreed(success: bool) -> bool:
+            """Every step that can fail locally (allocation, IPC export / open) is followed by a MIN all-reduce
+            of the outcome, so that all ranks take the same path and no collective is left half-entered."""
+            t = torch.tensor([1 if success else 0], dtype=torch.int32, device=ops.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+            return bool(t.item())
+
+        mine = torch.zeros(128, dtype=torch.uint8, device=ops.device)
+        try:
+            if os.environ.get("B200_NO_PEER"):   # tests: behave as a node without peer mappings
+                raise capi.B200Error(9, "peer mappings disabled by B200_NO_PEER")
+            self.keys = capi.PeerBuffer(ops.ctx, capacity * 8)
+            self.rows = capi.PeerBuffer(ops.ctx, capacity * 4)
+            mine = torch.tensor(list(self.keys.handle() + self.rows.handle()), dtype=torch.uint8, device=ops.device)
+            good = True
+        except capi.B200Error:
+            good = False
+        if not agreed(good):
+            self._release()
+            return
         every = torch.empty(self.world * mine.numel(), dtype=torch.uint8, device=ops.device)
         dist.all_gather_into_tensor(every, mine, group=group)
         blob = every.cpu().numpy().tobytes()
-        self.key_ptrs, self.row_ptrs = [], []
-        for r in range(self.world):
-            h = blob[r * 128: (r + 1) * 128]
-            if r == self.rank:
-                self.key_ptrs.append(self.keys.ptr)
-                self.row_ptrs.append(self.rows.ptr)
-            else:
-                self.key_ptrs.append(self.keys.open(h[:64]))
-                self.row_ptrs.append(self.rows.open(h[64:]))
-        self.flag = torch.zeros(1, dtype=torch.int32, device=ops.device)
+        try:
+            for r in range(self.world):
+                h = blob[r * 128: (r + 1) * 128]
+                if r == self.rank:
+                    self.key_ptrs.append(self.keys.ptr)
+                    self.row_ptrs.append(self.rows.ptr)
+                else:
+                    self.key_ptrs.append(self.keys.open(h[:64]))
+                    self.row_ptrs.append(self.rows.open(h[64:]))
+            good = True
+        except capi.B200Error:
+            good = False
+        if not agreed(good):
+            self.keys.close_peers()
+            self.rows.close_peers()
+            dist.barrier(group=group)
+            self._release()
+            return
+        self.ok = True
+
+    def _release(self) -> None:
+        for b in (self.keys, self.rows):
+            if b is not None:
+                b.close()
+        self.keys = self.rows = None
 
     def fence(self, group=None) -> None:
         """Stream-ordered barrier: returns (on the stream) once every rank's earlier work has completed."""
@@ -162,11 +202,12 @@ class PeerSortExchange:
     def close(self, group=None) -> None:
         torch.cuda.synchronize()
         dist.barrier(group=group)       # nobody is still writing into a peer
+        if self.keys is None:
+            return
         self.keys.close_peers()
         self.rows.close_peers()
         dist.barrier(group=group)       # every mapping of this rank's buffers is gone
-        self.keys.close()
-        self.rows.close()
+        self._release()
 
 
 # ------------------------------------------------------------------------------------------------
@@ -267,6 +308,7 @@ def dist_sort_indices(ops, col: Column, order: int, row_base: int, group=None):
     spl_unsigned = [(int(x) ^ _I64_MIN) & ((1 << 64) - 1) for x in splitters.tolist()]
     _mark("splitters")
     fused = (hasattr(ops, "peer_sort_exchange") and FUSED_EXCHANGE and world < 16
+             and not getattr(getattr(ops, "ctx", None), "_peer_sort_failed", False)
              and max(m[2] + m[1] for m in metas) <= (1 << 30))
     if fused:
         return _exchange_fused(ops, col, order, row_base, spl_unsigned, max(m[1] for m in metas), world, rank, group)
@@ -297,6 +339,8 @@ def _exchange_fused(ops, col, order, row_base, spl_unsigned, max_rows, world, ra
     incoming = body[:-1] + [body[-1] + tail]
     _mark("count")
     ex = ops.peer_sort_exchange(max(max(incoming), max_rows), group)
+    if not ex.ok:
+        return _exchange_all_to_all(ops, col, order, row_base, spl_unsigned, world, rank, group)
     offsets = [sum(m[src][q] for src in range(rank)) for q in range(world)]
     offsets.append(body[-1] + sum(m[src][world] for src in range(rank)))
     plan.push(row_base, ex.key_ptrs + [ex.key_ptrs[-1]], ex.row_ptrs + [ex.row_ptrs[-1]], offsets, rows32=True)

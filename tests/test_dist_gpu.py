@@ -30,6 +30,11 @@ def _worker(rank, world, port, job, path):
     for case in job:
         col, base = case["shards"][rank]
         bd.FUSED_EXCHANGE = case["fused"]
+        if case.get("no_peer"):   # a node without peer mappings: every rank must agree to fall back to NCCL
+            os.environ["B200_NO_PEER"] = "1"
+            ops.ctx._peer_sort, ops.ctx._peer_sort_failed = None, False
+        elif os.environ.pop("B200_NO_PEER", None):
+            ops.ctx._peer_sort, ops.ctx._peer_sort_failed = None, False
         out, off = bd.dist_sort_indices(ops, col.to_device(), case["order"], base)
         res.append((out.cpu().numpy().view(U64).copy(), off))
     with open(path + ".%d" % rank, "wb") as f:
@@ -50,6 +55,8 @@ def test_dist_sort_indices_fused_and_all_to_all_match_oracle(world):
     cases.append(Column.from_numpy(f, rng.random(n) > 0.02))
     cases.append(Column.from_numpy(rng.integers(-2**63, 2**63 - 1, size=n, dtype=np.int64)))
     job, wants = [], []
+    job.append({"order": 0, "fused": True, "no_peer": True, "shards": shard(cases[0], world)})
+    wants.append(oracle.sort_indices(cases[0], 0, kind=ORACLE))
     for col in cases:
         for order in (0, 1):
             for fused in (True, False):
