@@ -73,9 +73,14 @@ def pinned_column(col: Column) -> Column:
                   col.length, col.offset, col.null_count)
 
 
+def _from_host(col: Column) -> bool:
+    """True for host columns and for columns Pipeline.stage() copied to the device ahead of their call."""
+    return (not col.on_device) or getattr(col, "from_host", False)
+
+
 def _h2d(col: Column, ctx: capi.Context) -> Tuple[Column, int]:
     if col.on_device:
-        return col, 0
+        return col, getattr(col, "staged_bytes", 0)
     dev = "cuda:%d" % ctx.device
     d = torch.from_numpy(col.data).to(dev, non_blocking=True)
     v = None
@@ -104,7 +109,7 @@ class Transfer:
 def Filter(values: Column, mask: Column, null_selection: int = DROP, ctx: Optional[capi.Context] = None,
            _wait: bool = True) -> Column:
     ctx = ctx or default_context()
-    host = not values.on_device
+    host = _from_host(values)
     dv, b0 = _h2d(values, ctx)
     dm, b1 = _h2d(mask, ctx)
     out = capi.filter(ctx, dv, dm, null_selection)
@@ -129,7 +134,7 @@ def Filter(values: Column, mask: Column, null_selection: int = DROP, ctx: Option
 def SortIndices(values: Column, order: int = ASCENDING, ctx: Optional[capi.Context] = None, _wait: bool = True):
     """uint64 indices: numpy array for host input, int64-typed torch tensor for device input."""
     ctx = ctx or default_context()
-    host = not values.on_device
+    host = _from_host(values)
     dv, b0 = _h2d(values, ctx)
     out = capi.sort_indices(ctx, dv, order)
     Transfer.h2d, Transfer.d2h = b0, 0
@@ -205,15 +210,35 @@ class Pipeline:
     def launches(self) -> int:
         return sum(ctx.launches for ctx, _ in self.lanes)
 
-    def submit(self, fn, *args, **kwargs) -> Pending:
-        """fn is Filter or SortIndices (calls that need a host-visible size mid-way, GroupBy's group count
-        or Filter's output length, block the submitting thread for that long but still overlap with the
-        other lanes' copies)."""
+    def stage(self, *cols: Column):
+        """Starts the host -> device copies of one call's host columns on the next lane and returns at once; pass
+        the results to submit() in place of the host columns.  Lets a caller start the copies of call i+1 before
+        call i reaches a point where it has to wait for the device (an output length, a collective's counts).
+        Returns one staged column, or a tuple of them."""
         i = self._next % len(self.lanes)
         self._next += 1
         ctx, stream = self.lanes[i]
+        out = []
         with torch.cuda.stream(stream):
-            if fn in (Filter, SortIndices):
+            for col in cols:
+                dev, nbytes = _h2d(col, ctx)
+                dev.from_host, dev.staged_bytes, dev.lane = True, nbytes, i
+                out.append(dev)
+        return out[0] if len(out) == 1 else tuple(out)
+
+    def submit(self, fn, *args, **kwargs) -> Pending:
+        """fn is Filter or SortIndices (calls that need a host-visible size mid-way, GroupBy's group count
+        or Filter's output length, block the submitting thread for that long but still overlap with the
+        other lanes' copies).  A staged column among the arguments pins the call to the lane that holds it."""
+        staged = [a for a in args if isinstance(a, Column) and getattr(a, "lane", None) is not None]
+        if staged:
+            i = staged[0].lane
+        else:
+            i = self._next % len(self.lanes)
+            self._next += 1
+        ctx, stream = self.lanes[i]
+        with torch.cuda.stream(stream):
+            if fn in (Filter, SortIndices) or getattr(fn, "_b200_async", False):
                 kwargs["_wait"] = False
             value = fn(*args, ctx=ctx, **kwargs)
             ev = torch.cuda.Event()

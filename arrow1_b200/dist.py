@@ -534,23 +534,40 @@ def bench_step(ctx, wl, cols_, bufs):
     raise SystemExit("bench: workload %s has no multi-GPU form yet" % wl.name)
 
 
+def SortIndicesSharded(values: Column, order: int = 0, row_base: int = 0, ctx=None, _wait: bool = True, group=None):
+    """The multi-GPU SortIndices from this rank's HOST shard: staged to the device, sorted across the ranks
+    (dist_sort_indices), this rank's slice of the global index array read back.  Returns (uint64 numpy indices,
+    global offset of the slice).  Collective: every rank calls it, in the same order.  Takes the `ctx` / `_wait`
+    keywords of compute.Pipeline lanes, so several calls can be in flight (their collectives are issued in
+    the same order on every rank; each lane's context owns its own exchange buffers)."""
+    from . import compute
+    import numpy as np
+    ctx = ctx or compute.default_context()
+    dv, b0 = compute._h2d(values, ctx)   # already on the device when the caller staged it (compute.Pipeline.stage)
+    out, offset = dist_sort_indices(CudaOps(ctx), dv, order, row_base, group)
+    h = compute._d2h(out, out.numel() * 8)
+    if _wait:
+        ctx.stream.synchronize()
+    compute.Transfer.h2d, compute.Transfer.d2h = b0, out.numel() * 8
+    return h.view(np.uint64), offset
+
+
+SortIndicesSharded._b200_async = True
+
+
 def bench_e2e_step(ctx, wl, host_cols):
     """Host shard -> device -> multi-GPU op -> host (the result slice / merged groups)."""
     from . import compute
     ops = CudaOps(ctx)
     rank, _ = _rank_world()
+    if wl.name.startswith("sort"):
+        return SortIndicesSharded(host_cols[0], 0, rank * wl.n, ctx=ctx)
     dev_cols, nbytes = [], 0
     for c in host_cols:
         d, b = compute._h2d(c, ctx)
         dev_cols.append(d)
         nbytes += b
     compute.Transfer.h2d = nbytes
-    if wl.name.startswith("sort"):
-        out, _ = dist_sort_indices(ops, dev_cols[0], 0, rank * wl.n)
-        h = compute._d2h(out, out.numel() * 8)
-        torch.cuda.current_stream().synchronize()
-        compute.Transfer.d2h = out.numel() * 8
-        return h
     if wl.name.startswith("filter"):
         return wl.e2e_step(host_cols)
     if wl.name == "groupby_c3":

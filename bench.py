@@ -649,7 +649,8 @@ def gpu_arm(args):
         serial_ms = timed(serial_loop, e2e_steps)
         h2d_b, d2h_b = compute.Transfer.h2d, compute.Transfer.d2h
         ems, depth = serial_ms, 1
-        if world == 1 and hasattr(sub, "e2e_submit"):
+        dist_sort = world > 1 and sub.name.startswith("sort")
+        if (world == 1 and hasattr(sub, "e2e_submit")) or dist_sort:
             # the same calls, `depth` in flight (compute.Pipeline: one b200_ctx + stream per lane): every step
             # still copies its own inputs in and its own result out inside the timed region, but step i+1's
             # H2D, step i's kernels and step i-1's D2H overlap
@@ -658,8 +659,19 @@ def gpu_arm(args):
 
             def piped_loop(k):
                 pend = []
-                for _ in range(k):
-                    pend.append(sub.e2e_submit(pipe, host_cols))
+                # the copy-in of step i+1 is started before step i is submitted: a step blocks the submitting
+                # thread wherever it needs a host-visible number (filter's output length, the sort's exchange
+                # counts), and the next copy should already be running by then
+                stage = lambda: tuple(pipe.stage(*host_cols)) if len(host_cols) > 1 else (pipe.stage(*host_cols),)  # noqa: E731
+                nxt = stage()
+                for i in range(k):
+                    cur = nxt
+                    if i + 1 < k:
+                        nxt = stage()
+                    if dist_sort:   # same submission order on every rank: the lanes' collectives line up
+                        pend.append(pipe.submit(b200_dist.SortIndicesSharded, cur[0], 0, rank * wl.n))
+                    else:
+                        pend.append(sub.e2e_submit(pipe, cur))
                     if len(pend) >= depth:
                         pend.pop(0).result()
                 while pend:

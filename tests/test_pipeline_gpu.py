@@ -28,6 +28,11 @@ def test_pipelined_sort_indices_match_oracle():
                 assert got.dtype == np.uint64
                 np.testing.assert_array_equal(got, oracle.sort_indices(b, order, 0, kind=ORACLE))
         assert pipe.launches > 0
+        # copies started ahead of the call (Pipeline.stage): same results
+        staged = [pipe.stage(b) for b in batches]
+        pending = [pipe.submit(compute.SortIndices, st, compute.ASCENDING) for st in staged]
+        for b, p in zip(batches, pending):
+            np.testing.assert_array_equal(p.result(), oracle.sort_indices(b, compute.ASCENDING, 0, kind=ORACLE))
     finally:
         pipe.close()
 
@@ -43,7 +48,11 @@ def test_pipelined_filter_matches_oracle_and_serial_calls():
             v = compute.pinned_column(rand_column(rng, cols.INT64, n, 0.2 if i % 2 else 0.0))
             m = compute.pinned_column(Column.from_numpy(rng.random(n) < 0.4, (rng.random(n) > 0.1) if i % 3 == 0 else None))
             for sel in (compute.DROP, compute.EMIT_NULL):
-                work.append((v, m, sel, pipe.submit(compute.Filter, v, m, sel)))
+                if i % 2:
+                    work.append((v, m, sel, pipe.submit(compute.Filter, v, m, sel)))
+                else:   # both columns staged on one lane ahead of the call
+                    sv, sm = pipe.stage(v, m)
+                    work.append((v, m, sel, pipe.submit(compute.Filter, sv, sm, sel)))
         for v, m, sel, p in work:
             got = p.result()
             want = oracle.filter(v, m, sel, kind=ORACLE)
