@@ -1758,6 +1758,72 @@ struct TinySmem {
   uint32_t new_groups, deferred;
 };
 
+// the CTA's thread-private partials S.sum / S.cnt [group][thread] -> tree reduction per group -> one thread folds the
+// group into the global table (shared by gb_tiny_kernel and gb_tiny8_kernel; the caller has synchronised)
+__device__ __forceinline__ void tiny_fold(const GbArgs& a, TinySmem& S, const int dom, const int64_t begin) {
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  // ---- per group: tree reduction of the thread-private partials, then one thread folds it into the table
+  for (int g = 0; g < kTinyGroups; ++g) {
+    const uint64_t key = S.keys[g];
+    if (key == kEmpty) break;   // entries fill in order
+    uint64_t sv = S.sum[g][t];
+    uint32_t cv = S.cnt[g][t];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      const uint64_t os = __shfl_down_sync(0xffffffffu, sv, d);
+      const uint32_t oc = __shfl_down_sync(0xffffffffu, cv, d);
+      if (dom == kFloat) sv = __double_as_longlong(__longlong_as_double(sv) + __longlong_as_double(os));
+      else sv += os;
+      cv += oc;
+    }
+    if (lane == 0) {
+      S.red_sum[warp] = sv;
+      S.red_cnt[warp] = cv;
+    }
+    __syncthreads();
+    if (t == 0) {
+      uint64_t ts = S.red_sum[0];
+      uint64_t tc = S.red_cnt[0];
+      for (int w = 1; w < kTinyThreads / 32; ++w) {
+        if (dom == kFloat) ts = __double_as_longlong(__longlong_as_double(ts) + __longlong_as_double(S.red_sum[w]));
+        else ts += S.red_sum[w];
+        tc += S.red_cnt[w];
+      }
+      bool claimed;
+      uint64_t slot_index;
+      char* gs = global_slot(a.t, a.s.stride, key, 0, true, &claimed, &slot_index);
+      if (!gs) {
+        gs = a.spill + size_t(atomicAdd(a.counters + 5, 1u)) * a.s.stride;
+        init_slot(gs, a.s);
+        reinterpret_cast<uint64_t*>(gs)[0] = key;
+        reinterpret_cast<uint64_t*>(gs)[a.s.stride / 8 - 1] = 0;
+        claimed = false;
+      }
+      if (claimed) S.new_groups += 1;
+      const uint64_t nulls = S.nulls[g];
+      if (S.first[g] != 0xFFFFFFFFu) atomic_min_checked(reinterpret_cast<uint64_t*>(gs) + 1, a.row_base + uint64_t(begin) + S.first[g]);
+      for (int j = 0; j < a.s.n_aggs; ++j) {
+        const GbAgg& ag = a.s.aggs[j];
+        if (ag.col != 0) continue;
+        uint64_t* d = reinterpret_cast<uint64_t*>(gs + ag.off);
+        if (ag.kind == B200_HASH_COUNT) {
+          const uint64_t c = ag.option ? nulls : tc;
+          if (c) atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)c);
+        } else if (tc) {   // hash_sum / hash_mean (this path is not chosen for hash_min_max)
+          if (ag.dom == kFloat) atomicAdd(reinterpret_cast<double*>(d), __longlong_as_double(ts));
+          else atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)ts);
+          atomicAdd(reinterpret_cast<unsigned long long*>(d + 1), (unsigned long long)tc);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (t == 0) {
+    if (S.new_groups) atomicAdd(a.counters + 0, S.new_groups);
+    if (S.deferred) atomicAdd(a.counters + 1, S.deferred);
+  }
+}
+
 __global__ void __launch_bounds__(kTinyThreads, 4) gb_tiny_kernel(const __grid_constant__ GbArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
   TinySmem& S = *reinterpret_cast<TinySmem*>(smem);
@@ -1843,66 +1909,112 @@ __global__ void __launch_bounds__(kTinyThreads, 4) gb_tiny_kernel(const __grid_c
     }
   }
   __syncthreads();
-  // ---- per group: tree reduction of the thread-private partials, then one thread folds it into the table
-  for (int g = 0; g < kTinyGroups; ++g) {
-    const uint64_t key = S.keys[g];
-    if (key == kEmpty) break;   // entries fill in order
-    uint64_t sv = S.sum[g][t];
-    uint32_t cv = S.cnt[g][t];
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) {
-      const uint64_t os = __shfl_down_sync(0xffffffffu, sv, d);
-      const uint32_t oc = __shfl_down_sync(0xffffffffu, cv, d);
-      if (dom == kFloat) sv = __double_as_longlong(__longlong_as_double(sv) + __longlong_as_double(os));
-      else sv += os;
-      cv += oc;
-    }
-    if (lane == 0) {
-      S.red_sum[warp] = sv;
-      S.red_cnt[warp] = cv;
-    }
-    __syncthreads();
-    if (t == 0) {
-      uint64_t ts = S.red_sum[0];
-      uint64_t tc = S.red_cnt[0];
-      for (int w = 1; w < kTinyThreads / 32; ++w) {
-        if (dom == kFloat) ts = __double_as_longlong(__longlong_as_double(ts) + __longlong_as_double(S.red_sum[w]));
-        else ts += S.red_sum[w];
-        tc += S.red_cnt[w];
-      }
-      bool claimed;
-      uint64_t slot_index;
-      char* gs = global_slot(a.t, a.s.stride, key, 0, true, &claimed, &slot_index);
-      if (!gs) {
-        gs = a.spill + size_t(atomicAdd(a.counters + 5, 1u)) * a.s.stride;
-        init_slot(gs, a.s);
-        reinterpret_cast<uint64_t*>(gs)[0] = key;
-        reinterpret_cast<uint64_t*>(gs)[a.s.stride / 8 - 1] = 0;
-        claimed = false;
-      }
-      if (claimed) S.new_groups += 1;
-      const uint64_t nulls = S.nulls[g];
-      if (S.first[g] != 0xFFFFFFFFu) atomic_min_checked(reinterpret_cast<uint64_t*>(gs) + 1, a.row_base + uint64_t(begin) + S.first[g]);
-      for (int j = 0; j < a.s.n_aggs; ++j) {
-        const GbAgg& ag = a.s.aggs[j];
-        if (ag.col != 0) continue;
-        uint64_t* d = reinterpret_cast<uint64_t*>(gs + ag.off);
-        if (ag.kind == B200_HASH_COUNT) {
-          const uint64_t c = ag.option ? nulls : tc;
-          if (c) atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)c);
-        } else if (tc) {   // hash_sum / hash_mean (this path is not chosen for hash_min_max)
-          if (ag.dom == kFloat) atomicAdd(reinterpret_cast<double*>(d), __longlong_as_double(ts));
-          else atomicAdd(reinterpret_cast<unsigned long long*>(d), (unsigned long long)ts);
-          atomicAdd(reinterpret_cast<unsigned long long*>(d + 1), (unsigned long long)tc);
-        }
-      }
-    }
-    __syncthreads();
+  tiny_fold(a, S, dom, begin);
+}
+
+// ---- <= 8 groups, byte-wide keys, one 64-bit value column: register accumulators ---------------------
+// The Q1 shape (two uint8 keys, float64 measures).  gb_tiny_kernel's generic loaders (a type switch and a bitmap
+// probe per key column and per value, 64-bit key compares) cost ~250 instructions per row; here the packed key
+// is at most 24 bits, the CTA's key table lives in 8 registers, and every thread keeps the 8 groups' sums and
+// counts in REGISTERS, updated with predicated adds (no shared memory while rows stream; a predicated add, not an
+// add of zero, so a group of -0.0 values keeps its sign).  The epilogue is gb_tiny_kernel's: the accumulators are
+// parked in its [group][thread] shared arrays, tree-reduced and folded into the global table.
+template <bool kFloatSum>
+__global__ void __launch_bounds__(kTinyThreads, 4) gb_tiny8_kernel(const __grid_constant__ GbArgs a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  TinySmem& S = *reinterpret_cast<TinySmem*>(smem);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  if (t < kTinyGroups) {
+    S.keys[t] = kEmpty;
+    S.nulls[t] = 0;
+    S.first[t] = 0xFFFFFFFFu;
   }
   if (t == 0) {
-    if (S.new_groups) atomicAdd(a.counters + 0, S.new_groups);
-    if (S.deferred) atomicAdd(a.counters + 1, S.deferred);
+    S.new_groups = 0;
+    S.deferred = 0;
   }
+  __syncthreads();
+  const int64_t begin = int64_t(blockIdx.x) * a.rows_per_block;
+  const int64_t end = min(a.n, begin + a.rows_per_block);
+  const uint8_t* k0 = reinterpret_cast<const uint8_t*>(a.keys[0].data);
+  const uint8_t* k1 = a.s.n_keys > 1 ? reinterpret_cast<const uint8_t*>(a.keys[1].data) : nullptr;
+  const uint8_t* k2 = a.s.n_keys > 2 ? reinterpret_cast<const uint8_t*>(a.keys[2].data) : nullptr;
+  const uint64_t* vals = reinterpret_cast<const uint64_t*>(a.cols[0].data);
+  const BitmapRef vv = a.cols[0].vv;
+  uint32_t tk[kTinyGroups];      // low words of the CTA's key table (EMPTY reads as 0xFFFFFFFF, above any 24-bit key)
+  uint64_t acc[kTinyGroups];
+  uint32_t cnt[kTinyGroups];
+#pragma unroll
+  for (int q = 0; q < kTinyGroups; ++q) {
+    tk[q] = 0xFFFFFFFFu;
+    acc[q] = 0;
+    cnt[q] = 0;
+  }
+  uint32_t seen = 0;
+  constexpr int kU = 4;   // rows in flight per thread
+#pragma unroll 1
+  for (int64_t row0 = begin + t; row0 < end; row0 += kU * kTinyThreads) {
+    uint32_t key[kU];
+    uint64_t v[kU];
+    bool valid[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t row = min(row0 + u * kTinyThreads, end - 1);   // clamped: the loads need no branch
+      uint32_t k = k0[row];
+      if (k1) k |= uint32_t(k1[row]) << 8;
+      if (k2) k |= uint32_t(k2[row]) << 16;
+      key[u] = k;
+      v[u] = vals[row];
+      valid[u] = bitmap_get(vv, row);
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t row = row0 + u * kTinyThreads;
+      if (row >= end) break;
+      int g = -1;
+#pragma unroll
+      for (int q = 0; q < kTinyGroups; ++q)
+        if (tk[q] == key[u]) g = q;
+      if (g < 0) {   // not in the snapshot: claim the first free entry, or find the key claimed meanwhile
+#pragma unroll 1
+        for (int q = 0; q < kTinyGroups && g < 0; ++q) {
+          const unsigned long long old = atomicCAS(reinterpret_cast<unsigned long long*>(&S.keys[q]), (unsigned long long)kEmpty,
+                                                   (unsigned long long)key[u]);
+          if (old == kEmpty || old == key[u]) g = q;
+        }
+#pragma unroll
+        for (int q = 0; q < kTinyGroups; ++q) tk[q] = uint32_t(*reinterpret_cast<const volatile uint64_t*>(&S.keys[q]));
+      }
+      if (g < 0) {   // a 9th group in this CTA: the generic kernel takes the row
+        atomicOr(a.defer_out + (row >> 5), 1u << (row & 31));
+        atomicAdd(&S.deferred, 1u);
+        continue;
+      }
+      if (!((seen >> g) & 1u)) {
+        seen |= 1u << g;
+        atomicMin(&S.first[g], uint32_t(row - begin));   // rows of a thread come in increasing order
+      }
+      if (valid[u]) {
+#pragma unroll
+        for (int q = 0; q < kTinyGroups; ++q) {
+          if (g == q) {
+            if (kFloatSum) acc[q] = __double_as_longlong(__longlong_as_double(acc[q]) + __longlong_as_double(v[u]));
+            else acc[q] += v[u];
+            cnt[q] += 1;
+          }
+        }
+      } else {
+        atomicAdd(&S.nulls[g], 1u);
+      }
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < kTinyGroups; ++q) {
+    S.sum[q][t] = acc[q];
+    S.cnt[q][t] = cnt[q];
+  }
+  __syncthreads();
+  tiny_fold(a, S, kFloatSum ? kFloat : kSigned, begin);
 }
 
 // ---- table maintenance ----------------------------------------------------------------------
@@ -2507,9 +2619,22 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
       static bool tattr = false;
       if (!tattr) {
         B200_CUDA(ctx, cudaFuncSetAttribute(gb_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(TinySmem))));
+        B200_CUDA(ctx, cudaFuncSetAttribute(gb_tiny8_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(TinySmem))));
+        B200_CUDA(ctx, cudaFuncSetAttribute(gb_tiny8_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(TinySmem))));
         tattr = true;
       }
-      B200_TIMED(ctx, "groupby_consume", (gb_tiny_kernel<<<grid, kTinyThreads, int(sizeof(TinySmem)), ctx->stream>>>(a)));
+      // byte-wide keys without nulls and a 64-bit value column (the Q1 shape): register accumulators
+      bool lean = a.s.n_keys <= 3 && !getenv("B200_GB_NO_TINY8");
+      for (int k = 0; k < a.s.n_keys; ++k)
+        if (a.keys[k].nbits != 8 || a.keys[k].vv.words != nullptr) lean = false;
+      const int vt = a.cols[0].type;
+      if (vt != B200_DOUBLE && vt != B200_INT64 && vt != B200_UINT64) lean = false;
+      if (lean && vt == B200_DOUBLE)
+        B200_TIMED(ctx, "groupby_consume", (gb_tiny8_kernel<true><<<grid, kTinyThreads, int(sizeof(TinySmem)), ctx->stream>>>(a)));
+      else if (lean)
+        B200_TIMED(ctx, "groupby_consume", (gb_tiny8_kernel<false><<<grid, kTinyThreads, int(sizeof(TinySmem)), ctx->stream>>>(a)));
+      else
+        B200_TIMED(ctx, "groupby_consume", (gb_tiny_kernel<<<grid, kTinyThreads, int(sizeof(TinySmem)), ctx->stream>>>(a)));
       uint32_t c[4];
       B200_RETURN_NOT_OK(read_counters(gb, c));
       const uint32_t tiny_deferred = c[1];

@@ -272,3 +272,39 @@ def test_groupby_low_card_kernel_spill_without_hint(ctx):
     a = run_groupby("gpu", [key], aggs, [a1, a2, a2], ctx, expected_groups=0)
     b = run_groupby(ORACLE, [key], aggs, [a1, a2, a2])
     assert_group_equal(a, b, aggs, rtol=RTOL)
+
+
+@pytest.mark.parametrize("n_keys", [1, 2, 3])
+@pytest.mark.parametrize("dt", [np.float64, np.int64, np.uint64])
+def test_groupby_tiny_byte_keys_register_accumulators(ctx, n_keys, dt):
+    """<= 8 groups over uint8 / int8 key columns and a 64-bit value column (the Q1 shape): gb_tiny8_kernel keeps
+    the sums and counts in registers.  Also: a 9th..12th group appearing late (those rows are deferred to the generic
+    kernel), value nulls, COUNT_NULL, a group made of -0.0 values only (its sum keeps the sign), int64 wrap-around."""
+    rng = np.random.default_rng(31 * n_keys + np.dtype(dt).num)
+    n = 300_000
+    combos = [(1, 2, 3), (1, 5, 3), (7, 2, 3), (7, 5, 9), (200, 2, 3), (200, 5, 250)][:5]
+    pick = rng.integers(0, len(combos), size=n)
+    pick[n - 5000:] = rng.integers(0, 12, size=5000) % 12          # late: more than 8 groups in the last CTAs
+    extra = [(10 + i, 100 + i, 50 + i) for i in range(12)]
+    table = np.array(combos + extra[: 12 - len(combos)], dtype=np.int64)
+    kcols = []
+    for k in range(n_keys):
+        vals = table[pick % len(table), k]
+        kcols.append(Column.from_numpy(vals.astype(np.uint8 if k != 1 else np.int8)))
+    if dt == np.float64:
+        v = rng.random(n) * 1e6 - 5e5
+        v[pick == 1] = -0.0                                         # a whole group of negative zeros
+    elif dt == np.int64:
+        v = rng.integers(-2**62, 2**62, size=n, dtype=np.int64)     # sums wrap
+    else:
+        v = rng.integers(0, 2**63, size=n, dtype=np.uint64)
+    arg = Column.from_numpy(v.astype(dt), rng.random(n) > 0.02)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MEAN), AggSpec(cols.HASH_COUNT), AggSpec(cols.HASH_COUNT, 1)]
+    a = run_groupby("gpu", kcols, aggs, [arg] * 4, ctx, expected_groups=6)
+    b = run_groupby(ORACLE, kcols, aggs, [arg] * 4)
+    assert_group_equal(a, b, aggs, rtol=RTOL)
+    # no nulls at all, one key column, streaming in two batches through the same handle shape
+    arg2 = Column.from_numpy(v.astype(dt))
+    a2 = run_groupby("gpu", kcols, aggs[:2], [arg2] * 2, ctx, expected_groups=6)
+    b2 = run_groupby(ORACLE, kcols, aggs[:2], [arg2] * 2)
+    assert_group_equal(a2, b2, aggs[:2], rtol=RTOL)
