@@ -459,6 +459,16 @@ class GroupBy:
     def consume(self, keys: Sequence[Column], args: Sequence[Column], row_base: int = 0):
         self.ctx.check(lib().b200_groupby_consume(self._h, col_array(keys), col_array(args), C.c_uint64(row_base)))
 
+    def consume_selected(self, keys: Sequence[Column], args: Sequence[Column], selection: Column, row_base: int = 0):
+        """b200_groupby_consume_selected: only the rows whose bit is set in `selection` (a boolean device Column
+        at offset 0 without nulls, e.g. compare_scalar's output on a column without nulls)."""
+        if selection.type != BOOL or selection.offset != 0 or (selection.validity is not None and selection.null_count != 0):
+            raise B200Error(10, "consume_selected: the selection must be a boolean column at offset 0 without nulls")
+        if selection.length != keys[0].length:
+            raise B200Error(4, "Array arguments must all be the same length")
+        self.ctx.check(lib().b200_groupby_consume_selected(self._h, col_array(keys), col_array(args), C.c_uint64(row_base),
+                                                           C.c_void_p(selection.data.data_ptr())))
+
     def consume_rows(self, keys: Sequence[Column], args: Sequence[Column], row_ids: torch.Tensor):
         """b200_groupby_consume_rows: explicit global row numbers (int64-typed tensor of uint64)."""
         self.ctx.check(lib().b200_groupby_consume_rows(self._h, col_array(keys), col_array(args),
@@ -588,11 +598,15 @@ def pack_validity(ctx: Context, valid_bytes: torch.Tensor):
 
 
 def group_by(ctx: Context, keys: Sequence[Column], aggs: Sequence[AggSpec], args: Sequence[Column],
-             expected_groups: int = 0, row_base: int = 0) -> GroupByOutput:
-    """== compute::internal::GroupBy(arguments, keys, aggregates) in one batch."""
+             expected_groups: int = 0, row_base: int = 0, selection: Optional[Column] = None) -> GroupByOutput:
+    """== compute::internal::GroupBy(arguments, keys, aggregates) in one batch; with `selection`, of the selected
+    rows only (== GroupBy over Filter(column, selection) of every column)."""
     gb = GroupBy(ctx, [k.type for k in keys], aggs, [a.type for a in args], expected_groups)
     try:
-        gb.consume(keys, args, row_base)
+        if selection is None:
+            gb.consume(keys, args, row_base)
+        else:
+            gb.consume_selected(keys, args, selection, row_base)
         return gb.finalize()
     finally:
         gb.close()

@@ -291,6 +291,22 @@ def Q1Pipeline(shipdate: Column, returnflag: Column, linestatus: Column, measure
     return capi.group_by(ctx, [rf, ls], [a for _, a in specs], [ms[i] for i, _ in specs], expected_groups=8)
 
 
+def Q1PipelineSelected(shipdate: Column, returnflag: Column, linestatus: Column, measures: Sequence[Column],
+                       ctx: Optional[capi.Context] = None):
+    """The same query with the Filter folded into the aggregation: the comparison's bitmap is
+    the selection of b200_groupby_consume_selected, so no filtered column is materialised — 38 B/row of traffic
+    instead of ~100.  Same result as Q1Pipeline (group order included); shipdate must not hold nulls."""
+    ctx = ctx or default_context()
+    if shipdate.validity is not None and shipdate.null_count != 0:
+        return Q1Pipeline(shipdate, returnflag, linestatus, measures, ctx)
+    mask = capi.compare_scalar(ctx, shipdate, "less_equal", Q1_SHIPDATE_CUTOFF)
+    ms = list(measures)
+    ms.append(capi.arithmetic(ctx, "multiply", ms[1], capi.arithmetic(ctx, "subtract", 1.0, ms[2])))
+    specs = q1_aggregates()
+    return capi.group_by(ctx, [returnflag, linestatus], [a for _, a in specs], [ms[i] for i, _ in specs], expected_groups=8,
+                         selection=mask)
+
+
 class GroupByResult:
     """Image of GroupBy's StructArray (hash_aggregate.cc:962-965): one entry per aggregate (a list
     of (values, valid) pairs: two for hash_min_max) then the key columns, `num_groups` long."""

@@ -327,7 +327,11 @@ class Q1WL(Workload):
     def step(self, ctx, cols_, bufs):
         from arrow1_b200 import compute
         ship, rf, ls, qty, price, disc = cols_
+        if self.fused:
+            return compute.Q1PipelineSelected(ship, rf, ls, [qty, price, disc], ctx)
         return compute.Q1Pipeline(ship, rf, ls, [qty, price, disc], ctx)
+
+    fused = False
 
     def e2e_step(self, host_cols):
         from arrow1_b200 import compute
@@ -359,6 +363,11 @@ class Q1WL(Workload):
 def make_workload(name, rows=None):
     if name == "q1":
         return Q1WL(rows or 600_000_000)
+    if name == "q1_selected":
+        w = Q1WL(rows or 600_000_000)
+        w.fused, w.name = True, "q1_selected"
+        w.description += "; Filter folded into the aggregation (b200_groupby_consume_selected)"
+        return w
     if name == "sort_i64":
         return SortWL(rows or 100_000_000, "int64")
     if name == "sort_f64":
@@ -442,7 +451,7 @@ def host_threads():
 
 def cpu_sample_rows(wl, threads):
     per_thread = {"sort_i64": 2_000_000, "sort_f64": 2_000_000, "filter": 16_000_000, "filter_10m": 10_000_000,
-                  "groupby_c3": 8_000_000, "groupby_c4": 4_000_000, "take_sorted": 2_000_000, "q1": 4_000_000}[wl.name]
+                  "groupby_c3": 8_000_000, "groupby_c4": 4_000_000, "take_sorted": 2_000_000, "q1": 4_000_000, "q1_selected": 4_000_000}[wl.name]
     return min(per_thread, wl.n)
 
 
@@ -695,7 +704,7 @@ def gpu_arm(args):
     if rank == 0 and world == 1 and not args.no_extras:
         del cols_, bufs
         torch.cuda.empty_cache()
-        for name in ("filter", "filter_10m", "sort_i64", "sort_f64", "take_sorted", "groupby_c3", "groupby_c4", "q1"):
+        for name in ("filter", "filter_10m", "sort_i64", "sort_f64", "take_sorted", "groupby_c3", "groupby_c4", "q1", "q1_selected"):
             if name == wl.name:
                 continue
             try:

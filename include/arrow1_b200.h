@@ -310,6 +310,13 @@ B200_API int b200_groupby_consume(b200_groupby* gb, const b200_col* keys, const 
  * aggregates rows that arrived from every shard (SURVEY §8e, high cardinality). */
 B200_API int b200_groupby_consume_rows(b200_groupby* gb, const b200_col* keys, const b200_col* args,
                                        const uint64_t* row_ids);
+/* As b200_groupby_consume over the rows whose bit is set in `selection` only: == consuming
+ * Filter(column, selection, DROP) of every key and argument column for a selection without nulls, without
+ * materialising the filtered columns (compare -> filter -> aggregate in fewer passes; the
+ * Q1 shape).  selection: DEVICE bitmap at bit offset 0, ceil(length / 32) whole 32-bit words, e.g. the output
+ * of b200_compare_scalar.  Group order is the first-occurrence order of the selected rows, as after a Filter. */
+B200_API int b200_groupby_consume_selected(b200_groupby* gb, const b200_col* keys, const b200_col* args,
+                                           uint64_t row_base, const void* selection);
 /* global first-occurrence row of every group, in output (group id) order: device uint64[num_groups].
  * Lets ranks holding disjoint key sets restore the reference's global group order
  * (hash_aggregate.cc:391-403) by ranking their groups on it. */

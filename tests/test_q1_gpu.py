@@ -73,6 +73,10 @@ def test_q1_pipeline_matches_oracle(ctx, n):
     b = GroupRes(want.num_groups, want.aggs, want.keys)
     assert a.num_groups == b.num_groups and a.num_groups <= 4   # A/F, N/F, N/O, R/F
     assert_group_equal(a, b, [s for _, s in specs], rtol=1e-12)
+    # the Filter folded into the aggregation (b200_groupby_consume_selected): same groups, same order, same values
+    got2 = compute.Q1PipelineSelected(ship, rf, ls, [qty, price, disc], ctx)
+    a2 = GroupRes(got2.num_groups, [[_host(c) for c in ag] for ag in got2.aggs], [_host(k) for k in got2.keys])
+    assert_group_equal(a2, b, [s for _, s in specs], rtol=1e-12)
 
 
 NP_ARITH = {"add": np.add, "subtract": np.subtract, "multiply": np.multiply}
@@ -120,3 +124,27 @@ def test_arithmetic_errors(ctx):
     with pytest.raises(B200Error) as e:
         capi.arithmetic(ctx, "add", a, c)
     assert e.value.code == 10
+
+
+@pytest.mark.parametrize("kt,groups", [(cols.UINT8, 5), (cols.INT32, 700), (cols.INT64, 200_000)])
+def test_groupby_consume_selected_equals_groupby_of_filtered_columns(ctx, kt, groups):
+    """b200_groupby_consume_selected == GroupBy over Filter(column, selection) of every column, for the tiny, the
+    shared-table and the global-table paths (min_max and nulls included)."""
+    rng = np.random.default_rng(groups)
+    n = 400_000
+    key = Column.from_numpy(rng.integers(0, groups, size=n).astype(cols.NP_OF[kt]))
+    arg = Column.from_numpy(rng.random(n) * 1e6 - 5e5, rng.random(n) > 0.03)
+    sel_bits = rng.random(n) < 0.6
+    sel = Column.from_numpy(sel_bits)
+    for aggs in ([AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT), AggSpec(cols.HASH_MEAN)],
+                 [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MIN_MAX), AggSpec(cols.HASH_COUNT, 1)]):
+        got = capi.group_by(ctx, [key.to_device()], aggs, [arg.to_device()] * len(aggs), expected_groups=groups,
+                            selection=sel.to_device())
+        fk = oracle.filter(key, sel, 0, kind=ORACLE)
+        fa = oracle.filter(arg, sel, 0, kind=ORACLE)
+        fkc = Column.from_numpy(fk.values().copy())
+        fac = Column.from_numpy(fa.values().copy(), fa.valid().copy())
+        want = oracle.groupby([fkc], aggs, [fac] * len(aggs), kind=ORACLE)
+        a = GroupRes(got.num_groups, [[_host(c) for c in ag] for ag in got.aggs], [_host(k) for k in got.keys])
+        b = GroupRes(want.num_groups, want.aggs, want.keys)
+        assert_group_equal(a, b, aggs, rtol=1e-12)
