@@ -773,6 +773,11 @@ Result<std::unique_ptr<internal::Grouper>> MakeGrouper(const std::vector<ValueDe
 
 Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Datum>& keys,
                       const std::vector<internal::Aggregate>& aggregates, ExecContext* ctx) {
+  return GroupBy(arguments, keys, aggregates, Datum(), ctx);
+}
+
+Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Datum>& keys,
+                      const std::vector<internal::Aggregate>& aggregates, const Datum& selection, ExecContext* ctx) {
   if (!ctx) return Status::Invalid("cuda::GroupBy needs an ExecContext carrying the CUDA registry");
   // GetKernels (hash_aggregate.cc:809-830)
   if (aggregates.size() != arguments.size()) {
@@ -815,6 +820,24 @@ Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Dat
   for (const auto& c : arg_chunks) if (c.size() != n_batches) return Status::NotImplemented("GroupBy: arguments and keys must share one chunk layout");
   for (const auto& c : key_chunks) if (c.size() != n_batches) return Status::NotImplemented("GroupBy: arguments and keys must share one chunk layout");
 
+  // the selection: a device-resident boolean column in the keys' chunk layout, no null slots (a
+  // filter with nulls drops or emits them by FilterOptions, vector_selection.cc:786-835 — that is
+  // Filter's business), every chunk's bitmap at a 32-bit word boundary
+  const bool selected = selection.kind() != Datum::NONE;
+  ArrayVector sel_chunks;
+  if (selected) {
+    if (selection.type()->id() != Type::BOOL) return Status::TypeError("GroupBy selection must be boolean, got ", selection.type()->ToString());
+    if (selection.length() != total) return Status::Invalid("Array arguments must all be the same length");
+    ARROW_ASSIGN_OR_RAISE(sel_chunks, ChunksOf(selection));
+    if (sel_chunks.size() != n_batches) return Status::NotImplemented("GroupBy: selection and keys must share one chunk layout");
+    for (const auto& c : sel_chunks) {
+      const ArrayData& d = *c->data();
+      if (d.buffers[0] && d.null_count.load() != 0) return Status::NotImplemented("GroupBy: selection with null slots (run Filter first)");
+      if (d.offset % 32 != 0 || (d.buffers[1] && d.buffers[1]->address() % 4 != 0))
+        return Status::NotImplemented("GroupBy: selection bitmap must start at a 32-bit word boundary");
+    }
+  }
+
   GroupByHandle handle;
   ARROW_ASSIGN_OR_RAISE(handle.dev, GetDevice(0));
   DeviceState* dev = handle.dev;
@@ -833,7 +856,14 @@ Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Dat
       if (arg_chunks[i][b]->length() != len) return Status::NotImplemented("GroupBy: arguments and keys must share one chunk layout");
       RETURN_NOT_OK(ToCol(*arg_chunks[i][b]->data(), specs[i].arg_type, &acols[i]));
     }
-    B200_OK_OR_RAISE(dev, b200_groupby_consume(handle.gb, kcols.data(), acols.data(), row_base));
+    if (selected) {
+      const ArrayData& d = *sel_chunks[b]->data();
+      if (d.length != len) return Status::NotImplemented("GroupBy: selection and keys must share one chunk layout");
+      const void* bits = reinterpret_cast<const void*>(d.buffers[1]->address() + d.offset / 8);
+      B200_OK_OR_RAISE(dev, b200_groupby_consume_selected(handle.gb, kcols.data(), acols.data(), row_base, bits));
+    } else {
+      B200_OK_OR_RAISE(dev, b200_groupby_consume(handle.gb, kcols.data(), acols.data(), row_base));
+    }
     row_base += uint64_t(len);
   }
   uint32_t num_groups = 0;

@@ -52,6 +52,14 @@ Result<std::unique_ptr<FunctionRegistry>> MakeCudaRegistry(int device = 0);
 Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Datum>& keys,
                       const std::vector<internal::Aggregate>& aggregates, ExecContext* ctx);
 
+/// GroupBy over the rows selected by a device-resident boolean column (no null slots):
+/// == GroupBy over Filter(column, selection) of every argument and key (FilterOptions::DROP), group
+/// order included, without materialising the filtered columns (b200_groupby_consume_selected).
+/// No counterpart upstream, where this is Filter on every column followed by GroupBy.
+Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Datum>& keys,
+                      const std::vector<internal::Aggregate>& aggregates, const Datum& selection,
+                      ExecContext* ctx);
+
 /// compute::internal::Grouper (api_aggregate.h:313-331) over device-resident key batches.
 /// The reference's Grouper::Make is a hard-wired static factory (hash_aggregate.cc:885-888) and
 /// cannot be swapped through the registry, hence this twin.  Consume() returns a device-resident

@@ -365,6 +365,24 @@ int main() {
       auto got = HostArray(GET(cp::cuda::GroupBy(da, dk, aggs, &gpu_ctx)));
       ExpectStructClose(got, want, "GroupBy random " + c.name);
     }
+    // selection folded into the aggregation == the reference's Filter on every column, then its GroupBy
+    {
+      auto sel = MakeRandom<BooleanBuilder, int>(n, rng, 0.0, 0, 2, false);
+      for (auto& c : cases) {
+        std::vector<Datum> hk, dk, ha, da;
+        for (auto& k : c.keys) { hk.push_back(GET(cp::CallFunction("filter", {Datum(k), Datum(sel)}, &cpu_ctx))); dk.push_back(DeviceDatum(k)); }
+        auto farg = GET(cp::CallFunction("filter", {Datum(c.arg), Datum(sel)}, &cpu_ctx));
+        for (size_t i = 0; i < aggs.size(); ++i) { ha.push_back(farg); da.push_back(DeviceDatum(c.arg)); }
+        auto want = GET(cp::internal::GroupBy(ha, hk, aggs, &cpu_ctx)).make_array();
+        auto got = HostArray(GET(cp::cuda::GroupBy(da, dk, aggs, DeviceDatum(sel), &gpu_ctx)));
+        ExpectStructClose(got, want, "GroupBy with selection == GroupBy(Filter(...)) " + c.name);
+      }
+      auto with_nulls = MakeRandom<BooleanBuilder, int>(n, rng, 0.1, 0, 2, false);
+      auto st = cp::cuda::GroupBy({DeviceDatum(vals)}, {DeviceDatum(keys32)}, {{"hash_sum", nullptr}}, DeviceDatum(with_nulls), &gpu_ctx).status();
+      CHECK_TRUE(st.IsNotImplemented(), "GroupBy selection with null slots -> NotImplemented");
+      auto st2 = cp::cuda::GroupBy({DeviceDatum(vals)}, {DeviceDatum(keys32)}, {{"hash_sum", nullptr}}, DeviceDatum(keys8), &gpu_ctx).status();
+      CHECK_TRUE(st2.IsTypeError(), "GroupBy non-boolean selection -> TypeError");
+    }
     // hash_mean == MeanImpl::Finalize over hash_sum / hash_count of the reference
     {
       auto want = GET(cp::internal::GroupBy({vals, vals}, {keys32}, {{"hash_sum", nullptr}, {"hash_count", nullptr}}, &cpu_ctx)).make_array();
