@@ -178,21 +178,30 @@ def compare_scalar(ctx: Context, values: Column, op: str, scalar) -> Column:
     return Column(BOOL, out, values.validity, n, 0, values.null_count if values.validity is not None else 0)
 
 
-def take(ctx: Context, values: Column, indices, boundscheck: bool = True, want_null_count: bool = True) -> Column:
-    """== compute::Take(values, indices, TakeOptions(boundscheck)) on device columns.  `indices` is a Column of
-    any integer type, or the int64-typed tensor b200_sort_indices returns (uint64 indices, no nulls)."""
+def take(ctx: Context, values, indices, boundscheck: bool = True, want_null_count: bool = True) -> Column:
+    """== compute::Take(values, indices, TakeOptions(boundscheck)) on device columns.  `values` is a Column or a
+    sequence of Columns of one type (the chunks of a ChunkedArray: indices address their concatenation,
+    b200_take_chunked).  `indices` is a Column of any integer type, or the int64-typed tensor b200_sort_indices
+    returns (uint64 indices, no nulls)."""
     from .columns import UINT64
     if isinstance(indices, torch.Tensor):
         indices = Column(UINT64, indices.view(torch.uint8).reshape(-1), None, indices.numel(), 0, 0)
+    chunks = None if isinstance(values, Column) else list(values)
+    vtype = values.type if chunks is None else chunks[0].type
     n = indices.length
-    bits = BITS[values.type]
+    bits = BITS[vtype]
     out = ctx.empty((n + 31) // 32 * 4 + 8 if bits == 1 else max(n, 1) * (bits // 8))
     out_v = ctx.empty((n + 31) // 32 * 4 + 8)
     nc = C.c_int64(-1)
-    v, i = values.desc(), indices.desc()
-    ctx.check(lib().b200_take(ctx._h, C.byref(v), C.byref(i), C.c_int(1 if boundscheck else 0), C.c_void_p(out.data_ptr()),
-                              C.c_void_p(out_v.data_ptr()), C.byref(nc) if want_null_count else None))
-    return Column(values.type, out, out_v, n, 0, int(nc.value) if want_null_count else -1)
+    i = indices.desc()
+    tail = (C.byref(i), C.c_int(1 if boundscheck else 0), C.c_void_p(out.data_ptr()), C.c_void_p(out_v.data_ptr()),
+            C.byref(nc) if want_null_count else None)
+    if chunks is None:
+        v = values.desc()
+        ctx.check(lib().b200_take(ctx._h, C.byref(v), *tail))
+    else:
+        ctx.check(lib().b200_take_chunked(ctx._h, col_array(chunks), C.c_int(len(chunks)), *tail))
+    return Column(vtype, out, out_v, n, 0, int(nc.value) if want_null_count else -1)
 
 
 ARITH_OPS = {"add": 0, "subtract": 1, "multiply": 2}

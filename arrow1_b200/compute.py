@@ -147,12 +147,21 @@ def SortIndices(values: Column, order: int = ASCENDING, ctx: Optional[capi.Conte
     return h.view(np.uint64)
 
 
-def Take(values: Column, indices, boundscheck: bool = True, ctx: Optional[capi.Context] = None) -> Column:
-    """== compute::Take (compute/api_vector.cc:101-105) for fixed-width values.  Host columns are staged to the
-    device and the result comes back to the host; device columns (or a device index tensor from SortIndices) stay."""
+def Take(values, indices, boundscheck: bool = True, ctx: Optional[capi.Context] = None) -> Column:
+    """== compute::Take (compute/api_vector.cc:101-105) for fixed-width values.  `values` is a Column or a
+    sequence of Columns (ChunkedArray values, TakeCA vector_selection.cc:1921-1944: indices address the
+    concatenation; the result is one Column).  Host columns are staged to the device and the result comes back
+    to the host; device columns (or a device index tensor from SortIndices) stay."""
     ctx = ctx or default_context()
-    host = not values.on_device
-    dv, b0 = _h2d(values, ctx)
+    if isinstance(values, Column):
+        host = not values.on_device
+        dv, b0 = _h2d(values, ctx)
+    else:
+        if len(values) == 0:
+            raise B200Error(4, "take: no chunks")
+        host = not values[0].on_device
+        staged = [_h2d(v, ctx) for v in values]
+        dv, b0 = [c for c, _ in staged], sum(b for _, b in staged)
     di, b1 = (indices, 0) if isinstance(indices, torch.Tensor) else _h2d(indices, ctx)
     out = capi.take(ctx, dv, di, boundscheck)
     Transfer.h2d, Transfer.d2h = b0 + b1, 0

@@ -14,6 +14,7 @@
 // HBM roofline: 8 B/row values + 3/8 B/row bitmaps read, s*(8+1/8) B/row written.
 #include <type_traits>
 
+#include <vector>
 #include "common.cuh"
 
 namespace {
@@ -379,7 +380,19 @@ struct TakeArgs {
   void* out;
   uint32_t* out_valid;
   unsigned long long* counters;   // [0] valid rows, [1] first row with an out-of-bounds index (or ~0)
+  // chunked values (b200_take_chunked): chunk c holds logical rows [starts[c], starts[c + 1])
+  const struct TakeChunk* chunks;
+  const int64_t* starts;          // device, n_chunks + 1 entries
+  int32_t n_chunks;
 };
+
+struct TakeChunk {
+  const void* vdata;   // shifted by the chunk's element offset (not for bool)
+  BitmapRef vbits;     // bool values
+  BitmapRef vv;        // validity (words == nullptr: no nulls)
+};
+
+constexpr int kTakeSharedStarts = 1024;   // chunk boundaries kept in shared memory up to this many chunks
 
 // the index as an unsigned number, and whether it is non-negative (I is the index C type: no per-row dispatch,
 // so the compiler can batch the loads of a thread's rows)
@@ -392,8 +405,16 @@ __device__ __forceinline__ bool take_index(const TakeArgs& a, int64_t row, uint6
 
 constexpr int kTakeItems = 8;   // gathers in flight per thread
 
-template <typename V, bool kBool, typename I>
+template <typename V, bool kBool, typename I, bool kChunked = false>
 __global__ void __launch_bounds__(256) take_kernel(const __grid_constant__ TakeArgs a) {
+  // chunked values: the boundaries go to shared memory once per CTA (global memory beyond 1024 chunks)
+  __shared__ int64_t s_starts[kChunked ? kTakeSharedStarts + 1 : 1];
+  const int64_t* starts = a.starts;
+  if (kChunked && a.n_chunks <= kTakeSharedStarts) {
+    for (int c = threadIdx.x; c <= a.n_chunks; c += blockDim.x) s_starts[c] = a.starts[c];
+    __syncthreads();
+    starts = s_starts;
+  }
   const int lane = threadIdx.x & 31;
   const int64_t warp = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const int64_t base = warp * (32 * kTakeItems);
@@ -421,10 +442,32 @@ __global__ void __launch_bounds__(256) take_kernel(const __grid_constant__ TakeA
   }
   V val[kTakeItems];
   bool vvalid[kTakeItems];
+  if (kChunked) {
+    // the last chunk whose first row is <= the index (empty chunks share a boundary with their successor and
+    // are never picked); the eight searches of a thread are independent and interleave
+    int chunk[kTakeItems];
 #pragma unroll
-  for (int k = 0; k < kTakeItems; ++k) {
-    vvalid[k] = bitmap_get(a.vv, int64_t(ix[k]));
-    val[k] = kBool ? V(bitmap_get(a.vbits, int64_t(ix[k]))) : reinterpret_cast<const V*>(a.vdata)[ix[k]];
+    for (int k = 0; k < kTakeItems; ++k) {
+      int lo = 0, hi = a.n_chunks;          // invariant: starts[lo] <= ix < starts[hi]
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (uint64_t(starts[mid]) <= ix[k]) lo = mid; else hi = mid;
+      }
+      chunk[k] = lo;
+      ix[k] -= uint64_t(starts[lo]);
+    }
+#pragma unroll
+    for (int k = 0; k < kTakeItems; ++k) {
+      const TakeChunk c = a.chunks[chunk[k]];
+      vvalid[k] = bitmap_get(c.vv, int64_t(ix[k]));
+      val[k] = kBool ? V(bitmap_get(c.vbits, int64_t(ix[k]))) : reinterpret_cast<const V*>(c.vdata)[ix[k]];
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < kTakeItems; ++k) {
+      vvalid[k] = bitmap_get(a.vv, int64_t(ix[k]));
+      val[k] = kBool ? V(bitmap_get(a.vbits, int64_t(ix[k]))) : reinterpret_cast<const V*>(a.vdata)[ix[k]];
+    }
   }
 #pragma unroll
   for (int k = 0; k < kTakeItems; ++k) {
@@ -452,7 +495,8 @@ template <typename V, bool kBool, typename I>
 int launch_take_i(b200_ctx* ctx, const TakeArgs& a) {
   const int64_t warps = (a.n + 32 * kTakeItems - 1) / (32 * kTakeItems);
   const unsigned grid = unsigned((warps * 32 + 255) / 256);
-  B200_TIMED(ctx, "take", (take_kernel<V, kBool, I><<<grid, 256, 0, ctx->stream>>>(a)));
+  if (a.chunks) B200_TIMED(ctx, "take", (take_kernel<V, kBool, I, true><<<grid, 256, 0, ctx->stream>>>(a)));
+  else B200_TIMED(ctx, "take", (take_kernel<V, kBool, I><<<grid, 256, 0, ctx->stream>>>(a)));
   return B200_OK;
 }
 
@@ -537,36 +581,70 @@ int launch_arith(b200_ctx* ctx, int op, const b200_col* a, const void* a_scalar,
 
 extern "C" {
 
-int b200_take(b200_ctx* ctx, const b200_col* values, const b200_col* indices, int boundscheck, void* out_data,
-              void* out_validity, int64_t* out_null_count) {
-  if (!ctx) return B200_INVALID;
-  if (!values || !indices) return b200_fail(ctx, B200_INVALID, "take: null argument");
+// values: one column (n_chunks == 0) or the chunks of one (n_chunks >= 1, all of one type)
+static int take_impl(b200_ctx* ctx, const b200_col* values, int n_chunks, const b200_col* indices, int boundscheck,
+                     void* out_data, void* out_validity, int64_t* out_null_count) {
   const int vbits = b200_type_bits(values->type);
   if (vbits == 0) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "take: unsupported values type %d", values->type);
   const int ibits = b200_type_bits(indices->type);
   if (ibits < 8 || indices->type == B200_FLOAT || indices->type == B200_DOUBLE)
     return b200_fail(ctx, B200_TYPE_ERROR, "take: indices must be an integer column, got type %d", indices->type);
-  if (values->length < 0 || values->offset < 0 || indices->length < 0 || indices->offset < 0)
-    return b200_fail(ctx, B200_INVALID, "take: negative length/offset");
+  if (indices->length < 0 || indices->offset < 0) return b200_fail(ctx, B200_INVALID, "take: negative length/offset");
+  const int n_cols = n_chunks > 0 ? n_chunks : 1;
+  int64_t vlen = 0;
+  for (int c = 0; c < n_cols; ++c) {
+    if (values[c].type != values->type) return b200_fail(ctx, B200_TYPE_ERROR, "take: chunks of different types");
+    if (values[c].length < 0 || values[c].offset < 0) return b200_fail(ctx, B200_INVALID, "take: negative length/offset");
+    if (values[c].length > 0 && !values[c].data) return b200_fail(ctx, B200_INVALID, "take: null values buffer");
+    vlen += values[c].length;
+  }
   const int64_t n = indices->length;
   if (out_null_count) *out_null_count = 0;
   if (n == 0) return B200_OK;
-  if (!indices->data || !out_data || !out_validity || (values->length > 0 && !values->data))
+  if (!indices->data || !out_data || !out_validity)
     return b200_fail(ctx, B200_INVALID, "take: null buffer (the output validity bitmap is always produced)");
-  B200_RETURN_NOT_OK(b200_ctx_reserve_scratch(ctx, 256));
+  const size_t starts_bytes = (size_t(n_cols) + 1) * sizeof(int64_t);
+  B200_RETURN_NOT_OK(b200_ctx_reserve_scratch(ctx, 256 + starts_bytes + size_t(n_cols) * sizeof(TakeChunk)));
   unsigned long long* counters = reinterpret_cast<unsigned long long*>(ctx->scratch);
   const unsigned long long init[2] = {0ull, ~0ull};
   ctx->host_words[8] = int64_t(init[0]);
   ctx->host_words[9] = int64_t(init[1]);
   B200_CUDA(ctx, cudaMemcpyAsync(counters, ctx->host_words + 8, 16, cudaMemcpyHostToDevice, ctx->stream));
   TakeArgs a;
-  a.vdata = vbits >= 8 ? reinterpret_cast<const char*>(values->data) + values->offset * (vbits / 8) : nullptr;
-  a.vbits = make_bitmap_ref(values->data, values->offset);
-  a.vv = (values->validity && values->null_count != 0) ? make_bitmap_ref(values->validity, values->offset) : BitmapRef{nullptr, 0};
-  a.vlen = values->length;
-  if (values->length == 0) {   // every index is out of range; the clamped gathers read row 0 of the scratch block
+  a.chunks = nullptr;
+  a.starts = nullptr;
+  a.n_chunks = 0;
+  a.vlen = vlen;
+  if (vlen == 0) {   // every index is out of range; the clamped gathers read row 0 of the scratch block
     a.vdata = counters;
     a.vbits = make_bitmap_ref(counters, 0);
+    a.vv = BitmapRef{nullptr, 0};
+  } else if (n_chunks <= 1) {
+    a.vdata = vbits >= 8 ? reinterpret_cast<const char*>(values->data) + values->offset * (vbits / 8) : nullptr;
+    a.vbits = make_bitmap_ref(values->data, values->offset);
+    a.vv = (values->validity && values->null_count != 0) ? make_bitmap_ref(values->validity, values->offset) : BitmapRef{nullptr, 0};
+  } else {
+    // chunk table: pageable source, so the runtime has staged it by the time the copy call returns
+    std::vector<int64_t> starts(size_t(n_cols) + 1);
+    std::vector<TakeChunk> table(n_cols);
+    int64_t at = 0;
+    for (int c = 0; c < n_cols; ++c) {
+      const b200_col& v = values[c];
+      starts[c] = at;
+      at += v.length;
+      table[c].vdata = vbits >= 8 ? reinterpret_cast<const char*>(v.data) + v.offset * (vbits / 8) : nullptr;
+      table[c].vbits = make_bitmap_ref(v.data, v.offset);
+      table[c].vv = (v.validity && v.null_count != 0) ? make_bitmap_ref(v.validity, v.offset) : BitmapRef{nullptr, 0};
+    }
+    starts[n_cols] = at;
+    char* base = reinterpret_cast<char*>(ctx->scratch) + 256;
+    B200_CUDA(ctx, cudaMemcpyAsync(base, starts.data(), starts_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    B200_CUDA(ctx, cudaMemcpyAsync(base + starts_bytes, table.data(), table.size() * sizeof(TakeChunk), cudaMemcpyHostToDevice, ctx->stream));
+    a.starts = reinterpret_cast<const int64_t*>(base);
+    a.chunks = reinterpret_cast<const TakeChunk*>(base + starts_bytes);
+    a.n_chunks = n_cols;
+    a.vdata = nullptr;
+    a.vbits = BitmapRef{nullptr, 0};
     a.vv = BitmapRef{nullptr, 0};
   }
   a.idata = reinterpret_cast<const char*>(indices->data) + indices->offset * (ibits / 8);
@@ -604,6 +682,20 @@ int b200_take(b200_ctx* ctx, const b200_col* values, const b200_col* indices, in
     if (out_null_count) *out_null_count = n - ctx->host_words[8];
   }
   return B200_OK;
+}
+
+int b200_take(b200_ctx* ctx, const b200_col* values, const b200_col* indices, int boundscheck, void* out_data,
+              void* out_validity, int64_t* out_null_count) {
+  if (!ctx) return B200_INVALID;
+  if (!values || !indices) return b200_fail(ctx, B200_INVALID, "take: null argument");
+  return take_impl(ctx, values, 0, indices, boundscheck, out_data, out_validity, out_null_count);
+}
+
+int b200_take_chunked(b200_ctx* ctx, const b200_col* chunks, int n_chunks, const b200_col* indices, int boundscheck,
+                      void* out_data, void* out_validity, int64_t* out_null_count) {
+  if (!ctx) return B200_INVALID;
+  if (!chunks || !indices || n_chunks < 1) return b200_fail(ctx, B200_INVALID, "take_chunked: null argument or no chunks");
+  return take_impl(ctx, chunks, n_chunks, indices, boundscheck, out_data, out_validity, out_null_count);
 }
 
 int b200_arithmetic(b200_ctx* ctx, int op, const b200_col* a, const void* a_scalar, const b200_col* b, const void* b_scalar,

@@ -14,6 +14,7 @@
 
 #include "arrow/array.h"
 #include "arrow/array/data.h"
+#include "arrow/array/util.h"
 #include "arrow/buffer.h"
 #include "arrow/chunked_array.h"
 #include "arrow/compute/api_vector.h"
@@ -153,20 +154,26 @@ Status ToCol(const ArrayData& a, int32_t type, b200_col* c) {
 }
 
 // ---- Filter --------------------------------------------------------------------------------------
-// == PrimitiveFilter (vector_selection.cc:786-835): GetFilterOutputSize -> PreallocateData -> Exec
-Result<std::shared_ptr<ArrayData>> FilterArray(DeviceState* dev, const ArrayData& values,
-                                               const ArrayData& mask, int null_selection) {
+// == PrimitiveFilter (vector_selection.cc:786-835): GetFilterOutputSize -> PreallocateData -> Exec, for every
+// column that shares the mask: ONE plan (the scan of the mask) serves all of them, which is what
+// FilterRecordBatch / FilterTable get from their shared take-index vector (vector_selection.cc:1776-1866)
+Result<std::vector<std::shared_ptr<ArrayData>>> FilterColumns(DeviceState* dev, const std::vector<const ArrayData*>& columns,
+                                                              const ArrayData& mask, int null_selection) {
   if (mask.type->id() != Type::BOOL) {
     return Status::NotImplemented("Filter argument must be boolean type");
   }
-  if (values.length != mask.length) {
-    // exec.cc:186-189 (ExecBatchIterator) — the code the reference's tests assert
-    return Status::Invalid("Array arguments must all be the same length");
-  }
-  ARROW_ASSIGN_OR_RAISE(const int32_t vtype, PhysicalType(*values.type));
-  b200_col v, m;
-  RETURN_NOT_OK(ToCol(values, vtype, &v));
+  b200_col m;
   RETURN_NOT_OK(ToCol(mask, B200_BOOL, &m));
+  std::vector<b200_col> v(columns.size());
+  std::vector<int32_t> vtypes(columns.size());
+  for (size_t c = 0; c < columns.size(); ++c) {
+    if (columns[c]->length != mask.length) {
+      // exec.cc:186-189 (ExecBatchIterator) — the code the reference's tests assert
+      return Status::Invalid("Array arguments must all be the same length");
+    }
+    ARROW_ASSIGN_OR_RAISE(vtypes[c], PhysicalType(*columns[c]->type));
+    RETURN_NOT_OK(ToCol(*columns[c], vtypes[c], &v[c]));
+  }
 
   std::lock_guard<std::mutex> lock(dev->mutex);
   size_t plan_bytes = 0;
@@ -176,24 +183,59 @@ Result<std::shared_ptr<ArrayData>> FilterArray(DeviceState* dev, const ArrayData
   int64_t out_len = 0;
   B200_OK_OR_RAISE(dev, b200_filter_plan(dev->ctx, &m, null_selection, plan_ptr, &out_len));
 
-  int allocate_validity = 0;
-  int64_t out_null_count = 0;
-  B200_OK_OR_RAISE(dev, b200_filter_out_spec(&v, &m, null_selection, &allocate_validity, &out_null_count));
-
-  const int bits = vtype == B200_BOOL ? 1 : checked_cast<const FixedWidthType&>(*values.type).bit_width();
-  const int64_t data_bytes = bits == 1 ? BitmapBytes(out_len) : out_len * (bits / 8);
-  ARROW_ASSIGN_OR_RAISE(auto out_data, AllocateDevice(dev, data_bytes));
-  std::shared_ptr<Buffer> out_validity;
-  if (allocate_validity) {
-    ARROW_ASSIGN_OR_RAISE(out_validity, AllocateDevice(dev, BitmapBytes(out_len)));
+  std::vector<std::shared_ptr<ArrayData>> out(columns.size());
+  for (size_t c = 0; c < columns.size(); ++c) {
+    int allocate_validity = 0;
+    int64_t out_null_count = 0;
+    B200_OK_OR_RAISE(dev, b200_filter_out_spec(&v[c], &m, null_selection, &allocate_validity, &out_null_count));
+    const int bits = vtypes[c] == B200_BOOL ? 1 : checked_cast<const FixedWidthType&>(*columns[c]->type).bit_width();
+    const int64_t data_bytes = bits == 1 ? BitmapBytes(out_len) : out_len * (bits / 8);
+    ARROW_ASSIGN_OR_RAISE(auto out_data, AllocateDevice(dev, data_bytes));
+    std::shared_ptr<Buffer> out_validity;
+    if (allocate_validity) {
+      ARROW_ASSIGN_OR_RAISE(out_validity, AllocateDevice(dev, BitmapBytes(out_len)));
+    }
+    B200_OK_OR_RAISE(dev, b200_filter_apply(dev->ctx, &v[c], &m, null_selection, plan_ptr,
+                                            reinterpret_cast<void*>(out_data->address()),
+                                            out_validity ? reinterpret_cast<void*>(out_validity->address()) : nullptr,
+                                            out_len));
+    out[c] = ArrayData::Make(columns[c]->type, out_len, {std::move(out_validity), std::move(out_data)}, out_null_count);
   }
-  B200_OK_OR_RAISE(dev, b200_filter_apply(dev->ctx, &v, &m, null_selection, plan_ptr,
-                                          reinterpret_cast<void*>(out_data->address()),
-                                          out_validity ? reinterpret_cast<void*>(out_validity->address()) : nullptr,
-                                          out_len));
   // the plan buffer is released when this returns: its last reader must have finished
   B200_OK_OR_RAISE(dev, b200_ctx_synchronize(dev->ctx));
-  return ArrayData::Make(values.type, out_len, {std::move(out_validity), std::move(out_data)}, out_null_count);
+  return out;
+}
+
+Result<std::shared_ptr<ArrayData>> FilterArray(DeviceState* dev, const ArrayData& values,
+                                               const ArrayData& mask, int null_selection) {
+  if (values.length != mask.length && mask.type->id() == Type::BOOL) {
+    return Status::Invalid("Array arguments must all be the same length");
+  }
+  ARROW_ASSIGN_OR_RAISE(auto out, FilterColumns(dev, {&values}, mask, null_selection));
+  return out[0];
+}
+
+// An output whose null count PrimitiveFilter leaves unknown (vector_selection.cc:799-812) must have it
+// settled before it becomes a chunk: ChunkedArray's constructor sums chunk->null_count()
+// (chunked_array.cc:46-63), which would scan the bitmap on the host.  The set bits of the validity bitmap are
+// counted on the device instead — GetFilterOutputSize of the bitmap read as a boolean column.
+Status SettleNullCount(DeviceState* dev, ArrayData* a) {
+  if (a->null_count.load() != kUnknownNullCount) return Status::OK();
+  if (!a->buffers[0] || a->length == 0) {
+    a->null_count = 0;
+    return Status::OK();
+  }
+  b200_col bits;
+  std::memset(&bits, 0, sizeof(bits));
+  bits.data = reinterpret_cast<const void*>(a->buffers[0]->address());
+  bits.type = B200_BOOL;
+  bits.length = a->length;
+  bits.offset = a->offset;
+  int64_t valid = 0;
+  std::lock_guard<std::mutex> lock(dev->mutex);
+  B200_OK_OR_RAISE(dev, b200_filter_count(dev->ctx, &bits, 0, &valid));
+  a->null_count = a->length - valid;
+  return Status::OK();
 }
 
 // ---- Take ----------------------------------------------------------------------------------------
@@ -219,6 +261,32 @@ Result<std::shared_ptr<ArrayData>> TakeArray(DeviceState* dev, const ArrayData& 
   return ArrayData::Make(values.type, n, {std::move(out_validity), std::move(out_data)}, null_count);
 }
 
+// == TakeCA (vector_selection.cc:1921-1944) without its Concatenate: the chunks are gathered from where
+// they lie (b200_take_chunked); one output array
+Result<std::shared_ptr<ArrayData>> TakeChunks(DeviceState* dev, const ChunkedArray& values, const ArrayData& indices,
+                                              bool boundscheck) {
+  if (values.num_chunks() == 0) return Status::Invalid("Must pass at least one array");   // Concatenate's
+  if (values.num_chunks() == 1) return TakeArray(dev, *values.chunk(0)->data(), indices, boundscheck);
+  ARROW_ASSIGN_OR_RAISE(const int32_t vtype, PhysicalType(*values.type()));
+  if (!is_integer(indices.type->id())) return Status::NotImplemented("Take indices must be integer type");
+  ARROW_ASSIGN_OR_RAISE(const int32_t itype, NumericType(*indices.type));
+  std::vector<b200_col> v(values.num_chunks());
+  for (int c = 0; c < values.num_chunks(); ++c) RETURN_NOT_OK(ToCol(*values.chunk(c)->data(), vtype, &v[c]));
+  b200_col i;
+  RETURN_NOT_OK(ToCol(indices, itype, &i));
+  std::lock_guard<std::mutex> lock(dev->mutex);
+  const int bits = vtype == B200_BOOL ? 1 : checked_cast<const FixedWidthType&>(*values.type()).bit_width();
+  const int64_t n = indices.length;
+  const int64_t bitmap_bytes = (n + 31) / 32 * 4;
+  ARROW_ASSIGN_OR_RAISE(auto out_data, AllocateDevice(dev, bits == 1 ? bitmap_bytes : n * (bits / 8)));
+  ARROW_ASSIGN_OR_RAISE(auto out_validity, AllocateDevice(dev, bitmap_bytes));
+  int64_t null_count = 0;
+  B200_OK_OR_RAISE(dev, b200_take_chunked(dev->ctx, v.data(), int(v.size()), &i, boundscheck ? 1 : 0,
+                                          reinterpret_cast<void*>(out_data->address()),
+                                          reinterpret_cast<void*>(out_validity->address()), &null_count));
+  return ArrayData::Make(values.type(), n, {std::move(out_validity), std::move(out_data)}, null_count);
+}
+
 struct TakeStateB200 : public KernelState {
   explicit TakeStateB200(bool boundscheck) : boundscheck(boundscheck) {}
   bool boundscheck;
@@ -232,18 +300,83 @@ const FunctionDoc take_doc("Select values by integer indices (CUDA)", "Array x A
                            {"input", "indices"}, "TakeOptions");
 const TakeOptions kDefaultTakeOptions = TakeOptions::Defaults();
 
-// == TakeMetaFunction (vector_selection.cc:2028-2081), Array x Array route
+// == TakeMetaFunction (vector_selection.cc:2028-2081) and its routes TakeAA / CA / CC / AC / RA / TA / TC
+// (:1914-2017): same dispatch, same output shapes (CA -> one chunk; CC, AC -> one chunk per index chunk)
 class CudaTakeMetaFunction : public MetaFunction {
  public:
-  CudaTakeMetaFunction() : MetaFunction("take", Arity::Binary(), &take_doc, &kDefaultTakeOptions) {}
+  explicit CudaTakeMetaFunction(int device)
+      : MetaFunction("take", Arity::Binary(), &take_doc, &kDefaultTakeOptions), device_(device) {}
   Result<Datum> ExecuteImpl(const std::vector<Datum>& args, const FunctionOptions* options,
                             ExecContext* ctx) const override {
-    if (args[0].kind() == Datum::ARRAY && args[1].kind() == Datum::ARRAY) {
-      return CallFunction("array_take", args, options, ctx);
+    const Datum::Kind index_kind = args[1].kind();
+    const bool boundscheck = options ? static_cast<const TakeOptions*>(options)->boundscheck : true;
+    ARROW_ASSIGN_OR_RAISE(DeviceState * dev, GetDevice(device_));
+    switch (args[0].kind()) {
+      case Datum::ARRAY:
+        if (index_kind == Datum::ARRAY) return CallFunction("array_take", args, options, ctx);
+        if (index_kind == Datum::CHUNKED_ARRAY) {   // TakeAC
+          ArrayVector out;
+          for (const auto& ix : args[1].chunked_array()->chunks()) {
+            ARROW_ASSIGN_OR_RAISE(auto piece, TakeArray(dev, *args[0].array(), *ix->data(), boundscheck));
+            out.push_back(MakeArray(piece));
+          }
+          return Datum(std::make_shared<ChunkedArray>(std::move(out), args[0].type()));
+        }
+        break;
+      case Datum::CHUNKED_ARRAY:
+        if (index_kind == Datum::ARRAY) return TakeCA(dev, *args[0].chunked_array(), *args[1].array(), boundscheck);
+        if (index_kind == Datum::CHUNKED_ARRAY) return TakeCC(dev, *args[0].chunked_array(), *args[1].chunked_array(), boundscheck);
+        break;
+      case Datum::RECORD_BATCH:
+        if (index_kind == Datum::ARRAY) {   // TakeRA
+          const auto& batch = *args[0].record_batch();
+          std::vector<std::shared_ptr<ArrayData>> columns(batch.num_columns());
+          for (int j = 0; j < batch.num_columns(); ++j) {
+            ARROW_ASSIGN_OR_RAISE(columns[j], TakeArray(dev, *batch.column_data(j), *args[1].array(), boundscheck));
+          }
+          return Datum(RecordBatch::Make(batch.schema(), args[1].length(), std::move(columns)));
+        }
+        break;
+      case Datum::TABLE: {
+        const auto& table = *args[0].table();
+        std::vector<std::shared_ptr<ChunkedArray>> columns(table.num_columns());
+        if (index_kind == Datum::ARRAY) {   // TakeTA
+          for (int j = 0; j < table.num_columns(); ++j) {
+            ARROW_ASSIGN_OR_RAISE(columns[j], TakeCA(dev, *table.column(j), *args[1].array(), boundscheck));
+          }
+          return Datum(Table::Make(table.schema(), std::move(columns)));
+        }
+        if (index_kind == Datum::CHUNKED_ARRAY) {   // TakeTC
+          for (int j = 0; j < table.num_columns(); ++j) {
+            ARROW_ASSIGN_OR_RAISE(columns[j], TakeCC(dev, *table.column(j), *args[1].chunked_array(), boundscheck));
+          }
+          return Datum(Table::Make(table.schema(), std::move(columns)));
+        }
+        break;
+      }
+      default:
+        break;
     }
     return Status::NotImplemented("Unsupported types for take operation: values=", args[0].ToString(),
                                   "indices=", args[1].ToString());
   }
+
+ private:
+  static Result<std::shared_ptr<ChunkedArray>> TakeCA(DeviceState* dev, const ChunkedArray& values, const ArrayData& indices,
+                                                      bool boundscheck) {
+    ARROW_ASSIGN_OR_RAISE(auto piece, TakeChunks(dev, values, indices, boundscheck));
+    return std::make_shared<ChunkedArray>(ArrayVector{MakeArray(piece)}, values.type());
+  }
+  static Result<std::shared_ptr<ChunkedArray>> TakeCC(DeviceState* dev, const ChunkedArray& values, const ChunkedArray& indices,
+                                                      bool boundscheck) {
+    ArrayVector out;
+    for (const auto& ix : indices.chunks()) {
+      ARROW_ASSIGN_OR_RAISE(auto piece, TakeChunks(dev, values, *ix->data(), boundscheck));
+      out.push_back(MakeArray(piece));
+    }
+    return std::make_shared<ChunkedArray>(std::move(out), values.type());
+  }
+  int device_;
 };
 
 int NullSelectionOf(const FunctionOptions* options) {
@@ -306,29 +439,67 @@ class CudaFilterMetaFunction : public MetaFunction {
     ARROW_ASSIGN_OR_RAISE(DeviceState * dev, GetDevice(device_));
     const int null_selection = NullSelectionOf(options);
     if (args[0].kind() == Datum::RECORD_BATCH) {
-      if (args[1].kind() != Datum::ARRAY) return Status::NotImplemented("filter(RecordBatch, non-Array)");
+      // FilterRecordBatch (vector_selection.cc:1776-1797): one scan of the mask, every column compacted by it
+      if (args[1].kind() != Datum::ARRAY) return Status::NotImplemented("Filter should be array-like");
       const auto& batch = *args[0].record_batch();
-      std::vector<std::shared_ptr<ArrayData>> columns(batch.num_columns());
+      if (batch.num_rows() != args[1].length()) return Status::Invalid("Filter inputs must all be the same length");
+      std::vector<const ArrayData*> in(batch.num_columns());
+      for (int i = 0; i < batch.num_columns(); ++i) in[i] = batch.column_data(i).get();
+      ARROW_ASSIGN_OR_RAISE(auto columns, FilterColumns(dev, in, *args[1].array(), null_selection));
       int64_t out_len = 0;
-      for (int i = 0; i < batch.num_columns(); ++i) {
-        ARROW_ASSIGN_OR_RAISE(columns[i], FilterArray(dev, *batch.column_data(i), *args[1].array(), null_selection));
-        out_len = columns[i]->length;
+      if (columns.empty()) {   // no columns: the row count still follows the mask
+        std::lock_guard<std::mutex> lock(dev->mutex);
+        b200_col m;
+        RETURN_NOT_OK(ToCol(*args[1].array(), B200_BOOL, &m));
+        B200_OK_OR_RAISE(dev, b200_filter_count(dev->ctx, &m, null_selection, &out_len));
+      } else {
+        out_len = columns[0]->length;
       }
       return Datum(RecordBatch::Make(batch.schema(), out_len, std::move(columns)));
     }
     if (args[0].kind() == Datum::TABLE) {
-      return Status::NotImplemented("filter(Table): filter each RecordBatch");
+      // FilterTable (vector_selection.cc:1799-1866): columns and mask re-chunked consistently (slices only move
+      // offsets; no buffer is touched), then every mask chunk is planned once and applied to all columns
+      const auto& table = *args[0].table();
+      if (args[1].kind() != Datum::ARRAY && args[1].kind() != Datum::CHUNKED_ARRAY) return Status::NotImplemented("Filter should be array-like");
+      if (table.num_rows() != args[1].length()) return Status::Invalid("Filter inputs must all be the same length");
+      if (table.num_rows() == 0) return Datum(Table::Make(table.schema(), table.columns(), 0));
+      const int num_columns = table.num_columns();
+      std::vector<ArrayVector> inputs(num_columns + 1);
+      for (int i = 0; i < num_columns; ++i) inputs[i] = table.column(i)->chunks();
+      ARROW_ASSIGN_OR_RAISE(inputs.back(), ChunksOf(args[1]));
+      inputs = arrow::internal::RechunkArraysConsistently(inputs);
+      std::vector<ArrayVector> out_columns(num_columns);
+      int64_t out_rows = 0;
+      for (size_t b = 0; b < inputs.back().size(); ++b) {
+        std::vector<const ArrayData*> in(num_columns);
+        for (int c = 0; c < num_columns; ++c) in[c] = inputs[c][b]->data().get();
+        ARROW_ASSIGN_OR_RAISE(auto pieces, FilterColumns(dev, in, *inputs.back()[b]->data(), null_selection));
+        if (num_columns == 0 || pieces[0]->length == 0) continue;   // like upstream, empty pieces are not kept
+        for (int c = 0; c < num_columns; ++c) {
+          RETURN_NOT_OK(SettleNullCount(dev, pieces[c].get()));
+          out_columns[c].push_back(MakeArray(pieces[c]));
+        }
+        out_rows += pieces[0]->length;
+      }
+      std::vector<std::shared_ptr<ChunkedArray>> out_chunks(num_columns);
+      for (int c = 0; c < num_columns; ++c) {
+        out_chunks[c] = std::make_shared<ChunkedArray>(std::move(out_columns[c]), table.column(c)->type());
+      }
+      return Datum(Table::Make(table.schema(), std::move(out_chunks), out_rows));
     }
     if (args[0].kind() == Datum::CHUNKED_ARRAY || args[1].kind() == Datum::CHUNKED_ARRAY) {
-      // chunk pairs must line up (the reference re-chunks on the host; device chunks are not re-sliced here)
+      // upstream: array_filter through ExecBatchIterator, which slices both inputs to common chunk boundaries
+      // (exec.cc:150-215); here the same slicing, one output chunk per common piece
       ARROW_ASSIGN_OR_RAISE(auto vchunks, ChunksOf(args[0]));
       ARROW_ASSIGN_OR_RAISE(auto mchunks, ChunksOf(args[1]));
       if (args[0].length() != args[1].length()) return Status::Invalid("Array arguments must all be the same length");
-      if (vchunks.size() != mchunks.size()) return Status::NotImplemented("filter: values and mask chunk layouts differ");
+      if (args[0].length() == 0) return Datum(std::make_shared<ChunkedArray>(ArrayVector{}, args[0].type()));
+      auto groups = arrow::internal::RechunkArraysConsistently({vchunks, mchunks});
       ArrayVector out;
-      for (size_t i = 0; i < vchunks.size(); ++i) {
-        if (vchunks[i]->length() != mchunks[i]->length()) return Status::NotImplemented("filter: values and mask chunk layouts differ");
-        ARROW_ASSIGN_OR_RAISE(auto piece, FilterArray(dev, *vchunks[i]->data(), *mchunks[i]->data(), null_selection));
+      for (size_t i = 0; i < groups[0].size(); ++i) {
+        ARROW_ASSIGN_OR_RAISE(auto piece, FilterArray(dev, *groups[0][i]->data(), *groups[1][i]->data(), null_selection));
+        RETURN_NOT_OK(SettleNullCount(dev, piece.get()));
         out.push_back(MakeArray(piece));
       }
       return Datum(std::make_shared<ChunkedArray>(std::move(out), args[0].type()));
@@ -713,7 +884,7 @@ Status RegisterCudaKernels(FunctionRegistry* registry, int device) {
     RETURN_NOT_OK(func->AddKernel(std::move(kernel)));
     RETURN_NOT_OK(registry->AddFunction(std::move(func)));
   }
-  RETURN_NOT_OK(registry->AddFunction(std::make_shared<CudaTakeMetaFunction>()));
+  RETURN_NOT_OK(registry->AddFunction(std::make_shared<CudaTakeMetaFunction>(device)));
   // array_sort_indices: one kernel per numeric / temporal type (vector_sort.cc:582-595)
   {
     auto func = std::make_shared<VectorFunction>("array_sort_indices", Arity::Unary(), &array_sort_indices_doc, &kDefaultArraySortOptions);

@@ -84,6 +84,27 @@ std::shared_ptr<ArrayData> ToHost(const ArrayData& a) {
 Datum DeviceDatum(const std::shared_ptr<Array>& a) { return Datum(ToDevice(*a->data())); }
 std::shared_ptr<Array> HostArray(const Datum& d) { return MakeArray(ToHost(*d.array())); }
 
+// host ChunkedArray -> device-resident twin.  Null counts are settled on the host first: ChunkedArray's
+// constructor sums chunk->null_count() (chunked_array.cc:46-63), which must not scan a device bitmap.
+std::shared_ptr<ChunkedArray> DeviceChunked(const ChunkedArray& h) {
+  ArrayVector d;
+  for (const auto& c : h.chunks()) { (void)c->null_count(); d.push_back(MakeArray(ToDevice(*c->data()))); }
+  return std::make_shared<ChunkedArray>(d, h.type());
+}
+// slices of one host array as a ChunkedArray (cuts: boundaries, first 0, last length)
+std::shared_ptr<ChunkedArray> Chunked(const std::shared_ptr<Array>& a, const std::vector<int64_t>& cuts) {
+  ArrayVector out;
+  for (size_t i = 0; i + 1 < cuts.size(); ++i) out.push_back(a->Slice(cuts[i], cuts[i + 1] - cuts[i]));
+  return std::make_shared<ChunkedArray>(out, a->type());
+}
+// all chunks as one host array
+std::shared_ptr<Array> Flatten(const ChunkedArray& c, bool on_device) {
+  ArrayVector host;
+  for (const auto& k : c.chunks()) host.push_back(on_device ? MakeArray(ToHost(*k->data())) : k);
+  if (host.empty()) return GET(MakeArrayOfNull(c.type(), 0));
+  return GET(Concatenate(host));
+}
+
 // ---- builders
 template <typename BuilderT, typename V>
 std::shared_ptr<Array> Make(const std::vector<V>& values, const std::vector<bool>& valid = {}) {
@@ -315,6 +336,96 @@ int main() {
     auto st_gpu = cp::CallFunction("take", {DeviceDatum(small), DeviceDatum(bad)}, &gpu_ctx).status();
     CHECK_TRUE(st_cpu.IsIndexError() && st_gpu.IsIndexError(), "take out of bounds -> IndexError");
     CHECK_TRUE(st_gpu.message().find("Index 200 out of bounds") != std::string::npos, "take IndexError message names the index");
+  }
+
+  // ---------------- chunked / table forms of Filter and Take (vector_selection.cc:1776-1866, 1914-2017) ------
+  {
+    std::mt19937_64 rng(99);
+    const int64_t n = 50000;
+    auto a = MakeRandom<Int64Builder, int64_t>(n, rng, 0.1, -1000, 1000, false);
+    auto b = MakeRandom<DoubleBuilder, double>(n, rng, 0.0, -1.0, 1.0, true);
+    auto c = MakeRandom<BooleanBuilder, int>(n, rng, 0.2, 0, 2, false);
+    auto mask = MakeRandom<BooleanBuilder, int>(n, rng, 0.05, 0, 2, false);
+    const std::vector<int64_t> cuts_a = {0, 0, 1, 4097, 20000, 20000, n}, cuts_b = {0, 33, 30001, n}, cuts_m = {0, 777, 40000, 40000, n};
+    auto ca = Chunked(a, cuts_a), cb = Chunked(b, cuts_b), cc = Chunked(c, cuts_a), cm = Chunked(mask, cuts_m);
+    auto da = DeviceChunked(*ca), db = DeviceChunked(*cb), dc = DeviceChunked(*cc), dm = DeviceChunked(*cm);
+    for (auto ns : {cp::FilterOptions::DROP, cp::FilterOptions::EMIT_NULL}) {
+      cp::FilterOptions opts(ns);
+      const std::string tag = ns ? " EMIT_NULL" : " DROP";
+      // ChunkedArray x ChunkedArray with different chunk layouts, ChunkedArray x Array, Array x ChunkedArray
+      auto want = GET(cp::CallFunction("filter", {Datum(ca), Datum(cm)}, &opts, &cpu_ctx)).chunked_array();
+      auto got = GET(cp::CallFunction("filter", {Datum(da), Datum(dm)}, &opts, &gpu_ctx)).chunked_array();
+      ExpectEqual(Flatten(*got, true), Flatten(*want, false), "filter(ChunkedArray, ChunkedArray), layouts differ" + tag);
+      CHECK_TRUE(got->null_count() == want->null_count(), "filter(ChunkedArray, ChunkedArray) null_count" + tag);
+      got = GET(cp::CallFunction("filter", {Datum(dc), DeviceDatum(mask)}, &opts, &gpu_ctx)).chunked_array();
+      want = GET(cp::CallFunction("filter", {Datum(cc), Datum(mask)}, &opts, &cpu_ctx)).chunked_array();
+      ExpectEqual(Flatten(*got, true), Flatten(*want, false), "filter(ChunkedArray bool, Array)" + tag);
+      got = GET(cp::CallFunction("filter", {DeviceDatum(b), Datum(dm)}, &opts, &gpu_ctx)).chunked_array();
+      want = GET(cp::CallFunction("filter", {Datum(b), Datum(cm)}, &opts, &cpu_ctx)).chunked_array();
+      ExpectEqual(Flatten(*got, true), Flatten(*want, false), "filter(Array, ChunkedArray)" + tag);
+      // Table x ChunkedArray and Table x Array: one plan per mask chunk shared by the three columns
+      auto sch = schema({field("a", a->type()), field("b", b->type()), field("c", c->type())});
+      auto htable = Table::Make(sch, {ca, cb, cc});
+      auto dtable = Table::Make(sch, {da, db, dc});
+      for (int form = 0; form < 2; ++form) {
+        auto wt = GET(cp::CallFunction("filter", {Datum(htable), form ? Datum(mask) : Datum(cm)}, &opts, &cpu_ctx)).table();
+        auto gt = GET(cp::CallFunction("filter", {Datum(dtable), form ? DeviceDatum(mask) : Datum(dm)}, &opts, &gpu_ctx)).table();
+        CHECK_TRUE(gt->num_rows() == wt->num_rows() && gt->schema()->Equals(*wt->schema()), "filter(Table) rows and schema" + tag);
+        for (int k = 0; k < 3; ++k)
+          ExpectEqual(Flatten(*gt->column(k), true), Flatten(*wt->column(k), false),
+                      std::string("filter(Table, ") + (form ? "Array" : "ChunkedArray") + ") column " + std::to_string(k) + tag);
+      }
+    }
+    auto short_mask = MakeRandom<BooleanBuilder, int>(n - 1, rng, 0.0, 0, 2, false);
+    auto sch = schema({field("a", a->type())});
+    auto st = cp::CallFunction("filter", {Datum(Table::Make(sch, {da})), DeviceDatum(short_mask)}, &gpu_ctx).status();
+    CHECK_TRUE(st.IsInvalid() && st.message().find("Filter inputs must all be the same length") != std::string::npos,
+               "filter(Table) length mismatch -> Invalid");
+
+    // Take: every route of TakeMetaFunction
+    auto idx = MakeRandom<Int32Builder, int32_t>(70000, rng, 0.1, 0, int32_t(n), false);
+    auto cidx = Chunked(idx, {0, 1, 1, 30000, 70000});
+    auto didx = DeviceChunked(*cidx);
+    {
+      auto want = GET(cp::CallFunction("take", {Datum(ca), Datum(idx)}, &cpu_ctx)).chunked_array();
+      auto got = GET(cp::CallFunction("take", {Datum(da), DeviceDatum(idx)}, &gpu_ctx)).chunked_array();
+      CHECK_TRUE(got->num_chunks() == want->num_chunks(), "take(ChunkedArray, Array) -> one chunk");
+      ExpectEqual(Flatten(*got, true), Flatten(*want, false), "take(ChunkedArray, Array): gathered from the chunks where they lie");
+      CHECK_TRUE(got->null_count() == want->null_count(), "take(ChunkedArray, Array) null_count");
+      want = GET(cp::CallFunction("take", {Datum(cc), Datum(cidx)}, &cpu_ctx)).chunked_array();
+      got = GET(cp::CallFunction("take", {Datum(dc), Datum(didx)}, &gpu_ctx)).chunked_array();
+      CHECK_TRUE(got->num_chunks() == want->num_chunks(), "take(ChunkedArray, ChunkedArray) -> one chunk per index chunk");
+      ExpectEqual(Flatten(*got, true), Flatten(*want, false), "take(ChunkedArray bool, ChunkedArray)");
+      want = GET(cp::CallFunction("take", {Datum(b), Datum(cidx)}, &cpu_ctx)).chunked_array();
+      got = GET(cp::CallFunction("take", {DeviceDatum(b), Datum(didx)}, &gpu_ctx)).chunked_array();
+      CHECK_TRUE(got->num_chunks() == want->num_chunks(), "take(Array, ChunkedArray) chunk count");
+      ExpectEqual(Flatten(*got, true), Flatten(*want, false), "take(Array, ChunkedArray)");
+    }
+    {
+      auto sch2 = schema({field("a", a->type()), field("c", c->type())});
+      auto hb = RecordBatch::Make(sch2, n, {a, c});
+      auto dbt = RecordBatch::Make(sch2, n, {ToDevice(*a->data()), ToDevice(*c->data())});
+      auto want = GET(cp::CallFunction("take", {Datum(hb), Datum(idx)}, &cpu_ctx)).record_batch();
+      auto got = GET(cp::CallFunction("take", {Datum(dbt), DeviceDatum(idx)}, &gpu_ctx)).record_batch();
+      CHECK_TRUE(got->num_rows() == want->num_rows(), "take(RecordBatch, Array) rows");
+      for (int k = 0; k < 2; ++k) ExpectEqual(MakeArray(ToHost(*got->column_data(k))), want->column(k), "take(RecordBatch, Array) column " + std::to_string(k));
+      auto sch3 = schema({field("a", a->type()), field("b", b->type()), field("c", c->type())});
+      auto htable = Table::Make(sch3, {ca, cb, cc});
+      auto dtable = Table::Make(sch3, {da, db, dc});
+      for (int form = 0; form < 2; ++form) {
+        auto wt = GET(cp::CallFunction("take", {Datum(htable), form ? Datum(cidx) : Datum(idx)}, &cpu_ctx)).table();
+        auto gt = GET(cp::CallFunction("take", {Datum(dtable), form ? Datum(didx) : DeviceDatum(idx)}, &gpu_ctx)).table();
+        CHECK_TRUE(gt->num_rows() == wt->num_rows(), "take(Table) rows");
+        for (int k = 0; k < 3; ++k)
+          ExpectEqual(Flatten(*gt->column(k), true), Flatten(*wt->column(k), false),
+                      std::string("take(Table, ") + (form ? "ChunkedArray" : "Array") + ") column " + std::to_string(k));
+      }
+      // the bound is the table's row count
+      auto bad = Make<Int64Builder, int64_t>({0, n, 1});
+      auto st_cpu = cp::CallFunction("take", {Datum(htable), Datum(bad)}, &cpu_ctx).status();
+      auto st_gpu = cp::CallFunction("take", {Datum(dtable), DeviceDatum(bad)}, &gpu_ctx).status();
+      CHECK_TRUE(st_cpu.IsIndexError() && st_gpu.IsIndexError(), "take(Table) out of bounds -> IndexError");
+    }
   }
 
   // ---------------- GroupBy ----------------

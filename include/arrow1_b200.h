@@ -235,6 +235,13 @@ B200_API int b200_sort_pairs32(b200_ctx* ctx, const uint64_t* keys, const uint32
  *   out_null_count (host, nullable): exact null count of the result (synchronises). */
 B200_API int b200_take(b200_ctx* ctx, const b200_col* values, const b200_col* indices, int boundscheck,
                        void* out_data, void* out_validity, int64_t* out_null_count /* host, nullable */);
+/* ChunkedArray values (TakeCA / TakeCC / TakeTA / TakeTC, vector_selection.cc:1921-2017): indices address the
+ * LOGICAL CONCATENATION of the chunks.  Upstream concatenates the chunks on the host and calls array_take; here
+ * each index is mapped to (chunk, row) by a search over the chunk boundaries and gathered from where the chunk
+ * lies — no concatenated copy of the column is made.  All chunks share one type; everything else as b200_take. */
+B200_API int b200_take_chunked(b200_ctx* ctx, const b200_col* chunks, int n_chunks, const b200_col* indices,
+                               int boundscheck, void* out_data, void* out_validity,
+                               int64_t* out_null_count /* host, nullable */);
 
 /* ---- Range partition fused with the exchange (multi-GPU sample sort over NVLink peer memory) ----
  * The partition's scatter kernel stores every destination's (key, row) run straight into THAT rank's receive

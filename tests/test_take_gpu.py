@@ -105,3 +105,85 @@ def test_take_applies_sort_indices(ctx):
     assert got.null_count == want.null_count == col.length - int(col.valid().sum())
     np.testing.assert_array_equal(got.valid(), want.valid())
     assert got.data[: col.length * 8].tobytes() == want.data[: col.length * 8].tobytes()
+
+
+def _chunked(rng, whole: Column, cuts, offsets=True):
+    """Slices of a host column as separate Columns (their own buffers, odd offsets, some without a validity)."""
+    vals, valid = whole.values(), whole.valid()
+    out = []
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        off = int(rng.integers(0, 13)) if offsets else 0
+        v = np.concatenate([np.ones(off, dtype=vals.dtype), vals[a:b]])
+        m = np.concatenate([np.ones(off, dtype=np.bool_), valid[a:b]])
+        out.append(Column.from_numpy(v, None if m[off:].all() and (a + b) % 2 else m, offset=off))
+    return out
+
+
+@pytest.mark.parametrize("t", [cols.INT8, cols.UINT16, cols.FLOAT, cols.INT64, cols.DOUBLE, cols.BOOL])
+def test_take_chunked_values_equal_take_of_the_concatenation(ctx, t):
+    """b200_take_chunked == TakeCA (vector_selection.cc:1921-1944): Concatenate(chunks) then array_take — the
+    oracle runs on the whole column, the device gathers from the chunks where they lie.  Empty chunks (leading,
+    middle, trailing), a chunk without validity, odd offsets, null indices."""
+    rng = np.random.default_rng(4000 + t)
+    for nv, cuts in ((10, [0, 0, 3, 3, 10, 10]), (5000, [0, 1, 2, 4097, 4097, 5000]), (70_000, None)):
+        if cuts is None:
+            cuts = [0] + sorted(rng.integers(0, nv, size=37).tolist()) + [nv]
+        if t == cols.BOOL:
+            whole = Column.from_numpy(rng.random(nv) < 0.5, rng.random(nv) >= 0.2)
+        else:
+            whole = rand_column(rng, t, nv, 0.2, special=True)
+        chunks = [c.to_device() for c in _chunked(rng, whole, cuts)]
+        ni = 3 * nv + 5
+        indices = Column.from_numpy(rng.integers(0, nv, size=ni).astype(np.int64), rng.random(ni) >= 0.1)
+        want = oracle.take(whole, indices, True, kind=ORACLE)
+        got = capi.take(ctx, chunks, indices.to_device(), True).to_host()
+        assert got.length == want.length and got.null_count == want.null_count
+        np.testing.assert_array_equal(got.valid(), want.valid())
+        np.testing.assert_array_equal(got.values(), want.values())   # zeros under nulls on both sides
+        # a single "chunk" and the plain call agree
+        one = capi.take(ctx, [whole.to_device()], indices.to_device(), True).to_host()
+        np.testing.assert_array_equal(one.values(), want.values())
+        np.testing.assert_array_equal(one.valid(), want.valid())
+
+
+def test_take_chunked_many_chunks_and_bounds(ctx):
+    rng = np.random.default_rng(77)
+    nv = 200_000
+    whole = rand_column(rng, cols.INT32, nv, 0.05)
+    cuts = [0] + sorted(rng.integers(0, nv, size=2999).tolist()) + [nv]      # 3000 chunks: boundaries in global memory
+    chunks = [c.to_device() for c in _chunked(rng, whole, cuts, offsets=False)]
+    ix = rng.integers(0, nv, size=300_000).astype(np.uint32)
+    want = oracle.take(whole, Column.from_numpy(ix), True, kind=ORACLE)
+    got = capi.take(ctx, chunks, Column.from_numpy(ix).to_device(), True).to_host()
+    np.testing.assert_array_equal(got.values(), want.values())
+    np.testing.assert_array_equal(got.valid(), want.valid())
+    assert got.null_count == want.null_count
+    # the bound is the TOTAL length
+    bad = Column.from_numpy(np.array([0, nv - 1, nv, 1], dtype=np.int64)).to_device()
+    with pytest.raises(B200Error) as e:
+        capi.take(ctx, chunks, bad, True)
+    assert e.value.code == 7 and "Index %d out of bounds" % nv in str(e.value)
+    ok = capi.take(ctx, chunks, bad, False).to_host()     # NoBoundsCheck: the row comes out null
+    np.testing.assert_array_equal(ok.valid()[[0, 1, 3]], whole.valid()[[0, nv - 1, 1]])
+    assert not ok.valid()[2]
+    # all chunks empty: every index is out of bounds
+    empty = [Column.from_numpy(np.zeros(0, dtype=np.int32)).to_device() for _ in range(3)]
+    with pytest.raises(B200Error):
+        capi.take(ctx, empty, Column.from_numpy(np.array([0], dtype=np.int8)).to_device(), True)
+    # chunks of different types
+    with pytest.raises(B200Error) as e:
+        capi.take(ctx, [chunks[0], Column.from_numpy(np.zeros(4, dtype=np.int64)).to_device()], bad, False)
+    assert e.value.code == 3
+
+
+def test_compute_take_accepts_host_chunks(ctx):
+    from arrow1_b200 import compute
+    rng = np.random.default_rng(5)
+    whole = rand_column(rng, cols.DOUBLE, 30_000, 0.1, special=True)
+    chunks = _chunked(rng, whole, [0, 10_000, 10_001, 30_000])
+    indices = Column.from_numpy(rng.integers(0, 30_000, size=50_000).astype(np.int32))
+    want = oracle.take(whole, indices, True, kind=ORACLE)
+    got = compute.Take(chunks, indices, ctx=ctx)
+    assert not got.on_device and got.null_count == want.null_count
+    np.testing.assert_array_equal(got.valid(), want.valid())
+    assert got.values().tobytes() == want.values().tobytes()
