@@ -302,6 +302,20 @@ def sort_indices_chunked(ctx: Context, chunks: Sequence[Column], order: int = 0)
     return out[:total]
 
 
+def sort_indices_multi(ctx: Context, keys: Sequence[Column], orders: Sequence[int]) -> torch.Tensor:
+    """== compute::SortIndices(RecordBatch | Table, SortOptions{sort_keys}): keys[0] most significant; every key
+    puts NaNs then nulls after its values; stable.  int64-typed tensor of uint64 row numbers."""
+    n = keys[0].length if keys else 0
+    out = torch.empty(max(n, 1), dtype=torch.int64, device="cuda:%d" % ctx.device)
+    nb = C.c_size_t(0)
+    ctx.check(lib().b200_sort_indices_multi_scratch_bytes(C.c_int64(n), C.byref(nb)))
+    scratch = ctx.empty(nb.value)
+    ords = (C.c_int * max(len(keys), 1))(*[int(o) for o in orders])
+    ctx.check(lib().b200_sort_indices_multi(ctx._h, col_array(keys) if keys else None, ords, C.c_int(len(keys)),
+                                            C.c_void_p(out.data_ptr()), C.c_void_p(scratch.data_ptr()), C.c_size_t(nb.value)))
+    return out[:n]
+
+
 def sort_range_partition(ctx: Context, values: Column, order: int, index_base: int, splitters: Sequence[int], n_parts: int):
     """b200_sort_range_partition -> (keys, rows, counts): the (radix key, global row | class << 62) pairs of
     the column grouped by destination (stable), int64-typed tensors; `splitters` are unsigned radix keys."""

@@ -131,19 +131,36 @@ def Filter(values: Column, mask: Column, null_selection: int = DROP, ctx: Option
     return Column(col.type, data, validity, col.length, 0, col.null_count)
 
 
-def SortIndices(values: Column, order: int = ASCENDING, ctx: Optional[capi.Context] = None, _wait: bool = True):
-    """uint64 indices: numpy array for host input, int64-typed torch tensor for device input."""
+def SortIndices(values, order=ASCENDING, ctx: Optional[capi.Context] = None, _wait: bool = True):
+    """== compute::SortIndices.  `values` is a Column (order: ASCENDING / DESCENDING), or a sequence of Columns
+    with a sequence of orders — the sort keys of SortIndices(RecordBatch | Table, SortOptions), most significant
+    first (vector_sort.cc:1632-1711).  uint64 indices: numpy array for host input, int64-typed torch tensor for
+    device input."""
     ctx = ctx or default_context()
-    host = _from_host(values)
-    dv, b0 = _h2d(values, ctx)
-    out = capi.sort_indices(ctx, dv, order)
+    if isinstance(values, Column):
+        host = _from_host(values)
+        dv, b0 = _h2d(values, ctx)
+        out = capi.sort_indices(ctx, dv, order)
+        n = values.length
+    else:
+        keys = list(values)
+        if len(keys) == 0:
+            raise B200Error(4, "Must specify one or more sort keys")
+        orders = [order] * len(keys) if isinstance(order, int) else list(order)
+        if len(orders) != len(keys):
+            raise B200Error(4, "SortIndices: one order per sort key")
+        host = _from_host(keys[0])
+        staged = [_h2d(k, ctx) for k in keys]
+        b0 = sum(b for _, b in staged)
+        out = capi.sort_indices_multi(ctx, [c for c, _ in staged], orders)
+        n = keys[0].length
     Transfer.h2d, Transfer.d2h = b0, 0
     if not host:
         return out
-    h = _d2h(out, values.length * 8)
+    h = _d2h(out, n * 8)
     if _wait:
         ctx.stream.synchronize()
-    Transfer.d2h = values.length * 8
+    Transfer.d2h = n * 8
     return h.view(np.uint64)
 
 

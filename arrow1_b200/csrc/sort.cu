@@ -29,6 +29,7 @@
 
 #include <algorithm>
 
+#include <vector>
 #include "common.cuh"
 
 namespace {
@@ -801,6 +802,28 @@ __global__ void chunk_strip_kernel(uint64_t* rows, int64_t n) {
   if (i < n) rows[i] &= (uint64_t(1) << 62) - 1;
 }
 
+// ---- several sort keys (SortIndices on a RecordBatch / Table): LSD over the keys, least significant first.
+// Each key is one stable sort of (value key, row | class << 30) pairs: the rows arrive in the order the less
+// significant keys left them (perm; nullptr = identity), nulls and NaNs share the all-ones value key so the
+// stable passes keep that order, and one more stable pass on the 2-bit class moves NaNs, then nulls, behind the
+// values (MultipleKeyComparator::CompareType, vector_sort.cc:1098-1170).
+__global__ void mk_keys_kernel(SortParams p, const uint64_t* perm, uint64_t* keys, uint32_t* pay) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < p.n) {
+    const int64_t row = perm ? int64_t(perm[i]) : i;
+    uint32_t cls;
+    keys[i] = source_key(p, row, &cls);
+    pay[i] = uint32_t(row) | (cls << 30);
+  }
+}
+__global__ void mk_class_kernel(const uint64_t* rows, int64_t n, uint64_t* ckeys, uint32_t* pay) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) {
+    ckeys[i] = rows[i] >> 30;
+    pay[i] = uint32_t(rows[i]) & 0x3fffffffu;
+  }
+}
+
 struct Layout {
   size_t hist, info, counters, err, state, zero_bytes, keys0, keys1, pays0, pays1, total;
 };
@@ -977,6 +1000,53 @@ int b200_sort_indices_chunked(b200_ctx* ctx, const b200_col* chunks, int n_chunk
   B200_RETURN_NOT_OK(b200_sort_pairs(ctx, keys, srows, total, nullptr, out_indices, pair_scratch, pair_bytes));
   chunk_strip_kernel<<<grid, 256, 0, ctx->stream>>>(out_indices, total);
   B200_LAUNCHED(ctx);
+  return B200_OK;
+}
+
+int b200_sort_indices_multi_scratch_bytes(int64_t length, size_t* out_bytes) {
+  if (!out_bytes || length < 0) return B200_INVALID;
+  // value keys (8 B) and payloads (4 B) of the key being sorted + the pair sort's own scratch
+  *out_bytes = b200_align_up(size_t(length) * 8, 256) + b200_align_up(size_t(length) * 4, 256) + layout_for(length).total + 1024;
+  return B200_OK;
+}
+
+int b200_sort_indices_multi(b200_ctx* ctx, const b200_col* keys, const int* orders, int n_keys, uint64_t* out_indices,
+                            void* scratch, size_t scratch_bytes) {
+  if (!ctx) return B200_INVALID;
+  if (n_keys < 1) return b200_fail(ctx, B200_INVALID, "Must specify one or more sort keys");   // vector_sort.cc:1636
+  if (!keys || !orders) return b200_fail(ctx, B200_INVALID, "sort_indices_multi: null argument");
+  if (n_keys == 1) return b200_sort_indices(ctx, &keys[0], orders[0], 0, out_indices, scratch, scratch_bytes);
+  const int64_t n = keys[0].length;
+  std::vector<SortParams> src(n_keys);
+  for (int k = 0; k < n_keys; ++k) {
+    memset(&src[k], 0, sizeof(SortParams));
+    B200_RETURN_NOT_OK(fill_column_source(ctx, &keys[k], orders[k], &src[k]));
+    if (keys[k].length != n) return b200_fail(ctx, B200_INVALID, "sort_indices_multi: sort keys of different lengths");
+  }
+  if (n == 0) return B200_OK;
+  if (n > kMaxRows)
+    return b200_fail(ctx, B200_NOT_IMPLEMENTED, "sort: %lld rows exceed the per-call limit of 2^30-1; shard the column", (long long)n);
+  size_t need = 0;
+  b200_sort_indices_multi_scratch_bytes(n, &need);
+  if (!out_indices || !scratch || scratch_bytes < need) return b200_fail(ctx, B200_INVALID, "sort_indices_multi: null output or scratch too small");
+  char* base = reinterpret_cast<char*>(b200_align_up(reinterpret_cast<uintptr_t>(scratch), 256));
+  uint64_t* vkeys = reinterpret_cast<uint64_t*>(base);
+  uint32_t* pay = reinterpret_cast<uint32_t*>(base + b200_align_up(size_t(n) * 8, 256));
+  char* pair_scratch = base + b200_align_up(size_t(n) * 8, 256) + b200_align_up(size_t(n) * 4, 256);
+  const size_t pair_bytes = scratch_bytes - size_t(pair_scratch - reinterpret_cast<char*>(scratch));
+  const unsigned grid = unsigned((n + 255) / 256);
+  // out_indices doubles as the permutation between keys: every kernel that reads it has finished (stream
+  // order) before the sort that rewrites it starts
+  for (int k = n_keys - 1; k >= 0; --k) {
+    mk_keys_kernel<<<grid, 256, 0, ctx->stream>>>(src[k], k == n_keys - 1 ? nullptr : out_indices, vkeys, pay);
+    B200_LAUNCHED(ctx);
+    B200_RETURN_NOT_OK(b200_sort_pairs32(ctx, vkeys, pay, n, nullptr, out_indices, pair_scratch, pair_bytes));
+    if (src[k].cls_digit >= 0) {   // the column can hold nulls or NaNs
+      mk_class_kernel<<<grid, 256, 0, ctx->stream>>>(out_indices, n, vkeys, pay);
+      B200_LAUNCHED(ctx);
+      B200_RETURN_NOT_OK(b200_sort_pairs32(ctx, vkeys, pay, n, nullptr, out_indices, pair_scratch, pair_bytes));
+    }
+  }
   return B200_OK;
 }
 

@@ -428,6 +428,49 @@ int main() {
     }
   }
 
+  // ---------------- SortIndices with several sort keys (vector_sort.cc:1632-1711) ----------------
+  {
+    // vector_sort_test.cc:783-842 golden cases: a ascending, b descending
+    {
+      auto a = Make<FloatBuilder, float>({0, 1, 3, 0, NAN, NAN, NAN, 1}, {false, true, true, false, true, true, true, true});
+      auto b = Make<DoubleBuilder, double>({5, 3, 0, 0, 0, NAN, 5, 5}, {true, true, false, false, false, true, true, true});
+      auto sch = schema({field("a", a->type()), field("b", b->type())});
+      auto dbatch = RecordBatch::Make(sch, 8, {ToDevice(*a->data()), ToDevice(*b->data())});
+      cp::SortOptions opts({cp::SortKey("a", cp::SortOrder::Ascending), cp::SortKey("b", cp::SortOrder::Descending)});
+      auto got = HostArray(GET(cp::CallFunction("sort_indices", {Datum(dbatch)}, &opts, &gpu_ctx)));
+      ExpectEqual(got, Make<UInt64Builder, uint64_t>({7, 1, 2, 6, 5, 4, 0, 3}), "sort_indices RecordBatch NaNAndNull golden");
+    }
+    std::mt19937_64 rng(4242);
+    const int64_t n = 60000;
+    auto k0 = MakeRandom<Int8Builder, int8_t>(n, rng, 0.1, 0, 4, false);
+    auto k1 = MakeRandom<DoubleBuilder, double>(n, rng, 0.1, 0.0, 3.0, false);   // few distinct values: floors of [0, 3)
+    auto k2 = MakeRandom<Int64Builder, int64_t>(n, rng, 0.0, -100000, 100000, false);
+    auto sch = schema({field("x", k0->type()), field("y", k1->type()), field("z", k2->type())});
+    auto hbatch = RecordBatch::Make(sch, n, {k0, k1, k2});
+    auto dbatch = RecordBatch::Make(sch, n, {ToDevice(*k0->data()), ToDevice(*k1->data()), ToDevice(*k2->data())});
+    for (int variant = 0; variant < 3; ++variant) {
+      std::vector<cp::SortKey> keys;
+      if (variant == 0) keys = {cp::SortKey("x", cp::SortOrder::Ascending), cp::SortKey("y", cp::SortOrder::Descending), cp::SortKey("z", cp::SortOrder::Ascending)};
+      if (variant == 1) keys = {cp::SortKey("y", cp::SortOrder::Ascending), cp::SortKey("x", cp::SortOrder::Descending)};
+      if (variant == 2) keys = {cp::SortKey("z", cp::SortOrder::Descending)};
+      cp::SortOptions opts(keys);
+      auto want = GET(cp::CallFunction("sort_indices", {Datum(hbatch)}, &opts, &cpu_ctx)).make_array();
+      auto got = HostArray(GET(cp::CallFunction("sort_indices", {Datum(dbatch)}, &opts, &gpu_ctx)));
+      ExpectEqual(got, want, "sort_indices RecordBatch, " + std::to_string(keys.size()) + " sort keys");
+      auto htable = GET(Table::FromRecordBatches({hbatch}));
+      auto dtable = GET(Table::FromRecordBatches({dbatch}));
+      auto want_t = GET(cp::CallFunction("sort_indices", {Datum(htable)}, &opts, &cpu_ctx)).make_array();
+      auto got_t = HostArray(GET(cp::CallFunction("sort_indices", {Datum(dtable)}, &opts, &gpu_ctx)));
+      ExpectEqual(got_t, want_t, "sort_indices Table, " + std::to_string(keys.size()) + " sort keys");
+    }
+    cp::SortOptions none;
+    auto st0 = cp::CallFunction("sort_indices", {Datum(dbatch)}, &none, &gpu_ctx).status();
+    CHECK_TRUE(st0.IsInvalid() && st0.message().find("Must specify one or more sort keys") != std::string::npos, "sort_indices RecordBatch without keys -> Invalid");
+    cp::SortOptions missing({cp::SortKey("x", cp::SortOrder::Ascending), cp::SortKey("nope", cp::SortOrder::Ascending)});
+    auto st1 = cp::CallFunction("sort_indices", {Datum(dbatch)}, &missing, &gpu_ctx).status();
+    CHECK_TRUE(st1.IsInvalid() && st1.message().find("Nonexistent sort key column: nope") != std::string::npos, "sort_indices nonexistent key -> Invalid");
+  }
+
   // ---------------- GroupBy ----------------
   {
     // hash_aggregate_test.cc:555-605 (CountAndSum shape): null key group sits at its first-occurrence position

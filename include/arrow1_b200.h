@@ -190,6 +190,16 @@ B200_API int b200_sort_indices(b200_ctx* ctx, const b200_col* values, int order,
 B200_API int b200_sort_indices_chunked_scratch_bytes(int64_t total_length, size_t* out_bytes);
 B200_API int b200_sort_indices_chunked(b200_ctx* ctx, const b200_col* chunks, int n_chunks, int order,
                                        uint64_t* out_indices, void* scratch, size_t scratch_bytes);
+/* Several sort keys: == SortIndices(RecordBatch | Table, SortOptions{sort_keys}) (SortIndicesMetaFunction,
+ * vector_sort.cc:1632-1711; RadixRecordBatchSorter :955-1048, MultipleKeyRecordBatchSorter :1184-1356,
+ * MultipleKeyComparator :1050-1181).  keys[0] is the most significant key; orders[k] as in b200_sort_indices.
+ * Rows are ordered by key 0, ties by key 1, ...; within every key values come first (by its order), then NaNs,
+ * then nulls; rows equal under all keys stay in row order (the reference's sorters are stable).  Done as an LSD
+ * over the keys — one stable radix sort per key, least significant first — instead of one comparison sort with a
+ * k-column comparator.  All keys have the same length (< 2^30 rows); n_keys == 1 is b200_sort_indices. */
+B200_API int b200_sort_indices_multi_scratch_bytes(int64_t length, size_t* out_bytes);
+B200_API int b200_sort_indices_multi(b200_ctx* ctx, const b200_col* keys, const int* orders, int n_keys,
+                                     uint64_t* out_indices, void* scratch, size_t scratch_bytes);
 /* Sample-sort building blocks for the multi-GPU path.  sort_keys writes the
  * order-preserving 64-bit radix key of every row (the same transform the local sort uses;
  * NaN -> 2^64-2, null -> 2^64-1) so that ranks can exchange (key, global row) pairs;

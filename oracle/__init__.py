@@ -168,6 +168,22 @@ def sort_indices(values: Column, order: int = 0, index_base: int = 0, kind: str 
     return out[: values.length]
 
 
+def sort_indices_multi(keys: Sequence[Column], orders: Sequence[int], kind: str = "port", as_table: bool = False,
+                       n_chunks: int = 1) -> np.ndarray:
+    """compute::SortIndices(RecordBatch | Table, SortOptions{sort_keys}); keys[0] is the most significant key.
+    kind="reference": as_table / n_chunks choose the Table form (MultipleKeyTableSorter) over a chunked table."""
+    n = keys[0].length if keys else 0
+    out = np.zeros(max(n, 1), dtype=np.uint64)
+    descs = (type(keys[0].desc()) * len(keys))(*[k.desc() for k in keys])
+    ords = (C.c_int * len(keys))(*[int(o) for o in orders])
+    if kind == "reference":
+        _check(kind, _fn(kind, "sort_indices_multi")(descs, ords, C.c_int(len(keys)), C.c_int(1 if as_table else 0),
+                                                     C.c_int(n_chunks), out.ctypes.data_as(C.c_void_p)))
+    else:
+        _check(kind, _fn(kind, "sort_indices_multi")(descs, ords, C.c_int(len(keys)), out.ctypes.data_as(C.c_void_p)))
+    return out[:n]
+
+
 class GroupByResult:
     """aggs: list (per requested aggregate) of list of (values, valid) numpy pairs; keys: list of
     (values, valid); ids: per-row group ids or None."""

@@ -129,6 +129,42 @@ int SortImpl(const b200_col* c, int order, uint64_t base, uint64_t* out) {
   return B200_OK;
 }
 
+// ---- several sort keys: MultipleKeyComparator (vector_sort.cc:1050-1181) under one std::stable_sort.
+// The reference's sorters (RadixRecordBatchSorter :955-1048, MultipleKeyRecordBatchSorter :1184-1356,
+// MultipleKeyTableSorter :1381-1560) partition nulls / NaNs of the first key first, but every step is a stable
+// sort or stable partition under this one ordering, so the result is the stable sort by the comparator.
+template <typename T>
+int CompareKey(const b200_col& c, int order, uint64_t l, uint64_t r) {
+  const bool lv = IsValid(c, int64_t(l)), rv = IsValid(c, int64_t(r));
+  if (!lv && !rv) return 0;          // :1108-1116 null handling
+  if (!lv) return 1;
+  if (!rv) return -1;
+  const T a = Value<T>(c, int64_t(l)), b = Value<T>(c, int64_t(r));
+  if (std::is_floating_point<T>::value) {   // :1146-1156 NaN handling
+    const bool an = a != a, bn = b != b;
+    if (an && bn) return 0;
+    if (an) return 1;
+    if (bn) return -1;
+  }
+  int cmp = a == b ? 0 : (a > b ? 1 : -1);
+  return order ? -cmp : cmp;
+}
+
+int CompareKeyDispatch(const b200_col& c, int order, uint64_t l, uint64_t r) {
+  switch (c.type) {
+    case B200_UINT8: return CompareKey<uint8_t>(c, order, l, r);
+    case B200_INT8: return CompareKey<int8_t>(c, order, l, r);
+    case B200_UINT16: return CompareKey<uint16_t>(c, order, l, r);
+    case B200_INT16: return CompareKey<int16_t>(c, order, l, r);
+    case B200_UINT32: return CompareKey<uint32_t>(c, order, l, r);
+    case B200_INT32: return CompareKey<int32_t>(c, order, l, r);
+    case B200_UINT64: return CompareKey<uint64_t>(c, order, l, r);
+    case B200_INT64: return CompareKey<int64_t>(c, order, l, r);
+    case B200_FLOAT: return CompareKey<float>(c, order, l, r);
+    default: return CompareKey<double>(c, order, l, r);
+  }
+}
+
 // ---- group-by ---------------------------------------------------------------------------
 struct AggState {
   b200_agg_spec spec;
@@ -283,6 +319,24 @@ B200_API int oracle_sort_indices(const b200_col* values, int order, uint64_t ind
     case B200_DOUBLE: return SortImpl<double>(values, order, index_base, out);
   }
   return B200_NOT_IMPLEMENTED;  // boolean has no array_sort_indices kernel (vector_sort.cc:577-606)
+}
+
+B200_API int oracle_sort_indices_multi(const b200_col* keys, const int* orders, int n_keys, uint64_t* out) {
+  if (n_keys < 1) return B200_INVALID;   // "Must specify one or more sort keys" (vector_sort.cc:1636)
+  const int64_t n = keys[0].length;
+  for (int k = 0; k < n_keys; ++k) {
+    if (BitsOf(keys[k].type) < 8) return B200_NOT_IMPLEMENTED;
+    if (keys[k].length != n) return B200_INVALID;
+  }
+  std::iota(out, out + n, uint64_t(0));
+  std::stable_sort(out, out + n, [&](uint64_t l, uint64_t r) {
+    for (int k = 0; k < n_keys; ++k) {
+      const int c = CompareKeyDispatch(keys[k], orders[k], l, r);
+      if (c != 0) return c < 0;
+    }
+    return false;
+  });
+  return B200_OK;
 }
 
 B200_API int oracle_groupby(int n_keys, const b200_col* keys, int n_aggs, const b200_agg_spec* aggs,

@@ -10,6 +10,7 @@
 // and copies the results into caller-owned buffers.  Column descriptors reuse the b200_col
 // layout of include/arrow1_b200.h with host pointers.  Used to (1) pin oracle/oracle.cc,
 // (2) act as parity checker in tests/, (3) be timed as bench.py's cpu_baseline ("reference").
+#include <algorithm>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -149,6 +150,44 @@ B200_API int ref_sort_indices(const b200_col* values, int order, uint64_t index_
   if (out) {
     for (int64_t i = 0; i < idx->length; ++i) out[i] = p[i] + index_base;
   }
+  return 0;
+}
+
+// compute::SortIndices(Datum(RecordBatch | Table), SortOptions{sort_keys}): keys[k] becomes column "k<k>".
+// as_table != 0 wraps the columns in a Table of `n_chunks` chunks (MultipleKeyTableSorter), else a RecordBatch
+// (RadixRecordBatchSorter up to 8 keys, MultipleKeyRecordBatchSorter beyond; vector_sort.cc:1632-1711).
+B200_API int ref_sort_indices_multi(const b200_col* keys, const int* orders, int n_keys, int as_table, int n_chunks,
+                                    uint64_t* out) {
+  compute::ExecContext ctx;
+  std::vector<std::shared_ptr<Field>> fields;
+  std::vector<std::shared_ptr<Array>> columns;
+  std::vector<compute::SortKey> sort_keys;
+  for (int k = 0; k < n_keys; ++k) {
+    const std::string name = "k" + std::to_string(k);
+    columns.push_back(MakeArray(Wrap(keys[k])));
+    fields.push_back(field(name, columns.back()->type()));
+    sort_keys.emplace_back(name, orders[k] ? compute::SortOrder::Descending : compute::SortOrder::Ascending);
+  }
+  compute::SortOptions options(sort_keys);
+  const int64_t n = n_keys > 0 ? keys[0].length : 0;
+  Datum input;
+  if (as_table) {
+    std::vector<std::shared_ptr<ChunkedArray>> chunked;
+    const int64_t step = std::max<int64_t>(1, (n + std::max(n_chunks, 1) - 1) / std::max(n_chunks, 1));
+    for (const auto& col : columns) {
+      ArrayVector pieces;
+      for (int64_t at = 0; at < n; at += step) pieces.push_back(col->Slice(at, std::min(step, n - at)));
+      chunked.push_back(std::make_shared<ChunkedArray>(pieces, col->type()));
+    }
+    input = Datum(Table::Make(schema(fields), chunked, n));
+  } else {
+    input = Datum(RecordBatch::Make(schema(fields), n, columns));
+  }
+  auto res = compute::SortIndices(input, options, &ctx);
+  if (!res.ok()) return Fail(res.status());
+  auto idx = res.ValueOrDie()->data();
+  const uint64_t* p = idx->GetValues<uint64_t>(1);
+  if (out) std::memcpy(out, p, size_t(idx->length) * 8);
   return 0;
 }
 

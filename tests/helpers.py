@@ -126,3 +126,39 @@ def assert_group_equal(a: GroupRes, b: GroupRes, aggs, rtol=1e-12, scales=None):
                 np.testing.assert_array_equal(xa[va].view(np.uint8), xb[vb].view(np.uint8), err_msg=spec.name())
     if a.ids is not None and b.ids is not None:
         np.testing.assert_array_equal(a.ids, b.ids)
+
+
+def MULTI_KEY_GOLDEN():
+    """vector_sort_test.cc:783-842 (TestRecordBatchSortIndices Null / NaN / NaNAndNull): a ascending, b descending."""
+    import numpy as np
+    from arrow1_b200 import columns as cols
+    nan = np.nan
+
+    def col(values, dtype):
+        valid = np.array([v is not None for v in values])
+        data = np.array([0 if v is None else v for v in values], dtype=dtype)
+        return cols.Column.from_numpy(data, valid if not valid.all() else None)
+    yield ([col([None, 1, 3, None, 2, 1], np.uint8), col([5, 3, None, None, 5, 5], np.uint32)], [0, 1], [5, 1, 4, 2, 0, 3])
+    yield ([col([3, 1, 3, 0, nan, nan, nan, 1], np.float32), col([5, nan, 4, 6, 5, nan, 5, 5], np.float64)], [0, 1],
+           [3, 7, 1, 0, 2, 4, 6, 5])
+    yield ([col([None, 1, 3, None, nan, nan, nan, 1], np.float32), col([5, 3, None, None, None, nan, 5, 5], np.float64)], [0, 1],
+           [7, 1, 2, 6, 5, 4, 0, 3])
+
+
+def multi_key_cases(rng, n):
+    import numpy as np
+    from arrow1_b200 import columns as cols
+    from gen import rand_column
+    """(keys, orders) lists: few distinct values per key so that ties reach the later keys; nulls, NaNs, -0.0."""
+    def small(t, k, nulls):
+        c = rand_column(rng, t, n, nulls, lo=0, hi=k) if t not in (cols.FLOAT, cols.DOUBLE) else None
+        if c is None:
+            v = rng.integers(-k, k, size=n).astype(np.float32 if t == cols.FLOAT else np.float64) / 2
+            v[rng.random(n) < 0.1] = np.nan
+            v[rng.random(n) < 0.05] = -0.0
+            c = cols.Column.from_numpy(v, (rng.random(n) >= nulls) if nulls else None)
+        return c
+    yield [small(cols.INT32, 5, 0.1), small(cols.DOUBLE, 4, 0.1)], [0, 1]
+    yield [small(cols.UINT8, 3, 0.0), small(cols.INT64, 3, 0.2), small(cols.FLOAT, 3, 0.0)], [1, 0, 0]
+    yield [small(cols.DOUBLE, 2, 0.3), small(cols.DOUBLE, 2, 0.3), small(cols.INT16, 2, 0.3), small(cols.UINT64, 50, 0.0)], [1, 1, 0, 1]
+    yield [small(cols.INT8, 4, 0.0), small(cols.UINT16, 4, 0.0)], [0, 0]

@@ -8,7 +8,7 @@ import oracle
 from arrow1_b200 import columns as cols
 from arrow1_b200.columns import AggSpec
 from gen import ALL_NUMERIC, rand_column, rand_mask
-from helpers import assert_filter_equal, assert_group_equal, run_filter, run_groupby, run_sort
+from helpers import multi_key_cases, assert_filter_equal, assert_group_equal, run_filter, run_groupby, run_sort
 
 needs_ref = pytest.mark.skipif(not oracle.have_reference(), reason="oracle/_ref not built")
 
@@ -121,3 +121,26 @@ def test_take_port_matches_reference(t):
             with pytest.raises(oracle.OracleError) as e:
                 oracle.take(values, Column.from_numpy(np.array(bad, dtype=np.int64)), True, kind=kind)
             assert e.value.code == 7
+
+
+@needs_ref
+def test_sort_multi_key_port_matches_reference_record_batch_and_table():
+    # vector_sort_test.cc TestTableSortIndices / TestRecordBatchSortIndices: nulls and NaNs last per key, stable
+    rng = np.random.default_rng(31)
+    for n in (0, 1, 7, 3000):
+        for keys, orders in multi_key_cases(rng, n):
+            port = oracle.sort_indices_multi(keys, orders)
+            np.testing.assert_array_equal(port, oracle.sort_indices_multi(keys, orders, kind="reference"))
+            np.testing.assert_array_equal(port, oracle.sort_indices_multi(keys, orders, kind="reference", as_table=True, n_chunks=3))
+    # nine keys: past kMaxRadixSortKeys the RecordBatch form switches to MultipleKeyRecordBatchSorter
+    keys = [rand_column(rng, cols.INT8, 2000, 0.1, lo=0, hi=2) for _ in range(9)]
+    orders = [i % 2 for i in range(9)]
+    np.testing.assert_array_equal(oracle.sort_indices_multi(keys, orders), oracle.sort_indices_multi(keys, orders, kind="reference"))
+    # one key == SortIndices of the column
+    np.testing.assert_array_equal(oracle.sort_indices_multi(keys[:1], [1]), oracle.sort_indices(keys[0], 1))
+
+
+def test_sort_multi_key_golden_vectors():
+    from helpers import MULTI_KEY_GOLDEN
+    for keys, orders, want in MULTI_KEY_GOLDEN():
+        np.testing.assert_array_equal(oracle.sort_indices_multi(keys, orders), np.array(want, dtype=np.uint64))

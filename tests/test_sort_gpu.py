@@ -3,7 +3,8 @@ import numpy as np
 import pytest
 
 import oracle
-from arrow1_b200 import columns as cols
+from arrow1_b200 import capi, columns as cols
+from arrow1_b200.capi import B200Error
 from arrow1_b200.columns import Column
 from conftest import rand_u64
 from gen import ALL_NUMERIC, rand_column
@@ -207,3 +208,52 @@ def test_range_partition_push_and_sort_pairs32_match_the_unfused_forms(ctx):
     finally:
         for b in kb + rb:
             b.close()
+
+
+def test_sort_indices_multi_key_golden_vectors(ctx):
+    from helpers import MULTI_KEY_GOLDEN
+    for keys, orders, want in MULTI_KEY_GOLDEN():
+        got = capi.sort_indices_multi(ctx, [k.to_device() for k in keys], orders).cpu().numpy().view(np.uint64)
+        np.testing.assert_array_equal(got, np.array(want, dtype=np.uint64))
+
+
+def test_sort_indices_multi_key_matches_oracle(ctx):
+    """b200_sort_indices_multi == SortIndices(RecordBatch, sort_keys) of the reference: LSD over the keys against
+    the reference's comparator sorts, every type, mixed orders, nulls / NaNs / -0.0 in every key, heavy ties."""
+    from helpers import multi_key_cases
+    rng = np.random.default_rng(8)
+    for n in (1, 100, 70_001):
+        for keys, orders in multi_key_cases(rng, n):
+            want = oracle.sort_indices_multi(keys, orders, kind=ORACLE)
+            got = capi.sort_indices_multi(ctx, [k.to_device() for k in keys], orders).cpu().numpy().view(np.uint64)
+            np.testing.assert_array_equal(got, want)
+    # every numeric type as the second key, offsets, wide value ranges
+    for t in ALL_NUMERIC:
+        first = rand_column(rng, cols.INT8, 50_000, 0.05, lo=0, hi=3)
+        second = rand_column(rng, t, 50_000, 0.1, offset=5, special=True)
+        for orders in ([0, 0], [1, 0], [0, 1]):
+            want = oracle.sort_indices_multi([first, second], orders, kind=ORACLE)
+            got = capi.sort_indices_multi(ctx, [first.to_device(), second.to_device()], orders).cpu().numpy().view(np.uint64)
+            np.testing.assert_array_equal(got, want)
+    # one key is the single-column sort; host columns go through compute.SortIndices
+    from arrow1_b200 import compute
+    one = rand_column(rng, cols.DOUBLE, 10_000, 0.1, special=True)
+    np.testing.assert_array_equal(capi.sort_indices_multi(ctx, [one.to_device()], [1]).cpu().numpy().view(np.uint64),
+                                  oracle.sort_indices(one, 1, kind=ORACLE))
+    keys, orders = next(multi_key_cases(rng, 5000))
+    np.testing.assert_array_equal(compute.SortIndices(keys, orders, ctx=ctx), oracle.sort_indices_multi(keys, orders, kind=ORACLE))
+
+
+def test_sort_indices_multi_key_errors(ctx):
+    a = Column.from_numpy(np.arange(10, dtype=np.int32)).to_device()
+    b = Column.from_numpy(np.arange(11, dtype=np.int32)).to_device()
+    with pytest.raises(B200Error) as e:
+        capi.sort_indices_multi(ctx, [a, b], [0, 0])
+    assert e.value.code == 4
+    with pytest.raises(B200Error) as e:
+        capi.sort_indices_multi(ctx, [], [])
+    assert e.value.code == 4 and "one or more sort keys" in str(e.value)
+    flag = Column.from_numpy(np.arange(10) % 2 == 0).to_device()
+    with pytest.raises(B200Error) as e:
+        capi.sort_indices_multi(ctx, [a, flag], [0, 0])
+    assert e.value.code == 10
