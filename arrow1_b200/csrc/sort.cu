@@ -1037,8 +1037,11 @@ int b200_sort_indices_multi(b200_ctx* ctx, const b200_col* keys, const int* orde
   const unsigned grid = unsigned((n + 255) / 256);
   // out_indices doubles as the permutation between keys: every kernel that reads it has finished (stream
   // order) before the sort that rewrites it starts
-  for (int k = n_keys - 1; k >= 0; --k) {
-    mk_keys_kernel<<<grid, 256, 0, ctx->stream>>>(src[k], k == n_keys - 1 ? nullptr : out_indices, vkeys, pay);
+  // the least significant key sees the rows in row order: that is the single-column sort as it stands (keys
+  // read straight from the column, NaN / null bins inside its class pass)
+  B200_RETURN_NOT_OK(b200_sort_indices(ctx, &keys[n_keys - 1], orders[n_keys - 1], 0, out_indices, pair_scratch, pair_bytes));
+  for (int k = n_keys - 2; k >= 0; --k) {
+    mk_keys_kernel<<<grid, 256, 0, ctx->stream>>>(src[k], out_indices, vkeys, pay);
     B200_LAUNCHED(ctx);
     B200_RETURN_NOT_OK(b200_sort_pairs32(ctx, vkeys, pay, n, nullptr, out_indices, pair_scratch, pair_bytes));
     if (src[k].cls_digit >= 0) {   // the column can hold nulls or NaNs

@@ -165,6 +165,44 @@ class SortWL(Workload):
         return oracle.sort_indices(host_cols[0], 0, 0, kind=kind)
 
 
+class SortMultiWL(Workload):
+    """SortIndices(RecordBatch, [key ascending, value descending]) — two sort keys."""
+    kernel = "sort_pass"
+    name = "sort_2keys"
+    dtype = "u64 radix keys (int32 and int64 columns)"
+
+    def __init__(self, rows):
+        super().__init__(rows)
+        self.description = ("SortIndices by (int32 key in [0, 1000) ascending, int64 value descending, 1%% nulls last), "
+                            "%d rows, stable" % rows)
+
+    def make(self, gen, start=0, n=None):
+        return (gen.groupby_c3(n or self.n, 1000, start)[0], gen.sort_c2(n or self.n, "int64", start))
+
+    def input_bytes(self):
+        return self.n * 12
+
+    def alg_bytes_per_launch(self, launches_per_step):
+        # value key: 8 live passes of (8 B key, 4 B row) pairs + 1 class pass; int32 key: 2 live passes
+        # (values < 1000); every pass reads and writes 12 B/row, the last of a sort writes 8 B rows
+        total = self.n * (11 * 24)
+        return total / max(launches_per_step, 1)
+
+    def prepare(self, ctx, cols_):
+        return {}
+
+    def step(self, ctx, cols_, bufs):
+        from arrow1_b200 import capi
+        return capi.sort_indices_multi(ctx, list(cols_), [0, 1])
+
+    def e2e_step(self, host_cols):
+        from arrow1_b200 import compute
+        return compute.SortIndices(list(host_cols), [compute.ASCENDING, compute.DESCENDING])
+
+    def cpu_step(self, oracle, kind, host_cols):
+        return oracle.sort_indices_multi(list(host_cols), [0, 1], kind=kind)
+
+
 class TakeWL(Workload):
     """the gather that follows SortIndices — Take(values, SortIndices(values)), i.e. the sorted
     column itself; the indices are a random permutation of the rows."""
@@ -374,6 +412,8 @@ def make_workload(name, rows=None):
         return SortWL(rows or 100_000_000, "float64")
     if name == "take_sorted":
         return TakeWL(rows or 100_000_000)
+    if name == "sort_2keys":
+        return SortMultiWL(rows or 100_000_000)
     if name == "filter":
         return FilterWL(rows or 100_000_000, "filter")
     if name == "filter_10m":
@@ -451,7 +491,7 @@ def host_threads():
 
 def cpu_sample_rows(wl, threads):
     per_thread = {"sort_i64": 2_000_000, "sort_f64": 2_000_000, "filter": 16_000_000, "filter_10m": 10_000_000,
-                  "groupby_c3": 8_000_000, "groupby_c4": 4_000_000, "take_sorted": 2_000_000, "q1": 4_000_000, "q1_selected": 4_000_000}[wl.name]
+                  "groupby_c3": 8_000_000, "groupby_c4": 4_000_000, "take_sorted": 2_000_000, "sort_2keys": 2_000_000, "q1": 4_000_000, "q1_selected": 4_000_000}[wl.name]
     return min(per_thread, wl.n)
 
 
@@ -704,7 +744,7 @@ def gpu_arm(args):
     if rank == 0 and world == 1 and not args.no_extras:
         del cols_, bufs
         torch.cuda.empty_cache()
-        for name in ("filter", "filter_10m", "sort_i64", "sort_f64", "take_sorted", "groupby_c3", "groupby_c4", "q1", "q1_selected"):
+        for name in ("filter", "filter_10m", "sort_i64", "sort_f64", "sort_2keys", "take_sorted", "groupby_c3", "groupby_c4", "q1", "q1_selected"):
             if name == wl.name:
                 continue
             try:
