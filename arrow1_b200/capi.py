@@ -302,15 +302,32 @@ def sort_indices_chunked(ctx: Context, chunks: Sequence[Column], order: int = 0)
     return out[:total]
 
 
-def sort_indices_multi(ctx: Context, keys: Sequence[Column], orders: Sequence[int]) -> torch.Tensor:
+def sort_indices_multi(ctx: Context, keys: Sequence, orders: Sequence[int]) -> torch.Tensor:
     """== compute::SortIndices(RecordBatch | Table, SortOptions{sort_keys}): keys[0] most significant; every key
-    puts NaNs then nulls after its values; stable.  int64-typed tensor of uint64 row numbers."""
-    n = keys[0].length if keys else 0
+    puts NaNs then nulls after its values; stable.  A key is a Column, or — every key alike — a sequence of
+    Columns (the chunks of a Table column, chunked the same way under every key; indices address the
+    concatenation).  int64-typed tensor of uint64 row numbers."""
+    chunked = len(keys) > 0 and not isinstance(keys[0], Column)
+    ords = (C.c_int * max(len(keys), 1))(*[int(o) for o in orders])
+    if chunked:
+        n_chunks = len(keys[0])
+        if any(len(k) != n_chunks for k in keys):
+            raise B200Error(4, "sort_indices_multi: sort keys chunked differently")
+        flat = [c for k in keys for c in k]
+        n = sum(c.length for c in keys[0])
+    else:
+        n = keys[0].length if keys else 0
     out = torch.empty(max(n, 1), dtype=torch.int64, device="cuda:%d" % ctx.device)
     nb = C.c_size_t(0)
+    if chunked:
+        ctx.check(lib().b200_sort_indices_multi_chunked_scratch_bytes(C.c_int64(n), C.byref(nb)))
+        scratch = ctx.empty(nb.value)
+        ctx.check(lib().b200_sort_indices_multi_chunked(ctx._h, col_array(flat) if flat else None, ords, C.c_int(len(keys)),
+                                                        C.c_int(n_chunks), C.c_void_p(out.data_ptr()),
+                                                        C.c_void_p(scratch.data_ptr()), C.c_size_t(nb.value)))
+        return out[:n]
     ctx.check(lib().b200_sort_indices_multi_scratch_bytes(C.c_int64(n), C.byref(nb)))
     scratch = ctx.empty(nb.value)
-    ords = (C.c_int * max(len(keys), 1))(*[int(o) for o in orders])
     ctx.check(lib().b200_sort_indices_multi(ctx._h, col_array(keys) if keys else None, ords, C.c_int(len(keys)),
                                             C.c_void_p(out.data_ptr()), C.c_void_p(scratch.data_ptr()), C.c_size_t(nb.value)))
     return out[:n]

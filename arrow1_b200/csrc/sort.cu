@@ -824,6 +824,26 @@ __global__ void mk_class_kernel(const uint64_t* rows, int64_t n, uint64_t* ckeys
   }
 }
 
+// chunked key columns: the key's (value key, class) of every row in row order first, then gathered through
+// the permutation like mk_keys_kernel does from a single column
+__global__ void mk_flat_kernel(SortParams p, int64_t off, uint64_t* flat_keys, uint8_t* flat_cls) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < p.n) {
+    uint32_t cls;
+    flat_keys[off + i] = source_key(p, i, &cls);
+    flat_cls[off + i] = uint8_t(cls);
+  }
+}
+__global__ void mk_gather_flat_kernel(const uint64_t* flat_keys, const uint8_t* flat_cls, const uint64_t* perm, int64_t n,
+                                      uint64_t* keys, uint32_t* pay) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const uint64_t row = perm[i];
+    keys[i] = flat_keys[row];
+    pay[i] = uint32_t(row) | (uint32_t(flat_cls[row]) << 30);
+  }
+}
+
 struct Layout {
   size_t hist, info, counters, err, state, zero_bytes, keys0, keys1, pays0, pays1, total;
 };
@@ -1045,6 +1065,78 @@ int b200_sort_indices_multi(b200_ctx* ctx, const b200_col* keys, const int* orde
     B200_LAUNCHED(ctx);
     B200_RETURN_NOT_OK(b200_sort_pairs32(ctx, vkeys, pay, n, nullptr, out_indices, pair_scratch, pair_bytes));
     if (src[k].cls_digit >= 0) {   // the column can hold nulls or NaNs
+      mk_class_kernel<<<grid, 256, 0, ctx->stream>>>(out_indices, n, vkeys, pay);
+      B200_LAUNCHED(ctx);
+      B200_RETURN_NOT_OK(b200_sort_pairs32(ctx, vkeys, pay, n, nullptr, out_indices, pair_scratch, pair_bytes));
+    }
+  }
+  return B200_OK;
+}
+
+int b200_sort_indices_multi_chunked_scratch_bytes(int64_t total_length, size_t* out_bytes) {
+  if (!out_bytes || total_length < 0) return B200_INVALID;
+  size_t chunked = 0, multi = 0;
+  b200_sort_indices_chunked_scratch_bytes(total_length, &chunked);
+  b200_sort_indices_multi_scratch_bytes(total_length, &multi);
+  // + the flat value keys (8 B) and classes (1 B) of the key being sorted
+  multi += b200_align_up(size_t(total_length) * 8, 256) + b200_align_up(size_t(total_length), 256);
+  *out_bytes = std::max(chunked, multi);
+  return B200_OK;
+}
+
+int b200_sort_indices_multi_chunked(b200_ctx* ctx, const b200_col* keys, const int* orders, int n_keys, int n_chunks,
+                                    uint64_t* out_indices, void* scratch, size_t scratch_bytes) {
+  if (!ctx) return B200_INVALID;
+  if (n_keys < 1) return b200_fail(ctx, B200_INVALID, "Must specify one or more sort keys");
+  if (n_chunks < 0 || !orders || (n_chunks > 0 && !keys)) return b200_fail(ctx, B200_INVALID, "sort_indices_multi_chunked: bad argument");
+  if (n_chunks == 0) return B200_OK;
+  if (n_chunks == 1) return b200_sort_indices_multi(ctx, keys, orders, n_keys, out_indices, scratch, scratch_bytes);
+  if (n_keys == 1) return b200_sort_indices_chunked(ctx, keys, n_chunks, orders[0], out_indices, scratch, scratch_bytes);
+  int64_t n = 0;
+  for (int c = 0; c < n_chunks; ++c) n += keys[c].length;
+  std::vector<SortParams> src(size_t(n_keys) * n_chunks);
+  for (int k = 0; k < n_keys; ++k) {
+    for (int c = 0; c < n_chunks; ++c) {
+      const b200_col& col = keys[k * n_chunks + c];
+      SortParams& p = src[size_t(k) * n_chunks + c];
+      memset(&p, 0, sizeof(SortParams));
+      if (col.type != keys[k * n_chunks].type) return b200_fail(ctx, B200_TYPE_ERROR, "sort_indices_multi_chunked: chunk types differ");
+      B200_RETURN_NOT_OK(fill_column_source(ctx, &col, orders[k], &p));
+      if (col.length != keys[c].length) return b200_fail(ctx, B200_INVALID, "sort_indices_multi_chunked: sort keys chunked differently");
+    }
+  }
+  if (n == 0) return B200_OK;
+  if (n > kMaxRows)
+    return b200_fail(ctx, B200_NOT_IMPLEMENTED, "sort: %lld rows exceed the per-call limit of 2^30-1; shard the column", (long long)n);
+  size_t need = 0;
+  b200_sort_indices_multi_chunked_scratch_bytes(n, &need);
+  if (!out_indices || !scratch || scratch_bytes < need) return b200_fail(ctx, B200_INVALID, "sort_indices_multi_chunked: null output or scratch too small");
+  // least significant key: the chunked single-column sort (global indices over the concatenation)
+  B200_RETURN_NOT_OK(b200_sort_indices_chunked(ctx, &keys[(n_keys - 1) * n_chunks], n_chunks, orders[n_keys - 1], out_indices, scratch, scratch_bytes));
+  char* base = reinterpret_cast<char*>(b200_align_up(reinterpret_cast<uintptr_t>(scratch), 256));
+  const size_t a8 = b200_align_up(size_t(n) * 8, 256), a4 = b200_align_up(size_t(n) * 4, 256), a1 = b200_align_up(size_t(n), 256);
+  uint64_t* vkeys = reinterpret_cast<uint64_t*>(base);
+  uint32_t* pay = reinterpret_cast<uint32_t*>(base + a8);
+  uint64_t* flat_keys = reinterpret_cast<uint64_t*>(base + a8 + a4);
+  uint8_t* flat_cls = reinterpret_cast<uint8_t*>(base + a8 + a4 + a8);
+  char* pair_scratch = base + a8 + a4 + a8 + a1;
+  const size_t pair_bytes = scratch_bytes - size_t(pair_scratch - reinterpret_cast<char*>(scratch));
+  const unsigned grid = unsigned((n + 255) / 256);
+  for (int k = n_keys - 2; k >= 0; --k) {
+    int64_t off = 0;
+    bool has_class = false;
+    for (int c = 0; c < n_chunks; ++c) {
+      const SortParams& p = src[size_t(k) * n_chunks + c];
+      if (p.n == 0) continue;
+      has_class = has_class || p.cls_digit >= 0;
+      mk_flat_kernel<<<unsigned((p.n + 255) / 256), 256, 0, ctx->stream>>>(p, off, flat_keys, flat_cls);
+      B200_LAUNCHED(ctx);
+      off += p.n;
+    }
+    mk_gather_flat_kernel<<<grid, 256, 0, ctx->stream>>>(flat_keys, flat_cls, out_indices, n, vkeys, pay);
+    B200_LAUNCHED(ctx);
+    B200_RETURN_NOT_OK(b200_sort_pairs32(ctx, vkeys, pay, n, nullptr, out_indices, pair_scratch, pair_bytes));
+    if (has_class) {
       mk_class_kernel<<<grid, 256, 0, ctx->stream>>>(out_indices, n, vkeys, pay);
       B200_LAUNCHED(ctx);
       B200_RETURN_NOT_OK(b200_sort_pairs32(ctx, vkeys, pay, n, nullptr, out_indices, pair_scratch, pair_bytes));

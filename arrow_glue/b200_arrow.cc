@@ -585,7 +585,7 @@ class CudaSortIndicesMetaFunction : public MetaFunction {
         return SortMulti(keys, sort_keys, batch.num_rows());
       }
       case Datum::TABLE: {
-        // SortIndices(Table) (vector_sort.cc:1672-1711); several keys: every key column in ONE chunk
+        // SortIndices(Table) (vector_sort.cc:1672-1711)
         const auto& table = *args[0].table();
         const auto& sort_keys = sort_options.sort_keys;
         if (sort_keys.empty()) return Status::Invalid("Must specify one or more sort keys");
@@ -596,18 +596,19 @@ class CudaSortIndicesMetaFunction : public MetaFunction {
           columns.push_back(chunked);
         }
         if (columns.size() == 1) return ExecuteImpl({Datum(columns[0])}, options, ctx);
-        std::vector<std::shared_ptr<ArrayData>> keys;
-        for (const auto& c : columns) {
-          if (table.num_rows() == 0) break;
-          if (c->num_chunks() != 1) return Status::NotImplemented("sort_indices(Table) with several sort keys needs single-chunk key columns");
-          keys.push_back(c->chunk(0)->data());
-        }
         if (table.num_rows() == 0) {
           ARROW_ASSIGN_OR_RAISE(DeviceState * dev, GetDevice(device_));
           ARROW_ASSIGN_OR_RAISE(auto out, AllocateDevice(dev, 0));
           return Datum(ArrayData::Make(uint64(), 0, {nullptr, std::move(out)}, 0));
         }
-        return SortMulti(keys, sort_keys, table.num_rows());
+        // key columns sliced to common chunk boundaries (offsets move, buffers stay), then one call
+        std::vector<ArrayVector> groups;
+        for (const auto& c : columns) groups.push_back(c->chunks());
+        groups = arrow::internal::RechunkArraysConsistently(groups);
+        std::vector<std::shared_ptr<ArrayData>> keys;
+        for (const auto& g : groups)
+          for (const auto& piece : g) keys.push_back(piece->data());
+        return SortMulti(keys, sort_keys, table.num_rows(), int(groups[0].size()));
       }
       default:
         break;
@@ -616,25 +617,26 @@ class CudaSortIndicesMetaFunction : public MetaFunction {
   }
 
  private:
-  // several sort keys: b200_sort_indices_multi (one stable radix sort per key, least significant first)
+  // several sort keys: b200_sort_indices_multi[_chunked] (one stable radix sort per key, least significant first).
+  // keys: key-major, n_chunks pieces per sort key
   Result<Datum> SortMulti(const std::vector<std::shared_ptr<ArrayData>>& keys, const std::vector<SortKey>& sort_keys,
-                          int64_t length) const {
+                          int64_t length, int n_chunks = 1) const {
     ARROW_ASSIGN_OR_RAISE(DeviceState * dev, GetDevice(device_));
     std::vector<b200_col> cols(keys.size());
-    std::vector<int> orders(keys.size());
-    for (size_t k = 0; k < keys.size(); ++k) {
-      ARROW_ASSIGN_OR_RAISE(const int32_t t, NumericType(*keys[k]->type));
-      RETURN_NOT_OK(ToCol(*keys[k], t, &cols[k]));
-      orders[k] = sort_keys[k].order == SortOrder::Descending ? 1 : 0;
+    std::vector<int> orders(sort_keys.size());
+    for (size_t i = 0; i < keys.size(); ++i) {
+      ARROW_ASSIGN_OR_RAISE(const int32_t t, NumericType(*keys[i]->type));
+      RETURN_NOT_OK(ToCol(*keys[i], t, &cols[i]));
     }
+    for (size_t k = 0; k < sort_keys.size(); ++k) orders[k] = sort_keys[k].order == SortOrder::Descending ? 1 : 0;
     std::lock_guard<std::mutex> lock(dev->mutex);
     size_t scratch_bytes = 0;
-    B200_OK_OR_RAISE(dev, b200_sort_indices_multi_scratch_bytes(length, &scratch_bytes));
+    B200_OK_OR_RAISE(dev, b200_sort_indices_multi_chunked_scratch_bytes(length, &scratch_bytes));
     ARROW_ASSIGN_OR_RAISE(auto scratch, AllocateDevice(dev, static_cast<int64_t>(scratch_bytes)));
     ARROW_ASSIGN_OR_RAISE(auto out, AllocateDevice(dev, length * 8));
-    B200_OK_OR_RAISE(dev, b200_sort_indices_multi(dev->ctx, cols.data(), orders.data(), int(cols.size()),
-                                                  reinterpret_cast<uint64_t*>(out->address()),
-                                                  reinterpret_cast<void*>(scratch->address()), scratch_bytes));
+    B200_OK_OR_RAISE(dev, b200_sort_indices_multi_chunked(dev->ctx, cols.data(), orders.data(), int(sort_keys.size()), n_chunks,
+                                                          reinterpret_cast<uint64_t*>(out->address()),
+                                                          reinterpret_cast<void*>(scratch->address()), scratch_bytes));
     B200_OK_OR_RAISE(dev, b200_ctx_synchronize(dev->ctx));  // scratch is released on return
     return Datum(ArrayData::Make(uint64(), length, {nullptr, std::move(out)}, 0));
   }

@@ -462,6 +462,13 @@ int main() {
       auto want_t = GET(cp::CallFunction("sort_indices", {Datum(htable)}, &opts, &cpu_ctx)).make_array();
       auto got_t = HostArray(GET(cp::CallFunction("sort_indices", {Datum(dtable)}, &opts, &gpu_ctx)));
       ExpectEqual(got_t, want_t, "sort_indices Table, " + std::to_string(keys.size()) + " sort keys");
+      // the same table in chunks, each column cut at different places (vector_sort_test.cc:886-980 "several chunks")
+      auto hx = Chunked(k0, {0, 7, 30000, n}), hy = Chunked(k1, {0, 20000, 20000, n}), hz = Chunked(k2, {0, 1, 59999, n});
+      auto htable_c = Table::Make(sch, {hx, hy, hz});
+      auto dtable_c = Table::Make(sch, {DeviceChunked(*hx), DeviceChunked(*hy), DeviceChunked(*hz)});
+      auto want_c = GET(cp::CallFunction("sort_indices", {Datum(htable_c)}, &opts, &cpu_ctx)).make_array();
+      auto got_c = HostArray(GET(cp::CallFunction("sort_indices", {Datum(dtable_c)}, &opts, &gpu_ctx)));
+      ExpectEqual(got_c, want_c, "sort_indices multi-chunk Table, " + std::to_string(keys.size()) + " sort keys");
     }
     cp::SortOptions none;
     auto st0 = cp::CallFunction("sort_indices", {Datum(dbatch)}, &none, &gpu_ctx).status();

@@ -200,6 +200,13 @@ B200_API int b200_sort_indices_chunked(b200_ctx* ctx, const b200_col* chunks, in
 B200_API int b200_sort_indices_multi_scratch_bytes(int64_t length, size_t* out_bytes);
 B200_API int b200_sort_indices_multi(b200_ctx* ctx, const b200_col* keys, const int* orders, int n_keys,
                                      uint64_t* out_indices, void* scratch, size_t scratch_bytes);
+/* The same over chunked key columns (SortIndices(Table), MultipleKeyTableSorter, vector_sort.cc:1381-1560):
+ * keys[k * n_chunks + c] is chunk c of sort key k; chunk c has the same length under every key (the binding
+ * slices the columns to common boundaries).  Indices address the logical concatenation. */
+B200_API int b200_sort_indices_multi_chunked_scratch_bytes(int64_t total_length, size_t* out_bytes);
+B200_API int b200_sort_indices_multi_chunked(b200_ctx* ctx, const b200_col* keys, const int* orders, int n_keys,
+                                             int n_chunks, uint64_t* out_indices, void* scratch,
+                                             size_t scratch_bytes);
 /* Sample-sort building blocks for the multi-GPU path.  sort_keys writes the
  * order-preserving 64-bit radix key of every row (the same transform the local sort uses;
  * NaN -> 2^64-2, null -> 2^64-1) so that ranks can exchange (key, global row) pairs;

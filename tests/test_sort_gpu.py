@@ -257,3 +257,31 @@ def test_sort_indices_multi_key_errors(ctx):
     with pytest.raises(B200Error) as e:
         capi.sort_indices_multi(ctx, [a, flag], [0, 0])
     assert e.value.code == 10
+
+
+def test_sort_indices_multi_key_chunked_table(ctx):
+    """b200_sort_indices_multi_chunked == SortIndices(Table) over multi-chunk columns (vector_sort_test.cc:886-980
+    "Same data, several chunks"): the golden cases cut in two, and random tables cut at random places (empty
+    chunks included) against the reference's MultipleKeyTableSorter on the whole columns."""
+    from helpers import MULTI_KEY_GOLDEN, multi_key_cases
+
+    def cut(col, cuts):
+        vals, valid = col.values(), col.valid()
+        return [Column.from_numpy(vals[a:b].copy(), None if (valid[a:b].all() and (a + b) % 2) else valid[a:b].copy()).to_device()
+                for a, b in zip(cuts[:-1], cuts[1:])]
+    for keys, orders, want in MULTI_KEY_GOLDEN():
+        n = keys[0].length
+        for cuts in ([0, n // 2, n], [0, 0, 1, n, n]):
+            got = capi.sort_indices_multi(ctx, [cut(k, cuts) for k in keys], orders).cpu().numpy().view(np.uint64)
+            np.testing.assert_array_equal(got, np.array(want, dtype=np.uint64))
+    rng = np.random.default_rng(12)
+    for n in (50, 40_000):
+        for keys, orders in multi_key_cases(rng, n):
+            cuts = [0] + sorted(rng.integers(0, n, size=5).tolist()) + [n]
+            want = oracle.sort_indices_multi(keys, orders, kind=ORACLE, as_table=True, n_chunks=4) if ORACLE == "reference" \
+                else oracle.sort_indices_multi(keys, orders)
+            got = capi.sort_indices_multi(ctx, [cut(k, cuts) for k in keys], orders).cpu().numpy().view(np.uint64)
+            np.testing.assert_array_equal(got, want)
+    with pytest.raises(B200Error):
+        a = Column.from_numpy(np.arange(10, dtype=np.int32)).to_device()
+        capi.sort_indices_multi(ctx, [[a, a], [a]], [0, 0])
