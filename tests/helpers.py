@@ -129,20 +129,11 @@ def assert_group_equal(a: GroupRes, b: GroupRes, aggs, rtol=1e-12, scales=None):
 
 
 def MULTI_KEY_GOLDEN():
-    """vector_sort_test.cc:783-842 (TestRecordBatchSortIndices Null / NaN / NaNAndNull): a ascending, b descending."""
-    import numpy as np
-    from arrow1_b200 import columns as cols
-    nan = np.nan
-
-    def col(values, dtype):
-        valid = np.array([v is not None for v in values])
-        data = np.array([0 if v is None else v for v in values], dtype=dtype)
-        return cols.Column.from_numpy(data, valid if not valid.all() else None)
-    yield ([col([None, 1, 3, None, 2, 1], np.uint8), col([5, 3, None, None, 5, 5], np.uint32)], [0, 1], [5, 1, 4, 2, 0, 3])
-    yield ([col([3, 1, 3, 0, nan, nan, nan, 1], np.float32), col([5, nan, 4, 6, 5, nan, 5, 5], np.float64)], [0, 1],
-           [3, 7, 1, 0, 2, 4, 6, 5])
-    yield ([col([None, 1, 3, None, nan, nan, nan, 1], np.float32), col([5, 3, None, None, None, nan, 5, 5], np.float64)], [0, 1],
-           [7, 1, 2, 6, 5, 4, 0, 3])
+    """tests/golden/sort_indices_multi.json (vector_sort_test.cc:763-842, 886-980) as (keys, orders, expected)."""
+    from conftest import column_from_json, load_golden
+    for case in load_golden("sort_indices_multi.json")["cases"]:
+        keys = [column_from_json(v, t) for v, t in zip(case["columns"], case["types"])]
+        yield keys, case["orders"], case["expected"]
 
 
 def multi_key_cases(rng, n):

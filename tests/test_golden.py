@@ -163,3 +163,28 @@ def test_grouper_golden(impl, request):
                 _grouper_sequence(impl, ctx, [t], seq["batches"])
         else:
             _grouper_sequence(impl, ctx, seq["key_types"], seq["batches"])
+
+
+@pytest.mark.parametrize("impl", IMPLS)
+def test_sort_indices_multi_key_golden(impl, request):
+    """TestRecordBatchSortIndices / TestTableSortIndices: two sort keys, nulls and NaNs, one chunk and several."""
+    g = load_golden("sort_indices_multi.json")
+    ctx = _ctx(impl, request)
+    for case in g["cases"]:
+        keys = [column_from_json(v, t) for v, t in zip(case["columns"], case["types"])]
+        want = np.array(case["expected"], dtype=np.uint64)
+        for cuts in case["chunks"]:
+            if impl == "gpu":
+                from arrow1_b200 import capi
+                if len(cuts) == 2:
+                    got = capi.sort_indices_multi(ctx, [k.to_device() for k in keys], case["orders"])
+                else:
+                    pieces = [[column_from_json(v[a:b], t).to_device() for a, b in zip(cuts[:-1], cuts[1:])]
+                              for v, t in zip(case["columns"], case["types"])]
+                    got = capi.sort_indices_multi(ctx, pieces, case["orders"])
+                got = got.cpu().numpy().view(np.uint64)
+            elif impl == "reference":
+                got = oracle.sort_indices_multi(keys, case["orders"], kind="reference", as_table=len(cuts) > 2, n_chunks=len(cuts) - 1)
+            else:
+                got = oracle.sort_indices_multi(keys, case["orders"])
+            np.testing.assert_array_equal(got, want, err_msg=case["name"])
