@@ -21,6 +21,7 @@ import numpy as np
 import torch
 
 from . import capi
+from .capi import B200Error
 from .columns import BITS, AggSpec, Column
 
 DROP, EMIT_NULL = 0, 1          # FilterOptions::NullSelectionBehavior (api_vector.h:37-49)
@@ -136,6 +137,13 @@ def SortIndices(values, order=ASCENDING, ctx: Optional[capi.Context] = None, _wa
     with a sequence of orders — the sort keys of SortIndices(RecordBatch | Table, SortOptions), most significant
     first (vector_sort.cc:1632-1711).  uint64 indices: numpy array for host input, int64-typed torch tensor for
     device input."""
+    if not isinstance(values, Column):   # argument errors come before any device work
+        keys = list(values)
+        if len(keys) == 0:
+            raise B200Error(4, "Must specify one or more sort keys")
+        orders = [order] * len(keys) if isinstance(order, int) else list(order)
+        if len(orders) != len(keys):
+            raise B200Error(4, "SortIndices: one order per sort key")
     ctx = ctx or default_context()
     if isinstance(values, Column):
         host = _from_host(values)
@@ -143,12 +151,6 @@ def SortIndices(values, order=ASCENDING, ctx: Optional[capi.Context] = None, _wa
         out = capi.sort_indices(ctx, dv, order)
         n = values.length
     else:
-        keys = list(values)
-        if len(keys) == 0:
-            raise B200Error(4, "Must specify one or more sort keys")
-        orders = [order] * len(keys) if isinstance(order, int) else list(order)
-        if len(orders) != len(keys):
-            raise B200Error(4, "SortIndices: one order per sort key")
         host = _from_host(keys[0])
         staged = [_h2d(k, ctx) for k in keys]
         b0 = sum(b for _, b in staged)
@@ -169,13 +171,13 @@ def Take(values, indices, boundscheck: bool = True, ctx: Optional[capi.Context] 
     sequence of Columns (ChunkedArray values, TakeCA vector_selection.cc:1921-1944: indices address the
     concatenation; the result is one Column).  Host columns are staged to the device and the result comes back
     to the host; device columns (or a device index tensor from SortIndices) stay."""
+    if not isinstance(values, Column) and len(values) == 0:
+        raise B200Error(4, "Must pass at least one array")   # Concatenate's message on TakeCA's route
     ctx = ctx or default_context()
     if isinstance(values, Column):
         host = not values.on_device
         dv, b0 = _h2d(values, ctx)
     else:
-        if len(values) == 0:
-            raise B200Error(4, "take: no chunks")
         host = not values[0].on_device
         staged = [_h2d(v, ctx) for v in values]
         dv, b0 = [c for c, _ in staged], sum(b for _, b in staged)

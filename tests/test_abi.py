@@ -75,3 +75,36 @@ def test_no_cpu_fallback_without_gpu():
     from arrow1_b200 import capi
     with pytest.raises(RuntimeError):
         capi.Context(0)
+
+
+def test_multi_key_and_chunked_scratch_sizes():
+    lib = _lib()
+    one, multi, chunked, multi_chunked = (C.c_size_t(0) for _ in range(4))
+    n = C.c_int64(1_000_000)
+    assert lib.b200_sort_indices_scratch_bytes(n, C.byref(one)) == 0
+    assert lib.b200_sort_indices_multi_scratch_bytes(n, C.byref(multi)) == 0
+    assert lib.b200_sort_indices_chunked_scratch_bytes(n, C.byref(chunked)) == 0
+    assert lib.b200_sort_indices_multi_chunked_scratch_bytes(n, C.byref(multi_chunked)) == 0
+    # a multi-key scratch also serves the single-key route it forwards to, and the chunked form both of its routes
+    assert multi.value >= one.value + 12 * 1_000_000
+    assert multi_chunked.value >= max(multi.value, chunked.value)
+    assert lib.b200_sort_indices_multi_scratch_bytes(C.c_int64(-1), C.byref(multi)) == 4
+
+
+def test_host_mirror_argument_errors_come_before_device_work():
+    """compute.SortIndices / Take reject malformed key / chunk lists with the reference's Invalid status without
+    needing a device (the messages are SortIndicesMetaFunction's and Concatenate's)."""
+    from arrow1_b200 import compute
+    from arrow1_b200.capi import B200Error
+    from arrow1_b200.columns import Column
+    import numpy as np
+    with pytest.raises(B200Error) as e:
+        compute.SortIndices([], [])
+    assert e.value.code == 4 and "one or more sort keys" in str(e.value)
+    a = Column.from_numpy(np.arange(4, dtype=np.int32))
+    with pytest.raises(B200Error) as e:
+        compute.SortIndices([a, a], [0])
+    assert e.value.code == 4
+    with pytest.raises(B200Error) as e:
+        compute.Take([], a)
+    assert e.value.code == 4
