@@ -496,6 +496,9 @@ class GroupBy:
         except Exception:
             pass
 
+    def set_option(self, name: str, value: int):
+        self.ctx.check(lib().b200_groupby_set_option(self._h, name.encode(), C.c_int64(value)))
+
     def consume(self, keys: Sequence[Column], args: Sequence[Column], row_base: int = 0):
         self.ctx.check(lib().b200_groupby_consume(self._h, col_array(keys), col_array(args), C.c_uint64(row_base)))
 
@@ -638,11 +641,14 @@ def pack_validity(ctx: Context, valid_bytes: torch.Tensor):
 
 
 def group_by(ctx: Context, keys: Sequence[Column], aggs: Sequence[AggSpec], args: Sequence[Column],
-             expected_groups: int = 0, row_base: int = 0, selection: Optional[Column] = None) -> GroupByOutput:
+             expected_groups: int = 0, row_base: int = 0, selection: Optional[Column] = None,
+             options: Optional[dict] = None) -> GroupByOutput:
     """== compute::internal::GroupBy(arguments, keys, aggregates) in one batch; with `selection`, of the selected
     rows only (== GroupBy over Filter(column, selection) of every column)."""
     gb = GroupBy(ctx, [k.type for k in keys], aggs, [a.type for a in args], expected_groups)
     try:
+        for name, value in (options or {}).items():
+            gb.set_option(name, value)
         if selection is None:
             gb.consume(keys, args, row_base)
         else:

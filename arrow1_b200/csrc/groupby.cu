@@ -304,10 +304,29 @@ __device__ __forceinline__ char* global_slot(const GbTable& t, int stride, uint6
   return nullptr;
 }
 
-__global__ void gb_init_kernel(GbSchema s, char* slots, uint64_t n_slots, int stride) {
-  const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i < n_slots) init_slot(slots + i * stride, s);
+// one thread per 8-byte word: consecutive threads write consecutive words (the per-slot form wrote 8 bytes at a
+// stride of one slot per store instruction: 1.8 TB/s)
+__global__ void gb_init_kernel(const __grid_constant__ GbSchema s, char* slots, uint64_t n_slots, int stride) {
+  __shared__ uint64_t image[64];
+  const int words = stride / 8;
+  if (threadIdx.x < 64) image[threadIdx.x] = 0;
+  __syncthreads();
+  if (threadIdx.x == 0) init_slot(reinterpret_cast<char*>(image), s);
+  __syncthreads();
+  const uint64_t total = n_slots * uint64_t(words);
+  uint64_t* out = reinterpret_cast<uint64_t*>(slots);
+  const uint64_t step = uint64_t(gridDim.x) * blockDim.x;
+  uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  int w = int(i % uint64_t(words));
+  const int step_w = int(step % uint64_t(words));
+  for (; i < total; i += step) {
+    out[i] = image[w];
+    w += step_w;
+    if (w >= words) w -= words;
+  }
 }
+
+#include "groupby_hp.cuh"
 
 // ---- the consume kernel ---------------------------------------------------------------------
 template <bool kLocal>
@@ -2081,13 +2100,35 @@ __global__ void gb_move_kernel(GbSchema s, const char* src, uint64_t n_src, int 
 __global__ void gb_collect_kernel(GbTable t, int stride, uint64_t* first_rows, uint64_t* slot_idx, uint32_t* counter,
                                   const uint32_t* slot_ids, int only_unassigned) {
   const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i >= t.cap + 2) return;
-  const uint64_t* w = reinterpret_cast<const uint64_t*>(t.slots + i * stride);
-  if (w[0] == kEmpty) return;
-  if (only_unassigned && slot_ids[i] != kNoId) return;
-  const uint32_t pos = atomicAdd(counter, 1u);
-  first_rows[pos] = w[1];
-  slot_idx[pos] = i;
+  bool take = i < t.cap + 2;
+  uint64_t first = 0;
+  if (take) {
+    const ulonglong2 kw = *reinterpret_cast<const ulonglong2*>(t.slots + i * stride);   // {key, first_row}: one 16-byte load
+    first = kw.y;
+    take = kw.x != kEmpty;
+    if (take && only_unassigned && slot_ids[i] != kNoId) take = false;
+  }
+  // one position claim per warp (10^8 groups bumping one counter would serialise in L2)
+  const unsigned m = __ballot_sync(0xffffffffu, take);
+  if (m == 0) return;
+  const int lane = threadIdx.x & 31;
+  uint32_t base = 0;
+  if (lane == __ffs(m) - 1) base = atomicAdd(counter, uint32_t(__popc(m)));
+  base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+  if (take) {
+    const uint32_t pos = base + __popc(m & ((1u << lane) - 1u));
+    first_rows[pos] = first;
+    slot_idx[pos] = i;
+  }
+}
+
+// the groups of a pending image list (see b200_groupby::pending): every image is a group
+__global__ void gb_collect_images_kernel(const char* images, int stride, uint32_t n, uint64_t* first_rows, uint64_t* slot_idx) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    first_rows[i] = reinterpret_cast<const uint64_t*>(images + size_t(i) * stride)[1];
+    slot_idx[i] = i;
+  }
 }
 
 // grouper: first_row of the newly claimed slots
@@ -2464,6 +2505,17 @@ struct b200_groupby {
   // scratch owned by the handle
   void* tmp = nullptr;
   size_t tmp_bytes = 0;
+  // Groups of a first, fully partitioned consume wait here as slot images (inside hp_tmp) instead of in the table:
+  // finalize reads them directly; any other use of the handle folds them into the table first (materialize()).
+  // With a cardinality hint in the partitioned path's range the table itself is only allocated when needed:
+  // at 10^8 expected groups it is a 17 GB array to initialise, fill and scan.
+  char* pending = nullptr;
+  uint32_t pending_n = 0;
+  // high-cardinality path (groupby_hp.cuh): partition buffers, and the sizes from which it is taken
+  void* hp_tmp = nullptr;
+  size_t hp_bytes = 0;
+  int64_t hp_min_rows = int64_t(1) << 22;
+  int64_t hp_min_groups = int64_t(1) << 21;   // a table of this many slots no longer fits in L2
 };
 
 namespace {
@@ -2520,8 +2572,11 @@ int read_counters(b200_groupby* gb, uint32_t out[4]) {
 }
 
 // grows the table to at least `min_cap` slots, re-inserting every group
+uint64_t initial_cap(const b200_groupby* gb) { return pow2_at_least(gb->expected > 0 ? gb->expected * 2 : (1u << 16)); }
+
 int grow_table(b200_groupby* gb, uint64_t min_cap) {
   b200_ctx* ctx = gb->ctx;
+  if (!gb->table.slots) return alloc_table(gb, std::max(pow2_at_least(min_cap), initial_cap(gb)), &gb->table);
   const uint64_t new_cap = pow2_at_least(min_cap);
   if (new_cap <= gb->table.cap) return B200_OK;
   GbTable nt;
@@ -2544,6 +2599,25 @@ int grow_table(b200_groupby* gb, uint64_t min_cap) {
     gb->ids_assigned = 0;
   }
   return B200_OK;
+}
+
+int ensure_table(b200_groupby* gb) { return gb->table.slots ? B200_OK : alloc_table(gb, initial_cap(gb), &gb->table); }
+
+// the table exists and holds every group (pending images folded in)
+int materialize(b200_groupby* gb) {
+  b200_ctx* ctx = gb->ctx;
+  B200_RETURN_NOT_OK(ensure_table(gb));
+  if (!gb->pending) return B200_OK;
+  const uint32_t n = gb->pending_n;
+  const char* images = gb->pending;
+  gb->pending = nullptr;
+  gb->pending_n = 0;
+  gb->groups = 0;
+  B200_CUDA(ctx, cudaMemsetAsync(gb->counters, 0, sizeof(uint32_t), ctx->stream));
+  B200_RETURN_NOT_OK(grow_table(gb, 2 * uint64_t(n)));
+  B200_TIMED(ctx, "groupby_import", (gb_hp_import_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(gb->schema, images, n, gb->table, gb->counters)));
+  uint32_t c[4];
+  return read_counters(gb, c);
 }
 
 int fill_keys(b200_groupby* gb, const b200_col* keys, GbArgs* a) {
@@ -2590,6 +2664,170 @@ int import_spilled(b200_groupby* gb, const char* spill) {
   return read_counters(gb, c);
 }
 
+
+// ---- high-cardinality path: partition by hash, aggregate the partitions in shared memory, import the groups
+bool hp_applicable(const b200_groupby* gb, const GbArgs& a, uint64_t likely_groups) {
+  if (a.mode != kModeFused || a.n_cols > 1 || a.defer_in) return false;
+  if (a.n < gb->hp_min_rows || a.n >= (int64_t(1) << 31)) return false;
+  if (likely_groups < uint64_t(gb->hp_min_groups)) return false;
+  for (int j = 0; j < a.s.n_aggs; ++j) {
+    const int kind = a.s.aggs[j].kind;
+    if (kind != B200_HASH_COUNT && kind != B200_HASH_SUM && kind != B200_HASH_MEAN) return false;
+  }
+  return true;
+}
+
+// *handled = false: not taken (explicit row numbers out of order); the caller goes on with the generic kernels
+int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* handled, uint32_t* deferred) {
+  b200_ctx* ctx = gb->ctx;
+  *handled = false;
+  *deferred = 0;
+  const int64_t n = a.n;
+  // partition plan
+  const uint64_t est = std::min<uint64_t>(uint64_t(n), std::max<uint64_t>(likely_groups, 1));
+  int bits = 1;
+  while (bits < 17 && (uint64_t(kHpKeysPerPart) << bits) < est) ++bits;
+  const int bits1 = bits <= 9 ? bits : bits / 2;
+  const int bits2 = bits - bits1;
+  const uint32_t parts1 = 1u << bits1, parts = 1u << bits;
+  // scratch: two tuple buffers + histograms / cursors / starts + work items
+  const size_t a8 = b200_align_up(size_t(n) * 8, 256), a4 = b200_align_up(size_t(n) * 4, 256);
+  const size_t buf_bytes = 2 * a8 + a4;
+  const size_t small = b200_align_up(size_t(parts + 1) * 4, 256);
+  const size_t need = 2 * buf_bytes + 9 * small + 1024;
+  if (need > gb->hp_bytes) {
+    if (gb->hp_tmp) b200_dev_free(ctx, gb->hp_tmp);
+    gb->hp_tmp = nullptr;
+    gb->hp_bytes = 0;
+    if (b200_dev_alloc(ctx, &gb->hp_tmp, need) != B200_OK) {
+      ctx->error.clear();
+      return B200_OK;   // not enough memory for the partition buffers: the generic path needs none
+    }
+    gb->hp_bytes = need;
+  }
+  char* base = reinterpret_cast<char*>(gb->hp_tmp);
+  auto bufs_at = [&](char* p) {
+    HpBufs b;
+    b.keys = reinterpret_cast<uint64_t*>(p);
+    b.vals = reinterpret_cast<uint64_t*>(p + a8);
+    b.rows = reinterpret_cast<uint32_t*>(p + 2 * a8);
+    return b;
+  };
+  const HpBufs buf_a = bufs_at(base), buf_b = bufs_at(base + buf_bytes);
+  char* sm = base + 2 * buf_bytes;
+  uint32_t* hist1 = reinterpret_cast<uint32_t*>(sm);
+  uint32_t* hist2 = reinterpret_cast<uint32_t*>(sm + small);
+  uint32_t* items = reinterpret_cast<uint32_t*>(sm + 2 * small);
+  uint32_t* misc = reinterpret_cast<uint32_t*>(sm + 3 * small);   // [0] ticket, [1] row-order flag
+  const size_t zero_bytes = 3 * small + 256;
+  uint32_t* cursor1 = reinterpret_cast<uint32_t*>(sm + 3 * small + 256);
+  uint32_t* base1 = reinterpret_cast<uint32_t*>(sm + 4 * small + 256);
+  uint32_t* cursor2 = reinterpret_cast<uint32_t*>(sm + 5 * small + 256);
+  uint32_t* base2 = reinterpret_cast<uint32_t*>(sm + 6 * small + 256);
+  uint32_t* item_base = reinterpret_cast<uint32_t*>(sm + 7 * small + 256);
+  B200_CUDA(ctx, cudaMemsetAsync(sm, 0, zero_bytes, ctx->stream));
+  if (a.row_ids) {
+    // the earliest row of a group is tracked by its position in the batch: explicit row numbers must ascend
+    gb_hp_monotone_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(a.row_ids, n, misc + 1);
+    B200_LAUNCHED(ctx);
+    B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 24, misc + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (*reinterpret_cast<const uint32_t*>(ctx->host_words + 24) != 0) return B200_OK;
+  }
+  // the table takes the expected groups at load <= 1/2; a partition = the hash bits just below its index width
+  // (the table itself may not exist yet, see b200_groupby::pending)
+  const uint64_t planned_cap = std::max<uint64_t>(gb->table.cap, pow2_at_least(2 * std::max<uint64_t>(likely_groups, 32 * 1024)));
+  int cap_bits = 0;
+  while ((uint64_t(1) << cap_bits) < planned_cap) ++cap_bits;
+  const int top = std::max(cap_bits, bits);   // partition id = hash bits [top - bits, top)
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_part_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpPartSmem))));
+    B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_part_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpPartSmem))));
+    B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_agg_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpAggSmem))));
+    B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_agg_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpAggSmem))));
+    attr = true;
+  }
+  const int64_t n_tiles = (n + kHpTile - 1) / kHpTile;
+  const unsigned grid = unsigned(std::min<int64_t>(n_tiles, int64_t(ctx->num_sms) * 8));
+  HpArgs h;
+  memset(&h, 0, sizeof(h));
+  h.has_val = a.n_cols > 0;
+  // level 1
+  h.dst = buf_a;
+  h.parts = 1;
+  h.hist = hist1;
+  h.cursor = cursor1;
+  h.bins = int(parts1);
+  h.shift = top - bits1;
+  B200_TIMED(ctx, "groupby_partition", (gb_hp_hist_kernel<1><<<grid, kHpThreads, 0, ctx->stream>>>(a, h)));
+  gb_hp_scan_kernel<<<1, 1024, 0, ctx->stream>>>(hist1, parts1, cursor1, base1);
+  B200_LAUNCHED(ctx);
+  B200_TIMED(ctx, "groupby_partition", (gb_hp_part_kernel<1><<<grid, kHpThreads, int(sizeof(HpPartSmem)), ctx->stream>>>(a, h)));
+  HpBufs agg_src = buf_a;
+  const uint32_t* agg_base = base1;
+  char* images = reinterpret_cast<char*>(buf_b.keys);
+  if (bits2 > 0) {
+    h.src = buf_a;
+    h.dst = buf_b;
+    h.base = base1;
+    h.parts = int(parts1);
+    h.hist = hist2;
+    h.cursor = cursor2;
+    h.bins = 1 << bits2;
+    h.shift = top - bits;
+    B200_TIMED(ctx, "groupby_partition", (gb_hp_hist_kernel<2><<<grid, kHpThreads, 0, ctx->stream>>>(a, h)));
+    gb_hp_scan_kernel<<<1, 1024, 0, ctx->stream>>>(hist2, parts, cursor2, base2);
+    B200_LAUNCHED(ctx);
+    B200_TIMED(ctx, "groupby_partition", (gb_hp_part_kernel<2><<<grid, kHpThreads, int(sizeof(HpPartSmem)), ctx->stream>>>(a, h)));
+    agg_src = buf_b;
+    agg_base = base2;
+    images = reinterpret_cast<char*>(buf_a.keys);
+  }
+  // aggregation: one work item per partition (several for a partition far above the average size)
+  const uint32_t seg_rows = uint32_t(std::max<int64_t>(int64_t(1) << 16, 8 * (n / parts)));
+  gb_hp_items_kernel<<<(parts + 255) / 256, 256, 0, ctx->stream>>>(agg_base, parts, seg_rows, items);
+  B200_LAUNCHED(ctx);
+  gb_hp_scan_kernel<<<1, 1024, 0, ctx->stream>>>(items, parts, nullptr, item_base);
+  B200_LAUNCHED(ctx);
+  const uint32_t image_cap = uint32_t(std::min<uint64_t>(buf_bytes / size_t(a.s.stride), 0xFFFFFFF0ull));
+  B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 6, 0, sizeof(uint32_t), ctx->stream));
+  bool float_sum = false;
+  for (int j = 0; j < a.s.n_aggs; ++j)
+    if (a.s.aggs[j].kind != B200_HASH_COUNT && a.s.aggs[j].dom == kFloat) float_sum = true;
+  const unsigned agg_grid = unsigned(std::min<int64_t>(int64_t(parts), int64_t(ctx->num_sms) * 2));
+  if (float_sum)
+    B200_TIMED(ctx, "groupby_consume", (gb_hp_agg_kernel<true><<<agg_grid, kHpThreads, int(sizeof(HpAggSmem)), ctx->stream>>>(
+                                           a, agg_src, agg_base, item_base, parts, seg_rows, images, image_cap, misc)));
+  else
+    B200_TIMED(ctx, "groupby_consume", (gb_hp_agg_kernel<false><<<agg_grid, kHpThreads, int(sizeof(HpAggSmem)), ctx->stream>>>(
+                                           a, agg_src, agg_base, item_base, parts, seg_rows, images, image_cap, misc)));
+  uint32_t c[4];
+  B200_RETURN_NOT_OK(read_counters(gb, c));
+  *deferred = c[1];
+  const uint32_t n_images = reinterpret_cast<const uint32_t*>(ctx->host_words + 16)[6];
+  const uint32_t n_items = reinterpret_cast<const uint32_t*>(ctx->host_words + 16)[7];
+  *handled = true;
+  if (gb->groups == 0 && c[1] == 0 && n_items <= parts && n_images > 0) {
+    // first groups of the handle, every row placed, no partition cut into several work items: the images are the
+    // groups, each key once.  They stay where they are until something needs the table.
+    gb->pending = images;
+    gb->pending_n = n_images;
+    gb->groups = n_images;
+    gb_fill_u32_kernel<<<1, 32, 0, ctx->stream>>>(gb->counters, 1, n_images);
+    B200_LAUNCHED(ctx);
+    return B200_OK;
+  }
+  B200_RETURN_NOT_OK(ensure_table(gb));
+  if (n_images) {
+    if (2 * (uint64_t(gb->groups) + n_images) > gb->table.cap) B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + n_images)));
+    B200_TIMED(ctx, "groupby_import", (gb_hp_import_kernel<<<(n_images + 255) / 256, 256, 0, ctx->stream>>>(gb->schema, images, n_images,
+                                                                                                           gb->table, gb->counters)));
+    B200_RETURN_NOT_OK(read_counters(gb, c));
+  }
+  return B200_OK;
+}
+
 // launches the consume kernel over all rows, then re-runs it over deferred rows after growing the
 // table until every row found a slot
 int run_consume(b200_groupby* gb, GbArgs& a) {
@@ -2624,8 +2862,27 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
   // one value column (or none) and a cardinality hint (or history) that fits the shared table: the fast kernel.
   // With no hint at all the fast kernel is tried too: a CTA whose table fills up bypasses it.
   const bool fast = a.mode == kModeFused && a.n_cols == 1 && likely_groups <= uint64_t(kFastMaxGroupsHint) && !gb->fast_disabled && !a.row_ids;
+  // (the partitioned path decides itself whether it needs the table)
+  const bool try_hp = hp_applicable(gb, a, likely_groups);
+  if (gb->pending || !try_hp) B200_RETURN_NOT_OK(materialize(gb));
   for (int round = 0; round < 8; ++round) {
     a.t = gb->table;
+    if (round == 0 && try_hp) {
+      bool handled = false;
+      uint32_t hp_deferred = 0;
+      B200_RETURN_NOT_OK(run_hp_consume(gb, a, likely_groups, &handled, &hp_deferred));
+      if (!handled) B200_RETURN_NOT_OK(materialize(gb));
+      if (handled) {
+        if (hp_deferred == 0) return B200_OK;
+        if (uint64_t(gb->groups) + hp_deferred > gb->table.cap / 2) B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + hp_deferred)));
+        a.defer_in = defer_a;
+        a.defer_out = defer_b;
+        B200_CUDA(ctx, cudaMemsetAsync(defer_b, 0, words * 4, ctx->stream));
+        B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 1, 0, sizeof(uint32_t), ctx->stream));
+        continue;
+      }
+      a.t = gb->table;
+    }
     bool tiny = false;
     if (fast && round == 0 && likely_groups > 0 && likely_groups <= uint64_t(kTinyGroups)) {
       tiny = true;
@@ -2877,12 +3134,14 @@ int b200_groupby_create(b200_ctx* ctx, int n_keys, const int32_t* key_types, int
     return B200_OUT_OF_MEMORY;
   }
   cudaMemsetAsync(gb->counters, 0, 8 * sizeof(uint32_t), ctx->stream);
-  const uint64_t cap = pow2_at_least(expected_groups > 0 ? uint64_t(expected_groups) * 2 : (1u << 16));
-  int st = alloc_table(gb, cap, &gb->table);
-  if (st != B200_OK) {
-    b200_dev_free(ctx, gb->counters);
-    delete gb;
-    return st;
+  // with a hint in the partitioned path's range the table is allocated when first needed (b200_groupby::pending)
+  if (int64_t(gb->expected) < gb->hp_min_groups) {
+    int st = alloc_table(gb, initial_cap(gb), &gb->table);
+    if (st != B200_OK) {
+      b200_dev_free(ctx, gb->counters);
+      delete gb;
+      return st;
+    }
   }
   *out = gb;
   return B200_OK;
@@ -2896,7 +3155,16 @@ int b200_groupby_destroy(b200_groupby* gb) {
   b200_dev_free(gb->ctx, gb->slot_ids);
   b200_dev_free(gb->ctx, gb->dense);
   b200_dev_free(gb->ctx, gb->tmp);
+  b200_dev_free(gb->ctx, gb->hp_tmp);
   delete gb;
+  return B200_OK;
+}
+
+int b200_groupby_set_option(b200_groupby* gb, const char* name, int64_t value) {
+  if (!gb || !name) return B200_INVALID;
+  if (!strcmp(name, "hp_min_rows")) gb->hp_min_rows = value;
+  else if (!strcmp(name, "hp_min_groups")) gb->hp_min_groups = value;
+  else return b200_fail(gb->ctx, B200_KEY_ERROR, "groupby: no option named %s", name);
   return B200_OK;
 }
 
@@ -3083,6 +3351,7 @@ int b200_grouper_consume(b200_groupby* gb, const b200_col* keys, uint32_t* out_i
   const int64_t n = a.n;
   if (n == 0) return B200_OK;
   if (!out_ids) return b200_fail(ctx, B200_INVALID, "grouper_consume: null output");
+  B200_RETURN_NOT_OK(materialize(gb));
   // row indices continue across calls so that first-occurrence order is global
   a.row_base = gb->dense_rows;
   gb->dense_rows += uint64_t(n);
@@ -3229,12 +3498,20 @@ static int collect_slots(b200_groupby* gb, uint64_t** first_rows, uint64_t** slo
   *first_rows = reinterpret_cast<uint64_t*>(gb->tmp);
   *slot_idx = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(gb->tmp) + arr);
   if (extra_ptr) *extra_ptr = reinterpret_cast<char*>(gb->tmp) + 2 * arr;
+  *n_out = G;
+  if (gb->pending) {
+    if (G > 0) {
+      gb_collect_images_kernel<<<(G + 255) / 256, 256, 0, ctx->stream>>>(gb->pending, gb->schema.stride, G, *first_rows, *slot_idx);
+      B200_LAUNCHED(ctx);
+    }
+    return B200_OK;
+  }
+  B200_RETURN_NOT_OK(ensure_table(gb));
   B200_CUDA(ctx, cudaMemsetAsync(gb->counters + 4, 0, sizeof(uint32_t), ctx->stream));
   const uint64_t n_slots = gb->table.cap + 2;
   gb_collect_kernel<<<(unsigned)((n_slots + 255) / 256), 256, 0, ctx->stream>>>(gb->table, gb->schema.stride, *first_rows, *slot_idx,
                                                                                gb->counters + 4, nullptr, 0);
   B200_LAUNCHED(ctx);
-  *n_out = G;
   return B200_OK;
 }
 
@@ -3261,6 +3538,7 @@ int b200_groupby_export(b200_groupby* gb, void* out_state, uint32_t* out_groups)
   b200_ctx* ctx = gb->ctx;
   uint64_t *first_rows, *slot_idx;
   uint32_t G;
+  B200_RETURN_NOT_OK(materialize(gb));
   B200_RETURN_NOT_OK(collect_slots(gb, &first_rows, &slot_idx, &G, 0, nullptr));
   if (G > 0) {
     if (!out_state) return b200_fail(ctx, B200_INVALID, "groupby_export: null output");
@@ -3278,6 +3556,7 @@ int b200_groupby_import(b200_groupby* gb, const void* state, uint32_t n_slots) {
   b200_ctx* ctx = gb->ctx;
   if (n_slots == 0) return B200_OK;
   if (!state) return b200_fail(ctx, B200_INVALID, "groupby_import: null state");
+  B200_RETURN_NOT_OK(materialize(gb));
   uint32_t c[4];
   B200_RETURN_NOT_OK(read_counters(gb, c));
   B200_RETURN_NOT_OK(grow_table(gb, 2 * (uint64_t(gb->groups) + n_slots)));
@@ -3292,6 +3571,8 @@ int b200_groupby_merge(b200_groupby* dst, b200_groupby* src) {
   b200_ctx* ctx = dst->ctx;
   if (memcmp(&dst->schema, &src->schema, sizeof(GbSchema)) != 0) return b200_fail(ctx, B200_TYPE_ERROR, "groupby_merge: schemas differ");
   if (dst->ctx != src->ctx) return b200_fail(ctx, B200_INVALID, "groupby_merge: handles belong to different contexts");
+  B200_RETURN_NOT_OK(materialize(dst));
+  B200_RETURN_NOT_OK(materialize(src));
   uint32_t c[4];
   B200_RETURN_NOT_OK(read_counters(src, c));
   const uint32_t src_groups = c[0];
@@ -3335,6 +3616,10 @@ int b200_groupby_finalize(b200_groupby* gb, b200_out_col* out_aggs, b200_out_col
     void* sort_scratch = extra + arr + 4096;
     if (G > 0) B200_RETURN_NOT_OK(b200_sort_pairs(ctx, first_rows, slot_idx, G, nullptr, sorted, sort_scratch, sort_bytes));
     e.t = gb->table;
+    if (gb->pending) {   // slot index = image index; no image is a special slot
+      e.t.slots = gb->pending;
+      e.t.cap = ~uint64_t(0);
+    }
     e.order = sorted;
   }
   e.n_groups = G;

@@ -1,0 +1,483 @@
+// High-cardinality consume: radix-partition the rows by hash, then aggregate every partition in shared memory.
+// (Included by groupby.cu inside its anonymous namespace, after the key / value loaders.)
+//
+// GrouperImpl::Consume + GroupedSumImpl / GroupedCountImpl::Consume (reference hash_aggregate.cc:358-408, 466-622)
+// at a cardinality where the table no longer fits in L2: one row per thread with atomics on a multi-GB table costs
+// 2-4 random 32-byte sector round trips per row (C4: 137 ms per 1 B rows, 1.8 % of the HBM peak).  Here the rows
+// stream instead:
+//   gb_hp_hist_kernel<1>   keys -> counts per level-1 partition (hash bits just below the table's index width, so
+//                          a partition's groups later land in one contiguous region of the table)
+//   gb_hp_part_kernel<1>   (key, value, row | null << 31) tuples scattered into the level-1 partitions: a 4096-row
+//                          tile is ranked per bin with native shared 32-bit atomics, grouped in shared memory, and
+//                          every bin's run leaves as contiguous stores at a position claimed from the bin's cursor
+//                          (order inside a partition is immaterial: the earliest row is carried, not implied)
+//   gb_hp_hist_kernel<2> / gb_hp_part_kernel<2>   the same once more inside every level-1 partition
+//   gb_hp_agg_kernel       one CTA per final partition (~1.5 K keys): open-addressing table in shared memory
+//                          {key, sum, valid count, null count, earliest row}; the groups leave as slot images
+//   gb_import_kernel       (groupby.cu) folds the images into the global table, partition by partition, i.e. region
+//                          by region of the table
+// Rows that cannot be placed (special keys, a shared table that fills up, no room for a partition's images) are
+// flagged in the deferred-row bitmap and taken by the generic kernel, like in the other fast paths.
+// HBM bytes per row at C4 (int64 key, float64 value): 8 + (16 + 20) + 8 + (20 + 20) + 20 = 132, + the images and one
+// sweep over the table.
+
+constexpr int kHpThreads = 512;
+constexpr int kHpItems = 8;
+constexpr int kHpTile = kHpThreads * kHpItems;   // 4096 rows
+constexpr int kHpMaxBins = 512;
+constexpr int kHpSlots = 4096;                   // shared-memory table of the aggregation kernel
+constexpr int kHpKeysPerPart = 1536;             // target distinct keys per final partition (load 3/8)
+constexpr int kHpProbe = 48;
+constexpr uint32_t kHpNullBit = 0x80000000u;
+constexpr uint32_t kHpRowMask = 0x7FFFFFFFu;
+
+struct HpBufs {
+  uint64_t* keys;
+  uint64_t* vals;
+  uint32_t* rows;   // row inside the batch | value-is-null << 31
+};
+
+struct HpArgs {
+  HpBufs src;             // level 2 input (level 1 reads the columns)
+  HpBufs dst;
+  const uint32_t* base;   // level 2: [parts + 1] starts of the level-1 partitions inside src
+  int32_t parts;          // level 2: number of level-1 partitions (1 at level 1)
+  uint32_t* hist;         // [parts * bins]
+  uint32_t* cursor;       // [parts * bins] next free position in dst
+  int32_t shift;          // bin = (mix64(key) >> shift) & (bins - 1)
+  int32_t bins;
+  int32_t has_val;
+};
+
+__device__ __forceinline__ bool hp_row_live(const GbArgs& a, int64_t row) {
+  return !(a.select && !((a.select[row >> 5] >> (row & 31)) & 1u));
+}
+
+// partition whose range holds `pos` (base ascends; empty partitions are stepped over by the callers)
+__device__ __forceinline__ uint32_t hp_find_part(const uint32_t* base, uint32_t parts, uint32_t pos) {
+  uint32_t lo = 0, hi = parts;   // invariant: base[lo] <= pos < base[hi]
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (base[mid] <= pos) lo = mid;
+    else hi = mid;
+  }
+  return lo;
+}
+
+// LEVEL 1 reads the key columns, LEVEL 2 the level-1 output.  Both walk a flat list of 4096-row tiles; at level 2
+// a tile that straddles level-1 partitions is taken segment by segment, so a skewed partition is still spread over
+// the whole grid.
+template <int LEVEL>
+__global__ void __launch_bounds__(kHpThreads) gb_hp_hist_kernel(const __grid_constant__ GbArgs a, const __grid_constant__ HpArgs h) {
+  __shared__ uint32_t cnt[kHpMaxBins];
+  const int t = threadIdx.x;
+  const uint32_t mask = uint32_t(h.bins - 1);
+  const int64_t n = LEVEL == 2 ? int64_t(h.base[h.parts]) : a.n;
+  uint32_t held = 0xFFFFFFFFu;   // partition whose counts sit in shared memory
+  for (int64_t tile0 = int64_t(blockIdx.x) * kHpTile; tile0 < n; tile0 += int64_t(gridDim.x) * kHpTile) {
+    const int64_t tile1 = min(n, tile0 + kHpTile);
+    int64_t seg0 = tile0;
+    uint32_t p = LEVEL == 2 ? hp_find_part(h.base, uint32_t(h.parts), uint32_t(tile0)) : 0;
+    while (seg0 < tile1) {
+      const int64_t seg1 = LEVEL == 2 ? min(tile1, int64_t(h.base[p + 1])) : tile1;
+      if (seg1 > seg0) {
+        if (p != held) {
+          __syncthreads();
+          for (int i = t; i < h.bins; i += kHpThreads) {
+            if (held != 0xFFFFFFFFu) {
+              const uint32_t c = cnt[i];
+              if (c) atomicAdd(h.hist + size_t(held) * h.bins + i, c);
+            }
+            cnt[i] = 0;
+          }
+          held = p;
+          __syncthreads();
+        }
+#pragma unroll
+        for (int i = 0; i < kHpItems; ++i) {
+          const int64_t row = seg0 + i * kHpThreads + t;
+          if (row < seg1) {
+            if (LEVEL == 1) {
+              if (hp_row_live(a, row)) {
+                int special;
+                const uint64_t key = load_key(a, row, &special);
+                if (!special) atomicAdd(&cnt[uint32_t(mix64(key) >> h.shift) & mask], 1u);
+              }
+            } else {
+              atomicAdd(&cnt[uint32_t(mix64(h.src.keys[row]) >> h.shift) & mask], 1u);
+            }
+          }
+        }
+      }
+      seg0 = seg1;
+      ++p;
+    }
+  }
+  __syncthreads();
+  if (held != 0xFFFFFFFFu) {
+    for (int i = t; i < h.bins; i += kHpThreads) {
+      const uint32_t c = cnt[i];
+      if (c) atomicAdd(h.hist + size_t(held) * h.bins + i, c);
+    }
+  }
+}
+
+// exclusive scan of `count` words (one CTA): starts -> cursor[i] and base[i]; base[count] = total
+__global__ void __launch_bounds__(1024) gb_hp_scan_kernel(const uint32_t* hist, uint32_t count, uint32_t* cursor, uint32_t* base) {
+  __shared__ uint32_t warp_sums[32];
+  __shared__ uint32_t carry_s;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  if (t == 0) carry_s = 0;
+  __syncthreads();
+  for (uint32_t b0 = 0; b0 < count; b0 += 1024) {
+    const uint32_t i = b0 + t;
+    const uint32_t c = i < count ? hist[i] : 0;
+    uint32_t incl = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    uint32_t wpre = 0;
+    for (int w = 0; w < warp; ++w) wpre += warp_sums[w];
+    const uint32_t carry = carry_s;
+    if (i < count) {
+      if (cursor) cursor[i] = carry + wpre + incl - c;
+      base[i] = carry + wpre + incl - c;
+    }
+    __syncthreads();
+    if (t == 1023) carry_s = carry + wpre + incl;
+    __syncthreads();
+  }
+  if (t == 0) base[count] = carry_s;
+}
+
+struct HpPartSmem {
+  uint64_t keys[kHpTile];
+  uint64_t vals[kHpTile];
+  uint32_t rows[kHpTile];
+  uint16_t bin[kHpTile];
+  uint32_t cnt[kHpMaxBins];
+  uint32_t off[kHpMaxBins];
+  uint32_t gbase[kHpMaxBins];
+  uint32_t warp_sums[kHpThreads / 32];
+  uint32_t deferred;
+};
+
+template <int LEVEL>
+__global__ void __launch_bounds__(kHpThreads, 2) gb_hp_part_kernel(const __grid_constant__ GbArgs a, const __grid_constant__ HpArgs h) {
+  extern __shared__ __align__(16) unsigned char hp_smem_raw[];
+  HpPartSmem& S = *reinterpret_cast<HpPartSmem*>(hp_smem_raw);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const uint32_t mask = uint32_t(h.bins - 1);
+  const int64_t n = LEVEL == 2 ? int64_t(h.base[h.parts]) : a.n;
+  if (t == 0) S.deferred = 0;
+  for (int64_t tile0 = int64_t(blockIdx.x) * kHpTile; tile0 < n; tile0 += int64_t(gridDim.x) * kHpTile) {
+    const int64_t tile1 = min(n, tile0 + kHpTile);
+    int64_t seg0 = tile0;
+    uint32_t p = LEVEL == 2 ? hp_find_part(h.base, uint32_t(h.parts), uint32_t(tile0)) : 0;
+    while (seg0 < tile1) {
+      const int64_t seg1 = LEVEL == 2 ? min(tile1, int64_t(h.base[p + 1])) : tile1;
+      if (seg1 > seg0) {
+        uint32_t* cursor = h.cursor + size_t(p) * h.bins;
+        __syncthreads();   // the previous segment's stores have read S
+        for (int i = t; i < h.bins; i += kHpThreads) S.cnt[i] = 0;
+        __syncthreads();
+        // ---- load, bin, rank inside the tile's bin (native ATOMS.ADD with return)
+        uint64_t key[kHpItems], val[kHpItems];
+        uint32_t r32[kHpItems], meta[kHpItems];   // meta = bin | rank << 16, 0xFFFFFFFF = not staged
+#pragma unroll
+        for (int i = 0; i < kHpItems; ++i) {
+          const int64_t row = seg0 + i * kHpThreads + t;
+          meta[i] = 0xFFFFFFFFu;
+          key[i] = 0;
+          val[i] = 0;
+          r32[i] = 0;
+          if (row < seg1) {
+            if (LEVEL == 1) {
+              if (hp_row_live(a, row)) {
+                int special;
+                key[i] = load_key(a, row, &special);
+                if (special) {   // the null key / the key equal to the EMPTY sentinel: left to the generic kernel
+                  atomicOr(a.defer_out + (row >> 5), 1u << (row & 31));
+                  atomicAdd(&S.deferred, 1u);
+                } else {
+                  r32[i] = uint32_t(row);
+                  if (h.has_val) {
+                    const Val v = load_val(a.cols[0], row);
+                    val[i] = v.bits;
+                    if (!v.valid) r32[i] |= kHpNullBit;
+                  }
+                  meta[i] = uint32_t(mix64(key[i]) >> h.shift) & mask;
+                }
+              }
+            } else {
+              key[i] = h.src.keys[row];
+              if (h.has_val) val[i] = h.src.vals[row];
+              r32[i] = h.src.rows[row];
+              meta[i] = uint32_t(mix64(key[i]) >> h.shift) & mask;
+            }
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < kHpItems; ++i)
+          if (meta[i] != 0xFFFFFFFFu) meta[i] |= atomicAdd(&S.cnt[meta[i]], 1u) << 16;
+        __syncthreads();
+        // ---- claim every bin's run in the destination; exclusive scan of the tile's counts
+        {
+          const uint32_t c = t < h.bins ? S.cnt[t] : 0;
+          if (t < h.bins) S.gbase[t] = c ? atomicAdd(cursor + t, c) : 0;
+          uint32_t incl = c;
+#pragma unroll
+          for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += o;
+          }
+          if (lane == 31) S.warp_sums[warp] = incl;
+          __syncthreads();
+          uint32_t wpre = 0;
+#pragma unroll
+          for (int w = 0; w < kHpThreads / 32; ++w)
+            if (w < warp) wpre += S.warp_sums[w];
+          if (t < h.bins) S.off[t] = wpre + incl - c;
+        }
+        __syncthreads();
+        const uint32_t staged = S.off[h.bins - 1] + S.cnt[h.bins - 1];
+        // ---- group the tile by bin in shared memory
+#pragma unroll
+        for (int i = 0; i < kHpItems; ++i) {
+          if (meta[i] != 0xFFFFFFFFu) {
+            const uint32_t b = meta[i] & 0xFFFFu;
+            const uint32_t pos = S.off[b] + (meta[i] >> 16);
+            S.keys[pos] = key[i];
+            S.vals[pos] = val[i];
+            S.rows[pos] = r32[i];
+            S.bin[pos] = uint16_t(b);
+          }
+        }
+        __syncthreads();
+        // ---- bin-contiguous stores
+        for (uint32_t j = t; j < staged; j += kHpThreads) {
+          const uint32_t b = S.bin[j];
+          const uint32_t g = S.gbase[b] + (j - S.off[b]);
+          h.dst.keys[g] = S.keys[j];
+          if (h.has_val) h.dst.vals[g] = S.vals[j];
+          h.dst.rows[g] = S.rows[j];
+        }
+      }
+      seg0 = seg1;
+      ++p;
+    }
+  }
+  if (LEVEL == 1) {
+    __syncthreads();
+    if (t == 0 && S.deferred) atomicAdd(a.counters + 1, S.deferred);
+  }
+}
+
+struct HpAggSmem {
+  uint64_t key[kHpSlots];
+  uint64_t sum[kHpSlots];
+  uint32_t cnt_valid[kHpSlots];
+  uint32_t cnt_null[kHpSlots];
+  uint32_t row[kHpSlots];
+  uint32_t warp_sums[kHpThreads / 32];
+  uint32_t part;
+  uint32_t image_base;
+  uint32_t deferred;
+};
+
+// sum += v on a 64-bit integer accumulator in shared memory with native 32-bit atomics: the carry out of the low
+// word is known to the thread whose add produced it
+__device__ __forceinline__ void hp_add_u64(uint64_t* acc, uint64_t v) {
+  uint32_t* w = reinterpret_cast<uint32_t*>(acc);
+  const uint32_t lo = uint32_t(v);
+  const uint32_t old = atomicAdd(w, lo);
+  const uint32_t hi = uint32_t(v >> 32) + (old + lo < old ? 1u : 0u);
+  if (hi) atomicAdd(w + 1, hi);
+}
+
+// work items of the aggregation kernel: a partition of more than seg_rows rows (a hot key) is cut into segments that
+// different CTAs aggregate; the import folds their images together
+__global__ void gb_hp_items_kernel(const uint32_t* base, uint32_t n_parts, uint32_t seg_rows, uint32_t* items) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_parts) items[i] = (base[i + 1] - base[i] + seg_rows - 1) / seg_rows;
+}
+
+// kFloatSum: the value column sums as float64 (ATOMS.CAS.64 loop), else as a wrapping 64-bit integer
+template <bool kFloatSum>
+__global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_constant__ GbArgs a, const HpBufs src, const uint32_t* base,
+                                                                  const uint32_t* item_base, const uint32_t n_parts,
+                                                                  const uint32_t seg_rows, char* images, const uint32_t image_cap,
+                                                                  uint32_t* ticket) {
+  extern __shared__ __align__(16) unsigned char hp_smem_raw[];
+  HpAggSmem& S = *reinterpret_cast<HpAggSmem*>(hp_smem_raw);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int words = a.s.stride / 8;
+  if (t == 0) S.deferred = 0;
+  if (t == 0 && blockIdx.x == 0) a.counters[7] = item_base[n_parts];   // the host wants to know if a partition was cut
+  for (;;) {
+    __syncthreads();
+    if (t == 0) S.part = atomicAdd(ticket, 1u);
+    for (int i = t; i < kHpSlots; i += kHpThreads) {
+      S.key[i] = kEmpty;
+      S.sum[i] = 0;
+      S.cnt_valid[i] = 0;
+      S.cnt_null[i] = 0;
+      S.row[i] = 0xFFFFFFFFu;
+    }
+    __syncthreads();
+    const uint32_t item = S.part;
+    if (item >= item_base[n_parts]) break;
+    const uint32_t p = hp_find_part(item_base, n_parts, item);
+    const uint32_t begin = base[p] + (item - item_base[p]) * seg_rows;
+    const uint32_t end = min(base[p + 1], begin + seg_rows);
+    constexpr int kU = 4;   // rows per thread in flight: their loads are issued together
+    for (uint32_t i0 = begin; i0 < end; i0 += kHpThreads * kU) {
+      uint64_t key[kU], v[kU];
+      uint32_t r32[kU];
+      bool in[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const uint32_t i = i0 + u * kHpThreads + t;
+        in[u] = i < end;
+        key[u] = in[u] ? src.keys[i] : 0;
+        r32[u] = in[u] ? src.rows[i] : 0;
+        v[u] = (in[u] && a.n_cols) ? src.vals[i] : 0;
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        __syncwarp();
+        if (!in[u]) continue;
+        uint32_t slot = uint32_t(mix64(key[u]) >> 50) & uint32_t(kHpSlots - 1);
+        bool found = false;
+        for (int probe = 0; probe < kHpProbe; ++probe) {
+          uint64_t cur = *reinterpret_cast<volatile uint64_t*>(&S.key[slot]);
+          if (cur == kEmpty) cur = atomicCAS(reinterpret_cast<unsigned long long*>(&S.key[slot]), (unsigned long long)kEmpty, (unsigned long long)key[u]);
+          if (cur == kEmpty || cur == key[u]) {
+            found = true;
+            break;
+          }
+          slot = (slot + 1) & uint32_t(kHpSlots - 1);
+        }
+        const uint32_t row = r32[u] & kHpRowMask;
+        if (!found) {   // more distinct keys than the shared table takes: the generic kernel aggregates this row
+          atomicOr(a.defer_out + (row >> 5), 1u << (row & 31));
+          atomicAdd(&S.deferred, 1u);
+          continue;
+        }
+        atomicMin(&S.row[slot], row);
+        if (r32[u] & kHpNullBit) {
+          atomicAdd(&S.cnt_null[slot], 1u);
+        } else {
+          atomicAdd(&S.cnt_valid[slot], 1u);
+          if (a.n_cols) {
+            if (kFloatSum) atomicAdd(reinterpret_cast<double*>(&S.sum[slot]), __longlong_as_double(v[u]));
+            else hp_add_u64(&S.sum[slot], v[u]);
+          }
+        }
+      }
+    }
+    __syncthreads();
+    // ---- the partition's groups leave as slot images: count, reserve, write
+    constexpr int kPer = kHpSlots / kHpThreads;   // consecutive slots per thread
+    uint32_t mine = 0;
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) mine += S.key[t * kPer + k] != kEmpty;
+    uint32_t incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    if (lane == 31) S.warp_sums[warp] = incl;
+    __syncthreads();
+    uint32_t wpre = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kHpThreads / 32; ++w) {
+      const uint32_t ws = S.warp_sums[w];
+      if (w < warp) wpre += ws;
+      total += ws;
+    }
+    if (t == 0) {
+      // all or nothing: a hole in the image list would be imported as a group
+      uint32_t old = *reinterpret_cast<volatile uint32_t*>(a.counters + 6);
+      uint32_t got = 0xFFFFFFFFu;
+      while (total && uint64_t(old) + total <= image_cap) {
+        const uint32_t prev = atomicCAS(a.counters + 6, old, old + total);
+        if (prev == old) {
+          got = old;
+          break;
+        }
+        old = prev;
+      }
+      S.image_base = total ? got : 0;
+    }
+    __syncthreads();
+    const uint32_t ibase = S.image_base;
+    if (ibase == 0xFFFFFFFFu) {
+      // no room for this partition's images: its rows go to the generic kernel
+      for (uint32_t i = begin + t; i < end; i += kHpThreads) {
+        const uint32_t row = src.rows[i] & kHpRowMask;
+        atomicOr(a.defer_out + (row >> 5), 1u << (row & 31));
+      }
+      if (t == 0) S.deferred += end - begin;
+      continue;
+    }
+    uint32_t pos = ibase + wpre + incl - mine;
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const int s = t * kPer + k;
+      const uint64_t key = S.key[s];
+      if (key == kEmpty) continue;
+      uint64_t* img = reinterpret_cast<uint64_t*>(images + size_t(pos) * a.s.stride);
+      ++pos;
+      const uint32_t row = S.row[s];
+      img[0] = key;
+      img[1] = a.row_ids ? a.row_ids[row] : a.row_base + uint64_t(row);
+      for (int w = 2; w < words; ++w) img[w] = 0;
+      for (int j = 0; j < a.s.n_aggs; ++j) {
+        const GbAgg& g = a.s.aggs[j];
+        uint64_t* st = img + g.off / 8;
+        if (g.kind == B200_HASH_COUNT) {
+          st[0] = g.option ? S.cnt_null[s] : S.cnt_valid[s];
+        } else {   // SUM / MEAN
+          st[0] = S.sum[s];
+          st[1] = S.cnt_valid[s];
+        }
+      }
+    }
+  }
+  if (t == 0 && S.deferred) atomicAdd(a.counters + 1, S.deferred);
+}
+
+// slot images -> global table (gb_import_kernel with the new-group count folded per CTA: at 10^8 groups one global
+// counter bumped per group would serialise in L2)
+__global__ void __launch_bounds__(256) gb_hp_import_kernel(const __grid_constant__ GbSchema s, const char* src, uint32_t n, GbTable dst,
+                                                           uint32_t* counters) {
+  __shared__ uint32_t s_new;
+  if (threadIdx.x == 0) s_new = 0;
+  __syncthreads();
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const char* ss = src + uint64_t(i) * s.stride;
+    bool claimed;
+    uint64_t slot_index;
+    char* ds = global_slot(dst, s.stride, *reinterpret_cast<const uint64_t*>(ss), 0, true, &claimed, &slot_index);
+    if (!ds) {
+      atomicExch(counters + 3, 4u);
+    } else {
+      if (claimed) atomicAdd(&s_new, 1u);
+      merge_state(ds, ss, s);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0 && s_new) atomicAdd(counters + 0, s_new);
+}
+
+__global__ void gb_hp_monotone_kernel(const uint64_t* row_ids, int64_t n, uint32_t* flag) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i > 0 && i < n && row_ids[i] <= row_ids[i - 1]) *flag = 1u;
+}

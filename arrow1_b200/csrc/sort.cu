@@ -28,7 +28,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
-
+#include <type_traits>
 #include <vector>
 #include "common.cuh"
 
@@ -63,7 +63,9 @@ struct PassInfo {
   int32_t skip;
   int32_t first;
   int32_t last;
-  int32_t src;  // ping-pong buffer read by this pass (ignored when first)
+  int32_t src;         // ping-pong buffer read by this pass (ignored when first)
+  int32_t out_narrow;  // the pass writes 32-bit keys: only the word the remaining passes still look at
+  int32_t pad[3];
 };
 
 struct SortParams {
@@ -87,6 +89,7 @@ struct SortParams {
   const uint32_t* pay_in;  // optional (with keys_in): 32-bit payload carried through the passes instead of the row number
   uint64_t* out_idx;
   uint64_t* out_keys;      // optional
+  int32_t narrow;          // passes that only look at one 32-bit word of the key carry that word alone
   uint32_t* hist;          // [8][kBinStride] counts, then exclusive bases
   PassInfo* info;          // [8]
   uint32_t* counters;      // [8] tile tickets
@@ -208,6 +211,16 @@ __global__ void __launch_bounds__(kHistThreads) sort_scan_kernel(SortParams p) {
       pi.first = (i == first);
       pi.last = (i == last);
       pi.src = src;
+      // 32-bit keys from the point where every pass still to run looks at the same word: the upper word of a
+      // 64-bit key after the last live pass over digits 0..3, the only word of a <= 32-bit column from the start
+      int next = -1;
+      for (int j = i + 1; j < kDigits; ++j)
+        if (!skip_s[j]) {
+          next = j;
+          break;
+        }
+      pi.out_narrow = p.narrow && next >= 0 && (next >= 4 || p.n_digits <= 4);
+      pi.pad[0] = pi.pad[1] = pi.pad[2] = 0;
       p.info[i] = pi;
       // the first pass writes buffer 0; every later executed pass flips
       if (!pi.skip) src = pi.first ? 0 : (src ^ 1);
@@ -230,6 +243,8 @@ __device__ __forceinline__ uint32_t key_digit(uint64_t key, int d) {
   return __byte_perm(w, 0u, 0x4440u | uint32_t(d & 3));
 }
 
+__device__ __forceinline__ uint32_t key_digit(uint32_t key, int d) { return __byte_perm(key, 0u, 0x4440u | uint32_t(d & 3)); }
+
 // m &= lanes whose bit `b` of `bin` equals this lane's: predicate, ballot, conditional complement, and
 __device__ __forceinline__ unsigned match_bit(unsigned m, uint32_t bin, uint32_t bitmask) {
   unsigned r;
@@ -248,8 +263,9 @@ __device__ __forceinline__ unsigned match_bit(unsigned m, uint32_t bin, uint32_t
   return r;
 }
 
+template <typename KeyT>
 struct PassSmem {
-  uint64_t keys[kTile];
+  KeyT keys[kTile];
   uint32_t pay[kTile];
   uint32_t whist[kWarps][kBinStride];
   uint32_t tile_count[kBinStride];
@@ -260,72 +276,85 @@ struct PassSmem {
 };
 
 // kClass: this pass carries the NaN / null bins (NBINS = 258).  kFull: the tile has 4096 rows.
-template <bool kClass, bool kFull>
-__device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d, const PassInfo info, PassSmem& s,
+// kNarrow: the pass looks at one 32-bit word of the key only (digits 4..7 of a 64-bit key, or any digit of a
+// <= 32-bit column) and holds, stages and writes that word alone: 8 B per row and pass instead of 12.
+template <bool kClass, bool kFull, bool kNarrow>
+__device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d, const PassInfo info,
+                                               PassSmem<typename std::conditional<kNarrow, uint32_t, uint64_t>::type>& s,
                                                const int64_t tile, const int tile_items) {
+  using KeyT = typename std::conditional<kNarrow, uint32_t, uint64_t>::type;
   constexpr int NBINS = kClass ? 258 : 256;
+  const int word_shift = (kNarrow && d >= 4) ? 32 : 0;                    // which word a narrow key is
+  const KeyT all_ones = KeyT(p.wmask >> word_shift);                       // NaN / null key in this pass's width
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const unsigned lt = lanemask_lt();
   const int64_t tile_row0 = tile * kTile;
-  const uint64_t* keys_src = p.keys[info.src];
+  const KeyT* keys_src = reinterpret_cast<const KeyT*>(p.keys[info.src]);
   const uint32_t* pays_src = p.pays[info.src];
   uint32_t* state = p.state + (size_t(d) * p.n_tiles + tile) * kBinStride;
   const int wbase = warp * (kItems * 32) + lane;  // item i sits at local index wbase + 32*i
   const int shift = 8 * d;
 
   // ---- load: all global loads are issued back to back, transforms follow
-  uint64_t key[kItems];
+  KeyT key[kItems];
   uint64_t cls_bits = 0;  // 2 bits per item: 1 NaN, 2 null (only in the class pass)
   if (info.first && !p.keys_in) {
     uint32_t vword = 0xffffffffu;  // validity word of step `lane` (lanes 0..15)
     if (p.vv.words && lane < kItems) vword = bitmap_load32(p.vv, tile_row0 + warp * (kItems * 32) + lane * 32, p.n);
     const char* src = reinterpret_cast<const char*>(p.vdata);
+    uint64_t raw[kItems];
     switch (p.width) {
       case 1:
 #pragma unroll
         for (int i = 0; i < kItems; ++i)
-          key[i] = (kFull || wbase + 32 * i < tile_items) ? reinterpret_cast<const uint8_t*>(src)[tile_row0 + wbase + 32 * i] : 0;
+          raw[i] = (kFull || wbase + 32 * i < tile_items) ? reinterpret_cast<const uint8_t*>(src)[tile_row0 + wbase + 32 * i] : 0;
         break;
       case 2:
 #pragma unroll
         for (int i = 0; i < kItems; ++i)
-          key[i] = (kFull || wbase + 32 * i < tile_items) ? reinterpret_cast<const uint16_t*>(src)[tile_row0 + wbase + 32 * i] : 0;
+          raw[i] = (kFull || wbase + 32 * i < tile_items) ? reinterpret_cast<const uint16_t*>(src)[tile_row0 + wbase + 32 * i] : 0;
         break;
       case 4:
 #pragma unroll
         for (int i = 0; i < kItems; ++i)
-          key[i] = (kFull || wbase + 32 * i < tile_items) ? reinterpret_cast<const uint32_t*>(src)[tile_row0 + wbase + 32 * i] : 0;
+          raw[i] = (kFull || wbase + 32 * i < tile_items) ? reinterpret_cast<const uint32_t*>(src)[tile_row0 + wbase + 32 * i] : 0;
         break;
       default:
 #pragma unroll
         for (int i = 0; i < kItems; ++i)
-          key[i] = (kFull || wbase + 32 * i < tile_items) ? reinterpret_cast<const uint64_t*>(src)[tile_row0 + wbase + 32 * i] : 0;
+          raw[i] = (kFull || wbase + 32 * i < tile_items) ? reinterpret_cast<const uint64_t*>(src)[tile_row0 + wbase + 32 * i] : 0;
         break;
     }
 #pragma unroll
     for (int i = 0; i < kItems; ++i) {
       const uint32_t vw = __shfl_sync(0xffffffffu, vword, i);
       uint32_t cls;
-      uint64_t k = transform_key(p, key[i], &cls);
+      uint64_t k = transform_key(p, raw[i], &cls);
       if (!((vw >> lane) & 1u)) {
         cls = 2;
         k = p.wmask;
       }
-      key[i] = k;
+      key[i] = KeyT(k >> word_shift);
       if (kClass) cls_bits |= uint64_t(cls) << (2 * i);
     }
   } else {
-    const uint64_t* src = info.first ? p.keys_in : keys_src;
+    if (info.first) {   // ready-made 64-bit keys
 #pragma unroll
-    for (int i = 0; i < kItems; ++i) key[i] = (kFull || wbase + 32 * i < tile_items) ? src[tile_row0 + wbase + 32 * i] : 0;
+      for (int i = 0; i < kItems; ++i)
+        key[i] = (kFull || wbase + 32 * i < tile_items) ? KeyT(p.keys_in[tile_row0 + wbase + 32 * i] >> word_shift) : KeyT(0);
+    } else {
+#pragma unroll
+      for (int i = 0; i < kItems; ++i) key[i] = (kFull || wbase + 32 * i < tile_items) ? keys_src[tile_row0 + wbase + 32 * i] : KeyT(0);
+    }
     if (kClass) {
-      // candidates have digit 255; the row's validity bit / the all-ones float key decide
+      // candidates have digit 255; the row's validity bit / the all-ones float key decide (a float key whose
+      // upper word is all ones is a NaN's: no number maps there, see transform_key)
 #pragma unroll
       for (int i = 0; i < kItems; ++i) {
-        if ((kFull || wbase + 32 * i < tile_items) && (uint32_t(key[i] >> shift) & 255u) == 255u) {
+        if ((kFull || wbase + 32 * i < tile_items) && key_digit(key[i], d) == 255u) {
           uint32_t cls = 0;
           if (p.vv.words && !bitmap_get(p.vv, pays_src[tile_row0 + wbase + 32 * i])) cls = 2;
-          else if (p.tkind == kFloatKey && key[i] == p.wmask) cls = 1;
+          else if (p.tkind == kFloatKey && key[i] == all_ones) cls = 1;
           cls_bits |= uint64_t(cls) << (2 * i);
         }
       }
@@ -513,12 +542,13 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
 
   // ---- digit-contiguous global stores
   uint64_t* keys_dst = p.keys[info.first ? 0 : (info.src ^ 1)];
+  uint32_t* keys32_dst = reinterpret_cast<uint32_t*>(keys_dst);
   uint32_t* pays_dst = p.pays[info.first ? 0 : (info.src ^ 1)];
 #pragma unroll 8
   for (int k = 0; k < kItems; ++k) {
     const int j = k * kThreads + t;
     if (kFull || j < tile_items) {
-      const uint64_t kk = s.keys[j];
+      const KeyT kk = s.keys[j];
       uint32_t pv = s.pay[j];
       uint32_t bin = key_digit(kk, d);
       if (kClass) {
@@ -529,29 +559,32 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
       const uint32_t pos = uint32_t(j) + s.bin_delta[bin];
       if (info.last) {
         p.out_idx[pos] = p.gather ? p.gather[pv] : (uint64_t(pv) + p.index_base);
-        if (p.out_keys) p.out_keys[pos] = kk;
+        if (!kNarrow && p.out_keys) p.out_keys[pos] = kk;
       } else {
-        keys_dst[pos] = kk;
+        if (kNarrow) keys32_dst[pos] = uint32_t(kk);
+        else if (info.out_narrow) keys32_dst[pos] = uint32_t(uint64_t(kk) >> (p.n_digits <= 4 ? 0 : 32));
+        else keys_dst[pos] = kk;
         pays_dst[pos] = pv;
       }
     }
   }
 }
 
-template <bool kClass>
-__global__ void __launch_bounds__(kThreads, kMinBlocks) sort_pass_kernel(SortParams p, int d) {
+template <bool kClass, bool kNarrow>
+__global__ void __launch_bounds__(kThreads, kNarrow ? kMinBlocks + 1 : kMinBlocks) sort_pass_kernel(SortParams p, int d) {
   const PassInfo info = p.info[d];
   if (info.skip) return;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  PassSmem& s = *reinterpret_cast<PassSmem*>(smem_raw);
+  using Smem = PassSmem<typename std::conditional<kNarrow, uint32_t, uint64_t>::type>;
+  Smem& s = *reinterpret_cast<Smem*>(smem_raw);
   const int t = threadIdx.x;
   if (t == 0) s.tile = atomicAdd(p.counters + d, 1u);
   for (int i = t; i < kWarps * kBinStride / 4; i += kThreads) reinterpret_cast<uint4*>(&s.whist[0][0])[i] = make_uint4(0, 0, 0, 0);
   __syncthreads();
   const int64_t tile = s.tile;
   const int tile_items = int(min(int64_t(kTile), p.n - tile * kTile));
-  if (tile_items == kTile) sort_pass_body<kClass, true>(p, d, info, s, tile, tile_items);
-  else sort_pass_body<kClass, false>(p, d, info, s, tile, tile_items);
+  if (tile_items == kTile) sort_pass_body<kClass, true, kNarrow>(p, d, info, s, tile, tile_items);
+  else sort_pass_body<kClass, false, kNarrow>(p, d, info, s, tile, tile_items);
 }
 
 __global__ void sort_keys_kernel(SortParams p, uint64_t* out, uint64_t* out_rows) {
@@ -917,20 +950,30 @@ int run_sort(b200_ctx* ctx, SortParams p, void* scratch, size_t scratch_bytes) {
   B200_CUDA(ctx, cudaMemsetAsync(base, 0, std::min(zero_bytes, L.zero_bytes), ctx->stream));
   const int hist_blocks = int(std::min<int64_t>((p.n + kHistTile - 1) / kHistTile, int64_t(ctx->num_sms) * 8));
   static bool attr_set = false;
-  const int smem = int(sizeof(PassSmem));
+  const int smem_wide = int(sizeof(PassSmem<uint64_t>)), smem_narrow = int(sizeof(PassSmem<uint32_t>));
   if (!attr_set) {
-    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_wide));
+    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_wide));
+    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_narrow));
+    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_narrow));
     attr_set = true;
   }
+  // the caller wants the sorted 64-bit keys back: every pass carries them whole
+  p.narrow = p.out_keys ? 0 : 1;
   B200_TIMED(ctx, "sort_hist", (sort_hist_kernel<<<hist_blocks, kHistThreads, 0, ctx->stream>>>(p)));
   sort_scan_kernel<<<1, kHistThreads, 0, ctx->stream>>>(p);
   B200_LAUNCHED(ctx);
   for (int d = 0; d < p.n_digits; ++d) {
-    if (d == p.cls_digit)
-      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<true><<<(unsigned)p.n_tiles, kThreads, smem, ctx->stream>>>(p, d)));
+    const bool narrow = p.narrow && (d >= 4 || p.n_digits <= 4);
+    const unsigned grid = unsigned(p.n_tiles);
+    if (d == p.cls_digit && narrow)
+      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<true, true><<<grid, kThreads, smem_narrow, ctx->stream>>>(p, d)));
+    else if (d == p.cls_digit)
+      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<true, false><<<grid, kThreads, smem_wide, ctx->stream>>>(p, d)));
+    else if (narrow)
+      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<false, true><<<grid, kThreads, smem_narrow, ctx->stream>>>(p, d)));
     else
-      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<false><<<(unsigned)p.n_tiles, kThreads, smem, ctx->stream>>>(p, d)));
+      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<false, false><<<grid, kThreads, smem_wide, ctx->stream>>>(p, d)));
   }
   return B200_OK;
 }

@@ -563,7 +563,8 @@ def kernel_times(ctx, names):
     return out
 
 
-ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume", "compare_scalar", "arithmetic", "take", "partition_plan", "partition_scatter", "sort_partition")
+ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume", "compare_scalar", "arithmetic", "take", "partition_plan", "partition_scatter", "sort_partition",
+               "groupby_partition", "groupby_import")
 
 
 def time_device(ctx, wl, cols_, steps, warmup, world, dist_step=None):

@@ -323,6 +323,11 @@ B200_API int b200_groupby_create(b200_ctx* ctx, int n_keys, const int32_t* key_t
                                  const b200_agg_spec* aggs, int64_t expected_groups,
                                  b200_groupby** out);
 B200_API int b200_groupby_destroy(b200_groupby* gb);
+/* Execution knobs of a handle (no reference counterpart; results never depend on them).  Names:
+ *   "hp_min_rows" / "hp_min_groups"   batch size and expected cardinality from which a consume call takes the
+ *                                     partition-then-aggregate path (defaults 2^22 rows, 2^21 groups)
+ * B200_KEY_ERROR for an unknown name. */
+B200_API int b200_groupby_set_option(b200_groupby* gb, const char* name, int64_t value);
 /* == one iteration of GroupBy's batch loop (hash_aggregate.cc:928-943): Grouper::Consume
  * (:358-408) fused with every aggregate's Consume.  args[i] feeds aggs[i].  row_base is the
  * global index of the batch's first row: group order is first-occurrence order of

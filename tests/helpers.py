@@ -56,7 +56,7 @@ class GroupRes:
         self.num_groups, self.aggs, self.keys, self.ids = num_groups, aggs, keys, ids
 
 
-def run_groupby(impl, keys, aggs, args, ctx=None, want_ids=False, expected_groups=0) -> GroupRes:
+def run_groupby(impl, keys, aggs, args, ctx=None, want_ids=False, expected_groups=0, options=None) -> GroupRes:
     if impl in ("port", "reference"):
         r = oracle.groupby(keys, aggs, args, want_ids=want_ids, kind=impl)
         return GroupRes(r.num_groups, r.aggs, r.keys, r.ids)
@@ -67,7 +67,7 @@ def run_groupby(impl, keys, aggs, args, ctx=None, want_ids=False, expected_group
             dev[id(c)] = c.to_device()
     dkeys = [dev[id(k)] for k in keys]
     dargs = [dev[id(a)] for a in args]
-    out = capi.group_by(ctx, dkeys, aggs, dargs, expected_groups=expected_groups)
+    out = capi.group_by(ctx, dkeys, aggs, dargs, expected_groups=expected_groups, options=options)
     res_aggs = [[(c.to_host().values().copy(), c.to_host().valid()) for c in a] for a in out.aggs]
     res_keys = [(c.to_host().values().copy(), c.to_host().valid()) for c in out.keys]
     ids = None

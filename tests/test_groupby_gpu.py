@@ -308,3 +308,133 @@ def test_groupby_tiny_byte_keys_register_accumulators(ctx, n_keys, dt):
     a2 = run_groupby("gpu", kcols, aggs[:2], [arg2] * 2, ctx, expected_groups=6)
     b2 = run_groupby(ORACLE, kcols, aggs[:2], [arg2] * 2)
     assert_group_equal(a2, b2, aggs[:2], rtol=RTOL)
+
+
+# ---- high-cardinality path (partition, then aggregate in shared memory): forced at test sizes through the
+# handle's options; the results must not depend on the path
+HP = {"hp_min_rows": 0, "hp_min_groups": 0}
+HP_AGGS = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT), AggSpec(cols.HASH_COUNT, 1), AggSpec(cols.HASH_MEAN)]
+
+
+@pytest.mark.parametrize("kt", [cols.UINT8, cols.INT32, cols.INT64, cols.UINT64, cols.DOUBLE])
+@pytest.mark.parametrize("at", [cols.INT8, cols.INT32, cols.UINT64, cols.INT64, cols.FLOAT, cols.DOUBLE])
+def test_groupby_partitioned_path_random(ctx, kt, at):
+    rng = np.random.default_rng(900 + 31 * kt + at)
+    for n, hi, hint in ((1, 100, 50), (5000, 100, 100), (300_000, 1 << 40, 300_000), (300_000, 40_000, 2_000_000)):
+        for null_prob in (0.0, 0.3):
+            top = hi if kt == cols.DOUBLE else min(hi, int(np.iinfo(cols.NP_OF[kt]).max))
+            key = rand_column(rng, kt, n, 0.05, lo=0, hi=top, special=(kt == cols.DOUBLE))
+            arg = rand_column(rng, at, n, null_prob, special=True)
+            args = [arg] * len(HP_AGGS)
+            a = run_groupby("gpu", [key], HP_AGGS, args, ctx, expected_groups=hint, options=HP)
+            b = run_groupby(ORACLE, [key], HP_AGGS, args)
+            assert_group_equal(a, b, HP_AGGS, rtol=RTOL, scales=abs_sum_scales([key], HP_AGGS, args))
+
+
+def test_groupby_partitioned_path_is_taken(ctx):
+    """The options do route the call through the partition kernels (launch count of the context goes up by the
+    partition / aggregate / import launches), and int64 sums wrap exactly like the reference's."""
+    from arrow1_b200 import capi
+    rng = np.random.default_rng(5)
+    n = 200_000
+    key = Column.from_numpy(rng.integers(0, 1 << 62, size=n, dtype=np.int64) % 50_000)
+    arg = Column.from_numpy(rng.integers(-2**63, 2**63 - 1, size=n, dtype=np.int64), rng.random(n) > 0.1)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MEAN), AggSpec(cols.HASH_COUNT)]
+    capi.lib().b200_ctx_set_kernel_timing(ctx._h, 1)
+    a = run_groupby("gpu", [key], aggs, [arg] * 3, ctx, expected_groups=50_000, options=HP)
+    import ctypes as C
+    ms, cnt = C.c_double(0), C.c_int64(0)
+    capi.lib().b200_ctx_kernel_time(ctx._h, b"groupby_partition", C.byref(ms), C.byref(cnt))
+    capi.lib().b200_ctx_set_kernel_timing(ctx._h, 0)
+    assert cnt.value >= 2, "partition kernels did not run"
+    b = run_groupby(ORACLE, [key], aggs, [arg] * 3)
+    assert_group_equal(a, b, aggs, rtol=RTOL)
+
+
+def test_groupby_partitioned_path_multi_key_and_no_aggs(ctx):
+    rng = np.random.default_rng(12)
+    n = 120_000
+    k0 = rand_column(rng, cols.UINT8, n, 0.1, lo=0, hi=200)
+    k1 = rand_column(rng, cols.INT16, n, 0.1, lo=-300, hi=300)
+    k2 = rand_column(rng, cols.BOOL, n, 0.1)
+    arg = rand_column(rng, cols.DOUBLE, n, 0.2)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT)]
+    a = run_groupby("gpu", [k0, k1, k2], aggs, [arg] * 2, ctx, expected_groups=100_000, options=HP)
+    b = run_groupby(ORACLE, [k0, k1, k2], aggs, [arg] * 2)
+    assert_group_equal(a, b, aggs, rtol=RTOL)
+    a = run_groupby("gpu", [k0, k1], [], [], ctx, expected_groups=100_000, options=HP)
+    b = run_groupby(ORACLE, [k0, k1], [], [])
+    assert_group_equal(a, b, [], rtol=RTOL)
+
+
+def test_groupby_partitioned_path_special_keys_and_skew(ctx):
+    """Null / all-ones 64-bit keys (special slots) are deferred to the generic kernel; a key that holds half of the
+    rows makes one partition far larger than the others (cut into several work items); a hint far below the real
+    cardinality overflows the shared tables (rows deferred) and the image list."""
+    rng = np.random.default_rng(13)
+    n = 400_000
+    v = rng.integers(0, 1 << 50, size=n, dtype=np.int64)
+    v[rng.random(n) < 0.5] = 42
+    v[rng.random(n) < 0.01] = -1
+    key = Column.from_numpy(v, rng.random(n) > 0.02)
+    arg = Column.from_numpy(rng.random(n) * 100.0, rng.random(n) > 0.05)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MEAN), AggSpec(cols.HASH_COUNT, 1)]
+    b = run_groupby(ORACLE, [key], aggs, [arg] * 3)
+    for hint in (n, 1000):
+        a = run_groupby("gpu", [key], aggs, [arg] * 3, ctx, expected_groups=hint, options=HP)
+        assert_group_equal(a, b, aggs, rtol=RTOL, scales=abs_sum_scales([key], aggs, [arg] * 3))
+
+
+def test_groupby_partitioned_path_streaming_selected_and_rows(ctx):
+    """Several batches into one handle (the import folds into groups of earlier batches), a selection bitmap, and
+    explicit row numbers (ascending: taken; shuffled: falls back to the generic kernels) — all equal one batch."""
+    from arrow1_b200 import capi
+    rng = np.random.default_rng(14)
+    n = 300_000
+    kv = rng.integers(0, 60_000, size=n).astype(np.int64) * 1_000_003
+    key = Column.from_numpy(kv)
+    arg = Column.from_numpy(rng.random(n), rng.random(n) > 0.1)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT)]
+    want = run_groupby(ORACLE, [key], aggs, [arg] * 2)
+    scales = abs_sum_scales([key], aggs, [arg] * 2)
+
+    def finish(gb):
+        out = gb.finalize()
+        gb.close()
+        res_aggs = [[(c.to_host().values().copy(), c.to_host().valid()) for c in a] for a in out.aggs]
+        res_keys = [(c.to_host().values().copy(), c.to_host().valid()) for c in out.keys]
+        from helpers import GroupRes
+        return GroupRes(out.num_groups, res_aggs, res_keys)
+
+    def handle(hint):
+        gb = capi.GroupBy(ctx, [key.type], aggs, [arg.type] * 2, hint)
+        for k, v_ in HP.items():
+            gb.set_option(k, v_)
+        return gb
+
+    # three batches
+    gb = handle(60_000)
+    cuts = [0, 100_000, 100_001, n]
+    dkey, darg = key.to_device(), arg.to_device()
+    for lo, hi in zip(cuts[:-1], cuts[1:]):
+        gb.consume([Column(dkey.type, dkey.data, None, hi - lo, lo, 0)],
+                   [Column(darg.type, darg.data, darg.validity, hi - lo, lo, -1)] * 2, row_base=lo)
+    assert_group_equal(finish(gb), want, aggs, rtol=RTOL, scales=scales)
+    # explicit row numbers
+    for shuffled in (False, True):
+        gb = handle(60_000)
+        rows = np.arange(n, dtype=np.uint64) * 3 + 7
+        if shuffled:
+            perm = rng.permutation(n)
+            k2, a2, rows = Column.from_numpy(kv[perm]), Column.from_numpy(arg.values()[perm], arg.valid()[perm]), rows[perm]
+        else:
+            k2, a2 = key, arg
+        gb.consume_rows([k2.to_device()], [a2.to_device()] * 2, torch.from_numpy(rows.view(np.int64)).cuda())
+        assert_group_equal(finish(gb), want, aggs, rtol=RTOL, scales=scales)
+    # selection
+    sel = rng.random(n) < 0.6
+    kept = np.flatnonzero(sel)
+    want_sel = run_groupby(ORACLE, [Column.from_numpy(kv[kept])], aggs, [Column.from_numpy(arg.values()[kept], arg.valid()[kept])] * 2)
+    gb = handle(60_000)
+    gb.consume_selected([key.to_device()], [arg.to_device()] * 2, Column.from_numpy(sel).to_device())
+    assert_group_equal(finish(gb), want_sel, aggs, rtol=RTOL)
