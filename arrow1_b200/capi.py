@@ -512,6 +512,27 @@ class GroupBy:
         self.ctx.check(lib().b200_groupby_consume_selected(self._h, col_array(keys), col_array(args), C.c_uint64(row_base),
                                                            C.c_void_p(selection.data.data_ptr())))
 
+    def consume_fused(self, keys: Sequence[Column], args: Sequence, predicate=None, row_base: int = 0):
+        """b200_groupby_consume_fused.  args[j] is a Column, or a tuple (op1, a, op2, scalar, b) meaning
+        `a op1 (scalar op2 b)` over float64 columns; predicate = (column, op name, scalar) or None."""
+        from .columns import b200_fused_arg, b200_predicate
+        arr = (b200_fused_arg * max(len(args), 1))()
+        for j, g in enumerate(args):
+            if isinstance(g, Column):
+                arr[j].kind = 0
+                arr[j].a = g.desc()
+            else:
+                op1, a, op2, scalar, b = g
+                arr[j].kind, arr[j].op1, arr[j].op2 = 1, ARITH_OPS[op1], ARITH_OPS[op2]
+                arr[j].a, arr[j].b, arr[j].scalar = a.desc(), b.desc(), float(scalar)
+        pred, keep = None, None
+        if predicate is not None:
+            col, op, scalar = predicate
+            keep = np.array([scalar], dtype=NP_OF[col.type])
+            pred = b200_predicate(col.desc(), CMP_OPS[op], 0, keep.ctypes.data)
+        self.ctx.check(lib().b200_groupby_consume_fused(self._h, col_array(keys), arr, C.c_uint64(row_base),
+                                                        C.byref(pred) if pred is not None else None))
+
     def consume_rows(self, keys: Sequence[Column], args: Sequence[Column], row_ids: torch.Tensor):
         """b200_groupby_consume_rows: explicit global row numbers (int64-typed tensor of uint64)."""
         self.ctx.check(lib().b200_groupby_consume_rows(self._h, col_array(keys), col_array(args),

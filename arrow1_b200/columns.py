@@ -50,6 +50,15 @@ class b200_agg_spec(C.Structure):
                 ("reserved", C.c_int32)]
 
 
+class b200_fused_arg(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("op1", C.c_int32), ("op2", C.c_int32), ("reserved", C.c_int32),
+                ("a", b200_col), ("b", b200_col), ("scalar", C.c_double)]
+
+
+class b200_predicate(C.Structure):
+    _fields_ = [("column", b200_col), ("op", C.c_int32), ("reserved", C.c_int32), ("scalar", C.c_void_p)]
+
+
 def pack_bits(bits: np.ndarray, pad_to: int = 8) -> np.ndarray:
     """bool array -> LSB-first bitmap (uint8), zero padded to a multiple of `pad_to` bytes."""
     packed = np.packbits(np.asarray(bits, dtype=np.bool_), bitorder="little")

@@ -288,6 +288,7 @@ class Pipeline:
         self.lanes = []
 
 
+DOUBLE_T = 12   # columns.DOUBLE
 Q1_SHIPDATE_CUTOFF = 10471   # 1998-09-02 as date32 (TPC-H Q1: l_shipdate <= date '1998-12-01' - 90 days)
 
 
@@ -333,6 +334,25 @@ def Q1PipelineSelected(shipdate: Column, returnflag: Column, linestatus: Column,
     specs = q1_aggregates()
     return capi.group_by(ctx, [returnflag, linestatus], [a for _, a in specs], [ms[i] for i, _ in specs], expected_groups=8,
                          selection=mask)
+
+
+def Q1PipelineFused(shipdate: Column, returnflag: Column, linestatus: Column, measures: Sequence[Column],
+                    ctx: Optional[capi.Context] = None):
+    """The same query in ONE pass over the inputs (b200_groupby_consume_fused): the predicate, the derived measure
+    extendedprice * (1 - discount) and all seven aggregates are evaluated while shipdate, the two key columns and
+    the three measures stream through once (30 B/row).  Same result as Q1Pipeline, group order included."""
+    ctx = ctx or default_context()
+    qty, price, disc = measures
+    derived = ("multiply", price, "subtract", 1.0, disc)
+    stream = [qty, price, disc, derived]
+    specs = q1_aggregates()
+    aggs = [a for _, a in specs]
+    gb = capi.GroupBy(ctx, [returnflag.type, linestatus.type], aggs, [DOUBLE_T] * len(aggs), 8)
+    try:
+        gb.consume_fused([returnflag, linestatus], [stream[i] for i, _ in specs], (shipdate, "less_equal", Q1_SHIPDATE_CUTOFF))
+        return gb.finalize()
+    finally:
+        gb.close()
 
 
 class GroupByResult:

@@ -36,7 +36,36 @@ struct b200_ctx {
     bool in_use;
   };
   std::vector<Block> blocks;
+  // kernels whose >48 KB dynamic shared memory opt-in has been set on this context's device (one bit per site:
+  // cudaFuncSetAttribute applies per device, so the opt-in is tracked per context, not per process)
+  uint32_t attr_done = 0;
+  // device word a kernel sets when it had to give up (the sort's look-back bail-out); read back by
+  // b200_ctx_synchronize, which fails with B200_UNKNOWN_ERROR when it is non-zero
+  uint32_t* async_err = nullptr;
 };
+
+// first call for `bit` on this context -> true
+static inline bool b200_ctx_once(b200_ctx* ctx, int bit) {
+  if (ctx->attr_done & (1u << bit)) return false;
+  ctx->attr_done |= 1u << bit;
+  return true;
+}
+
+// Every entry point runs on its context's device whatever device is current in the calling thread (a process that
+// holds contexts on several GPUs, or a fresh thread whose current device is 0), and puts the caller's device back.
+struct b200_device_guard {
+  int prev = -1;
+  bool switched = false;
+  explicit b200_device_guard(const b200_ctx* ctx) {
+    if (ctx && cudaGetDevice(&prev) == cudaSuccess && prev != ctx->device) switched = cudaSetDevice(ctx->device) == cudaSuccess;
+  }
+  ~b200_device_guard() {
+    if (switched) cudaSetDevice(prev);
+  }
+  b200_device_guard(const b200_device_guard&) = delete;
+  b200_device_guard& operator=(const b200_device_guard&) = delete;
+};
+#define B200_ENTER(ctx) b200_device_guard _b200_device_guard(ctx)
 
 // caching device allocator of a context: cudaMalloc / cudaFree stay out of the steady state
 int b200_dev_alloc(b200_ctx* ctx, void** out, size_t bytes);

@@ -4,6 +4,7 @@
 #include "common.cuh"
 
 int b200_fail(b200_ctx* ctx, int code, const char* fmt, ...) {
+  B200_ENTER(ctx);
   char buf[1024];
   va_list ap;
   va_start(ap, fmt);
@@ -14,6 +15,7 @@ int b200_fail(b200_ctx* ctx, int code, const char* fmt, ...) {
 }
 
 int b200_ctx_reserve_scratch(b200_ctx* ctx, size_t bytes) {
+  B200_ENTER(ctx);
   if (bytes <= ctx->scratch_bytes) return B200_OK;
   if (ctx->scratch) {
     B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -28,6 +30,7 @@ int b200_ctx_reserve_scratch(b200_ctx* ctx, size_t bytes) {
 }
 
 int b200_dev_alloc(b200_ctx* ctx, void** out, size_t bytes) {
+  B200_ENTER(ctx);
   bytes = b200_align_up(bytes ? bytes : 1, 512);
   int best = -1;
   for (size_t i = 0; i < ctx->blocks.size(); ++i) {
@@ -109,6 +112,7 @@ static void clear_timed(b200_ctx* ctx) {
 extern "C" {
 
 int b200_ctx_set_kernel_timing(b200_ctx* ctx, int enabled) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   cudaStreamSynchronize(ctx->stream);
   clear_timed(ctx);
@@ -117,6 +121,7 @@ int b200_ctx_set_kernel_timing(b200_ctx* ctx, int enabled) {
 }
 
 int b200_ctx_kernel_time(b200_ctx* ctx, const char* name, double* total_ms, int64_t* launches) {
+  B200_ENTER(ctx);
   if (!ctx || !name) return B200_INVALID;
   B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   double total = 0;
@@ -167,6 +172,11 @@ int b200_ctx_create(int device, void* cu_stream, b200_ctx** out) {
     delete ctx;
     return B200_OUT_OF_MEMORY;
   }
+  if (cudaMalloc(reinterpret_cast<void**>(&ctx->async_err), 256) != cudaSuccess || cudaMemset(ctx->async_err, 0, 256) != cudaSuccess) {
+    cudaFreeHost(ctx->host_words);
+    delete ctx;
+    return B200_OUT_OF_MEMORY;
+  }
   *out = ctx;
   return B200_OK;
 }
@@ -180,11 +190,13 @@ int b200_ctx_destroy(b200_ctx* ctx) {
   for (auto& b : ctx->blocks) cudaFree(b.ptr);
   ctx->blocks.clear();
   if (ctx->host_words) cudaFreeHost(ctx->host_words);
+  if (ctx->async_err) cudaFree(ctx->async_err);
   delete ctx;
   return B200_OK;
 }
 
 int b200_ctx_set_stream(b200_ctx* ctx, void* cu_stream) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   cudaStreamSynchronize(ctx->stream);  // cached device blocks are reused in stream order
   ctx->stream = reinterpret_cast<cudaStream_t>(cu_stream);
@@ -192,6 +204,7 @@ int b200_ctx_set_stream(b200_ctx* ctx, void* cu_stream) {
 }
 
 int b200_ctx_synchronize(b200_ctx* ctx) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return B200_OK;

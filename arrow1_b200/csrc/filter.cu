@@ -168,6 +168,9 @@ struct ApplyArgs {
   const uint32_t* tile_prefix;
   void* out_data;
   uint32_t* out_valid;   // nullable
+  const int64_t* out_length;   // the plan's number of emitted rows (device)
+  int64_t capacity;            // rows the caller's output buffers hold
+  uint32_t* err;               // context flag: set to 2 when the plan emits more rows than the buffers hold
 };
 
 // Appends compacted bit groups to an output bitmap as whole 32-bit words.  All lanes carry the
@@ -219,6 +222,11 @@ filter_apply_kernel(ApplyArgs a) {
   __shared__ uint32_t warp_totals[8];
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int64_t tile = blockIdx.x;
+  // never write past the caller's buffers: an undersized output is reported through the context (b200_ctx_synchronize)
+  if (*a.out_length > a.capacity) {
+    if (tile == 0 && threadIdx.x == 0) atomicExch(a.err, 2u);
+    return;
+  }
   const int64_t out_base = a.super_prefix[tile / kTilesPerSuper] + a.tile_prefix[tile];
   const int64_t wrow0 = tile * int64_t(kTileRows) + int64_t(warp) * 512;
   const BitmapRef ones{nullptr, 0};
@@ -686,6 +694,7 @@ static int take_impl(b200_ctx* ctx, const b200_col* values, int n_chunks, const 
 
 int b200_take(b200_ctx* ctx, const b200_col* values, const b200_col* indices, int boundscheck, void* out_data,
               void* out_validity, int64_t* out_null_count) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (!values || !indices) return b200_fail(ctx, B200_INVALID, "take: null argument");
   return take_impl(ctx, values, 0, indices, boundscheck, out_data, out_validity, out_null_count);
@@ -693,6 +702,7 @@ int b200_take(b200_ctx* ctx, const b200_col* values, const b200_col* indices, in
 
 int b200_take_chunked(b200_ctx* ctx, const b200_col* chunks, int n_chunks, const b200_col* indices, int boundscheck,
                       void* out_data, void* out_validity, int64_t* out_null_count) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (!chunks || !indices || n_chunks < 1) return b200_fail(ctx, B200_INVALID, "take_chunked: null argument or no chunks");
   return take_impl(ctx, chunks, n_chunks, indices, boundscheck, out_data, out_validity, out_null_count);
@@ -700,6 +710,7 @@ int b200_take_chunked(b200_ctx* ctx, const b200_col* chunks, int n_chunks, const
 
 int b200_arithmetic(b200_ctx* ctx, int op, const b200_col* a, const void* a_scalar, const b200_col* b, const void* b_scalar,
                     void* out_data, void* out_validity) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (op < 0 || op > 2) return b200_fail(ctx, B200_INVALID, "arithmetic: bad operator %d", op);
   if (!a && !b) return b200_fail(ctx, B200_INVALID, "arithmetic: at least one operand must be a column");
@@ -749,6 +760,7 @@ const int64_t* b200_filter_plan_length_ptr(const void* plan) {
 }
 
 int b200_filter_plan(b200_ctx* ctx, const b200_col* mask, int null_selection, void* plan, int64_t* out_len) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   B200_RETURN_NOT_OK(check_mask(ctx, mask));
   if (!plan) return b200_fail(ctx, B200_INVALID, "filter_plan: null plan buffer");
@@ -774,6 +786,7 @@ int b200_filter_plan(b200_ctx* ctx, const b200_col* mask, int null_selection, vo
 }
 
 int b200_compare_scalar(b200_ctx* ctx, const b200_col* values, int op, const void* scalar, void* out_bitmap) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (!values || !scalar) return b200_fail(ctx, B200_INVALID, "compare_scalar: null argument");
   if (op < kCmpEq || op > kCmpLe) return b200_fail(ctx, B200_INVALID, "compare_scalar: bad operator %d", op);
@@ -798,6 +811,7 @@ int b200_compare_scalar(b200_ctx* ctx, const b200_col* values, int op, const voi
 }
 
 int b200_filter_count(b200_ctx* ctx, const b200_col* mask, int null_selection, int64_t* out_len) {
+  B200_ENTER(ctx);
   if (!ctx || !out_len) return B200_INVALID;
   B200_RETURN_NOT_OK(check_mask(ctx, mask));
   size_t bytes = plan_bytes_for(mask->length);
@@ -819,6 +833,7 @@ int b200_filter_out_spec(const b200_col* values, const b200_col* mask, int null_
 
 int b200_filter_apply(b200_ctx* ctx, const b200_col* values, const b200_col* mask, int null_selection,
                       const void* plan, void* out_data, void* out_validity, int64_t out_capacity) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   B200_RETURN_NOT_OK(check_mask(ctx, mask));
   if (!values || !plan) return b200_fail(ctx, B200_INVALID, "filter_apply: null argument");
@@ -829,8 +844,8 @@ int b200_filter_apply(b200_ctx* ctx, const b200_col* values, const b200_col* mas
   if (bits == 0) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "filter: unsupported values type %d", values->type);
   if (out_capacity < 0) return b200_fail(ctx, B200_INVALID, "filter_apply: negative out_capacity");
   const int64_t length = mask->length;
-  if (length == 0 || out_capacity == 0) return B200_OK;
-  if (!out_data) return b200_fail(ctx, B200_INVALID, "filter_apply: null out_data");
+  if (length == 0) return B200_OK;
+  if (!out_data && out_capacity > 0) return b200_fail(ctx, B200_INVALID, "filter_apply: null out_data");
   if ((reinterpret_cast<uintptr_t>(out_data) & 7) || (reinterpret_cast<uintptr_t>(out_validity) & 7))
     return b200_fail(ctx, B200_INVALID, "filter_apply: output buffers must be 8-byte aligned");
   PlanView pv = plan_view(const_cast<void*>(plan), length);
@@ -846,9 +861,12 @@ int b200_filter_apply(b200_ctx* ctx, const b200_col* values, const b200_col* mas
   a.tile_prefix = pv.tile_prefix;
   a.out_data = out_data;
   a.out_valid = reinterpret_cast<uint32_t*>(out_validity);
+  a.out_length = &pv.header->out_length;
+  a.capacity = out_capacity;
+  a.err = ctx->async_err;
   const size_t bitmap_bytes = b200_align_up(size_t((out_capacity + 7) / 8), 4);
   if (out_validity) B200_CUDA(ctx, cudaMemsetAsync(out_validity, 0, bitmap_bytes, ctx->stream));
-  if (bits == 1) B200_CUDA(ctx, cudaMemsetAsync(out_data, 0, bitmap_bytes, ctx->stream));
+  if (bits == 1 && out_data) B200_CUDA(ctx, cudaMemsetAsync(out_data, 0, bitmap_bytes, ctx->stream));
   const int64_t nt = n_tiles_for(length);
   switch (bits) {
     case 1: return launch_apply<uint8_t, true>(ctx, a, nt);

@@ -23,6 +23,14 @@
 
 #include "common.cuh"
 
+// kernel-variant switches of the timing experiments (profiles/): environment lookups only in a debug build
+#ifdef B200_DEBUG_KNOBS
+#include <stdlib.h>
+#define B200_KNOB(name) getenv(name)
+#else
+#define B200_KNOB(name) (static_cast<const char*>(nullptr))
+#endif
+
 namespace {
 
 constexpr int kMaxKeys = 4;
@@ -2061,6 +2069,8 @@ __global__ void __launch_bounds__(kTinyThreads, 4) gb_tiny8_kernel(const __grid_
   tiny_fold(a, S, kFloatSum ? kFloat : kSigned, begin);
 }
 
+#include "groupby_q1.cuh"
+
 // ---- table maintenance ----------------------------------------------------------------------
 // moves every occupied slot of `src` (stride bytes each) into table `dst`; when `merge` the states
 // are folded (duplicates allowed), otherwise copied (rehash: keys are unique)
@@ -2740,19 +2750,20 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
   int cap_bits = 0;
   while ((uint64_t(1) << cap_bits) < planned_cap) ++cap_bits;
   const int top = std::max(cap_bits, bits);   // partition id = hash bits [top - bits, top)
-  static bool attr = false;
-  if (!attr) {
+  if (b200_ctx_once(ctx, 1)) {
     B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_part_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpPartSmem))));
     B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_part_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpPartSmem))));
     B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_agg_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpAggSmem))));
     B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_agg_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpAggSmem))));
-    attr = true;
   }
   const int64_t n_tiles = (n + kHpTile - 1) / kHpTile;
   const unsigned grid = unsigned(std::min<int64_t>(n_tiles, int64_t(ctx->num_sms) * 8));
   HpArgs h;
   memset(&h, 0, sizeof(h));
   h.has_val = a.n_cols > 0;
+  if (a.s.n_keys == 1 && !a.keys[0].vv.words && (a.keys[0].nbits == 64 || a.keys[0].nbits == 32) &&
+      (a.n_cols == 0 || (b200_type_bits(a.cols[0].type) == 64 && !a.cols[0].vv.words)))
+    h.fast = a.keys[0].nbits / 8;
   // level 1
   h.dst = buf_a;
   h.parts = 1;
@@ -2898,17 +2909,15 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
       B200_RETURN_NOT_OK(grow_table(gb, 2 * std::max<uint64_t>(likely_groups, 32 * 1024)));
       a.t = gb->table;
       a.rows_per_block = int(rpb);
-      static bool tattr = false;
-      if (!tattr) {
+      if (b200_ctx_once(ctx, 4)) {
         B200_CUDA(ctx, cudaFuncSetAttribute(gb_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(TinySmem))));
         B200_CUDA(ctx, cudaFuncSetAttribute(gb_tiny8_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(TinySmem))));
         B200_CUDA(ctx, cudaFuncSetAttribute(gb_tiny8_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(TinySmem))));
         B200_CUDA(ctx, cudaFuncSetAttribute(gb_tiny8_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(TinySmem))));
         B200_CUDA(ctx, cudaFuncSetAttribute(gb_tiny8_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(TinySmem))));
-        tattr = true;
       }
       // byte-wide keys without nulls and a 64-bit value column (the Q1 shape): register accumulators
-      bool lean = a.s.n_keys <= 3 && !getenv("B200_GB_NO_TINY8");
+      bool lean = a.s.n_keys <= 3 && !B200_KNOB("B200_GB_NO_TINY8");
       for (int k = 0; k < a.s.n_keys; ++k)
         if (a.keys[k].nbits != 8 || a.keys[k].vv.words != nullptr) lean = false;
       const int vt = a.cols[0].type;
@@ -2946,7 +2955,7 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
       // The binned kernels want many groups: a group may hold kBinCap values per 8192-row tile before rows
       // take the slow overflow path, so below ~512 expected groups (>= 16 rows per group per tile) the
       // counting-sort kernel, whose bins are sized exactly by a scan, is the right one.
-      static const bool binned_ok = getenv("B200_GB_V1") == nullptr && getenv("B200_GB_DIRECT") == nullptr;
+      static const bool binned_ok = !B200_KNOB("B200_GB_V1") && !B200_KNOB("B200_GB_DIRECT");
       const bool binned = binned_ok && likely_groups * kBinCap >= uint64_t(kBinTile);
       const int64_t tile_rows = binned ? kBinTile : kFastTile;
       const int64_t n_full = n / tile_rows * tile_rows;
@@ -2961,7 +2970,7 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
         a.t = gb->table;
 
         a.local_slots = kFastSlots32;
-        static const int dbg = getenv("B200_GB_DBG") ? atoi(getenv("B200_GB_DBG")) : 0;
+        static const int dbg = B200_KNOB("B200_GB_DBG") ? atoi(B200_KNOB("B200_GB_DBG")) : 0;
         a.dbg = dbg;
         a.rows_per_block = int(rpb);
         a.n = n_full;
@@ -2971,8 +2980,7 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
         const bool k32 = a.s.n_keys == 1 && a.keys[0].nbits == 32 && !a.keys[0].vv.words && (reinterpret_cast<uintptr_t>(a.keys[0].data) & 15) == 0;
         const bool k64 = a.s.n_keys == 1 && a.keys[0].nbits == 64 && !a.keys[0].vv.words && (reinterpret_cast<uintptr_t>(a.keys[0].data) & 15) == 0;
         const bool vfast = a.n_cols == 1 && b200_type_bits(a.cols[0].type) == 64 && (reinterpret_cast<uintptr_t>(a.cols[0].data) & 15) == 0;
-        static bool fattr = false;
-        if (!fattr) {
+        if (b200_ctx_once(ctx, 5)) {
           const int mx = int(sizeof(FastSmem));
           B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<0, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
           B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<0, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
@@ -2994,16 +3002,15 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
           B200_CUDA(ctx, cudaFuncSetAttribute(gb_bin_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bx));
           B200_CUDA(ctx, cudaFuncSetAttribute(gb_bin_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bx));
           B200_CUDA(ctx, cudaFuncSetAttribute(gb_bin32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bx));
-          fattr = true;
         }
-        static const bool direct = getenv("B200_GB_DIRECT") != nullptr;
+        static const bool direct = B200_KNOB("B200_GB_DIRECT") != nullptr;
 #define B200_FAST_LAUNCH(KM, VF) \
   do {                                                                                                              \
     if (binned) B200_TIMED(ctx, "groupby_consume", (gb_bin_kernel<KM, VF><<<grid, kBinThreads, smem, ctx->stream>>>(a)));          \
     else if (direct) B200_TIMED(ctx, "groupby_consume", (gb_fast_kernel<KM, VF, true><<<grid, kFastThreads, smem, ctx->stream>>>(a)));  \
     else B200_TIMED(ctx, "groupby_consume", (gb_fast_kernel<KM, VF, false><<<grid, kFastThreads, smem, ctx->stream>>>(a)));        \
   } while (0)
-        static const bool pipelined = getenv("B200_GB_V2") == nullptr;
+        static const bool pipelined = B200_KNOB("B200_GB_V2") == nullptr;
         if (binned && pipelined && k32 && vfast && a.keys[0].nbits == 32) {
           B200_TIMED(ctx, "groupby_consume", (gb_bin32_kernel<<<grid, kBinThreads, smem, ctx->stream>>>(a)));
         } else if (k32) { if (vfast) B200_FAST_LAUNCH(1, true); else B200_FAST_LAUNCH(1, false); }
@@ -3038,10 +3045,8 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
       a.rows_per_block = int((n + blocks - 1) / blocks);
       a.rows_per_block = (a.rows_per_block + 1023) / 1024 * 1024;
       const int smem = local_slots * a.s.lstride;
-      static bool attr = false;
-      if (!attr) {
+      if (b200_ctx_once(ctx, 2)) {
         B200_CUDA(ctx, cudaFuncSetAttribute(gb_consume_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr = true;
       }
       B200_TIMED(ctx, "groupby_consume", (gb_consume_kernel<true><<<blocks, 1024, smem, ctx->stream>>>(a)));
     } else {
@@ -3080,6 +3085,7 @@ extern "C" {
 
 int b200_groupby_create(b200_ctx* ctx, int n_keys, const int32_t* key_types, int n_aggs, const b200_agg_spec* aggs,
                         int64_t expected_groups, b200_groupby** out) {
+  B200_ENTER(ctx);
   if (!ctx || !out) return B200_INVALID;
   *out = nullptr;
   if (n_keys < 1 || n_keys > kMaxKeys) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby: %d key columns (1..%d supported)", n_keys, kMaxKeys);
@@ -3148,6 +3154,7 @@ int b200_groupby_create(b200_ctx* ctx, int n_keys, const int32_t* key_types, int
 }
 
 int b200_groupby_destroy(b200_groupby* gb) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   if (!gb) return B200_OK;
   cudaStreamSynchronize(gb->ctx->stream);
   b200_dev_free(gb->ctx, gb->table.slots);
@@ -3161,6 +3168,7 @@ int b200_groupby_destroy(b200_groupby* gb) {
 }
 
 int b200_groupby_set_option(b200_groupby* gb, const char* name, int64_t value) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   if (!gb || !name) return B200_INVALID;
   if (!strcmp(name, "hp_min_rows")) gb->hp_min_rows = value;
   else if (!strcmp(name, "hp_min_groups")) gb->hp_min_groups = value;
@@ -3172,17 +3180,20 @@ static int groupby_consume_impl(b200_groupby* gb, const b200_col* keys, const b2
                                 const uint64_t* row_ids, const uint32_t* select = nullptr);
 
 int b200_groupby_consume(b200_groupby* gb, const b200_col* keys, const b200_col* args, uint64_t row_base) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   return groupby_consume_impl(gb, keys, args, row_base, nullptr);
 }
 
 int b200_groupby_consume_selected(b200_groupby* gb, const b200_col* keys, const b200_col* args, uint64_t row_base,
                                   const void* selection) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   if (gb && !selection && keys && keys[0].length > 0) return b200_fail(gb->ctx, B200_INVALID, "groupby_consume_selected: null selection");
   if (gb && (reinterpret_cast<uintptr_t>(selection) & 3)) return b200_fail(gb->ctx, B200_INVALID, "groupby_consume_selected: selection must be 4-byte aligned");
   return groupby_consume_impl(gb, keys, args, row_base, nullptr, reinterpret_cast<const uint32_t*>(selection));
 }
 
 int b200_groupby_consume_rows(b200_groupby* gb, const b200_col* keys, const b200_col* args, const uint64_t* row_ids) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   if (gb && !row_ids && keys && keys[0].length > 0) return b200_fail(gb->ctx, B200_INVALID, "groupby_consume_rows: null row_ids");
   return groupby_consume_impl(gb, keys, args, 0, row_ids);
 }
@@ -3238,6 +3249,226 @@ static int groupby_consume_impl(b200_groupby* gb, const b200_col* keys, const b2
   return run_consume(gb, a);
 }
 
+
+// ---- fused compare -> filter -> derive -> aggregate ----------------------------------------------------
+namespace {
+bool same_col(const b200_col& x, const b200_col& y) {
+  return x.data == y.data && x.validity == y.validity && x.offset == y.offset && x.type == y.type && x.length == y.length;
+}
+bool col_has_nulls(const b200_col& c) { return c.validity != nullptr && c.null_count != 0; }
+
+// the one-pass kernel: *taken = false when the shape is not its own or a CTA met a 9th group (nothing was changed)
+int try_fused8(b200_groupby* gb, const b200_col* keys, const b200_fused_arg* args, uint64_t row_base, const b200_predicate* pred,
+               bool* taken) {
+  b200_ctx* ctx = gb->ctx;
+  *taken = false;
+  const GbSchema& s = gb->schema;
+  const uint64_t likely = std::max<uint64_t>(gb->groups, gb->expected);
+  if (likely == 0 || likely > uint64_t(kTinyGroups) || s.n_keys > 3 || s.n_aggs == 0) return B200_OK;
+  const int64_t n = keys[0].length;
+  if (n < kBinTile) return B200_OK;
+  for (int k = 0; k < s.n_keys; ++k)
+    if (s.key_bits[k] != 8 || col_has_nulls(keys[k])) return B200_OK;
+  if (pred) {
+    if ((pred->column.type != B200_INT32 && pred->column.type != B200_UINT32) || col_has_nulls(pred->column)) return B200_OK;
+  }
+  FusedArgs f;
+  memset(&f, 0, sizeof(f));
+  b200_col cols[kFusedCols];
+  auto col_index = [&](const b200_col& c) -> int {
+    for (int i = 0; i < f.n_cols; ++i)
+      if (same_col(cols[i], c)) return i;
+    if (f.n_cols == kFusedCols) return -1;
+    cols[f.n_cols] = c;
+    f.cols[f.n_cols] = reinterpret_cast<const double*>(c.data) + c.offset;
+    return f.n_cols++;
+  };
+  GbArgs a;
+  memset(&a, 0, sizeof(a));
+  a.s = s;
+  B200_RETURN_NOT_OK(fill_keys(gb, keys, &a));
+  for (int j = 0; j < s.n_aggs; ++j) {
+    const b200_fused_arg& g = args[j];
+    if (s.aggs[j].kind == B200_HASH_MIN_MAX) return B200_OK;
+    if (g.a.type != B200_DOUBLE || col_has_nulls(g.a) || g.a.length != n) return B200_OK;
+    if (g.kind == 1 && (g.b.type != B200_DOUBLE || col_has_nulls(g.b) || g.b.length != n)) return B200_OK;
+    FusedStream st;
+    memset(&st, 0, sizeof(st));
+    st.kind = g.kind;
+    st.ia = col_index(g.a);
+    st.ib = g.kind == 1 ? col_index(g.b) : 0;
+    if (st.ia < 0 || st.ib < 0) return B200_OK;
+    st.op1 = g.op1;
+    st.op2 = g.op2;
+    st.scalar = g.scalar;
+    int found = -1;
+    for (int q = 0; q < f.n_streams; ++q) {
+      const FusedStream& o = f.streams[q];
+      if (o.kind == st.kind && o.ia == st.ia && (st.kind == 0 || (o.ib == st.ib && o.op1 == st.op1 && o.op2 == st.op2 &&
+                                                                  memcmp(&o.scalar, &st.scalar, sizeof(double)) == 0)))
+        found = q;
+    }
+    if (found < 0) {
+      if (f.n_streams == kFusedStreams) return B200_OK;
+      f.streams[f.n_streams] = st;
+      found = f.n_streams++;
+    }
+    a.s.aggs[j].col = found;
+  }
+  if (pred) {
+    f.pred_data = reinterpret_cast<const char*>(pred->column.data) + pred->column.offset * 4;
+    f.pred_type = pred->column.type;
+    f.pred_op = pred->op;
+    f.pred_scalar = pred->column.type == B200_INT32 ? int64_t(*reinterpret_cast<const int32_t*>(pred->scalar))
+                                                    : int64_t(*reinterpret_cast<const uint32_t*>(pred->scalar));
+  }
+  const int grid = int(std::min<int64_t>(int64_t(ctx->num_sms) * 3, (n + 4095) / 4096));
+  int64_t rpb = (n + grid - 1) / grid;
+  rpb = (rpb + 31) / 32 * 32;
+  a.rows_per_block = int(rpb);
+  a.row_base = row_base;
+  a.n_cols = f.n_streams;
+  const uint32_t n_images = uint32_t(grid) * kTinyGroups;
+  B200_RETURN_NOT_OK(gb_reserve_tmp(gb, size_t(n_images) * s.stride + 512));
+  f.overflow = reinterpret_cast<uint32_t*>(gb->tmp);
+  f.images = reinterpret_cast<char*>(gb->tmp) + 256;
+  B200_CUDA(ctx, cudaMemsetAsync(f.overflow, 0, sizeof(uint32_t), ctx->stream));
+  if (b200_ctx_once(ctx, 3)) {
+    B200_CUDA(ctx, cudaFuncSetAttribute(gb_fused8_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(FusedSmem<1>))));
+    B200_CUDA(ctx, cudaFuncSetAttribute(gb_fused8_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(FusedSmem<2>))));
+    B200_CUDA(ctx, cudaFuncSetAttribute(gb_fused8_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(FusedSmem<3>))));
+    B200_CUDA(ctx, cudaFuncSetAttribute(gb_fused8_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(FusedSmem<4>))));
+  }
+  switch (f.n_streams) {
+    case 1: B200_TIMED(ctx, "groupby_fused", (gb_fused8_kernel<1><<<grid, kTinyThreads, int(sizeof(FusedSmem<1>)), ctx->stream>>>(a, f))); break;
+    case 2: B200_TIMED(ctx, "groupby_fused", (gb_fused8_kernel<2><<<grid, kTinyThreads, int(sizeof(FusedSmem<2>)), ctx->stream>>>(a, f))); break;
+    case 3: B200_TIMED(ctx, "groupby_fused", (gb_fused8_kernel<3><<<grid, kTinyThreads, int(sizeof(FusedSmem<3>)), ctx->stream>>>(a, f))); break;
+    default: B200_TIMED(ctx, "groupby_fused", (gb_fused8_kernel<4><<<grid, kTinyThreads, int(sizeof(FusedSmem<4>)), ctx->stream>>>(a, f))); break;
+  }
+  B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 24, f.overflow, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (*reinterpret_cast<const uint32_t*>(ctx->host_words + 24) != 0) return B200_OK;   // more than 8 groups: not taken
+  B200_RETURN_NOT_OK(materialize(gb));
+  gb_hp_import_kernel<<<(n_images + 255) / 256, 256, 0, ctx->stream>>>(gb->schema, f.images, n_images, gb->table, gb->counters);
+  B200_LAUNCHED(ctx);
+  uint32_t c[4];
+  B200_RETURN_NOT_OK(read_counters(gb, c));
+  *taken = true;
+  return B200_OK;
+}
+}  // namespace
+
+int b200_groupby_consume_fused(b200_groupby* gb, const b200_col* keys, const b200_fused_arg* args, uint64_t row_base,
+                               const b200_predicate* pred) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
+  if (!gb) return B200_INVALID;
+  b200_ctx* ctx = gb->ctx;
+  const GbSchema& s = gb->schema;
+  if (!keys || (s.n_aggs > 0 && !args)) return b200_fail(ctx, B200_INVALID, "groupby_consume_fused: null argument");
+  if (gb->dense_used) return b200_fail(ctx, B200_INVALID, "groupby: handle already used through b200_hash_agg_consume");
+  const int64_t n = keys[0].length;
+  for (int j = 0; j < s.n_aggs; ++j) {
+    const b200_fused_arg& g = args[j];
+    if (g.kind != 0 && g.kind != 1) return b200_fail(ctx, B200_INVALID, "groupby_consume_fused: argument %d has kind %d", j, g.kind);
+    if (g.kind == 1) {
+      if (g.a.type != B200_DOUBLE || g.b.type != B200_DOUBLE)
+        return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby_consume_fused: derived arguments are float64 expressions");
+      if (g.op1 < B200_ADD || g.op1 > B200_MULTIPLY || g.op2 < B200_ADD || g.op2 > B200_MULTIPLY)
+        return b200_fail(ctx, B200_INVALID, "groupby_consume_fused: bad arithmetic operator");
+      if (g.b.length != n) return b200_fail(ctx, B200_INVALID, "Array arguments must all be the same length");
+    }
+    if (g.a.length != n) return b200_fail(ctx, B200_INVALID, "Array arguments must all be the same length");
+    const int want = g.kind == 1 ? B200_DOUBLE : g.a.type;
+    if (want != s.aggs[j].arg_type) return b200_fail(ctx, B200_TYPE_ERROR, "groupby: argument %d has type %d, expected %d", j, want, s.aggs[j].arg_type);
+  }
+  if (pred) {
+    if (!pred->scalar) return b200_fail(ctx, B200_INVALID, "groupby_consume_fused: predicate without a scalar");
+    if (pred->column.length != n) return b200_fail(ctx, B200_INVALID, "Array arguments must all be the same length");
+    if (pred->op < 0 || pred->op > 5) return b200_fail(ctx, B200_INVALID, "groupby_consume_fused: bad comparison %d", pred->op);
+    if (col_has_nulls(pred->column)) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby_consume_fused: predicate column with nulls (use Filter)");
+  }
+  if (n == 0) return B200_OK;
+  bool taken = false;
+  B200_RETURN_NOT_OK(try_fused8(gb, keys, args, row_base, pred, &taken));
+  if (taken) return B200_OK;
+  // ---- the same through the separate operations: comparison -> selection, arithmetic -> derived columns
+  std::vector<void*> temps;
+  auto release = [&]() {
+    for (void* p : temps) b200_dev_free(ctx, p);
+  };
+  void* selection = nullptr;
+  int st = B200_OK;
+  if (pred) {
+    st = b200_dev_alloc(ctx, &selection, size_t((n + 31) / 32) * 4);
+    if (st == B200_OK) {
+      temps.push_back(selection);
+      st = b200_compare_scalar(ctx, &pred->column, pred->op, pred->scalar, selection);
+    }
+  }
+  std::vector<b200_col> cols(std::max(s.n_aggs, 1));
+  for (int j = 0; j < s.n_aggs && st == B200_OK; ++j) {
+    const b200_fused_arg& g = args[j];
+    if (g.kind == 0) {
+      cols[j] = g.a;
+      continue;
+    }
+    int same = -1;
+    for (int q = 0; q < j; ++q)
+      if (args[q].kind == 1 && same_col(args[q].a, g.a) && same_col(args[q].b, g.b) && args[q].op1 == g.op1 && args[q].op2 == g.op2 &&
+          memcmp(&args[q].scalar, &g.scalar, sizeof(double)) == 0)
+        same = q;
+    if (same >= 0) {
+      cols[j] = cols[same];
+      continue;
+    }
+    void *inner = nullptr, *data = nullptr, *valid = nullptr;
+    const bool nulls = col_has_nulls(g.a) || col_has_nulls(g.b);
+    st = b200_dev_alloc(ctx, &inner, size_t(n) * 8);
+    if (st == B200_OK) temps.push_back(inner);
+    if (st == B200_OK) st = b200_dev_alloc(ctx, &data, size_t(n) * 8);
+    if (st == B200_OK) temps.push_back(data);
+    if (st == B200_OK && nulls) {
+      st = b200_dev_alloc(ctx, &valid, size_t((n + 63) / 64) * 8);
+      if (st == B200_OK) temps.push_back(valid);
+    }
+    if (st != B200_OK) break;
+    st = b200_arithmetic(ctx, g.op2, nullptr, &g.scalar, &g.b, nullptr, inner, nullptr);   // validity of b rides with b below
+    if (st != B200_OK) break;
+    b200_col t = g.b;
+    t.data = inner;
+    t.offset = 0;
+    if (col_has_nulls(g.b)) {
+      // the inner result's validity is b's bitmap at b's offset: keep addressing it through b's descriptor
+      t.validity = g.b.validity;
+      t.offset = g.b.offset;
+      t.data = reinterpret_cast<char*>(inner) - g.b.offset * 8;
+    } else {
+      t.validity = nullptr;
+      t.null_count = 0;
+    }
+    st = b200_arithmetic(ctx, g.op1, &g.a, nullptr, &t, nullptr, data, valid);
+    b200_col d;
+    memset(&d, 0, sizeof(d));
+    d.type = B200_DOUBLE;
+    d.data = data;
+    d.validity = valid;
+    d.length = n;
+    d.offset = 0;
+    d.null_count = valid ? -1 : 0;
+    cols[j] = d;
+  }
+  if (st == B200_OK) {
+    st = selection ? b200_groupby_consume_selected(gb, keys, cols.data(), row_base, selection)
+                   : b200_groupby_consume(gb, keys, cols.data(), row_base);
+  }
+  if (st == B200_OK) {
+    // the temporaries go back to the context's block cache: make sure the kernels that read them have run
+    cudaStreamSynchronize(ctx->stream);
+  }
+  release();
+  return st;
+}
+
 // ---- hash repartitioning -------------------------------------------------------------------------
 int b200_partition_scratch_bytes(int64_t length, size_t* out_bytes) {
   if (!out_bytes || length < 0) return B200_INVALID;
@@ -3248,6 +3479,7 @@ int b200_partition_scratch_bytes(int64_t length, size_t* out_bytes) {
 
 int b200_groupby_partition_plan(b200_groupby* gb, const b200_col* keys, int n_parts, uint32_t* out_pos, int64_t* out_counts,
                                 void* scratch, size_t scratch_bytes) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   if (!gb) return B200_INVALID;
   b200_ctx* ctx = gb->ctx;
   if (!keys || !out_counts) return b200_fail(ctx, B200_INVALID, "partition_plan: null argument");
@@ -3277,6 +3509,7 @@ int b200_groupby_partition_plan(b200_groupby* gb, const b200_col* keys, int n_pa
 }
 
 int b200_partition_scatter(b200_ctx* ctx, const b200_col* col, const uint32_t* pos, void* out_data, uint8_t* out_valid) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (!col) return b200_fail(ctx, B200_INVALID, "partition_scatter: null column");
   const int64_t n = col->length;
@@ -3298,6 +3531,7 @@ int b200_partition_scatter(b200_ctx* ctx, const b200_col* col, const uint32_t* p
 }
 
 int b200_partition_rows(b200_ctx* ctx, int64_t length, uint64_t row_base, const uint32_t* pos, uint64_t* out_rows) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (length < 0) return b200_fail(ctx, B200_INVALID, "partition_rows: negative length");
   if (length == 0) return B200_OK;
@@ -3308,6 +3542,7 @@ int b200_partition_rows(b200_ctx* ctx, int64_t length, uint64_t row_base, const 
 }
 
 int b200_pack_validity(b200_ctx* ctx, const uint8_t* valid_bytes, int64_t length, void* out_bitmap, int64_t* out_null_count) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (length < 0) return b200_fail(ctx, B200_INVALID, "pack_validity: negative length");
   if (out_null_count) *out_null_count = 0;
@@ -3327,6 +3562,7 @@ int b200_pack_validity(b200_ctx* ctx, const uint8_t* valid_bytes, int64_t length
 }
 
 int b200_groupby_num_groups(b200_groupby* gb, uint32_t* out) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   if (!gb || !out) return B200_INVALID;
   if (gb->dense_used) {
     *out = gb->dense_groups;
@@ -3339,6 +3575,7 @@ int b200_groupby_num_groups(b200_groupby* gb, uint32_t* out) {
 }
 
 int b200_grouper_consume(b200_groupby* gb, const b200_col* keys, uint32_t* out_ids) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   if (!gb) return B200_INVALID;
   b200_ctx* ctx = gb->ctx;
   if (!keys) return b200_fail(ctx, B200_INVALID, "grouper_consume: null keys");
@@ -3421,6 +3658,7 @@ int b200_grouper_consume(b200_groupby* gb, const b200_col* keys, uint32_t* out_i
 }
 
 int b200_hash_agg_consume(b200_groupby* gb, int agg_index, const b200_col* arg, const uint32_t* ids, uint32_t num_groups) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   if (!gb) return B200_INVALID;
   b200_ctx* ctx = gb->ctx;
   if (agg_index < 0 || agg_index >= gb->schema.n_aggs) return b200_fail(ctx, B200_INVALID, "hash_agg_consume: bad aggregate index");
@@ -3454,6 +3692,7 @@ int b200_hash_agg_consume(b200_groupby* gb, int agg_index, const b200_col* arg, 
 }
 
 int b200_hash_agg_merge(b200_groupby* dst, b200_groupby* src) {
+  B200_ENTER(dst ? dst->ctx : nullptr);
   if (!dst || !src) return B200_INVALID;
   b200_ctx* ctx = dst->ctx;
   if (dst->ctx != src->ctx) return b200_fail(ctx, B200_INVALID, "hash_agg_merge: handles belong to different contexts");
@@ -3482,6 +3721,7 @@ int b200_hash_agg_merge(b200_groupby* dst, b200_groupby* src) {
 }
 
 int b200_groupby_state_layout(b200_groupby* gb, size_t* slot_bytes) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   if (!gb || !slot_bytes) return B200_INVALID;
   *slot_bytes = size_t(gb->schema.stride);
   return B200_OK;
@@ -3516,6 +3756,7 @@ static int collect_slots(b200_groupby* gb, uint64_t** first_rows, uint64_t** slo
 }
 
 int b200_groupby_first_rows(b200_groupby* gb, uint64_t* out_first_rows) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   if (!gb) return B200_INVALID;
   b200_ctx* ctx = gb->ctx;
   if (gb->dense_used) return b200_fail(ctx, B200_INVALID, "groupby_first_rows: dense handle has no row order");
@@ -3534,6 +3775,7 @@ int b200_groupby_first_rows(b200_groupby* gb, uint64_t* out_first_rows) {
 }
 
 int b200_groupby_export(b200_groupby* gb, void* out_state, uint32_t* out_groups) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   if (!gb || !out_groups) return B200_INVALID;
   b200_ctx* ctx = gb->ctx;
   uint64_t *first_rows, *slot_idx;
@@ -3552,6 +3794,7 @@ int b200_groupby_export(b200_groupby* gb, void* out_state, uint32_t* out_groups)
 }
 
 int b200_groupby_import(b200_groupby* gb, const void* state, uint32_t n_slots) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   if (!gb) return B200_INVALID;
   b200_ctx* ctx = gb->ctx;
   if (n_slots == 0) return B200_OK;
@@ -3567,6 +3810,7 @@ int b200_groupby_import(b200_groupby* gb, const void* state, uint32_t n_slots) {
 }
 
 int b200_groupby_merge(b200_groupby* dst, b200_groupby* src) {
+  B200_ENTER(dst ? dst->ctx : nullptr);
   if (!dst || !src) return B200_INVALID;
   b200_ctx* ctx = dst->ctx;
   if (memcmp(&dst->schema, &src->schema, sizeof(GbSchema)) != 0) return b200_fail(ctx, B200_TYPE_ERROR, "groupby_merge: schemas differ");
@@ -3586,6 +3830,7 @@ int b200_groupby_merge(b200_groupby* dst, b200_groupby* src) {
 }
 
 int b200_groupby_finalize(b200_groupby* gb, b200_out_col* out_aggs, b200_out_col* out_keys) {
+  B200_ENTER(gb ? gb->ctx : nullptr);
   if (!gb) return B200_INVALID;
   b200_ctx* ctx = gb->ctx;
   EmitArgs e;
@@ -3618,7 +3863,7 @@ int b200_groupby_finalize(b200_groupby* gb, b200_out_col* out_aggs, b200_out_col
     e.t = gb->table;
     if (gb->pending) {   // slot index = image index; no image is a special slot
       e.t.slots = gb->pending;
-      e.t.cap = ~uint64_t(0);
+      e.t.cap = ~uint64_t(0) - 16;   // cap and cap + 1 (the special slots) match no image index
     }
     e.order = sorted;
   }

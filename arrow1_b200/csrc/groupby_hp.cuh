@@ -47,6 +47,8 @@ struct HpArgs {
   int32_t shift;          // bin = (mix64(key) >> shift) & (bins - 1)
   int32_t bins;
   int32_t has_val;
+  int32_t fast;           // level 1: one key column of `fast` bytes (4 / 8) without nulls, 64-bit value column without
+                          // nulls (or none): straight-line loads, all of a thread's rows in flight together
 };
 
 __device__ __forceinline__ bool hp_row_live(const GbArgs& a, int64_t row) {
@@ -70,16 +72,21 @@ __device__ __forceinline__ uint32_t hp_find_part(const uint32_t* base, uint32_t 
 template <int LEVEL>
 __global__ void __launch_bounds__(kHpThreads) gb_hp_hist_kernel(const __grid_constant__ GbArgs a, const __grid_constant__ HpArgs h) {
   __shared__ uint32_t cnt[kHpMaxBins];
+  __shared__ uint32_t sbase[kHpMaxBins + 1];   // level 2: the partition starts (searched once per tile by every thread)
   const int t = threadIdx.x;
   const uint32_t mask = uint32_t(h.bins - 1);
-  const int64_t n = LEVEL == 2 ? int64_t(h.base[h.parts]) : a.n;
+  if (LEVEL == 2) {
+    for (int i = t; i <= h.parts; i += kHpThreads) sbase[i] = h.base[i];
+    __syncthreads();
+  }
+  const int64_t n = LEVEL == 2 ? int64_t(sbase[h.parts]) : a.n;
   uint32_t held = 0xFFFFFFFFu;   // partition whose counts sit in shared memory
   for (int64_t tile0 = int64_t(blockIdx.x) * kHpTile; tile0 < n; tile0 += int64_t(gridDim.x) * kHpTile) {
     const int64_t tile1 = min(n, tile0 + kHpTile);
     int64_t seg0 = tile0;
-    uint32_t p = LEVEL == 2 ? hp_find_part(h.base, uint32_t(h.parts), uint32_t(tile0)) : 0;
+    uint32_t p = LEVEL == 2 ? hp_find_part(sbase, uint32_t(h.parts), uint32_t(tile0)) : 0;
     while (seg0 < tile1) {
-      const int64_t seg1 = LEVEL == 2 ? min(tile1, int64_t(h.base[p + 1])) : tile1;
+      const int64_t seg1 = LEVEL == 2 ? min(tile1, int64_t(sbase[p + 1])) : tile1;
       if (seg1 > seg0) {
         if (p != held) {
           __syncthreads();
@@ -93,18 +100,38 @@ __global__ void __launch_bounds__(kHpThreads) gb_hp_hist_kernel(const __grid_con
           held = p;
           __syncthreads();
         }
+        if (LEVEL == 2 || h.fast) {
+          uint64_t key[kHpItems];
+          const uint64_t* k64 = LEVEL == 2 ? h.src.keys : reinterpret_cast<const uint64_t*>(a.keys[0].data);
+          const uint32_t* k32 = reinterpret_cast<const uint32_t*>(a.keys[0].data);
+          if (LEVEL == 2 || h.fast == 8) {
 #pragma unroll
-        for (int i = 0; i < kHpItems; ++i) {
-          const int64_t row = seg0 + i * kHpThreads + t;
-          if (row < seg1) {
-            if (LEVEL == 1) {
-              if (hp_row_live(a, row)) {
-                int special;
-                const uint64_t key = load_key(a, row, &special);
-                if (!special) atomicAdd(&cnt[uint32_t(mix64(key) >> h.shift) & mask], 1u);
-              }
-            } else {
-              atomicAdd(&cnt[uint32_t(mix64(h.src.keys[row]) >> h.shift) & mask], 1u);
+            for (int i = 0; i < kHpItems; ++i) {
+              const int64_t row = seg0 + i * kHpThreads + t;
+              key[i] = row < seg1 ? k64[row] : 0;
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < kHpItems; ++i) {
+              const int64_t row = seg0 + i * kHpThreads + t;
+              key[i] = row < seg1 ? uint64_t(k32[row]) : 0;
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < kHpItems; ++i) {
+            const int64_t row = seg0 + i * kHpThreads + t;
+            bool live = row < seg1;
+            if (LEVEL == 1 && live) live = hp_row_live(a, row) && !(h.fast == 8 && key[i] == kEmpty);
+            if (live) atomicAdd(&cnt[uint32_t(mix64(key[i]) >> h.shift) & mask], 1u);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < kHpItems; ++i) {
+            const int64_t row = seg0 + i * kHpThreads + t;
+            if (row < seg1 && hp_row_live(a, row)) {
+              int special;
+              const uint64_t key = load_key(a, row, &special);
+              if (!special) atomicAdd(&cnt[uint32_t(mix64(key) >> h.shift) & mask], 1u);
             }
           }
         }
@@ -163,6 +190,7 @@ struct HpPartSmem {
   uint32_t off[kHpMaxBins];
   uint32_t gbase[kHpMaxBins];
   uint32_t warp_sums[kHpThreads / 32];
+  uint32_t sbase[kHpMaxBins + 1];
   uint32_t deferred;
 };
 
@@ -172,14 +200,18 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_part_kernel(const __grid_
   HpPartSmem& S = *reinterpret_cast<HpPartSmem*>(hp_smem_raw);
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const uint32_t mask = uint32_t(h.bins - 1);
-  const int64_t n = LEVEL == 2 ? int64_t(h.base[h.parts]) : a.n;
+  if (LEVEL == 2) {
+    for (int i = t; i <= h.parts; i += kHpThreads) S.sbase[i] = h.base[i];
+    __syncthreads();
+  }
+  const int64_t n = LEVEL == 2 ? int64_t(S.sbase[h.parts]) : a.n;
   if (t == 0) S.deferred = 0;
   for (int64_t tile0 = int64_t(blockIdx.x) * kHpTile; tile0 < n; tile0 += int64_t(gridDim.x) * kHpTile) {
     const int64_t tile1 = min(n, tile0 + kHpTile);
     int64_t seg0 = tile0;
-    uint32_t p = LEVEL == 2 ? hp_find_part(h.base, uint32_t(h.parts), uint32_t(tile0)) : 0;
+    uint32_t p = LEVEL == 2 ? hp_find_part(S.sbase, uint32_t(h.parts), uint32_t(tile0)) : 0;
     while (seg0 < tile1) {
-      const int64_t seg1 = LEVEL == 2 ? min(tile1, int64_t(h.base[p + 1])) : tile1;
+      const int64_t seg1 = LEVEL == 2 ? min(tile1, int64_t(S.sbase[p + 1])) : tile1;
       if (seg1 > seg0) {
         uint32_t* cursor = h.cursor + size_t(p) * h.bins;
         __syncthreads();   // the previous segment's stores have read S
@@ -188,36 +220,68 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_part_kernel(const __grid_
         // ---- load, bin, rank inside the tile's bin (native ATOMS.ADD with return)
         uint64_t key[kHpItems], val[kHpItems];
         uint32_t r32[kHpItems], meta[kHpItems];   // meta = bin | rank << 16, 0xFFFFFFFF = not staged
+        if (LEVEL == 2 || h.fast) {
+          // straight-line loads: all of the thread's rows are requested before the first is looked at
+          const uint64_t* k64 = LEVEL == 2 ? h.src.keys : reinterpret_cast<const uint64_t*>(a.keys[0].data);
+          const uint32_t* k32 = reinterpret_cast<const uint32_t*>(a.keys[0].data);
+          const uint64_t* vp = LEVEL == 2 ? h.src.vals : reinterpret_cast<const uint64_t*>(a.cols[0].data);
+          if (LEVEL == 2 || h.fast == 8) {
 #pragma unroll
-        for (int i = 0; i < kHpItems; ++i) {
-          const int64_t row = seg0 + i * kHpThreads + t;
-          meta[i] = 0xFFFFFFFFu;
-          key[i] = 0;
-          val[i] = 0;
-          r32[i] = 0;
-          if (row < seg1) {
-            if (LEVEL == 1) {
-              if (hp_row_live(a, row)) {
-                int special;
-                key[i] = load_key(a, row, &special);
-                if (special) {   // the null key / the key equal to the EMPTY sentinel: left to the generic kernel
-                  atomicOr(a.defer_out + (row >> 5), 1u << (row & 31));
-                  atomicAdd(&S.deferred, 1u);
-                } else {
-                  r32[i] = uint32_t(row);
-                  if (h.has_val) {
-                    const Val v = load_val(a.cols[0], row);
-                    val[i] = v.bits;
-                    if (!v.valid) r32[i] |= kHpNullBit;
-                  }
-                  meta[i] = uint32_t(mix64(key[i]) >> h.shift) & mask;
-                }
+            for (int i = 0; i < kHpItems; ++i) {
+              const int64_t row = seg0 + i * kHpThreads + t;
+              key[i] = row < seg1 ? k64[row] : 0;
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < kHpItems; ++i) {
+              const int64_t row = seg0 + i * kHpThreads + t;
+              key[i] = row < seg1 ? uint64_t(k32[row]) : 0;
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < kHpItems; ++i) {
+            const int64_t row = seg0 + i * kHpThreads + t;
+            val[i] = (h.has_val && row < seg1) ? vp[row] : 0;
+            r32[i] = LEVEL == 2 ? (row < seg1 ? h.src.rows[row] : 0u) : uint32_t(row);
+          }
+#pragma unroll
+          for (int i = 0; i < kHpItems; ++i) {
+            const int64_t row = seg0 + i * kHpThreads + t;
+            meta[i] = 0xFFFFFFFFu;
+            bool live = row < seg1;
+            if (LEVEL == 1 && live) {
+              live = hp_row_live(a, row);
+              if (live && h.fast == 8 && key[i] == kEmpty) {   // the key equal to the EMPTY sentinel: generic kernel
+                atomicOr(a.defer_out + (row >> 5), 1u << (row & 31));
+                atomicAdd(&S.deferred, 1u);
+                live = false;
               }
-            } else {
-              key[i] = h.src.keys[row];
-              if (h.has_val) val[i] = h.src.vals[row];
-              r32[i] = h.src.rows[row];
-              meta[i] = uint32_t(mix64(key[i]) >> h.shift) & mask;
+            }
+            if (live) meta[i] = uint32_t(mix64(key[i]) >> h.shift) & mask;
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < kHpItems; ++i) {
+            const int64_t row = seg0 + i * kHpThreads + t;
+            meta[i] = 0xFFFFFFFFu;
+            key[i] = 0;
+            val[i] = 0;
+            r32[i] = 0;
+            if (row < seg1 && hp_row_live(a, row)) {
+              int special;
+              key[i] = load_key(a, row, &special);
+              if (special) {   // the null key / the key equal to the EMPTY sentinel: left to the generic kernel
+                atomicOr(a.defer_out + (row >> 5), 1u << (row & 31));
+                atomicAdd(&S.deferred, 1u);
+              } else {
+                r32[i] = uint32_t(row);
+                if (h.has_val) {
+                  const Val v = load_val(a.cols[0], row);
+                  val[i] = v.bits;
+                  if (!v.valid) r32[i] |= kHpNullBit;
+                }
+                meta[i] = uint32_t(mix64(key[i]) >> h.shift) & mask;
+              }
             }
           }
         }
@@ -284,7 +348,7 @@ struct HpAggSmem {
   uint32_t cnt_null[kHpSlots];
   uint32_t row[kHpSlots];
   uint32_t warp_sums[kHpThreads / 32];
-  uint32_t part;
+  uint32_t part, begin, end;
   uint32_t image_base;
   uint32_t deferred;
 };
@@ -303,7 +367,8 @@ __device__ __forceinline__ void hp_add_u64(uint64_t* acc, uint64_t v) {
 // different CTAs aggregate; the import folds their images together
 __global__ void gb_hp_items_kernel(const uint32_t* base, uint32_t n_parts, uint32_t seg_rows, uint32_t* items) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n_parts) items[i] = (base[i + 1] - base[i] + seg_rows - 1) / seg_rows;
+  // (at least one item per partition: while no partition is cut, item i IS partition i and needs no search)
+  if (i < n_parts) items[i] = max(1u, (base[i + 1] - base[i] + seg_rows - 1) / seg_rows);
 }
 
 // kFloatSum: the value column sums as float64 (ATOMS.CAS.64 loop), else as a wrapping 64-bit integer
@@ -320,7 +385,20 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_c
   if (t == 0 && blockIdx.x == 0) a.counters[7] = item_base[n_parts];   // the host wants to know if a partition was cut
   for (;;) {
     __syncthreads();
-    if (t == 0) S.part = atomicAdd(ticket, 1u);
+    if (t == 0) {
+      // the next work item: one thread walks the dependent loads while the others clear the table
+      const uint32_t item = atomicAdd(ticket, 1u);
+      const uint32_t n_items = item_base[n_parts];
+      uint32_t b = 0, e = 0;
+      if (item < n_items) {
+        const uint32_t p = n_items == n_parts ? item : hp_find_part(item_base, n_parts, item);
+        b = base[p] + (item - item_base[p]) * seg_rows;
+        e = min(base[p + 1], b + seg_rows);
+      }
+      S.part = item < n_items ? item : 0xFFFFFFFFu;
+      S.begin = b;
+      S.end = e;
+    }
     for (int i = t; i < kHpSlots; i += kHpThreads) {
       S.key[i] = kEmpty;
       S.sum[i] = 0;
@@ -329,11 +407,8 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_c
       S.row[i] = 0xFFFFFFFFu;
     }
     __syncthreads();
-    const uint32_t item = S.part;
-    if (item >= item_base[n_parts]) break;
-    const uint32_t p = hp_find_part(item_base, n_parts, item);
-    const uint32_t begin = base[p] + (item - item_base[p]) * seg_rows;
-    const uint32_t end = min(base[p + 1], begin + seg_rows);
+    if (S.part == 0xFFFFFFFFu) break;
+    const uint32_t begin = S.begin, end = S.end;
     constexpr int kU = 4;   // rows per thread in flight: their loads are issued together
     for (uint32_t i0 = begin; i0 < end; i0 += kHpThreads * kU) {
       uint64_t key[kU], v[kU];
@@ -463,10 +538,13 @@ __global__ void __launch_bounds__(256) gb_hp_import_kernel(const __grid_constant
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) {
     const char* ss = src + uint64_t(i) * s.stride;
-    bool claimed;
+    bool claimed = false;
     uint64_t slot_index;
-    char* ds = global_slot(dst, s.stride, *reinterpret_cast<const uint64_t*>(ss), 0, true, &claimed, &slot_index);
-    if (!ds) {
+    const uint64_t key = *reinterpret_cast<const uint64_t*>(ss);
+    char* ds = key == kEmpty ? nullptr : global_slot(dst, s.stride, key, 0, true, &claimed, &slot_index);
+    if (key == kEmpty) {
+      // an unused entry of a fixed-size image list (gb_fused8_kernel)
+    } else if (!ds) {
       atomicExch(counters + 3, 4u);
     } else {
       if (claimed) atomicAdd(&s_new, 1u);

@@ -939,7 +939,9 @@ int run_sort(b200_ctx* ctx, SortParams p, void* scratch, size_t scratch_bytes) {
   p.hist = reinterpret_cast<uint32_t*>(base + L.hist);
   p.info = reinterpret_cast<PassInfo*>(base + L.info);
   p.counters = reinterpret_cast<uint32_t*>(base + L.counters);
-  p.err = reinterpret_cast<uint32_t*>(base + L.err);
+  // the look-back's bail-out flag lives in the context: b200_ctx_synchronize reports it (a preempted or time-sliced
+  // GPU must not turn into a silently wrong permutation)
+  p.err = ctx->async_err;
   p.state = reinterpret_cast<uint32_t*>(base + L.state);
   p.keys[0] = reinterpret_cast<uint64_t*>(base + L.keys0);
   p.keys[1] = reinterpret_cast<uint64_t*>(base + L.keys1);
@@ -949,14 +951,12 @@ int run_sort(b200_ctx* ctx, SortParams p, void* scratch, size_t scratch_bytes) {
   const size_t zero_bytes = L.state + b200_align_up(size_t(p.n_digits) * size_t(p.n_tiles) * kBinStride * 4, 256);
   B200_CUDA(ctx, cudaMemsetAsync(base, 0, std::min(zero_bytes, L.zero_bytes), ctx->stream));
   const int hist_blocks = int(std::min<int64_t>((p.n + kHistTile - 1) / kHistTile, int64_t(ctx->num_sms) * 8));
-  static bool attr_set = false;
   const int smem_wide = int(sizeof(PassSmem<uint64_t>)), smem_narrow = int(sizeof(PassSmem<uint32_t>));
-  if (!attr_set) {
+  if (b200_ctx_once(ctx, 0)) {
     B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_wide));
     B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_wide));
     B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_narrow));
     B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_narrow));
-    attr_set = true;
   }
   // the caller wants the sorted 64-bit keys back: every pass carries them whole
   p.narrow = p.out_keys ? 0 : 1;
@@ -994,6 +994,7 @@ int b200_sort_pairs_scratch_bytes(int64_t length, size_t* out_bytes) {
 
 int b200_sort_indices(b200_ctx* ctx, const b200_col* values, int order, uint64_t index_base,
                       uint64_t* out_indices, void* scratch, size_t scratch_bytes) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   SortParams p;
   memset(&p, 0, sizeof(p));
@@ -1006,6 +1007,7 @@ int b200_sort_indices(b200_ctx* ctx, const b200_col* values, int order, uint64_t
 
 int b200_sort_keys_rows(b200_ctx* ctx, const b200_col* values, int order, uint64_t index_base, uint64_t* out_keys,
                         uint64_t* out_rows) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   SortParams p;
   memset(&p, 0, sizeof(p));
@@ -1029,6 +1031,7 @@ int b200_sort_indices_chunked_scratch_bytes(int64_t total_length, size_t* out_by
 
 int b200_sort_indices_chunked(b200_ctx* ctx, const b200_col* chunks, int n_chunks, int order, uint64_t* out_indices,
                               void* scratch, size_t scratch_bytes) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (n_chunks < 0 || (n_chunks > 0 && !chunks)) return b200_fail(ctx, B200_INVALID, "sort_indices_chunked: bad chunk list");
   int64_t total = 0;
@@ -1075,6 +1078,7 @@ int b200_sort_indices_multi_scratch_bytes(int64_t length, size_t* out_bytes) {
 
 int b200_sort_indices_multi(b200_ctx* ctx, const b200_col* keys, const int* orders, int n_keys, uint64_t* out_indices,
                             void* scratch, size_t scratch_bytes) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (n_keys < 1) return b200_fail(ctx, B200_INVALID, "Must specify one or more sort keys");   // vector_sort.cc:1636
   if (!keys || !orders) return b200_fail(ctx, B200_INVALID, "sort_indices_multi: null argument");
@@ -1129,6 +1133,7 @@ int b200_sort_indices_multi_chunked_scratch_bytes(int64_t total_length, size_t* 
 
 int b200_sort_indices_multi_chunked(b200_ctx* ctx, const b200_col* keys, const int* orders, int n_keys, int n_chunks,
                                     uint64_t* out_indices, void* scratch, size_t scratch_bytes) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (n_keys < 1) return b200_fail(ctx, B200_INVALID, "Must specify one or more sort keys");
   if (n_chunks < 0 || !orders || (n_chunks > 0 && !keys)) return b200_fail(ctx, B200_INVALID, "sort_indices_multi_chunked: bad argument");
@@ -1247,6 +1252,7 @@ int partition_counts_to_host(b200_ctx* ctx, const PartitionPlan& pl, int64_t* ou
 int b200_sort_range_partition(b200_ctx* ctx, const b200_col* values, int order, uint64_t index_base,
                               const uint64_t* splitters, int n_parts, uint64_t* out_keys, uint64_t* out_rows,
                               int64_t* out_counts, void* scratch, size_t scratch_bytes) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (!out_counts) return b200_fail(ctx, B200_INVALID, "sort_range_partition: null out_counts");
   PartitionPlan pl;
@@ -1270,6 +1276,7 @@ int b200_sort_range_partition(b200_ctx* ctx, const b200_col* values, int order, 
 
 int b200_sort_range_partition_count(b200_ctx* ctx, const b200_col* values, int order, const uint64_t* splitters,
                                     int n_parts, int64_t* out_counts, void* scratch, size_t scratch_bytes) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (!out_counts) return b200_fail(ctx, B200_INVALID, "sort_range_partition_count: null out_counts");
   PartitionPlan pl;
@@ -1284,6 +1291,7 @@ int b200_sort_range_partition_push(b200_ctx* ctx, const b200_col* values, int or
                                    const uint64_t* splitters, int n_parts, uint64_t* const* dst_keys,
                                    void* const* dst_rows, const int64_t* dst_offsets, int rows32, void* scratch,
                                    size_t scratch_bytes) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (!dst_keys || !dst_rows || !dst_offsets) return b200_fail(ctx, B200_INVALID, "sort_range_partition_push: null destination table");
   PartitionPlan pl;
@@ -1307,6 +1315,7 @@ int b200_sort_range_partition_push(b200_ctx* ctx, const b200_col* values, int or
 }
 
 int b200_peer_alloc(b200_ctx* ctx, size_t bytes, void** out_ptr) {
+  B200_ENTER(ctx);
   if (!ctx || !out_ptr) return B200_INVALID;
   *out_ptr = nullptr;
   B200_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -1314,11 +1323,13 @@ int b200_peer_alloc(b200_ctx* ctx, size_t bytes, void** out_ptr) {
   return B200_OK;
 }
 int b200_peer_free(b200_ctx* ctx, void* ptr) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (ptr) B200_CUDA(ctx, cudaFree(ptr));
   return B200_OK;
 }
 int b200_peer_export(b200_ctx* ctx, void* ptr, unsigned char* out_handle) {
+  B200_ENTER(ctx);
   if (!ctx || !ptr || !out_handle) return B200_INVALID;
   static_assert(sizeof(cudaIpcMemHandle_t) == B200_PEER_HANDLE_BYTES, "IPC handle size");
   cudaIpcMemHandle_t h;
@@ -1327,6 +1338,7 @@ int b200_peer_export(b200_ctx* ctx, void* ptr, unsigned char* out_handle) {
   return B200_OK;
 }
 int b200_peer_open(b200_ctx* ctx, const unsigned char* handle, void** out_ptr) {
+  B200_ENTER(ctx);
   if (!ctx || !handle || !out_ptr) return B200_INVALID;
   cudaIpcMemHandle_t h;
   memcpy(&h, handle, sizeof(h));
@@ -1336,17 +1348,20 @@ int b200_peer_open(b200_ctx* ctx, const unsigned char* handle, void** out_ptr) {
   return B200_OK;
 }
 int b200_peer_close(b200_ctx* ctx, void* ptr) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (ptr) B200_CUDA(ctx, cudaIpcCloseMemHandle(ptr));
   return B200_OK;
 }
 
 int b200_sort_keys(b200_ctx* ctx, const b200_col* values, int order, uint64_t* out_keys) {
+  B200_ENTER(ctx);
   return b200_sort_keys_rows(ctx, values, order, 0, out_keys, nullptr);
 }
 
 int b200_sort_pairs(b200_ctx* ctx, const uint64_t* keys, const uint64_t* payload, int64_t length,
                     uint64_t* out_keys, uint64_t* out_payload, void* scratch, size_t scratch_bytes) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (length < 0) return b200_fail(ctx, B200_INVALID, "sort_pairs: negative length");
   if (length == 0) return B200_OK;
@@ -1366,6 +1381,7 @@ int b200_sort_pairs(b200_ctx* ctx, const uint64_t* keys, const uint64_t* payload
 
 int b200_sort_pairs32(b200_ctx* ctx, const uint64_t* keys, const uint32_t* payload32, int64_t length,
                       uint64_t* out_keys, uint64_t* out_payload, void* scratch, size_t scratch_bytes) {
+  B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
   if (length < 0) return b200_fail(ctx, B200_INVALID, "sort_pairs32: negative length");
   if (length == 0) return B200_OK;

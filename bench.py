@@ -365,6 +365,8 @@ class Q1WL(Workload):
     def step(self, ctx, cols_, bufs):
         from arrow1_b200 import compute
         ship, rf, ls, qty, price, disc = cols_
+        if self.fused == "one_pass":
+            return compute.Q1PipelineFused(ship, rf, ls, [qty, price, disc], ctx)
         if self.fused:
             return compute.Q1PipelineSelected(ship, rf, ls, [qty, price, disc], ctx)
         return compute.Q1Pipeline(ship, rf, ls, [qty, price, disc], ctx)
@@ -405,6 +407,14 @@ def make_workload(name, rows=None):
         w = Q1WL(rows or 600_000_000)
         w.fused, w.name = True, "q1_selected"
         w.description += "; Filter folded into the aggregation (b200_groupby_consume_selected)"
+        return w
+    if name == "q1_fused":
+        w = Q1WL(rows or 600_000_000)
+        w.fused, w.name, w.kernel = "one_pass", "q1_fused", "groupby_fused"
+        w.description = w.description.replace("; unfused (each operation reads and writes HBM)",
+                                              "; predicate, price*(1-discount) and the 7 aggregates in ONE pass over the 6 input columns "
+                                              "(b200_groupby_consume_fused, 30 B/row)")
+        w.alg_bytes_per_launch = lambda launches_per_step, n=w.n: n * 30 / max(launches_per_step, 1)
         return w
     if name == "sort_i64":
         return SortWL(rows or 100_000_000, "int64")
@@ -491,7 +501,7 @@ def host_threads():
 
 def cpu_sample_rows(wl, threads):
     per_thread = {"sort_i64": 2_000_000, "sort_f64": 2_000_000, "filter": 16_000_000, "filter_10m": 10_000_000,
-                  "groupby_c3": 8_000_000, "groupby_c4": 4_000_000, "take_sorted": 2_000_000, "sort_2keys": 2_000_000, "q1": 4_000_000, "q1_selected": 4_000_000}[wl.name]
+                  "groupby_c3": 8_000_000, "groupby_c4": 4_000_000, "take_sorted": 2_000_000, "sort_2keys": 2_000_000, "q1": 4_000_000, "q1_selected": 4_000_000, "q1_fused": 4_000_000}[wl.name]
     return min(per_thread, wl.n)
 
 
@@ -564,7 +574,7 @@ def kernel_times(ctx, names):
 
 
 ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume", "compare_scalar", "arithmetic", "take", "partition_plan", "partition_scatter", "sort_partition",
-               "groupby_partition", "groupby_import")
+               "groupby_partition", "groupby_import", "groupby_fused")
 
 
 def time_device(ctx, wl, cols_, steps, warmup, world, dist_step=None):
@@ -745,7 +755,7 @@ def gpu_arm(args):
     if rank == 0 and world == 1 and not args.no_extras:
         del cols_, bufs
         torch.cuda.empty_cache()
-        for name in ("filter", "filter_10m", "sort_i64", "sort_f64", "sort_2keys", "take_sorted", "groupby_c3", "groupby_c4", "q1", "q1_selected"):
+        for name in ("filter", "filter_10m", "sort_i64", "sort_f64", "sort_2keys", "take_sorted", "groupby_c3", "groupby_c4", "q1", "q1_selected", "q1_fused"):
             if name == wl.name:
                 continue
             try:

@@ -96,7 +96,13 @@ typedef struct b200_ctx b200_ctx;
 B200_API int b200_ctx_create(int device, void* cu_stream, b200_ctx** out);
 B200_API int b200_ctx_destroy(b200_ctx* ctx);
 B200_API int b200_ctx_set_stream(b200_ctx* ctx, void* cu_stream);
+/* Waits for the context's stream.  Also the point where a kernel that had to give up is reported: the sort's
+ * decoupled look-back bails out instead of spinning forever when a preceding tile never publishes (a preempted or
+ * time-sliced GPU) and flags the context; synchronize then returns B200_UNKNOWN_ERROR and clears the flag.  Callers
+ * that consume results through their own stream synchronisation should call this once per batch of work. */
 B200_API int b200_ctx_synchronize(b200_ctx* ctx);
+/* test hook: sets the flag b200_ctx_synchronize reports */
+B200_API int b200_ctx_inject_async_error(b200_ctx* ctx, uint32_t code);
 /* message of the last failure on this context ("" if none); valid until the next call */
 B200_API const char* b200_last_error(b200_ctx* ctx);
 /* number of kernels this context has launched since creation (bench.py's gpu_launches) */
@@ -346,6 +352,34 @@ B200_API int b200_groupby_consume_rows(b200_groupby* gb, const b200_col* keys, c
  * of b200_compare_scalar.  Group order is the first-occurrence order of the selected rows, as after a Filter. */
 B200_API int b200_groupby_consume_selected(b200_groupby* gb, const b200_col* keys, const b200_col* args,
                                            uint64_t row_base, const void* selection);
+/* Compare -> filter -> derive -> aggregate in one call (the Q1 shape of config C5).  Upstream this
+ * is four operations over whole columns: a comparison (compute/kernels/scalar_compare.cc) producing the mask, Filter
+ * of every used column (vector_selection.cc:1776-1866), "multiply" / "subtract" for the derived measures
+ * (scalar_arithmetic.cc:69-190) and GroupBy (hash_aggregate.cc:890-966).  Here:
+ *   args[j]    the argument of aggregate j: a column (kind 0), or `a op1 (scalar op2 b)` over float64 columns
+ *              (kind 1; e.g. extendedprice * (1 - discount) = {MULTIPLY, SUBTRACT, a = price, scalar = 1, b = discount}),
+ *              each operation a single IEEE operation as in b200_arithmetic, validity = a's AND b's
+ *   predicate  nullable; rows with `column OP *scalar` false do not exist (== Filter(DROP) of every column by the
+ *              comparison's result).  The predicate column must hold no nulls.
+ * The result is that of the four operations run one after the other (group order included).  For <= 8 expected
+ * groups, byte-wide keys and float64 arguments without nulls every input byte is read exactly once
+ * (gb_fused8_kernel); other shapes are evaluated through b200_compare_scalar / b200_arithmetic /
+ * b200_groupby_consume_selected internally. */
+typedef struct b200_fused_arg {
+  int32_t kind;     /* 0 = column a; 1 = a op1 (scalar op2 b) */
+  int32_t op1, op2; /* b200_arith_op */
+  int32_t reserved;
+  b200_col a, b;
+  double scalar;
+} b200_fused_arg;
+typedef struct b200_predicate {
+  b200_col column;
+  int32_t op;          /* 0 equal, 1 not_equal, 2 greater, 3 greater_equal, 4 less, 5 less_equal */
+  int32_t reserved;
+  const void* scalar;  /* HOST pointer to one value of the column's type */
+} b200_predicate;
+B200_API int b200_groupby_consume_fused(b200_groupby* gb, const b200_col* keys, const b200_fused_arg* args,
+                                        uint64_t row_base, const b200_predicate* predicate /* nullable */);
 /* global first-occurrence row of every group, in output (group id) order: device uint64[num_groups].
  * Lets ranks holding disjoint key sets restore the reference's global group order
  * (hash_aggregate.cc:391-403) by ranking their groups on it. */

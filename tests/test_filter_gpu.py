@@ -130,3 +130,33 @@ def test_filter_idempotent_with_all_true_mask(ctx):
     assert a.length == n
     np.testing.assert_array_equal(a.valid, values.valid())
     np.testing.assert_array_equal(a.values.view(np.uint64), values.values().view(np.uint64))
+
+
+def test_filter_apply_rejects_small_output_and_sync_reports_it(ctx):
+    """an output smaller than the plan's length is never written past; the context reports it at the next
+    synchronisation (B200_UNKNOWN_ERROR), once.  Same channel as the sort's look-back bail-out (injected here)."""
+    import ctypes as C
+    import torch
+    from arrow1_b200 import capi
+    from arrow1_b200.capi import B200Error
+    rng = np.random.default_rng(3)
+    n = 100_000
+    values = Column.from_numpy(rng.integers(0, 1 << 40, size=n, dtype=np.int64)).to_device()
+    mask = Column.from_numpy(rng.random(n) < 0.5).to_device()
+    plan = capi.FilterPlan(ctx, mask, 0, sync=True)
+    assert plan.out_length > 1000
+    small = 1000
+    out = torch.full((small * 8 + 4096,), 0x5A, dtype=torch.uint8, device="cuda")
+    v, m = values.desc(), mask.desc()
+    ctx.check(capi.lib().b200_filter_apply(ctx._h, C.byref(v), C.byref(m), C.c_int(0), C.c_void_p(plan.buf.data_ptr()),
+                                           C.c_void_p(out.data_ptr()), None, C.c_int64(small)))
+    with pytest.raises(B200Error) as e:
+        ctx.synchronize()
+    assert e.value.code == 9 and "filter output" in str(e.value)
+    assert bool((out == 0x5A).all()), "nothing may be written when the output is too small"
+    ctx.synchronize()   # the flag is cleared by the report
+    ctx.check(capi.lib().b200_ctx_inject_async_error(ctx._h, C.c_uint32(1)))
+    with pytest.raises(B200Error) as e:
+        ctx.synchronize()
+    assert "look-back" in str(e.value)
+    ctx.synchronize()

@@ -77,6 +77,57 @@ def test_q1_pipeline_matches_oracle(ctx, n):
     got2 = compute.Q1PipelineSelected(ship, rf, ls, [qty, price, disc], ctx)
     a2 = GroupRes(got2.num_groups, [[_host(c) for c in ag] for ag in got2.aggs], [_host(k) for k in got2.keys])
     assert_group_equal(a2, b, [s for _, s in specs], rtol=1e-12)
+    # everything in one pass over the inputs (b200_groupby_consume_fused; below 8192 rows through the separate operations)
+    got3 = compute.Q1PipelineFused(ship, rf, ls, [qty, price, disc], ctx)
+    a3 = GroupRes(got3.num_groups, [[_host(c) for c in ag] for ag in got3.aggs], [_host(k) for k in got3.keys])
+    assert_group_equal(a3, b, [s for _, s in specs], rtol=1e-12)
+    # counts, keys and group order of the fused and the unfused form are the same bits
+    for x, y in zip(a3.keys, a.keys):
+        np.testing.assert_array_equal(x[0], y[0])
+    np.testing.assert_array_equal(a3.aggs[6][0][0], a.aggs[6][0][0])
+
+
+@pytest.mark.parametrize("shape", ["fast", "nine_groups", "int_keys_nulls", "no_predicate"])
+def test_groupby_consume_fused_equals_separate_operations(ctx, shape):
+    """b200_groupby_consume_fused == compare_scalar -> Filter(DROP) of every column -> arithmetic -> GroupBy, for the
+    one-pass kernel's shape, for a 9th group (the kernel gives up, the call is redone unfused), for other key types and
+    nullable arguments (evaluated through the separate operations), and without a predicate."""
+    rng = np.random.default_rng(hash(shape) % 1000)
+    n = 300_000
+    groups = 9 if shape == "nine_groups" else 6
+    if shape == "int_keys_nulls":
+        k0 = Column.from_numpy(rng.integers(0, 50, size=n).astype(np.int32), rng.random(n) > 0.05)
+        k1 = Column.from_numpy(rng.integers(0, 3, size=n).astype(np.uint8))
+        hint = 200
+    else:
+        k0 = Column.from_numpy(rng.integers(0, groups, size=n).astype(np.uint8))
+        k1 = Column.from_numpy(np.zeros(n, dtype=np.uint8) + 7)
+        hint = 8
+    nulls = shape == "int_keys_nulls"
+    x = Column.from_numpy(rng.random(n) * 1e3, (rng.random(n) > 0.1) if nulls else None)
+    y = Column.from_numpy(rng.random(n), (rng.random(n) > 0.1) if nulls else None)
+    date = Column.from_numpy(rng.integers(0, 1000, size=n).astype(np.int32))
+    pred = None if shape == "no_predicate" else (date, "greater", 300)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MEAN), AggSpec(cols.HASH_COUNT), AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MEAN)]
+    gb = capi.GroupBy(ctx, [k0.type, k1.type], aggs, [cols.DOUBLE] * 5, hint)
+    dk0, dk1, dx, dy, dd = (c.to_device() for c in (k0, k1, x, y, date))
+    derived = ("add", dx, "multiply", 2.5, dy)
+    gb.consume_fused([dk0, dk1], [dx, dy, dx, derived, derived], None if pred is None else (dd, pred[1], pred[2]))
+    got = gb.finalize()
+    gb.close()
+    keep = np.ones(n, dtype=bool) if pred is None else (date.values() > 300)
+    idx = np.flatnonzero(keep)
+
+    def filt(c):
+        return Column.from_numpy(c.values()[idx].copy(), c.valid()[idx].copy() if c.validity is not None else None)
+
+    fx, fy = filt(x), filt(y)
+    dv = fx.values() + 2.5 * fy.values()
+    fd = Column.from_numpy(dv, (fx.valid() & fy.valid()) if nulls else None)
+    want = oracle.groupby([filt(k0), filt(k1)], aggs, [fx, fy, fx, fd, fd], kind=ORACLE)
+    a = GroupRes(got.num_groups, [[_host(c) for c in ag] for ag in got.aggs], [_host(k) for k in got.keys])
+    b = GroupRes(want.num_groups, want.aggs, want.keys)
+    assert_group_equal(a, b, aggs, rtol=1e-12)
 
 
 NP_ARITH = {"add": np.add, "subtract": np.subtract, "multiply": np.multiply}
