@@ -206,6 +206,24 @@ int b200_ctx_set_stream(b200_ctx* ctx, void* cu_stream) {
 int b200_ctx_synchronize(b200_ctx* ctx) {
   B200_ENTER(ctx);
   if (!ctx) return B200_INVALID;
+  // the word kernels set when they had to give up rides back with the synchronisation
+  B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 63, ctx->async_err, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  const uint32_t err = *reinterpret_cast<const uint32_t*>(ctx->host_words + 63);
+  if (err != 0) {
+    B200_CUDA(ctx, cudaMemsetAsync(ctx->async_err, 0, sizeof(uint32_t), ctx->stream));
+    return b200_fail(ctx, B200_UNKNOWN_ERROR, "a kernel on this context gave up (code %u: %s); results since the last synchronisation are invalid",
+                     err,
+                     err == 1 ? "sort look-back timed out waiting for a preceding tile"
+                              : (err == 2 ? "filter output buffers smaller than the plan's output length" : "injected"));
+  }
+  return B200_OK;
+}
+
+int b200_ctx_inject_async_error(b200_ctx* ctx, uint32_t code) {
+  B200_ENTER(ctx);
+  if (!ctx) return B200_INVALID;
+  B200_CUDA(ctx, cudaMemcpyAsync(ctx->async_err, &code, sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
   B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return B200_OK;
 }
