@@ -2521,6 +2521,9 @@ struct b200_groupby {
   // at 10^8 expected groups it is a 17 GB array to initialise, fill and scan.
   char* pending = nullptr;
   uint32_t pending_n = 0;
+  // upper bound of every global row number consumed so far (2^64-1 once unknown): first rows below 2^32 are ranked
+  // by a sort that carries 32-bit keys
+  uint64_t row_bound = 0;
   // high-cardinality path (groupby_hp.cuh): partition buffers, and the sizes from which it is taken
   void* hp_tmp = nullptr;
   size_t hp_bytes = 0;
@@ -2816,7 +2819,7 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
   uint32_t c[4];
   B200_RETURN_NOT_OK(read_counters(gb, c));
   *deferred = c[1];
-  const uint32_t n_images = reinterpret_cast<const uint32_t*>(ctx->host_words + 16)[6];
+  const uint32_t n_images = std::min(reinterpret_cast<const uint32_t*>(ctx->host_words + 16)[6], image_cap);
   const uint32_t n_items = reinterpret_cast<const uint32_t*>(ctx->host_words + 16)[7];
   *handled = true;
   if (gb->groups == 0 && c[1] == 0 && n_items <= parts && n_images > 0) {
@@ -3231,6 +3234,7 @@ static int groupby_consume_impl(b200_groupby* gb, const b200_col* keys, const b2
   a.row_base = row_base;
   a.row_ids = row_ids;
   a.select = select;
+  gb->row_bound = row_ids ? ~uint64_t(0) : std::max(gb->row_bound, row_base + uint64_t(a.n));
   // Several distinct argument columns at low cardinality (the Q1 shape): aggregates over different columns
   // are independent, so the batch is consumed once per column with the binned single-column kernel — the
   // key columns are re-read (2 B/row for Q1) instead of funnelling every column's float sums through CAS
@@ -3287,33 +3291,39 @@ int try_fused8(b200_groupby* gb, const b200_col* keys, const b200_fused_arg* arg
   memset(&a, 0, sizeof(a));
   a.s = s;
   B200_RETURN_NOT_OK(fill_keys(gb, keys, &a));
-  for (int j = 0; j < s.n_aggs; ++j) {
-    const b200_fused_arg& g = args[j];
-    if (s.aggs[j].kind == B200_HASH_MIN_MAX) return B200_OK;
-    if (g.a.type != B200_DOUBLE || col_has_nulls(g.a) || g.a.length != n) return B200_OK;
-    if (g.kind == 1 && (g.b.type != B200_DOUBLE || col_has_nulls(g.b) || g.b.length != n)) return B200_OK;
-    FusedStream st;
-    memset(&st, 0, sizeof(st));
-    st.kind = g.kind;
-    st.ia = col_index(g.a);
-    st.ib = g.kind == 1 ? col_index(g.b) : 0;
-    if (st.ia < 0 || st.ib < 0) return B200_OK;
-    st.op1 = g.op1;
-    st.op2 = g.op2;
-    st.scalar = g.scalar;
-    int found = -1;
-    for (int q = 0; q < f.n_streams; ++q) {
-      const FusedStream& o = f.streams[q];
-      if (o.kind == st.kind && o.ia == st.ia && (st.kind == 0 || (o.ib == st.ib && o.op1 == st.op1 && o.op2 == st.op2 &&
-                                                                  memcmp(&o.scalar, &st.scalar, sizeof(double)) == 0)))
-        found = q;
+  // streams: the plain columns first (stream i reads column i), then the derived arguments
+  for (int pass = 0; pass < 2; ++pass) {
+    for (int j = 0; j < s.n_aggs; ++j) {
+      const b200_fused_arg& g = args[j];
+      if (g.kind != pass) continue;
+      if (s.aggs[j].kind == B200_HASH_MIN_MAX) return B200_OK;
+      if (g.a.type != B200_DOUBLE || col_has_nulls(g.a) || g.a.length != n) return B200_OK;
+      if (g.kind == 1 && (g.b.type != B200_DOUBLE || col_has_nulls(g.b) || g.b.length != n)) return B200_OK;
+      FusedStream st;
+      memset(&st, 0, sizeof(st));
+      st.kind = g.kind;
+      st.ia = col_index(g.a);
+      st.ib = g.kind == 1 ? col_index(g.b) : 0;
+      if (st.ia < 0 || st.ib < 0) return B200_OK;
+      st.op1 = g.op1;
+      st.op2 = g.op2;
+      st.scalar = g.scalar;
+      int found = -1;
+      for (int q = 0; q < f.n_streams; ++q) {
+        const FusedStream& o = f.streams[q];
+        if (o.kind == st.kind && o.ia == st.ia && (st.kind == 0 || (o.ib == st.ib && o.op1 == st.op1 && o.op2 == st.op2 &&
+                                                                    memcmp(&o.scalar, &st.scalar, sizeof(double)) == 0)))
+          found = q;
+      }
+      if (found < 0) {
+        if (f.n_streams == kFusedStreams) return B200_OK;
+        f.streams[f.n_streams] = st;
+        found = f.n_streams++;
+      }
+      a.s.aggs[j].col = found;
     }
-    if (found < 0) {
-      if (f.n_streams == kFusedStreams) return B200_OK;
-      f.streams[f.n_streams] = st;
-      found = f.n_streams++;
-    }
-    a.s.aggs[j].col = found;
+    // (during pass 0 every new column comes with its own new plain stream, so stream i reads column i)
+    if (pass == 0) f.n_plain = f.n_streams;
   }
   if (pred) {
     f.pred_data = reinterpret_cast<const char*>(pred->column.data) + pred->column.offset * 4;
@@ -3328,6 +3338,7 @@ int try_fused8(b200_groupby* gb, const b200_col* keys, const b200_fused_arg* arg
   a.rows_per_block = int(rpb);
   a.row_base = row_base;
   a.n_cols = f.n_streams;
+  gb->row_bound = std::max(gb->row_bound, row_base + uint64_t(n));
   const uint32_t n_images = uint32_t(grid) * kTinyGroups;
   B200_RETURN_NOT_OK(gb_reserve_tmp(gb, size_t(n_images) * s.stride + 512));
   f.overflow = reinterpret_cast<uint32_t*>(gb->tmp);
@@ -3592,6 +3603,7 @@ int b200_grouper_consume(b200_groupby* gb, const b200_col* keys, uint32_t* out_i
   // row indices continue across calls so that first-occurrence order is global
   a.row_base = gb->dense_rows;
   gb->dense_rows += uint64_t(n);
+  gb->row_bound = std::max(gb->row_bound, gb->dense_rows);
   // make room up front: a rehash in the middle of a batch would invalidate positional slot ids
   {
     uint32_t c[4];
@@ -3799,6 +3811,7 @@ int b200_groupby_import(b200_groupby* gb, const void* state, uint32_t n_slots) {
   b200_ctx* ctx = gb->ctx;
   if (n_slots == 0) return B200_OK;
   if (!state) return b200_fail(ctx, B200_INVALID, "groupby_import: null state");
+  gb->row_bound = ~uint64_t(0);
   B200_RETURN_NOT_OK(materialize(gb));
   uint32_t c[4];
   B200_RETURN_NOT_OK(read_counters(gb, c));
@@ -3815,6 +3828,7 @@ int b200_groupby_merge(b200_groupby* dst, b200_groupby* src) {
   b200_ctx* ctx = dst->ctx;
   if (memcmp(&dst->schema, &src->schema, sizeof(GbSchema)) != 0) return b200_fail(ctx, B200_TYPE_ERROR, "groupby_merge: schemas differ");
   if (dst->ctx != src->ctx) return b200_fail(ctx, B200_INVALID, "groupby_merge: handles belong to different contexts");
+  dst->row_bound = std::max(dst->row_bound, src->row_bound);
   B200_RETURN_NOT_OK(materialize(dst));
   B200_RETURN_NOT_OK(materialize(src));
   uint32_t c[4];
@@ -3859,7 +3873,10 @@ int b200_groupby_finalize(b200_groupby* gb, b200_out_col* out_aggs, b200_out_col
     uint64_t* sorted = reinterpret_cast<uint64_t*>(extra);
     e.null_counts = reinterpret_cast<uint32_t*>(extra + arr);
     void* sort_scratch = extra + arr + 4096;
-    if (G > 0) B200_RETURN_NOT_OK(b200_sort_pairs(ctx, first_rows, slot_idx, G, nullptr, sorted, sort_scratch, sort_bytes));
+    // pending images: slot index == position, so the sort emits the permutation itself (no gather of a payload)
+    const int row_bits = gb->row_bound <= (uint64_t(1) << 32) ? 32 : 64;
+    if (G > 0)
+      B200_RETURN_NOT_OK(b200_sort_pairs_bits(ctx, first_rows, gb->pending ? nullptr : slot_idx, G, row_bits, sorted, sort_scratch, sort_bytes));
     e.t = gb->table;
     if (gb->pending) {   // slot index = image index; no image is a special slot
       e.t.slots = gb->pending;

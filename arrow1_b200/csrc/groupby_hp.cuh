@@ -477,18 +477,18 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_c
       total += ws;
     }
     if (t == 0) {
-      // all or nothing: a hole in the image list would be imported as a group
-      uint32_t old = *reinterpret_cast<volatile uint32_t*>(a.counters + 6);
-      uint32_t got = 0xFFFFFFFFu;
-      while (total && uint64_t(old) + total <= image_cap) {
-        const uint32_t prev = atomicCAS(a.counters + 6, old, old + total);
-        if (prev == old) {
-          got = old;
-          break;
+      // one atomicAdd (a CAS loop on this counter, contended by every CTA, cost ~7 L2 round trips per item with
+      // all other warps waiting at the barrier).  When the list is full the part of the claim that lies inside it
+      // is filled with EMPTY keys, which the import skips.
+      uint32_t got = 0;
+      if (total) {
+        got = atomicAdd(a.counters + 6, total);
+        if (uint64_t(got) + total > image_cap) {
+          for (uint32_t i = got; i < image_cap; ++i) *reinterpret_cast<uint64_t*>(images + size_t(i) * a.s.stride) = kEmpty;
+          got = 0xFFFFFFFFu;
         }
-        old = prev;
       }
-      S.image_base = total ? got : 0;
+      S.image_base = got;
     }
     __syncthreads();
     const uint32_t ibase = S.image_base;

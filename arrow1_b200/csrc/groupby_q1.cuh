@@ -30,6 +30,8 @@ struct FusedArgs {
   const double* cols[kFusedCols];
   FusedStream streams[kFusedStreams];
   int32_t n_cols, n_streams;
+  int32_t n_plain;         // streams [0, n_plain) are the columns [0, n_plain) as they are (no operand selection per
+                           // row); the derived streams follow and pick their operands among all columns
   const void* pred_data;   // nullable: 4-byte predicate column (shifted by its offset)
   int32_t pred_type;       // B200_INT32 / B200_UINT32
   int32_t pred_op;         // kCmp* order of b200_compare_scalar: 0 eq, 1 ne, 2 gt, 3 ge, 4 lt, 5 le
@@ -145,10 +147,11 @@ __global__ void __launch_bounds__(kTinyThreads, 3) gb_fused8_kernel(const __grid
         const int ga = g >= 0 ? g : 0;
 #pragma unroll
         for (int s = 0; s < NS; ++s) {
-          const FusedStream& st = f.streams[s];
-          const double va = fused_pick(st.ia, c[u]);
-          double v = va;
-          if (st.kind == 1) v = fused_arith(st.op1, va, fused_arith(st.op2, st.scalar, fused_pick(st.ib, c[u])));
+          double v = c[u][s];   // plain stream s reads column s
+          if (s >= f.n_plain) {
+            const FusedStream& st = f.streams[s];
+            v = fused_arith(st.op1, fused_pick(st.ia, c[u]), fused_arith(st.op2, st.scalar, fused_pick(st.ib, c[u])));
+          }
           S.acc[ga][s][t] = __dadd_rn(S.acc[ga][s][t], add ? v : -0.0);
         }
         S.cnt[ga][t] += add ? 1u : 0u;

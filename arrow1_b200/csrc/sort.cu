@@ -1379,6 +1379,25 @@ int b200_sort_pairs(b200_ctx* ctx, const uint64_t* keys, const uint64_t* payload
   return run_sort(ctx, p, scratch, scratch_bytes);
 }
 
+int b200_sort_pairs_bits(b200_ctx* ctx, const uint64_t* keys, const uint64_t* payload, int64_t length, int key_bits,
+                         uint64_t* out_payload, void* scratch, size_t scratch_bytes) {
+  B200_ENTER(ctx);
+  if (!ctx) return B200_INVALID;
+  if (length < 0 || key_bits < 1 || key_bits > 64) return b200_fail(ctx, B200_INVALID, "sort_pairs_bits: bad argument");
+  if (length == 0) return B200_OK;
+  if (!keys || !out_payload) return b200_fail(ctx, B200_INVALID, "sort_pairs_bits: null argument");
+  SortParams p;
+  memset(&p, 0, sizeof(p));
+  p.keys_in = keys;
+  p.n = length;
+  p.n_digits = (key_bits + 7) / 8;   // the digits above are zero by the caller's word: not read, not sorted
+  p.cls_digit = -1;
+  p.wmask = ~uint64_t(0);
+  p.gather = payload;
+  p.out_idx = out_payload;
+  return run_sort(ctx, p, scratch, scratch_bytes);
+}
+
 int b200_sort_pairs32(b200_ctx* ctx, const uint64_t* keys, const uint32_t* payload32, int64_t length,
                       uint64_t* out_keys, uint64_t* out_payload, void* scratch, size_t scratch_bytes) {
   B200_ENTER(ctx);

@@ -381,7 +381,8 @@ class Q1WL(Workload):
             d, b = compute._h2d(c, ctx)
             dev.append(d)
             nbytes += b
-        out = compute.Q1Pipeline(dev[0], dev[1], dev[2], dev[3:], ctx)
+        fn = {False: compute.Q1Pipeline, True: compute.Q1PipelineSelected, "one_pass": compute.Q1PipelineFused}[self.fused]
+        out = fn(dev[0], dev[1], dev[2], dev[3:], ctx)
         d2h = 0
         for cols__ in out.aggs + [out.keys]:
             for c in cols__:
@@ -499,30 +500,41 @@ def host_threads():
         return max(1, os.cpu_count() or 1)
 
 
-def cpu_sample_rows(wl, threads):
-    per_thread = {"sort_i64": 2_000_000, "sort_f64": 2_000_000, "filter": 16_000_000, "filter_10m": 10_000_000,
-                  "groupby_c3": 8_000_000, "groupby_c4": 4_000_000, "take_sorted": 2_000_000, "sort_2keys": 2_000_000, "q1": 4_000_000, "q1_selected": 4_000_000, "q1_fused": 4_000_000}[wl.name]
-    return min(per_thread, wl.n)
+# rows up to which the CPU arm processes the WHOLE configuration (P shards of rows / P each); above it a bounded sample
+CPU_FULL_ROWS = 200_000_000
+CPU_SAMPLE_PER_THREAD = {"groupby_c3": 8_000_000, "groupby_c4": 4_000_000, "q1": 4_000_000, "q1_selected": 4_000_000,
+                         "q1_fused": 4_000_000}
+
+
+def cpu_shard_rows(wl, threads):
+    """(rows per shard, whole configuration?)  SURVEY §8(d): P shards of the SAME rows, rows / P each."""
+    if wl.n <= CPU_FULL_ROWS:
+        return (wl.n + threads - 1) // threads, True
+    return min(CPU_SAMPLE_PER_THREAD.get(wl.name, 4_000_000), wl.n), False
 
 
 def run_cpu(wl, steps, warmup, threads):
-    """Times the reference's CPU kernels on `threads` independent row-range shards (the kernels
-    are single-threaded by construction, compute/exec.h:86-92): rows/s = rows of all shards / time.
-    Sort and group-by shards are not merged, i.e. an upper bound for the CPU."""
+    """Times the reference's CPU kernels on `threads` row-range shards (the kernels are single-threaded by
+    construction, compute/exec.h:86-92), one reference call per shard and step on its own host thread:
+    rows/s = rows of all shards / time.  Up to CPU_FULL_ROWS the shards cover the whole configuration (100 M rows
+    for the sort: P shards of 100 M / P rows); the 600 M - 1 B row configurations are sampled.  Sort and group-by
+    shards are not merged, i.e. an upper bound for the CPU."""
     import oracle
     from arrow1_b200 import synth
     kind = "reference" if oracle.have_reference() else "port"
     if kind == "port":
         oracle.build()
-    per = cpu_sample_rows(wl, threads)
+    per, full = cpu_shard_rows(wl, threads)
     gen = synth.Gen(None)
-    shards = [wl.make(gen, start=i * per, n=per) for i in range(threads)]
-    sub = make_workload(wl.name, per)
+    bounds = [(i * per, min(per, wl.n - i * per)) for i in range(threads) if i * per < wl.n] if full else \
+             [(i * per, per) for i in range(threads)]
+    shards = [wl.make(gen, start=lo, n=ln) for lo, ln in bounds]
+    subs = {ln: make_workload(wl.name, ln) for _, ln in bounds}
     pool = ThreadPoolExecutor(max_workers=threads)
 
     def one():
         t0 = time.perf_counter()
-        list(pool.map(lambda cols_: sub.cpu_step(oracle, kind, cols_), shards))
+        list(pool.map(lambda x: subs[x[0][1]].cpu_step(oracle, kind, x[1]), zip(bounds, shards)))
         return time.perf_counter() - t0
 
     for _ in range(warmup):
@@ -530,27 +542,38 @@ def run_cpu(wl, steps, warmup, threads):
     times = [one() for _ in range(steps)]
     pool.shutdown()
     total = sum(times)
-    rows = per * threads
+    rows = sum(ln for _, ln in bounds)
+    what = ("the whole configuration: %d rows as %d row-range shards of %d rows" % (rows, len(bounds), per)) if full else \
+           ("a bounded sample: %d shards x %d rows of the %d-row configuration" % (len(bounds), per, wl.n))
     return {"rows_per_s": rows * steps / total, "ms_per_step": 1e3 * total / steps, "kind": kind, "cores": threads,
-            "sample": "%d independent shards x %d rows of the %s columns (same generator), one reference call per shard "
-                      "per step, %d steps; shards not merged" % (threads, per, wl.name, steps)}
+            "rows": rows, "full_config": full,
+            "sample": "%s (%s columns, same generator), one reference call per shard per step on its own host thread, "
+                      "%d steps after %d warm-up; shards not merged" % (what, wl.name, steps, warmup)}
+
+
+def workload_config(wl, world):
+    """`config` of the JSON line — the same object on the GPU arm and on the reference arm."""
+    return {"workload": wl.name, "description": wl.description, "rows_per_gpu": wl.n, "rows_total": wl.n * world,
+            "l2": "inputs (%.0f MB per step) larger than the 126 MB L2; no explicit flush" % (wl.input_bytes() / 1e6)
+            if wl.input_bytes() > 2 * L2_BYTES else "inputs fit in L2: numbers are L2-warm",
+            "parallelism": "row-range shards, one process per GPU" if world > 1 else "single GPU"}
 
 
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
     wl = make_workload(args.workload, args.rows)
     threads = host_threads()
-    r = run_cpu(wl, max(args.steps, 1), min(args.warmup, 1) if args.warmup else 0, threads)
+    r = run_cpu(wl, max(args.steps, 1), max(args.warmup, 0), threads)
     line = {
         "metric": METRIC, "impl": "reference", "value": r["rows_per_s"], "unit": "rows/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": wl.dtype, "data": "synthetic",
-        "config": {"workload": wl.name, "description": wl.description, "rows_full_config": wl.n,
-                   "note": "CPU reference on a bounded sample of the workload"},
+        "config": workload_config(wl, world),
         "cpu_baseline": {"value": r["rows_per_s"], "unit": "rows/s", "cores": r["cores"], "kind": r["kind"],
-                         "sample": r["sample"]},
+                         "sample": r["sample"], "rows_per_step": r["rows"], "whole_configuration": r["full_config"]},
         "e2e": {"value": r["rows_per_s"], "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "input_gbs": r["rows_per_s"] * wl.input_bytes() / wl.n / 1e9,
         "gpu_launches": 0,
@@ -578,15 +601,16 @@ ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby
 
 
 def time_device(ctx, wl, cols_, steps, warmup, world, dist_step=None):
-    """W warm-up + K timed steps with per-launch kernel events; returns per-step ms (max over
-    ranks when world > 1), kernel times, launch count."""
+    """W warm-up + K timed steps (CUDA events on the launching stream, max over ranks when world > 1, the library's
+    per-launch event hook OFF so that launch-bound steps are not charged two event records per kernel), then a
+    second pass of up to 5 steps with the hook on for the per-kernel times.  Returns per-step ms, kernel times
+    {name: (total ms, launches)} of the second pass, its step count, launches per timed region, buffers."""
     import torch
     from arrow1_b200 import capi
     bufs = wl.prepare(ctx, cols_)
     fn = (lambda: dist_step(ctx, wl, cols_, bufs)) if dist_step else (lambda: wl.step(ctx, cols_, bufs))
     for _ in range(warmup):
         fn()
-    capi.lib().b200_ctx_set_kernel_timing(ctx._h, 1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if world > 1:
         import torch.distributed as dist
@@ -602,13 +626,20 @@ def time_device(ctx, wl, cols_, steps, warmup, world, dist_step=None):
         dist.barrier()
     ms = e0.elapsed_time(e1)
     launches = ctx.launches - l0
-    kt = kernel_times(ctx, ALL_KERNELS)
-    capi.lib().b200_ctx_set_kernel_timing(ctx._h, 0)
     if world > 1:
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    return ms / steps, kt, launches, bufs
+    k2 = max(1, min(steps, 5))
+    capi.lib().b200_ctx_set_kernel_timing(ctx._h, 1)
+    for _ in range(k2):
+        fn()
+    torch.cuda.synchronize()
+    kt = kernel_times(ctx, ALL_KERNELS)
+    capi.lib().b200_ctx_set_kernel_timing(ctx._h, 0)
+    if world > 1:
+        dist.barrier()
+    return ms / steps, kt, k2, launches, bufs
 
 
 def roofline_of(wl, kt, steps, peak, peak_src):
@@ -622,6 +653,98 @@ def roofline_of(wl, kt, steps, peak, peak_src):
             "frac_of_8TBs": achieved / 8000.0, "traffic": None, "peak_source": peak_src,
             "launches_per_step": n / steps, "avg_launch_ms": per_launch_ms, "algorithmic_bytes_per_launch": alg,
             "kernel_share_of_step_events": None}
+
+
+def measure_e2e(wl, ctx, rank, world, local, steps, pipelined=True):
+    """The same metric end to end through arrow1_b200.compute (the reference-facing API): pinned HOST columns in,
+    host result out, the copies inside the timed region.  Serial (one call at a time) and, where the workload has
+    an asynchronous form, with 3 calls in flight (compute.Pipeline)."""
+    import torch
+    from arrow1_b200 import compute, synth
+    if world > 1:
+        import torch.distributed as dist
+        from arrow1_b200 import dist as b200_dist
+    e2e_rows = wl.n if wl.n <= 200_000_000 else 200_000_000
+    sub = make_workload(wl.name, e2e_rows)
+    hgen = synth.Gen(None)
+    t0 = time.time()
+    host_cols = tuple(compute.pinned_column(c) for c in sub.make(hgen, start=rank * wl.n, n=e2e_rows))
+    log("[rank %d] host columns for e2e (%d rows) in %.1f s" % (rank, e2e_rows, time.time() - t0))
+    if world > 1:
+        from arrow1_b200 import dist as b200_dist
+        e2e_fn = lambda: b200_dist.bench_e2e_step(ctx, sub, host_cols)  # noqa: E731
+    else:
+        e2e_fn = lambda: sub.e2e_step(host_cols)  # noqa: E731
+    for _ in range(2):
+        r = e2e_fn()
+        del r
+    e2e_steps = max(3, min(steps, 10))
+
+    def timed(loop, k):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        loop(k)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / k
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    def serial_loop(k):
+        for _ in range(k):
+            r = e2e_fn()
+            del r
+
+    serial_ms = timed(serial_loop, e2e_steps)
+    h2d_b, d2h_b = compute.Transfer.h2d, compute.Transfer.d2h
+    ems, depth = serial_ms, 1
+    dist_sort = world > 1 and sub.name.startswith("sort")
+    if pipelined and ((world == 1 and hasattr(sub, "e2e_submit")) or dist_sort):
+        # the same calls, `depth` in flight (compute.Pipeline: one b200_ctx + stream per lane): every step
+        # still copies its own inputs in and its own result out inside the timed region, but step i+1's
+        # H2D, step i's kernels and step i-1's D2H overlap
+        depth = 3
+        pipe = compute.Pipeline(depth=depth, device=local)
+
+        def piped_loop(k):
+            pend = []
+            # the copy-in of step i+1 is started before step i is submitted: a step blocks the submitting
+            # thread wherever it needs a host-visible number (filter's output length, the sort's exchange
+            # counts), and the next copy should already be running by then
+            stage = lambda: tuple(pipe.stage(*host_cols)) if len(host_cols) > 1 else (pipe.stage(*host_cols),)  # noqa: E731
+            nxt = stage()
+            for i in range(k):
+                cur = nxt
+                if i + 1 < k:
+                    nxt = stage()
+                if dist_sort:   # same submission order on every rank: the lanes' collectives line up
+                    pend.append(pipe.submit(b200_dist.SortIndicesSharded, cur[0], 0, rank * wl.n))
+                else:
+                    pend.append(sub.e2e_submit(pipe, cur))
+                if len(pend) >= depth:
+                    pend.pop(0).result()
+            while pend:
+                pend.pop(0).result()
+            pipe.join()
+
+        piped_loop(2 * depth)   # warm the lanes' allocator pools and pinned result buffers
+        e2e_steps *= 2              # the fill and drain of the pipeline are inside the timed region
+        ems = timed(piped_loop, e2e_steps)
+        pipe.close()
+    e2e = {"value": e2e_rows * world / (ems * 1e-3), "unit": "rows/s", "h2d_bytes_per_step": h2d_b,
+           "d2h_bytes_per_step": d2h_b, "ms_per_step": ems, "rows_per_step_per_gpu": e2e_rows,
+           "steps": e2e_steps, "calls_in_flight": depth, "serial_ms_per_step": serial_ms,
+           "serial_value": e2e_rows * world / (serial_ms * 1e-3),
+           "api": "arrow1_b200.compute (mirror of compute::Filter / SortIndices / internal::GroupBy)"
+                  + ("; compute.Pipeline keeps %d calls in flight, one lane (b200_ctx + stream) each" % depth if depth > 1 else "")}
+    del host_cols
+    return e2e
 
 
 def gpu_arm(args):
@@ -652,13 +775,13 @@ def gpu_arm(args):
 
     sampler = ClockSampler(local)
     sampler.start()
-    ms_step, kt, launches, bufs = time_device(ctx, wl, cols_, args.steps, args.warmup, world, dist_step)
+    ms_step, kt, kt_steps, launches, bufs = time_device(ctx, wl, cols_, args.steps, args.warmup, world, dist_step)
     clocks = sampler.stop()
     rows_total = wl.n * world
     value = rows_total / (ms_step * 1e-3)
-    roof = roofline_of(wl, kt, args.steps, peak, peak_src)
+    roof = roofline_of(wl, kt, kt_steps, peak, peak_src)
     if roof:
-        roof["kernel_share_of_step_events"] = (kt[wl.kernel][0] / args.steps) / ms_step
+        roof["kernel_share_of_step_events"] = (kt[wl.kernel][0] / kt_steps) / ms_step
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if roof and os.path.exists(traffic_file):
         try:
@@ -669,86 +792,7 @@ def gpu_arm(args):
     # ---- e2e: host (pinned) -> device -> op -> host, through arrow1_b200.compute
     e2e = None
     if not args.no_e2e:
-        e2e_rows = wl.n if wl.n <= 200_000_000 else 200_000_000
-        sub = make_workload(wl.name, e2e_rows)
-        hgen = synth.Gen(None)
-        t0 = time.time()
-        host_cols = tuple(compute.pinned_column(c) for c in sub.make(hgen, start=rank * wl.n, n=e2e_rows))
-        log("[rank %d] host columns for e2e (%d rows) in %.1f s" % (rank, e2e_rows, time.time() - t0))
-        if world > 1:
-            from arrow1_b200 import dist as b200_dist
-            e2e_fn = lambda: b200_dist.bench_e2e_step(ctx, sub, host_cols)  # noqa: E731
-        else:
-            e2e_fn = lambda: sub.e2e_step(host_cols)  # noqa: E731
-        for _ in range(2):
-            r = e2e_fn()
-            del r
-        e2e_steps = max(3, min(args.steps, 10))
-
-        def timed(loop, k):
-            if world > 1:
-                dist.barrier()
-            torch.cuda.synchronize()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            loop(k)
-            e1.record()
-            torch.cuda.synchronize()
-            ms = e0.elapsed_time(e1) / k
-            if world > 1:
-                t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                ms = float(t.item())
-            return ms
-
-        def serial_loop(k):
-            for _ in range(k):
-                r = e2e_fn()
-                del r
-
-        serial_ms = timed(serial_loop, e2e_steps)
-        h2d_b, d2h_b = compute.Transfer.h2d, compute.Transfer.d2h
-        ems, depth = serial_ms, 1
-        dist_sort = world > 1 and sub.name.startswith("sort")
-        if (world == 1 and hasattr(sub, "e2e_submit")) or dist_sort:
-            # the same calls, `depth` in flight (compute.Pipeline: one b200_ctx + stream per lane): every step
-            # still copies its own inputs in and its own result out inside the timed region, but step i+1's
-            # H2D, step i's kernels and step i-1's D2H overlap
-            depth = 3
-            pipe = compute.Pipeline(depth=depth, device=local)
-
-            def piped_loop(k):
-                pend = []
-                # the copy-in of step i+1 is started before step i is submitted: a step blocks the submitting
-                # thread wherever it needs a host-visible number (filter's output length, the sort's exchange
-                # counts), and the next copy should already be running by then
-                stage = lambda: tuple(pipe.stage(*host_cols)) if len(host_cols) > 1 else (pipe.stage(*host_cols),)  # noqa: E731
-                nxt = stage()
-                for i in range(k):
-                    cur = nxt
-                    if i + 1 < k:
-                        nxt = stage()
-                    if dist_sort:   # same submission order on every rank: the lanes' collectives line up
-                        pend.append(pipe.submit(b200_dist.SortIndicesSharded, cur[0], 0, rank * wl.n))
-                    else:
-                        pend.append(sub.e2e_submit(pipe, cur))
-                    if len(pend) >= depth:
-                        pend.pop(0).result()
-                while pend:
-                    pend.pop(0).result()
-                pipe.join()
-
-            piped_loop(2 * depth)   # warm the lanes' allocator pools and pinned result buffers
-            e2e_steps *= 2              # the fill and drain of the pipeline are inside the timed region
-            ems = timed(piped_loop, e2e_steps)
-            pipe.close()
-        e2e = {"value": e2e_rows * world / (ems * 1e-3), "unit": "rows/s", "h2d_bytes_per_step": h2d_b,
-               "d2h_bytes_per_step": d2h_b, "ms_per_step": ems, "rows_per_step_per_gpu": e2e_rows,
-               "steps": e2e_steps, "calls_in_flight": depth, "serial_ms_per_step": serial_ms,
-               "serial_value": e2e_rows * world / (serial_ms * 1e-3),
-               "api": "arrow1_b200.compute (mirror of compute::Filter / SortIndices / internal::GroupBy)"
-                      + ("; compute.Pipeline keeps %d calls in flight, one lane (b200_ctx + stream) each" % depth if depth > 1 else "")}
-        del host_cols
+        e2e = measure_e2e(wl, ctx, rank, world, local, args.steps)
 
     # ---- the other configs, device-resident numbers only
     extras = {}
@@ -762,13 +806,30 @@ def gpu_arm(args):
                 w2 = make_workload(name, None)
                 c2 = w2.make(gen)
                 k2 = max(3, min(args.steps, 10))
-                ms2, kt2, l2, b2 = time_device(ctx, w2, c2, k2, 3, 1)
-                r2 = roofline_of(w2, kt2, k2, peak, peak_src)
+                ms2, kt2, ks2, l2, b2 = time_device(ctx, w2, c2, k2, 3, 1)
+                r2 = roofline_of(w2, kt2, ks2, peak, peak_src)
+                if r2:
+                    r2["kernel_share_of_step_events"] = (kt2[w2.kernel][0] / ks2) / ms2
                 extras[name] = {"rows": w2.n, "ms_per_step": ms2, "rows_per_s": w2.n / (ms2 * 1e-3),
                                 "input_gbs": w2.input_bytes() / (ms2 * 1e-3) / 1e9, "gpu_launches": l2,
-                                "roofline": r2, "description": w2.description}
+                                "roofline": r2, "description": w2.description,
+                                "kernel_ms_per_step": {k: v[0] / ks2 for k, v in kt2.items() if v[1]}}
                 del c2, b2
                 torch.cuda.empty_cache()
+                # the same metric from host buffers (copies timed) and the reference's CPU kernels beside it
+                if not args.no_e2e:
+                    try:
+                        extras[name]["e2e"] = measure_e2e(w2, ctx, rank, world, local, 3)
+                    except Exception as ex:
+                        extras[name]["e2e"] = {"error": repr(ex)[:300]}
+                    torch.cuda.empty_cache()
+                if not args.no_cpu:
+                    try:
+                        r = run_cpu(w2, 1, 0 if w2.n > 50_000_000 else 1, host_threads())
+                        extras[name]["cpu_baseline"] = {"value": r["rows_per_s"], "unit": "rows/s", "cores": r["cores"],
+                                                        "kind": r["kind"], "sample": r["sample"]}
+                    except Exception as ex:
+                        extras[name]["cpu_baseline"] = {"value": None, "sample": "failed: %r" % (ex,)}
             except Exception as ex:  # an extra must never take the main line down
                 extras[name] = {"error": repr(ex)[:300]}
 
@@ -785,13 +846,11 @@ def gpu_arm(args):
             "metric": METRIC, "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": wl.dtype,
             "data": "synthetic",
-            "config": {"workload": wl.name, "description": wl.description, "rows_per_gpu": wl.n, "rows_total": rows_total,
-                       "l2": "inputs (%.0f MB per step) larger than the 126 MB L2; no explicit flush" % (wl.input_bytes() / 1e6)
-                       if wl.input_bytes() > 2 * L2_BYTES else "inputs fit in L2: numbers are L2-warm",
-                       "parallelism": "row-range shards, one process per GPU" if world > 1 else "single GPU"},
+            "config": workload_config(wl, world),
             "input_gbs": value * wl.input_bytes() / wl.n / 1e9,
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-            "kernel_ms_per_step": {k: v[0] / args.steps for k, v in kt.items() if v[1]},
+            "kernel_ms_per_step": {k: v[0] / kt_steps for k, v in kt.items() if v[1]},
+            "kernel_timing": "per-launch CUDA events of a second pass of %d steps (the hook is off during the timed steps)" % kt_steps,
         }
         if extras:
             line["workloads"] = extras

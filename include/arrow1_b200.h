@@ -239,6 +239,11 @@ B200_API int b200_sort_pairs(b200_ctx* ctx, const uint64_t* keys, const uint64_t
                              uint64_t* out_payload, void* scratch, size_t scratch_bytes);
 /* As b200_sort_pairs with a 32-bit payload that travels through the passes (no gather at the end):
  * out_payload[i] = (uint64_t)payload32[perm[i]].  Scratch: b200_sort_pairs_scratch_bytes. */
+/* b200_sort_pairs for keys the caller knows to be below 2^key_bits (e.g. row numbers): only the digits that can
+ * vary are histogrammed and sorted, and with key_bits <= 32 every pass carries 32-bit keys.  No sorted keys out. */
+B200_API int b200_sort_pairs_bits(b200_ctx* ctx, const uint64_t* keys, const uint64_t* payload /* nullable */,
+                                  int64_t length, int key_bits, uint64_t* out_payload, void* scratch,
+                                  size_t scratch_bytes);
 B200_API int b200_sort_pairs32(b200_ctx* ctx, const uint64_t* keys, const uint32_t* payload32,
                                int64_t length, uint64_t* out_keys /* nullable */,
                                uint64_t* out_payload, void* scratch, size_t scratch_bytes);

@@ -24,7 +24,7 @@ _ROOT = os.path.dirname(_HERE)
 if _ROOT not in sys.path:
     sys.path.insert(0, _ROOT)
 
-from arrow1_b200.columns import (BITS, BOOL, HASH_MIN_MAX, NP_OF, AggSpec, Column, agg_out_types,  # noqa: E402
+from arrow1_b200.columns import (BITS, BOOL, HASH_MIN_MAX, HASH_SUM, NP_OF, AggSpec, Column, agg_out_types,  # noqa: E402
                                  b200_agg_spec, b200_col, b200_out_col, col_array, unpack_bits)
 
 PORT_SO = os.path.join(_HERE, "_build", "liboracle.so")
@@ -233,3 +233,35 @@ def groupby(keys: Sequence[Column], aggs: Sequence[AggSpec], args: Sequence[Colu
         res_aggs.append(cols)
     res_keys = [_decode(t, d, v, G) for (t, d, v) in key_holders]
     return GroupByResult(G, res_aggs, res_keys, None if ids is None else ids[:n])
+
+
+def groupby_sum_chunked(key_chunks: Sequence[Sequence[Column]], arg_chunks: Sequence[Sequence[Column]], max_groups: int):
+    """The reference's GroupBy with hash_sum aggregates over CHUNKED columns (kind="reference" only):
+    key_chunks[k][c] / arg_chunks[j][c] = chunk c of key k / argument j, every chunk its own buffers at offset 0.
+    This is the multi-batch form upstream computes correctly; sums accumulate in row order across the chunks
+    (hash_aggregate.cc:533-545, 926-943).  Returns (num_groups, [(values, valid) per aggregate], [(values, valid) per key])."""
+    n_keys, n_aggs, n_chunks = len(key_chunks), len(arg_chunks), len(key_chunks[0])
+    flat_keys = [c for cs in key_chunks for c in cs]
+    flat_args = [c for cs in arg_chunks for c in cs]
+    for c in flat_keys + flat_args:
+        assert c.offset == 0 and c.length <= (1 << 27)
+    out_aggs = (b200_out_col * max(n_aggs, 1))()
+    holders = []
+    for j in range(n_aggs):
+        t = agg_out_types(HASH_SUM, arg_chunks[j][0].type)[0]
+        oc, d, v = _out_col(t, max_groups)
+        out_aggs[j] = oc
+        holders.append((t, d, v))
+    out_keys = (b200_out_col * n_keys)()
+    key_holders = []
+    for k in range(n_keys):
+        oc, d, v = _out_col(key_chunks[k][0].type, max_groups)
+        out_keys[k] = oc
+        key_holders.append((key_chunks[k][0].type, d, v))
+    num_groups = C.c_uint32(0)
+    _check("reference", _fn("reference", "groupby_sum_chunked")(C.c_int(n_keys), C.c_int(n_chunks), col_array(flat_keys),
+                                                                  C.c_int(n_aggs), col_array(flat_args), out_aggs, out_keys,
+                                                                  C.byref(num_groups)))
+    G = num_groups.value
+    assert G <= max_groups
+    return G, [_decode(t, d, v, G) for (t, d, v) in holders], [_decode(t, d, v, G) for (t, d, v) in key_holders]

@@ -319,4 +319,34 @@ B200_API int ref_groupby(int n_keys, const b200_col* keys, int n_aggs, const b20
   return 0;
 }
 
+// compute::internal::GroupBy over CHUNKED inputs, hash_sum aggregates only: the one multi-batch form the reference
+// computes correctly (multi-batch hash_count / hash_min_max are broken upstream; counts are obtained as
+// hash_sum over an int64 column of ones carrying the value's validity).  keys[k * n_chunks + c] / args[j * n_chunks + c]
+// are chunk c of key k / argument j; every chunk is its own buffer at offset 0 and at most 2^27 rows, so that
+// ExecBatchIterator yields one batch per chunk and the int32 key-bytes limit of GrouperImpl::Consume is kept.
+// This is how the reference sums a column longer than one batch: sums[g] += v in row order across the batches.
+B200_API int ref_groupby_sum_chunked(int n_keys, int n_chunks, const b200_col* keys, int n_aggs, const b200_col* args,
+                                     b200_out_col* out_aggs, b200_out_col* out_keys, uint32_t* out_num_groups) {
+  compute::ExecContext ctx;
+  auto chunked = [&](const b200_col* cols) {
+    ArrayVector pieces;
+    for (int c = 0; c < n_chunks; ++c) pieces.push_back(MakeArray(Wrap(cols[c])));
+    return Datum(std::make_shared<ChunkedArray>(pieces, TypeOf(cols[0].type)));
+  };
+  std::vector<Datum> key_datums, arg_datums;
+  for (int k = 0; k < n_keys; ++k) key_datums.push_back(chunked(keys + size_t(k) * n_chunks));
+  std::vector<compute::internal::Aggregate> specs;
+  for (int j = 0; j < n_aggs; ++j) {
+    arg_datums.push_back(chunked(args + size_t(j) * n_chunks));
+    specs.push_back({"hash_sum", nullptr});
+  }
+  auto res = compute::internal::GroupBy(arg_datums, key_datums, specs, &ctx);
+  if (!res.ok()) return Fail(res.status());
+  auto st = res.ValueOrDie().array();
+  for (int j = 0; j < n_aggs; ++j) CopyOut(*st->child_data[j], &out_aggs[j]);
+  for (int k = 0; k < n_keys; ++k) CopyOut(*st->child_data[n_aggs + k], &out_keys[k]);
+  if (out_num_groups) *out_num_groups = static_cast<uint32_t>(st->length);
+  return 0;
+}
+
 }  // extern "C"

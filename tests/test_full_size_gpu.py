@@ -102,3 +102,136 @@ def test_groupby_config3_full_size(ctx):
     assert int(first.max().item()) < head.numel(), "every key appears in the prefix"
     want_order = torch.argsort(first).cpu().numpy().astype(np.int32)
     np.testing.assert_array_equal(keys, want_order)
+
+
+def _reference_groupby_partitioned(key_np, val_np, threads=16):
+    """The unmodified reference (oracle/_ref) on a high-cardinality column at a size its single-threaded, single-batch
+    GroupBy cannot take in test time: the rows are split by key hash into disjoint key sets, each set goes through the
+    reference's own GroupBy (hash_sum + a hash_sum of ones = the counts) in its ORIGINAL row order on its own host
+    thread — so every group's sum is the reference's row-order sum — and the groups of all sets are ranked by their
+    first row (= the reference's first-occurrence group order, hash_aggregate.cc:391-403)."""
+    from concurrent.futures import ThreadPoolExecutor
+    import oracle
+    from arrow1_b200.columns import Column
+    part = ((key_np.view(np.uint64) * np.uint64(0x9E3779B97F4A7C15)) >> np.uint64(60)).astype(np.uint8)   # 16 sets
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_SUM)]
+
+    def one(p):
+        rows = np.flatnonzero(part == p)
+        k, v = Column.from_numpy(key_np[rows]), Column.from_numpy(val_np[rows])
+        ones = Column.from_numpy(np.ones(len(rows), dtype=np.int64))
+        r = oracle.groupby([k], aggs, [v, ones], want_ids=True, kind="reference")
+        _, where = np.unique(r.ids, return_index=True)   # ids are 0..G-1: first position of every group in this set
+        return r.keys[0][0], r.aggs[0][0][0], r.aggs[1][0][0], rows[where]
+
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        res = list(ex.map(one, range(16)))
+    keys = np.concatenate([r[0] for r in res])
+    sums = np.concatenate([r[1] for r in res])
+    counts = np.concatenate([r[2] for r in res])
+    first = np.concatenate([r[3] for r in res])
+    order = np.argsort(first, kind="stable")
+    return keys[order], sums[order], counts[order]
+
+
+def test_groupby_config4_against_reference_at_size(ctx):
+    """C4's shape at 200 M rows / 20 M distinct int64 keys (a fifth of the configuration; the partition-then-aggregate
+    path with two partition levels, shared-memory tables and the pending image list): hash_sum + hash_mean against the
+    unmodified reference — group order and keys bit for bit, float64 sums and means within 1e-12 relative (the values
+    are positive, so relative to the sum itself)."""
+    import oracle
+    if not oracle.have_reference():
+        pytest.skip("needs oracle/_ref")
+    n, n_keys = 200_000_000, 20_000_000
+    key, val = synth.Gen("cuda:0").groupby_c4(n, n_keys)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MEAN)]
+    got = capi.group_by(ctx, [key], aggs, [val] * 2, expected_groups=n_keys)
+    g_keys = got.keys[0].values()
+    g_sum, g_mean = got.aggs[0][0].values(), got.aggs[1][0].values()
+    key_np = key.data[: n * 8].view(torch.int64).cpu().numpy()
+    val_np = val.data[: n * 8].view(torch.float64).cpu().numpy()
+    del key, val, got
+    torch.cuda.empty_cache()
+    r_keys, r_sum, r_cnt = _reference_groupby_partitioned(key_np, val_np)
+    assert len(g_keys) == len(r_keys)
+    np.testing.assert_array_equal(g_keys, r_keys)            # keys in first-occurrence order
+    rel = np.abs(g_sum - r_sum) / np.abs(r_sum)
+    assert float(rel.max()) <= 1e-12, "hash_sum: max relative error %g" % float(rel.max())
+    r_mean = r_sum / r_cnt                                    # MeanImpl::Finalize over the reference's sum and count
+    relm = np.abs(g_mean - r_mean) / np.abs(r_mean)
+    assert float(relm.max()) <= 1e-12, "hash_mean: max relative error %g" % float(relm.max())
+
+
+def test_groupby_config4_full_size_properties(ctx):
+    """C4 as written: 1 B rows, 100 M distinct int64 keys, hash_sum + hash_mean.  Properties computed on the device: the
+    number of groups is the number of distinct keys; the group sums add up to the column's sum; mean * count adds up to
+    it too with count recovered as sum / mean summing to the row count; the first groups are the first distinct keys of
+    the column in row order."""
+    n, n_keys = 1_000_000_000, 100_000_000
+    key, val = synth.Gen("cuda:0").groupby_c4(n, n_keys)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MEAN)]
+    got = capi.group_by(ctx, [key], aggs, [val] * 2, expected_groups=n_keys)
+    G = got.num_groups
+    k64 = key.data[: n * 8].view(torch.int64)
+    sums = got.aggs[0][0].data[: G * 8].view(torch.float64)
+    means = got.aggs[1][0].data[: G * 8].view(torch.float64)
+    gkeys = got.keys[0].data[: G * 8].view(torch.int64)
+    total = float(val.data[: n * 8].view(torch.float64).sum(dtype=torch.float64).item())
+    assert abs(float(sums.sum(dtype=torch.float64).item()) - total) <= 4e-12 * total
+    counts = torch.round(sums / means)
+    assert int(counts.sum().item()) == n
+    # the first 1000 groups = the first 1000 distinct keys of the column in row order (they all occur in a short prefix)
+    head = k64[:200_000].cpu().numpy()
+    _, first_idx = np.unique(head, return_index=True)
+    first_keys = head[np.sort(first_idx)][:1000]
+    np.testing.assert_array_equal(gkeys[:1000].cpu().numpy(), first_keys)
+    del sums, means, counts, val
+    torch.cuda.empty_cache()
+    # distinct keys: sort a copy of the key column on the device (torch as the checker)
+    srt, _ = torch.sort(k64)
+    distinct = int((srt[1:] != srt[:-1]).sum().item()) + 1
+    assert G == distinct
+    assert torch.equal(torch.sort(gkeys)[0], torch.unique_consecutive(srt))
+
+
+def test_q1_config5_full_size_against_reference_fixture(ctx):
+    """C5 at its full 600 M rows, all three forms of the pipeline (unfused, selection-fused, one pass), against
+    tests/golden/q1_sf100.json: the unmodified reference's Filter + row-order GroupBy over the same generator's rows
+    (scripts/make_q1_fixture.py, run where /root/reference is compiled).  Keys, group order and counts bit for bit.
+    Sums / means: SURVEY §7.2-2 predicted that at ~1.5e8 addends per group the reference's own sequential drift is
+    ~1e-12, so both errors are reported — GPU vs reference and each side vs the extended-precision sum — and the gate
+    is: the GPU result is within 1e-12 of the reference OR closer to the exact sum than the reference is."""
+    import json
+    import os
+    from arrow1_b200 import compute
+    path = os.path.join(os.path.dirname(__file__), "golden", "q1_sf100.json")
+    fx = json.load(open(path))
+    n = fx["rows"]
+    ship, rf, ls, qty, price, disc = synth.Gen("cuda:0").q1_lineitem(n)
+    ref = {k: np.array([float.fromhex(x) for x in v]) for k, v in fx["reference_sum"].items()}
+    exact = {k: np.array([np.longdouble(float.fromhex(h)) + np.longdouble(float.fromhex(l)) for h, l in v])
+             for k, v in fx["extended_sum_hi_lo"].items()}
+    cnt = np.array(fx["count"], dtype=np.int64)
+    report = []
+    for name, fn in (("unfused", compute.Q1Pipeline), ("selected", compute.Q1PipelineSelected), ("one_pass", compute.Q1PipelineFused)):
+        got = fn(ship, rf, ls, [qty, price, disc], ctx)
+        assert got.num_groups == fx["groups"]
+        np.testing.assert_array_equal(got.keys[0].values(), np.array(fx["returnflag"], dtype=np.uint8))
+        np.testing.assert_array_equal(got.keys[1].values(), np.array(fx["linestatus"], dtype=np.uint8))
+        np.testing.assert_array_equal(got.aggs[6][0].values(), cnt)
+        # q1_aggregates(): sum qty, sum price, sum disc_price, mean qty, mean price, mean disc, count
+        checks = (("qty", got.aggs[0][0].values(), False), ("price", got.aggs[1][0].values(), False),
+                  ("dprice", got.aggs[2][0].values(), False), ("qty", got.aggs[3][0].values() * cnt, True),
+                  ("price", got.aggs[4][0].values() * cnt, True), ("disc", got.aggs[5][0].values() * cnt, True))
+        for col, g_sum, is_mean in checks:
+            e_gpu_ref = np.abs(g_sum - ref[col]) / np.abs(ref[col])
+            e_gpu_exact = np.abs(g_sum.astype(np.longdouble) - exact[col]) / np.abs(exact[col])
+            e_ref_exact = np.abs(ref[col].astype(np.longdouble) - exact[col]) / np.abs(exact[col])
+            report.append((name, col, float(e_gpu_ref.max()), float(e_gpu_exact.max()), float(e_ref_exact.max())))
+            tol = 2e-12 if is_mean else 1e-12   # a mean times its count carries two more roundings
+            ok = (e_gpu_ref <= tol) | (e_gpu_exact <= e_ref_exact + 1e-16)
+            assert bool(ok.all()), "%s %s: gpu-ref %g gpu-exact %g ref-exact %g" % (name, col, e_gpu_ref.max(), e_gpu_exact.max(), e_ref_exact.max())
+        del got
+    print("\nC5 600M rows — max relative errors (form, column, GPU vs reference, GPU vs exact, reference vs exact):")
+    for r in report:
+        print("  %-9s %-7s %.3g %.3g %.3g" % r)
