@@ -534,6 +534,92 @@ def bench_step(ctx, wl, cols_, bufs):
     raise SystemExit("bench: workload %s has no multi-GPU form yet" % wl.name)
 
 
+def bench_self_check(ctx, wl, cols_, bufs):
+    """One more step of the workload, outside the timed region, checked against what the counter-based generator
+    says (every SCALE run doubles as a parity run).  Collective: every rank calls it.  Returns a JSON-able dict.
+      sort      this rank's slice of the global index array is strictly increasing in (class, key, row) with the keys
+                REGENERATED from the row numbers (rows come from every rank), the boundary to the next rank's slice
+                is in order too, all rows lie in [0, N), and the slices hold N rows together  ==> a permutation in
+                the reference's stable order
+      filter    output length == number of set mask bits of the shard
+      group-by  low cardinality: every rank holds the same number of groups and the counts add up to the valid rows
+                of all shards; high cardinality: the per-rank counts (sum / mean) add up to all rows"""
+    import numpy as np
+    from . import synth
+    rank, world = _rank_world()
+    res = bench_step(ctx, wl, cols_, bufs)
+    dev = cols_[0].data.device
+    n_total = wl.n * world
+
+    def allsum(x):
+        t = torch.tensor([int(x)], dtype=torch.int64, device=dev)
+        if world > 1:
+            dist.all_reduce(t)
+        return int(t.item())
+
+    if wl.name.startswith("sort"):
+        out, off = res
+        idx = out.view(torch.int64)
+        m = idx.numel()
+        ok = allsum(m) == n_total and bool(((idx >= 0) & (idx < n_total)).all()) if m else allsum(0) == n_total
+        valid = (synth._lsr(synth.r_at(6, idx), 33) % 100) != 0
+        if wl.name == "sort_i64":
+            key = synth.r_at(4, idx)
+        else:
+            key = (synth._lsr(synth.r_at(5, idx), 11).to(torch.float64) * 2.0 ** -53 * 1e14).view(torch.int64)   # positive doubles order like their bits
+        cls = (~valid).to(torch.int64)
+        key = torch.where(valid, key, torch.zeros_like(key))
+        if m > 1:
+            a = (cls[:-1], key[:-1], idx[:-1])
+            b = (cls[1:], key[1:], idx[1:])
+            lt = (a[0] < b[0]) | ((a[0] == b[0]) & ((a[1] < b[1]) | ((a[1] == b[1]) & (a[2] < b[2]))))
+            ok = ok and bool(lt.all())
+        # boundaries: (first, last) triple of every rank
+        edge = torch.zeros(6, dtype=torch.int64, device=dev)
+        if m:
+            edge = torch.stack([cls[0], key[0], idx[0], cls[-1], key[-1], idx[-1]])
+        edges = [torch.zeros_like(edge) for _ in range(world)]
+        sizes = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
+        if world > 1:
+            dist.all_gather(edges, edge)
+            dist.all_gather(sizes, torch.tensor([m], dtype=torch.int64, device=dev))
+        else:
+            edges, sizes = [edge], [torch.tensor([m], device=dev)]
+        prev = None
+        for e, sz in zip(edges, sizes):
+            if int(sz.item()) == 0:
+                continue
+            e = e.tolist()
+            if prev is not None and not (tuple(prev) < tuple(e[:3])):
+                ok = False
+            prev = e[3:]
+        return {"workload": wl.name, "rows_total": n_total, "permutation_in_stable_order": bool(allsum(0 if ok else 1) == 0)}
+    if wl.name.startswith("filter"):
+        from .capi import FilterPlan
+        mask = cols_[1]
+        bits = mask.data[: (mask.length + 7) // 8]
+        w = torch.tensor([1, 2, 4, 8, 16, 32, 64, 128], dtype=torch.uint8, device=dev)
+        want = int(((bits.unsqueeze(1) & w) != 0).reshape(-1)[: mask.length].sum().item())
+        return {"workload": wl.name, "rows_total": n_total, "selected_rows_total": allsum(res.length),
+                "output_length_matches_mask": bool(allsum(0 if res.length == want else 1) == 0)}
+    if wl.name == "groupby_c3":
+        counts = res.aggs[1][0].values()
+        valid_local = wl.n - cols_[1].null_count
+        total_valid = allsum(valid_local)
+        same = allsum(res.num_groups) == res.num_groups * world
+        return {"workload": wl.name, "rows_total": n_total, "groups": int(res.num_groups),
+                "counts_add_up_to_valid_rows": bool(int(counts.sum()) == total_valid and same)}
+    if wl.name == "groupby_c4":
+        out = res.out
+        G = out.num_groups
+        sums = out.aggs[0][0].data[: G * 8].view(torch.float64)
+        means = out.aggs[1][0].data[: G * 8].view(torch.float64)
+        local = int(torch.round(sums / means).sum().item()) if G else 0
+        return {"workload": wl.name, "rows_total": n_total, "groups_total": allsum(G),
+                "counts_add_up_to_rows": bool(allsum(local) == n_total)}
+    return {"workload": wl.name, "checked": False}
+
+
 def SortIndicesSharded(values: Column, order: int = 0, row_base: int = 0, ctx=None, _wait: bool = True, group=None):
     """The multi-GPU SortIndices from this rank's HOST shard: staged to the device, sorted across the ranks
     (dist_sort_indices), this rank's slice of the global index array read back.  Returns (uint64 numpy indices,

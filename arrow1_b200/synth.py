@@ -51,6 +51,16 @@ def r_t(seed: int, start: int, n: int, device):
     return z ^ _lsr(z, 31)
 
 
+def r_at(seed: int, idx):
+    """r(seed, i) for an int64 tensor of row numbers (the multi-GPU self-check regenerates the keys of the rows a rank
+    received from the other ranks)."""
+    x = idx + _s64(seed * GOLDEN)
+    x = x + _s64(GOLDEN)
+    z = (x ^ _lsr(x, 30)) * _s64(_M1)
+    z = (z ^ _lsr(z, 27)) * _s64(_M2)
+    return z ^ _lsr(z, 31)
+
+
 def u_t(seed: int, start: int, n: int, device):
     import torch
     return _lsr(r_t(seed, start, n, device), 11).to(torch.float64) * 2.0 ** -53

@@ -794,8 +794,55 @@ def gpu_arm(args):
     if not args.no_e2e:
         e2e = measure_e2e(wl, ctx, rank, world, local, args.steps)
 
+    # ---- multi-GPU: the step's result checked against the generator, once, outside the timed region
+    self_check = None
+    if world > 1:
+        try:
+            self_check = b200_dist.bench_self_check(ctx, wl, cols_, bufs)
+        except Exception as ex:
+            self_check = {"error": repr(ex)[:300]}
+
     # ---- the other configs, device-resident numbers only
     extras = {}
+    if world > 1 and not args.no_extras:
+        # the other three §8(e) rows at this world size: Filter (no collective), low-cardinality merge (all-gather of
+        # the slots), high-cardinality hash repartition (NCCL all-to-all).  C4 is the configuration as written: 1 B rows
+        # and 100 M distinct keys IN TOTAL, i.e. strong scaling; the others keep the rows per GPU.
+        del cols_, bufs
+        torch.cuda.empty_cache()
+        collective = {"filter": "none", "groupby_c3": "all_gather of the occupied slots + merge in rank order",
+                      "groupby_c4": "all_to_all_single per column + row numbers (hash repartition)"}
+        for name in ("sort_i64", "filter", "groupby_c3", "groupby_c4"):
+            if name == wl.name:
+                continue
+            try:
+                rows2 = 1_000_000_000 // world if name == "groupby_c4" else None
+                w2 = make_workload(name, rows2)
+                if name == "groupby_c4":
+                    w2.n_keys = 100_000_000
+                    w2.description = "hash_sum+hash_mean over %d rows in total of (int64 key, float64 value), 100000000 distinct keys" % (w2.n * world)
+                c2 = w2.make(gen, start=rank * w2.n)
+                k2 = max(3, min(args.steps, 5))
+                ms2, kt2, ks2, l2, b2 = time_device(ctx, w2, c2, k2, 3, world, dist_step)
+                entry = None
+                chk = b200_dist.bench_self_check(ctx, w2, c2, b2)
+                if rank == 0:
+                    r2 = roofline_of(w2, kt2, ks2, peak, peak_src)
+                    entry = {"rows_per_gpu": w2.n, "rows_total": w2.n * world, "ms_per_step": ms2,
+                             "rows_per_s": w2.n * world / (ms2 * 1e-3), "scaling": "strong" if name == "groupby_c4" else "weak",
+                             "collective": collective.get(name, "all_gather (sample, counts) + peer stores over NVLink"),
+                             "gpu_launches": l2, "roofline": r2, "description": w2.description, "self_check": chk,
+                             "kernel_ms_per_step": {k: v[0] / ks2 for k, v in kt2.items() if v[1]}}
+                    if name == "groupby_c4":
+                        # bytes this rank sends in the all-to-all: (key 8 + value 8 + row number 8) of (world-1)/world of its rows
+                        sent = w2.n * 24 * (world - 1) / world
+                        entry["all_to_all_bytes_sent_per_gpu"] = sent
+                extras[name] = entry
+                del c2, b2
+                torch.cuda.empty_cache()
+            except Exception as ex:
+                extras[name] = {"error": repr(ex)[:300]}
+        cols_, bufs = None, None
     if rank == 0 and world == 1 and not args.no_extras:
         del cols_, bufs
         torch.cuda.empty_cache()
@@ -852,6 +899,8 @@ def gpu_arm(args):
             "kernel_ms_per_step": {k: v[0] / kt_steps for k, v in kt.items() if v[1]},
             "kernel_timing": "per-launch CUDA events of a second pass of %d steps (the hook is off during the timed steps)" % kt_steps,
         }
+        if self_check is not None:
+            line["self_check"] = self_check
         if extras:
             line["workloads"] = extras
         emit(line)
