@@ -18,6 +18,8 @@
 //            gb_rehash / gb_merge / gb_collect / gb_emit / gb_dense_consume
 // Algorithmic HBM bytes per row: every key and argument column read once:
 // C3 12.125 B/row, C4 16 B/row.
+#include <stddef.h>
+
 #include <algorithm>
 #include <vector>
 
@@ -2070,6 +2072,7 @@ __global__ void __launch_bounds__(kTinyThreads, 4) gb_tiny8_kernel(const __grid_
 }
 
 #include "groupby_q1.cuh"
+#include "groupby_wide.cuh"
 
 // ---- table maintenance ----------------------------------------------------------------------
 // moves every occupied slot of `src` (stride bytes each) into table `dst`; when `merge` the states
@@ -2521,6 +2524,18 @@ struct b200_groupby {
   // at 10^8 expected groups it is a 17 GB array to initialise, fill and scan.
   char* pending = nullptr;
   uint32_t pending_n = 0;
+  // wide keys (groupby_wide.cuh): the key columns as the caller declared them, the key -> id table and the key store;
+  // `schema` then describes ONE uint32 key column holding the ids
+  bool wide = false;
+  int32_t wn_keys = 0, wwords = 0;
+  int32_t wtypes[kWideMaxKeys], wbits[kWideMaxKeys], woff[kWideMaxKeys];
+  uint64_t* wslots = nullptr;
+  uint64_t wcap = 0;
+  uint64_t* wstore = nullptr;
+  uint32_t wstore_cap = 0, wcount = 0;
+  uint32_t* wcounters = nullptr;
+  void* wtmp = nullptr;
+  size_t wtmp_bytes = 0;
   // upper bound of every global row number consumed so far (2^64-1 once unknown): first rows below 2^32 are ranked
   // by a sort that carries 32-bit keys
   uint64_t row_bound = 0;
@@ -2705,7 +2720,7 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
   const uint32_t parts1 = 1u << bits1, parts = 1u << bits;
   // scratch: two tuple buffers + histograms / cursors / starts + work items
   const size_t a8 = b200_align_up(size_t(n) * 8, 256), a4 = b200_align_up(size_t(n) * 4, 256);
-  const size_t buf_bytes = 2 * a8 + a4;
+  const size_t buf_bytes = 2 * a8 + a4 + (a.row_ids ? a4 : 0);
   const size_t small = b200_align_up(size_t(parts + 1) * 4, 256);
   const size_t need = 2 * buf_bytes + 9 * small + 1024;
   if (need > gb->hp_bytes) {
@@ -2724,6 +2739,7 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
     b.keys = reinterpret_cast<uint64_t*>(p);
     b.vals = reinterpret_cast<uint64_t*>(p + a8);
     b.rows = reinterpret_cast<uint32_t*>(p + 2 * a8);
+    b.ord = a.row_ids ? reinterpret_cast<uint32_t*>(p + 2 * a8 + a4) : nullptr;
     return b;
   };
   const HpBufs buf_a = bufs_at(base), buf_b = bufs_at(base + buf_bytes);
@@ -2739,13 +2755,21 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
   uint32_t* base2 = reinterpret_cast<uint32_t*>(sm + 6 * small + 256);
   uint32_t* item_base = reinterpret_cast<uint32_t*>(sm + 7 * small + 256);
   B200_CUDA(ctx, cudaMemsetAsync(sm, 0, zero_bytes, ctx->stream));
+  uint64_t ord_base = 0;
   if (a.row_ids) {
-    // the earliest row of a group is tracked by its position in the batch: explicit row numbers must ascend
-    gb_hp_monotone_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(a.row_ids, n, misc + 1);
+    // explicit row numbers ride along as 32-bit offsets from the batch's smallest one (the earliest row of a group is
+    // the minimum of them); a batch whose numbers span 2^31 or more goes through the generic kernels
+    unsigned long long* mm = reinterpret_cast<unsigned long long*>(misc + 2);
+    const unsigned long long init[2] = {~0ull, 0ull};
+    B200_CUDA(ctx, cudaMemcpyAsync(mm, init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
+    gb_hp_minmax_kernel<<<ctx->num_sms * 4, 256, 0, ctx->stream>>>(a.row_ids, n, mm);
     B200_LAUNCHED(ctx);
-    B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 24, misc + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 24, mm, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
     B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    if (*reinterpret_cast<const uint32_t*>(ctx->host_words + 24) != 0) return B200_OK;
+    const uint64_t lo = uint64_t(ctx->host_words[24]), hi = uint64_t(ctx->host_words[25]);
+    if (hi - lo >= (uint64_t(1) << 31)) return B200_OK;
+    ord_base = lo;
+    a.row_base = lo;   // (unused by the kernels that read row_ids) the aggregation kernel adds it to the smallest offset
   }
   // the table takes the expected groups at load <= 1/2; a partition = the hash bits just below its index width
   // (the table itself may not exist yet, see b200_groupby::pending)
@@ -2754,8 +2778,10 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
   while ((uint64_t(1) << cap_bits) < planned_cap) ++cap_bits;
   const int top = std::max(cap_bits, bits);   // partition id = hash bits [top - bits, top)
   if (b200_ctx_once(ctx, 1)) {
-    B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_part_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpPartSmem))));
-    B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_part_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpPartSmem))));
+    B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_part_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(offsetof(HpPartSmem, ord))));
+    B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_part_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(offsetof(HpPartSmem, ord))));
+    B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_part_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpPartSmem))));
+    B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_part_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpPartSmem))));
     B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_agg_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpAggSmem))));
     B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_agg_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpAggSmem))));
   }
@@ -2764,6 +2790,7 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
   HpArgs h;
   memset(&h, 0, sizeof(h));
   h.has_val = a.n_cols > 0;
+  h.ord_base = ord_base;
   if (a.s.n_keys == 1 && !a.keys[0].vv.words && (a.keys[0].nbits == 64 || a.keys[0].nbits == 32) &&
       (a.n_cols == 0 || (b200_type_bits(a.cols[0].type) == 64 && !a.cols[0].vv.words)))
     h.fast = a.keys[0].nbits / 8;
@@ -2777,7 +2804,10 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
   B200_TIMED(ctx, "groupby_partition", (gb_hp_hist_kernel<1><<<grid, kHpThreads, 0, ctx->stream>>>(a, h)));
   gb_hp_scan_kernel<<<1, 1024, 0, ctx->stream>>>(hist1, parts1, cursor1, base1);
   B200_LAUNCHED(ctx);
-  B200_TIMED(ctx, "groupby_partition", (gb_hp_part_kernel<1><<<grid, kHpThreads, int(sizeof(HpPartSmem)), ctx->stream>>>(a, h)));
+  if (a.row_ids)
+    B200_TIMED(ctx, "groupby_partition", (gb_hp_part_kernel<1, true><<<grid, kHpThreads, int(sizeof(HpPartSmem)), ctx->stream>>>(a, h)));
+  else
+    B200_TIMED(ctx, "groupby_partition", (gb_hp_part_kernel<1, false><<<grid, kHpThreads, int(offsetof(HpPartSmem, ord)), ctx->stream>>>(a, h)));
   HpBufs agg_src = buf_a;
   const uint32_t* agg_base = base1;
   char* images = reinterpret_cast<char*>(buf_b.keys);
@@ -2793,7 +2823,10 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
     B200_TIMED(ctx, "groupby_partition", (gb_hp_hist_kernel<2><<<grid, kHpThreads, 0, ctx->stream>>>(a, h)));
     gb_hp_scan_kernel<<<1, 1024, 0, ctx->stream>>>(hist2, parts, cursor2, base2);
     B200_LAUNCHED(ctx);
-    B200_TIMED(ctx, "groupby_partition", (gb_hp_part_kernel<2><<<grid, kHpThreads, int(sizeof(HpPartSmem)), ctx->stream>>>(a, h)));
+    if (a.row_ids)
+      B200_TIMED(ctx, "groupby_partition", (gb_hp_part_kernel<2, true><<<grid, kHpThreads, int(sizeof(HpPartSmem)), ctx->stream>>>(a, h)));
+    else
+      B200_TIMED(ctx, "groupby_partition", (gb_hp_part_kernel<2, false><<<grid, kHpThreads, int(offsetof(HpPartSmem, ord)), ctx->stream>>>(a, h)));
     agg_src = buf_b;
     agg_base = base2;
     images = reinterpret_cast<char*>(buf_a.keys);
@@ -3091,29 +3124,40 @@ int b200_groupby_create(b200_ctx* ctx, int n_keys, const int32_t* key_types, int
   B200_ENTER(ctx);
   if (!ctx || !out) return B200_INVALID;
   *out = nullptr;
-  if (n_keys < 1 || n_keys > kMaxKeys) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby: %d key columns (1..%d supported)", n_keys, kMaxKeys);
+  if (n_keys < 1 || n_keys > kWideMaxKeys)
+    return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby: %d key columns (1..%d supported)", n_keys, kWideMaxKeys);
   if (n_aggs < 0 || n_aggs > kMaxAggs) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby: %d aggregates (max %d)", n_aggs, kMaxAggs);
   GbSchema s;
   memset(&s, 0, sizeof(s));
-  s.n_keys = n_keys;
   s.n_aggs = n_aggs;
   int total = 0;
   for (int k = 0; k < n_keys; ++k) {
-    const int bits = b200_type_bits(key_types[k]);
     // GrouperImpl::Make: "Keys of type ..." NotImplemented for unsupported types (hash_aggregate.cc:352)
-    if (bits == 0) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "Keys of type %d", key_types[k]);
+    if (b200_type_bits(key_types[k]) == 0) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "Keys of type %d", key_types[k]);
+    total += b200_type_bits(key_types[k]);
+  }
+  // Keys that fit one 64-bit register (values + one null flag per column, or a single 64-bit column) are packed;
+  // anything wider goes through the key -> id table of groupby_wide.cuh and is grouped by a uint32 id column.
+  const int wide_n = n_keys;
+  const bool wide = n_keys > kMaxKeys || !(total + n_keys <= 64 || (n_keys == 1 && total == 64));
+  int32_t wide_types[kWideMaxKeys];
+  if (wide) {
+    for (int k = 0; k < n_keys; ++k) wide_types[k] = key_types[k];
+    static const int32_t id_type = B200_UINT32;
+    key_types = &id_type;
+    n_keys = 1;
+    total = 32;
+  }
+  s.n_keys = n_keys;
+  total = 0;
+  for (int k = 0; k < n_keys; ++k) {
+    const int bits = b200_type_bits(key_types[k]);
     s.key_type[k] = key_types[k];
     s.key_bits[k] = bits;
     s.key_shift[k] = total;
     total += bits;
   }
-  if (total + n_keys <= 64) {
-    s.null_shift = total;
-  } else if (n_keys == 1 && total == 64) {
-    s.null_shift = -1;
-  } else {
-    return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby: packed key of %d bits + %d null flags exceeds 64 bits", total, n_keys);
-  }
+  s.null_shift = (total + n_keys <= 64) ? total : -1;
   int off = 16;
   for (int j = 0; j < n_aggs; ++j) {
     const int kind = aggs[j].kind, t = aggs[j].arg_type;
@@ -3138,6 +3182,18 @@ int b200_groupby_create(b200_ctx* ctx, int n_keys, const int32_t* key_types, int
   gb->schema = s;
   gb->specs.assign(aggs, aggs + n_aggs);
   gb->expected = expected_groups > 0 ? uint64_t(expected_groups) : 0;
+  if (wide) {
+    gb->wide = true;
+    int pos = 0;
+    gb->wn_keys = wide_n;
+    for (int k = 0; k < wide_n; ++k) {
+      gb->wtypes[k] = wide_types[k];
+      gb->wbits[k] = b200_type_bits(wide_types[k]);
+      gb->woff[k] = pos;
+      pos += 1 + (gb->wbits[k] == 1 ? 1 : gb->wbits[k] / 8);
+    }
+    gb->wwords = (pos + 7) / 8;
+  }
   if (b200_dev_alloc(ctx, reinterpret_cast<void**>(&gb->counters), 8 * sizeof(uint32_t)) != B200_OK) {
     delete gb;
     return B200_OUT_OF_MEMORY;
@@ -3166,9 +3222,125 @@ int b200_groupby_destroy(b200_groupby* gb) {
   b200_dev_free(gb->ctx, gb->dense);
   b200_dev_free(gb->ctx, gb->tmp);
   b200_dev_free(gb->ctx, gb->hp_tmp);
+  b200_dev_free(gb->ctx, gb->wslots);
+  b200_dev_free(gb->ctx, gb->wstore);
+  b200_dev_free(gb->ctx, gb->wcounters);
+  b200_dev_free(gb->ctx, gb->wtmp);
   delete gb;
   return B200_OK;
 }
+
+
+// ---- wide keys: key columns -> one uint32 column of key ids (groupby_wide.cuh) ------------------------------------
+namespace {
+__global__ void wide_fill_kernel(uint64_t* p, uint64_t n) {
+  const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = kWideEmpty;
+}
+
+int wide_translate(b200_groupby* gb, const b200_col* keys, const uint32_t* select, b200_col* out) {
+  b200_ctx* ctx = gb->ctx;
+  const int64_t n = keys[0].length;
+  WideArgs a;
+  memset(&a, 0, sizeof(a));
+  a.n_keys = gb->wn_keys;
+  a.words = gb->wwords;
+  a.n = n;
+  a.select = select;
+  for (int k = 0; k < gb->wn_keys; ++k) {
+    const b200_col& c = keys[k];
+    if (c.type != gb->wtypes[k]) return b200_fail(ctx, B200_TYPE_ERROR, "groupby: key %d has type %d, expected %d", k, c.type, gb->wtypes[k]);
+    if (c.length != n) return b200_fail(ctx, B200_INVALID, "Array arguments must all be the same length");
+    if (n > 0 && !c.data) return b200_fail(ctx, B200_INVALID, "groupby: key %d has no data buffer", k);
+    WideKeyCol& w = a.cols[k];
+    const int bits = gb->wbits[k];
+    w.nbits = bits;
+    w.byte_off = gb->woff[k];
+    w.data = bits >= 8 ? reinterpret_cast<const char*>(c.data) + c.offset * (bits / 8) : nullptr;
+    w.bits = make_bitmap_ref(bits == 1 ? c.data : nullptr, c.offset);
+    const bool has_nulls = c.validity != nullptr && c.null_count != 0;
+    w.vv = has_nulls ? make_bitmap_ref(c.validity, c.offset) : BitmapRef{nullptr, 0};
+  }
+  memset(out, 0, sizeof(*out));
+  out->type = B200_UINT32;
+  out->length = n;
+  if (n == 0) return B200_OK;
+  if (n >= (int64_t(1) << 32)) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby: more than 2^32-1 rows per call with wide keys");
+  if (!gb->wcounters) {
+    B200_RETURN_NOT_OK(b200_dev_alloc(ctx, reinterpret_cast<void**>(&gb->wcounters), 64));
+    B200_CUDA(ctx, cudaMemsetAsync(gb->wcounters, 0, 64, ctx->stream));
+  }
+  // table at load <= 1/2 even if every row brings a new key; a grown table gets the stored keys back
+  uint64_t want = 1024;
+  while (want < 2 * (uint64_t(gb->wcount) + uint64_t(n))) want <<= 1;
+  if (want > gb->wcap) {
+    if (gb->wslots) b200_dev_free(ctx, gb->wslots);
+    gb->wslots = nullptr;
+    B200_RETURN_NOT_OK(b200_dev_alloc(ctx, reinterpret_cast<void**>(&gb->wslots), want * 8));
+    gb->wcap = want;
+    wide_fill_kernel<<<(unsigned)((want + 255) / 256), 256, 0, ctx->stream>>>(gb->wslots, want);
+    B200_LAUNCHED(ctx);
+    if (gb->wcount) {
+      wide_rehash_kernel<<<(gb->wcount + 255) / 256, 256, 0, ctx->stream>>>(gb->wstore, gb->wwords, gb->wcount, gb->wslots, gb->wcap, gb->wcounters);
+      B200_LAUNCHED(ctx);
+    }
+  }
+  const size_t a4 = b200_align_up(size_t(n) * 4, 256);
+  if (3 * a4 > gb->wtmp_bytes) {
+    if (gb->wtmp) b200_dev_free(ctx, gb->wtmp);
+    gb->wtmp = nullptr;
+    gb->wtmp_bytes = 0;
+    B200_RETURN_NOT_OK(b200_dev_alloc(ctx, &gb->wtmp, 3 * a4));
+    gb->wtmp_bytes = 3 * a4;
+  }
+  a.slots = gb->wslots;
+  a.cap = gb->wcap;
+  a.store = gb->wstore;
+  a.counters = gb->wcounters;
+  a.new_slots = reinterpret_cast<uint32_t*>(gb->wtmp);
+  a.row_slot = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(gb->wtmp) + a4);
+  a.ids = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(gb->wtmp) + 2 * a4);
+  B200_CUDA(ctx, cudaMemsetAsync(gb->wcounters + 1, 0, sizeof(uint32_t), ctx->stream));
+  const unsigned grid = unsigned((n + 255) / 256);
+  B200_TIMED(ctx, "groupby_wide_keys", (wide_insert_kernel<<<grid, 256, 0, ctx->stream>>>(a)));
+  B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 40, gb->wcounters, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  const uint32_t* hc = reinterpret_cast<const uint32_t*>(ctx->host_words + 40);
+  if (hc[2] != 0) return b200_fail(ctx, B200_UNKNOWN_ERROR, "groupby: wide-key table error %u", hc[2]);
+  const uint32_t n_new = hc[1];
+  if (n_new) {
+    if (uint64_t(gb->wcount) + n_new > gb->wstore_cap) {
+      uint64_t cap = std::max<uint64_t>(1024, gb->wstore_cap);
+      while (cap < uint64_t(gb->wcount) + n_new) cap <<= 1;
+      if (cap > 0xFFFFFFF0ull) return b200_fail(ctx, B200_CAPACITY_ERROR, "groupby: more than 2^32 distinct wide keys");
+      uint64_t* ns = nullptr;
+      B200_RETURN_NOT_OK(b200_dev_alloc(ctx, reinterpret_cast<void**>(&ns), cap * gb->wwords * 8));
+      if (gb->wcount) B200_CUDA(ctx, cudaMemcpyAsync(ns, gb->wstore, size_t(gb->wcount) * gb->wwords * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+      if (gb->wstore) {
+        B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        b200_dev_free(ctx, gb->wstore);
+      }
+      gb->wstore = ns;
+      gb->wstore_cap = uint32_t(cap);
+      a.store = ns;
+    }
+    wide_assign_kernel<<<(n_new + 255) / 256, 256, 0, ctx->stream>>>(a, n_new, gb->wcount);
+    B200_LAUNCHED(ctx);
+    gb->wcount += n_new;
+  }
+  B200_TIMED(ctx, "groupby_wide_keys", (wide_ids_kernel<<<grid, 256, 0, ctx->stream>>>(a)));
+  out->data = a.ids;
+  out->null_count = 0;
+  return B200_OK;
+}
+}  // namespace
+
+#define B200_NARROW_KEYS(gb, keys, select)                                   \
+  b200_col _narrow_key;                                                      \
+  if ((gb) && (gb)->wide && (keys)) {                                        \
+    B200_RETURN_NOT_OK(wide_translate((gb), (keys), (select), &_narrow_key)); \
+    (keys) = &_narrow_key;                                                   \
+  }
 
 int b200_groupby_set_option(b200_groupby* gb, const char* name, int64_t value) {
   B200_ENTER(gb ? gb->ctx : nullptr);
@@ -3207,6 +3379,7 @@ static int groupby_consume_impl(b200_groupby* gb, const b200_col* keys, const b2
   b200_ctx* ctx = gb->ctx;
   if (!keys || (gb->schema.n_aggs > 0 && !args)) return b200_fail(ctx, B200_INVALID, "groupby_consume: null argument");
   if (gb->dense_used) return b200_fail(ctx, B200_INVALID, "groupby: handle already used through b200_hash_agg_consume");
+  B200_NARROW_KEYS(gb, keys, select);
   GbArgs a;
   memset(&a, 0, sizeof(a));
   a.s = gb->schema;
@@ -3268,7 +3441,7 @@ int try_fused8(b200_groupby* gb, const b200_col* keys, const b200_fused_arg* arg
   *taken = false;
   const GbSchema& s = gb->schema;
   const uint64_t likely = std::max<uint64_t>(gb->groups, gb->expected);
-  if (likely == 0 || likely > uint64_t(kTinyGroups) || s.n_keys > 3 || s.n_aggs == 0) return B200_OK;
+  if (gb->wide || likely == 0 || likely > uint64_t(kTinyGroups) || s.n_keys > 3 || s.n_aggs == 0) return B200_OK;
   const int64_t n = keys[0].length;
   if (n < kBinTile) return B200_OK;
   for (int k = 0; k < s.n_keys; ++k)
@@ -3495,6 +3668,7 @@ int b200_groupby_partition_plan(b200_groupby* gb, const b200_col* keys, int n_pa
   b200_ctx* ctx = gb->ctx;
   if (!keys || !out_counts) return b200_fail(ctx, B200_INVALID, "partition_plan: null argument");
   if (n_parts < 1 || n_parts > kPartMax) return b200_fail(ctx, B200_INVALID, "partition_plan: 1..%d partitions", kPartMax);
+  if (gb->wide) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "partition_plan: keys wider than 64 packed bits");
   GbArgs a;
   memset(&a, 0, sizeof(a));
   a.s = gb->schema;
@@ -3590,6 +3764,7 @@ int b200_grouper_consume(b200_groupby* gb, const b200_col* keys, uint32_t* out_i
   if (!gb) return B200_INVALID;
   b200_ctx* ctx = gb->ctx;
   if (!keys) return b200_fail(ctx, B200_INVALID, "grouper_consume: null keys");
+  B200_NARROW_KEYS(gb, keys, nullptr);
   GbArgs a;
   memset(&a, 0, sizeof(a));
   a.s = gb->schema;
@@ -3792,6 +3967,7 @@ int b200_groupby_export(b200_groupby* gb, void* out_state, uint32_t* out_groups)
   b200_ctx* ctx = gb->ctx;
   uint64_t *first_rows, *slot_idx;
   uint32_t G;
+  if (gb->wide) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby_export: keys wider than 64 packed bits (the key store is not part of the state image)");
   B200_RETURN_NOT_OK(materialize(gb));
   B200_RETURN_NOT_OK(collect_slots(gb, &first_rows, &slot_idx, &G, 0, nullptr));
   if (G > 0) {
@@ -3811,6 +3987,7 @@ int b200_groupby_import(b200_groupby* gb, const void* state, uint32_t n_slots) {
   b200_ctx* ctx = gb->ctx;
   if (n_slots == 0) return B200_OK;
   if (!state) return b200_fail(ctx, B200_INVALID, "groupby_import: null state");
+  if (gb->wide) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby_import: keys wider than 64 packed bits");
   gb->row_bound = ~uint64_t(0);
   B200_RETURN_NOT_OK(materialize(gb));
   uint32_t c[4];
@@ -3828,6 +4005,7 @@ int b200_groupby_merge(b200_groupby* dst, b200_groupby* src) {
   b200_ctx* ctx = dst->ctx;
   if (memcmp(&dst->schema, &src->schema, sizeof(GbSchema)) != 0) return b200_fail(ctx, B200_TYPE_ERROR, "groupby_merge: schemas differ");
   if (dst->ctx != src->ctx) return b200_fail(ctx, B200_INVALID, "groupby_merge: handles belong to different contexts");
+  if (dst->wide || src->wide) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby_merge: keys wider than 64 packed bits");
   dst->row_bound = std::max(dst->row_bound, src->row_bound);
   B200_RETURN_NOT_OK(materialize(dst));
   B200_RETURN_NOT_OK(materialize(src));
@@ -3886,7 +4064,19 @@ int b200_groupby_finalize(b200_groupby* gb, b200_out_col* out_aggs, b200_out_col
   }
   e.n_groups = G;
   B200_CUDA(ctx, cudaMemsetAsync(e.null_counts, 0, (kMaxKeys + 2 * kMaxAggs) * sizeof(uint32_t), ctx->stream));
-  for (int k = 0; k < e.s.n_keys; ++k) {
+  uint32_t* wide_ids = nullptr;   // wide keys: the stand-in uint32 key column is emitted here, then decoded
+  if (gb->wide && out_keys && !gb->dense_used) {
+    B200_RETURN_NOT_OK(b200_dev_alloc(ctx, reinterpret_cast<void**>(&wide_ids), size_t(std::max<uint32_t>(G, 1)) * 4 + 512));
+    e.keys[0].data = wide_ids;
+    e.keys[0].validity = nullptr;
+    e.keys[0].type = B200_UINT32;
+    for (int k = 0; k < gb->wn_keys; ++k)
+      if (G > 0 && !out_keys[k].data) {
+        b200_dev_free(ctx, wide_ids);
+        return b200_fail(ctx, B200_INVALID, "groupby_finalize: key %d has no data buffer", k);
+      }
+  }
+  for (int k = 0; k < e.s.n_keys && !gb->wide; ++k) {
     if (out_keys && !gb->dense_used) {
       e.keys[k].data = out_keys[k].data;
       e.keys[k].validity = reinterpret_cast<uint32_t*>(out_keys[k].validity);
@@ -3908,11 +4098,42 @@ int b200_groupby_finalize(b200_groupby* gb, b200_out_col* out_aggs, b200_out_col
     gb_emit_kernel<<<(G + 255) / 256, 256, 0, ctx->stream>>>(e);
     B200_LAUNCHED(ctx);
   }
+  if (wide_ids) {
+    WideDecodeArgs d;
+    memset(&d, 0, sizeof(d));
+    d.ids = wide_ids;
+    d.n_groups = G;
+    d.store = gb->wstore;
+    d.words = gb->wwords;
+    d.n_keys = gb->wn_keys;
+    d.null_counts = wide_ids + ((size_t(std::max<uint32_t>(G, 1)) * 4 + 255) / 256 * 256) / 4;
+    for (int k = 0; k < gb->wn_keys; ++k) {
+      d.nbits[k] = gb->wbits[k];
+      d.byte_off[k] = gb->woff[k];
+      d.data[k] = out_keys[k].data;
+      d.validity[k] = reinterpret_cast<uint32_t*>(out_keys[k].validity);
+    }
+    B200_CUDA(ctx, cudaMemsetAsync(d.null_counts, 0, kWideMaxKeys * sizeof(uint32_t), ctx->stream));
+    if (G > 0) {
+      wide_decode_kernel<<<(G + 255) / 256, 256, 0, ctx->stream>>>(d);
+      B200_LAUNCHED(ctx);
+    }
+    B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 44, d.null_counts, kWideMaxKeys * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  }
   B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 24, e.null_counts, (kMaxKeys + 2 * kMaxAggs) * sizeof(uint32_t),
                                  cudaMemcpyDeviceToHost, ctx->stream));
   B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   const uint32_t* nc = reinterpret_cast<const uint32_t*>(ctx->host_words + 24);
-  for (int k = 0; k < e.s.n_keys && out_keys && !gb->dense_used; ++k) {
+  if (wide_ids) {
+    const uint32_t* wnc = reinterpret_cast<const uint32_t*>(ctx->host_words + 44);
+    for (int k = 0; k < gb->wn_keys; ++k) {
+      out_keys[k].length = G;
+      out_keys[k].null_count = wnc[k];
+      out_keys[k].type = gb->wtypes[k];
+    }
+    b200_dev_free(ctx, wide_ids);
+  }
+  for (int k = 0; k < e.s.n_keys && out_keys && !gb->dense_used && !gb->wide; ++k) {
     out_keys[k].length = G;
     out_keys[k].null_count = nc[k];
     out_keys[k].type = e.s.key_type[k];

@@ -35,6 +35,8 @@ struct HpBufs {
   uint64_t* keys;
   uint64_t* vals;
   uint32_t* rows;   // row inside the batch | value-is-null << 31
+  uint32_t* ord;    // nullable: explicit global row number - the batch's smallest one (b200_groupby_consume_rows);
+                    // the earliest row of a group is then the minimum of these instead of the minimum of `rows`
 };
 
 struct HpArgs {
@@ -47,6 +49,7 @@ struct HpArgs {
   int32_t shift;          // bin = (mix64(key) >> shift) & (bins - 1)
   int32_t bins;
   int32_t has_val;
+  uint64_t ord_base;      // level 1 with explicit row numbers: the smallest one
   int32_t fast;           // level 1: one key column of `fast` bytes (4 / 8) without nulls, 64-bit value column without
                           // nulls (or none): straight-line loads, all of a thread's rows in flight together
 };
@@ -192,9 +195,10 @@ struct HpPartSmem {
   uint32_t warp_sums[kHpThreads / 32];
   uint32_t sbase[kHpMaxBins + 1];
   uint32_t deferred;
+  uint32_t ord[kHpTile];   // last: only the kernels that carry explicit row numbers allocate it
 };
 
-template <int LEVEL>
+template <int LEVEL, bool kOrd>
 __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_part_kernel(const __grid_constant__ GbArgs a, const __grid_constant__ HpArgs h) {
   extern __shared__ __align__(16) unsigned char hp_smem_raw[];
   HpPartSmem& S = *reinterpret_cast<HpPartSmem*>(hp_smem_raw);
@@ -220,6 +224,16 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_part_kernel(const __grid_
         // ---- load, bin, rank inside the tile's bin (native ATOMS.ADD with return)
         uint64_t key[kHpItems], val[kHpItems];
         uint32_t r32[kHpItems], meta[kHpItems];   // meta = bin | rank << 16, 0xFFFFFFFF = not staged
+        uint32_t ord[kOrd ? kHpItems : 1];
+        constexpr bool has_ord = kOrd;
+        if (kOrd) {
+#pragma unroll
+          for (int i = 0; i < kHpItems; ++i) {
+            const int64_t row = seg0 + i * kHpThreads + t;
+            ord[kOrd ? i : 0] = 0;
+            if (row < seg1) ord[kOrd ? i : 0] = LEVEL == 2 ? h.src.ord[row] : uint32_t(a.row_ids[row] - h.ord_base);
+          }
+        }
         if (LEVEL == 2 || h.fast) {
           // straight-line loads: all of the thread's rows are requested before the first is looked at
           const uint64_t* k64 = LEVEL == 2 ? h.src.keys : reinterpret_cast<const uint64_t*>(a.keys[0].data);
@@ -318,6 +332,7 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_part_kernel(const __grid_
             S.keys[pos] = key[i];
             S.vals[pos] = val[i];
             S.rows[pos] = r32[i];
+            if (kOrd) S.ord[pos] = ord[kOrd ? i : 0];
             S.bin[pos] = uint16_t(b);
           }
         }
@@ -329,6 +344,7 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_part_kernel(const __grid_
           h.dst.keys[g] = S.keys[j];
           if (h.has_val) h.dst.vals[g] = S.vals[j];
           h.dst.rows[g] = S.rows[j];
+          if (has_ord) h.dst.ord[g] = S.ord[j];
         }
       }
       seg0 = seg1;
@@ -412,7 +428,7 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_c
     constexpr int kU = 4;   // rows per thread in flight: their loads are issued together
     for (uint32_t i0 = begin; i0 < end; i0 += kHpThreads * kU) {
       uint64_t key[kU], v[kU];
-      uint32_t r32[kU];
+      uint32_t r32[kU], ord[kU];
       bool in[kU];
 #pragma unroll
       for (int u = 0; u < kU; ++u) {
@@ -420,6 +436,7 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_c
         in[u] = i < end;
         key[u] = in[u] ? src.keys[i] : 0;
         r32[u] = in[u] ? src.rows[i] : 0;
+        ord[u] = (in[u] && src.ord) ? src.ord[i] : (r32[u] & kHpRowMask);
         v[u] = (in[u] && a.n_cols) ? src.vals[i] : 0;
       }
 #pragma unroll
@@ -443,7 +460,7 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_c
           atomicAdd(&S.deferred, 1u);
           continue;
         }
-        atomicMin(&S.row[slot], row);
+        atomicMin(&S.row[slot], ord[u]);
         if (r32[u] & kHpNullBit) {
           atomicAdd(&S.cnt_null[slot], 1u);
         } else {
@@ -511,7 +528,7 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_c
       ++pos;
       const uint32_t row = S.row[s];
       img[0] = key;
-      img[1] = a.row_ids ? a.row_ids[row] : a.row_base + uint64_t(row);
+      img[1] = a.row_base + uint64_t(row);   // with explicit row numbers row_base is the batch's smallest one
       for (int w = 2; w < words; ++w) img[w] = 0;
       for (int j = 0; j < a.s.n_aggs; ++j) {
         const GbAgg& g = a.s.aggs[j];
@@ -555,7 +572,21 @@ __global__ void __launch_bounds__(256) gb_hp_import_kernel(const __grid_constant
   if (threadIdx.x == 0 && s_new) atomicAdd(counters + 0, s_new);
 }
 
-__global__ void gb_hp_monotone_kernel(const uint64_t* row_ids, int64_t n, uint32_t* flag) {
-  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i > 0 && i < n && row_ids[i] <= row_ids[i - 1]) *flag = 1u;
+// smallest and largest explicit row number of a batch -> mm[0], mm[1] (mm[0] starts at all ones, mm[1] at zero)
+__global__ void gb_hp_minmax_kernel(const uint64_t* row_ids, int64_t n, unsigned long long* mm) {
+  uint64_t lo = ~uint64_t(0), hi = 0;
+  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+    const uint64_t r = row_ids[i];
+    lo = min(lo, r);
+    hi = max(hi, r);
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, d));
+    hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, d));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMin(mm, (unsigned long long)lo);
+    atomicMax(mm + 1, (unsigned long long)hi);
+  }
 }

@@ -141,7 +141,8 @@ def test_dist_group_by_merge_and_repartition_match_oracle(world):
     cases.append(("merge", [k], aggs3, [v, v, v], 1000))
     k2 = Column.from_numpy(rng.integers(0, 5, size=n).astype(np.uint8), rng.random(n) > 0.05)
     cases.append(("merge", [k2, k], [AggSpec(cols.HASH_MEAN), AggSpec(cols.HASH_COUNT, 1)], [v, v], 0))
-    k64 = Column.from_numpy((rng.integers(0, 150_000, size=n).astype(np.int64) * 0x9E3779B97F4A7C15) >> 3)
+    with np.errstate(over="ignore"):
+        k64 = Column.from_numpy((rng.integers(0, 150_000, size=n).astype(np.uint64) * np.uint64(0x9E3779B97F4A7C15)).view(np.int64))
     aggs4 = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_MEAN)]
     cases.append(("repartition", [k64], aggs4, [v, v], 150_000))
     kn = Column.from_numpy(rng.integers(-40_000, 40_000, size=n).astype(np.int64), rng.random(n) > 0.03)

@@ -223,9 +223,14 @@ def test_groupby_unsupported(ctx):
     with pytest.raises(capi.B200Error) as ei:  # summing booleans (hash_aggregate.cc:550-556)
         capi.GroupBy(ctx, [cols.INT32], [AggSpec(cols.HASH_SUM)], [cols.BOOL])
     assert ei.value.code == 10
-    with pytest.raises(capi.B200Error) as ei:  # packed key wider than 64 bits
-        capi.GroupBy(ctx, [cols.INT64, cols.INT64], [], [])
+    with pytest.raises(capi.B200Error) as ei:  # more key columns than the key encoder of this library takes
+        capi.GroupBy(ctx, [cols.INT64] * 17, [], [])
     assert ei.value.code == 10
+    gb = capi.GroupBy(ctx, [cols.INT64, cols.INT64], [], [])   # wide keys are grouped through the key -> id table,
+    with pytest.raises(capi.B200Error) as ei:                   # but their state image cannot be exported
+        gb.export_state()
+    assert ei.value.code == 10
+    gb.close()
 
 
 def test_groupby_config3_shape(ctx):
@@ -438,3 +443,57 @@ def test_groupby_partitioned_path_streaming_selected_and_rows(ctx):
     gb = handle(60_000)
     gb.consume_selected([key.to_device()], [arg.to_device()] * 2, Column.from_numpy(sel).to_device())
     assert_group_equal(finish(gb), want_sel, aggs, rtol=RTOL)
+
+
+# ---- keys wider than 64 packed bits / more than 4 key columns (FixedWidthKeyEncoder takes any, hash_aggregate.cc:142-196)
+@pytest.mark.parametrize("kts", [(cols.INT64, cols.INT64), (cols.INT64, cols.INT32, cols.UINT8),
+                                 (cols.DOUBLE, cols.BOOL, cols.INT16, cols.UINT64, cols.FLOAT),
+                                 (cols.UINT8,) * 6, (cols.INT32,) * 3])
+def test_groupby_wide_keys(ctx, kts):
+    rng = np.random.default_rng(sum(kts) + len(kts))
+    for n, hi in ((1, 3), (3000, 3), (200_000, 40)):
+        keys = [rand_column(rng, t, n, 0.1 if i % 2 == 0 else 0.0, lo=0, hi=(1 if t == cols.BOOL else hi),
+                            special=(t in (cols.FLOAT, cols.DOUBLE))) for i, t in enumerate(kts)]
+        arg = rand_column(rng, cols.DOUBLE, n, 0.2)
+        iarg = rand_column(rng, cols.INT32, n, 0.1)
+        aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT), AggSpec(cols.HASH_MIN_MAX), AggSpec(cols.HASH_MEAN), AggSpec(cols.HASH_SUM)]
+        args = [arg, arg, arg, arg, iarg]
+        a = run_groupby("gpu", keys, aggs, args, ctx, want_ids=True)
+        b = run_groupby(ORACLE, keys, aggs, args, want_ids=True)
+        assert_group_equal(a, b, aggs, rtol=RTOL, scales=abs_sum_scales(keys, aggs, args))
+
+
+def test_groupby_wide_keys_streaming_and_selection(ctx):
+    """Two 64-bit keys over several batches (the key table grows and keeps the ids of earlier batches) and through a
+    selection; Grouper ids continue across calls."""
+    from arrow1_b200 import capi
+    from helpers import GroupRes
+    rng = np.random.default_rng(99)
+    n = 150_000
+    k0 = Column.from_numpy(rng.integers(0, 300, size=n).astype(np.int64) * (1 << 40))
+    k1 = Column.from_numpy(rng.integers(-50, 50, size=n).astype(np.int64), rng.random(n) > 0.05)
+    arg = Column.from_numpy(rng.random(n), rng.random(n) > 0.1)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT)]
+    want = run_groupby(ORACLE, [k0, k1], aggs, [arg] * 2, want_ids=True)
+    d0, d1, da = k0.to_device(), k1.to_device(), arg.to_device()
+    gb = capi.GroupBy(ctx, [k0.type, k1.type], aggs, [arg.type] * 2)
+    gr = capi.GroupBy(ctx, [k0.type, k1.type], [], [])
+    ids = []
+    for lo, hi in ((0, 1000), (1000, 70_000), (70_000, n)):
+        sl = lambda c, nc: Column(c.type, c.data, c.validity, hi - lo, lo, nc)   # noqa: E731
+        gb.consume([sl(d0, 0), sl(d1, -1)], [sl(da, -1)] * 2, row_base=lo)
+        ids.append(gr.grouper_consume([sl(d0, 0), sl(d1, -1)]).cpu().numpy().view(np.uint32).copy())
+    out = gb.finalize()
+    gb.close()
+    gr.close()
+    a = GroupRes(out.num_groups, [[(c.to_host().values().copy(), c.to_host().valid()) for c in ag] for ag in out.aggs],
+                 [(c.to_host().values().copy(), c.to_host().valid()) for c in out.keys], np.concatenate(ids))
+    assert_group_equal(a, GroupRes(want.num_groups, want.aggs, want.keys, want.ids), aggs, rtol=RTOL)
+    sel = rng.random(n) < 0.5
+    kept = np.flatnonzero(sel)
+    f = lambda c: Column.from_numpy(c.values()[kept].copy(), c.valid()[kept].copy() if c.validity is not None else None)   # noqa: E731
+    want_sel = run_groupby(ORACLE, [f(k0), f(k1)], aggs, [f(arg)] * 2)
+    got = capi.group_by(ctx, [d0, d1], aggs, [da] * 2, selection=Column.from_numpy(sel).to_device())
+    a = GroupRes(got.num_groups, [[(c.to_host().values().copy(), c.to_host().valid()) for c in ag] for ag in got.aggs],
+                 [(c.to_host().values().copy(), c.to_host().valid()) for c in got.keys])
+    assert_group_equal(a, want_sel, aggs, rtol=RTOL)
