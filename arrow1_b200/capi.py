@@ -161,6 +161,47 @@ class FilterPlan:
         return FilterOutput(col, has_validity)
 
 
+class FusedFilterScratch:
+    """Look-back state of b200_filter_fused for masks of up to `length` rows; its first 8 bytes hold the int64
+    output length of the last call (device)."""
+
+    def __init__(self, ctx: Context, length: int):
+        nbytes = C.c_size_t(0)
+        ctx.check(lib().b200_filter_fused_scratch_bytes(C.c_int64(length), C.byref(nbytes)))
+        self.length = length
+        self.buf = ctx.empty(nbytes.value + 64)
+        self.ptr = (self.buf.data_ptr() + 63) // 64 * 64
+
+    def length_tensor(self) -> torch.Tensor:
+        off = self.ptr - self.buf.data_ptr()
+        return self.buf[off: off + 8].view(torch.int64)
+
+
+def filter_fused(ctx: Context, values: Column, mask: Column, null_selection: int = 0,
+                 out_data: Optional[torch.Tensor] = None, out_validity: Optional[torch.Tensor] = None,
+                 capacity: Optional[int] = None, scratch: Optional[FusedFilterScratch] = None, sync: bool = True) -> FilterOutput:
+    """b200_filter_fused: Filter in one launch into an output of `capacity` rows (default: the mask length).
+    sync=False leaves the output length on the device (scratch.length_tensor()); the Column's length is then -1."""
+    cap = mask.length if capacity is None else capacity
+    has_validity, null_count = filter_out_spec(values, mask, null_selection)
+    bits = BITS[values.type]
+    if out_data is None:
+        out_data = ctx.empty((cap + 7) // 8 + 8 if bits == 1 else max(cap, 1) * (bits // 8))
+    if has_validity and out_validity is None:
+        out_validity = ctx.empty((cap + 7) // 8 + 8)
+    if scratch is None or scratch.length < mask.length:
+        scratch = FusedFilterScratch(ctx, mask.length)
+    v, m = values.desc(), mask.desc()
+    out_len = C.c_int64(-1)
+    ctx.check(lib().b200_filter_fused(ctx._h, C.byref(v), C.byref(m), C.c_int(null_selection), C.c_void_p(scratch.ptr),
+                                      C.c_void_p(out_data.data_ptr()), C.c_void_p(out_validity.data_ptr()) if has_validity else None,
+                                      C.c_int64(cap), C.byref(out_len) if sync else None))
+    col = Column(values.type, out_data, out_validity if has_validity else None, int(out_len.value) if sync else -1, 0, null_count)
+    out = FilterOutput(col, has_validity)
+    out.scratch = scratch
+    return out
+
+
 CMP_OPS = {"equal": 0, "not_equal": 1, "greater": 2, "greater_equal": 3, "less": 4, "less_equal": 5}
 
 

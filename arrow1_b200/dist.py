@@ -600,8 +600,10 @@ def bench_self_check(ctx, wl, cols_, bufs):
         bits = mask.data[: (mask.length + 7) // 8]
         w = torch.tensor([1, 2, 4, 8, 16, 32, 64, 128], dtype=torch.uint8, device=dev)
         want = int(((bits.unsqueeze(1) & w) != 0).reshape(-1)[: mask.length].sum().item())
-        return {"workload": wl.name, "rows_total": n_total, "selected_rows_total": allsum(res.length),
-                "output_length_matches_mask": bool(allsum(0 if res.length == want else 1) == 0)}
+        ctx.synchronize()
+        got = res.length if res.length >= 0 else int(res.scratch.length_tensor().item())   # the bench step keeps it on the device
+        return {"workload": wl.name, "rows_total": n_total, "selected_rows_total": allsum(got),
+                "output_length_matches_mask": bool(allsum(0 if got == want else 1) == 0)}
     if wl.name == "groupby_c3":
         counts = res.aggs[1][0].values()
         valid_local = wl.n - cols_[1].null_count

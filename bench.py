@@ -269,14 +269,19 @@ class FilterWL(Workload):
         sel = (self.out_len or self.n // 2)
         return self.n * (8 + 1 / 8 + 1 / 8) + sel * (8 + 1 / 8)
 
+    kernel = "filter_fused"
+
     def prepare(self, ctx, cols_):
-        return {"data": ctx.empty(self.n * 8), "validity": ctx.empty((self.n + 7) // 8)}
+        from arrow1_b200 import capi
+        return {"data": ctx.empty(self.n * 8), "validity": ctx.empty((self.n + 7) // 8 + 8),
+                "scratch": capi.FusedFilterScratch(ctx, self.n)}
 
     def step(self, ctx, cols_, bufs):
+        # one launch into reused buffers sized by the mask length; the output length stays on the device
+        # (b200_filter_fused; the plan + apply form with the host round trip is what compute.Filter / e2e use)
         from arrow1_b200 import capi
-        plan = capi.FilterPlan(ctx, cols_[1], 0, sync=True)   # GetFilterOutputSize -> host (vector_selection.cc:61-88)
-        self.out_len = plan.out_length
-        return plan.apply(cols_[0], bufs["data"], bufs["validity"])
+        out = capi.filter_fused(ctx, cols_[0], cols_[1], 0, bufs["data"], bufs["validity"], self.n, bufs["scratch"], sync=False)
+        return out
 
     def e2e_step(self, host_cols):
         from arrow1_b200 import compute
@@ -597,7 +602,7 @@ def kernel_times(ctx, names):
 
 
 ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume", "compare_scalar", "arithmetic", "take", "partition_plan", "partition_scatter", "sort_partition",
-               "groupby_partition", "groupby_import", "groupby_fused")
+               "groupby_partition", "groupby_import", "groupby_fused", "filter_fused", "groupby_wide_keys")
 
 
 def time_device(ctx, wl, cols_, steps, warmup, world, dist_step=None):

@@ -147,6 +147,18 @@ B200_API int b200_filter_apply(b200_ctx* ctx, const b200_col* values, const b200
                                void* out_validity /* nullable */, int64_t out_capacity);
 B200_API int b200_filter_out_spec(const b200_col* values, const b200_col* mask, int null_selection,
                                   int* allocate_validity, int64_t* out_null_count);
+/* Filter in ONE launch for callers that already own an output of `out_capacity` rows (a reused buffer sized by the
+ * mask length or by the previous batch): count, output offsets (decoupled look-back over 4096-row tiles) and
+ * compaction in the same kernel, no host round trip.  == GetFilterOutputSize + PrimitiveFilterImpl::Exec
+ * (vector_selection.cc:61-88, 570-764) without PreallocateData in between.  `scratch`: DEVICE, 64-byte aligned,
+ * b200_filter_fused_scratch_bytes(mask length) bytes; its first 8 bytes receive the int64 output length (readable
+ * through b200_filter_plan_length_ptr).  out_len: HOST, nullable; when given the call synchronises and returns the
+ * length.  If the selection emits more than out_capacity rows nothing past the capacity is written and the context
+ * reports it at the next b200_ctx_synchronize. */
+B200_API int b200_filter_fused_scratch_bytes(int64_t mask_length, size_t* out_bytes);
+B200_API int b200_filter_fused(b200_ctx* ctx, const b200_col* values, const b200_col* mask, int null_selection,
+                               void* scratch, void* out_data, void* out_validity /* nullable */,
+                               int64_t out_capacity, int64_t* out_len /* host, nullable */);
 /* device address of the int64 output length inside a plan (for fully asynchronous callers) */
 B200_API const int64_t* b200_filter_plan_length_ptr(const void* plan);
 

@@ -22,7 +22,10 @@ def run_filter(impl, values: Column, mask: Column, null_selection: int, ctx=None
         return FilterRes(r.length, r.null_count, r.has_validity, r.values(), r.valid(), r.data_bytes(),
                          r.validity_bytes())
     from arrow1_b200 import capi
-    out = capi.filter(ctx, values.to_device(), mask.to_device(), null_selection)
+    if impl == "gpu_fused":   # one launch, output sized by the mask length, no host round trip inside
+        out = capi.filter_fused(ctx, values.to_device(), mask.to_device(), null_selection)
+    else:
+        out = capi.filter(ctx, values.to_device(), mask.to_device(), null_selection)
     col = out.col
     host = col.to_host()
     valid = host.valid() if out.has_validity else np.ones(col.length, dtype=np.bool_)

@@ -26,6 +26,7 @@ def test_filter_random_matrix(ctx, t):
                     mask = rand_mask(rng, 1024, true_prob, mask_null, offset=moff)
                     for null_sel in (0, 1):
                         a = run_filter("gpu", values, mask, null_sel, ctx)
+                        assert_filter_equal(run_filter("gpu_fused", values, mask, null_sel, ctx), a)
                         b = run_filter(ORACLE, values, mask, null_sel)
                         assert_filter_equal(a, b)
 
@@ -39,6 +40,7 @@ def test_filter_sizes_and_offsets(ctx, n):
             values = rand_column(rng, t, n, 0.1, offset=voff)
             mask = rand_mask(rng, n, 0.5, 0.05, offset=moff)
             for null_sel in (0, 1):
+                assert_filter_equal(run_filter("gpu_fused", values, mask, null_sel, ctx), run_filter(ORACLE, values, mask, null_sel))
                 assert_filter_equal(run_filter("gpu", values, mask, null_sel, ctx),
                                     run_filter(ORACLE, values, mask, null_sel))
 
@@ -113,6 +115,7 @@ def test_filter_config1_full_size(ctx):
         bits = (rand_u64(3, n) & np.uint64(1)).astype(np.bool_)
     v = Column.from_numpy(values, valid)
     m = Column.from_numpy(bits)
+    assert_filter_equal(run_filter("gpu_fused", v, m, 0, ctx), run_filter("gpu", v, m, 0, ctx))
     a = run_filter("gpu", v, m, 0, ctx)
     b = run_filter(ORACLE, v, m, 0)
     assert_filter_equal(a, b)
@@ -159,4 +162,34 @@ def test_filter_apply_rejects_small_output_and_sync_reports_it(ctx):
     with pytest.raises(B200Error) as e:
         ctx.synchronize()
     assert "look-back" in str(e.value)
+    ctx.synchronize()
+
+
+def test_filter_fused_async_and_small_capacity(ctx):
+    """b200_filter_fused without a host round trip: the length stays on the device; a capacity below the output
+    length writes nothing past it and is reported at the next synchronisation."""
+    import torch
+    from arrow1_b200 import capi
+    from arrow1_b200.capi import B200Error
+    rng = np.random.default_rng(31)
+    n = 1_000_003
+    values = Column.from_numpy(rng.integers(-2**62, 2**62, size=n, dtype=np.int64), rng.random(n) > 0.01)
+    mask = Column.from_numpy(rng.random(n) < 0.5)
+    want = run_filter(ORACLE, values, mask, 0)
+    dv, dm = values.to_device(), mask.to_device()
+    scratch = capi.FusedFilterScratch(ctx, n)
+    for _ in range(3):   # the scratch is reused call after call
+        out = capi.filter_fused(ctx, dv, dm, 0, scratch=scratch, sync=False)
+        ctx.synchronize()
+        m = int(scratch.length_tensor().item())
+        assert m == want.length
+        assert out.col.data[: m * 8].cpu().numpy().tobytes() == want.data_bytes
+        assert out.col.validity[: (m + 7) // 8].cpu().numpy().tobytes() == want.validity_bytes
+    small = want.length - 5000
+    data = torch.full((small * 8 + 65536,), 0x5A, dtype=torch.uint8, device="cuda")
+    capi.filter_fused(ctx, dv, dm, 0, out_data=data, capacity=small, scratch=scratch, sync=False)
+    with pytest.raises(B200Error) as e:
+        ctx.synchronize()
+    assert "filter output" in str(e.value)
+    assert bool((data[small * 8:] == 0x5A).all())
     ctx.synchronize()
