@@ -169,8 +169,8 @@ class FusedFilterScratch:
         nbytes = C.c_size_t(0)
         ctx.check(lib().b200_filter_fused_scratch_bytes(C.c_int64(length), C.byref(nbytes)))
         self.length = length
-        self.buf = ctx.empty(nbytes.value + 64)
-        self.ptr = (self.buf.data_ptr() + 63) // 64 * 64
+        self.buf = ctx.empty(nbytes.value + 256)
+        self.ptr = (self.buf.data_ptr() + 255) // 256 * 256
 
     def length_tensor(self) -> torch.Tensor:
         off = self.ptr - self.buf.data_ptr()
@@ -700,6 +700,22 @@ def pack_validity(ctx: Context, valid_bytes: torch.Tensor):
     ctx.check(lib().b200_pack_validity(ctx._h, C.c_void_p(valid_bytes.data_ptr()), C.c_int64(n), C.c_void_p(bitmap.data_ptr()),
                                        C.byref(nulls)))
     return bitmap, int(nulls.value)
+
+
+def make_groupings(ctx: Context, ids: torch.Tensor, num_groups: int):
+    """== Grouper::MakeGroupings (hash_aggregate.cc:968-1001): ids = uint32 group ids as an int32-typed device
+    tensor.  Returns (offsets int32[num_groups + 1], indices int32[n]) — the buffers of a list<int32> array."""
+    n = ids.numel()
+    dev = "cuda:%d" % ctx.device
+    offsets = torch.empty(num_groups + 1, dtype=torch.int32, device=dev)
+    indices = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    nbytes = C.c_size_t(0)
+    ctx.check(lib().b200_make_groupings_scratch_bytes(C.c_int64(n), C.byref(nbytes)))
+    scratch = ctx.empty(nbytes.value)
+    ctx.check(lib().b200_make_groupings(ctx._h, C.c_void_p(ids.data_ptr()), C.c_int64(n), C.c_uint32(num_groups),
+                                        C.c_void_p(offsets.data_ptr()), C.c_void_p(indices.data_ptr()),
+                                        C.c_void_p(scratch.data_ptr()), C.c_size_t(scratch.numel())))
+    return offsets, indices[:n]
 
 
 def group_by(ctx: Context, keys: Sequence[Column], aggs: Sequence[AggSpec], args: Sequence[Column],

@@ -396,3 +396,41 @@ def GroupBy(arguments: Sequence[Column], keys: Sequence[Column], aggregates: Seq
         res_keys.append((h.values().copy(), h.valid()))
     Transfer.d2h = d2h
     return GroupByResult(out.num_groups, res_aggs, res_keys)
+
+
+# ---- other consumers of the Grouper -----------------------------------------------------------
+def MakeGroupings(ids, num_groups: int, ctx: Optional[capi.Context] = None):
+    """== Grouper::MakeGroupings (hash_aggregate.cc:968-1001): uint32 group ids (device tensor) -> the offsets and
+    values buffers of the list<int32> array whose slot g lists the rows holding id g."""
+    ctx = ctx or default_context()
+    return capi.make_groupings(ctx, ids, num_groups)
+
+
+def ApplyGroupings(groupings, array: Column, ctx: Optional[capi.Context] = None):
+    """== Grouper::ApplyGroupings (hash_aggregate.cc:1003-1018): Take(array, groupings.values) under the same offsets.
+    Returns (offsets, values Column)."""
+    ctx = ctx or default_context()
+    offsets, indices = groupings
+    from .columns import INT32
+    idx = Column(INT32, indices.view(torch.uint8), None, indices.numel(), 0, 0)
+    return offsets, capi.take(ctx, array, idx, True)
+
+
+def Unique(values: Column, ctx: Optional[capi.Context] = None) -> Column:
+    """== "unique" (compute/kernels/vector_hash.cc:723-782) for fixed-width columns: the distinct values in
+    first-occurrence order, a null (if any) as one null entry — the Grouper's GetUniques over the one column."""
+    ctx = ctx or default_context()
+    out = capi.group_by(ctx, [values], [], [])
+    return out.keys[0]
+
+
+def ValueCounts(values: Column, ctx: Optional[capi.Context] = None):
+    """== "value_counts" (vector_hash.cc): (distinct values in first-occurrence order, int64 counts); the null entry
+    counts the nulls (hash_count in both CountOptions modes over the column itself: one of the two is zero per group)."""
+    ctx = ctx or default_context()
+    from . import columns as cols
+    out = capi.group_by(ctx, [values], [AggSpec(cols.HASH_COUNT, 0), AggSpec(cols.HASH_COUNT, 1)], [values, values])
+    G = out.num_groups
+    a = out.aggs[0][0].data[: G * 8].view(torch.int64)
+    b = out.aggs[1][0].data[: G * 8].view(torch.int64)
+    return out.keys[0], a + b

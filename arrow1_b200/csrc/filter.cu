@@ -304,39 +304,29 @@ filter_apply_kernel(ApplyArgs a) {
 }
 
 
-// ---- Filter in ONE launch: count, global offset and compaction in the same kernel --------------------
-// filter_plan + filter_apply read the mask twice and hand the output length to the host in between
-// (GetFilterOutputSize -> PreallocateData -> Exec upstream, vector_selection.cc:786-835).  A caller that already owns
-// an output of `capacity` rows (a reused buffer, the last batch's size, or simply the mask length) needs neither: here
-// every 4096-row tile counts its emitted rows, learns its output offset from the tiles before it by decoupled look-back
-// (one 64-bit {status, rows} word per tile; tiles are handed out by an atomic ticket so that a tile's predecessors are
-// always running or done), and compacts.  The last tile leaves the output length in the header, where
-// b200_filter_plan_length_ptr finds it.  64-bit values are loaded two rows per lane (LDG.E.128), unconditionally:
-// at any selectivity above a few percent every 32-byte sector holds a selected row anyway.
-constexpr uint64_t kFsPartial = uint64_t(1) << 62, kFsInclusive = uint64_t(2) << 62, kFsValue = (uint64_t(1) << 62) - 1;
-
-struct FilterFusedArgs {
-  ApplyArgs a;
-  unsigned long long* state;   // [n_tiles], zeroed
-  uint32_t* ticket;            // zeroed
-  int64_t n_tiles;
-  int64_t* out_length;         // plan header
-};
-
-template <typename T, bool kBool, bool kHasValid, bool kVec>
+// ---- compaction with 128-bit value loads (64-bit values at a 16-byte aligned address) ------------------------------
+// filter_apply_kernel requests one 8-byte value per lane and only for selected rows; here every lane loads two
+// consecutive rows with one LDG.E.128, unconditionally: at any selectivity above a few percent every 32-byte sector
+// holds a selected row anyway, and the warp issues 8 load instructions per 512 rows instead of 16.
+// (Measured and dropped in round 2: the same kernel with the tile offsets taken by decoupled look-back instead of
+// from filter_plan_kernel's prefix arrays — one launch, but 0.41 ms per 100 M rows against 0.02 + 0.25 ms: with
+// ~1200 short tiles in flight a new tile walks dozens of look-back windows before it meets an inclusive state, and
+// the plan kernel only reads the 12.5 MB mask.  b200_filter_fused therefore runs plan + apply back to back.)
+template <bool kHasValid>
 __global__ void __launch_bounds__(kThreads)
-filter_fused_kernel(const __grid_constant__ FilterFusedArgs fa) {
-  const ApplyArgs& a = fa.a;
+filter_apply_vec_kernel(ApplyArgs a) {
+  using T = uint64_t;
   __shared__ uint32_t warp_totals[8];
-  __shared__ int64_t s_tile, s_base;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  if (t == 0) s_tile = atomicAdd(fa.ticket, 1u);
-  __syncthreads();
-  const int64_t tile = s_tile;
+  const int64_t tile = blockIdx.x;
+  if (*a.out_length > a.capacity) {   // never write past the caller's buffers (reported by b200_ctx_synchronize)
+    if (tile == 0 && t == 0) atomicExch(a.err, 2u);
+    return;
+  }
+  const int64_t out_base = a.super_prefix[tile / kTilesPerSuper] + a.tile_prefix[tile];
   const int64_t wrow0 = tile * int64_t(kTileRows) + int64_t(warp) * 512;
   const BitmapRef ones{nullptr, 0};
-
-  uint32_t e = 0, iv = 0, vvw = 0, dbw = 0;
+  uint32_t e = 0, iv = 0, vvw = 0;
   if (lane < 16) {
     int64_t r = wrow0 + lane * 32;
     if (r < a.length) {
@@ -346,33 +336,20 @@ filter_fused_kernel(const __grid_constant__ FilterFusedArgs fa) {
       iv = f & fv;
       e = a.null_sel ? ((f | ~fv) & in) : iv;
       if (kHasValid) vvw = bitmap_load32(a.vv, r, a.length);
-      if (kBool) dbw = bitmap_load32(a.vbits, r, a.length);
     }
   }
-  // the value loads do not depend on the offset: request them before the look-back
+  // lane l holds rows 64 j + 2 l and 64 j + 2 l + 1 of the warp's 512 rows
   const T* vals = reinterpret_cast<const T*>(a.vdata);
   T vreg[16];
-  if (!kBool) {
-    if (kVec) {
-      // 8 x 128-bit loads: lane l holds rows 64 j + 2 l and 64 j + 2 l + 1 of the warp's 512 rows
-      const int64_t last_full = a.length - 2;
+  const int64_t last_full = a.length - 2;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int64_t r = wrow0 + 64 * j + 2 * lane;
-        ulonglong2 v = make_ulonglong2(0, 0);
-        if (r <= last_full) v = __ldg(reinterpret_cast<const ulonglong2*>(vals + r));
-        else if (r < a.length) v.x = uint64_t(__ldg(vals + r));
-        vreg[2 * j] = T(v.x);
-        vreg[2 * j + 1] = T(v.y);
-      }
-    } else {
-#pragma unroll
-      for (int s = 0; s < 16; ++s) {
-        const uint32_t ivs = __shfl_sync(0xffffffffu, iv, s);
-        vreg[s] = T(0);
-        if ((ivs >> lane) & 1u) vreg[s] = __ldg(vals + wrow0 + s * 32 + lane);
-      }
-    }
+  for (int j = 0; j < 8; ++j) {
+    const int64_t r = wrow0 + 64 * j + 2 * lane;
+    ulonglong2 v = make_ulonglong2(0, 0);
+    if (r <= last_full) v = __ldg(reinterpret_cast<const ulonglong2*>(vals + r));
+    else if (r < a.length) v.x = __ldg(vals + r);
+    vreg[2 * j] = v.x;
+    vreg[2 * j + 1] = v.y;
   }
   const uint32_t cnt = __popc(e);
   const uint32_t incl = warp_inclusive_scan(cnt);
@@ -380,124 +357,45 @@ filter_fused_kernel(const __grid_constant__ FilterFusedArgs fa) {
   const uint32_t wtotal = __shfl_sync(0xffffffffu, incl, 31);
   if (lane == 0) warp_totals[warp] = wtotal;
   __syncthreads();
-  uint32_t wprefix = 0, ttotal = 0;
+  uint32_t wprefix = 0;
 #pragma unroll
-  for (int w = 0; w < 8; ++w) {
+  for (int w = 0; w < 8; ++w)
     if (w < warp) wprefix += warp_totals[w];
-    ttotal += warp_totals[w];
-  }
-  // ---- decoupled look-back by warp 0: lane j reads the state of tile - 1 - j
-  if (warp == 0) {
-    unsigned long long* st = fa.state + tile;
-    if (lane == 0) {
-      __threadfence();
-      atomicExch(st, (tile == 0 ? kFsInclusive : kFsPartial) | uint64_t(ttotal));
-    }
-    int64_t excl = 0;
-    int64_t back = tile - 1;
-    uint32_t spins = 0;
-    while (back >= 0) {
-      const int64_t idx = back - lane;
-      unsigned long long v = idx >= 0 ? *reinterpret_cast<volatile unsigned long long*>(fa.state + idx) : kFsInclusive;
-      const unsigned ready = __ballot_sync(0xffffffffu, (v >> 62) != 0);
-      const unsigned incl_m = __ballot_sync(0xffffffffu, (v >> 62) == 2);
-      // usable run: lanes 0 .. k-1 all published; stop at the first inclusive one
-      const int n_ready = __ffs(~ready) - 1 < 0 ? 32 : __ffs(~ready) - 1;
-      const int first_incl = incl_m ? __ffs(incl_m) - 1 : 32;
-      const int take = min(n_ready, first_incl + 1);
-      int64_t part = lane < take ? int64_t(v & kFsValue) : 0;
-#pragma unroll
-      for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
-      excl += part;
-      if (first_incl < take) break;
-      back -= take;
-      if (take == 0) {
-        if (++spins > (1u << 22)) {   // never hang the GPU: flag and bail out (reported by b200_ctx_synchronize)
-          if (lane == 0) atomicExch(a.err, 1u);
-          break;
-        }
-        __nanosleep(40);
-      }
-    }
-    if (lane == 0) {
-      if (tile > 0) {
-        __threadfence();
-        atomicExch(st, kFsInclusive | uint64_t(excl + ttotal));
-      }
-      s_base = excl;
-      if (tile == fa.n_tiles - 1) *fa.out_length = excl + ttotal;
-    }
-  }
-  __syncthreads();
-  const int64_t out_base = s_base;
-  if (out_base + ttotal > a.capacity) {   // never write past the caller's buffers
-    if (t == 0) atomicExch(a.err, 2u);
-    return;
-  }
   if (wtotal == 0) return;  // warp-uniform: nothing emitted by this warp
-
   const int64_t wout = out_base + wprefix;
-  BitAppender valid_app, data_app;
-  if (kHasValid) valid_app.init(a.out_valid, wout);
-  if (kBool) data_app.init(reinterpret_cast<uint32_t*>(a.out_data), wout);
   T* out = reinterpret_cast<T*>(a.out_data);
-  const unsigned lt = lanemask_lt();
-  if (!kBool && kVec) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const uint32_t e0 = __shfl_sync(0xffffffffu, e, 2 * j), e1 = __shfl_sync(0xffffffffu, e, 2 * j + 1);
-      const uint32_t i0 = __shfl_sync(0xffffffffu, iv, 2 * j), i1 = __shfl_sync(0xffffffffu, iv, 2 * j + 1);
-      const uint32_t ps = __shfl_sync(0xffffffffu, step_prefix, 2 * j);
-      const uint64_t e64 = (uint64_t(e1) << 32) | e0, i64 = (uint64_t(i1) << 32) | i0;
-      if (e64 == 0) continue;   // warp-uniform
-      const int b = 2 * lane;
-      const uint32_t rank = __popcll(e64 & ((uint64_t(1) << b) - 1));
-      const bool em0 = (e64 >> b) & 1u, em1 = (e64 >> (b + 1)) & 1u;
-      // an emitted filter-null writes zero (vector_selection.cc:743-746)
-      if (em0) out[wout + ps + rank] = ((i64 >> b) & 1u) ? vreg[2 * j] : T(0);
-      if (em1) out[wout + ps + rank + (em0 ? 1 : 0)] = ((i64 >> (b + 1)) & 1u) ? vreg[2 * j + 1] : T(0);
-    }
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t e0 = __shfl_sync(0xffffffffu, e, 2 * j), e1 = __shfl_sync(0xffffffffu, e, 2 * j + 1);
+    const uint32_t i0 = __shfl_sync(0xffffffffu, iv, 2 * j), i1 = __shfl_sync(0xffffffffu, iv, 2 * j + 1);
+    const uint32_t ps = __shfl_sync(0xffffffffu, step_prefix, 2 * j);
+    const uint64_t e64 = (uint64_t(e1) << 32) | e0, i64 = (uint64_t(i1) << 32) | i0;
+    if (e64 == 0) continue;   // warp-uniform
+    const int b = 2 * lane;
+    const uint32_t rank = __popcll(e64 & ((uint64_t(1) << b) - 1));
+    const bool em0 = (e64 >> b) & 1u, em1 = (e64 >> (b + 1)) & 1u;
+    // an emitted filter-null writes zero (vector_selection.cc:743-746)
+    if (em0) out[wout + ps + rank] = ((i64 >> b) & 1u) ? vreg[2 * j] : T(0);
+    if (em1) out[wout + ps + rank + (em0 ? 1 : 0)] = ((i64 >> (b + 1)) & 1u) ? vreg[2 * j + 1] : T(0);
   }
+  if (kHasValid) {
+    BitAppender valid_app;
+    valid_app.init(a.out_valid, wout);
+    const unsigned lt = lanemask_lt();
 #pragma unroll
-  for (int s = 0; s < 16; ++s) {
-    if (!kBool && kVec && !kHasValid) break;
-    const uint32_t es = __shfl_sync(0xffffffffu, e, s);
-    if (es == 0) continue;  // warp-uniform
-    const uint32_t ivs = __shfl_sync(0xffffffffu, iv, s);
-    const uint32_t ps = __shfl_sync(0xffffffffu, step_prefix, s);
-    const bool emit = (es >> lane) & 1u;
-    const bool isv = (ivs >> lane) & 1u;
-    const uint32_t rank = __popc(es & lt);
-    if (!kBool) {
-      if (!kVec && emit) out[wout + ps + rank] = vreg[s];
-    } else {
-      const uint32_t ds = __shfl_sync(0xffffffffu, dbw, s);
-      const uint32_t bit = (isv && ((ds >> lane) & 1u)) ? (1u << rank) : 0u;
-      const uint32_t cw = __reduce_or_sync(0xffffffffu, bit);
-      data_app.append(cw, __popc(es), lane);
-    }
-    if (kHasValid) {
+    for (int s = 0; s < 16; ++s) {
+      const uint32_t es = __shfl_sync(0xffffffffu, e, s);
+      if (es == 0) continue;  // warp-uniform
+      const uint32_t ivs = __shfl_sync(0xffffffffu, iv, s);
+      const bool isv = (ivs >> lane) & 1u;
+      const uint32_t rank = __popc(es & lt);
       const uint32_t vs = __shfl_sync(0xffffffffu, vvw, s);
       const uint32_t bit = (isv && ((vs >> lane) & 1u)) ? (1u << rank) : 0u;
       const uint32_t cw = __reduce_or_sync(0xffffffffu, bit);
       valid_app.append(cw, __popc(es), lane);
     }
+    valid_app.finish(lane);
   }
-  if (kHasValid) valid_app.finish(lane);
-  if (kBool) data_app.finish(lane);
-}
-
-template <typename T, bool kBool>
-int launch_fused(b200_ctx* ctx, const FilterFusedArgs& fa, bool vec) {
-  dim3 grid((unsigned)fa.n_tiles), block(kThreads);
-  if (fa.a.out_valid) {
-    if (vec) B200_TIMED(ctx, "filter_fused", (filter_fused_kernel<T, kBool, true, !kBool && sizeof(T) == 8><<<grid, block, 0, ctx->stream>>>(fa)));
-    else B200_TIMED(ctx, "filter_fused", (filter_fused_kernel<T, kBool, true, false><<<grid, block, 0, ctx->stream>>>(fa)));
-  } else {
-    if (vec) B200_TIMED(ctx, "filter_fused", (filter_fused_kernel<T, kBool, false, !kBool && sizeof(T) == 8><<<grid, block, 0, ctx->stream>>>(fa)));
-    else B200_TIMED(ctx, "filter_fused", (filter_fused_kernel<T, kBool, false, false><<<grid, block, 0, ctx->stream>>>(fa)));
-  }
-  return B200_OK;
 }
 
 int check_mask(b200_ctx* ctx, const b200_col* mask) {
@@ -513,6 +411,11 @@ int check_mask(b200_ctx* ctx, const b200_col* mask) {
 template <typename T, bool kBool>
 int launch_apply(b200_ctx* ctx, const ApplyArgs& a, int64_t n_tiles) {
   dim3 grid((unsigned)n_tiles), block(kThreads);
+  if (!kBool && sizeof(T) == 8 && (reinterpret_cast<uintptr_t>(a.vdata) & 15) == 0) {
+    if (a.out_valid) B200_TIMED(ctx, "filter_apply", (filter_apply_vec_kernel<true><<<grid, block, 0, ctx->stream>>>(a)));
+    else B200_TIMED(ctx, "filter_apply", (filter_apply_vec_kernel<false><<<grid, block, 0, ctx->stream>>>(a)));
+    return B200_OK;
+  }
   if (a.out_valid)
     B200_TIMED(ctx, "filter_apply", (filter_apply_kernel<T, kBool, true><<<grid, block, 0, ctx->stream>>>(a)));
   else
@@ -1016,65 +919,19 @@ int b200_filter_count(b200_ctx* ctx, const b200_col* mask, int null_selection, i
   return b200_filter_plan(ctx, mask, null_selection, ctx->scratch, out_len);
 }
 
-int b200_filter_fused_scratch_bytes(int64_t mask_length, size_t* out_bytes) {
-  if (!out_bytes || mask_length < 0) return B200_INVALID;
-  *out_bytes = 128 + size_t(n_tiles_for(mask_length)) * 8 + 64;
-  return B200_OK;
-}
+int b200_filter_fused_scratch_bytes(int64_t mask_length, size_t* out_bytes) { return b200_filter_plan_bytes(mask_length, out_bytes); }
 
 int b200_filter_fused(b200_ctx* ctx, const b200_col* values, const b200_col* mask, int null_selection, void* scratch,
                       void* out_data, void* out_validity, int64_t out_capacity, int64_t* out_len) {
-  B200_ENTER(ctx);
-  if (!ctx) return B200_INVALID;
-  B200_RETURN_NOT_OK(check_mask(ctx, mask));
-  if (!values || !scratch) return b200_fail(ctx, B200_INVALID, "filter_fused: null argument");
-  if (values->length != mask->length) return b200_fail(ctx, B200_INVALID, "Array arguments must all be the same length");
-  const int bits = b200_type_bits(values->type);
-  if (bits == 0) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "filter: unsupported values type %d", values->type);
-  if (out_capacity < 0) return b200_fail(ctx, B200_INVALID, "filter_fused: negative out_capacity");
-  if ((reinterpret_cast<uintptr_t>(scratch) & 63) != 0) return b200_fail(ctx, B200_INVALID, "filter_fused: scratch must be 64-byte aligned");
-  const int64_t length = mask->length;
-  if (out_len) *out_len = 0;
-  char* base = reinterpret_cast<char*>(scratch);
-  const int64_t nt = n_tiles_for(length);
-  B200_CUDA(ctx, cudaMemsetAsync(base, 0, 128 + size_t(nt) * 8, ctx->stream));
-  if (length == 0) return B200_OK;
-  if (!out_data && out_capacity > 0) return b200_fail(ctx, B200_INVALID, "filter_fused: null out_data");
-  if ((reinterpret_cast<uintptr_t>(out_data) & 7) || (reinterpret_cast<uintptr_t>(out_validity) & 7))
-    return b200_fail(ctx, B200_INVALID, "filter_fused: output buffers must be 8-byte aligned");
-  FilterFusedArgs fa;
-  memset(&fa, 0, sizeof(fa));
-  ApplyArgs& a = fa.a;
-  a.f = make_bitmap_ref(mask->data, mask->offset);
-  a.fv = make_bitmap_ref(mask->validity, mask->offset);
-  a.vv = make_bitmap_ref(values->validity, values->offset);
-  a.vbits = make_bitmap_ref(values->data, values->offset);
-  a.vdata = bits >= 8 ? reinterpret_cast<const char*>(values->data) + values->offset * (bits / 8) : nullptr;
-  a.length = length;
-  a.null_sel = null_selection;
-  a.out_data = out_data;
-  a.out_valid = reinterpret_cast<uint32_t*>(out_validity);
-  a.capacity = out_capacity;
-  a.err = ctx->async_err;
-  fa.out_length = reinterpret_cast<int64_t*>(base);
-  fa.ticket = reinterpret_cast<uint32_t*>(base + 64);
-  fa.state = reinterpret_cast<unsigned long long*>(base + 128);
-  fa.n_tiles = nt;
-  const size_t bitmap_bytes = b200_align_up(size_t((out_capacity + 7) / 8), 4);
-  if (out_validity) B200_CUDA(ctx, cudaMemsetAsync(out_validity, 0, bitmap_bytes, ctx->stream));
-  if (bits == 1 && out_data) B200_CUDA(ctx, cudaMemsetAsync(out_data, 0, bitmap_bytes, ctx->stream));
-  const bool vec = bits == 64 && (reinterpret_cast<uintptr_t>(a.vdata) & 15) == 0;
-  int st = B200_OK;
-  switch (bits) {
-    case 1: st = launch_fused<uint8_t, true>(ctx, fa, false); break;
-    case 8: st = launch_fused<uint8_t, false>(ctx, fa, false); break;
-    case 16: st = launch_fused<uint16_t, false>(ctx, fa, false); break;
-    case 32: st = launch_fused<uint32_t, false>(ctx, fa, false); break;
-    default: st = launch_fused<uint64_t, false>(ctx, fa, vec); break;
-  }
-  B200_RETURN_NOT_OK(st);
+  // the plan (a scan of the mask alone: 1/64 of the value bytes) and the compaction, back to back on the stream;
+  // the output length only travels to the host when the caller asks for it
+  B200_RETURN_NOT_OK(b200_filter_plan(ctx, mask, null_selection, scratch, nullptr));
+  B200_RETURN_NOT_OK(b200_filter_apply(ctx, values, mask, null_selection, scratch, out_data, out_validity, out_capacity));
   if (out_len) {
-    B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words, fa.out_length, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    B200_ENTER(ctx);
+    *out_len = 0;
+    if (mask->length == 0) return B200_OK;
+    B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words, b200_filter_plan_length_ptr(scratch), sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
     B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     *out_len = ctx->host_words[0];
   }

@@ -3653,6 +3653,78 @@ int b200_groupby_consume_fused(b200_groupby* gb, const b200_col* keys, const b20
   return st;
 }
 
+
+// ---- Grouper::MakeGroupings (hash_aggregate.cc:968-1001): group ids -> per group the list of its rows ----------------
+// The reference counts the ids, scans, and places row i at offsets[id[i]]++ (a stable counting sort).  Here: the ids
+// are ranked by the stable radix sort (only the digits below num_groups are live), which IS the list values, and the
+// offsets fall out of the sorted order — position i starts every group in (id of i-1, id of i].
+namespace {
+__global__ void mg_keys_kernel(const uint32_t* ids, int64_t n, uint32_t num_groups, uint64_t* keys, uint32_t* err) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t g = ids[i];
+  if (g >= num_groups) atomicExch(err, 1u);
+  keys[i] = g;
+}
+__global__ void mg_emit_kernel(const uint32_t* ids, const uint64_t* perm, int64_t n, uint32_t num_groups, int32_t* offsets,
+                               int32_t* indices) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i > n) return;
+  // position n closes the groups behind the last id
+  const int64_t cur = i < n ? min(int64_t(ids[perm[i]]), int64_t(num_groups)) : int64_t(num_groups);   // (bad ids: reported, not written)
+  const int64_t prev = i > 0 ? min(int64_t(ids[perm[i - 1]]), int64_t(num_groups)) : -1;
+  for (int64_t g = prev + 1; g <= cur; ++g) offsets[g] = int32_t(i);
+  if (i < n) indices[i] = int32_t(perm[i]);
+}
+}  // namespace
+
+int b200_make_groupings_scratch_bytes(int64_t length, size_t* out_bytes) {
+  if (!out_bytes || length < 0) return B200_INVALID;
+  size_t sort_bytes = 0;
+  b200_sort_pairs_scratch_bytes(length, &sort_bytes);
+  *out_bytes = 2 * b200_align_up(size_t(length) * 8, 256) + sort_bytes + 1024;
+  return B200_OK;
+}
+
+int b200_make_groupings(b200_ctx* ctx, const uint32_t* ids, int64_t length, uint32_t num_groups, int32_t* out_offsets,
+                        int32_t* out_indices, void* scratch, size_t scratch_bytes) {
+  B200_ENTER(ctx);
+  if (!ctx) return B200_INVALID;
+  if (length < 0) return b200_fail(ctx, B200_INVALID, "make_groupings: negative length");
+  if (!out_offsets) return b200_fail(ctx, B200_INVALID, "make_groupings: null offsets");
+  // offsets and indices are int32 (list<int32>), like the reference's
+  if (length > 0x7FFFFFFF) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "make_groupings: more than 2^31-1 rows");
+  if (length == 0) {
+    B200_CUDA(ctx, cudaMemsetAsync(out_offsets, 0, (size_t(num_groups) + 1) * 4, ctx->stream));
+    return B200_OK;
+  }
+  size_t need = 0;
+  b200_make_groupings_scratch_bytes(length, &need);
+  if (!ids || !out_indices || !scratch || scratch_bytes < need) return b200_fail(ctx, B200_INVALID, "make_groupings: null argument or scratch too small");
+  char* base = reinterpret_cast<char*>(b200_align_up(reinterpret_cast<uintptr_t>(scratch), 256));
+  const size_t arr = b200_align_up(size_t(length) * 8, 256);
+  uint64_t* keys = reinterpret_cast<uint64_t*>(base);
+  uint64_t* perm = reinterpret_cast<uint64_t*>(base + arr);
+  void* sort_scratch = base + 2 * arr;
+  const size_t sort_bytes = scratch_bytes - size_t(base - reinterpret_cast<char*>(scratch)) - 2 * arr;
+  const unsigned grid = unsigned((length + 255) / 256);
+  mg_keys_kernel<<<grid, 256, 0, ctx->stream>>>(ids, length, num_groups, keys, ctx->async_err + 1);
+  B200_LAUNCHED(ctx);
+  int bits = 1;
+  while (bits < 32 && (uint64_t(1) << bits) < uint64_t(num_groups)) ++bits;
+  B200_RETURN_NOT_OK(b200_sort_pairs_bits(ctx, keys, nullptr, length, bits, perm, sort_scratch, sort_bytes));
+  mg_emit_kernel<<<unsigned((length + 256) / 256), 256, 0, ctx->stream>>>(ids, perm, length, num_groups, out_offsets, out_indices);
+  B200_LAUNCHED(ctx);
+  // an id >= num_groups is a caller error (DCHECK upstream): reported, not written out of bounds
+  B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 62, ctx->async_err + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (*reinterpret_cast<const uint32_t*>(ctx->host_words + 62) != 0) {
+    B200_CUDA(ctx, cudaMemsetAsync(ctx->async_err + 1, 0, sizeof(uint32_t), ctx->stream));
+    return b200_fail(ctx, B200_INDEX_ERROR, "make_groupings: group id >= num_groups (%u)", num_groups);
+  }
+  return B200_OK;
+}
+
 // ---- hash repartitioning -------------------------------------------------------------------------
 int b200_partition_scratch_bytes(int64_t length, size_t* out_bytes) {
   if (!out_bytes || length < 0) return B200_INVALID;

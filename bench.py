@@ -269,16 +269,14 @@ class FilterWL(Workload):
         sel = (self.out_len or self.n // 2)
         return self.n * (8 + 1 / 8 + 1 / 8) + sel * (8 + 1 / 8)
 
-    kernel = "filter_fused"
-
     def prepare(self, ctx, cols_):
         from arrow1_b200 import capi
         return {"data": ctx.empty(self.n * 8), "validity": ctx.empty((self.n + 7) // 8 + 8),
                 "scratch": capi.FusedFilterScratch(ctx, self.n)}
 
     def step(self, ctx, cols_, bufs):
-        # one launch into reused buffers sized by the mask length; the output length stays on the device
-        # (b200_filter_fused; the plan + apply form with the host round trip is what compute.Filter / e2e use)
+        # reused buffers sized by the mask length; plan + apply back to back, the output length stays on the device
+        # (b200_filter_fused; the form with the host round trip between them is what compute.Filter / e2e use)
         from arrow1_b200 import capi
         out = capi.filter_fused(ctx, cols_[0], cols_[1], 0, bufs["data"], bufs["validity"], self.n, bufs["scratch"], sync=False)
         return out

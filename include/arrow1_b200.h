@@ -147,14 +147,13 @@ B200_API int b200_filter_apply(b200_ctx* ctx, const b200_col* values, const b200
                                void* out_validity /* nullable */, int64_t out_capacity);
 B200_API int b200_filter_out_spec(const b200_col* values, const b200_col* mask, int null_selection,
                                   int* allocate_validity, int64_t* out_null_count);
-/* Filter in ONE launch for callers that already own an output of `out_capacity` rows (a reused buffer sized by the
- * mask length or by the previous batch): count, output offsets (decoupled look-back over 4096-row tiles) and
- * compaction in the same kernel, no host round trip.  == GetFilterOutputSize + PrimitiveFilterImpl::Exec
- * (vector_selection.cc:61-88, 570-764) without PreallocateData in between.  `scratch`: DEVICE, 64-byte aligned,
- * b200_filter_fused_scratch_bytes(mask length) bytes; its first 8 bytes receive the int64 output length (readable
- * through b200_filter_plan_length_ptr).  out_len: HOST, nullable; when given the call synchronises and returns the
- * length.  If the selection emits more than out_capacity rows nothing past the capacity is written and the context
- * reports it at the next b200_ctx_synchronize. */
+/* Filter without a host round trip, for callers that already own an output of `out_capacity` rows (a reused buffer
+ * sized by the mask length or by the previous batch): b200_filter_plan and b200_filter_apply back to back on the
+ * stream.  == GetFilterOutputSize + PrimitiveFilterImpl::Exec (vector_selection.cc:61-88, 570-764) without
+ * PreallocateData in between.  `scratch`: DEVICE, b200_filter_fused_scratch_bytes(mask length) bytes (a plan); its
+ * first 8 bytes receive the int64 output length (b200_filter_plan_length_ptr).  out_len: HOST, nullable; when given
+ * the call synchronises and returns the length.  If the selection emits more than out_capacity rows nothing is
+ * written and the context reports it at the next b200_ctx_synchronize. */
 B200_API int b200_filter_fused_scratch_bytes(int64_t mask_length, size_t* out_bytes);
 B200_API int b200_filter_fused(b200_ctx* ctx, const b200_col* values, const b200_col* mask, int null_selection,
                                void* scratch, void* out_data, void* out_validity /* nullable */,
@@ -404,6 +403,15 @@ B200_API int b200_groupby_first_rows(b200_groupby* gb, uint64_t* out_first_rows)
 /* == Grouper::Consume proper (hash_aggregate.cc:358-408): writes the uint32 group id of every
  * row, ids handed out in first-occurrence order across calls. */
 B200_API int b200_grouper_consume(b200_groupby* gb, const b200_col* keys, uint32_t* out_ids);
+/* == Grouper::MakeGroupings (hash_aggregate.cc:968-1001; api_aggregate.h:333-359): for every group id in
+ * [0, num_groups) the ascending list of rows holding it, as the two buffers of a list<int32> array:
+ * out_offsets int32[num_groups + 1], out_indices int32[length] (both DEVICE).  Used upstream by dataset partitioning
+ * (dataset/partition.cc:115-122).  Grouper::ApplyGroupings (hash_aggregate.cc:1003-1018) is then
+ * b200_take(array, out_indices) under the same offsets.  An id >= num_groups fails with B200_INDEX_ERROR.
+ * Synchronises. */
+B200_API int b200_make_groupings_scratch_bytes(int64_t length, size_t* out_bytes);
+B200_API int b200_make_groupings(b200_ctx* ctx, const uint32_t* ids, int64_t length, uint32_t num_groups,
+                                 int32_t* out_offsets, int32_t* out_indices, void* scratch, size_t scratch_bytes);
 /* == HashAggregateKernel::consume with the reference signature (arg, uint32 ids, num_groups)
  * (hash_aggregate.cc:783-789): accumulates aggregate `agg_index` of `gb` by dense group id. */
 B200_API int b200_hash_agg_consume(b200_groupby* gb, int agg_index, const b200_col* arg,

@@ -265,3 +265,26 @@ def groupby_sum_chunked(key_chunks: Sequence[Sequence[Column]], arg_chunks: Sequ
     G = num_groups.value
     assert G <= max_groups
     return G, [_decode(t, d, v, G) for (t, d, v) in holders], [_decode(t, d, v, G) for (t, d, v) in key_holders]
+
+
+def make_groupings(ids: np.ndarray, num_groups: int):
+    """Grouper::MakeGroupings of the reference (kind="reference" only): (offsets int32[num_groups + 1], indices int32[n])."""
+    ids = np.ascontiguousarray(ids, dtype=np.uint32)
+    offsets = np.zeros(num_groups + 1, dtype=np.int32)
+    indices = np.zeros(max(len(ids), 1), dtype=np.int32)
+    _check("reference", _fn("reference", "make_groupings")(ids.ctypes.data_as(C.c_void_p), C.c_int64(len(ids)), C.c_uint32(num_groups),
+                                                             offsets.ctypes.data_as(C.c_void_p), indices.ctypes.data_as(C.c_void_p)))
+    return offsets, indices[: len(ids)]
+
+
+def value_counts(values: Column, want_counts: bool = True):
+    """"unique" / "value_counts" of the reference (vector_hash.cc): ((values, valid), counts or None) in
+    first-occurrence order."""
+    n = values.length
+    oc, d, v = _out_col(values.type, max(n, 1))
+    counts = np.zeros(max(n, 1), dtype=np.int64)
+    out_n = C.c_int64(0)
+    _check("reference", _fn("reference", "value_counts")(C.byref(values.desc()), C.byref(oc),
+                                                           counts.ctypes.data_as(C.c_void_p) if want_counts else None, C.byref(out_n)))
+    g = out_n.value
+    return _decode(values.type, d, v, g), (counts[:g].copy() if want_counts else None)

@@ -349,4 +349,39 @@ B200_API int ref_groupby_sum_chunked(int n_keys, int n_chunks, const b200_col* k
   return 0;
 }
 
+// Grouper::MakeGroupings (hash_aggregate.cc:968-1001): list<int32> offsets and values
+B200_API int ref_make_groupings(const uint32_t* ids, int64_t n, uint32_t num_groups, int32_t* out_offsets, int32_t* out_indices) {
+  compute::ExecContext ctx;
+  auto buf = std::make_shared<Buffer>(reinterpret_cast<const uint8_t*>(ids), n * 4);
+  UInt32Array arr(n, buf);
+  auto res = compute::internal::Grouper::MakeGroupings(arr, num_groups, &ctx);
+  if (!res.ok()) return Fail(res.status());
+  auto list = res.ValueOrDie();
+  std::memcpy(out_offsets, list->raw_value_offsets(), (size_t(num_groups) + 1) * 4);
+  auto values = std::static_pointer_cast<Int32Array>(list->values());
+  if (n > 0) std::memcpy(out_indices, values->raw_values(), size_t(n) * 4);
+  return 0;
+}
+
+// "unique" / "value_counts" (compute/kernels/vector_hash.cc:723-782) on one fixed-width column.
+// out_values: the distinct values in first-occurrence order (a null, if any, is one entry); out_counts nullable.
+B200_API int ref_value_counts(const b200_col* values, b200_out_col* out_values, int64_t* out_counts, int64_t* out_n) {
+  compute::ExecContext ctx;
+  if (out_counts) {
+    auto res = compute::CallFunction("value_counts", {Datum(Wrap(*values))}, &ctx);
+    if (!res.ok()) return Fail(res.status());
+    auto st = res.ValueOrDie().array();
+    CopyOut(*st->child_data[0], out_values);
+    std::memcpy(out_counts, st->child_data[1]->GetValues<int64_t>(1), size_t(st->length) * 8);
+    *out_n = st->length;
+    return 0;
+  }
+  auto res = compute::CallFunction("unique", {Datum(Wrap(*values))}, &ctx);
+  if (!res.ok()) return Fail(res.status());
+  auto arr = res.ValueOrDie().array();
+  CopyOut(*arr, out_values);
+  *out_n = arr->length;
+  return 0;
+}
+
 }  // extern "C"

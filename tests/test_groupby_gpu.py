@@ -497,3 +497,51 @@ def test_groupby_wide_keys_streaming_and_selection(ctx):
     a = GroupRes(got.num_groups, [[(c.to_host().values().copy(), c.to_host().valid()) for c in ag] for ag in got.aggs],
                  [(c.to_host().values().copy(), c.to_host().valid()) for c in got.keys])
     assert_group_equal(a, want_sel, aggs, rtol=RTOL)
+
+
+# ---- other consumers of the Grouper: MakeGroupings / ApplyGroupings, unique, value_counts
+def test_make_and_apply_groupings_match_reference(ctx):
+    from arrow1_b200 import capi, compute
+    if ORACLE != "reference":
+        pytest.skip("needs oracle/_ref")
+    # the documented example of api_aggregate.h:340-383
+    ids = np.array([2, 2, 5, 5, 2, 3], dtype=np.uint32)
+    off, idx = compute.MakeGroupings(torch.from_numpy(ids.view(np.int32)).cuda(), 8, ctx)
+    assert off.cpu().tolist() == [0, 0, 0, 3, 4, 4, 6, 6, 6] and idx.cpu().tolist() == [0, 1, 4, 5, 2, 3]
+    rng = np.random.default_rng(8)
+    for n, g in ((0, 3), (1, 1), (1000, 7), (300_000, 5000), (300_000, 3)):
+        ids = rng.integers(0, max(g - 1, 1), size=n).astype(np.uint32)   # the last group stays empty
+        want_off, want_idx = oracle.make_groupings(ids, g)
+        dids = torch.from_numpy(ids.view(np.int32)).cuda()
+        off, idx = compute.MakeGroupings(dids, g, ctx)
+        np.testing.assert_array_equal(off.cpu().numpy(), want_off)
+        np.testing.assert_array_equal(idx.cpu().numpy(), want_idx)
+        if n:
+            vals = Column.from_numpy(rng.random(n), rng.random(n) > 0.1)
+            _, taken = compute.ApplyGroupings((off, idx), vals.to_device(), ctx)
+            h = taken.to_host()
+            np.testing.assert_array_equal(h.valid(), vals.valid()[want_idx])
+            np.testing.assert_array_equal(h.values()[h.valid()], vals.values()[want_idx][h.valid()])
+    with pytest.raises(capi.B200Error) as e:
+        compute.MakeGroupings(torch.tensor([0, 9, 1], dtype=torch.int32).cuda(), 4, ctx)
+    assert e.value.code == 7
+
+
+@pytest.mark.parametrize("t", [cols.BOOL, cols.INT8, cols.UINT16, cols.INT32, cols.INT64, cols.FLOAT, cols.DOUBLE])
+def test_unique_and_value_counts_match_reference(ctx, t):
+    from arrow1_b200 import compute
+    if ORACLE != "reference":
+        pytest.skip("needs oracle/_ref")
+    rng = np.random.default_rng(60 + t)
+    for n, nulls in ((1, 0.0), (5000, 0.0), (200_000, 0.1)):
+        col = rand_column(rng, t, n, nulls, lo=0, hi=(1 if t == cols.BOOL else 90))
+        (wv, wvalid), wc = oracle.value_counts(col, True)
+        uv, _ = oracle.value_counts(col, False)
+        got_u = compute.Unique(col.to_device(), ctx).to_host()
+        np.testing.assert_array_equal(got_u.valid(), uv[1])
+        np.testing.assert_array_equal(got_u.values()[uv[1]].view(np.uint8), uv[0][uv[1]].view(np.uint8))
+        keys, counts = compute.ValueCounts(col.to_device(), ctx)
+        hk = keys.to_host()
+        np.testing.assert_array_equal(hk.valid(), wvalid)
+        np.testing.assert_array_equal(hk.values()[wvalid].view(np.uint8), wv[wvalid].view(np.uint8))
+        np.testing.assert_array_equal(counts.cpu().numpy(), wc)
