@@ -304,99 +304,13 @@ filter_apply_kernel(ApplyArgs a) {
 }
 
 
-// ---- compaction with 128-bit value loads (64-bit values at a 16-byte aligned address) ------------------------------
-// filter_apply_kernel requests one 8-byte value per lane and only for selected rows; here every lane loads two
-// consecutive rows with one LDG.E.128, unconditionally: at any selectivity above a few percent every 32-byte sector
-// holds a selected row anyway, and the warp issues 8 load instructions per 512 rows instead of 16.
-// (Measured and dropped in round 2: the same kernel with the tile offsets taken by decoupled look-back instead of
-// from filter_plan_kernel's prefix arrays — one launch, but 0.41 ms per 100 M rows against 0.02 + 0.25 ms: with
-// ~1200 short tiles in flight a new tile walks dozens of look-back windows before it meets an inclusive state, and
-// the plan kernel only reads the 12.5 MB mask.  b200_filter_fused therefore runs plan + apply back to back.)
-template <bool kHasValid>
-__global__ void __launch_bounds__(kThreads)
-filter_apply_vec_kernel(ApplyArgs a) {
-  using T = uint64_t;
-  __shared__ uint32_t warp_totals[8];
-  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const int64_t tile = blockIdx.x;
-  if (*a.out_length > a.capacity) {   // never write past the caller's buffers (reported by b200_ctx_synchronize)
-    if (tile == 0 && t == 0) atomicExch(a.err, 2u);
-    return;
-  }
-  const int64_t out_base = a.super_prefix[tile / kTilesPerSuper] + a.tile_prefix[tile];
-  const int64_t wrow0 = tile * int64_t(kTileRows) + int64_t(warp) * 512;
-  const BitmapRef ones{nullptr, 0};
-  uint32_t e = 0, iv = 0, vvw = 0;
-  if (lane < 16) {
-    int64_t r = wrow0 + lane * 32;
-    if (r < a.length) {
-      uint32_t f = bitmap_load32(a.f, r, a.length);
-      uint32_t fv = bitmap_load32(a.fv, r, a.length);
-      uint32_t in = bitmap_load32(ones, r, a.length);
-      iv = f & fv;
-      e = a.null_sel ? ((f | ~fv) & in) : iv;
-      if (kHasValid) vvw = bitmap_load32(a.vv, r, a.length);
-    }
-  }
-  // lane l holds rows 64 j + 2 l and 64 j + 2 l + 1 of the warp's 512 rows
-  const T* vals = reinterpret_cast<const T*>(a.vdata);
-  T vreg[16];
-  const int64_t last_full = a.length - 2;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int64_t r = wrow0 + 64 * j + 2 * lane;
-    ulonglong2 v = make_ulonglong2(0, 0);
-    if (r <= last_full) v = __ldg(reinterpret_cast<const ulonglong2*>(vals + r));
-    else if (r < a.length) v.x = __ldg(vals + r);
-    vreg[2 * j] = v.x;
-    vreg[2 * j + 1] = v.y;
-  }
-  const uint32_t cnt = __popc(e);
-  const uint32_t incl = warp_inclusive_scan(cnt);
-  const uint32_t step_prefix = incl - cnt;
-  const uint32_t wtotal = __shfl_sync(0xffffffffu, incl, 31);
-  if (lane == 0) warp_totals[warp] = wtotal;
-  __syncthreads();
-  uint32_t wprefix = 0;
-#pragma unroll
-  for (int w = 0; w < 8; ++w)
-    if (w < warp) wprefix += warp_totals[w];
-  if (wtotal == 0) return;  // warp-uniform: nothing emitted by this warp
-  const int64_t wout = out_base + wprefix;
-  T* out = reinterpret_cast<T*>(a.out_data);
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const uint32_t e0 = __shfl_sync(0xffffffffu, e, 2 * j), e1 = __shfl_sync(0xffffffffu, e, 2 * j + 1);
-    const uint32_t i0 = __shfl_sync(0xffffffffu, iv, 2 * j), i1 = __shfl_sync(0xffffffffu, iv, 2 * j + 1);
-    const uint32_t ps = __shfl_sync(0xffffffffu, step_prefix, 2 * j);
-    const uint64_t e64 = (uint64_t(e1) << 32) | e0, i64 = (uint64_t(i1) << 32) | i0;
-    if (e64 == 0) continue;   // warp-uniform
-    const int b = 2 * lane;
-    const uint32_t rank = __popcll(e64 & ((uint64_t(1) << b) - 1));
-    const bool em0 = (e64 >> b) & 1u, em1 = (e64 >> (b + 1)) & 1u;
-    // an emitted filter-null writes zero (vector_selection.cc:743-746)
-    if (em0) out[wout + ps + rank] = ((i64 >> b) & 1u) ? vreg[2 * j] : T(0);
-    if (em1) out[wout + ps + rank + (em0 ? 1 : 0)] = ((i64 >> (b + 1)) & 1u) ? vreg[2 * j + 1] : T(0);
-  }
-  if (kHasValid) {
-    BitAppender valid_app;
-    valid_app.init(a.out_valid, wout);
-    const unsigned lt = lanemask_lt();
-#pragma unroll
-    for (int s = 0; s < 16; ++s) {
-      const uint32_t es = __shfl_sync(0xffffffffu, e, s);
-      if (es == 0) continue;  // warp-uniform
-      const uint32_t ivs = __shfl_sync(0xffffffffu, iv, s);
-      const bool isv = (ivs >> lane) & 1u;
-      const uint32_t rank = __popc(es & lt);
-      const uint32_t vs = __shfl_sync(0xffffffffu, vvw, s);
-      const uint32_t bit = (isv && ((vs >> lane) & 1u)) ? (1u << rank) : 0u;
-      const uint32_t cw = __reduce_or_sync(0xffffffffu, bit);
-      valid_app.append(cw, __popc(es), lane);
-    }
-    valid_app.finish(lane);
-  }
-}
+// Measured and dropped in round 2 (profiles/r02_filter_variants.txt):
+//  * one launch with the tile offsets taken by decoupled look-back instead of from filter_plan_kernel's prefix arrays:
+//    0.41 ms per 100 M rows against 0.02 + 0.25 ms — with ~1200 short tiles in flight a new tile walks dozens of
+//    look-back windows before it meets an inclusive state, while the plan kernel only reads the 12.5 MB mask;
+//  * two rows per lane with unconditional LDG.E.128 value loads: 0.30 ms against 0.25 ms (every sector is fetched
+//    either way at 50 % selectivity, and each lane then issues two scattered 8-byte stores per load).
+// b200_filter_fused therefore is filter_plan + filter_apply back to back on the stream, without the host round trip.
 
 int check_mask(b200_ctx* ctx, const b200_col* mask) {
   if (!mask) return b200_fail(ctx, B200_INVALID, "filter: null mask descriptor");
@@ -411,11 +325,6 @@ int check_mask(b200_ctx* ctx, const b200_col* mask) {
 template <typename T, bool kBool>
 int launch_apply(b200_ctx* ctx, const ApplyArgs& a, int64_t n_tiles) {
   dim3 grid((unsigned)n_tiles), block(kThreads);
-  if (!kBool && sizeof(T) == 8 && (reinterpret_cast<uintptr_t>(a.vdata) & 15) == 0) {
-    if (a.out_valid) B200_TIMED(ctx, "filter_apply", (filter_apply_vec_kernel<true><<<grid, block, 0, ctx->stream>>>(a)));
-    else B200_TIMED(ctx, "filter_apply", (filter_apply_vec_kernel<false><<<grid, block, 0, ctx->stream>>>(a)));
-    return B200_OK;
-  }
   if (a.out_valid)
     B200_TIMED(ctx, "filter_apply", (filter_apply_kernel<T, kBool, true><<<grid, block, 0, ctx->stream>>>(a)));
   else

@@ -43,4 +43,8 @@ g++ $CXXFLAGS -c "$HERE/test_glue.cc" -o "$OUT/test_glue.o"
 g++ -o "$HERE/test_glue" "$OUT/test_glue.o" "$HERE/libarrow1_b200_arrow.a" "$OUT"/gpu_*.o \
   "$ROOT/oracle/_ref/libarrow_ref.a" -L"$ROOT/arrow1_b200" -larrow1_b200 -L"$CUDA/lib64/stubs" -lcuda \
   -Wl,-rpath,'$ORIGIN/../arrow1_b200' -lpthread -ldl
+g++ $CXXFLAGS -c "$HERE/bench_glue.cc" -o "$OUT/bench_glue.o"
+g++ -o "$HERE/bench_glue" "$OUT/bench_glue.o" "$HERE/libarrow1_b200_arrow.a" "$OUT"/gpu_*.o \
+  "$ROOT/oracle/_ref/libarrow_ref.a" -L"$ROOT/arrow1_b200" -larrow1_b200 -L"$CUDA/lib64/stubs" -lcuda \
+  -Wl,-rpath,'$ORIGIN/../arrow1_b200' -lpthread -ldl
 echo "arrow_glue: $(ls -la "$HERE/libarrow1_b200_arrow.a" "$HERE/test_glue" | awk '{print $5, $9}' | tr '\n' ' ')"

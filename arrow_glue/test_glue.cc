@@ -517,7 +517,11 @@ int main() {
     std::vector<Case> cases = {{"int32 key (1K groups, C3 shape) x float64", {keys32}, vals},
                                {"int64 key (100K groups) x int64", {keys64}, ivals},
                                {"(uint8, bool) keys (Q1 shape) x float64", {keys8, keysb}, vals},
-                               {"(int32, uint8) keys x int32", {keys32, keys8}, i32vals}};
+                               {"(int32, uint8) keys x int32", {keys32, keys8}, i32vals},
+                               // keys wider than 64 packed bits (FixedWidthKeyEncoder takes any, hash_aggregate.cc:142-196)
+                               {"(int64, int64) keys x float64", {keys64, ivals}, vals},
+                               {"(int64, int32, uint8) keys x int64", {keys64, keys32, keys8}, ivals},
+                               {"(uint8, bool, int32, uint8, int32) keys x float64", {keys8, keysb, keys32, keys8, i32vals}, vals}};
     for (auto& c : cases) {
       std::vector<Datum> hk, dk, ha, da;
       for (auto& k : c.keys) { hk.push_back(k); dk.push_back(DeviceDatum(k)); }
