@@ -6,10 +6,11 @@
 //             non-negatives / all bits of negatives | Descending: bitwise NOT inside the type width
 //             (ties keep ascending row order in both orders, vector_sort.cc:394-401).
 //   classes   the reference's layout [values | NaNs | nulls], the last two in row order for both
-//             orders (vector_sort.cc:269-302), costs no partition pass: NaN and null rows ride through
-//             the low digits with an all-ones key and are split off in the pass over the type's most
-//             significant digit, which has 258 bins: 0..255, 256 = NaN, 257 = null (null-ness is read
-//             from the row's validity bit, so a genuine INT64_MAX is never confused with a null).
+//             orders (vector_sort.cc:269-302), costs no partition pass and no special bins: NaN and null rows
+//             ride through every pass with an all-ones key, so the stable sort leaves them — together with
+//             genuine maxima — at the very end in row order, and tail_*_kernel split that tail (its length is
+//             counted by the first pass) stably into [maxima | NaNs | nulls]; null-ness is read from the
+//             validity bit, so a genuine INT64_MAX is never confused with a null.
 //   kernels   sort_hist_kernel   one read of the column: the digit histograms of every live digit
 //                                (shared-memory atomics, flushed once per CTA)
 //             sort_scan_kernel   exclusive digit bases; a digit that is constant over the column is
@@ -43,6 +44,9 @@ constexpr int kHistTile = kHistThreads * kHistItems;
 #define B200_SORT_ITEMS 16
 #define B200_SORT_MINBLOCKS 3
 #endif
+#ifndef B200_SORT_NARROW_MINBLOCKS
+#define B200_SORT_NARROW_MINBLOCKS (B200_SORT_MINBLOCKS + 1)   // 32-bit keys: 64 registers, 4 CTAs per SM
+#endif
 constexpr int kThreads = B200_SORT_THREADS;   // pass kernel: threads x keys per thread (tuned on B200, see
 constexpr int kItems = B200_SORT_ITEMS;       // profiles/r01_sort_tile_sweep.txt)
 constexpr int kTile = kThreads * kItems;
@@ -74,7 +78,7 @@ struct SortParams {
   BitmapRef vv;        // validity (words == nullptr: no nulls)
   int32_t width;       // bytes per value
   int32_t tkind;       // kUnsignedKey / kSignedKey / kFloatKey
-  int32_t cls_digit;   // digit whose pass carries the NaN / null bins, -1 = none
+  int32_t cls_digit;   // >= 0: the column can hold nulls or NaNs (its most significant digit), -1 = it cannot
   int32_t n_digits;    // digits that can vary (width, or 8 for ready-made keys)
   uint64_t sign;       // sign bit of the type
   uint64_t wmask;      // all ones inside the type width
@@ -89,6 +93,8 @@ struct SortParams {
   const uint32_t* pay_in;  // optional (with keys_in): 32-bit payload carried through the passes instead of the row number
   uint64_t* out_idx;
   uint64_t* out_keys;      // optional
+  int32_t tail_fix;        // NaN / null rows are ordered by the tail fix-up after the last pass (no 258-bin class pass)
+  uint32_t* tail_count;    // rows whose key is all ones: nulls, NaNs and genuine maxima (they end up last, in row order)
   int32_t narrow;          // passes that only look at one 32-bit word of the key carry that word alone
   uint32_t* hist;          // [8][kBinStride] counts, then exclusive bases
   PassInfo* info;          // [8]
@@ -156,9 +162,7 @@ __global__ void __launch_bounds__(kHistThreads) sort_hist_kernel(SortParams p) {
 #pragma unroll
         for (int d = 0; d < kDigits; ++d) {
           if (d < p.n_digits) {
-            uint32_t bin = uint32_t(key >> (8 * d)) & 255u;
-            if (d == p.cls_digit && cls) bin = 255u + cls;
-            atomicAdd(&h[d][bin], 1u);
+            atomicAdd(&h[d][uint32_t(key >> (8 * d)) & 255u], 1u);
           }
         }
       }
@@ -275,17 +279,17 @@ struct PassSmem {
   uint32_t tile;
 };
 
-// kClass: this pass carries the NaN / null bins (NBINS = 258).  kFull: the tile has 4096 rows.
+// kFull: the tile has 4096 rows.  (NaN / null rows are no business of the passes: they carry the all-ones key and
+// are ordered by the tail fix-up after the last pass; round 1 ranked every row of the last pass over 258 bins.)
 // kNarrow: the pass looks at one 32-bit word of the key only (digits 4..7 of a 64-bit key, or any digit of a
 // <= 32-bit column) and holds, stages and writes that word alone: 8 B per row and pass instead of 12.
-template <bool kClass, bool kFull, bool kNarrow>
+template <bool kFull, bool kNarrow>
 __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d, const PassInfo info,
                                                PassSmem<typename std::conditional<kNarrow, uint32_t, uint64_t>::type>& s,
                                                const int64_t tile, const int tile_items) {
   using KeyT = typename std::conditional<kNarrow, uint32_t, uint64_t>::type;
-  constexpr int NBINS = kClass ? 258 : 256;
+  constexpr int NBINS = 256;
   const int word_shift = (kNarrow && d >= 4) ? 32 : 0;                    // which word a narrow key is
-  const KeyT all_ones = KeyT(p.wmask >> word_shift);                       // NaN / null key in this pass's width
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const unsigned lt = lanemask_lt();
   const int64_t tile_row0 = tile * kTile;
@@ -297,12 +301,12 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
 
   // ---- load: all global loads are issued back to back, transforms follow
   KeyT key[kItems];
-  uint64_t cls_bits = 0;  // 2 bits per item: 1 NaN, 2 null (only in the class pass)
   if (info.first && !p.keys_in) {
     uint32_t vword = 0xffffffffu;  // validity word of step `lane` (lanes 0..15)
     if (p.vv.words && lane < kItems) vword = bitmap_load32(p.vv, tile_row0 + warp * (kItems * 32) + lane * 32, p.n);
     const char* src = reinterpret_cast<const char*>(p.vdata);
     uint64_t raw[kItems];
+    uint32_t tail = 0;
     switch (p.width) {
       case 1:
 #pragma unroll
@@ -335,7 +339,12 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
         k = p.wmask;
       }
       key[i] = KeyT(k >> word_shift);
-      if (kClass) cls_bits |= uint64_t(cls) << (2 * i);
+      if (k == p.wmask && (kFull || wbase + 32 * i < tile_items)) ++tail;
+    }
+    // rows whose key is all ones (nulls, NaNs, genuine maxima): the tail the fix-up kernels re-order after the last pass
+    if (p.tail_fix) {
+      tail = __reduce_add_sync(0xffffffffu, tail);
+      if (lane == 0 && tail) atomicAdd(p.tail_count, tail);
     }
   } else {
     if (info.first) {   // ready-made 64-bit keys
@@ -346,19 +355,6 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
 #pragma unroll
       for (int i = 0; i < kItems; ++i) key[i] = (kFull || wbase + 32 * i < tile_items) ? keys_src[tile_row0 + wbase + 32 * i] : KeyT(0);
     }
-    if (kClass) {
-      // candidates have digit 255; the row's validity bit / the all-ones float key decide (a float key whose
-      // upper word is all ones is a NaN's: no number maps there, see transform_key)
-#pragma unroll
-      for (int i = 0; i < kItems; ++i) {
-        if ((kFull || wbase + 32 * i < tile_items) && key_digit(key[i], d) == 255u) {
-          uint32_t cls = 0;
-          if (p.vv.words && !bitmap_get(p.vv, pays_src[tile_row0 + wbase + 32 * i])) cls = 2;
-          else if (p.tkind == kFloatKey && key[i] == all_ones) cls = 1;
-          cls_bits |= uint64_t(cls) << (2 * i);
-        }
-      }
-    }
   }
 
   // ---- rank inside the warp (stable: items visited in index order, lanes in lane order).
@@ -367,7 +363,7 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
   // return value is the group's base rank.  Items go in groups of kRankGroup: all atomics of a group
   // are issued before the first return value is consumed, so their latencies overlap instead of
   // forming a 16-deep dependency chain (the short-scoreboard stall that dominated v2's profile).
-  constexpr int NB = kClass ? 9 : 8;
+  constexpr int NB = 8;
   constexpr int kRankGroup = kItems < 8 ? kItems : 8;
   uint32_t rank2[kItems / 2];  // two 16-bit ranks per register
   uint32_t* myhist = s.whist[warp];
@@ -379,11 +375,7 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
     for (int q = 0; q < kRankGroup; ++q) {
       const int i = g0 + q;
       const bool in = kFull || wbase + 32 * i < tile_items;
-      uint32_t bin = key_digit(key[i], d);
-      if (kClass) {
-        const uint32_t cls = uint32_t(cls_bits >> (2 * i)) & 3u;
-        if (cls) bin = 255u + cls;
-      }
+      const uint32_t bin = key_digit(key[i], d);
       unsigned m = kFull ? 0xffffffffu : __ballot_sync(0xffffffffu, in);
 #pragma unroll
       for (int b = 0; b < NB; ++b) m = match_bit(m, bin, 1u << b);
@@ -452,15 +444,6 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
       // shared-memory wavefronts (57 % of them bank conflicts from digit-random addresses)
 #pragma unroll
       for (int w = 0; w < kWarps; ++w) s.whist[w][t] += pre;
-      if (kClass && t == 255) {
-        const uint32_t p256 = wpre + incl, p257 = wpre + incl + s.tile_count[256];
-        s.tile_prefix[256] = p256;
-        s.tile_prefix[257] = p257;
-        for (int w = 0; w < kWarps; ++w) {
-          s.whist[w][256] += p256;
-          s.whist[w][257] += p257;
-        }
-      }
     }
   }
   __syncthreads();
@@ -469,16 +452,10 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
   // of the kernel's stall samples) and before the shared-memory scatter, which hides the first trip.
   const uint32_t* base_hist = p.hist + d * kBinStride;
   uint32_t look[kLook];
-  uint32_t look2[kLook];   // class pass: threads 0 / 1 also own the NaN / null bins (256 / 257)
   if (tile > 0 && t < 256) {
 #pragma unroll
     for (int j = 0; j < kLook; ++j)
       look[j] = tile - 1 - j >= 0 ? ld_volatile_u32(state + t - (j + 1) * kBinStride) : kStatusInclusive;
-    if (kClass && t < 2) {
-#pragma unroll
-      for (int j = 0; j < kLook; ++j)
-        look2[j] = tile - 1 - j >= 0 ? ld_volatile_u32(state + 256 + t - (j + 1) * kBinStride) : kStatusInclusive;
-    }
   }
 
   // ---- scatter into shared memory in tile-sorted order (needs tile_prefix + warp offsets only)
@@ -486,13 +463,8 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
   for (int i = 0; i < kItems; ++i) {
     const int local = wbase + 32 * i;
     if (kFull || local < tile_items) {
-      uint32_t bin = key_digit(key[i], d);
-      uint32_t pv = pay[i];
-      if (kClass) {
-        const uint32_t cls = uint32_t(cls_bits >> (2 * i)) & 3u;
-        if (cls) bin = 255u + cls;
-        pv |= cls << 30;
-      }
+      const uint32_t bin = key_digit(key[i], d);
+      const uint32_t pv = pay[i];
       const uint32_t r = (i & 1) ? (rank2[i >> 1] >> 16) : (rank2[i >> 1] & 0xFFFFu);
       const uint32_t pos = myhist[bin] + r;
       s.keys[pos] = key[i];
@@ -534,10 +506,7 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
     }
     s.bin_delta[b] = base_hist[b] + excl - s.tile_prefix[b];
   };
-  if (t < 256) {
-    resolve(t, look);
-    if (kClass && t < 2) resolve(256 + t, look2);
-  }
+  if (t < 256) resolve(t, look);
   __syncthreads();
 
   // ---- digit-contiguous global stores
@@ -549,13 +518,8 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
     const int j = k * kThreads + t;
     if (kFull || j < tile_items) {
       const KeyT kk = s.keys[j];
-      uint32_t pv = s.pay[j];
-      uint32_t bin = key_digit(kk, d);
-      if (kClass) {
-        const uint32_t cls = pv >> 30;
-        if (cls) bin = 255u + cls;
-        pv &= kValueMask;
-      }
+      const uint32_t pv = s.pay[j];
+      const uint32_t bin = key_digit(kk, d);
       const uint32_t pos = uint32_t(j) + s.bin_delta[bin];
       if (info.last) {
         p.out_idx[pos] = p.gather ? p.gather[pv] : (uint64_t(pv) + p.index_base);
@@ -570,8 +534,8 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
   }
 }
 
-template <bool kClass, bool kNarrow>
-__global__ void __launch_bounds__(kThreads, kNarrow ? kMinBlocks + 1 : kMinBlocks) sort_pass_kernel(SortParams p, int d) {
+template <bool kNarrow>
+__global__ void __launch_bounds__(kThreads, kNarrow ? B200_SORT_NARROW_MINBLOCKS : kMinBlocks) sort_pass_kernel(SortParams p, int d) {
   const PassInfo info = p.info[d];
   if (info.skip) return;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -583,8 +547,124 @@ __global__ void __launch_bounds__(kThreads, kNarrow ? kMinBlocks + 1 : kMinBlock
   __syncthreads();
   const int64_t tile = s.tile;
   const int tile_items = int(min(int64_t(kTile), p.n - tile * kTile));
-  if (tile_items == kTile) sort_pass_body<kClass, true, kNarrow>(p, d, info, s, tile, tile_items);
-  else sort_pass_body<kClass, false, kNarrow>(p, d, info, s, tile, tile_items);
+  if (tile_items == kTile) sort_pass_body<true, kNarrow>(p, d, info, s, tile, tile_items);
+  else sort_pass_body<false, kNarrow>(p, d, info, s, tile, tile_items);
+}
+
+
+// ---- NaN / null rows without a class pass ----------------------------------------------------------------------------
+// Null and NaN rows carry the all-ones key through every pass like genuine maxima do, so a plain stable LSD sort leaves
+// exactly the rows whose key is all ones at the very end, in row order.  Their number is counted by the histogram
+// kernel; the three kernels below split that tail stably into [genuine maxima | NaNs | nulls] (vector_sort.cc:269-302).
+// A column with 1 % nulls re-orders 1 % of the rows instead of ranking every row of the last pass over 258 bins with a
+// ninth ballot and a validity gather (1.02 ms against 0.70 ms for a plain pass at 100 M rows, round 1).
+constexpr int kTailThreads = 256;
+constexpr int kTailMaxBlocks = 1024;
+
+struct TailArgs {
+  SortParams p;
+  uint64_t* idx;      // the sorted indices (out_idx)
+  uint64_t* tmp;      // >= tail entries
+  uint32_t* counts;   // [blocks][4] class counts, then exclusive positions
+};
+
+__device__ __forceinline__ uint32_t tail_class(const SortParams& p, uint64_t out_index) {
+  const int64_t row = int64_t(out_index - p.index_base);
+  if (!bitmap_get(p.vv, row)) return 2;
+  if (p.tkind == kFloatKey && ((load_raw(p, row) & ~p.sign) > p.nan_above)) return 1;
+  return 0;
+}
+
+__device__ __forceinline__ void tail_range(const TailArgs& a, int64_t* begin, int64_t* end, int64_t* first) {
+  const int64_t T = *a.p.tail_count;
+  int64_t chunk = (T + gridDim.x - 1) / gridDim.x;
+  chunk = (chunk + kTailThreads - 1) / kTailThreads * kTailThreads;
+  *first = a.p.n - T;
+  *begin = min(T, int64_t(blockIdx.x) * chunk);
+  *end = min(T, *begin + chunk);
+}
+
+__global__ void __launch_bounds__(kTailThreads) tail_count_kernel(const __grid_constant__ TailArgs a) {
+  __shared__ uint32_t c[4];
+  if (threadIdx.x < 4) c[threadIdx.x] = 0;
+  __syncthreads();
+  int64_t begin, end, first;
+  tail_range(a, &begin, &end, &first);
+  for (int64_t i = begin + threadIdx.x; i < end; i += kTailThreads) atomicAdd(&c[tail_class(a.p, a.idx[first + i])], 1u);
+  __syncthreads();
+  if (threadIdx.x < 4) a.counts[blockIdx.x * 4 + threadIdx.x] = c[threadIdx.x];
+}
+
+// one CTA: counts[b][c] -> where block b's rows of class c start inside the tail
+__global__ void __launch_bounds__(kTailMaxBlocks) tail_scan_kernel(uint32_t* counts, int blocks) {
+  __shared__ uint32_t warp_sums[32];
+  __shared__ uint32_t class_start;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  if (t == 0) class_start = 0;
+  __syncthreads();
+  for (int c = 0; c < 3; ++c) {
+    const uint32_t v = t < blocks ? counts[t * 4 + c] : 0;
+    uint32_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    uint32_t wpre = 0, total = 0;
+    for (int w = 0; w < kTailMaxBlocks / 32; ++w) {
+      if (w < warp) wpre += warp_sums[w];
+      total += warp_sums[w];
+    }
+    const uint32_t start = class_start;
+    if (t < blocks) counts[t * 4 + c] = start + wpre + incl - v;
+    __syncthreads();
+    if (t == 0) class_start = start + total;
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(kTailThreads) tail_scatter_kernel(const __grid_constant__ TailArgs a) {
+  __shared__ uint32_t run[4];                        // next position of every class for this block
+  __shared__ uint32_t wcnt[kTailThreads / 32][4];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const unsigned lt = lanemask_lt();
+  if (t < 4) run[t] = a.counts[blockIdx.x * 4 + t];
+  int64_t begin, end, first;
+  tail_range(a, &begin, &end, &first);
+  for (int64_t base = begin; base < end; base += kTailThreads) {
+    const int64_t i = base + t;
+    const bool in = i < end;
+    const uint64_t v = in ? a.idx[first + i] : 0;
+    const uint32_t c = in ? tail_class(a.p, v) : 3;
+    uint32_t rank = 0;
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+      const unsigned m = __ballot_sync(0xffffffffu, c == q);
+      if (c == q) rank = __popc(m & lt);
+      if (lane == 0) wcnt[warp][q] = __popc(m);
+    }
+    __syncthreads();
+    if (in) {
+      uint32_t pre = run[c];
+      for (int w = 0; w < warp; ++w) pre += wcnt[w][c];
+      a.tmp[pre + rank] = v;
+    }
+    __syncthreads();
+    if (t < 3) {
+      uint32_t add = 0;
+      for (int w = 0; w < kTailThreads / 32; ++w) add += wcnt[w][t];
+      run[t] += add;
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void tail_copy_kernel(const __grid_constant__ TailArgs a) {
+  const int64_t T = *a.p.tail_count;
+  uint64_t* dst = a.idx + (a.p.n - T);
+  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < T; i += int64_t(gridDim.x) * blockDim.x) dst[i] = a.tmp[i];
 }
 
 __global__ void sort_keys_kernel(SortParams p, uint64_t* out, uint64_t* out_rows) {
@@ -878,7 +958,7 @@ __global__ void mk_gather_flat_kernel(const uint64_t* flat_keys, const uint8_t* 
 }
 
 struct Layout {
-  size_t hist, info, counters, err, state, zero_bytes, keys0, keys1, pays0, pays1, total;
+  size_t hist, info, counters, err, tail, state, zero_bytes, keys0, keys1, pays0, pays1, total;
 };
 
 Layout layout_for(int64_t n) {
@@ -889,6 +969,7 @@ Layout layout_for(int64_t n) {
   L.info = off; off += 256;
   L.counters = off; off += 128;
   L.err = off; off += 128;
+  L.tail = off; off += size_t(kTailMaxBlocks) * 16;
   L.state = off; off += b200_align_up(size_t(kDigits) * n_tiles * kBinStride * 4, 256);
   L.zero_bytes = off;
   L.keys0 = off; off += b200_align_up(size_t(n) * 8, 256);
@@ -953,27 +1034,38 @@ int run_sort(b200_ctx* ctx, SortParams p, void* scratch, size_t scratch_bytes) {
   const int hist_blocks = int(std::min<int64_t>((p.n + kHistTile - 1) / kHistTile, int64_t(ctx->num_sms) * 8));
   const int smem_wide = int(sizeof(PassSmem<uint64_t>)), smem_narrow = int(sizeof(PassSmem<uint32_t>));
   if (b200_ctx_once(ctx, 0)) {
-    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_wide));
-    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_wide));
-    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_narrow));
-    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_narrow));
+    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_wide));
+    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_narrow));
   }
   // the caller wants the sorted 64-bit keys back: every pass carries them whole
   p.narrow = p.out_keys ? 0 : 1;
+  // a column that can hold nulls or NaNs: plain passes, then the tail fix-up (layout slot `err` is free: the bail-out
+  // flag lives in the context)
+  p.tail_fix = p.cls_digit >= 0 ? 1 : 0;
+  p.tail_count = reinterpret_cast<uint32_t*>(base + L.err);
   B200_TIMED(ctx, "sort_hist", (sort_hist_kernel<<<hist_blocks, kHistThreads, 0, ctx->stream>>>(p)));
   sort_scan_kernel<<<1, kHistThreads, 0, ctx->stream>>>(p);
   B200_LAUNCHED(ctx);
   for (int d = 0; d < p.n_digits; ++d) {
     const bool narrow = p.narrow && (d >= 4 || p.n_digits <= 4);
     const unsigned grid = unsigned(p.n_tiles);
-    if (d == p.cls_digit && narrow)
-      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<true, true><<<grid, kThreads, smem_narrow, ctx->stream>>>(p, d)));
-    else if (d == p.cls_digit)
-      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<true, false><<<grid, kThreads, smem_wide, ctx->stream>>>(p, d)));
-    else if (narrow)
-      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<false, true><<<grid, kThreads, smem_narrow, ctx->stream>>>(p, d)));
+    if (narrow)
+      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<true><<<grid, kThreads, smem_narrow, ctx->stream>>>(p, d)));
     else
-      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<false, false><<<grid, kThreads, smem_wide, ctx->stream>>>(p, d)));
+      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<false><<<grid, kThreads, smem_wide, ctx->stream>>>(p, d)));
+  }
+  if (p.tail_fix) {
+    TailArgs ta;
+    ta.p = p;
+    ta.idx = p.out_idx;
+    ta.tmp = p.keys[0];
+    ta.counts = reinterpret_cast<uint32_t*>(base + L.tail);
+    const int blocks = std::min(kTailMaxBlocks, ctx->num_sms * 4);
+    B200_TIMED(ctx, "sort_tail", (tail_count_kernel<<<blocks, kTailThreads, 0, ctx->stream>>>(ta)));
+    tail_scan_kernel<<<1, kTailMaxBlocks, 0, ctx->stream>>>(ta.counts, blocks);
+    B200_LAUNCHED(ctx);
+    B200_TIMED(ctx, "sort_tail", (tail_scatter_kernel<<<blocks, kTailThreads, 0, ctx->stream>>>(ta)));
+    B200_TIMED(ctx, "sort_tail", (tail_copy_kernel<<<blocks, kTailThreads, 0, ctx->stream>>>(ta)));
   }
   return B200_OK;
 }

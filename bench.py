@@ -339,7 +339,7 @@ class GroupByWL(Workload):
 
     def cpu_step(self, oracle, kind, host_cols):
         k, v = host_cols
-        return oracle.groupby([k], self._specs(), [v] * len(self.agg_names), kind=kind, max_groups=self.n_keys + 2)
+        return oracle.groupby([k], self._specs(), [v] * len(self.agg_names), kind=kind, max_groups=min(k.length, self.n_keys + 2))
 
 
 class Q1WL(Workload):
@@ -533,6 +533,9 @@ def run_cpu(wl, steps, warmup, threads):
              [(i * per, per) for i in range(threads)]
     shards = [wl.make(gen, start=lo, n=ln) for lo, ln in bounds]
     subs = {ln: make_workload(wl.name, ln) for _, ln in bounds}
+    for sub in subs.values():   # shards of the SAME columns: keep the parent's key cardinality
+        if hasattr(wl, "n_keys"):
+            sub.n_keys = wl.n_keys
     pool = ThreadPoolExecutor(max_workers=threads)
 
     def one():
