@@ -22,6 +22,7 @@
 #include <memory>
 #include <vector>
 
+#include "arrow/c/abi.h"
 #include "arrow/compute/api_aggregate.h"
 #include "arrow/compute/exec.h"
 #include "arrow/compute/registry.h"
@@ -66,6 +67,21 @@ Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Dat
 /// UInt32Array of group ids (ids in first-occurrence order), GetUniques() device-resident keys.
 Result<std::unique_ptr<internal::Grouper>> MakeGrouper(const std::vector<ValueDescr>& descrs,
                                                        ExecContext* ctx, int device = 0);
+
+/// Ingest / egress of columns.  CopyToDevice returns the same ArrayData with every host buffer
+/// replaced by a pooled CudaBuffer holding its bytes (offsets kept, the null count settled on the host first);
+/// CopyToHost is the way back, into pinned CudaHostBuffers.  Pinned sources / destinations (CudaHostBuffer,
+/// AllocatePinned, registered memory) move by DMA at PCIe speed; pageable ones go through two pinned staging blocks,
+/// the CPU copy of one chunk overlapping the DMA of the previous one.  Replaces CudaBuffer::CopyFromHost /
+/// CopyToHost (gpu/cuda_memory.h:64-71), which are synchronous copies from pageable memory.
+Result<std::shared_ptr<ArrayData>> CopyToDevice(const ArrayData& host, int device = 0);
+Result<std::shared_ptr<ArrayData>> CopyToHost(const ArrayData& device_data, int device = 0);
+/// A pinned host buffer (CudaHostBuffer) for columns that are produced on the host and consumed on the device.
+Result<std::shared_ptr<Buffer>> AllocatePinned(int64_t nbytes, int device = 0);
+/// Arrow C Data Interface (arrow/c/abi.h, c/bridge.h): an exported host array -> device-resident ArrayData (the
+/// structs are consumed, like ImportArray), and a device-resident array exported as a host array.
+Result<std::shared_ptr<ArrayData>> ImportToDevice(struct ArrowArray* array, struct ArrowSchema* schema, int device = 0);
+Status ExportFromDevice(const ArrayData& device_data, struct ArrowArray* out, struct ArrowSchema* out_schema, int device = 0);
 
 }  // namespace cuda
 }  // namespace compute

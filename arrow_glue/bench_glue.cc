@@ -6,8 +6,12 @@
 // Two numbers per workload, both with CUDA-event-free wall clocks around device-synchronising calls (every registry
 // call returns after its results are on the device and the context is synchronised):
 //   device   inputs already CudaBuffers; one registry call per step
-//   e2e      host Arrow arrays in, host Arrow array out: CudaBuffer::CopyFromHost of every input buffer
-//            (gpu/cuda_memory.h:71), the registry call, CudaBuffer::CopyToHost of every output buffer (:64) per step
+//   e2e      host Arrow arrays in, host Arrow array out, per step: cuda::CopyToDevice of every input column, the
+//            registry call, cuda::CopyToHost of the result (arrow_glue's ingest / egress: DMA from / to pinned
+//            memory, pooled device blocks).  The input columns live in pinned host buffers (cuda::AllocatePinned), as
+//            a pipeline that feeds the GPU would keep them.
+//   e2e_ref  the same with the reference's own copies, CudaBuffer::CopyFromHost / CopyToHost (gpu/cuda_memory.h:64-71:
+//            synchronous cuMemcpy, here from the same pinned buffers), for comparison
 // The columns are the generator of arrow1_b200/synth.py restated in C++ (splitmix64 of seed * GOLDEN + row).
 // Built by arrow_glue/build.sh where /root/reference exists; shipped prebuilt to the GPU box.
 #include <chrono>
@@ -46,6 +50,15 @@ T Unwrap(Result<T> r, const char* what) {
 
 static std::shared_ptr<cuda::CudaContext> g_cuda;
 
+std::shared_ptr<Buffer> PinnedBuffer(int64_t nbytes) {
+  auto r = cp::cuda::AllocatePinned(nbytes, 0);
+  if (!r.ok()) {
+    std::cerr << "ABORT AllocatePinned: " << r.status().ToString() << std::endl;
+    std::exit(2);
+  }
+  return r.MoveValueUnsafe();
+}
+
 static inline uint64_t R(uint64_t seed, uint64_t i) {
   uint64_t x = i + seed * 0x9E3779B97F4A7C15ull + 0x9E3779B97F4A7C15ull;
   uint64_t z = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -54,7 +67,7 @@ static inline uint64_t R(uint64_t seed, uint64_t i) {
 }
 
 std::shared_ptr<Buffer> ValidityOf(uint64_t seed, int64_t n, int64_t* nulls) {
-  auto buf = GET(AllocateBitmap(n));
+  auto buf = PinnedBuffer(BitUtil::BytesForBits(n));
   std::memset(buf->mutable_data(), 0, buf->size());
   int64_t zeros = 0;
   for (int64_t i = 0; i < n; ++i) {
@@ -63,7 +76,7 @@ std::shared_ptr<Buffer> ValidityOf(uint64_t seed, int64_t n, int64_t* nulls) {
     else ++zeros;
   }
   *nulls = zeros;
-  return std::move(buf);
+  return buf;
 }
 
 std::shared_ptr<ArrayData> ToDevice(const ArrayData& a) {
@@ -109,30 +122,30 @@ int main(int argc, char** argv) {
 
   std::vector<std::shared_ptr<ArrayData>> host;   // the workload's input columns
   if (wl == "sort_i64") {
-    auto data = GET(AllocateBuffer(n * 8));
+    auto data = PinnedBuffer(n * 8);
     auto* v = reinterpret_cast<int64_t*>(data->mutable_data());
     for (int64_t i = 0; i < n; ++i) v[i] = int64_t(R(4, i));
     int64_t nulls = 0;
     auto valid = ValidityOf(6, n, &nulls);
     host.push_back(ArrayData::Make(int64(), n, {valid, std::move(data)}, nulls));
   } else if (wl == "filter") {
-    auto data = GET(AllocateBuffer(n * 8));
+    auto data = PinnedBuffer(n * 8);
     auto* v = reinterpret_cast<int64_t*>(data->mutable_data());
     for (int64_t i = 0; i < n; ++i) v[i] = int64_t(R(1, i));
     int64_t nulls = 0;
     auto valid = ValidityOf(2, n, &nulls);
     host.push_back(ArrayData::Make(int64(), n, {valid, std::move(data)}, nulls));
-    auto mask = GET(AllocateBitmap(n));
+    auto mask = PinnedBuffer(BitUtil::BytesForBits(n));
     std::memset(mask->mutable_data(), 0, mask->size());
     for (int64_t i = 0; i < n; ++i)
       if (R(3, i) & 1) BitUtil::SetBit(mask->mutable_data(), i);
     host.push_back(ArrayData::Make(boolean(), n, {nullptr, std::move(mask)}, 0));
   } else if (wl == "groupby_c3") {
-    auto keys = GET(AllocateBuffer(n * 4));
+    auto keys = PinnedBuffer(n * 4);
     auto* k = reinterpret_cast<int32_t*>(keys->mutable_data());
     for (int64_t i = 0; i < n; ++i) k[i] = int32_t((R(7, i) >> 20) % 1000);
     host.push_back(ArrayData::Make(int32(), n, {nullptr, std::move(keys)}, 0));
-    auto data = GET(AllocateBuffer(n * 8));
+    auto data = PinnedBuffer(n * 8);
     auto* v = reinterpret_cast<double*>(data->mutable_data());
     for (int64_t i = 0; i < n; ++i) v[i] = double(R(8, i) >> 11) * std::ldexp(1.0, -53) * 1e14;
     int64_t nulls = 0;
@@ -169,27 +182,34 @@ int main(int argc, char** argv) {
 
   // ---- end to end: host arrays in, host array out
   int64_t h2d = 0, d2h = 0;
-  auto e2e = [&]() {
+  auto e2e = [&](bool glue_copies) {
     std::vector<std::shared_ptr<ArrayData>> d;
     h2d = 0;
     for (auto& h : host) {
-      d.push_back(ToDevice(*h));
+      d.push_back(glue_copies ? GET(cp::cuda::CopyToDevice(*h, 0)) : ToDevice(*h));
       h2d += BytesOf(*h);
     }
     Datum out = run(d);
-    auto back = ToHost(*out.array());
+    auto back = glue_copies ? GET(cp::cuda::CopyToHost(*out.array(), 0)) : ToHost(*out.array());
     d2h = BytesOf(*back);
   };
-  e2e();
+  e2e(true);
+  e2e(true);
   t0 = Now();
-  for (int i = 0; i < steps; ++i) e2e();
+  for (int i = 0; i < steps; ++i) e2e(true);
   const double e2e_ms = (Now() - t0) * 1e3 / steps;
+  e2e(false);
+  t0 = Now();
+  for (int i = 0; i < 2; ++i) e2e(false);
+  const double e2e_ref_ms = (Now() - t0) * 1e3 / 2;
 
   std::cout << "{\"workload\": \"" << wl << "\", \"rows\": " << n << ", \"steps\": " << steps
             << ", \"api\": \"compute::CallFunction / cuda::GroupBy over the CUDA FunctionRegistry (arrow_glue)\""
             << ", \"device_ms_per_step\": " << dev_ms << ", \"device_rows_per_s\": " << double(n) / (dev_ms * 1e-3)
             << ", \"e2e_ms_per_step\": " << e2e_ms << ", \"e2e_rows_per_s\": " << double(n) / (e2e_ms * 1e-3)
             << ", \"h2d_bytes_per_step\": " << h2d << ", \"d2h_bytes_per_step\": " << d2h
-            << ", \"copies\": \"CudaBuffer::CopyFromHost / CopyToHost (synchronous cuMemcpy from pageable host memory)\"}" << std::endl;
+            << ", \"e2e_with_reference_copies_ms_per_step\": " << e2e_ref_ms
+            << ", \"copies\": \"cuda::CopyToDevice / CopyToHost (DMA from / to pinned host buffers, pooled device blocks); "
+               "reference copies = CudaBuffer::CopyFromHost / CopyToHost\"}" << std::endl;
   return 0;
 }

@@ -19,6 +19,7 @@
 #include "arrow/gpu/cuda_api.h"
 #include "arrow/util/checked_cast.h"
 
+#include "arrow/c/bridge.h"
 #include "b200_arrow.h"
 
 using namespace arrow;  // NOLINT
@@ -176,6 +177,37 @@ int main() {
     for (const char* name : {"filter", "array_filter", "sort_indices", "array_sort_indices", "take", "array_take", "hash_count", "hash_sum", "hash_min_max", "hash_mean"})
       CHECK_TRUE(registry->GetFunction(name).ok(), std::string("registered: ") + name);
     CHECK_TRUE(registry->GetFunction("unique").status().IsKeyError(), "unknown function -> KeyError (registry.cc:62-64)");
+  }
+
+  // ---------------- ingest / egress: cuda::CopyToDevice / CopyToHost, C Data Interface ----------------
+  {
+    const int64_t n = 3000001;   // several staging blocks, ragged tail
+    auto vals = MakeRandom<Int64Builder, int64_t>(n, rng, 0.05, -(1LL << 60), 1LL << 60, false);
+    auto sliced = vals->Slice(12345, n - 20000);
+    auto dev = GET(cp::cuda::CopyToDevice(*sliced->data(), 0));   // pageable source: staged through pinned blocks
+    CHECK_TRUE(!dev->buffers[1]->is_cpu() && dev->offset == sliced->data()->offset && dev->null_count.load() == sliced->null_count(),
+               "CopyToDevice keeps offset and settles the null count");
+    auto back = MakeArray(GET(cp::cuda::CopyToHost(*dev, 0)));
+    ExpectEqual(back, sliced, "CopyToDevice -> CopyToHost round trip (pageable source, sliced)");
+    // pinned source: straight DMA
+    auto pinned = GET(cp::cuda::AllocatePinned(n * 8, 0));
+    std::memcpy(pinned->mutable_data(), vals->data()->buffers[1]->data(), n * 8);
+    auto parr = ArrayData::Make(int64(), n, {vals->data()->buffers[0], pinned}, vals->null_count());
+    auto pdev = GET(cp::cuda::CopyToDevice(*parr, 0));
+    ExpectEqual(MakeArray(GET(cp::cuda::CopyToHost(*pdev, 0))), vals, "CopyToDevice from a pinned buffer");
+    // C Data Interface: export on the host, import onto the device, compute, export back
+    struct ArrowArray c_array;
+    struct ArrowSchema c_schema;
+    ABORT_NOT_OK(ExportArray(*vals, &c_array, &c_schema));
+    auto imported = GET(cp::cuda::ImportToDevice(&c_array, &c_schema, 0));
+    auto mask = MakeRandom<BooleanBuilder, int>(n, rng, 0.0, 0, 2, false);
+    auto want = GET(cp::Filter(vals, mask, cp::FilterOptions::Defaults(), &cpu_ctx)).make_array();
+    auto got = GET(cp::Filter(Datum(imported), DeviceDatum(mask), cp::FilterOptions::Defaults(), &gpu_ctx));
+    struct ArrowArray c_out;
+    struct ArrowSchema c_out_schema;
+    ABORT_NOT_OK(cp::cuda::ExportFromDevice(*got.array(), &c_out, &c_out_schema, 0));
+    auto round = GET(ImportArray(&c_out, &c_out_schema));
+    ExpectEqual(round, want, "C Data Interface: ImportToDevice -> filter -> ExportFromDevice");
   }
 
   // ---------------- Filter ----------------

@@ -42,7 +42,7 @@ array/util.cc array/validate.cc builder.cc buffer.cc chunked_array.cc compare.cc
 device.cc extension_type.cc memory_pool.cc pretty_print.cc record_batch.cc result.cc scalar.cc
 sparse_tensor.cc status.cc table.cc table_builder.cc tensor.cc tensor/coo_converter.cc
 tensor/csf_converter.cc tensor/csx_converter.cc type.cc visitor.cc
-io/interfaces.cc io/memory.cc
+io/interfaces.cc io/memory.cc c/bridge.cc
 util/basic_decimal.cc util/bit_block_counter.cc util/bit_run_reader.cc util/bit_util.cc
 util/bitmap.cc util/bitmap_builders.cc util/bitmap_ops.cc util/bpacking.cc util/cancel.cc
 util/cpu_info.cc util/decimal.cc util/delimiting.cc util/formatting.cc util/future.cc
