@@ -381,19 +381,31 @@ def GroupBy(arguments: Sequence[Column], keys: Sequence[Column], aggregates: Seq
     if not host:
         return out
     d2h = 0
-    res_aggs = []
-    for cols_ in out.aggs:
-        lst = []
-        for c in cols_:
-            h = c.to_host()
-            d2h += h.nbytes()
-            lst.append((h.values().copy(), h.valid()))
-        res_aggs.append(lst)
-    res_keys = []
-    for c in out.keys:
-        h = c.to_host()
-        d2h += h.nbytes()
-        res_keys.append((h.values().copy(), h.valid()))
+
+    def pair(c):
+        """device result column -> (values, valid) on the host through the pinned pool (DMA, no pageable staging)"""
+        nonlocal d2h
+        from .columns import BITS, NP_OF, BOOL, unpack_bits
+        g = c.length
+        bits = BITS[c.type]
+        nb = (g + 7) // 8 if bits == 1 else g * (bits // 8)
+        data = _d2h(c.data, nb)
+        vbytes = _d2h(c.validity, (g + 7) // 8) if c.validity is not None else None
+        d2h += nb + (0 if vbytes is None else (g + 7) // 8)
+        return c.type, data, vbytes, g
+
+    staged_aggs = [[pair(c) for c in cols_] for cols_ in out.aggs]
+    staged_keys = [pair(c) for c in out.keys]
+    ctx.stream.synchronize()
+
+    def finish(t, data, vbytes, g):
+        from .columns import BITS, NP_OF, BOOL, unpack_bits
+        vals = unpack_bits(data, g) if t == BOOL else data[: g * (BITS[t] // 8)].view(NP_OF[t])
+        valid = np.ones(g, dtype=np.bool_) if vbytes is None else unpack_bits(vbytes, g)
+        return vals, valid
+
+    res_aggs = [[finish(*p) for p in lst] for lst in staged_aggs]
+    res_keys = [finish(*p) for p in staged_keys]
     Transfer.d2h = d2h
     return GroupByResult(out.num_groups, res_aggs, res_keys)
 

@@ -267,6 +267,41 @@ __device__ __forceinline__ unsigned match_bit(unsigned m, uint32_t bin, uint32_t
   return r;
 }
 
+// ---- bulk-asynchronous tile loads (sm_90+ cp.async.bulk, the 1-D form of TMA; SASS: UBLKCP + SYNCS) -----------------
+// A pass after the first reads its tile as two contiguous ranges (4096 keys, 4096 row numbers).  One thread hands both
+// to the copy engine as soon as it knows the tile — before the CTA has even zeroed its histograms — and the engine
+// lands them in the staging arrays the scatter will later overwrite; the threads then read their 16 keys and row
+// numbers with conflict-free shared loads instead of 32 global loads each.
+#ifndef B200_SORT_TMA
+#define B200_SORT_TMA 1
+#endif
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+               "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+// false if the bytes never arrived (never hang the GPU: the caller flags the context)
+__device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  for (uint32_t spins = 0; spins < (1u << 24); ++spins) {
+    uint32_t ok;
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok)
+                 : "r"(addr), "r"(parity)
+                 : "memory");
+    if (ok) return true;
+  }
+  return false;
+}
+
 template <typename KeyT>
 struct PassSmem {
   KeyT keys[kTile];
@@ -277,6 +312,7 @@ struct PassSmem {
   uint32_t bin_delta[kBinStride];
   uint32_t warp_sums[kWarps];
   uint32_t tile;
+  uint64_t mbar;   // completion barrier of the tile's bulk loads
 };
 
 // kFull: the tile has 4096 rows.  (NaN / null rows are no business of the passes: they carry the all-ones key and
@@ -351,6 +387,11 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
 #pragma unroll
       for (int i = 0; i < kItems; ++i)
         key[i] = (kFull || wbase + 32 * i < tile_items) ? KeyT(p.keys_in[tile_row0 + wbase + 32 * i] >> word_shift) : KeyT(0);
+    } else if (kFull && B200_SORT_TMA) {
+      // the tile was requested by the kernel's prologue: wait for the copy engine, read from the staging arrays
+      if (!mbar_wait(&s.mbar, 0)) atomicExch(p.err, 3u);
+#pragma unroll
+      for (int i = 0; i < kItems; ++i) key[i] = s.keys[wbase + 32 * i];
     } else {
 #pragma unroll
       for (int i = 0; i < kItems; ++i) key[i] = (kFull || wbase + 32 * i < tile_items) ? keys_src[tile_row0 + wbase + 32 * i] : KeyT(0);
@@ -401,6 +442,7 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
   for (int i = 0; i < kItems; ++i) {
     const int local = wbase + 32 * i;
     if (info.first && !p.pay_in) pay[i] = uint32_t(tile_row0 + local);
+    else if (kFull && B200_SORT_TMA && !info.first) pay[i] = s.pay[local];
     else pay[i] = (kFull || local < tile_items) ? (info.first ? p.pay_in : pays_src)[tile_row0 + local] : 0u;
   }
   __syncthreads();
@@ -541,8 +583,19 @@ __global__ void __launch_bounds__(kThreads, kNarrow ? B200_SORT_NARROW_MINBLOCKS
   extern __shared__ __align__(16) unsigned char smem_raw[];
   using Smem = PassSmem<typename std::conditional<kNarrow, uint32_t, uint64_t>::type>;
   Smem& s = *reinterpret_cast<Smem*>(smem_raw);
+  using KeyT = typename std::conditional<kNarrow, uint32_t, uint64_t>::type;
   const int t = threadIdx.x;
-  if (t == 0) s.tile = atomicAdd(p.counters + d, 1u);
+  if (t == 0) {
+    const uint32_t tk = atomicAdd(p.counters + d, 1u);
+    s.tile = tk;
+    if (B200_SORT_TMA && !info.first && (int64_t(tk) + 1) * kTile <= p.n) {
+      // a full tile of a later pass: both ranges go to the copy engine now
+      mbar_init(&s.mbar, 1);
+      mbar_expect_tx(&s.mbar, uint32_t(kTile * (sizeof(KeyT) + 4)));
+      bulk_load(s.keys, reinterpret_cast<const KeyT*>(p.keys[info.src]) + size_t(tk) * kTile, uint32_t(kTile * sizeof(KeyT)), &s.mbar);
+      bulk_load(s.pay, p.pays[info.src] + size_t(tk) * kTile, uint32_t(kTile * 4), &s.mbar);
+    }
+  }
   for (int i = t; i < kWarps * kBinStride / 4; i += kThreads) reinterpret_cast<uint4*>(&s.whist[0][0])[i] = make_uint4(0, 0, 0, 0);
   __syncthreads();
   const int64_t tile = s.tile;

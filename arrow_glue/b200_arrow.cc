@@ -1179,7 +1179,7 @@ Status ExportFromDevice(const ArrayData& device_data, struct ArrowArray* out, st
 
 Result<std::shared_ptr<Buffer>> AllocatePinned(int64_t nbytes, int device) {
   ARROW_ASSIGN_OR_RAISE(auto buf, ::arrow::cuda::AllocateCudaHostBuffer(device, std::max<int64_t>(nbytes, 64)));
-  return SliceBuffer(std::shared_ptr<Buffer>(std::move(buf)), 0, nbytes);
+  return SliceMutableBuffer(std::shared_ptr<Buffer>(std::move(buf)), 0, nbytes);
 }
 
 Result<std::unique_ptr<internal::Grouper>> MakeGrouper(const std::vector<ValueDescr>& descrs, ExecContext*, int device) {

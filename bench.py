@@ -400,6 +400,7 @@ class Q1WL(Workload):
         ship, rf, ls, qty, price, disc = host_cols
         mask = Column.from_numpy(ship.values() <= compute.Q1_SHIPDATE_CUTOFF)
         f = [Column.from_numpy(oracle.filter(c, mask, 0, kind=kind).values().copy()) for c in (rf, ls, qty, price, disc)]
+        f.append(Column.from_numpy(f[3].values() * (1.0 - f[4].values())))   # disc_price: two IEEE operations, like multiply / subtract
         specs = compute.q1_aggregates()
         return oracle.groupby([f[0], f[1]], [a for _, a in specs], [f[2 + i] for i, _ in specs], kind=kind, max_groups=8)
 
