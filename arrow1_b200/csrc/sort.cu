@@ -268,12 +268,16 @@ __device__ __forceinline__ unsigned match_bit(unsigned m, uint32_t bin, uint32_t
 }
 
 // ---- bulk-asynchronous tile loads (sm_90+ cp.async.bulk, the 1-D form of TMA; SASS: UBLKCP + SYNCS) -----------------
-// A pass after the first reads its tile as two contiguous ranges (4096 keys, 4096 row numbers).  One thread hands both
-// to the copy engine as soon as it knows the tile — before the CTA has even zeroed its histograms — and the engine
-// lands them in the staging arrays the scatter will later overwrite; the threads then read their 16 keys and row
-// numbers with conflict-free shared loads instead of 32 global loads each.
+// A pass after the first reads its tile as two contiguous ranges (4096 keys, 4096 row numbers).  With B200_SORT_TMA one
+// thread hands both to the copy engine as soon as it knows the tile — before the CTA has even zeroed its histograms —
+// and the engine lands them in the staging arrays the scatter will later overwrite; the threads then read their 16
+// keys and row numbers with conflict-free shared loads instead of 32 global loads each.
+// MEASURED AND LEFT OFF (round 2, profiles/r02_sort_variants.txt): 5.89 ms per 100 M int64 rows against 5.60 ms with
+// the per-thread LDGs.  A CTA handles one tile, so nothing is prefetched: the bulk copy only changes who asks for the
+// bytes, makes all 256 threads wait for the whole 48 KB instead of each for its own 32 requests, and adds the shared
+// loads.  The build keeps it behind the macro (-DB200_SORT_TMA=1) for the persistent, double-buffered form.
 #ifndef B200_SORT_TMA
-#define B200_SORT_TMA 1
+#define B200_SORT_TMA 0
 #endif
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {

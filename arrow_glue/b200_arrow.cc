@@ -57,6 +57,9 @@ struct DeviceState {
   std::mutex pool_mutex;
   std::multimap<int64_t, std::shared_ptr<::arrow::cuda::CudaBuffer>> pool;
   int64_t pool_bytes = 0;
+  // pinned host blocks of results that went out of scope (cuMemHostAlloc of an 800 MB result costs ~0.3 s)
+  std::multimap<int64_t, std::shared_ptr<::arrow::cuda::CudaHostBuffer>> host_pool;
+  int64_t host_pool_bytes = 0;
   // ingest / egress: a copy stream and two pinned staging blocks for pageable host buffers
   CUstream copy_stream = nullptr;
   void* staging[2] = {nullptr, nullptr};
@@ -65,6 +68,18 @@ struct DeviceState {
 
 constexpr int64_t kPoolLimitBytes = int64_t(48) << 30;   // idle bytes kept per device
 constexpr int64_t kStagingBytes = int64_t(32) << 20;
+constexpr int64_t kHostPoolLimitBytes = int64_t(8) << 30;
+
+// A pinned host buffer over a pooled block (see PooledCudaBuffer)
+class PooledHostBuffer : public MutableBuffer {
+ public:
+  PooledHostBuffer(struct DeviceState* dev, std::shared_ptr<::arrow::cuda::CudaHostBuffer> block, int64_t size);
+  ~PooledHostBuffer() override;
+
+ private:
+  struct DeviceState* dev_;
+  std::shared_ptr<::arrow::cuda::CudaHostBuffer> block_;
+};
 
 // A CudaBuffer over a pooled block: when the last reference goes, the block returns to its device's pool.
 class PooledCudaBuffer : public ::arrow::cuda::CudaBuffer {
@@ -114,6 +129,35 @@ Result<DeviceState*> GetDevice(int device) {
     const int _code = (expr);                                \
     if (_code != B200_OK) return FromB200((dev)->ctx, _code); \
   } while (0)
+
+PooledHostBuffer::PooledHostBuffer(DeviceState* dev, std::shared_ptr<::arrow::cuda::CudaHostBuffer> block, int64_t size)
+    : MutableBuffer(block->mutable_data(), size), dev_(dev), block_(std::move(block)) {}
+PooledHostBuffer::~PooledHostBuffer() {
+  std::lock_guard<std::mutex> lock(dev_->pool_mutex);
+  if (dev_->host_pool_bytes + block_->size() <= kHostPoolLimitBytes) {
+    dev_->host_pool_bytes += block_->size();
+    dev_->host_pool.emplace(block_->size(), std::move(block_));
+  }
+}
+
+Result<std::shared_ptr<Buffer>> AllocatePinnedPooled(DeviceState* dev, int64_t nbytes) {
+  const int64_t padded = ((nbytes < 1 ? 1 : nbytes) + 63) / 64 * 64;
+  std::shared_ptr<::arrow::cuda::CudaHostBuffer> block;
+  {
+    std::lock_guard<std::mutex> lock(dev->pool_mutex);
+    auto it = dev->host_pool.lower_bound(padded);
+    if (it != dev->host_pool.end() && it->first <= padded + padded / 4 + (int64_t(1) << 20)) {
+      block = std::move(it->second);
+      dev->host_pool_bytes -= it->first;
+      dev->host_pool.erase(it);
+    }
+  }
+  if (!block) {
+    const int64_t cap = padded < (int64_t(1) << 20) ? padded : (padded + (int64_t(2) << 20) - 1) / (int64_t(2) << 20) * (int64_t(2) << 20);
+    ARROW_ASSIGN_OR_RAISE(block, ::arrow::cuda::AllocateCudaHostBuffer(dev->arrow_ctx->device_number(), cap));
+  }
+  return std::static_pointer_cast<Buffer>(std::make_shared<PooledHostBuffer>(dev, std::move(block), nbytes));
+}
 
 // Device allocation through the reference's own allocator; zero-filled when asked (bitmaps must
 // come back zero-padded, compute/kernel.cc:51-59).  cuMemAlloc rejects 0 bytes, and the C ABI
@@ -1142,9 +1186,9 @@ Result<std::shared_ptr<ArrayData>> MoveArrayData(DeviceState* dev, const ArrayDa
       buf = std::move(dbuf);
     } else {
       if (buf->is_cpu()) continue;
-      ARROW_ASSIGN_OR_RAISE(auto hbuf, ::arrow::cuda::AllocateCudaHostBuffer(dev->arrow_ctx->device_number(), std::max<int64_t>(buf->size(), 64)));
+      ARROW_ASSIGN_OR_RAISE(auto hbuf, AllocatePinnedPooled(dev, buf->size()));
       RETURN_NOT_OK(CopyStaged(dev, false, buf->address(), hbuf->mutable_data(), buf->size()));
-      buf = SliceBuffer(std::shared_ptr<Buffer>(std::move(hbuf)), 0, buf->size());
+      buf = std::move(hbuf);
     }
   }
   for (auto& child : out->child_data) { ARROW_ASSIGN_OR_RAISE(child, MoveArrayData(dev, *child, to_device)); }
@@ -1178,8 +1222,8 @@ Status ExportFromDevice(const ArrayData& device_data, struct ArrowArray* out, st
 }
 
 Result<std::shared_ptr<Buffer>> AllocatePinned(int64_t nbytes, int device) {
-  ARROW_ASSIGN_OR_RAISE(auto buf, ::arrow::cuda::AllocateCudaHostBuffer(device, std::max<int64_t>(nbytes, 64)));
-  return SliceMutableBuffer(std::shared_ptr<Buffer>(std::move(buf)), 0, nbytes);
+  ARROW_ASSIGN_OR_RAISE(DeviceState * dev, GetDevice(device));
+  return AllocatePinnedPooled(dev, nbytes);
 }
 
 Result<std::unique_ptr<internal::Grouper>> MakeGrouper(const std::vector<ValueDescr>& descrs, ExecContext*, int device) {
