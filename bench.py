@@ -754,6 +754,22 @@ def measure_e2e(wl, ctx, rank, world, local, steps, pipelined=True):
     return e2e
 
 
+def glue_timing(name, rows, steps=5):
+    """The same workload through the reference's own API — compute::CallFunction / cuda::GroupBy over the CUDA
+    FunctionRegistry of arrow_glue (C++), device-resident and host-to-host — timed by arrow_glue/bench_glue, a binary
+    built where the reference's headers are and shipped prebuilt.  None when the binary or the workload is missing."""
+    exe = os.path.join(ROOT, "arrow_glue", "bench_glue")
+    if not os.path.exists(exe) or name not in ("sort_i64", "filter", "groupby_c3"):
+        return None
+    try:
+        r = subprocess.run([exe, name, str(rows), str(steps)], capture_output=True, text=True, timeout=600)
+        if r.returncode != 0:
+            return {"error": (r.stderr or r.stdout)[-300:]}
+        return json.loads(r.stdout.strip().splitlines()[-1])
+    except Exception as ex:
+        return {"error": repr(ex)[:300]}
+
+
 def gpu_arm(args):
     import torch
     if not torch.cuda.is_available():
@@ -877,6 +893,10 @@ def gpu_arm(args):
                     except Exception as ex:
                         extras[name]["e2e"] = {"error": repr(ex)[:300]}
                     torch.cuda.empty_cache()
+                if not args.no_e2e:
+                    g = glue_timing(name, min(w2.n, 200_000_000), 3)
+                    if g is not None:
+                        extras[name]["glue"] = g
                 if not args.no_cpu:
                     try:
                         r = run_cpu(w2, 1, 0 if w2.n > 50_000_000 else 1, host_threads())
@@ -906,6 +926,10 @@ def gpu_arm(args):
             "kernel_ms_per_step": {k: v[0] / kt_steps for k, v in kt.items() if v[1]},
             "kernel_timing": "per-launch CUDA events of a second pass of %d steps (the hook is off during the timed steps)" % kt_steps,
         }
+        if world == 1 and not args.no_e2e:
+            g = glue_timing(wl.name, min(wl.n, 200_000_000))
+            if g is not None:
+                line["glue"] = g
         if self_check is not None:
             line["self_check"] = self_check
         if extras:
