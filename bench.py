@@ -138,9 +138,10 @@ class SortWL(Workload):
         return self.n * 8
 
     def alg_bytes_per_launch(self, launches_per_step):
-        # 8 live digit passes of a 64-bit column (DESIGN.md "Sort"): first reads 8.125 B/row and
-        # writes key+row number (12), six middle passes read 12 write 12, the last reads 12 writes 8
-        total = self.n * (8.125 + 12 + 6 * 24 + 12 + 8)
+        # 8 live digit passes of a 64-bit column (DESIGN.md "Sort"): the first reads 8.125 B/row and writes key + row
+        # number (12); passes 1, 2 read and write 12; pass 3 reads 12 and writes the upper key word + row (8); passes
+        # 4..6 read and write 8; the last reads 8 and writes the 8-byte index
+        total = self.n * (8.125 + 12 + 2 * 24 + 12 + 8 + 3 * 16 + 8 + 8)
         return total / max(launches_per_step, 1)
 
     def prepare(self, ctx, cols_):
