@@ -718,6 +718,19 @@ def make_groupings(ctx: Context, ids: torch.Tensor, num_groups: int):
     return offsets, indices[:n]
 
 
+def dictionary_indices(ctx: Context, ids: torch.Tensor, null_group: int = -1):
+    """== DictEncodeAction (vector_hash.cc:165-226): uint32 group ids (int32-typed device tensor) -> (int32 indices,
+    validity bitmap bytes or None).  null_group >= 0: DictionaryEncodeOptions::MASK with a null in the column."""
+    n = ids.numel()
+    dev = "cuda:%d" % ctx.device
+    out = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    validity = torch.zeros(((n + 31) // 32) * 4 + 64, dtype=torch.uint8, device=dev) if null_group >= 0 else None
+    ctx.check(lib().b200_dictionary_indices(ctx._h, C.c_void_p(ids.data_ptr()), C.c_int64(n), C.c_int64(null_group),
+                                            C.c_void_p(out.data_ptr()),
+                                            C.c_void_p(validity.data_ptr()) if validity is not None else None))
+    return out[:n], validity
+
+
 def group_by(ctx: Context, keys: Sequence[Column], aggs: Sequence[AggSpec], args: Sequence[Column],
              expected_groups: int = 0, row_base: int = 0, selection: Optional[Column] = None,
              options: Optional[dict] = None) -> GroupByOutput:

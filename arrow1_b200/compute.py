@@ -446,3 +446,30 @@ def ValueCounts(values: Column, ctx: Optional[capi.Context] = None):
     a = out.aggs[0][0].data[: G * 8].view(torch.int64)
     b = out.aggs[1][0].data[: G * 8].view(torch.int64)
     return out.keys[0], a + b
+
+
+def DictionaryEncode(values: Column, encode_nulls: bool = False, ctx: Optional[capi.Context] = None):
+    """== "dictionary_encode" (vector_hash.cc:165-226, 764-779) for a fixed-width device column: (int32 indices
+    Column, dictionary Column).  The dictionary lists the distinct values in first-occurrence order.
+    encode_nulls False == DictionaryEncodeOptions::MASK (the default upstream): a null row gets a null index and the
+    null has no dictionary entry; True == ENCODE: the null is a dictionary entry like any value."""
+    ctx = ctx or default_context()
+    from . import columns as cols
+    gb = capi.GroupBy(ctx, [values.type], [], [], 0)
+    try:
+        ids = gb.grouper_consume([values])
+        uniq = gb.finalize().keys[0]
+    finally:
+        gb.close()
+    null_group, dictionary = -1, uniq
+    if not encode_nulls and uniq.null_count != 0:
+        # the one null entry of the dictionary: where is it (G bits to the host), and the dictionary without it
+        G = uniq.length
+        bits = cols.unpack_bits(uniq.validity[: (G + 7) // 8].cpu().numpy(), G)
+        null_group = int(np.flatnonzero(~bits)[0])
+        dictionary = capi.filter(ctx, uniq, Column(cols.BOOL, uniq.validity, None, G, 0, 0), DROP)
+    idx, validity = capi.dictionary_indices(ctx, ids, null_group)
+    n = values.length
+    nulls = 0 if validity is None else (values.null_count if values.null_count >= 0 else -1)
+    return Column(cols.INT32, idx.view(torch.uint8), validity, n, 0, nulls), dictionary
+

@@ -2136,6 +2136,12 @@ __global__ void gb_collect_kernel(GbTable t, int stride, uint64_t* first_rows, u
 }
 
 // the groups of a pending image list (see b200_groupby::pending): every image is a group
+// first rows in output order through the order finalize left behind
+__global__ void gb_first_rows_kernel(const char* slots, int stride, const uint64_t* order, uint32_t n, uint64_t* out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = reinterpret_cast<const uint64_t*>(slots + order[i] * uint64_t(stride))[1];
+}
+
 __global__ void gb_collect_images_kernel(const char* images, int stride, uint32_t n, uint64_t* first_rows, uint64_t* slot_idx) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) {
@@ -2536,6 +2542,11 @@ struct b200_groupby {
   uint32_t* wcounters = nullptr;
   void* wtmp = nullptr;
   size_t wtmp_bytes = 0;
+  // the group order finalize computed (slot / image index per output rank, inside `tmp`): b200_groupby_first_rows right
+  // after a finalize gathers through it instead of collecting and sorting once more; dropped by any change of state
+  const uint64_t* order_cache = nullptr;
+  const char* order_slots = nullptr;
+  uint32_t order_n = 0;
   // upper bound of every global row number consumed so far (2^64-1 once unknown): first rows below 2^32 are ranked
   // by a sort that carries 32-bit keys
   uint64_t row_bound = 0;
@@ -2558,6 +2569,7 @@ int domain_of(int t) {
 
 int gb_reserve_tmp(b200_groupby* gb, size_t bytes) {
   b200_ctx* ctx = gb->ctx;
+  gb->order_cache = nullptr;   // whoever asks for scratch is about to overwrite it
   if (bytes <= gb->tmp_bytes) return B200_OK;
   if (gb->tmp) {
     b200_dev_free(ctx, gb->tmp);
@@ -2604,6 +2616,7 @@ uint64_t initial_cap(const b200_groupby* gb) { return pow2_at_least(gb->expected
 
 int grow_table(b200_groupby* gb, uint64_t min_cap) {
   b200_ctx* ctx = gb->ctx;
+  gb->order_cache = nullptr;
   if (!gb->table.slots) return alloc_table(gb, std::max(pow2_at_least(min_cap), initial_cap(gb)), &gb->table);
   const uint64_t new_cap = pow2_at_least(min_cap);
   if (new_cap <= gb->table.cap) return B200_OK;
@@ -2634,6 +2647,7 @@ int ensure_table(b200_groupby* gb) { return gb->table.slots ? B200_OK : alloc_ta
 // the table exists and holds every group (pending images folded in)
 int materialize(b200_groupby* gb) {
   b200_ctx* ctx = gb->ctx;
+  if (gb->pending) gb->order_cache = nullptr;
   B200_RETURN_NOT_OK(ensure_table(gb));
   if (!gb->pending) return B200_OK;
   const uint32_t n = gb->pending_n;
@@ -3379,6 +3393,7 @@ static int groupby_consume_impl(b200_groupby* gb, const b200_col* keys, const b2
   b200_ctx* ctx = gb->ctx;
   if (!keys || (gb->schema.n_aggs > 0 && !args)) return b200_fail(ctx, B200_INVALID, "groupby_consume: null argument");
   if (gb->dense_used) return b200_fail(ctx, B200_INVALID, "groupby: handle already used through b200_hash_agg_consume");
+  gb->order_cache = nullptr;
   B200_NARROW_KEYS(gb, keys, select);
   GbArgs a;
   memset(&a, 0, sizeof(a));
@@ -3550,6 +3565,7 @@ int b200_groupby_consume_fused(b200_groupby* gb, const b200_col* keys, const b20
   const GbSchema& s = gb->schema;
   if (!keys || (s.n_aggs > 0 && !args)) return b200_fail(ctx, B200_INVALID, "groupby_consume_fused: null argument");
   if (gb->dense_used) return b200_fail(ctx, B200_INVALID, "groupby: handle already used through b200_hash_agg_consume");
+  gb->order_cache = nullptr;
   const int64_t n = keys[0].length;
   for (int j = 0; j < s.n_aggs; ++j) {
     const b200_fused_arg& g = args[j];
@@ -3725,6 +3741,36 @@ int b200_make_groupings(b200_ctx* ctx, const uint32_t* ids, int64_t length, uint
   return B200_OK;
 }
 
+// ---- dictionary_encode's indices (DictEncodeAction, vector_hash.cc:165-226) from the Grouper's ids --------------------
+// DictionaryEncodeOptions::MASK: the null key has no dictionary entry: its rows become null indices (value 0, as
+// Int32Builder::UnsafeAppendNull leaves them) and every id handed out after the null group's shifts down by one.
+namespace {
+__global__ void dict_indices_kernel(const uint32_t* ids, int64_t n, uint32_t null_group, int32_t* out, uint32_t* validity) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  const bool in = i < n;
+  const uint32_t id = in ? ids[i] : 0u;
+  const bool valid = in && id != null_group;
+  if (in) out[i] = valid ? int32_t(id - (id > null_group ? 1u : 0u)) : 0;
+  const unsigned word = __ballot_sync(0xffffffffu, valid);
+  if (validity && (threadIdx.x & 31) == 0 && in) validity[i >> 5] = word;
+}
+}  // namespace
+
+int b200_dictionary_indices(b200_ctx* ctx, const uint32_t* ids, int64_t length, int64_t null_group, int32_t* out_indices,
+                            void* out_validity) {
+  B200_ENTER(ctx);
+  if (!ctx) return B200_INVALID;
+  if (length < 0) return b200_fail(ctx, B200_INVALID, "dictionary_indices: negative length");
+  if (length == 0) return B200_OK;
+  if (!ids || !out_indices) return b200_fail(ctx, B200_INVALID, "dictionary_indices: null argument");
+  if (null_group >= 0 && !out_validity) return b200_fail(ctx, B200_INVALID, "dictionary_indices: a null group needs a validity bitmap");
+  if (null_group > int64_t(0xFFFFFFFEu)) return b200_fail(ctx, B200_INVALID, "dictionary_indices: null group out of range");
+  dict_indices_kernel<<<unsigned((length + 255) / 256), 256, 0, ctx->stream>>>(
+      ids, length, null_group < 0 ? 0xFFFFFFFFu : uint32_t(null_group), out_indices, reinterpret_cast<uint32_t*>(out_validity));
+  B200_LAUNCHED(ctx);
+  return B200_OK;
+}
+
 // ---- hash repartitioning -------------------------------------------------------------------------
 int b200_partition_scratch_bytes(int64_t length, size_t* out_bytes) {
   if (!out_bytes || length < 0) return B200_INVALID;
@@ -3836,6 +3882,7 @@ int b200_grouper_consume(b200_groupby* gb, const b200_col* keys, uint32_t* out_i
   if (!gb) return B200_INVALID;
   b200_ctx* ctx = gb->ctx;
   if (!keys) return b200_fail(ctx, B200_INVALID, "grouper_consume: null keys");
+  gb->order_cache = nullptr;
   B200_NARROW_KEYS(gb, keys, nullptr);
   GbArgs a;
   memset(&a, 0, sizeof(a));
@@ -4019,6 +4066,14 @@ int b200_groupby_first_rows(b200_groupby* gb, uint64_t* out_first_rows) {
   if (!gb) return B200_INVALID;
   b200_ctx* ctx = gb->ctx;
   if (gb->dense_used) return b200_fail(ctx, B200_INVALID, "groupby_first_rows: dense handle has no row order");
+  if (gb->order_cache && out_first_rows) {   // finalize has just ranked the groups
+    if (gb->order_n) {
+      gb_first_rows_kernel<<<(gb->order_n + 255) / 256, 256, 0, ctx->stream>>>(gb->order_slots, gb->schema.stride, gb->order_cache,
+                                                                                gb->order_n, out_first_rows);
+      B200_LAUNCHED(ctx);
+    }
+    return B200_OK;
+  }
   uint64_t *first_rows, *slot_idx;
   size_t sort_bytes = 0;
   uint32_t c[4];
@@ -4059,6 +4114,7 @@ int b200_groupby_import(b200_groupby* gb, const void* state, uint32_t n_slots) {
   b200_ctx* ctx = gb->ctx;
   if (n_slots == 0) return B200_OK;
   if (!state) return b200_fail(ctx, B200_INVALID, "groupby_import: null state");
+  gb->order_cache = nullptr;
   if (gb->wide) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby_import: keys wider than 64 packed bits");
   gb->row_bound = ~uint64_t(0);
   B200_RETURN_NOT_OK(materialize(gb));
@@ -4077,6 +4133,7 @@ int b200_groupby_merge(b200_groupby* dst, b200_groupby* src) {
   b200_ctx* ctx = dst->ctx;
   if (memcmp(&dst->schema, &src->schema, sizeof(GbSchema)) != 0) return b200_fail(ctx, B200_TYPE_ERROR, "groupby_merge: schemas differ");
   if (dst->ctx != src->ctx) return b200_fail(ctx, B200_INVALID, "groupby_merge: handles belong to different contexts");
+  dst->order_cache = nullptr;
   if (dst->wide || src->wide) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "groupby_merge: keys wider than 64 packed bits");
   dst->row_bound = std::max(dst->row_bound, src->row_bound);
   B200_RETURN_NOT_OK(materialize(dst));
@@ -4133,6 +4190,9 @@ int b200_groupby_finalize(b200_groupby* gb, b200_out_col* out_aggs, b200_out_col
       e.t.cap = ~uint64_t(0) - 16;   // cap and cap + 1 (the special slots) match no image index
     }
     e.order = sorted;
+    gb->order_cache = sorted;
+    gb->order_slots = e.t.slots;
+    gb->order_n = G;
   }
   e.n_groups = G;
   B200_CUDA(ctx, cudaMemsetAsync(e.null_counts, 0, (kMaxKeys + 2 * kMaxAggs) * sizeof(uint32_t), ctx->stream));

@@ -412,6 +412,16 @@ B200_API int b200_grouper_consume(b200_groupby* gb, const b200_col* keys, uint32
 B200_API int b200_make_groupings_scratch_bytes(int64_t length, size_t* out_bytes);
 B200_API int b200_make_groupings(b200_ctx* ctx, const uint32_t* ids, int64_t length, uint32_t num_groups,
                                  int32_t* out_offsets, int32_t* out_indices, void* scratch, size_t scratch_bytes);
+/* == DictEncodeAction (compute/kernels/vector_hash.cc:165-226), the indices half of "dictionary_encode": the
+ * uint32 group ids b200_grouper_consume wrote for one key column -> int32 dictionary indices.
+ * null_group < 0: the column has no null, or DictionaryEncodeOptions::ENCODE (the null keeps its dictionary entry):
+ *   indices = ids, no validity written (out_validity may be NULL).
+ * null_group >= 0 (DictionaryEncodeOptions::MASK, the default): the id of the null key's group, which has NO
+ *   dictionary entry: its rows get a null index (value 0), ids above it shift down by one, and out_validity
+ *   (DEVICE, ceil(length / 32) whole 32-bit words) receives the index validity.  The dictionary is the handle's
+ *   key column (b200_groupby_finalize) with entry null_group removed.  Asynchronous on the context's stream. */
+B200_API int b200_dictionary_indices(b200_ctx* ctx, const uint32_t* ids, int64_t length, int64_t null_group,
+                                     int32_t* out_indices, void* out_validity);
 /* == HashAggregateKernel::consume with the reference signature (arg, uint32 ids, num_groups)
  * (hash_aggregate.cc:783-789): accumulates aggregate `agg_index` of `gb` by dense group id. */
 B200_API int b200_hash_agg_consume(b200_groupby* gb, int agg_index, const b200_col* arg,

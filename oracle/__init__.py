@@ -288,3 +288,18 @@ def value_counts(values: Column, want_counts: bool = True):
                                                            counts.ctypes.data_as(C.c_void_p) if want_counts else None, C.byref(out_n)))
     g = out_n.value
     return _decode(values.type, d, v, g), (counts[:g].copy() if want_counts else None)
+
+
+def dictionary_encode(values: Column, encode_nulls: bool = False):
+    """"dictionary_encode" of the reference (vector_hash.cc:165-226): (indices int32, index validity bool,
+    (dictionary values, valid))."""
+    n = values.length
+    idx = np.zeros(max(n, 1), dtype=np.int32)
+    valid = np.zeros(max(n, 1), dtype=np.uint8)
+    oc, d, v = _out_col(values.type, max(n, 1))
+    out_n = C.c_int64(0)
+    _check("reference", _fn("reference", "dictionary_encode")(C.byref(values.desc()), C.c_int(1 if encode_nulls else 0),
+                                                                idx.ctypes.data_as(C.c_void_p), valid.ctypes.data_as(C.c_void_p),
+                                                                C.byref(oc), C.byref(out_n)))
+    return idx[:n].copy(), valid[:n].astype(bool), _decode(values.type, d, v, out_n.value)
+

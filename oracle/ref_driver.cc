@@ -384,4 +384,26 @@ B200_API int ref_value_counts(const b200_col* values, b200_out_col* out_values, 
   return 0;
 }
 
+// "dictionary_encode" (compute/kernels/vector_hash.cc:165-226, 648-668) on one fixed-width column.
+// encode_nulls == 0: DictionaryEncodeOptions::MASK (null rows -> null indices, no null in the dictionary); != 0: ENCODE.
+// out_indices: int32 per row; out_index_valid: one byte per row; out_dict: the dictionary; out_n: its length.
+B200_API int ref_dictionary_encode(const b200_col* values, int encode_nulls, int32_t* out_indices, uint8_t* out_index_valid,
+                                   b200_out_col* out_dict, int64_t* out_n) {
+  compute::ExecContext ctx;
+  compute::DictionaryEncodeOptions opts(encode_nulls ? compute::DictionaryEncodeOptions::ENCODE
+                                                     : compute::DictionaryEncodeOptions::MASK);
+  auto res = compute::CallFunction("dictionary_encode", {Datum(Wrap(*values))}, &opts, &ctx);
+  if (!res.ok()) return Fail(res.status());
+  auto arr = res.ValueOrDie().array();
+  const int32_t* idx = arr->GetValues<int32_t>(1);
+  for (int64_t i = 0; i < arr->length; ++i) {
+    const bool valid = !arr->buffers[0] || BitUtil::GetBit(arr->buffers[0]->data(), arr->offset + i);
+    out_indices[i] = valid ? idx[i] : 0;
+    out_index_valid[i] = valid ? 1 : 0;
+  }
+  CopyOut(*arr->dictionary, out_dict);
+  *out_n = arr->dictionary->length;
+  return 0;
+}
+
 }  // extern "C"

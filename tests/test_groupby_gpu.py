@@ -445,6 +445,41 @@ def test_groupby_partitioned_path_streaming_selected_and_rows(ctx):
     assert_group_equal(finish(gb), want_sel, aggs, rtol=RTOL)
 
 
+@pytest.mark.parametrize("hp", [False, True])
+def test_groupby_first_rows_before_and_after_finalize(ctx, hp):
+    """b200_groupby_first_rows right after finalize reuses finalize's ranking; after further batches (or with no
+    finalize at all) it ranks the groups itself.  Either way: the first row of every group, ascending."""
+    from arrow1_b200 import capi
+    rng = np.random.default_rng(41)
+    n = 200_000
+    kv = rng.integers(0, 30_000, size=n).astype(np.int64) * 7919
+    arg = Column.from_numpy(rng.random(n))
+    aggs = [AggSpec(cols.HASH_SUM)]
+
+    def expect(upto, base):
+        _, first = np.unique(kv[:upto], return_index=True)
+        return np.sort(first).astype(np.uint64) + np.uint64(base)
+
+    gb = capi.GroupBy(ctx, [cols.INT64], aggs, [cols.DOUBLE], 30_000)
+    if hp:
+        for k, v_ in HP.items():
+            gb.set_option(k, v_)
+    dkey, darg = Column.from_numpy(kv).to_device(), arg.to_device()
+    half = n // 2
+    gb.consume([Column(dkey.type, dkey.data, None, half, 0, 0)], [Column(darg.type, darg.data, None, half, 0, 0)], row_base=1000)
+    np.testing.assert_array_equal(gb.first_rows().cpu().numpy().view(np.uint64), expect(half, 1000))   # no finalize yet
+    out = gb.finalize()
+    np.testing.assert_array_equal(gb.first_rows().cpu().numpy().view(np.uint64), expect(half, 1000))   # finalize's ranking
+    np.testing.assert_array_equal(out.keys[0].to_host().values(), kv[(expect(half, 1000) - np.uint64(1000)).astype(np.int64)])
+    gb.consume([Column(dkey.type, dkey.data, None, n - half, half, 0)], [Column(darg.type, darg.data, None, n - half, half, 0)],
+               row_base=1000 + half)
+    np.testing.assert_array_equal(gb.first_rows().cpu().numpy().view(np.uint64), expect(n, 1000))      # cache dropped
+    out = gb.finalize()
+    np.testing.assert_array_equal(gb.first_rows().cpu().numpy().view(np.uint64), expect(n, 1000))
+    np.testing.assert_array_equal(out.keys[0].to_host().values(), kv[(expect(n, 1000) - np.uint64(1000)).astype(np.int64)])
+    gb.close()
+
+
 # ---- keys wider than 64 packed bits / more than 4 key columns (FixedWidthKeyEncoder takes any, hash_aggregate.cc:142-196)
 @pytest.mark.parametrize("kts", [(cols.INT64, cols.INT64), (cols.INT64, cols.INT32, cols.UINT8),
                                  (cols.DOUBLE, cols.BOOL, cols.INT16, cols.UINT64, cols.FLOAT),
@@ -545,3 +580,25 @@ def test_unique_and_value_counts_match_reference(ctx, t):
         np.testing.assert_array_equal(hk.valid(), wvalid)
         np.testing.assert_array_equal(hk.values()[wvalid].view(np.uint8), wv[wvalid].view(np.uint8))
         np.testing.assert_array_equal(counts.cpu().numpy(), wc)
+
+
+@pytest.mark.parametrize("encode_nulls", [False, True])
+@pytest.mark.parametrize("t", [cols.BOOL, cols.UINT8, cols.INT32, cols.INT64, cols.DOUBLE])
+def test_dictionary_encode_matches_reference(ctx, t, encode_nulls):
+    """"dictionary_encode" (vector_hash.cc:165-226): indices, their validity and the dictionary, both
+    DictionaryEncodeOptions::NullEncodingBehavior modes; the null first met in the middle (ids behind it shift)."""
+    from arrow1_b200 import compute
+    if ORACLE != "reference":
+        pytest.skip("needs oracle/_ref")
+    rng = np.random.default_rng(160 + t)
+    for n, nulls in ((1, 0.0), (33, 0.2), (5000, 0.0), (200_000, 0.05)):
+        col = rand_column(rng, t, n, nulls, lo=0, hi=(1 if t == cols.BOOL else 300))
+        widx, wvalid, (dv, dvalid) = oracle.dictionary_encode(col, encode_nulls)
+        idx, dictionary = compute.DictionaryEncode(col.to_device(), encode_nulls, ctx)
+        hi, hd = idx.to_host(), dictionary.to_host()
+        np.testing.assert_array_equal(hi.valid(), wvalid)
+        np.testing.assert_array_equal(hi.values()[wvalid], widx[wvalid])
+        if not encode_nulls:
+            assert (hi.values()[~wvalid] == 0).all()
+        np.testing.assert_array_equal(hd.valid(), dvalid)
+        np.testing.assert_array_equal(hd.values()[dvalid].view(np.uint8), dv[dvalid].view(np.uint8))
