@@ -540,6 +540,11 @@ class GroupBy:
     def set_option(self, name: str, value: int):
         self.ctx.check(lib().b200_groupby_set_option(self._h, name.encode(), C.c_int64(value)))
 
+    def stat(self, name: str) -> int:
+        v = C.c_int64(0)
+        self.ctx.check(lib().b200_groupby_stat(self._h, name.encode(), C.byref(v)))
+        return int(v.value)
+
     def consume(self, keys: Sequence[Column], args: Sequence[Column], row_base: int = 0):
         self.ctx.check(lib().b200_groupby_consume(self._h, col_array(keys), col_array(args), C.c_uint64(row_base)))
 

@@ -467,7 +467,8 @@ def DictionaryEncode(values: Column, encode_nulls: bool = False, ctx: Optional[c
         G = uniq.length
         bits = cols.unpack_bits(uniq.validity[: (G + 7) // 8].cpu().numpy(), G)
         null_group = int(np.flatnonzero(~bits)[0])
-        dictionary = capi.filter(ctx, uniq, Column(cols.BOOL, uniq.validity, None, G, 0, 0), DROP)
+        kept = capi.filter(ctx, uniq, Column(cols.BOOL, uniq.validity, None, G, 0, 0), DROP).col
+        dictionary = Column(uniq.type, kept.data, None, kept.length, 0, 0)   # every entry left is valid
     idx, validity = capi.dictionary_indices(ctx, ids, null_group)
     n = values.length
     nulls = 0 if validity is None else (values.null_count if values.null_count >= 0 else -1)

@@ -2544,6 +2544,7 @@ struct b200_groupby {
   size_t wtmp_bytes = 0;
   // the group order finalize computed (slot / image index per output rank, inside `tmp`): b200_groupby_first_rows right
   // after a finalize gathers through it instead of collecting and sorting once more; dropped by any change of state
+  int64_t hp_calls = 0, hp_alloc_failures = 0, hp_span_refusals = 0;   // b200_groupby_stat
   const uint64_t* order_cache = nullptr;
   const char* order_slots = nullptr;
   uint32_t order_n = 0;
@@ -2743,6 +2744,7 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
     gb->hp_bytes = 0;
     if (b200_dev_alloc(ctx, &gb->hp_tmp, need) != B200_OK) {
       ctx->error.clear();
+      ++gb->hp_alloc_failures;
       return B200_OK;   // not enough memory for the partition buffers: the generic path needs none
     }
     gb->hp_bytes = need;
@@ -2781,7 +2783,10 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
     B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 24, mm, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
     B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const uint64_t lo = uint64_t(ctx->host_words[24]), hi = uint64_t(ctx->host_words[25]);
-    if (hi - lo >= (uint64_t(1) << 31)) return B200_OK;
+    if (hi - lo >= (uint64_t(1) << 31)) {
+      ++gb->hp_span_refusals;
+      return B200_OK;
+    }
     ord_base = lo;
     a.row_base = lo;   // (unused by the kernels that read row_ids) the aggregation kernel adds it to the smallest offset
   }
@@ -2869,6 +2874,7 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
   const uint32_t n_images = std::min(reinterpret_cast<const uint32_t*>(ctx->host_words + 16)[6], image_cap);
   const uint32_t n_items = reinterpret_cast<const uint32_t*>(ctx->host_words + 16)[7];
   *handled = true;
+  ++gb->hp_calls;
   if (gb->groups == 0 && c[1] == 0 && n_items <= parts && n_images > 0) {
     // first groups of the handle, every row placed, no partition cut into several work items: the images are the
     // groups, each key once.  They stay where they are until something needs the table.
@@ -3362,6 +3368,15 @@ int b200_groupby_set_option(b200_groupby* gb, const char* name, int64_t value) {
   if (!strcmp(name, "hp_min_rows")) gb->hp_min_rows = value;
   else if (!strcmp(name, "hp_min_groups")) gb->hp_min_groups = value;
   else return b200_fail(gb->ctx, B200_KEY_ERROR, "groupby: no option named %s", name);
+  return B200_OK;
+}
+
+int b200_groupby_stat(b200_groupby* gb, const char* name, int64_t* out) {
+  if (!gb || !name || !out) return B200_INVALID;
+  if (!strcmp(name, "partitioned_calls")) *out = gb->hp_calls;
+  else if (!strcmp(name, "partitioned_alloc_failures")) *out = gb->hp_alloc_failures;
+  else if (!strcmp(name, "partitioned_span_refusals")) *out = gb->hp_span_refusals;
+  else return b200_fail(gb->ctx, B200_KEY_ERROR, "groupby: no statistic named %s", name);
   return B200_OK;
 }
 

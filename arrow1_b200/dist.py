@@ -436,8 +436,9 @@ class ShardedGroups:
     output in local first-occurrence order) plus each group's global first row, which ranks the groups
     of all ranks into the reference's order (hash_aggregate.cc:391-403)."""
 
-    def __init__(self, out, first_rows):
+    def __init__(self, out, first_rows, stats=None):
         self.out, self.first_rows = out, first_rows
+        self.stats = stats or {}   # which way the local aggregation went (b200_groupby_stat)
 
     @property
     def num_groups(self):
@@ -501,7 +502,10 @@ def dist_group_by_repartition(ops, keys: Sequence[Column], aggs: Sequence[AggSpe
         rargs = [recv_cols[index[(id(c.data), id(c.validity), c.offset)]] for c in args]
         if total:
             gb.consume_rows(rkeys, rargs, rrows)
-        return ShardedGroups(gb.finalize(), gb.first_rows())
+        stats = {}
+        if hasattr(gb, "stat"):
+            stats = {k: gb.stat(k) for k in ("partitioned_calls", "partitioned_alloc_failures", "partitioned_span_refusals")}
+        return ShardedGroups(gb.finalize(), gb.first_rows(), stats)
     finally:
         gb.close()
 
@@ -618,7 +622,7 @@ def bench_self_check(ctx, wl, cols_, bufs):
         means = out.aggs[1][0].data[: G * 8].view(torch.float64)
         local = int(torch.round(sums / means).sum().item()) if G else 0
         return {"workload": wl.name, "rows_total": n_total, "groups_total": allsum(G),
-                "counts_add_up_to_rows": bool(allsum(local) == n_total)}
+                "counts_add_up_to_rows": bool(allsum(local) == n_total), "local_aggregation_rank0": dict(res.stats)}
     return {"workload": wl.name, "checked": False}
 
 

@@ -26,6 +26,7 @@
 #include "arrow/scalar.h"
 #include "arrow/table.h"
 #include "arrow/type.h"
+#include "arrow/util/bit_util.h"
 #include "arrow/util/checked_cast.h"
 #include "arrow/util/make_unique.h"
 
@@ -221,6 +222,29 @@ Result<int32_t> PhysicalType(const DataType& type) {
     default: break;
   }
   return Status::NotImplemented("bit width of ", type.ToString());
+}
+
+// group keys: fixed-width columns, and dictionary columns through their index column (DictionaryKeyEncoder,
+// hash_aggregate.cc:198-233: the indices are the key, the dictionary rides along)
+Result<int32_t> KeyPhysicalType(const DataType& type) {
+  if (type.id() == Type::DICTIONARY) return PhysicalType(*checked_cast<const DictionaryType&>(type).index_type());
+  if (type.id() != Type::BOOL && !is_primitive(type.id())) return Status::NotImplemented("Keys of type ", type.ToString());
+  return PhysicalType(type);
+}
+int KeyBitWidth(const DataType& type) {
+  if (type.id() == Type::DICTIONARY) return checked_cast<const FixedWidthType&>(*checked_cast<const DictionaryType&>(type).index_type()).bit_width();
+  return checked_cast<const FixedWidthType&>(type).bit_width();
+}
+// every batch of a dictionary key must carry the first batch's dictionary ("Unifying differing dictionaries" is
+// NotImplemented upstream too, hash_aggregate.cc:205-210); device dictionaries are compared by identity
+Status NoteKeyDictionary(const ArrayData& key, std::shared_ptr<ArrayData>* seen) {
+  if (key.type->id() != Type::DICTIONARY) return Status::OK();
+  if (!*seen) {
+    *seen = key.dictionary;
+  } else if (seen->get() != key.dictionary.get()) {
+    return Status::NotImplemented("Unifying differing dictionaries");
+  }
+  return Status::OK();
 }
 
 // logical b200_type: ordering and arithmetic depend on signedness / floating point
@@ -935,10 +959,10 @@ class CudaGrouper : public internal::Grouper {
     ARROW_ASSIGN_OR_RAISE(g->handle_.dev, GetDevice(device));
     for (const auto& d : descrs) {
       // GrouperImpl::Make: "Keys of type ..." (hash_aggregate.cc:325-352)
-      if (d.type->id() != Type::BOOL && !is_primitive(d.type->id())) return Status::NotImplemented("Keys of type ", d.type->ToString());
-      ARROW_ASSIGN_OR_RAISE(const int32_t t, PhysicalType(*d.type));
+      ARROW_ASSIGN_OR_RAISE(const int32_t t, KeyPhysicalType(*d.type));
       g->key_types_.push_back(t);
       g->types_.push_back(d.type);
+      g->dictionaries_.emplace_back();
     }
     std::lock_guard<std::mutex> lock(g->handle_.dev->mutex);
     B200_OK_OR_RAISE(g->handle_.dev, b200_groupby_create(g->handle_.dev->ctx, int(g->key_types_.size()), g->key_types_.data(), 0, nullptr, 0, &g->handle_.gb));
@@ -949,7 +973,10 @@ class CudaGrouper : public internal::Grouper {
     DeviceState* dev = handle_.dev;
     std::vector<b200_col> keys(batch.num_values());
     if (size_t(batch.num_values()) != key_types_.size()) return Status::Invalid("expected ", key_types_.size(), " key columns");
-    for (int k = 0; k < batch.num_values(); ++k) RETURN_NOT_OK(ToCol(*batch[k].array(), key_types_[k], &keys[k]));
+    for (int k = 0; k < batch.num_values(); ++k) {
+      RETURN_NOT_OK(NoteKeyDictionary(*batch[k].array(), &dictionaries_[k]));
+      RETURN_NOT_OK(ToCol(*batch[k].array(), key_types_[k], &keys[k]));
+    }
     std::lock_guard<std::mutex> lock(dev->mutex);
     ARROW_ASSIGN_OR_RAISE(auto ids, AllocateDevice(dev, batch.length * 4));
     B200_OK_OR_RAISE(dev, b200_grouper_consume(handle_.gb, keys.data(), reinterpret_cast<uint32_t*>(ids->address())));
@@ -962,7 +989,17 @@ class CudaGrouper : public internal::Grouper {
     std::lock_guard<std::mutex> lock(dev->mutex);
     ARROW_ASSIGN_OR_RAISE(auto keys, EmitKeys(&handle_, types_, key_types_, num_groups_));
     ExecBatch out({}, num_groups_);
-    for (auto& k : keys) out.values.emplace_back(std::move(k));
+    for (size_t k = 0; k < keys.size(); ++k) {
+      if (types_[k]->id() == Type::DICTIONARY) {   // DictionaryKeyEncoder::Decode (hash_aggregate.cc:215-230)
+        if (dictionaries_[k]) {
+          keys[k]->dictionary = dictionaries_[k];
+        } else {
+          ARROW_ASSIGN_OR_RAISE(auto empty, MakeArrayOfNull(checked_cast<const DictionaryType&>(*types_[k]).value_type(), 0));
+          keys[k]->dictionary = empty->data();
+        }
+      }
+      out.values.emplace_back(std::move(keys[k]));
+    }
     return out;
   }
 
@@ -975,7 +1012,7 @@ class CudaGrouper : public internal::Grouper {
     std::vector<b200_out_col> outs(types.size());
     std::vector<std::shared_ptr<Buffer>> data(types.size()), validity(types.size());
     for (size_t k = 0; k < types.size(); ++k) {
-      const int bits = key_types[k] == B200_BOOL ? 1 : checked_cast<const FixedWidthType&>(*types[k]).bit_width();
+      const int bits = key_types[k] == B200_BOOL ? 1 : KeyBitWidth(*types[k]);
       ARROW_ASSIGN_OR_RAISE(data[k], AllocateDevice(dev, bits == 1 ? BitmapBytes(num_groups) : int64_t(num_groups) * (bits / 8)));
       ARROW_ASSIGN_OR_RAISE(validity[k], AllocateDevice(dev, BitmapBytes(num_groups)));
       std::memset(&outs[k], 0, sizeof(b200_out_col));
@@ -995,7 +1032,169 @@ class CudaGrouper : public internal::Grouper {
   GroupByHandle handle_;
   std::vector<int32_t> key_types_;
   std::vector<std::shared_ptr<DataType>> types_;
+  std::vector<std::shared_ptr<ArrayData>> dictionaries_;
   uint32_t num_groups_ = 0;
+};
+
+
+// ---- unique / value_counts / dictionary_encode (kernels/vector_hash.cc:723-782) ---------------------------------
+// Upstream these are VectorKernels whose state (a memo table) is fed chunk by chunk (HashExec) and flushed by a
+// finalize step; here one device group-by handle plays the memo table: its group ids ARE the memo indices
+// (both are handed out in first-occurrence order), its key column the dictionary.  MetaFunctions, because a
+// device ChunkedArray must never be re-sliced or concatenated by the host executor.
+const FunctionDoc unique_doc("Compute unique elements (CUDA)", "Distinct values in first-occurrence order.", {"array"});
+const FunctionDoc value_counts_doc("Compute counts of unique elements (CUDA)",
+                                   "struct<values, counts: int64> of the distinct values in first-occurrence order.", {"array"});
+const FunctionDoc dictionary_encode_doc("Dictionary-encode array (CUDA)", "int32 indices into the distinct values.", {"array"},
+                                        "DictionaryEncodeOptions");
+const auto kDefaultDictionaryEncodeOptions = DictionaryEncodeOptions::Defaults();
+
+enum class HashOp { kUnique, kValueCounts, kDictionaryEncode };
+
+class CudaHashMetaFunction : public MetaFunction {
+ public:
+  CudaHashMetaFunction(const char* name, HashOp op, const FunctionDoc* doc, const FunctionOptions* defaults, int device)
+      : MetaFunction(name, Arity::Unary(), doc, defaults), op_(op), device_(device) {}
+
+  Result<Datum> ExecuteImpl(const std::vector<Datum>& args, const FunctionOptions* options, ExecContext*) const override {
+    ARROW_ASSIGN_OR_RAISE(auto chunks, ChunksOf(args[0]));
+    const auto type = args[0].type();
+    // the index column of a dictionary array is hashed like any integer column (DictionaryHashKernel,
+    // vector_hash.cc:520-603); dictionary_encode of a dictionary is not supported upstream either (:775-777)
+    const bool is_dict = type->id() == Type::DICTIONARY;
+    if (is_dict && op_ == HashOp::kDictionaryEncode) return Status::NotImplemented("dictionary_encode of a dictionary array");
+    const std::shared_ptr<DataType> value_type = is_dict ? checked_cast<const DictionaryType&>(*type).index_type() : type;
+    if (value_type->id() != Type::BOOL && !is_primitive(value_type->id())) {
+      return Status::NotImplemented("CUDA-backed ", name(), " handles fixed-width primitive columns, got ", type->ToString());
+    }
+    ARROW_ASSIGN_OR_RAISE(const int32_t ktype, PhysicalType(*value_type));
+    std::shared_ptr<ArrayData> dictionary;
+    if (is_dict) {
+      for (const auto& c : chunks) {
+        if (!dictionary) dictionary = c->data()->dictionary;
+        // "Only hashing for data with equal dictionaries currently supported" (vector_hash.cc:549-552); device
+        // dictionaries are compared by identity: their values cannot be read here
+        else if (c->data()->dictionary.get() != dictionary.get()) {
+          return Status::Invalid("Only hashing for data with equal dictionaries currently supported");
+        }
+      }
+    }
+    GroupByHandle handle;
+    ARROW_ASSIGN_OR_RAISE(handle.dev, GetDevice(device_));
+    DeviceState* dev = handle.dev;
+    std::unique_lock<std::mutex> lock(dev->mutex);
+    b200_agg_spec count_all;
+    std::memset(&count_all, 0, sizeof(count_all));
+    count_all.kind = B200_HASH_COUNT;
+    count_all.arg_type = ktype;
+    const bool counts = op_ == HashOp::kValueCounts;
+    B200_OK_OR_RAISE(dev, b200_groupby_create(dev->ctx, 1, &ktype, counts ? 1 : 0, counts ? &count_all : nullptr, 0, &handle.gb));
+    std::vector<std::shared_ptr<Buffer>> id_chunks;
+    uint64_t row_base = 0;
+    for (const auto& c : chunks) {
+      b200_col key;
+      RETURN_NOT_OK(ToCol(*c->data(), ktype, &key));
+      if (op_ == HashOp::kDictionaryEncode) {
+        ARROW_ASSIGN_OR_RAISE(auto ids, AllocateDevice(dev, c->length() * 4));
+        if (c->length() > 0) B200_OK_OR_RAISE(dev, b200_grouper_consume(handle.gb, &key, reinterpret_cast<uint32_t*>(ids->address())));
+        id_chunks.push_back(std::move(ids));
+      } else if (c->length() > 0) {
+        // value_counts counts every row of a group, the null group's too (ValueCountsAction::ObserveNullFound,
+        // vector_hash.cc:120-163): the counted argument is the key column read without its validity
+        b200_col all_rows = key;
+        all_rows.validity = nullptr;
+        all_rows.null_count = 0;
+        B200_OK_OR_RAISE(dev, b200_groupby_consume(handle.gb, &key, counts ? &all_rows : nullptr, row_base));
+      }
+      row_base += uint64_t(c->length());
+    }
+    uint32_t num_groups = 0;
+    B200_OK_OR_RAISE(dev, b200_groupby_num_groups(handle.gb, &num_groups));
+    std::shared_ptr<ArrayData> uniques, count_data;
+    if (counts) {
+      std::vector<b200_out_col> key_outs(1);
+      const int bits = ktype == B200_BOOL ? 1 : checked_cast<const FixedWidthType&>(*value_type).bit_width();
+      ARROW_ASSIGN_OR_RAISE(auto kdata, AllocateDevice(dev, bits == 1 ? BitmapBytes(num_groups) : int64_t(num_groups) * (bits / 8)));
+      ARROW_ASSIGN_OR_RAISE(auto kvalid, AllocateDevice(dev, BitmapBytes(num_groups)));
+      std::memset(&key_outs[0], 0, sizeof(b200_out_col));
+      key_outs[0].data = reinterpret_cast<void*>(kdata->address());
+      key_outs[0].validity = reinterpret_cast<void*>(kvalid->address());
+      AggInfo info;
+      info.kind = B200_HASH_COUNT;
+      info.out_type = int64();
+      ARROW_ASSIGN_OR_RAISE(auto aggs, FinalizeAggregates(&handle, {info}, {value_type}, num_groups, &key_outs));
+      count_data = aggs[0];
+      const int64_t nulls = key_outs[0].null_count;
+      uniques = ArrayData::Make(type, num_groups, {nulls ? kvalid : nullptr, kdata}, nulls);
+    } else {
+      ARROW_ASSIGN_OR_RAISE(auto keys, CudaGrouper::EmitKeys(&handle, {type}, {ktype}, num_groups));
+      uniques = keys[0];
+    }
+    if (is_dict) uniques->dictionary = dictionary;
+    if (op_ == HashOp::kUnique) {
+      lock.unlock();
+      return Datum(uniques);
+    }
+    if (op_ == HashOp::kValueCounts) {
+      lock.unlock();
+      auto out_type = struct_({field(kValuesFieldName, type), field(kCountsFieldName, int64())});
+      return Datum(ArrayData::Make(std::move(out_type), num_groups, {nullptr}, {uniques, count_data}, 0));
+    }
+    // ---- dictionary_encode: DictEncodeAction + DictEncodeFinalize (vector_hash.cc:165-226, 624-636)
+    const auto* encode_options = static_cast<const DictionaryEncodeOptions*>(options);
+    const bool mask_nulls = !encode_options || encode_options->null_encoding_behavior == DictionaryEncodeOptions::MASK;
+    int64_t null_group = -1;
+    std::shared_ptr<ArrayData> dict_values = uniques;
+    if (mask_nulls && uniques->null_count.load() != 0) {
+      // where the one null entry sits: num_groups validity bits to the host; the dictionary is the key column without it
+      std::vector<uint8_t> bits(size_t(BitmapBytes(num_groups)));
+      B200_OK_OR_RAISE(dev, b200_ctx_synchronize(dev->ctx));
+      ARROW_ASSIGN_OR_RAISE(auto cuda_validity, ::arrow::cuda::CudaBuffer::FromBuffer(uniques->buffers[0]));
+      RETURN_NOT_OK(cuda_validity->CopyToHost(0, int64_t(bits.size()), bits.data()));
+      for (uint32_t g = 0; g < num_groups; ++g)
+        if (!BitUtil::GetBit(bits.data(), g)) {
+          null_group = g;
+          break;
+        }
+      auto as_mask = ArrayData::Make(boolean(), num_groups, {nullptr, uniques->buffers[0]}, 0);
+      lock.unlock();
+      ARROW_ASSIGN_OR_RAISE(dict_values, FilterArray(dev, *uniques, *as_mask, 0 /* DROP */));
+      lock.lock();
+      dict_values->buffers[0] = nullptr;   // every entry left is valid
+      dict_values->null_count = 0;
+    }
+    auto dict_type = ::arrow::dictionary(int32(), type);
+    ArrayVector out_chunks;
+    for (size_t i = 0; i < chunks.size(); ++i) {
+      const int64_t n = chunks[i]->length();
+      // zero-length chunks of a ChunkedArray yield no output chunk (ExecBatchIterator skips them, exec.cc:221-229)
+      if (n == 0 && args[0].kind() == Datum::CHUNKED_ARRAY) continue;
+      std::shared_ptr<Buffer> validity;
+      int64_t nulls = 0;
+      if (null_group >= 0) {
+        ARROW_ASSIGN_OR_RAISE(validity, AllocateDevice(dev, (n + 31) / 32 * 4));
+        ARROW_ASSIGN_OR_RAISE(auto indices, AllocateDevice(dev, n * 4));
+        B200_OK_OR_RAISE(dev, b200_dictionary_indices(dev->ctx, reinterpret_cast<const uint32_t*>(id_chunks[i]->address()), n, null_group,
+                                                      reinterpret_cast<int32_t*>(indices->address()), reinterpret_cast<void*>(validity->address())));
+        id_chunks[i] = std::move(indices);
+        nulls = chunks[i]->data()->buffers[0] ? chunks[i]->data()->null_count.load() : 0;   // may stay unknown, like the input's
+        if (nulls == 0) validity = nullptr;
+      }
+      // ENCODE, or no null anywhere: the ids are the indices (uint32 ids < 2^31 read as int32)
+      auto data = ArrayData::Make(dict_type, n, {std::move(validity), id_chunks[i]}, nulls);
+      data->dictionary = dict_values;
+      out_chunks.push_back(MakeArray(std::move(data)));
+    }
+    B200_OK_OR_RAISE(dev, b200_ctx_synchronize(dev->ctx));
+    lock.unlock();
+    if (args[0].kind() == Datum::ARRAY) return Datum(out_chunks[0]);
+    for (auto& c : out_chunks) RETURN_NOT_OK(SettleNullCount(dev, c->data().get()));
+    return Datum(std::make_shared<ChunkedArray>(std::move(out_chunks), dict_type));
+  }
+
+ private:
+  HashOp op_;
+  int device_;
 };
 
 }  // namespace
@@ -1097,6 +1296,11 @@ Status RegisterCudaKernels(FunctionRegistry* registry, int device) {
       RETURN_NOT_OK(registry->AddFunction(std::move(func)));
     }
   }
+  // unique / value_counts / dictionary_encode (vector_hash.cc:723-782)
+  RETURN_NOT_OK(registry->AddFunction(std::make_shared<CudaHashMetaFunction>("unique", HashOp::kUnique, &unique_doc, nullptr, device)));
+  RETURN_NOT_OK(registry->AddFunction(std::make_shared<CudaHashMetaFunction>("value_counts", HashOp::kValueCounts, &value_counts_doc, nullptr, device)));
+  RETURN_NOT_OK(registry->AddFunction(std::make_shared<CudaHashMetaFunction>("dictionary_encode", HashOp::kDictionaryEncode,
+                                                                             &dictionary_encode_doc, &kDefaultDictionaryEncodeOptions, device)));
   return Status::OK();
 }
 
@@ -1230,6 +1434,37 @@ Result<std::unique_ptr<internal::Grouper>> MakeGrouper(const std::vector<ValueDe
   return CudaGrouper::Make(descrs, device);
 }
 
+// == Grouper::MakeGroupings (hash_aggregate.cc:980-1018): the counting sort of the ids runs on the device
+Result<std::shared_ptr<ListArray>> MakeGroupings(const ArrayData& ids, uint32_t num_groups, int device) {
+  if (ids.type->id() != Type::UINT32) return Status::TypeError("MakeGroupings takes uint32 group ids, got ", ids.type->ToString());
+  if (ids.buffers[0] && ids.null_count.load() != 0) return Status::Invalid("MakeGroupings with null ids");
+  ARROW_ASSIGN_OR_RAISE(DeviceState * dev, GetDevice(device));
+  b200_col c;
+  RETURN_NOT_OK(ToCol(ids, B200_UINT32, &c));
+  std::lock_guard<std::mutex> lock(dev->mutex);
+  ARROW_ASSIGN_OR_RAISE(auto offsets, AllocateDevice(dev, (int64_t(num_groups) + 1) * 4));
+  ARROW_ASSIGN_OR_RAISE(auto indices, AllocateDevice(dev, ids.length * 4));
+  size_t scratch_bytes = 0;
+  B200_OK_OR_RAISE(dev, b200_make_groupings_scratch_bytes(ids.length, &scratch_bytes));
+  ARROW_ASSIGN_OR_RAISE(auto scratch, AllocateDevice(dev, int64_t(scratch_bytes)));
+  B200_OK_OR_RAISE(dev, b200_make_groupings(dev->ctx, reinterpret_cast<const uint32_t*>(ids.buffers[1]->address()) + ids.offset, ids.length,
+                                            num_groups, reinterpret_cast<int32_t*>(offsets->address()),
+                                            reinterpret_cast<int32_t*>(indices->address()), reinterpret_cast<void*>(scratch->address()),
+                                            scratch_bytes));
+  auto values = ArrayData::Make(int32(), ids.length, {nullptr, std::move(indices)}, 0);
+  auto data = ArrayData::Make(list(int32()), num_groups, {nullptr, std::move(offsets)}, {std::move(values)}, 0);
+  return std::make_shared<ListArray>(std::move(data));
+}
+
+// == Grouper::ApplyGroupings (hash_aggregate.cc:968-978): Take without bounds check under the same offsets
+Result<std::shared_ptr<ListArray>> ApplyGroupings(const ListArray& groupings, const ArrayData& array, int device) {
+  ARROW_ASSIGN_OR_RAISE(DeviceState * dev, GetDevice(device));
+  ARROW_ASSIGN_OR_RAISE(auto sorted, TakeArray(dev, array, *groupings.data()->child_data[0], /*boundscheck=*/false));
+  auto data = ArrayData::Make(list(array.type), groupings.length(), {nullptr, groupings.data()->buffers[1]}, {std::move(sorted)}, 0,
+                              groupings.offset());
+  return std::make_shared<ListArray>(std::move(data));
+}
+
 Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Datum>& keys,
                       const std::vector<internal::Aggregate>& aggregates, ExecContext* ctx) {
   return GroupBy(arguments, keys, aggregates, Datum(), ctx);
@@ -1260,8 +1495,7 @@ Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Dat
   std::vector<int32_t> key_types;
   std::vector<std::shared_ptr<DataType>> key_dtypes;
   for (const auto& k : keys) {
-    if (k.type()->id() != Type::BOOL && !is_primitive(k.type()->id())) return Status::NotImplemented("Keys of type ", k.type()->ToString());
-    ARROW_ASSIGN_OR_RAISE(const int32_t t, PhysicalType(*k.type()));
+    ARROW_ASSIGN_OR_RAISE(const int32_t t, KeyPhysicalType(*k.type()));
     key_types.push_back(t);
     key_dtypes.push_back(k.type());
   }
@@ -1303,12 +1537,14 @@ Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Dat
   std::unique_lock<std::mutex> lock(dev->mutex);
   B200_OK_OR_RAISE(dev, b200_groupby_create(dev->ctx, int(key_types.size()), key_types.data(), int(specs.size()), specs.data(), 0, &handle.gb));
   uint64_t row_base = 0;
+  std::vector<std::shared_ptr<ArrayData>> key_dictionaries(keys.size());
   for (size_t b = 0; b < n_batches; ++b) {
     const int64_t len = key_chunks[0][b]->length();
     if (len == 0) continue;
     std::vector<b200_col> kcols(keys.size()), acols(arguments.size());
     for (size_t k = 0; k < keys.size(); ++k) {
       if (key_chunks[k][b]->length() != len) return Status::NotImplemented("GroupBy: arguments and keys must share one chunk layout");
+      RETURN_NOT_OK(NoteKeyDictionary(*key_chunks[k][b]->data(), &key_dictionaries[k]));
       RETURN_NOT_OK(ToCol(*key_chunks[k][b]->data(), key_types[k], &kcols[k]));
     }
     for (size_t i = 0; i < arguments.size(); ++i) {
@@ -1332,7 +1568,7 @@ Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Dat
   std::vector<b200_out_col> key_outs(keys.size());
   std::vector<std::shared_ptr<Buffer>> key_data(keys.size()), key_validity(keys.size());
   for (size_t k = 0; k < keys.size(); ++k) {
-    const int bits = key_types[k] == B200_BOOL ? 1 : checked_cast<const FixedWidthType&>(*key_dtypes[k]).bit_width();
+    const int bits = key_types[k] == B200_BOOL ? 1 : KeyBitWidth(*key_dtypes[k]);
     ARROW_ASSIGN_OR_RAISE(key_data[k], AllocateDevice(dev, bits == 1 ? BitmapBytes(num_groups) : int64_t(num_groups) * (bits / 8)));
     ARROW_ASSIGN_OR_RAISE(key_validity[k], AllocateDevice(dev, BitmapBytes(num_groups)));
     std::memset(&key_outs[k], 0, sizeof(b200_out_col));
@@ -1345,6 +1581,14 @@ Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Dat
   for (size_t k = 0; k < keys.size(); ++k) {
     const int64_t nulls = key_outs[k].null_count;
     out_data.push_back(ArrayData::Make(key_dtypes[k], num_groups, {nulls ? key_validity[k] : nullptr, key_data[k]}, nulls));
+    if (key_dtypes[k]->id() == Type::DICTIONARY) {
+      if (key_dictionaries[k]) {
+        out_data.back()->dictionary = key_dictionaries[k];
+      } else {
+        ARROW_ASSIGN_OR_RAISE(auto empty, MakeArrayOfNull(checked_cast<const DictionaryType&>(*key_dtypes[k]).value_type(), 0));
+        out_data.back()->dictionary = empty->data();
+      }
+    }
     out_fields.push_back(field("key_" + std::to_string(k), key_dtypes[k]));
   }
   lock.unlock();  // ~GroupByHandle takes the device mutex again

@@ -17,11 +17,14 @@
 //   sort_indices, array_sort_indices     kernels/vector_sort.cc:1565-1711, 1741-1755
 //   hash_count, hash_sum, hash_min_max   kernels/hash_aggregate.cc:1039-1062
 //   hash_mean                            absent upstream; MeanImpl::Finalize over the sum state
+//   take, array_take                     kernels/vector_selection.cc:1905-2081, 2154-2176
+//   unique, value_counts, dictionary_encode   kernels/vector_hash.cc:723-782
 #pragma once
 
 #include <memory>
 #include <vector>
 
+#include "arrow/array/array_nested.h"
 #include "arrow/c/abi.h"
 #include "arrow/compute/api_aggregate.h"
 #include "arrow/compute/exec.h"
@@ -67,6 +70,12 @@ Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Dat
 /// UInt32Array of group ids (ids in first-occurrence order), GetUniques() device-resident keys.
 Result<std::unique_ptr<internal::Grouper>> MakeGrouper(const std::vector<ValueDescr>& descrs,
                                                        ExecContext* ctx, int device = 0);
+
+/// Grouper::MakeGroupings / ApplyGroupings (api_aggregate.h:333-386, hash_aggregate.cc:968-1018) over device-resident
+/// group ids (the output of the Grouper twin's Consume) and arrays: the reference's are static functions that walk
+/// the ids on the host.  Results are device-resident ListArrays (offsets and values in CudaBuffers).
+Result<std::shared_ptr<ListArray>> MakeGroupings(const ArrayData& ids, uint32_t num_groups, int device = 0);
+Result<std::shared_ptr<ListArray>> ApplyGroupings(const ListArray& groupings, const ArrayData& array, int device = 0);
 
 /// Ingest / egress of columns.  CopyToDevice returns the same ArrayData with every host buffer
 /// replaced by a pooled CudaBuffer holding its bytes (offsets kept, the null count settled on the host first);

@@ -66,6 +66,7 @@ std::shared_ptr<ArrayData> ToDevice(const ArrayData& a) {
     buf = dbuf;
   }
   for (auto& child : out->child_data) child = ToDevice(*child);
+  if (out->dictionary) out->dictionary = ToDevice(*out->dictionary);
   return out;
 }
 std::shared_ptr<ArrayData> ToHost(const ArrayData& a) {
@@ -80,6 +81,7 @@ std::shared_ptr<ArrayData> ToHost(const ArrayData& a) {
     buf = std::move(hbuf);
   }
   for (auto& child : out->child_data) child = ToHost(*child);
+  if (out->dictionary) out->dictionary = ToHost(*out->dictionary);
   return out;
 }
 Datum DeviceDatum(const std::shared_ptr<Array>& a) { return Datum(ToDevice(*a->data())); }
@@ -176,7 +178,7 @@ int main() {
   {  // the registry holds exactly the reference's names for the path
     for (const char* name : {"filter", "array_filter", "sort_indices", "array_sort_indices", "take", "array_take", "hash_count", "hash_sum", "hash_min_max", "hash_mean"})
       CHECK_TRUE(registry->GetFunction(name).ok(), std::string("registered: ") + name);
-    CHECK_TRUE(registry->GetFunction("unique").status().IsKeyError(), "unknown function -> KeyError (registry.cc:62-64)");
+    CHECK_TRUE(registry->GetFunction("cumulative_sum").status().IsKeyError(), "unknown function -> KeyError (registry.cc:62-64)");
   }
 
   // ---------------- ingest / egress: cuda::CopyToDevice / CopyToHost, C Data Interface ----------------
@@ -631,6 +633,90 @@ int main() {
         auto want_all = GET(cp::internal::GroupBy({ivals}, {keys64}, {{fname, nullptr}}, &cpu_ctx)).make_array();
         ExpectEqual(HostArray(out), internal::checked_cast<const StructArray&>(*want_all).field(0), std::string("HashAggregateKernel consume/finalize over device ids: ") + fname);
       }
+    }
+  }
+
+  // ---- unique / value_counts / dictionary_encode (vector_hash.cc:723-782) and the Grouper's other consumers
+  {
+    const int64_t n = 50000;
+    std::vector<std::pair<std::string, std::shared_ptr<Array>>> columns = {
+        {"int32 with nulls", MakeRandom<Int32Builder, int32_t>(n, rng, 0.05, -200, 200, false)},
+        {"int64 no nulls", MakeRandom<Int64Builder, int64_t>(n, rng, 0.0, 0, 3000, false)},
+        {"uint8 with nulls", MakeRandom<UInt8Builder, int>(n, rng, 0.2, 0, 255, false)},
+        {"double with nulls", MakeRandom<DoubleBuilder, double>(n, rng, 0.1, 0.0, 50.0, false)},
+        {"bool with nulls", MakeRandom<BooleanBuilder, int>(n, rng, 0.3, 0, 2, false)},
+        {"tiny", Make<Int16Builder, int>({5, 7, 5, 0, 9, 7, 0, 3}, {true, true, true, false, true, true, false, true})},
+        {"all null", Make<Int32Builder, int>({0, 0, 0}, {false, false, false})},
+        {"empty", Make<Int32Builder, int>({})}};
+    cp::DictionaryEncodeOptions mask_opts(cp::DictionaryEncodeOptions::MASK), encode_opts(cp::DictionaryEncodeOptions::ENCODE);
+    for (auto& c : columns) {
+      auto dev = DeviceDatum(c.second);
+      ExpectEqual(HostArray(GET(cp::CallFunction("unique", {dev}, &gpu_ctx))), GET(cp::CallFunction("unique", {Datum(c.second)}, &cpu_ctx)).make_array(),
+                  "unique " + c.first);
+      ExpectEqual(HostArray(GET(cp::CallFunction("value_counts", {dev}, &gpu_ctx))),
+                  GET(cp::CallFunction("value_counts", {Datum(c.second)}, &cpu_ctx)).make_array(), "value_counts " + c.first);
+      for (auto* opts : {&mask_opts, &encode_opts}) {
+        auto want = GET(cp::CallFunction("dictionary_encode", {Datum(c.second)}, opts, &cpu_ctx)).make_array();
+        auto got = HostArray(GET(cp::CallFunction("dictionary_encode", {dev}, opts, &gpu_ctx)));
+        ExpectEqual(got, want, std::string("dictionary_encode ") + (opts == &mask_opts ? "MASK " : "ENCODE ") + c.first);
+      }
+    }
+    // chunked input: one memo table across the chunks (HashExec per chunk, vector_hash.cc:605-610)
+    {
+      auto col = columns[0].second;
+      auto chunked = Chunked(col, {0, 1000, 1000, 20000, n});
+      auto dchunked = DeviceChunked(*chunked);
+      ExpectEqual(HostArray(GET(cp::CallFunction("unique", {Datum(dchunked)}, &gpu_ctx))),
+                  GET(cp::CallFunction("unique", {Datum(chunked)}, &cpu_ctx)).make_array(), "unique chunked");
+      ExpectEqual(HostArray(GET(cp::CallFunction("value_counts", {Datum(dchunked)}, &gpu_ctx))),
+                  GET(cp::CallFunction("value_counts", {Datum(chunked)}, &cpu_ctx)).make_array(), "value_counts chunked");
+      auto want = GET(cp::CallFunction("dictionary_encode", {Datum(chunked)}, &mask_opts, &cpu_ctx)).chunked_array();
+      auto got = GET(cp::CallFunction("dictionary_encode", {Datum(dchunked)}, &mask_opts, &gpu_ctx)).chunked_array();
+      CHECK_TRUE(got->num_chunks() == want->num_chunks(), "dictionary_encode chunked: chunk count");
+      for (int i = 0; i < std::min(got->num_chunks(), want->num_chunks()); ++i) {
+        ExpectEqual(MakeArray(ToHost(*got->chunk(i)->data())), want->chunk(i), "dictionary_encode chunked, chunk " + std::to_string(i));
+      }
+    }
+    // dictionary columns: hashed / grouped through their indices, the dictionary rides along (DictionaryHashKernel
+    // vector_hash.cc:520-603; DictionaryKeyEncoder hash_aggregate.cc:198-233)
+    {
+      auto indices = MakeRandom<Int8Builder, int>(n, rng, 0.1, 0, 5, false);
+      auto dict_values = Make<Int64Builder, int64_t>({100, 200, 300, 400, 500});
+      auto dict_type = dictionary(int8(), int64());
+      auto darr = GET(DictionaryArray::FromArrays(dict_type, indices, dict_values));
+      auto dev = DeviceDatum(darr);
+      ExpectEqual(HostArray(GET(cp::CallFunction("unique", {dev}, &gpu_ctx))), GET(cp::CallFunction("unique", {Datum(darr)}, &cpu_ctx)).make_array(),
+                  "unique of a dictionary array");
+      ExpectEqual(HostArray(GET(cp::CallFunction("value_counts", {dev}, &gpu_ctx))),
+                  GET(cp::CallFunction("value_counts", {Datum(darr)}, &cpu_ctx)).make_array(), "value_counts of a dictionary array");
+      auto vals = MakeRandom<DoubleBuilder, double>(n, rng, 0.05, 0.0, 1.0, true);
+      std::vector<cp::internal::Aggregate> aggs = {{"hash_sum", nullptr}, {"hash_count", nullptr}};
+      auto want = GET(cp::internal::GroupBy({vals, vals}, {darr}, aggs, &cpu_ctx)).make_array();
+      auto got = HostArray(GET(cp::cuda::GroupBy({DeviceDatum(vals), DeviceDatum(vals)}, {dev}, aggs, &gpu_ctx)));
+      ExpectStructClose(got, want, "GroupBy with a dictionary key");
+      auto other = GET(DictionaryArray::FromArrays(dict_type, indices, Make<Int64Builder, int64_t>({1, 2, 3, 4, 5})));
+      auto two = std::make_shared<ChunkedArray>(ArrayVector{MakeArray(dev.array()), MakeArray(ToDevice(*other->data()))}, dict_type);
+      auto vals2 = std::make_shared<ChunkedArray>(ArrayVector{MakeArray(ToDevice(*vals->data())), MakeArray(ToDevice(*vals->data()))}, float64());
+      auto st = cp::cuda::GroupBy({Datum(vals2)}, {Datum(two)}, {{"hash_sum", nullptr}}, &gpu_ctx).status();
+      CHECK_TRUE(st.IsNotImplemented(), "GroupBy: batches with differing key dictionaries -> NotImplemented");
+    }
+    // MakeGroupings / ApplyGroupings (hash_aggregate.cc:968-1018) over the Grouper twin's ids
+    {
+      auto keys = MakeRandom<Int32Builder, int32_t>(n, rng, 0.05, 0, 700, false);
+      auto payload = MakeRandom<DoubleBuilder, double>(n, rng, 0.1, 0.0, 1.0, true);
+      auto cpu_grouper = GET(cp::internal::Grouper::Make({ValueDescr::Array(int32())}, &cpu_ctx));
+      auto gpu_grouper = GET(cp::cuda::MakeGrouper({ValueDescr::Array(int32())}, &gpu_ctx));
+      auto want_ids = GET(cpu_grouper->Consume(GET(cp::ExecBatch::Make({Datum(keys)})))).make_array();
+      auto got_ids = GET(gpu_grouper->Consume(GET(cp::ExecBatch::Make({DeviceDatum(keys)}))));
+      const uint32_t groups = cpu_grouper->num_groups();
+      auto want = GET(cp::internal::Grouper::MakeGroupings(internal::checked_cast<const UInt32Array&>(*want_ids), groups + 3, &cpu_ctx));
+      auto got = GET(cp::cuda::MakeGroupings(*got_ids.array(), groups + 3));
+      ExpectEqual(MakeArray(ToHost(*got->data())), want, "MakeGroupings (with empty trailing groups)");
+      auto want_applied = GET(cp::internal::Grouper::ApplyGroupings(*want, *payload, &cpu_ctx));
+      auto got_applied = GET(cp::cuda::ApplyGroupings(*got, *ToDevice(*payload->data())));
+      ExpectEqual(MakeArray(ToHost(*got_applied->data())), want_applied, "ApplyGroupings");
+      auto st = cp::cuda::MakeGroupings(*got_ids.array(), groups - 1).status();
+      CHECK_TRUE(st.IsIndexError(), "MakeGroupings: id >= num_groups -> IndexError");
     }
   }
 

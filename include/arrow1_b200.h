@@ -350,6 +350,13 @@ B200_API int b200_groupby_destroy(b200_groupby* gb);
  *                                     partition-then-aggregate path (defaults 2^22 rows, 2^21 groups)
  * B200_KEY_ERROR for an unknown name. */
 B200_API int b200_groupby_set_option(b200_groupby* gb, const char* name, int64_t value);
+/* Which way the handle's consume calls went (no reference counterpart).  Names:
+ *   "partitioned_calls"            consume calls served by the partition-then-aggregate path
+ *   "partitioned_alloc_failures"   calls that qualified but whose partition buffers (2 x 24 B per row) could not be
+ *                                  allocated: served by the global-table kernels instead
+ *   "partitioned_span_refusals"    calls with explicit row numbers spanning 2^31 or more: likewise
+ * B200_KEY_ERROR for an unknown name. */
+B200_API int b200_groupby_stat(b200_groupby* gb, const char* name, int64_t* out);
 /* == one iteration of GroupBy's batch loop (hash_aggregate.cc:928-943): Grouper::Consume
  * (:358-408) fused with every aggregate's Consume.  args[i] feeds aggs[i].  row_base is the
  * global index of the batch's first row: group order is first-occurrence order of

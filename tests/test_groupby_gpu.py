@@ -592,7 +592,7 @@ def test_dictionary_encode_matches_reference(ctx, t, encode_nulls):
         pytest.skip("needs oracle/_ref")
     rng = np.random.default_rng(160 + t)
     for n, nulls in ((1, 0.0), (33, 0.2), (5000, 0.0), (200_000, 0.05)):
-        col = rand_column(rng, t, n, nulls, lo=0, hi=(1 if t == cols.BOOL else 300))
+        col = rand_column(rng, t, n, nulls, lo=0, hi=(1 if t == cols.BOOL else 200))
         widx, wvalid, (dv, dvalid) = oracle.dictionary_encode(col, encode_nulls)
         idx, dictionary = compute.DictionaryEncode(col.to_device(), encode_nulls, ctx)
         hi, hd = idx.to_host(), dictionary.to_host()
