@@ -2249,7 +2249,22 @@ __global__ void gb_emit_kernel(const __grid_constant__ EmitArgs e) {
   const uint64_t slot_index = in ? (e.order ? e.order[r] : r) : 0;
   const char* slot = e.t.slots + slot_index * e.s.stride;
   const uint64_t* w = reinterpret_cast<const uint64_t*>(slot);
-  const uint64_t key = w[0];
+  // The slots are visited in first-row order, i.e. at random: every load of a slot is a DRAM round trip, and the
+  // decode below (run-time aggregate kinds, warp votes in between) would take them one after the other.  The first
+  // 64 bytes of the slot are requested up front, all loads in flight together; states beyond them are read in place.
+  constexpr int kPre = 8;
+  uint64_t pre[kPre];
+  const int slot_words = e.s.stride / 8;
+#pragma unroll
+  for (int i = 0; i < kPre; ++i) pre[i] = i < slot_words ? w[i] : 0;
+  auto word = [&](const uint64_t* st, int i) -> uint64_t {
+    const int idx = int(st - w) + i;
+    uint64_t v = pre[0];
+#pragma unroll
+    for (int q = 1; q < kPre; ++q) v = idx == q ? pre[q] : v;
+    return idx < kPre ? v : st[i];
+  };
+  const uint64_t key = pre[0];
   const bool special_null = e.order && e.s.null_shift < 0 && slot_index == e.t.cap;
   const bool special_full = e.order && e.s.null_shift < 0 && slot_index == e.t.cap + 1;
   // keys: GetUniques / Decode (hash_aggregate.cc:412-429, 65-94, 174-192)
@@ -2296,16 +2311,16 @@ __global__ void gb_emit_kernel(const __grid_constant__ EmitArgs e) {
       const EmitOut& omin = e.aggs[oi];
       const EmitOut& omax = e.aggs[oi + 1];
       if (in) {
-        const uint64_t flags = st[3];
+        const uint64_t flags = word(st, 3);
         const bool has_values = flags & 1, has_nulls = flags & 2;
         valid = has_values && !(g.option == 1 && has_nulls);  // hash_aggregate.cc:722-732
         if (g.dom == kFloat) {
           double mn = __longlong_as_double(0x7FF0000000000000ull), mx = __longlong_as_double(0xFFF0000000000000ull);
-          if (st[0] != ~uint64_t(0)) {  // at least one non-NaN value
-            mn = unord_f64(st[0]);
-            mx = unord_f64(st[1]);
-            if (st[2] != ~uint64_t(0)) {  // a zero was seen: the earliest zero row decides the sign
-              const double z = (st[2] & 1ull) ? -0.0 : 0.0;
+          if (word(st, 0) != ~uint64_t(0)) {  // at least one non-NaN value
+            mn = unord_f64(word(st, 0));
+            mx = unord_f64(word(st, 1));
+            if (word(st, 2) != ~uint64_t(0)) {  // a zero was seen: the earliest zero row decides the sign
+              const double z = (word(st, 2) & 1ull) ? -0.0 : 0.0;
               if (mn == 0.0) mn = z;
               if (mx == 0.0) mx = z;
             }
@@ -2315,8 +2330,8 @@ __global__ void gb_emit_kernel(const __grid_constant__ EmitArgs e) {
         } else {
           uint64_t mn = anti_extreme_bits(g.arg_type, true), mx = anti_extreme_bits(g.arg_type, false);
           if (has_values) {
-            mn = g.dom == kSigned ? (st[0] ^ 0x8000000000000000ull) : st[0];
-            mx = g.dom == kSigned ? (st[1] ^ 0x8000000000000000ull) : st[1];
+            mn = g.dom == kSigned ? (word(st, 0) ^ 0x8000000000000000ull) : word(st, 0);
+            mx = g.dom == kSigned ? (word(st, 1) ^ 0x8000000000000000ull) : word(st, 1);
           }
           store_typed(omin.data, g.arg_type, r, mn, 0.0);
           store_typed(omax.data, g.arg_type, r, mx, 0.0);
@@ -2339,15 +2354,15 @@ __global__ void gb_emit_kernel(const __grid_constant__ EmitArgs e) {
     const EmitOut& o = e.aggs[oi];
     if (in) {
       if (g.kind == B200_HASH_COUNT) {
-        reinterpret_cast<int64_t*>(o.data)[r] = int64_t(st[0]);
+        reinterpret_cast<int64_t*>(o.data)[r] = int64_t(word(st, 0));
       } else if (g.kind == B200_HASH_SUM) {
-        valid = st[1] > 0;  // hash_aggregate.cc:595-605
-        reinterpret_cast<uint64_t*>(o.data)[r] = st[0];
+        valid = word(st, 1) > 0;  // hash_aggregate.cc:595-605
+        reinterpret_cast<uint64_t*>(o.data)[r] = word(st, 0);
       } else {              // MeanImpl::Finalize: static_cast<double>(sum) / count
-        valid = st[1] > 0;
-        double s = g.dom == kFloat ? __longlong_as_double(st[0])
-                                   : (g.dom == kSigned ? double(int64_t(st[0])) : double(st[0]));
-        reinterpret_cast<double*>(o.data)[r] = valid ? s / double(st[1]) : 0.0;
+        valid = word(st, 1) > 0;
+        double s = g.dom == kFloat ? __longlong_as_double(word(st, 0))
+                                   : (g.dom == kSigned ? double(int64_t(word(st, 0))) : double(word(st, 0)));
+        reinterpret_cast<double*>(o.data)[r] = valid ? s / double(word(st, 1)) : 0.0;
       }
     }
     const unsigned vw = __ballot_sync(0xffffffffu, in && valid);
@@ -2556,6 +2571,7 @@ struct b200_groupby {
   size_t hp_bytes = 0;
   int64_t hp_min_rows = int64_t(1) << 22;
   int64_t hp_min_groups = int64_t(1) << 21;   // a table of this many slots no longer fits in L2
+  int64_t hp_keys_per_part = kHpKeysPerPart;  // target distinct keys per final partition
 };
 
 namespace {
@@ -2729,7 +2745,7 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
   // partition plan
   const uint64_t est = std::min<uint64_t>(uint64_t(n), std::max<uint64_t>(likely_groups, 1));
   int bits = 1;
-  while (bits < 17 && (uint64_t(kHpKeysPerPart) << bits) < est) ++bits;
+  while (bits < 17 && (uint64_t(gb->hp_keys_per_part) << bits) < est) ++bits;
   const int bits1 = bits <= 9 ? bits : bits / 2;
   const int bits2 = bits - bits1;
   const uint32_t parts1 = 1u << bits1, parts = 1u << bits;
@@ -3367,6 +3383,7 @@ int b200_groupby_set_option(b200_groupby* gb, const char* name, int64_t value) {
   if (!gb || !name) return B200_INVALID;
   if (!strcmp(name, "hp_min_rows")) gb->hp_min_rows = value;
   else if (!strcmp(name, "hp_min_groups")) gb->hp_min_groups = value;
+  else if (!strcmp(name, "hp_keys_per_part")) gb->hp_keys_per_part = std::max<int64_t>(64, std::min<int64_t>(value, kHpSlots / 2));
   else return b200_fail(gb->ctx, B200_KEY_ERROR, "groupby: no option named %s", name);
   return B200_OK;
 }

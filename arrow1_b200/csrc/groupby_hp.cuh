@@ -363,11 +363,16 @@ struct HpAggSmem {
   uint32_t cnt_valid[kHpSlots];
   uint32_t cnt_null[kHpSlots];
   uint32_t row[kHpSlots];
-  uint32_t warp_sums[kHpThreads / 32];
+  uint8_t list[kHpThreads / 32][32];   // per warp: the lanes whose slot is in use, compacted
+  uint8_t code[64];                    // per 64-bit word of a slot image: where its value comes from (kImg*)
   uint32_t part, begin, end;
   uint32_t image_base;
   uint32_t deferred;
+  uint32_t n_keys;                     // slots claimed for the current work item
+  uint32_t cursor;                     // images handed out so far (of n_keys)
 };
+enum { kImgZero = 0, kImgKey, kImgRow, kImgValid, kImgNull, kImgSum };
+static_assert(2 * (sizeof(HpAggSmem) + 1024) <= 228 * 1024, "two aggregation CTAs per SM");
 
 // sum += v on a 64-bit integer accumulator in shared memory with native 32-bit atomics: the carry out of the low
 // word is known to the thread whose add produced it
@@ -399,6 +404,20 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_c
   const int words = a.s.stride / 8;
   if (t == 0) S.deferred = 0;
   if (t == 0 && blockIdx.x == 0) a.counters[7] = item_base[n_parts];   // the host wants to know if a partition was cut
+  if (t < 64) {
+    // layout of a slot image (gb_import_kernel / gb_emit_kernel read it): [key][first row][aggregate states]
+    int c = t == 0 ? kImgKey : (t == 1 ? kImgRow : kImgZero);
+    for (int j = 0; j < a.s.n_aggs; ++j) {
+      const GbAgg& g = a.s.aggs[j];
+      if (g.kind == B200_HASH_COUNT) {
+        if (g.off / 8 == t) c = g.option ? kImgNull : kImgValid;
+      } else {   // SUM / MEAN: {sum, count of valid values}
+        if (g.off / 8 == t) c = kImgSum;
+        if (g.off / 8 + 1 == t) c = kImgValid;
+      }
+    }
+    S.code[t] = uint8_t(c);
+  }
   for (;;) {
     __syncthreads();
     if (t == 0) {
@@ -414,6 +433,8 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_c
       S.part = item < n_items ? item : 0xFFFFFFFFu;
       S.begin = b;
       S.end = e;
+      S.n_keys = 0;
+      S.cursor = 0;
     }
     for (int i = t; i < kHpSlots; i += kHpThreads) {
       S.key[i] = kEmpty;
@@ -445,12 +466,22 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_c
         if (!in[u]) continue;
         uint32_t slot = uint32_t(mix64(key[u]) >> 50) & uint32_t(kHpSlots - 1);
         bool found = false;
+        // (a warp's row costs the LONGEST probe sequence among its 32 lanes: the step is kept short — the hit first,
+        // the claim only on an empty slot — and rolled, so that the address is one add and one mask)
+#pragma unroll 1
         for (int probe = 0; probe < kHpProbe; ++probe) {
           uint64_t cur = *reinterpret_cast<volatile uint64_t*>(&S.key[slot]);
-          if (cur == kEmpty) cur = atomicCAS(reinterpret_cast<unsigned long long*>(&S.key[slot]), (unsigned long long)kEmpty, (unsigned long long)key[u]);
-          if (cur == kEmpty || cur == key[u]) {
+          if (cur == key[u]) {
             found = true;
             break;
+          }
+          if (cur == kEmpty) {
+            cur = atomicCAS(reinterpret_cast<unsigned long long*>(&S.key[slot]), (unsigned long long)kEmpty, (unsigned long long)key[u]);
+            if (cur == kEmpty) atomicAdd(&S.n_keys, 1u);
+            if (cur == kEmpty || cur == key[u]) {
+              found = true;
+              break;
+            }
           }
           slot = (slot + 1) & uint32_t(kHpSlots - 1);
         }
@@ -466,6 +497,9 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_c
         } else {
           atomicAdd(&S.cnt_valid[slot], 1u);
           if (a.n_cols) {
+            // (one row after the other on purpose: with the four rows' compare-and-swaps issued together — 2048 rows
+            // of a CTA in flight over ~1500 groups — the window between reading a sum and swapping it grows, most
+            // swaps lose and retry, and the kernel took 22.9 ms instead of 11.0 per 1 B rows)
             if (kFloatSum) atomicAdd(reinterpret_cast<double*>(&S.sum[slot]), __longlong_as_double(v[u]));
             else hp_add_u64(&S.sum[slot], v[u]);
           }
@@ -473,30 +507,11 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_c
       }
     }
     __syncthreads();
-    // ---- the partition's groups leave as slot images: count, reserve, write
-    constexpr int kPer = kHpSlots / kHpThreads;   // consecutive slots per thread
-    uint32_t mine = 0;
-#pragma unroll
-    for (int k = 0; k < kPer; ++k) mine += S.key[t * kPer + k] != kEmpty;
-    uint32_t incl = mine;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
-      if (lane >= d) incl += o;
-    }
-    if (lane == 31) S.warp_sums[warp] = incl;
-    __syncthreads();
-    uint32_t wpre = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < kHpThreads / 32; ++w) {
-      const uint32_t ws = S.warp_sums[w];
-      if (w < warp) wpre += ws;
-      total += ws;
-    }
+    // ---- the partition's groups leave as slot images (in any order: finalize ranks them by first row)
     if (t == 0) {
-      // one atomicAdd (a CAS loop on this counter, contended by every CTA, cost ~7 L2 round trips per item with
-      // all other warps waiting at the barrier).  When the list is full the part of the claim that lies inside it
-      // is filled with EMPTY keys, which the import skips.
+      // one atomicAdd reserves the whole item's images.  When the list is full the part of the claim that lies
+      // inside it is filled with EMPTY keys, which the import skips.
+      const uint32_t total = S.n_keys;
       uint32_t got = 0;
       if (total) {
         got = atomicAdd(a.counters + 6, total);
@@ -518,28 +533,37 @@ __global__ void __launch_bounds__(kHpThreads, 2) gb_hp_agg_kernel(const __grid_c
       if (t == 0) S.deferred += end - begin;
       continue;
     }
-    uint32_t pos = ibase + wpre + incl - mine;
-#pragma unroll
-    for (int k = 0; k < kPer; ++k) {
-      const int s = t * kPer + k;
-      const uint64_t key = S.key[s];
-      if (key == kEmpty) continue;
-      uint64_t* img = reinterpret_cast<uint64_t*>(images + size_t(pos) * a.s.stride);
-      ++pos;
-      const uint32_t row = S.row[s];
-      img[0] = key;
-      img[1] = a.row_base + uint64_t(row);   // with explicit row numbers row_base is the batch's smallest one
-      for (int w = 2; w < words; ++w) img[w] = 0;
-      for (int j = 0; j < a.s.n_aggs; ++j) {
-        const GbAgg& g = a.s.aggs[j];
-        uint64_t* st = img + g.off / 8;
-        if (g.kind == B200_HASH_COUNT) {
-          st[0] = g.option ? S.cnt_null[s] : S.cnt_valid[s];
-        } else {   // SUM / MEAN
-          st[0] = S.sum[s];
-          st[1] = S.cnt_valid[s];
+    // A warp looks at 32 consecutive slots at a time, compacts the used ones into a list and writes their images
+    // WORD by word across its lanes: consecutive lanes store consecutive 8-byte words (one thread per image and
+    // a run-time walk over the aggregates took 28 % of the kernel, profiles/r02_gb_hp_agg_ncu_summary.txt).
+    for (int grp = warp; grp < kHpSlots / 32; grp += kHpThreads / 32) {
+      const int s = grp * 32 + lane;
+      const bool used = S.key[s] != kEmpty;
+      const unsigned m = __ballot_sync(0xffffffffu, used);
+      if (m == 0) continue;
+      const int cnt = __popc(m);
+      uint32_t first = 0;
+      if (lane == 0) first = atomicAdd(&S.cursor, uint32_t(cnt));
+      first = __shfl_sync(0xffffffffu, first, 0);
+      if (used) S.list[warp][__popc(m & ((1u << lane) - 1u))] = uint8_t(lane);
+      __syncwarp();
+      uint64_t* out = reinterpret_cast<uint64_t*>(images + size_t(ibase + first) * a.s.stride);
+      const int n_words = cnt * words;
+      for (int idx = lane; idx < n_words; idx += 32) {
+        const int mi = idx / words, w = idx - mi * words;
+        const int slot = grp * 32 + S.list[warp][mi];
+        uint64_t v = 0;
+        switch (S.code[w]) {
+          case kImgKey: v = S.key[slot]; break;
+          case kImgRow: v = a.row_base + uint64_t(S.row[slot]); break;   // with explicit row numbers row_base is the batch's smallest one
+          case kImgValid: v = S.cnt_valid[slot]; break;
+          case kImgNull: v = S.cnt_null[slot]; break;
+          case kImgSum: v = S.sum[slot]; break;
+          default: break;
         }
+        out[idx] = v;
       }
+      __syncwarp();
     }
   }
   if (t == 0 && S.deferred) atomicAdd(a.counters + 1, S.deferred);

@@ -331,7 +331,10 @@ class GroupByWL(Workload):
     def step(self, ctx, cols_, bufs):
         from arrow1_b200 import capi
         k, v = cols_
-        return capi.group_by(ctx, [k], self._specs(), [v] * len(self.agg_names), expected_groups=self.n_keys)
+        opts = None
+        if os.environ.get("B200_BENCH_GB_OPTIONS"):   # experiments: "name=value,name=value" -> b200_groupby_set_option
+            opts = {a.split("=")[0]: int(a.split("=")[1]) for a in os.environ["B200_BENCH_GB_OPTIONS"].split(",")}
+        return capi.group_by(ctx, [k], self._specs(), [v] * len(self.agg_names), expected_groups=self.n_keys, options=opts)
 
     def e2e_step(self, host_cols):
         from arrow1_b200 import compute

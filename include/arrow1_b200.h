@@ -348,6 +348,8 @@ B200_API int b200_groupby_destroy(b200_groupby* gb);
 /* Execution knobs of a handle (no reference counterpart; results never depend on them).  Names:
  *   "hp_min_rows" / "hp_min_groups"   batch size and expected cardinality from which a consume call takes the
  *                                     partition-then-aggregate path (defaults 2^22 rows, 2^21 groups)
+ *   "hp_keys_per_part"                distinct keys that path aims at per final partition (default 1536 of the 4096
+ *                                     slots of a partition's shared-memory table; clamped to [64, 2048])
  * B200_KEY_ERROR for an unknown name. */
 B200_API int b200_groupby_set_option(b200_groupby* gb, const char* name, int64_t value);
 /* Which way the handle's consume calls went (no reference counterpart).  Names:
