@@ -2821,7 +2821,7 @@ int run_hp_consume(b200_groupby* gb, GbArgs& a, uint64_t likely_groups, bool* ha
     B200_CUDA(ctx, cudaFuncSetAttribute(gb_hp_agg_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(HpAggSmem))));
   }
   const int64_t n_tiles = (n + kHpTile - 1) / kHpTile;
-  const unsigned grid = unsigned(std::min<int64_t>(n_tiles, int64_t(ctx->num_sms) * 8));
+  const unsigned grid = unsigned(std::min<int64_t>(n_tiles, int64_t(ctx->num_sms) * 4 * B200_HP_PART_MINBLOCKS));
   HpArgs h;
   memset(&h, 0, sizeof(h));
   h.has_val = a.n_cols > 0;

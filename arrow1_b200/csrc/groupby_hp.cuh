@@ -21,8 +21,15 @@
 // HBM bytes per row at C4 (int64 key, float64 value): 8 + (16 + 20) + 8 + (20 + 20) + 20 = 132, + the images and one
 // sweep over the table.
 
+// tile shape of the partition kernels (a tuning sweep builds variants with -D)
+#ifndef B200_HP_ITEMS
+#define B200_HP_ITEMS 8
+#endif
+#ifndef B200_HP_PART_MINBLOCKS
+#define B200_HP_PART_MINBLOCKS 2
+#endif
 constexpr int kHpThreads = 512;
-constexpr int kHpItems = 8;
+constexpr int kHpItems = B200_HP_ITEMS;
 constexpr int kHpTile = kHpThreads * kHpItems;   // 4096 rows
 constexpr int kHpMaxBins = 512;
 constexpr int kHpSlots = 4096;                   // shared-memory table of the aggregation kernel
@@ -199,7 +206,7 @@ struct HpPartSmem {
 };
 
 template <int LEVEL, bool kOrd>
-__global__ void __launch_bounds__(kHpThreads, 2) gb_hp_part_kernel(const __grid_constant__ GbArgs a, const __grid_constant__ HpArgs h) {
+__global__ void __launch_bounds__(kHpThreads, B200_HP_PART_MINBLOCKS) gb_hp_part_kernel(const __grid_constant__ GbArgs a, const __grid_constant__ HpArgs h) {
   extern __shared__ __align__(16) unsigned char hp_smem_raw[];
   HpPartSmem& S = *reinterpret_cast<HpPartSmem*>(hp_smem_raw);
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;

@@ -279,6 +279,14 @@ __device__ __forceinline__ unsigned match_bit(unsigned m, uint32_t bin, uint32_t
 #ifndef B200_SORT_TMA
 #define B200_SORT_TMA 0
 #endif
+// lanes of a warp that hold the same digit: matched with one vote per digit bit (0), or through one shared-memory word
+// per (warp, digit) — ATOMS.OR, LDS, STS per item instead of 8 VOTE + 24 ALU instructions (1).  MEASURED AND LEFT OFF
+// (round 2, profiles/r02_sort_variants.txt): 5.85 ms per 100 M int64 rows against 5.66 ms with the votes — the pass
+// already spends its shared-memory wavefronts on digit-random addresses (48 % bank conflicts), three more per item
+// cost more than the issue slots they free.
+#ifndef B200_SORT_MATCH_ATOMIC
+#define B200_SORT_MATCH_ATOMIC 0
+#endif
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
@@ -412,6 +420,7 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
   constexpr int kRankGroup = kItems < 8 ? kItems : 8;
   uint32_t rank2[kItems / 2];  // two 16-bit ranks per register
   uint32_t* myhist = s.whist[warp];
+  uint32_t* match_words = s.pay + warp * NBINS;   // the staging array is free until the scatter; zeroed by the prologue
 #pragma unroll
   for (int g0 = 0; g0 < kItems; g0 += kRankGroup) {
     unsigned peers[kRankGroup];
@@ -421,9 +430,23 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
       const int i = g0 + q;
       const bool in = kFull || wbase + 32 * i < tile_items;
       const uint32_t bin = key_digit(key[i], d);
-      unsigned m = kFull ? 0xffffffffu : __ballot_sync(0xffffffffu, in);
+      unsigned m;
+      if (B200_SORT_MATCH_ATOMIC && !B200_SORT_TMA) {
+        // lanes holding the same digit find each other through one word per (warp, digit) in shared memory: every
+        // lane ORs its bit in, reads the word back, and clears it for the next item — three shared-memory
+        // instructions whose addresses do not depend on each other's results, against eight votes and 24 ALU
+        // instructions (a warp's shared-memory instructions execute in program order)
+        uint32_t* word = match_words + bin;
+        if (in) atomicOr(word, 1u << lane);
+        __syncwarp();
+        m = in ? *reinterpret_cast<volatile uint32_t*>(word) : 0u;
+        __syncwarp();
+        if (in) *reinterpret_cast<volatile uint32_t*>(word) = 0u;
+      } else {
+        m = kFull ? 0xffffffffu : __ballot_sync(0xffffffffu, in);
 #pragma unroll
-      for (int b = 0; b < NB; ++b) m = match_bit(m, bin, 1u << b);
+        for (int b = 0; b < NB; ++b) m = match_bit(m, bin, 1u << b);
+      }
       peers[q] = m;
       base[q] = 0;
       // same-warp shared atomics issue in program order: item i's bump precedes item i+1's
@@ -601,6 +624,9 @@ __global__ void __launch_bounds__(kThreads, kNarrow ? B200_SORT_NARROW_MINBLOCKS
     }
   }
   for (int i = t; i < kWarps * kBinStride / 4; i += kThreads) reinterpret_cast<uint4*>(&s.whist[0][0])[i] = make_uint4(0, 0, 0, 0);
+  if (B200_SORT_MATCH_ATOMIC && !B200_SORT_TMA) {
+    for (int i = t; i < kWarps * 256 / 4; i += kThreads) reinterpret_cast<uint4*>(&s.pay[0])[i] = make_uint4(0, 0, 0, 0);
+  }
   __syncthreads();
   const int64_t tile = s.tile;
   const int tile_items = int(min(int64_t(kTile), p.n - tile * kTile));

@@ -500,6 +500,11 @@ def dist_group_by_repartition(ops, keys: Sequence[Column], aggs: Sequence[AggSpe
         rrows = _all_to_all_bytes(rows.view(torch.uint8), 8, counts, recv_counts, group).view(torch.int64)
         rkeys = [recv_cols[index[(id(c.data), id(c.validity), c.offset)]] for c in keys]
         rargs = [recv_cols[index[(id(c.data), id(c.validity), c.offset)]] for c in args]
+        # the send-side copies are dead; the partition-then-aggregate path of the local aggregation wants 48 B per
+        # received row of scratch from cudaMalloc, which PyTorch's cached blocks may be sitting on
+        del datas, valids, rows, d, v
+        if dev.type == "cuda" and torch.cuda.mem_get_info(dev)[0] < total * 48 + (2 << 30):
+            torch.cuda.empty_cache()
         if total:
             gb.consume_rows(rkeys, rargs, rrows)
         stats = {}
