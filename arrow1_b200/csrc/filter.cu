@@ -15,6 +15,8 @@
 #include <type_traits>
 
 #include <vector>
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -845,6 +847,52 @@ int b200_filter_fused(b200_ctx* ctx, const b200_col* values, const b200_col* mas
     *out_len = ctx->host_words[0];
   }
   return B200_OK;
+}
+
+// ---- Filter for callers that must not allocate --------------------------------------------------------------------------
+// b200_filter_fused with its plan in a file-scope device array instead of caller scratch: no cudaMalloc, no cudaFree, no
+// allocating library call anywhere on the path (CUDA graph capture, serving loops, harnesses that forbid allocation).
+// The array costs kStaticPlanBytes on every GPU that loads the library, until the process exits.
+constexpr int64_t kStaticMaxRows = int64_t(1) << 28;   // 268 435 456 mask rows
+constexpr size_t kStaticPlanBytes = sizeof(PlanHeader) + size_t(kStaticMaxRows / kSuperRows) * 16 + size_t(kStaticMaxRows / kTileRows) * 4 + 64 + 256;
+static __device__ __align__(256) unsigned char g_static_plan[kStaticPlanBytes];   // 272.4 KB
+
+// In host code `g_static_plan` is only a stand-in for the symbol, not a device address: the address is asked for once
+// per device, with that device current (B200_ENTER has made it so), and cached.
+static int static_plan_address(b200_ctx* ctx, void** out) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static void* addr[kMaxDevices] = {};
+  if (ctx->device < 0 || ctx->device >= kMaxDevices) return b200_fail(ctx, B200_INVALID, "filter_fused_noalloc: device ordinal %d", ctx->device);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[ctx->device]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_static_plan);
+    if (e != cudaSuccess || !p) {
+      cudaGetLastError();
+      return b200_fail(ctx, B200_UNKNOWN_ERROR, "filter_fused_noalloc: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+    }
+    addr[ctx->device] = p;
+  }
+  *out = addr[ctx->device];
+  return B200_OK;
+}
+
+int64_t b200_filter_fused_noalloc_max_rows(void) { return kStaticMaxRows; }
+
+int b200_filter_fused_noalloc(b200_ctx* ctx, const b200_col* values, const b200_col* mask, int null_selection, void* out_data,
+                              void* out_validity, int64_t out_capacity, int64_t* out_len) {
+  B200_ENTER(ctx);
+  if (!ctx) return B200_INVALID;
+  B200_RETURN_NOT_OK(check_mask(ctx, mask));
+  if (mask->length > kStaticMaxRows || plan_bytes_for(mask->length) > kStaticPlanBytes)
+    return b200_fail(ctx, B200_CAPACITY_ERROR, "filter_fused_noalloc: %lld rows exceed the built-in plan's maximum of %lld (use b200_filter_fused with caller scratch)",
+                     (long long)mask->length, (long long)kStaticMaxRows);
+  void* plan = nullptr;
+  B200_RETURN_NOT_OK(static_plan_address(ctx, &plan));
+  // the array keeps the previous call's contents: b200_filter_plan zeroes the header (output length, done counter) on
+  // the stream and rewrites every prefix entry the apply kernel reads
+  return b200_filter_fused(ctx, values, mask, null_selection, plan, out_data, out_validity, out_capacity, out_len);
 }
 
 int b200_filter_out_spec(const b200_col* values, const b200_col* mask, int null_selection,

@@ -158,6 +158,20 @@ B200_API int b200_filter_fused_scratch_bytes(int64_t mask_length, size_t* out_by
 B200_API int b200_filter_fused(b200_ctx* ctx, const b200_col* values, const b200_col* mask, int null_selection,
                                void* scratch, void* out_data, void* out_validity /* nullable */,
                                int64_t out_capacity, int64_t* out_len /* host, nullable */);
+/* b200_filter_fused for callers that must not allocate and own no scratch (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, results and error behaviour as b200_filter_fused minus `scratch`: the plan lives
+ * in a static device array inside the library (272 KB on every GPU that loads the library, held until the process
+ * exits), and the call makes no cudaMalloc / cudaFree / allocating library call.
+ * Limit: mask->length <= b200_filter_fused_noalloc_max_rows() (2^28 = 268 435 456 rows); longer masks fail with
+ * B200_CAPACITY_ERROR and nothing is launched.
+ * All calls on a device share the one array: calls that may overlap on the GPU (two contexts / streams on the same
+ * device) race on it and must be ordered by the caller; calls on one context are ordered by its stream.  The array
+ * keeps the previous call's contents; every call re-initialises what it reads. */
+B200_API int64_t b200_filter_fused_noalloc_max_rows(void);
+B200_API int b200_filter_fused_noalloc(b200_ctx* ctx, const b200_col* values, const b200_col* mask,
+                                       int null_selection, void* out_data, void* out_validity /* nullable */,
+                                       int64_t out_capacity, int64_t* out_len /* host, nullable */);
 /* device address of the int64 output length inside a plan (for fully asynchronous callers) */
 B200_API const int64_t* b200_filter_plan_length_ptr(const void* plan);
 
