@@ -12,7 +12,7 @@ from typing import List, Optional, Sequence
 import numpy as np
 import torch
 
-from .columns import (BITS, BOOL, DOUBLE, HASH_MIN_MAX, INT64, NP_OF, UINT64, AggSpec, Column, agg_out_types,
+from .columns import (BINARY, BITS, BOOL, DOUBLE, HASH_MIN_MAX, INT64, NP_OF, UINT64, AggSpec, Column, agg_out_types,
                       b200_agg_spec, b200_col, b200_out_col, col_array)
 
 _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libarrow1_b200.so")
@@ -657,11 +657,18 @@ class GroupBy:
         out_keys = (b200_out_col * max(len(self.key_types), 1))()
         kbufs = []
         for i, t in enumerate(self.key_types):
-            bits = BITS[t]
-            d = ctx.empty((G + 7) // 8 + 8 if bits == 1 else max(G, 1) * (bits // 8))
+            x = None
+            if t == BINARY:   # int32 offsets + the value bytes, sized by the library
+                nbytes = C.c_int64(0)
+                ctx.check(lib().b200_groupby_key_bytes(self._h, C.c_int(i), C.byref(nbytes)))
+                d = ctx.empty((G + 1) * 4 + 8)
+                x = ctx.empty(max(int(nbytes.value), 1) + 8)
+            else:
+                bits = BITS[t]
+                d = ctx.empty((G + 7) // 8 + 8 if bits == 1 else max(G, 1) * (bits // 8))
             v = ctx.empty((G + 7) // 8 + 8)
-            out_keys[i] = b200_out_col(v.data_ptr(), d.data_ptr(), t, 0, 0, 0)
-            kbufs.append((t, d, v))
+            out_keys[i] = b200_out_col(v.data_ptr(), d.data_ptr(), t, 0, 0, 0, x.data_ptr() if x is not None else None)
+            kbufs.append((t, d, v, x))
         ctx.check(lib().b200_groupby_finalize(self._h, out_aggs, out_keys))
         ctx.synchronize()
         aggs, i = [], 0
@@ -674,7 +681,7 @@ class GroupBy:
             if len(cols) == 2:
                 cols[1] = Column(cols[1].type, cols[1].data, cols[0].validity, G, 0, cols[0].null_count)
             aggs.append(cols)
-        keys = [Column(t, d, v, G, 0, int(out_keys[k].null_count)) for k, (t, d, v) in enumerate(kbufs)]
+        keys = [Column(t, d, v, G, 0, int(out_keys[k].null_count), x) for k, (t, d, v, x) in enumerate(kbufs)]
         return GroupByOutput(G, aggs, keys)
 
 

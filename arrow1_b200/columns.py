@@ -16,6 +16,7 @@ import numpy as np
 
 # == arrow::Type::type (type_fwd.h) == b200_type
 BOOL, UINT8, INT8, UINT16, INT16, UINT32, INT32, UINT64, INT64, FLOAT, DOUBLE = 1, 2, 3, 4, 5, 6, 7, 8, 9, 11, 12
+BINARY = 13   # binary / utf8 with int32 offsets: group keys only; `data` = offsets, `extra` = value bytes
 
 NP_OF = {
     UINT8: np.uint8, INT8: np.int8, UINT16: np.uint16, INT16: np.int16, UINT32: np.uint32,
@@ -27,7 +28,7 @@ BITS = {BOOL: 1, UINT8: 8, INT8: 8, UINT16: 16, INT16: 16, UINT32: 32, INT32: 32
         INT64: 64, FLOAT: 32, DOUBLE: 64}
 NAMES = {BOOL: "bool", UINT8: "uint8", INT8: "int8", UINT16: "uint16", INT16: "int16",
          UINT32: "uint32", INT32: "int32", UINT64: "uint64", INT64: "int64", FLOAT: "float",
-         DOUBLE: "double"}
+         DOUBLE: "double", BINARY: "binary"}
 
 # aggregate kinds == b200_agg_kind
 HASH_COUNT, HASH_SUM, HASH_MIN_MAX, HASH_MEAN = 0, 1, 2, 3
@@ -37,12 +38,12 @@ AGG_NAMES = {HASH_COUNT: "hash_count", HASH_SUM: "hash_sum", HASH_MIN_MAX: "hash
 class b200_col(C.Structure):
     _fields_ = [("validity", C.c_void_p), ("data", C.c_void_p), ("type", C.c_int32),
                 ("reserved", C.c_int32), ("length", C.c_int64), ("offset", C.c_int64),
-                ("null_count", C.c_int64)]
+                ("null_count", C.c_int64), ("extra", C.c_void_p)]
 
 
 class b200_out_col(C.Structure):
     _fields_ = [("validity", C.c_void_p), ("data", C.c_void_p), ("type", C.c_int32),
-                ("reserved", C.c_int32), ("length", C.c_int64), ("null_count", C.c_int64)]
+                ("reserved", C.c_int32), ("length", C.c_int64), ("null_count", C.c_int64), ("extra", C.c_void_p)]
 
 
 class b200_agg_spec(C.Structure):
@@ -88,6 +89,7 @@ class Column:
     length: int
     offset: int = 0
     null_count: int = -1
+    extra: Optional[object] = None   # BINARY: the value bytes (`data` holds the int32 offsets)
 
     # ---- constructors ------------------------------------------------------------------
     @staticmethod
@@ -114,10 +116,34 @@ class Column:
             nc = null_count
         return Column(t, data, vbuf, n, offset, nc)
 
+    @staticmethod
+    def from_strings(items, offset: int = 0) -> "Column":
+        """A BINARY column (int32 offsets) from bytes / str / None entries; the column is parent[offset:]."""
+        raw = [None if x is None else (x.encode() if isinstance(x, str) else bytes(x)) for x in items]
+        lens = np.array([0 if x is None else len(x) for x in raw], dtype=np.int64)
+        offs = np.zeros(len(raw) + 1, dtype=np.int32)
+        np.cumsum(lens, out=offs[1:])
+        blob = b"".join(x for x in raw if x is not None)
+        data = np.zeros((offs.nbytes + 63) // 64 * 64 + 64, dtype=np.uint8)
+        data[: offs.nbytes] = offs.view(np.uint8)
+        extra = np.zeros((len(blob) + 63) // 64 * 64 + 64, dtype=np.uint8)
+        extra[: len(blob)] = np.frombuffer(blob, dtype=np.uint8)
+        valid = np.array([x is not None for x in raw], dtype=np.bool_)
+        vbuf = None if valid.all() else pack_bits(valid)
+        return Column(BINARY, data, vbuf, len(raw) - offset, offset, int((~valid[offset:]).sum()), extra)
+
+    def strings(self):
+        """BINARY column -> list of bytes / None."""
+        h = self.to_host()
+        offs = h.data[: (h.offset + h.length + 1) * 4].view(np.int32)[h.offset:]
+        valid = h.valid()
+        blob = h.extra.tobytes() if h.extra is not None else b""
+        return [blob[offs[i]: offs[i + 1]] if valid[i] else None for i in range(h.length)]
+
     # ---- views -------------------------------------------------------------------------
     def desc(self) -> b200_col:
         return b200_col(_ptr(self.validity), _ptr(self.data), self.type, 0, self.length, self.offset,
-                        self.null_count)
+                        self.null_count, _ptr(self.extra))
 
     @property
     def on_device(self) -> bool:
@@ -127,14 +153,16 @@ class Column:
         import torch
         d = torch.from_numpy(self.data).to(device)
         v = None if self.validity is None else torch.from_numpy(self.validity).to(device)
-        return Column(self.type, d, v, self.length, self.offset, self.null_count)
+        x = None if self.extra is None else torch.from_numpy(self.extra).to(device)
+        return Column(self.type, d, v, self.length, self.offset, self.null_count, x)
 
     def to_host(self) -> "Column":
         if not self.on_device:
             return self
         d = self.data.cpu().numpy()
         v = None if self.validity is None else self.validity.cpu().numpy()
-        return Column(self.type, d, v, self.length, self.offset, self.null_count)
+        x = None if self.extra is None else self.extra.cpu().numpy()
+        return Column(self.type, d, v, self.length, self.offset, self.null_count, x)
 
     def values(self) -> np.ndarray:
         """Logical values (host) as a numpy array of the column type (bool for BOOL)."""

@@ -89,7 +89,11 @@ def _h2d(col: Column, ctx: capi.Context) -> Tuple[Column, int]:
     if col.validity is not None:
         v = torch.from_numpy(col.validity).to(dev, non_blocking=True)
         n += col.validity.nbytes
-    return Column(col.type, d, v, col.length, col.offset, col.null_count), n
+    x = None
+    if col.extra is not None:   # BINARY key column: the value bytes
+        x = torch.from_numpy(col.extra).to(dev, non_blocking=True)
+        n += col.extra.nbytes
+    return Column(col.type, d, v, col.length, col.offset, col.null_count, x), n
 
 
 def _d2h(t: torch.Tensor, nbytes: int) -> np.ndarray:
@@ -385,8 +389,12 @@ def GroupBy(arguments: Sequence[Column], keys: Sequence[Column], aggregates: Seq
     def pair(c):
         """device result column -> (values, valid) on the host through the pinned pool (DMA, no pageable staging)"""
         nonlocal d2h
-        from .columns import BITS, NP_OF, BOOL, unpack_bits
+        from .columns import BINARY, BITS, NP_OF, BOOL, unpack_bits
         g = c.length
+        if c.type == BINARY:   # a variable-length key column comes back as a host Column (offsets + bytes)
+            h = c.to_host()
+            d2h += (g + 1) * 4 + (int(h.data[: (g + 1) * 4].view(np.int32)[g]) if g else 0) + (g + 7) // 8
+            return c.type, h, None, g
         bits = BITS[c.type]
         nb = (g + 7) // 8 if bits == 1 else g * (bits // 8)
         data = _d2h(c.data, nb)
@@ -399,7 +407,12 @@ def GroupBy(arguments: Sequence[Column], keys: Sequence[Column], aggregates: Seq
     ctx.stream.synchronize()
 
     def finish(t, data, vbytes, g):
-        from .columns import BITS, NP_OF, BOOL, unpack_bits
+        from .columns import BINARY, BITS, NP_OF, BOOL, unpack_bits
+        if t == BINARY:
+            vals = np.empty(g, dtype=object)
+            for i, x in enumerate(data.strings()):
+                vals[i] = b"" if x is None else x
+            return vals, data.valid()
         vals = unpack_bits(data, g) if t == BOOL else data[: g * (BITS[t] // 8)].view(NP_OF[t])
         valid = np.ones(g, dtype=np.bool_) if vbytes is None else unpack_bits(vbytes, g)
         return vals, valid
@@ -441,11 +454,12 @@ def ValueCounts(values: Column, ctx: Optional[capi.Context] = None):
     counts the nulls (hash_count in both CountOptions modes over the column itself: one of the two is zero per group)."""
     ctx = ctx or default_context()
     from . import columns as cols
-    out = capi.group_by(ctx, [values], [AggSpec(cols.HASH_COUNT, 0), AggSpec(cols.HASH_COUNT, 1)], [values, values])
+    # every row of a group counts, the null group's too (ValueCountsAction::ObserveNullFound, vector_hash.cc:120-163):
+    # hash_count over the column read WITHOUT its validity (a binary column through its int32 offsets buffer)
+    all_rows = Column(cols.INT32 if values.type == cols.BINARY else values.type, values.data, None, values.length, values.offset, 0)
+    out = capi.group_by(ctx, [values], [AggSpec(cols.HASH_COUNT, 0)], [all_rows])
     G = out.num_groups
-    a = out.aggs[0][0].data[: G * 8].view(torch.int64)
-    b = out.aggs[1][0].data[: G * 8].view(torch.int64)
-    return out.keys[0], a + b
+    return out.keys[0], out.aggs[0][0].data[: G * 8].view(torch.int64)
 
 
 def DictionaryEncode(values: Column, encode_nulls: bool = False, ctx: Optional[capi.Context] = None):
@@ -467,8 +481,14 @@ def DictionaryEncode(values: Column, encode_nulls: bool = False, ctx: Optional[c
         G = uniq.length
         bits = cols.unpack_bits(uniq.validity[: (G + 7) // 8].cpu().numpy(), G)
         null_group = int(np.flatnonzero(~bits)[0])
-        kept = capi.filter(ctx, uniq, Column(cols.BOOL, uniq.validity, None, G, 0, 0), DROP).col
-        dictionary = Column(uniq.type, kept.data, None, kept.length, 0, 0)   # every entry left is valid
+        if uniq.type == cols.BINARY:
+            # the null entry holds no bytes: the value buffer stays, the int32 offsets lose entry null_group + 1
+            offs = uniq.data[: (G + 1) * 4].view(torch.int32)
+            kept = torch.cat([offs[: null_group + 1], offs[null_group + 2:]]).contiguous().view(torch.uint8)
+            dictionary = Column(uniq.type, kept, None, G - 1, 0, 0, uniq.extra)
+        else:
+            kept = capi.filter(ctx, uniq, Column(cols.BOOL, uniq.validity, None, G, 0, 0), DROP).col
+            dictionary = Column(uniq.type, kept.data, None, kept.length, 0, 0)   # every entry left is valid
     idx, validity = capi.dictionary_indices(ctx, ids, null_group)
     n = values.length
     nulls = 0 if validity is None else (values.null_count if values.null_count >= 0 else -1)

@@ -2557,6 +2557,14 @@ struct b200_groupby {
   uint32_t* wcounters = nullptr;
   void* wtmp = nullptr;
   size_t wtmp_bytes = 0;
+  // variable-length key columns: heap of the stored keys' bytes, where each stored key's bytes start, bytes per column
+  int32_t wn_var = 0;
+  int32_t wvar_col[kWideMaxKeys], wvar_index[kWideMaxKeys];
+  uint8_t* wheap = nullptr;
+  uint64_t wheap_cap = 0, wheap_used = 0;
+  uint64_t* wstore_var = nullptr;
+  unsigned long long* wvar_bytes = nullptr;   // device [kWideMaxKeys]
+  uint64_t wvar_bytes_host[kWideMaxKeys] = {};
   // the group order finalize computed (slot / image index per output rank, inside `tmp`): b200_groupby_first_rows right
   // after a finalize gathers through it instead of collecting and sorting once more; dropped by any change of state
   int64_t hp_calls = 0, hp_alloc_failures = 0, hp_span_refusals = 0;   // b200_groupby_stat
@@ -3167,15 +3175,20 @@ int b200_groupby_create(b200_ctx* ctx, int n_keys, const int32_t* key_types, int
   memset(&s, 0, sizeof(s));
   s.n_aggs = n_aggs;
   int total = 0;
+  bool any_var = false;   // a variable-length key column: always through the key -> id table
   for (int k = 0; k < n_keys; ++k) {
     // GrouperImpl::Make: "Keys of type ..." NotImplemented for unsupported types (hash_aggregate.cc:352)
+    if (key_types[k] == B200_BINARY) {
+      any_var = true;
+      continue;
+    }
     if (b200_type_bits(key_types[k]) == 0) return b200_fail(ctx, B200_NOT_IMPLEMENTED, "Keys of type %d", key_types[k]);
     total += b200_type_bits(key_types[k]);
   }
   // Keys that fit one 64-bit register (values + one null flag per column, or a single 64-bit column) are packed;
   // anything wider goes through the key -> id table of groupby_wide.cuh and is grouped by a uint32 id column.
   const int wide_n = n_keys;
-  const bool wide = n_keys > kMaxKeys || !(total + n_keys <= 64 || (n_keys == 1 && total == 64));
+  const bool wide = any_var || n_keys > kMaxKeys || !(total + n_keys <= 64 || (n_keys == 1 && total == 64));
   int32_t wide_types[kWideMaxKeys];
   if (wide) {
     for (int k = 0; k < n_keys; ++k) wide_types[k] = key_types[k];
@@ -3226,7 +3239,14 @@ int b200_groupby_create(b200_ctx* ctx, int n_keys, const int32_t* key_types, int
       gb->wtypes[k] = wide_types[k];
       gb->wbits[k] = b200_type_bits(wide_types[k]);
       gb->woff[k] = pos;
-      pos += 1 + (gb->wbits[k] == 1 ? 1 : gb->wbits[k] / 8);
+      gb->wvar_index[k] = -1;
+      if (wide_types[k] == B200_BINARY) {   // [null byte][4-byte length]
+        gb->wvar_index[k] = gb->wn_var;
+        gb->wvar_col[gb->wn_var++] = k;
+        pos += 5;
+      } else {
+        pos += 1 + (gb->wbits[k] == 1 ? 1 : gb->wbits[k] / 8);
+      }
     }
     gb->wwords = (pos + 7) / 8;
   }
@@ -3262,6 +3282,9 @@ int b200_groupby_destroy(b200_groupby* gb) {
   b200_dev_free(gb->ctx, gb->wstore);
   b200_dev_free(gb->ctx, gb->wcounters);
   b200_dev_free(gb->ctx, gb->wtmp);
+  b200_dev_free(gb->ctx, gb->wheap);
+  b200_dev_free(gb->ctx, gb->wstore_var);
+  b200_dev_free(gb->ctx, gb->wvar_bytes);
   delete gb;
   return B200_OK;
 }
@@ -3292,6 +3315,12 @@ int wide_translate(b200_groupby* gb, const b200_col* keys, const uint32_t* selec
     const int bits = gb->wbits[k];
     w.nbits = bits;
     w.byte_off = gb->woff[k];
+    w.var_index = gb->wvar_index[k];
+    if (c.type == B200_BINARY) {
+      // (a column of empty strings may come without a value buffer: any non-null pointer will do, nothing is read)
+      w.bytes = reinterpret_cast<const uint8_t*>(c.extra ? c.extra : c.data);
+      w.offsets = reinterpret_cast<const int32_t*>(c.data) + c.offset;
+    }
     w.data = bits >= 8 ? reinterpret_cast<const char*>(c.data) + c.offset * (bits / 8) : nullptr;
     w.bits = make_bitmap_ref(bits == 1 ? c.data : nullptr, c.offset);
     const bool has_nulls = c.validity != nullptr && c.null_count != 0;
@@ -3317,18 +3346,36 @@ int wide_translate(b200_groupby* gb, const b200_col* keys, const uint32_t* selec
     wide_fill_kernel<<<(unsigned)((want + 255) / 256), 256, 0, ctx->stream>>>(gb->wslots, want);
     B200_LAUNCHED(ctx);
     if (gb->wcount) {
-      wide_rehash_kernel<<<(gb->wcount + 255) / 256, 256, 0, ctx->stream>>>(gb->wstore, gb->wwords, gb->wcount, gb->wslots, gb->wcap, gb->wcounters);
+      WideVarInfo vi;
+      memset(&vi, 0, sizeof(vi));
+      vi.n_var = gb->wn_var;
+      for (int v = 0; v < gb->wn_var; ++v) vi.byte_off[v] = gb->woff[gb->wvar_col[v]];
+      vi.store_var = gb->wstore_var;
+      vi.heap = gb->wheap;
+      wide_rehash_kernel<<<(gb->wcount + 255) / 256, 256, 0, ctx->stream>>>(gb->wstore, gb->wwords, gb->wcount, gb->wslots, gb->wcap, gb->wcounters, vi);
       B200_LAUNCHED(ctx);
     }
   }
   const size_t a4 = b200_align_up(size_t(n) * 4, 256);
-  if (3 * a4 > gb->wtmp_bytes) {
+  const size_t tmp_need = 3 * a4 + (gb->wn_var ? a4 + 256 : 0);
+  if (tmp_need > gb->wtmp_bytes) {
     if (gb->wtmp) b200_dev_free(ctx, gb->wtmp);
     gb->wtmp = nullptr;
     gb->wtmp_bytes = 0;
-    B200_RETURN_NOT_OK(b200_dev_alloc(ctx, &gb->wtmp, 3 * a4));
-    gb->wtmp_bytes = 3 * a4;
+    B200_RETURN_NOT_OK(b200_dev_alloc(ctx, &gb->wtmp, tmp_need));
+    gb->wtmp_bytes = tmp_need;
   }
+  if (gb->wn_var && !gb->wvar_bytes) {
+    B200_RETURN_NOT_OK(b200_dev_alloc(ctx, reinterpret_cast<void**>(&gb->wvar_bytes), kWideMaxKeys * sizeof(unsigned long long)));
+    B200_CUDA(ctx, cudaMemsetAsync(gb->wvar_bytes, 0, kWideMaxKeys * sizeof(unsigned long long), ctx->stream));
+  }
+  a.var_bytes = gb->wvar_bytes;
+  a.new_len = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(gb->wtmp) + 3 * a4);
+  a.n_var = gb->wn_var;
+  for (int v = 0; v < gb->wn_var; ++v) a.var_col[v] = gb->wvar_col[v];
+  a.store_var = gb->wstore_var;
+  a.heap = gb->wheap;
+  a.var_bytes = gb->wvar_bytes;
   a.slots = gb->wslots;
   a.cap = gb->wcap;
   a.store = gb->wstore;
@@ -3357,11 +3404,53 @@ int wide_translate(b200_groupby* gb, const b200_col* keys, const uint32_t* selec
         b200_dev_free(ctx, gb->wstore);
       }
       gb->wstore = ns;
-      gb->wstore_cap = uint32_t(cap);
       a.store = ns;
+      if (gb->wn_var) {
+        uint64_t* nv = nullptr;
+        B200_RETURN_NOT_OK(b200_dev_alloc(ctx, reinterpret_cast<void**>(&nv), cap * gb->wn_var * 8));
+        if (gb->wcount) B200_CUDA(ctx, cudaMemcpyAsync(nv, gb->wstore_var, size_t(gb->wcount) * gb->wn_var * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+        if (gb->wstore_var) {
+          B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+          b200_dev_free(ctx, gb->wstore_var);
+        }
+        gb->wstore_var = nv;
+        a.store_var = nv;
+      }
+      gb->wstore_cap = uint32_t(cap);
     }
-    wide_assign_kernel<<<(n_new + 255) / 256, 256, 0, ctx->stream>>>(a, n_new, gb->wcount);
-    B200_LAUNCHED(ctx);
+    if (gb->wn_var) {
+      // bytes the new keys add to the heap: lengths -> scan -> total on the host -> room in the heap
+      wide_new_len_kernel<<<(n_new + 255) / 256, 256, 0, ctx->stream>>>(a, n_new);
+      B200_LAUNCHED(ctx);
+      gb_hp_scan_kernel<<<1, 1024, 0, ctx->stream>>>(a.new_len, n_new, nullptr, a.new_len);
+      B200_LAUNCHED(ctx);
+      B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 44, a.new_len + n_new, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+      B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 46, gb->wvar_bytes, kWideMaxKeys * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+      B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+      const uint64_t add = *reinterpret_cast<const uint32_t*>(ctx->host_words + 44);
+      for (int v = 0; v < gb->wn_var; ++v) gb->wvar_bytes_host[v] = uint64_t(ctx->host_words[46 + v]);
+      // (a batch's value buffers are addressed by int32 offsets: its new keys cannot add 4 GB, the scan cannot wrap)
+      if (gb->wheap_used + add > gb->wheap_cap) {
+        uint64_t cap = std::max<uint64_t>(1 << 20, gb->wheap_cap);
+        while (cap < gb->wheap_used + add) cap <<= 1;
+        uint8_t* nh = nullptr;
+        B200_RETURN_NOT_OK(b200_dev_alloc(ctx, reinterpret_cast<void**>(&nh), cap));
+        if (gb->wheap_used) B200_CUDA(ctx, cudaMemcpyAsync(nh, gb->wheap, gb->wheap_used, cudaMemcpyDeviceToDevice, ctx->stream));
+        if (gb->wheap) {
+          B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+          b200_dev_free(ctx, gb->wheap);
+        }
+        gb->wheap = nh;
+        gb->wheap_cap = cap;
+      }
+      a.heap = gb->wheap;
+      wide_assign_kernel<<<(n_new + 255) / 256, 256, 0, ctx->stream>>>(a, n_new, gb->wcount, gb->wheap_used);
+      B200_LAUNCHED(ctx);
+      gb->wheap_used += add;
+    } else {
+      wide_assign_kernel<<<(n_new + 255) / 256, 256, 0, ctx->stream>>>(a, n_new, gb->wcount, 0);
+      B200_LAUNCHED(ctx);
+    }
     gb->wcount += n_new;
   }
   B200_TIMED(ctx, "groupby_wide_keys", (wide_ids_kernel<<<grid, 256, 0, ctx->stream>>>(a)));
@@ -3377,6 +3466,20 @@ int wide_translate(b200_groupby* gb, const b200_col* keys, const uint32_t* selec
     B200_RETURN_NOT_OK(wide_translate((gb), (keys), (select), &_narrow_key)); \
     (keys) = &_narrow_key;                                                   \
   }
+
+int b200_groupby_key_bytes(b200_groupby* gb, int key_index, int64_t* out_bytes) {
+  if (!gb || !out_bytes) return B200_INVALID;
+  *out_bytes = 0;
+  if (!gb->wide) return key_index >= 0 && key_index < gb->schema.n_keys ? B200_OK : b200_fail(gb->ctx, B200_INVALID, "groupby_key_bytes: no key %d", key_index);
+  if (key_index < 0 || key_index >= gb->wn_keys) return b200_fail(gb->ctx, B200_INVALID, "groupby_key_bytes: no key %d", key_index);
+  if (gb->wvar_index[key_index] >= 0) {
+    const uint64_t b = gb->wvar_bytes_host[gb->wvar_index[key_index]];
+    // BinaryType's offsets are int32 (VarLengthKeyEncoder::Decode sums into Offset, hash_aggregate.cc:282-285)
+    if (b > 0x7FFFFFFFull) return b200_fail(gb->ctx, B200_CAPACITY_ERROR, "groupby: %llu bytes of distinct keys in column %d exceed int32 offsets", (unsigned long long)b, key_index);
+    *out_bytes = int64_t(b);
+  }
+  return B200_OK;
+}
 
 int b200_groupby_set_option(b200_groupby* gb, const char* name, int64_t value) {
   B200_ENTER(gb ? gb->ctx : nullptr);
@@ -4271,15 +4374,39 @@ int b200_groupby_finalize(b200_groupby* gb, b200_out_col* out_aggs, b200_out_col
     d.words = gb->wwords;
     d.n_keys = gb->wn_keys;
     d.null_counts = wide_ids + ((size_t(std::max<uint32_t>(G, 1)) * 4 + 255) / 256 * 256) / 4;
+    d.n_var = gb->wn_var;
+    d.store_var = gb->wstore_var;
+    d.heap = gb->wheap;
     for (int k = 0; k < gb->wn_keys; ++k) {
       d.nbits[k] = gb->wbits[k];
       d.byte_off[k] = gb->woff[k];
       d.data[k] = out_keys[k].data;
       d.validity[k] = reinterpret_cast<uint32_t*>(out_keys[k].validity);
+      d.var_index[k] = gb->wvar_index[k];
+      d.out_bytes[k] = reinterpret_cast<uint8_t*>(out_keys[k].extra);
+      if (gb->wtypes[k] == B200_BINARY && G > 0 && gb->wvar_bytes_host[gb->wvar_index[k]] > 0 && !out_keys[k].extra) {
+        b200_dev_free(ctx, wide_ids);
+        return b200_fail(ctx, B200_INVALID, "groupby_finalize: variable-length key %d has no value buffer (b200_groupby_key_bytes)", k);
+      }
     }
     B200_CUDA(ctx, cudaMemsetAsync(d.null_counts, 0, kWideMaxKeys * sizeof(uint32_t), ctx->stream));
     if (G > 0) {
       wide_decode_kernel<<<(G + 255) / 256, 256, 0, ctx->stream>>>(d);
+      B200_LAUNCHED(ctx);
+    }
+    // variable-length keys: the lengths just written become the int32 offsets (one scan per column), then the bytes
+    for (int k = 0; k < gb->wn_keys; ++k) {
+      if (gb->wtypes[k] != B200_BINARY) continue;
+      uint32_t* off = reinterpret_cast<uint32_t*>(out_keys[k].data);
+      if (G == 0) {
+        if (off) B200_CUDA(ctx, cudaMemsetAsync(off, 0, sizeof(uint32_t), ctx->stream));
+        continue;
+      }
+      gb_hp_scan_kernel<<<1, 1024, 0, ctx->stream>>>(off, G, nullptr, off);
+      B200_LAUNCHED(ctx);
+    }
+    if (G > 0 && gb->wn_var) {
+      wide_decode_bytes_kernel<<<(G + 255) / 256, 256, 0, ctx->stream>>>(d);
       B200_LAUNCHED(ctx);
     }
     B200_CUDA(ctx, cudaMemcpyAsync(ctx->host_words + 44, d.null_counts, kWideMaxKeys * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));

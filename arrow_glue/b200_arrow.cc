@@ -228,12 +228,41 @@ Result<int32_t> PhysicalType(const DataType& type) {
 // hash_aggregate.cc:198-233: the indices are the key, the dictionary rides along)
 Result<int32_t> KeyPhysicalType(const DataType& type) {
   if (type.id() == Type::DICTIONARY) return PhysicalType(*checked_cast<const DictionaryType&>(type).index_type());
+  // VarLengthKeyEncoder<BinaryType / StringType> (hash_aggregate.cc:344-347); the 64-bit-offset forms are not bound
+  if (type.id() == Type::BINARY || type.id() == Type::STRING) return B200_BINARY;
   if (type.id() != Type::BOOL && !is_primitive(type.id())) return Status::NotImplemented("Keys of type ", type.ToString());
   return PhysicalType(type);
 }
 int KeyBitWidth(const DataType& type) {
   if (type.id() == Type::DICTIONARY) return checked_cast<const FixedWidthType&>(*checked_cast<const DictionaryType&>(type).index_type()).bit_width();
   return checked_cast<const FixedWidthType&>(type).bit_width();
+}
+// the buffers of one key column of `num_groups` groups, sized for b200_groupby_finalize
+struct KeyOut {
+  std::shared_ptr<Buffer> data, validity, bytes;   // bytes: variable-length keys only (data = int32 offsets)
+};
+Result<KeyOut> AllocateKeyOut(DeviceState* dev, b200_groupby* gb, int key_index, int32_t key_type, const DataType& type,
+                              uint32_t num_groups, b200_out_col* out) {
+  KeyOut k;
+  std::memset(out, 0, sizeof(*out));
+  if (key_type == B200_BINARY) {
+    int64_t nbytes = 0;
+    B200_OK_OR_RAISE(dev, b200_groupby_key_bytes(gb, key_index, &nbytes));
+    ARROW_ASSIGN_OR_RAISE(k.data, AllocateDevice(dev, (int64_t(num_groups) + 1) * 4));
+    ARROW_ASSIGN_OR_RAISE(k.bytes, AllocateDevice(dev, nbytes));
+    out->extra = reinterpret_cast<void*>(k.bytes->address());
+  } else {
+    const int bits = key_type == B200_BOOL ? 1 : KeyBitWidth(type);
+    ARROW_ASSIGN_OR_RAISE(k.data, AllocateDevice(dev, bits == 1 ? BitmapBytes(num_groups) : int64_t(num_groups) * (bits / 8)));
+  }
+  ARROW_ASSIGN_OR_RAISE(k.validity, AllocateDevice(dev, BitmapBytes(num_groups)));
+  out->data = reinterpret_cast<void*>(k.data->address());
+  out->validity = reinterpret_cast<void*>(k.validity->address());
+  return k;
+}
+std::shared_ptr<ArrayData> KeyArrayData(const std::shared_ptr<DataType>& type, uint32_t num_groups, const KeyOut& k, int64_t nulls) {
+  if (k.bytes) return ArrayData::Make(type, num_groups, {nulls ? k.validity : nullptr, k.data, k.bytes}, nulls);
+  return ArrayData::Make(type, num_groups, {nulls ? k.validity : nullptr, k.data}, nulls);
 }
 // every batch of a dictionary key must carry the first batch's dictionary ("Unifying differing dictionaries" is
 // NotImplemented upstream too, hash_aggregate.cc:205-210); device dictionaries are compared by identity
@@ -271,6 +300,11 @@ Status ToCol(const ArrayData& a, int32_t type, b200_col* c) {
   RETURN_NOT_OK(CheckOnDevice(a.buffers[0], "validity"));
   RETURN_NOT_OK(CheckOnDevice(a.buffers[1], "data"));
   std::memset(c, 0, sizeof(*c));
+  if (type == B200_BINARY) {   // offsets in buffers[1], value bytes in buffers[2]
+    if (a.buffers.size() < 3) return Status::Invalid("expected a binary array layout");
+    RETURN_NOT_OK(CheckOnDevice(a.buffers[2], "value"));
+    c->extra = a.buffers[2] ? reinterpret_cast<const void*>(a.buffers[2]->address()) : nullptr;
+  }
   c->validity = a.buffers[0] ? reinterpret_cast<const void*>(a.buffers[0]->address()) : nullptr;
   c->data = a.buffers[1] ? reinterpret_cast<const void*>(a.buffers[1]->address()) : nullptr;
   c->type = type;
@@ -1010,21 +1044,13 @@ class CudaGrouper : public internal::Grouper {
                                           const std::vector<int32_t>& key_types, uint32_t num_groups) {
     DeviceState* dev = h->dev;
     std::vector<b200_out_col> outs(types.size());
-    std::vector<std::shared_ptr<Buffer>> data(types.size()), validity(types.size());
+    std::vector<KeyOut> bufs(types.size());
     for (size_t k = 0; k < types.size(); ++k) {
-      const int bits = key_types[k] == B200_BOOL ? 1 : KeyBitWidth(*types[k]);
-      ARROW_ASSIGN_OR_RAISE(data[k], AllocateDevice(dev, bits == 1 ? BitmapBytes(num_groups) : int64_t(num_groups) * (bits / 8)));
-      ARROW_ASSIGN_OR_RAISE(validity[k], AllocateDevice(dev, BitmapBytes(num_groups)));
-      std::memset(&outs[k], 0, sizeof(b200_out_col));
-      outs[k].data = reinterpret_cast<void*>(data[k]->address());
-      outs[k].validity = reinterpret_cast<void*>(validity[k]->address());
+      ARROW_ASSIGN_OR_RAISE(bufs[k], AllocateKeyOut(dev, h->gb, int(k), key_types[k], *types[k], num_groups, &outs[k]));
     }
     B200_OK_OR_RAISE(dev, b200_groupby_finalize(h->gb, nullptr, outs.data()));
     ArrayDataVector result;
-    for (size_t k = 0; k < types.size(); ++k) {
-      const int64_t nulls = outs[k].null_count;
-      result.push_back(ArrayData::Make(types[k], num_groups, {nulls ? validity[k] : nullptr, data[k]}, nulls));
-    }
+    for (size_t k = 0; k < types.size(); ++k) result.push_back(KeyArrayData(types[k], num_groups, bufs[k], outs[k].null_count));
     return result;
   }
 
@@ -1064,10 +1090,11 @@ class CudaHashMetaFunction : public MetaFunction {
     const bool is_dict = type->id() == Type::DICTIONARY;
     if (is_dict && op_ == HashOp::kDictionaryEncode) return Status::NotImplemented("dictionary_encode of a dictionary array");
     const std::shared_ptr<DataType> value_type = is_dict ? checked_cast<const DictionaryType&>(*type).index_type() : type;
-    if (value_type->id() != Type::BOOL && !is_primitive(value_type->id())) {
-      return Status::NotImplemented("CUDA-backed ", name(), " handles fixed-width primitive columns, got ", type->ToString());
+    const bool is_var = value_type->id() == Type::BINARY || value_type->id() == Type::STRING;
+    if (!is_var && value_type->id() != Type::BOOL && !is_primitive(value_type->id())) {
+      return Status::NotImplemented("CUDA-backed ", name(), " handles fixed-width primitive and binary / utf8 columns, got ", type->ToString());
     }
-    ARROW_ASSIGN_OR_RAISE(const int32_t ktype, PhysicalType(*value_type));
+    ARROW_ASSIGN_OR_RAISE(const int32_t ktype, KeyPhysicalType(*value_type));
     std::shared_ptr<ArrayData> dictionary;
     if (is_dict) {
       for (const auto& c : chunks) {
@@ -1086,7 +1113,7 @@ class CudaHashMetaFunction : public MetaFunction {
     b200_agg_spec count_all;
     std::memset(&count_all, 0, sizeof(count_all));
     count_all.kind = B200_HASH_COUNT;
-    count_all.arg_type = ktype;
+    count_all.arg_type = is_var ? B200_INT32 : ktype;   // (a binary column is counted through its offsets buffer)
     const bool counts = op_ == HashOp::kValueCounts;
     B200_OK_OR_RAISE(dev, b200_groupby_create(dev->ctx, 1, &ktype, counts ? 1 : 0, counts ? &count_all : nullptr, 0, &handle.gb));
     std::vector<std::shared_ptr<Buffer>> id_chunks;
@@ -1104,6 +1131,8 @@ class CudaHashMetaFunction : public MetaFunction {
         b200_col all_rows = key;
         all_rows.validity = nullptr;
         all_rows.null_count = 0;
+        all_rows.type = count_all.arg_type;
+        all_rows.extra = nullptr;
         B200_OK_OR_RAISE(dev, b200_groupby_consume(handle.gb, &key, counts ? &all_rows : nullptr, row_base));
       }
       row_base += uint64_t(c->length());
@@ -1113,19 +1142,13 @@ class CudaHashMetaFunction : public MetaFunction {
     std::shared_ptr<ArrayData> uniques, count_data;
     if (counts) {
       std::vector<b200_out_col> key_outs(1);
-      const int bits = ktype == B200_BOOL ? 1 : checked_cast<const FixedWidthType&>(*value_type).bit_width();
-      ARROW_ASSIGN_OR_RAISE(auto kdata, AllocateDevice(dev, bits == 1 ? BitmapBytes(num_groups) : int64_t(num_groups) * (bits / 8)));
-      ARROW_ASSIGN_OR_RAISE(auto kvalid, AllocateDevice(dev, BitmapBytes(num_groups)));
-      std::memset(&key_outs[0], 0, sizeof(b200_out_col));
-      key_outs[0].data = reinterpret_cast<void*>(kdata->address());
-      key_outs[0].validity = reinterpret_cast<void*>(kvalid->address());
+      ARROW_ASSIGN_OR_RAISE(auto kbuf, AllocateKeyOut(dev, handle.gb, 0, ktype, *value_type, num_groups, &key_outs[0]));
       AggInfo info;
       info.kind = B200_HASH_COUNT;
       info.out_type = int64();
       ARROW_ASSIGN_OR_RAISE(auto aggs, FinalizeAggregates(&handle, {info}, {value_type}, num_groups, &key_outs));
       count_data = aggs[0];
-      const int64_t nulls = key_outs[0].null_count;
-      uniques = ArrayData::Make(type, num_groups, {nulls ? kvalid : nullptr, kdata}, nulls);
+      uniques = KeyArrayData(type, num_groups, kbuf, key_outs[0].null_count);
     } else {
       ARROW_ASSIGN_OR_RAISE(auto keys, CudaGrouper::EmitKeys(&handle, {type}, {ktype}, num_groups));
       uniques = keys[0];
@@ -1156,12 +1179,24 @@ class CudaHashMetaFunction : public MetaFunction {
           null_group = g;
           break;
         }
-      auto as_mask = ArrayData::Make(boolean(), num_groups, {nullptr, uniques->buffers[0]}, 0);
-      lock.unlock();
-      ARROW_ASSIGN_OR_RAISE(dict_values, FilterArray(dev, *uniques, *as_mask, 0 /* DROP */));
-      lock.lock();
-      dict_values->buffers[0] = nullptr;   // every entry left is valid
-      dict_values->null_count = 0;
+      if (is_var) {
+        // the null entry holds no bytes: the value buffer stays, the offsets lose entry null_group + 1
+        // (== entry null_group).  Two device-to-device copies.
+        ARROW_ASSIGN_OR_RAISE(auto offsets, AllocateDevice(dev, int64_t(num_groups) * 4));
+        const uintptr_t src = uniques->buffers[1]->address();
+        const int64_t head = (null_group + 1) * 4, tail = (int64_t(num_groups) - 1 - null_group) * 4;
+        ARROW_ASSIGN_OR_RAISE(auto cuda_offsets, ::arrow::cuda::CudaBuffer::FromBuffer(offsets));
+        RETURN_NOT_OK(cuda_offsets->CopyFromDevice(0, reinterpret_cast<const void*>(src), head));
+        if (tail > 0) RETURN_NOT_OK(cuda_offsets->CopyFromDevice(head, reinterpret_cast<const void*>(src + head + 4), tail));
+        dict_values = ArrayData::Make(type, int64_t(num_groups) - 1, {nullptr, std::move(offsets), uniques->buffers[2]}, 0);
+      } else {
+        auto as_mask = ArrayData::Make(boolean(), num_groups, {nullptr, uniques->buffers[0]}, 0);
+        lock.unlock();
+        ARROW_ASSIGN_OR_RAISE(dict_values, FilterArray(dev, *uniques, *as_mask, 0 /* DROP */));
+        lock.lock();
+        dict_values->buffers[0] = nullptr;   // every entry left is valid
+        dict_values->null_count = 0;
+      }
     }
     auto dict_type = ::arrow::dictionary(int32(), type);
     ArrayVector out_chunks;
@@ -1566,21 +1601,15 @@ Result<Datum> GroupBy(const std::vector<Datum>& arguments, const std::vector<Dat
 
   // outputs: aggregates then keys (hash_aggregate.cc:946-965)
   std::vector<b200_out_col> key_outs(keys.size());
-  std::vector<std::shared_ptr<Buffer>> key_data(keys.size()), key_validity(keys.size());
+  std::vector<KeyOut> key_bufs(keys.size());
   for (size_t k = 0; k < keys.size(); ++k) {
-    const int bits = key_types[k] == B200_BOOL ? 1 : KeyBitWidth(*key_dtypes[k]);
-    ARROW_ASSIGN_OR_RAISE(key_data[k], AllocateDevice(dev, bits == 1 ? BitmapBytes(num_groups) : int64_t(num_groups) * (bits / 8)));
-    ARROW_ASSIGN_OR_RAISE(key_validity[k], AllocateDevice(dev, BitmapBytes(num_groups)));
-    std::memset(&key_outs[k], 0, sizeof(b200_out_col));
-    key_outs[k].data = reinterpret_cast<void*>(key_data[k]->address());
-    key_outs[k].validity = reinterpret_cast<void*>(key_validity[k]->address());
+    ARROW_ASSIGN_OR_RAISE(key_bufs[k], AllocateKeyOut(dev, handle.gb, int(k), key_types[k], *key_dtypes[k], num_groups, &key_outs[k]));
   }
   ARROW_ASSIGN_OR_RAISE(auto out_data, FinalizeAggregates(&handle, infos, arg_types, num_groups, &key_outs));
   FieldVector out_fields;
   for (size_t i = 0; i < aggregates.size(); ++i) out_fields.push_back(field(aggregates[i].function, infos[i].out_type));
   for (size_t k = 0; k < keys.size(); ++k) {
-    const int64_t nulls = key_outs[k].null_count;
-    out_data.push_back(ArrayData::Make(key_dtypes[k], num_groups, {nulls ? key_validity[k] : nullptr, key_data[k]}, nulls));
+    out_data.push_back(KeyArrayData(key_dtypes[k], num_groups, key_bufs[k], key_outs[k].null_count));
     if (key_dtypes[k]->id() == Type::DICTIONARY) {
       if (key_dictionaries[k]) {
         out_data.back()->dictionary = key_dictionaries[k];

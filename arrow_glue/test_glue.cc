@@ -700,6 +700,67 @@ int main() {
       auto st = cp::cuda::GroupBy({Datum(vals2)}, {Datum(two)}, {{"hash_sum", nullptr}}, &gpu_ctx).status();
       CHECK_TRUE(st.IsNotImplemented(), "GroupBy: batches with differing key dictionaries -> NotImplemented");
     }
+    // binary / utf8 keys (VarLengthKeyEncoder, hash_aggregate.cc:236-311) and the hash kernels on strings
+    {
+      std::vector<std::string> vocab = {"", "a", std::string("a\0", 2), std::string("a\0b", 3), "ab", "abc", "abcdefgh", "abcdefghi"};
+      std::uniform_int_distribution<int> len(0, 20), byte(0, 255);
+      while (vocab.size() < 400) {
+        std::string w(size_t(len(rng)), '\0');
+        for (auto& ch : w) ch = char(byte(rng) & 0x7F);   // ASCII: utf8 arrays must pass ValidateFull
+        vocab.push_back(w);
+      }
+      std::uniform_int_distribution<size_t> pick(0, vocab.size() - 1);
+      std::uniform_real_distribution<double> u(0, 1);
+      StringBuilder sb;
+      BinaryBuilder bb;
+      for (int64_t i = 0; i < n; ++i) {
+        if (u(rng) < 0.05) { ABORT_NOT_OK(sb.AppendNull()); ABORT_NOT_OK(bb.AppendNull()); continue; }
+        const std::string& w = vocab[pick(rng)];
+        ABORT_NOT_OK(sb.Append(w));
+        ABORT_NOT_OK(bb.Append(w));
+      }
+      auto strings = GET(sb.Finish());
+      auto binaries = GET(bb.Finish());
+      auto vals = MakeRandom<DoubleBuilder, double>(n, rng, 0.05, 0.0, 1.0, true);
+      auto ikeys = MakeRandom<Int32Builder, int32_t>(n, rng, 0.05, 0, 4, false);
+      std::vector<cp::internal::Aggregate> aggs = {{"hash_sum", nullptr}, {"hash_count", nullptr}, {"hash_min_max", nullptr}};
+      for (auto& kc : std::vector<std::pair<std::string, std::vector<std::shared_ptr<Array>>>>{
+               {"utf8", {strings}}, {"binary", {binaries}}, {"utf8 + int32", {strings, ikeys}}, {"int32 + binary + utf8", {ikeys, binaries, strings}}}) {
+        std::vector<Datum> hk, dk;
+        for (auto& k : kc.second) { hk.push_back(k); dk.push_back(DeviceDatum(k)); }
+        auto want = GET(cp::internal::GroupBy({vals, vals, vals}, hk, aggs, &cpu_ctx)).make_array();
+        auto got = HostArray(GET(cp::cuda::GroupBy({DeviceDatum(vals), DeviceDatum(vals), DeviceDatum(vals)}, dk, aggs, &gpu_ctx)));
+        ExpectStructClose(got, want, "GroupBy keyed by " + kc.first);
+      }
+      // chunked: later chunks bring new strings
+      {
+        auto ck = Chunked(strings, {0, 100, 100, n / 2, n}), cv = Chunked(vals, {0, 100, 100, n / 2, n});
+        auto want = GET(cp::internal::GroupBy({Datum(cv)}, {Datum(ck)}, {{"hash_sum", nullptr}}, &cpu_ctx)).make_array();
+        auto got = HostArray(GET(cp::cuda::GroupBy({Datum(DeviceChunked(*cv))}, {Datum(DeviceChunked(*ck))}, {{"hash_sum", nullptr}}, &gpu_ctx)));
+        ExpectStructClose(got, want, "GroupBy keyed by utf8, chunked");
+      }
+      auto dev = DeviceDatum(strings);
+      ExpectEqual(HostArray(GET(cp::CallFunction("unique", {dev}, &gpu_ctx))), GET(cp::CallFunction("unique", {Datum(strings)}, &cpu_ctx)).make_array(),
+                  "unique utf8");
+      ExpectEqual(HostArray(GET(cp::CallFunction("value_counts", {dev}, &gpu_ctx))),
+                  GET(cp::CallFunction("value_counts", {Datum(strings)}, &cpu_ctx)).make_array(), "value_counts utf8");
+      cp::DictionaryEncodeOptions mask_opts(cp::DictionaryEncodeOptions::MASK), encode_opts(cp::DictionaryEncodeOptions::ENCODE);
+      for (auto* opts : {&mask_opts, &encode_opts}) {
+        auto want = GET(cp::CallFunction("dictionary_encode", {Datum(strings)}, opts, &cpu_ctx)).make_array();
+        auto got = HostArray(GET(cp::CallFunction("dictionary_encode", {dev}, opts, &gpu_ctx)));
+        ExpectEqual(got, want, std::string("dictionary_encode utf8 ") + (opts == &mask_opts ? "MASK" : "ENCODE"));
+      }
+      // the Grouper twin on (utf8, int32)
+      auto cpu_grouper = GET(cp::internal::Grouper::Make({ValueDescr::Array(utf8()), ValueDescr::Array(int32())}, &cpu_ctx));
+      auto gpu_grouper = GET(cp::cuda::MakeGrouper({ValueDescr::Array(utf8()), ValueDescr::Array(int32())}, &gpu_ctx));
+      auto want_ids = GET(cpu_grouper->Consume(GET(cp::ExecBatch::Make({Datum(strings), Datum(ikeys)})))).make_array();
+      auto got_ids = HostArray(GET(gpu_grouper->Consume(GET(cp::ExecBatch::Make({dev, DeviceDatum(ikeys)})))));
+      ExpectEqual(got_ids, want_ids, "Grouper::Consume ids keyed by (utf8, int32)");
+      auto want_u = GET(cpu_grouper->GetUniques());
+      auto got_u = GET(gpu_grouper->GetUniques());
+      ExpectEqual(HostArray(got_u[0]), want_u[0].make_array(), "Grouper::GetUniques utf8 column");
+      ExpectEqual(HostArray(got_u[1]), want_u[1].make_array(), "Grouper::GetUniques int32 column");
+    }
     // MakeGroupings / ApplyGroupings (hash_aggregate.cc:968-1018) over the Grouper twin's ids
     {
       auto keys = MakeRandom<Int32Builder, int32_t>(n, rng, 0.05, 0, 700, false);

@@ -59,7 +59,11 @@ typedef enum b200_type {
   B200_UINT64 = 8,
   B200_INT64 = 9,
   B200_FLOAT = 11,
-  B200_DOUBLE = 12
+  B200_DOUBLE = 12,
+  /* binary / utf8 with int32 offsets (BinaryType, StringType).  GROUP KEYS ONLY (VarLengthKeyEncoder,
+   * hash_aggregate.cc:236-311): `data` = the int32 offsets buffer (length + 1 entries past `offset`),
+   * `extra` = the value bytes. */
+  B200_BINARY = 13
 } b200_type;
 
 /* Device column descriptor: mirror of compute::internal::PrimitiveArg
@@ -74,6 +78,7 @@ typedef struct b200_col {
   int64_t length;       /* elements                                                        */
   int64_t offset;       /* elements (bits for bitmaps)                                     */
   int64_t null_count;   /* -1 = unknown (kUnknownNullCount); ignored if validity == NULL   */
+  const void* extra;    /* device; B200_BINARY: the value bytes (buffers[2]); NULL otherwise */
 } b200_col;
 
 /* Mutable twin used for outputs the library fills. */
@@ -84,6 +89,7 @@ typedef struct b200_out_col {
   int32_t reserved;
   int64_t length;
   int64_t null_count; /* filled by the library: exact count or -1 */
+  void* extra;        /* device; B200_BINARY outputs: the value bytes (`data` = int32 offsets, length + 1 entries) */
 } b200_out_col;
 
 typedef struct b200_ctx b200_ctx;
@@ -352,13 +358,19 @@ typedef struct b200_agg_spec {
 typedef struct b200_groupby b200_groupby;
 
 /* == Grouper::Make + GetKernels/InitKernels (hash_aggregate.cc:314-356, 809-859).
- * Keys: 1..4 fixed-width columns (B200_BOOL..B200_DOUBLE) whose packed width is <= 64 bits;
- * otherwise B200_NOT_IMPLEMENTED, as GrouperImpl::Make does for unsupported key types.
+ * Keys: 1..16 columns, fixed-width (B200_BOOL..B200_DOUBLE) or variable-length (B200_BINARY: binary / utf8 with
+ * int32 offsets).  Up to 4 fixed-width columns of <= 64 packed bits are grouped on a packed register key; anything
+ * else goes through a key -> id table first (csrc/groupby_wide.cuh).  Other key types: B200_NOT_IMPLEMENTED, as
+ * GrouperImpl::Make does ("Keys of type ...", hash_aggregate.cc:352).
  * expected_groups: sizing hint for the open-addressing table (0 = unknown, the table grows). */
 B200_API int b200_groupby_create(b200_ctx* ctx, int n_keys, const int32_t* key_types, int n_aggs,
                                  const b200_agg_spec* aggs, int64_t expected_groups,
                                  b200_groupby** out);
 B200_API int b200_groupby_destroy(b200_groupby* gb);
+/* Bytes the value buffer of variable-length key column `key_index` needs at b200_groupby_finalize (== the sum of
+ * the distinct keys' lengths, what VarLengthKeyEncoder::Decode adds up, hash_aggregate.cc:282-285); 0 for a
+ * fixed-width key.  Call it after the last consume. */
+B200_API int b200_groupby_key_bytes(b200_groupby* gb, int key_index, int64_t* out_bytes);
 /* Execution knobs of a handle (no reference counterpart; results never depend on them).  Names:
  *   "hp_min_rows" / "hp_min_groups"   batch size and expected cardinality from which a consume call takes the
  *                                     partition-then-aggregate path (defaults 2^22 rows, 2^21 groups)

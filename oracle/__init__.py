@@ -24,7 +24,7 @@ _ROOT = os.path.dirname(_HERE)
 if _ROOT not in sys.path:
     sys.path.insert(0, _ROOT)
 
-from arrow1_b200.columns import (BITS, BOOL, HASH_MIN_MAX, HASH_SUM, NP_OF, AggSpec, Column, agg_out_types,  # noqa: E402
+from arrow1_b200.columns import (BINARY, BITS, BOOL, HASH_MIN_MAX, HASH_SUM, NP_OF, AggSpec, Column, agg_out_types,  # noqa: E402
                                  b200_agg_spec, b200_col, b200_out_col, col_array, unpack_bits)
 
 PORT_SO = os.path.join(_HERE, "_build", "liboracle.so")
@@ -44,14 +44,15 @@ def _run(cmd: List[str]) -> None:
 def build(force: bool = False) -> None:
     """Compiles the C++ restatement and, when /root/reference is present, the reference driver."""
     src = os.path.join(_HERE, "oracle.cc")
+    hdr = os.path.getmtime(os.path.join(_ROOT, "include", "arrow1_b200.h"))   # b200_col lives there
     os.makedirs(os.path.dirname(PORT_SO), exist_ok=True)
-    if force or not os.path.exists(PORT_SO) or os.path.getmtime(PORT_SO) < os.path.getmtime(src):
+    if force or not os.path.exists(PORT_SO) or os.path.getmtime(PORT_SO) < max(os.path.getmtime(src), hdr):
         _run(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-I", os.path.join(_ROOT, "include"), src, "-o", PORT_SO])
     if os.path.isdir(REFERENCE_SRC):
         drv = os.path.join(_HERE, "ref_driver.cc")
         if force or not os.path.exists(REF_LIB):
             _run(["bash", os.path.join(_HERE, "build_ref.sh")])
-        if force or not os.path.exists(REF_SO) or os.path.getmtime(REF_SO) < max(os.path.getmtime(drv), os.path.getmtime(REF_LIB)):
+        if force or not os.path.exists(REF_SO) or os.path.getmtime(REF_SO) < max(os.path.getmtime(drv), os.path.getmtime(REF_LIB), hdr):
             _run(["g++", "-std=c++11", "-O2", "-fPIC", "-shared", "-w", "-include", "limits", "-include", "cstdint",
                   "-DARROW_STATIC", "-I", os.path.join(_HERE, "_ref", "include"), "-I", REFERENCE_SRC,
                   "-I", os.path.join(_ROOT, "include"), drv, "-o", REF_SO, REF_LIB, "-lpthread", "-ldl"])
@@ -101,8 +102,15 @@ def _check(kind: str, code: int) -> None:
         raise OracleError(code, msg)
 
 
-def _out_col(type_: int, n: int):
-    """Allocates host output buffers for n elements; returns (struct, data, validity)."""
+def _out_col(type_: int, n: int, extra_cap: int = 0):
+    """Allocates host output buffers for n elements; returns (struct, data, validity).  BINARY (reference only):
+    `data` is the pair (int32 offsets [n + 1], value bytes [extra_cap])."""
+    if type_ == BINARY:
+        offs = np.zeros(n + 2, dtype=np.int32)
+        blob = np.zeros(max(extra_cap, 1) + 8, dtype=np.uint8)
+        validity = np.zeros((n + 7) // 8 + 8, dtype=np.uint8)
+        oc = b200_out_col(validity.ctypes.data, offs.ctypes.data, type_, 0, 0, 0, blob.ctypes.data)
+        return oc, (offs, blob), validity
     bits = BITS[type_]
     nbytes = (n + 7) // 8 + 8 if bits == 1 else n * (bits // 8) + 8
     data = np.zeros(nbytes, dtype=np.uint8)
@@ -111,7 +119,15 @@ def _out_col(type_: int, n: int):
     return oc, data, validity
 
 
-def _decode(type_: int, data: np.ndarray, validity: np.ndarray, n: int):
+def _decode(type_: int, data, validity: np.ndarray, n: int):
+    if type_ == BINARY:
+        offs, blob = data
+        valid = unpack_bits(validity, n)
+        raw = blob.tobytes()
+        vals = np.empty(n, dtype=object)
+        for i in range(n):
+            vals[i] = raw[offs[i]: offs[i + 1]] if valid[i] else b""
+        return vals, valid
     if type_ == BOOL:
         vals = unpack_bits(data, n)
     else:
@@ -212,7 +228,7 @@ def groupby(keys: Sequence[Column], aggs: Sequence[AggSpec], args: Sequence[Colu
     out_keys = (b200_out_col * len(keys))()
     key_holders = []
     for i, k in enumerate(keys):
-        oc, d, v = _out_col(k.type, cap)
+        oc, d, v = _out_col(k.type, cap, 0 if k.extra is None else len(k.extra))
         out_keys[i] = oc
         key_holders.append((k.type, d, v))
     ids = np.zeros(max(n, 1), dtype=np.uint32) if want_ids else None
@@ -281,7 +297,7 @@ def value_counts(values: Column, want_counts: bool = True):
     """"unique" / "value_counts" of the reference (vector_hash.cc): ((values, valid), counts or None) in
     first-occurrence order."""
     n = values.length
-    oc, d, v = _out_col(values.type, max(n, 1))
+    oc, d, v = _out_col(values.type, max(n, 1), 0 if values.extra is None else len(values.extra))
     counts = np.zeros(max(n, 1), dtype=np.int64)
     out_n = C.c_int64(0)
     _check("reference", _fn("reference", "value_counts")(C.byref(values.desc()), C.byref(oc),
@@ -296,7 +312,7 @@ def dictionary_encode(values: Column, encode_nulls: bool = False):
     n = values.length
     idx = np.zeros(max(n, 1), dtype=np.int32)
     valid = np.zeros(max(n, 1), dtype=np.uint8)
-    oc, d, v = _out_col(values.type, max(n, 1))
+    oc, d, v = _out_col(values.type, max(n, 1), 0 if values.extra is None else len(values.extra))
     out_n = C.c_int64(0)
     _check("reference", _fn("reference", "dictionary_encode")(C.byref(values.desc()), C.c_int(1 if encode_nulls else 0),
                                                                 idx.ctypes.data_as(C.c_void_p), valid.ctypes.data_as(C.c_void_p),

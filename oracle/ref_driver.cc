@@ -47,6 +47,7 @@ std::shared_ptr<DataType> TypeOf(int t) {
     case B200_INT64: return int64();
     case B200_FLOAT: return float32();
     case B200_DOUBLE: return float64();
+    case B200_BINARY: return binary();
   }
   return nullptr;
 }
@@ -66,6 +67,13 @@ std::shared_ptr<ArrayData> Wrap(const b200_col& c) {
   const int64_t n = c.offset + c.length;
   std::shared_ptr<Buffer> validity;
   if (c.validity) validity = std::make_shared<Buffer>(static_cast<const uint8_t*>(c.validity), BitUtil::BytesForBits(n));
+  if (c.type == B200_BINARY) {   // data = int32 offsets, extra = value bytes
+    const int32_t* offs = static_cast<const int32_t*>(c.data);
+    auto offsets = std::make_shared<Buffer>(static_cast<const uint8_t*>(c.data), (n + 1) * 4);
+    static const uint8_t kNoBytes[1] = {0};
+    auto bytes = std::make_shared<Buffer>(c.extra ? static_cast<const uint8_t*>(c.extra) : kNoBytes, offs[n]);
+    return ArrayData::Make(binary(), c.length, {validity, offsets, bytes}, c.validity ? c.null_count : 0, c.offset);
+  }
   auto data = std::make_shared<Buffer>(static_cast<const uint8_t*>(c.data),
                                        bits == 1 ? BitUtil::BytesForBits(n) : n * (bits / 8));
   return ArrayData::Make(TypeOf(c.type), c.length, {validity, data}, c.validity ? c.null_count : 0, c.offset);
@@ -73,9 +81,22 @@ std::shared_ptr<ArrayData> Wrap(const b200_col& c) {
 
 // copies an Arrow primitive array into caller buffers (offset 0 on the output side)
 void CopyOut(const ArrayData& a, b200_out_col* out) {
-  const int bits = arrow::internal::checked_cast<const FixedWidthType&>(*a.type).bit_width();
   out->length = a.length;
   out->null_count = a.null_count.load();
+  if (a.type->id() == Type::BINARY || a.type->id() == Type::STRING) {
+    // offsets rebased to 0 into out->data (length + 1 entries), the bytes into out->extra
+    const int32_t* offs = a.GetValues<int32_t>(1);
+    int32_t* dst = static_cast<int32_t*>(out->data);
+    for (int64_t i = 0; i <= a.length; ++i) dst[i] = offs[i] - offs[0];
+    if (out->extra && a.buffers[2] && dst[a.length] > 0) std::memcpy(out->extra, a.buffers[2]->data() + offs[0], size_t(dst[a.length]));
+    if (out->validity) {
+      std::memset(out->validity, 0, BitUtil::BytesForBits(a.length));
+      if (a.buffers[0]) arrow::internal::CopyBitmap(a.buffers[0]->data(), a.offset, a.length, static_cast<uint8_t*>(out->validity), 0);
+      else BitUtil::SetBitsTo(static_cast<uint8_t*>(out->validity), 0, a.length, true);
+    }
+    return;
+  }
+  const int bits = arrow::internal::checked_cast<const FixedWidthType&>(*a.type).bit_width();
   if (a.length == 0) return;
   if (out->data) {
     if (bits == 1) {

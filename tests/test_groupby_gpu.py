@@ -602,3 +602,104 @@ def test_dictionary_encode_matches_reference(ctx, t, encode_nulls):
             assert (hi.values()[~wvalid] == 0).all()
         np.testing.assert_array_equal(hd.valid(), dvalid)
         np.testing.assert_array_equal(hd.values()[dvalid].view(np.uint8), dv[dvalid].view(np.uint8))
+
+
+# ---- variable-length (binary / utf8) group keys (VarLengthKeyEncoder, hash_aggregate.cc:236-311)
+def _random_strings(rng, n, n_distinct, null_p, max_len=14):
+    vocab = [b"", b"a", b"a\x00", b"a\x00b", b"ab", b"abc", b"abcdefgh", b"abcdefghi", b"abcdefgh\x00"]
+    while len(vocab) < n_distinct:
+        ln = int(rng.integers(0, max_len + 1))
+        vocab.append(bytes(rng.integers(0, 256, size=ln, dtype=np.uint8)))
+    vocab = vocab[:n_distinct]
+    pick = rng.integers(0, len(vocab), size=n)
+    nulls = rng.random(n) < null_p
+    return [None if nulls[i] else vocab[pick[i]] for i in range(n)]
+
+
+@pytest.mark.parametrize("shape", ["s", "s+i32", "i64+s+s", "s,no nulls"])
+def test_groupby_string_keys_match_reference(ctx, shape):
+    if ORACLE != "reference":
+        pytest.skip("needs oracle/_ref")
+    rng = np.random.default_rng(300 + len(shape))
+    n = 60_000
+    s1 = Column.from_strings(_random_strings(rng, n, 700, 0.0 if "no nulls" in shape else 0.05))
+    keys = [s1]
+    if shape == "s+i32":
+        keys = [s1, rand_column(rng, cols.INT32, n, 0.05, lo=0, hi=5)]
+    if shape == "i64+s+s":
+        keys = [rand_column(rng, cols.INT64, n, 0.02, lo=0, hi=3), s1, Column.from_strings(_random_strings(rng, n, 9, 0.3, max_len=40))]
+    arg = rand_column(rng, cols.DOUBLE, n, 0.1)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT), AggSpec(cols.HASH_MIN_MAX)]
+    args = [arg] * 3
+    got = run_groupby("gpu", keys, aggs, args, ctx, want_ids=True)
+    want = run_groupby(ORACLE, keys, aggs, args, want_ids=True)
+    assert_group_equal(got, want, aggs, rtol=RTOL, scales=abs_sum_scales(keys, aggs, args, ORACLE))
+    np.testing.assert_array_equal(got.ids, want.ids)
+
+
+def test_groupby_string_keys_streaming_and_edge_cases(ctx):
+    """Batches into one handle (later batches bring new strings: the key heap and the id table grow), a sliced
+    column (non-zero offset), an all-empty-string column, an empty batch."""
+    if ORACLE != "reference":
+        pytest.skip("needs oracle/_ref")
+    from arrow1_b200 import capi
+    from helpers import GroupRes, _host_key
+    rng = np.random.default_rng(77)
+    n = 90_000
+    items = _random_strings(rng, n, 40, 0.1)[: n // 3] + _random_strings(rng, n, 5000, 0.1)[n // 3:]
+    key = Column.from_strings(items)
+    arg = Column.from_numpy(rng.random(n), rng.random(n) > 0.1)
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT)]
+    want = run_groupby(ORACLE, [key], aggs, [arg] * 2)
+    gb = capi.GroupBy(ctx, [cols.BINARY], aggs, [arg.type] * 2, 0)
+    dkey, darg = key.to_device(), arg.to_device()
+    cuts = [0, 10, 10, n // 3 + 17, n]
+    for lo, hi in zip(cuts[:-1], cuts[1:]):
+        gb.consume([Column(dkey.type, dkey.data, dkey.validity, hi - lo, lo, -1, dkey.extra)],
+                   [Column(darg.type, darg.data, darg.validity, hi - lo, lo, -1)] * 2, row_base=lo)
+    out = gb.finalize()
+    gb.close()
+    got = GroupRes(out.num_groups, [[(c.to_host().values().copy(), c.to_host().valid()) for c in a] for a in out.aggs],
+                   [_host_key(c) for c in out.keys])
+    assert_group_equal(got, want, aggs, rtol=RTOL, scales=abs_sum_scales([key], aggs, [arg] * 2, ORACLE))
+    # all rows the empty string / all null / no rows
+    for items in ([""] * 100, [None] * 100, []):
+        k = Column.from_strings(items)
+        a = Column.from_numpy(np.arange(len(items), dtype=np.int64))
+        cnt = [AggSpec(cols.HASH_COUNT)]
+        got = run_groupby("gpu", [k], cnt, [a], ctx)
+        if items:
+            assert_group_equal(got, run_groupby(ORACLE, [k], cnt, [a]), cnt)
+        else:
+            assert got.num_groups == 0
+
+
+def test_string_hash_kernels_and_host_groupby(ctx):
+    """unique / value_counts / dictionary_encode on a binary column against the reference, and compute.GroupBy from
+    HOST columns keyed by strings (the value bytes travel with the offsets)."""
+    from arrow1_b200 import compute
+    from helpers import GroupRes
+    if ORACLE != "reference":
+        pytest.skip("needs oracle/_ref")
+    rng = np.random.default_rng(19)
+    n = 40_000
+    col = Column.from_strings(_random_strings(rng, n, 300, 0.08))
+    (wv, wvalid), wc = oracle.value_counts(col, True)
+    (uv, uvalid), _ = oracle.value_counts(col, False)
+    got_u = compute.Unique(col.to_device(), ctx).to_host()
+    assert got_u.strings() == [x if v else None for x, v in zip(uv, uvalid)]
+    keys, counts = compute.ValueCounts(col.to_device(), ctx)
+    assert keys.to_host().strings() == [x if v else None for x, v in zip(wv, wvalid)]
+    np.testing.assert_array_equal(counts.cpu().numpy(), wc)
+    for encode_nulls in (False, True):
+        widx, wivalid, (dv, dvalid) = oracle.dictionary_encode(col, encode_nulls)
+        idx, dictionary = compute.DictionaryEncode(col.to_device(), encode_nulls, ctx)
+        hi = idx.to_host()
+        np.testing.assert_array_equal(hi.valid(), wivalid)
+        np.testing.assert_array_equal(hi.values()[wivalid], widx[wivalid])
+        assert dictionary.to_host().strings() == [x if v else None for x, v in zip(dv, dvalid)]
+    arg = Column.from_numpy(rng.random(n))
+    aggs = [AggSpec(cols.HASH_SUM), AggSpec(cols.HASH_COUNT)]
+    res = compute.GroupBy([arg, arg], [col], aggs, ctx)
+    want = run_groupby(ORACLE, [col], aggs, [arg, arg])
+    assert_group_equal(GroupRes(res.num_groups, res.aggs, res.keys), want, aggs, rtol=RTOL)
