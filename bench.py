@@ -884,6 +884,10 @@ def gpu_arm(args):
                 r2 = roofline_of(w2, kt2, ks2, peak, peak_src)
                 if r2:
                     r2["kernel_share_of_step_events"] = (kt2[w2.kernel][0] / ks2) / ms2
+                    try:
+                        r2["traffic"] = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(name, {}).get("dram_bytes_per_launch")
+                    except Exception:
+                        pass
                 extras[name] = {"rows": w2.n, "ms_per_step": ms2, "rows_per_s": w2.n / (ms2 * 1e-3),
                                 "input_gbs": w2.input_bytes() / (ms2 * 1e-3) / 1e9, "gpu_launches": l2,
                                 "roofline": r2, "description": w2.description,
