@@ -80,6 +80,9 @@ class Context:
     def synchronize(self):
         self.check(lib().b200_ctx_synchronize(self._h))
 
+    def set_option(self, name: str, value: int):
+        self.check(lib().b200_ctx_set_option(self._h, name.encode(), C.c_int64(value)))
+
     @property
     def launches(self) -> int:
         return int(lib().b200_ctx_launch_count(self._h))

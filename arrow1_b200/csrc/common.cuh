@@ -12,6 +12,7 @@
 
 struct b200_ctx {
   int device = 0;
+  int sort_high_word_first = 0;   // b200_ctx_set_option: 0 = decided per call from the digit histograms, 1 = forced, -1 = off
   cudaStream_t stream = nullptr;
   int num_sms = 148;
   int64_t launches = 0;

@@ -1,6 +1,8 @@
 // Context: one device + one stream, error message storage, small scratch (SURVEY §8b "Threading").
 #include <stdarg.h>
 
+#include <cstring>
+
 #include "common.cuh"
 
 int b200_fail(b200_ctx* ctx, int code, const char* fmt, ...) {
@@ -225,6 +227,13 @@ int b200_ctx_inject_async_error(b200_ctx* ctx, uint32_t code) {
   if (!ctx) return B200_INVALID;
   B200_CUDA(ctx, cudaMemcpyAsync(ctx->async_err, &code, sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
   B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return B200_OK;
+}
+
+int b200_ctx_set_option(b200_ctx* ctx, const char* name, int64_t value) {
+  if (!ctx || !name) return B200_INVALID;
+  if (!strcmp(name, "sort_high_word_first")) ctx->sort_high_word_first = value > 0 ? 1 : (value < 0 ? -1 : 0);
+  else return b200_fail(ctx, B200_KEY_ERROR, "context: no option named %s", name);
   return B200_OK;
 }
 

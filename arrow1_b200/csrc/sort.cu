@@ -69,7 +69,28 @@ struct PassInfo {
   int32_t last;
   int32_t src;         // ping-pong buffer read by this pass (ignored when first)
   int32_t out_narrow;  // the pass writes 32-bit keys: only the word the remaining passes still look at
-  int32_t pad[3];
+  int32_t hw;          // high-word-first plan (see HwState): the last pass also leaves the sorted high words behind
+  int32_t pad[2];
+};
+
+// ---- high word first (64-bit keys whose upper 32 bits almost identify the row) ---------------------------------------
+// An LSD sort of 64-bit keys runs 8 passes although, for n << 2^32 keys with a high-entropy upper word (ids, hashes,
+// random int64), the upper word alone orders all but a few percent of the rows.  The plan kernel estimates the number of
+// distinct upper words from the digit histograms it already has (2^(sum of the entropies of digits 4..7), an upper bound
+// of the joint figure) and, when that is >= 8 n, runs ONLY the four narrow passes over digits 4..7 — stable, so rows
+// that tie on the upper word stay in row order — and then repairs the ties: every run of equal upper words (found in
+// the sorted upper words the last pass leaves behind) is sorted by the lower word, read from the column, by one
+// thread (runs of up to 32 rows).  The run of the all-ones upper word holds the null / NaN rows (key all ones): it is
+// first split stably into [other keys | genuine maxima | NaNs | nulls] by the tail kernels, and only its first part is a
+// run to repair.  If a run is longer than 32 rows the estimate was wrong (correlated digits): a flag is raised and the
+// ordinary 8-pass plan runs after all (round 2: its launches are gated on the flag and otherwise exit at once).
+struct HwState {
+  uint32_t hw;            // the plan kernel chose high word first
+  uint32_t fail;          // a tie run was too long: round 2 runs the ordinary plan
+  int64_t top_start;      // first position of the run of the all-ones upper word (n if there is none)
+  uint32_t class_total[4];
+  uint32_t n_runs;        // runs of equal upper words found by the repair
+  uint32_t pad;
 };
 
 struct SortParams {
@@ -98,6 +119,10 @@ struct SortParams {
   int32_t narrow;          // passes that only look at one 32-bit word of the key carry that word alone
   uint32_t* hist;          // [8][kBinStride] counts, then exclusive bases
   PassInfo* info;          // [8]
+  PassInfo* info2;         // [8] the ordinary plan, for round 2 of a failed high-word-first attempt
+  HwState* hws;
+  int32_t hw_allowed;      // host: a 64-bit column, indices only
+  int32_t round2;          // this launch belongs to round 2: it runs only if hws->fail is set
   uint32_t* counters;      // [8] tile tickets
   uint32_t* err;
   uint32_t* state;         // [8][n_tiles][kBinStride]
@@ -175,17 +200,59 @@ __global__ void __launch_bounds__(kHistThreads) sort_hist_kernel(SortParams p) {
   }
 }
 
-// one warp per digit: exclusive scan of its 258 bins; then thread 0 plans the passes
+// the passes of a plan: which digits run, which buffers they read, where the keys become 32-bit
+__device__ void write_plan(const SortParams& p, const int* skip_in, bool hw, PassInfo* out) {
+  int skip[kDigits];
+  int live = 0;
+  for (int i = 0; i < kDigits; ++i) {
+    skip[i] = skip_in[i] || (hw && i < 4);
+    live += !skip[i];
+  }
+  if (live == 0) skip[0] = 0;  // at least one pass must run to emit the indices
+  int first = -1, last = -1;
+  for (int i = 0; i < kDigits; ++i)
+    if (!skip[i]) {
+      if (first < 0) first = i;
+      last = i;
+    }
+  int src = 0;
+  for (int i = 0; i < kDigits; ++i) {
+    PassInfo pi;
+    pi.skip = skip[i];
+    pi.first = (i == first);
+    pi.last = (i == last);
+    pi.src = src;
+    // 32-bit keys from the point where every pass still to run looks at the same word: the upper word of a
+    // 64-bit key after the last live pass over digits 0..3, the only word of a <= 32-bit column from the start
+    int next = -1;
+    for (int j = i + 1; j < kDigits; ++j)
+      if (!skip[j]) {
+        next = j;
+        break;
+      }
+    pi.out_narrow = p.narrow && next >= 0 && (next >= 4 || p.n_digits <= 4);
+    pi.hw = hw ? 1 : 0;
+    pi.pad[0] = pi.pad[1] = 0;
+    out[i] = pi;
+    // the first pass writes buffer 0; every later executed pass flips
+    if (!pi.skip) src = pi.first ? 0 : (src ^ 1);
+  }
+}
+
+// one warp per digit: exclusive scan of its 258 bins (and the digit's entropy); then thread 0 plans the passes
 __global__ void __launch_bounds__(kHistThreads) sort_scan_kernel(SortParams p) {
   __shared__ int skip_s[kDigits];
+  __shared__ double entropy_s[kDigits];
   const int lane = threadIdx.x & 31, d = threadIdx.x >> 5;
   uint32_t* h = p.hist + d * kBinStride;
   uint32_t carry = 0;
   bool single = d >= p.n_digits;  // digits above the type width are constant (zero)
+  double clogc = 0.0;             // sum of c * log2(c) over the digit's bins
   for (int base = 0; base < 258; base += 32) {
     const int b = base + lane;
     const uint32_t c = b < 258 ? h[b] : 0;
     if (c == uint32_t(p.n)) single = true;
+    if (c > 1) clogc += double(c) * log2(double(c));
     uint32_t incl = c;
 #pragma unroll
     for (int s = 1; s < 32; s <<= 1) {
@@ -196,38 +263,28 @@ __global__ void __launch_bounds__(kHistThreads) sort_scan_kernel(SortParams p) {
     carry += __shfl_sync(0xffffffffu, incl, 31);
   }
   single = __any_sync(0xffffffffu, single);
-  if (lane == 0) skip_s[d] = single ? 1 : 0;
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) clogc += __shfl_xor_sync(0xffffffffu, clogc, s);
+  if (lane == 0) {
+    skip_s[d] = single ? 1 : 0;
+    // H = log2(n) - sum(c log2 c) / n bits
+    entropy_s[d] = (d < p.n_digits && p.n > 0) ? log2(double(p.n)) - clogc / double(p.n) : 0.0;
+  }
   __syncthreads();
   if (threadIdx.x == 0) {
-    int live = 0;
-    for (int i = 0; i < kDigits; ++i) live += !skip_s[i];
-    if (live == 0) skip_s[0] = 0;  // at least one pass must run to emit the indices
-    int first = -1, last = -1;
-    for (int i = 0; i < kDigits; ++i)
-      if (!skip_s[i]) {
-        if (first < 0) first = i;
-        last = i;
-      }
-    int src = 0;
-    for (int i = 0; i < kDigits; ++i) {
-      PassInfo pi;
-      pi.skip = skip_s[i];
-      pi.first = (i == first);
-      pi.last = (i == last);
-      pi.src = src;
-      // 32-bit keys from the point where every pass still to run looks at the same word: the upper word of a
-      // 64-bit key after the last live pass over digits 0..3, the only word of a <= 32-bit column from the start
-      int next = -1;
-      for (int j = i + 1; j < kDigits; ++j)
-        if (!skip_s[j]) {
-          next = j;
-          break;
-        }
-      pi.out_narrow = p.narrow && next >= 0 && (next >= 4 || p.n_digits <= 4);
-      pi.pad[0] = pi.pad[1] = pi.pad[2] = 0;
-      p.info[i] = pi;
-      // the first pass writes buffer 0; every later executed pass flips
-      if (!pi.skip) src = pi.first ? 0 : (src ^ 1);
+    // high word first?  2^(entropies of digits 4..7) bounds the number of distinct upper words from above; with D
+    // distinct, equally likely words a row ties with another with probability ~ n / D
+    bool hw = false;
+    if (p.hw_allowed && p.n_digits == 8 && p.narrow && p.n > 1) {
+      const double bits = entropy_s[4] + entropy_s[5] + entropy_s[6] + entropy_s[7];
+      hw = bits >= log2(double(p.n)) + 3.0;
+      if (p.hw_allowed == 2) hw = !(skip_s[4] && skip_s[5] && skip_s[6] && skip_s[7]);   // forced (tests)
+    }
+    write_plan(p, skip_s, hw, p.info);
+    if (p.hws) {
+      p.hws->hw = hw ? 1u : 0u;
+      p.hws->top_start = p.n;
+      if (p.info2) write_plan(p, skip_s, false, p.info2);
     }
   }
 }
@@ -593,6 +650,7 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
       if (info.last) {
         p.out_idx[pos] = p.gather ? p.gather[pv] : (uint64_t(pv) + p.index_base);
         if (!kNarrow && p.out_keys) p.out_keys[pos] = kk;
+        if (kNarrow && info.hw) keys32_dst[pos] = uint32_t(kk);   // the sorted upper words: the tie repair reads them
       } else {
         if (kNarrow) keys32_dst[pos] = uint32_t(kk);
         else if (info.out_narrow) keys32_dst[pos] = uint32_t(uint64_t(kk) >> (p.n_digits <= 4 ? 0 : 32));
@@ -603,35 +661,44 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
   }
 }
 
-template <bool kNarrow>
+// kLoop (round 2 of a failed high-word-first attempt, normally idle): a grid of a few CTAs per SM takes tiles until none
+// is left — tickets are handed out in order, so every tile a look-back waits for is already running — and the idle case
+// costs a few hundred CTAs that exit at once instead of one per tile
+template <bool kNarrow, bool kLoop>
 __global__ void __launch_bounds__(kThreads, kNarrow ? B200_SORT_NARROW_MINBLOCKS : kMinBlocks) sort_pass_kernel(SortParams p, int d) {
   const PassInfo info = p.info[d];
   if (info.skip) return;
+  if (kLoop && p.hws->fail == 0) return;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   using Smem = PassSmem<typename std::conditional<kNarrow, uint32_t, uint64_t>::type>;
   Smem& s = *reinterpret_cast<Smem*>(smem_raw);
   using KeyT = typename std::conditional<kNarrow, uint32_t, uint64_t>::type;
   const int t = threadIdx.x;
-  if (t == 0) {
-    const uint32_t tk = atomicAdd(p.counters + d, 1u);
-    s.tile = tk;
-    if (B200_SORT_TMA && !info.first && (int64_t(tk) + 1) * kTile <= p.n) {
-      // a full tile of a later pass: both ranges go to the copy engine now
-      mbar_init(&s.mbar, 1);
-      mbar_expect_tx(&s.mbar, uint32_t(kTile * (sizeof(KeyT) + 4)));
-      bulk_load(s.keys, reinterpret_cast<const KeyT*>(p.keys[info.src]) + size_t(tk) * kTile, uint32_t(kTile * sizeof(KeyT)), &s.mbar);
-      bulk_load(s.pay, p.pays[info.src] + size_t(tk) * kTile, uint32_t(kTile * 4), &s.mbar);
+  for (;;) {
+    if (t == 0) {
+      const uint32_t tk = atomicAdd(p.counters + d, 1u);
+      s.tile = tk;
+      if (B200_SORT_TMA && !kLoop && !info.first && (int64_t(tk) + 1) * kTile <= p.n) {
+        // a full tile of a later pass: both ranges go to the copy engine now
+        mbar_init(&s.mbar, 1);
+        mbar_expect_tx(&s.mbar, uint32_t(kTile * (sizeof(KeyT) + 4)));
+        bulk_load(s.keys, reinterpret_cast<const KeyT*>(p.keys[info.src]) + size_t(tk) * kTile, uint32_t(kTile * sizeof(KeyT)), &s.mbar);
+        bulk_load(s.pay, p.pays[info.src] + size_t(tk) * kTile, uint32_t(kTile * 4), &s.mbar);
+      }
     }
+    for (int i = t; i < kWarps * kBinStride / 4; i += kThreads) reinterpret_cast<uint4*>(&s.whist[0][0])[i] = make_uint4(0, 0, 0, 0);
+    if (B200_SORT_MATCH_ATOMIC && !B200_SORT_TMA) {
+      for (int i = t; i < kWarps * 256 / 4; i += kThreads) reinterpret_cast<uint4*>(&s.pay[0])[i] = make_uint4(0, 0, 0, 0);
+    }
+    __syncthreads();
+    const int64_t tile = s.tile;
+    if (kLoop && tile >= p.n_tiles) return;
+    const int tile_items = int(min(int64_t(kTile), p.n - tile * kTile));
+    if (tile_items == kTile) sort_pass_body<true, kNarrow>(p, d, info, s, tile, tile_items);
+    else sort_pass_body<false, kNarrow>(p, d, info, s, tile, tile_items);
+    if (!kLoop) return;
+    __syncthreads();   // the staging arrays and the ticket are about to be reused
   }
-  for (int i = t; i < kWarps * kBinStride / 4; i += kThreads) reinterpret_cast<uint4*>(&s.whist[0][0])[i] = make_uint4(0, 0, 0, 0);
-  if (B200_SORT_MATCH_ATOMIC && !B200_SORT_TMA) {
-    for (int i = t; i < kWarps * 256 / 4; i += kThreads) reinterpret_cast<uint4*>(&s.pay[0])[i] = make_uint4(0, 0, 0, 0);
-  }
-  __syncthreads();
-  const int64_t tile = s.tile;
-  const int tile_items = int(min(int64_t(kTile), p.n - tile * kTile));
-  if (tile_items == kTile) sort_pass_body<true, kNarrow>(p, d, info, s, tile, tile_items);
-  else sort_pass_body<false, kNarrow>(p, d, info, s, tile, tile_items);
 }
 
 
@@ -643,23 +710,47 @@ __global__ void __launch_bounds__(kThreads, kNarrow ? B200_SORT_NARROW_MINBLOCKS
 // ninth ballot and a validity gather (1.02 ms against 0.70 ms for a plain pass at 100 M rows, round 1).
 constexpr int kTailThreads = 256;
 constexpr int kTailMaxBlocks = 1024;
+constexpr int kTailClasses = 4;   // other keys (high word first only) | genuine maxima | NaNs | nulls
 
 struct TailArgs {
   SortParams p;
   uint64_t* idx;      // the sorted indices (out_idx)
-  uint64_t* tmp;      // >= tail entries
   uint32_t* counts;   // [blocks][4] class counts, then exclusive positions
 };
 
+// the pass that wrote the indices (the plan lives in device memory)
+__device__ __forceinline__ PassInfo last_pass(const SortParams& p) {
+  PassInfo pi = p.info[0];
+  for (int d = 0; d < kDigits; ++d)
+    if (!p.info[d].skip && p.info[d].last) pi = p.info[d];
+  return pi;
+}
+// scratch of the tail kernels: the key buffer the last pass read (free since)
+__device__ __forceinline__ uint64_t* tail_tmp(const SortParams& p) {
+  const PassInfo pi = last_pass(p);
+  return p.keys[pi.first ? 1 : pi.src];
+}
+
 __device__ __forceinline__ uint32_t tail_class(const SortParams& p, uint64_t out_index) {
   const int64_t row = int64_t(out_index - p.index_base);
-  if (!bitmap_get(p.vv, row)) return 2;
-  if (p.tkind == kFloatKey && ((load_raw(p, row) & ~p.sign) > p.nan_above)) return 1;
-  return 0;
+  if (!bitmap_get(p.vv, row)) return 3;
+  uint32_t cls;
+  const uint64_t k = transform_key(p, load_raw(p, row), &cls);
+  if (cls) return 2;
+  return k == p.wmask ? 1 : 0;   // 0: only in the run of the all-ones upper word of a high-word-first sort
+}
+
+// does this launch have anything to do?  (round 2 runs only after a failed high-word-first attempt)
+__device__ __forceinline__ bool tail_active(const TailArgs& a) { return !(a.p.round2 && a.p.hws->fail == 0); }
+// rows of the tail: the keys that are all ones — or, after the passes of a high-word-first plan, the whole run of the
+// all-ones upper word
+__device__ __forceinline__ int64_t tail_rows(const TailArgs& a) {
+  const bool top = !a.p.round2 && a.p.hws && a.p.hws->hw != 0;
+  return top ? a.p.n - a.p.hws->top_start : int64_t(*a.p.tail_count);
 }
 
 __device__ __forceinline__ void tail_range(const TailArgs& a, int64_t* begin, int64_t* end, int64_t* first) {
-  const int64_t T = *a.p.tail_count;
+  const int64_t T = tail_rows(a);
   int64_t chunk = (T + gridDim.x - 1) / gridDim.x;
   chunk = (chunk + kTailThreads - 1) / kTailThreads * kTailThreads;
   *first = a.p.n - T;
@@ -668,25 +759,28 @@ __device__ __forceinline__ void tail_range(const TailArgs& a, int64_t* begin, in
 }
 
 __global__ void __launch_bounds__(kTailThreads) tail_count_kernel(const __grid_constant__ TailArgs a) {
-  __shared__ uint32_t c[4];
-  if (threadIdx.x < 4) c[threadIdx.x] = 0;
+  if (!tail_active(a)) return;
+  __shared__ uint32_t c[kTailClasses];
+  if (threadIdx.x < kTailClasses) c[threadIdx.x] = 0;
   __syncthreads();
   int64_t begin, end, first;
   tail_range(a, &begin, &end, &first);
   for (int64_t i = begin + threadIdx.x; i < end; i += kTailThreads) atomicAdd(&c[tail_class(a.p, a.idx[first + i])], 1u);
   __syncthreads();
-  if (threadIdx.x < 4) a.counts[blockIdx.x * 4 + threadIdx.x] = c[threadIdx.x];
+  if (threadIdx.x < kTailClasses) a.counts[blockIdx.x * kTailClasses + threadIdx.x] = c[threadIdx.x];
 }
 
-// one CTA: counts[b][c] -> where block b's rows of class c start inside the tail
-__global__ void __launch_bounds__(kTailMaxBlocks) tail_scan_kernel(uint32_t* counts, int blocks) {
+// one CTA: counts[b][c] -> where block b's rows of class c start inside the tail; the class totals go to hws
+__global__ void __launch_bounds__(kTailMaxBlocks) tail_scan_kernel(const __grid_constant__ TailArgs a, int blocks) {
+  if (!tail_active(a)) return;
+  uint32_t* counts = a.counts;
   __shared__ uint32_t warp_sums[32];
   __shared__ uint32_t class_start;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   if (t == 0) class_start = 0;
   __syncthreads();
-  for (int c = 0; c < 3; ++c) {
-    const uint32_t v = t < blocks ? counts[t * 4 + c] : 0;
+  for (int c = 0; c < kTailClasses; ++c) {
+    const uint32_t v = t < blocks ? counts[t * kTailClasses + c] : 0;
     uint32_t incl = v;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -701,29 +795,34 @@ __global__ void __launch_bounds__(kTailMaxBlocks) tail_scan_kernel(uint32_t* cou
       total += warp_sums[w];
     }
     const uint32_t start = class_start;
-    if (t < blocks) counts[t * 4 + c] = start + wpre + incl - v;
+    if (t < blocks) counts[t * kTailClasses + c] = start + wpre + incl - v;
     __syncthreads();
-    if (t == 0) class_start = start + total;
+    if (t == 0) {
+      class_start = start + total;
+      if (a.p.hws) a.p.hws->class_total[c] = total;
+    }
     __syncthreads();
   }
 }
 
 __global__ void __launch_bounds__(kTailThreads) tail_scatter_kernel(const __grid_constant__ TailArgs a) {
-  __shared__ uint32_t run[4];                        // next position of every class for this block
-  __shared__ uint32_t wcnt[kTailThreads / 32][4];
+  if (!tail_active(a)) return;
+  __shared__ uint32_t run[kTailClasses];                        // next position of every class for this block
+  __shared__ uint32_t wcnt[kTailThreads / 32][kTailClasses];
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const unsigned lt = lanemask_lt();
-  if (t < 4) run[t] = a.counts[blockIdx.x * 4 + t];
+  uint64_t* tmp = tail_tmp(a.p);
+  if (t < kTailClasses) run[t] = a.counts[blockIdx.x * kTailClasses + t];
   int64_t begin, end, first;
   tail_range(a, &begin, &end, &first);
   for (int64_t base = begin; base < end; base += kTailThreads) {
     const int64_t i = base + t;
     const bool in = i < end;
     const uint64_t v = in ? a.idx[first + i] : 0;
-    const uint32_t c = in ? tail_class(a.p, v) : 3;
+    const uint32_t c = in ? tail_class(a.p, v) : kTailClasses;
     uint32_t rank = 0;
 #pragma unroll
-    for (int q = 0; q < 3; ++q) {
+    for (int q = 0; q < kTailClasses; ++q) {
       const unsigned m = __ballot_sync(0xffffffffu, c == q);
       if (c == q) rank = __popc(m & lt);
       if (lane == 0) wcnt[warp][q] = __popc(m);
@@ -732,10 +831,10 @@ __global__ void __launch_bounds__(kTailThreads) tail_scatter_kernel(const __grid
     if (in) {
       uint32_t pre = run[c];
       for (int w = 0; w < warp; ++w) pre += wcnt[w][c];
-      a.tmp[pre + rank] = v;
+      tmp[pre + rank] = v;
     }
     __syncthreads();
-    if (t < 3) {
+    if (t < kTailClasses) {
       uint32_t add = 0;
       for (int w = 0; w < kTailThreads / 32; ++w) add += wcnt[w][t];
       run[t] += add;
@@ -745,9 +844,158 @@ __global__ void __launch_bounds__(kTailThreads) tail_scatter_kernel(const __grid
 }
 
 __global__ void tail_copy_kernel(const __grid_constant__ TailArgs a) {
-  const int64_t T = *a.p.tail_count;
+  if (!tail_active(a)) return;
+  const int64_t T = tail_rows(a);
   uint64_t* dst = a.idx + (a.p.n - T);
-  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < T; i += int64_t(gridDim.x) * blockDim.x) dst[i] = a.tmp[i];
+  const uint64_t* tmp = tail_tmp(a.p);
+  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < T; i += int64_t(gridDim.x) * blockDim.x) dst[i] = tmp[i];
+}
+
+// ---- high word first: the repair of the ties (see HwState) ------------------------------------------------------------
+constexpr int kHwMaxRun = 32;
+
+// the sorted upper words the last pass of a high-word-first plan left behind
+__device__ __forceinline__ const uint32_t* hw_words(const SortParams& p) {
+  const PassInfo pi = last_pass(p);
+  return reinterpret_cast<const uint32_t*>(p.keys[pi.first ? 0 : (pi.src ^ 1)]);
+}
+
+// where the run of the all-ones upper word starts (the words are sorted: a binary search by one thread)
+__global__ void hw_top_kernel(SortParams p) {
+  if (p.hws->hw == 0) return;
+  const uint32_t* hi = hw_words(p);
+  int64_t lo = 0, up = p.n;   // first position whose word is all ones
+  while (lo < up) {
+    const int64_t mid = (lo + up) >> 1;
+    if (hi[mid] == 0xFFFFFFFFu) up = mid;
+    else lo = mid + 1;
+  }
+  p.hws->top_start = lo;
+}
+
+// where the repair may look: with nulls / NaNs in play the run of the all-ones word was split by the tail kernels and only
+// its first part (keys that are not all ones) is a run to repair
+__device__ __forceinline__ int64_t hw_limit(const SortParams& p) {
+  return p.tail_fix ? p.hws->top_start + int64_t(p.hws->class_total[0]) : p.n;
+}
+// the list of run starts: the payload buffer the last pass did not write is free by now
+__device__ __forceinline__ uint32_t* hw_run_list(const SortParams& p) {
+  const PassInfo pi = last_pass(p);
+  return p.pays[pi.first ? 1 : pi.src];
+}
+
+// repair, step 1 (streaming): the positions where a run of equal upper words starts, appended to a list.  A CTA takes
+// 4096 positions at a time, 16 consecutive ones per thread, and claims room in the list with ONE atomic per tile (a
+// warp-level claim per 32 positions serialised a million atomics on one address: 0.6 ms).  (One kernel that repaired
+// a run where it met it ran at a fifth of the memory bandwidth: a warp in which one lane had found a run waited for
+// that lane's three dependent gathers, every third warp iteration.)
+constexpr int kHwRunsPerThread = 16;
+__global__ void __launch_bounds__(256) hw_runs_kernel(SortParams p) {
+  if (p.hws->hw == 0) return;
+  __shared__ uint32_t warp_sums[8];
+  __shared__ uint32_t tile_base;
+  const uint32_t* hi = hw_words(p);
+  uint32_t* list = hw_run_list(p);
+  const int64_t limit = hw_limit(p);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  constexpr int kTilePositions = 256 * kHwRunsPerThread;
+  for (int64_t base = int64_t(blockIdx.x) * kTilePositions; base < limit; base += int64_t(gridDim.x) * kTilePositions) {
+    const int64_t i0 = base + int64_t(t) * kHwRunsPerThread;
+    // words i0 - 1 .. i0 + 16 (the buffer is 256-byte aligned and i0 a multiple of 16: four aligned 16-byte loads)
+    uint32_t w[kHwRunsPerThread + 2];
+    if (i0 + kHwRunsPerThread <= limit) {
+#pragma unroll
+      for (int q = 0; q < kHwRunsPerThread / 4; ++q) {
+        const uint4 v = reinterpret_cast<const uint4*>(hi + i0)[q];
+        w[1 + 4 * q] = v.x;
+        w[2 + 4 * q] = v.y;
+        w[3 + 4 * q] = v.z;
+        w[4 + 4 * q] = v.w;
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < kHwRunsPerThread; ++q) w[1 + q] = i0 + q < limit ? hi[i0 + q] : 0u;
+    }
+    w[0] = i0 > 0 && i0 - 1 < limit ? hi[i0 - 1] : 0u;
+    w[kHwRunsPerThread + 1] = i0 + kHwRunsPerThread < limit ? hi[i0 + kHwRunsPerThread] : 0u;
+    uint32_t starts = 0;
+#pragma unroll
+    for (int q = 0; q < kHwRunsPerThread; ++q) {
+      const int64_t i = i0 + q;
+      const bool start = i + 1 < limit && w[q + 2] == w[q + 1] && (i == 0 || w[q] != w[q + 1]);
+      starts |= uint32_t(start) << q;
+    }
+    // exclusive scan of the threads' counts over the CTA
+    const uint32_t c = __popc(starts);
+    uint32_t incl = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += o;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    uint32_t wpre = 0, total = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (k < warp) wpre += warp_sums[k];
+      total += warp_sums[k];
+    }
+    if (t == 0) tile_base = total ? atomicAdd(&p.hws->n_runs, total) : 0u;
+    __syncthreads();
+    uint32_t at = tile_base + wpre + incl - c;
+    while (starts) {
+      const int q = __ffs(starts) - 1;
+      starts &= starts - 1;
+      list[at++] = uint32_t(i0 + q);
+    }
+    __syncthreads();   // warp_sums / tile_base are rewritten by the next tile
+  }
+}
+
+// repair, step 2: one thread per run puts it in (lower word, row) order; every thread is gathering, so the dependent
+// loads (index -> row -> column value) of thousands of runs are in flight together
+__global__ void __launch_bounds__(256) hw_fix_kernel(SortParams p) {
+  if (p.hws->hw == 0) return;
+  const uint32_t* hi = hw_words(p);
+  const uint32_t* list = hw_run_list(p);
+  const int64_t limit = hw_limit(p);
+  const uint32_t n_runs = p.hws->n_runs;
+  for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_runs; r += gridDim.x * blockDim.x) {
+    const int64_t i = list[r];
+    const uint32_t w = hi[i];
+    int len = 2;
+    while (len <= kHwMaxRun && i + len < limit && hi[i + len] == w) ++len;
+    if (len > kHwMaxRun) {   // the estimate of the plan kernel was wrong: the ordinary plan runs after all
+      p.hws->fail = 1u;
+      continue;
+    }
+    uint64_t idx[kHwMaxRun];
+    uint32_t low[kHwMaxRun];
+    for (int j = 0; j < len; ++j) {
+      const uint64_t v = p.out_idx[i + j];
+      uint32_t cls;
+      const uint32_t l = uint32_t(source_key(p, int64_t(v - p.index_base), &cls));
+      // stable insertion: the rows arrive in row order
+      int q = j;
+      while (q > 0 && low[q - 1] > l) {
+        low[q] = low[q - 1];
+        idx[q] = idx[q - 1];
+        --q;
+      }
+      low[q] = l;
+      idx[q] = v;
+    }
+    for (int j = 0; j < len; ++j) p.out_idx[i + j] = idx[j];
+  }
+}
+
+// round 2 needs the look-back state of digits 4..7 clean again
+__global__ void hw_rezero_kernel(SortParams p) {
+  if (p.hws->fail == 0) return;
+  uint4* s = reinterpret_cast<uint4*>(p.state + size_t(4) * p.n_tiles * kBinStride);
+  const size_t words = size_t(4) * p.n_tiles * kBinStride / 4;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < words; i += size_t(gridDim.x) * blockDim.x) s[i] = make_uint4(0, 0, 0, 0);
 }
 
 __global__ void sort_keys_kernel(SortParams p, uint64_t* out, uint64_t* out_rows) {
@@ -1041,7 +1289,7 @@ __global__ void mk_gather_flat_kernel(const uint64_t* flat_keys, const uint8_t* 
 }
 
 struct Layout {
-  size_t hist, info, counters, err, tail, state, zero_bytes, keys0, keys1, pays0, pays1, total;
+  size_t hist, info, info2, hw, counters, err, tail, state, zero_bytes, keys0, keys1, pays0, pays1, total;
 };
 
 Layout layout_for(int64_t n) {
@@ -1050,6 +1298,8 @@ Layout layout_for(int64_t n) {
   size_t off = 0;
   L.hist = off; off += b200_align_up(size_t(kDigits) * kBinStride * 4, 256);
   L.info = off; off += 256;
+  L.info2 = off; off += 256;
+  L.hw = off; off += 256;      // HwState, then round 2's tile tickets (+64) and tail count (+128)
   L.counters = off; off += 128;
   L.err = off; off += 128;
   L.tail = off; off += size_t(kTailMaxBlocks) * 16;
@@ -1117,8 +1367,10 @@ int run_sort(b200_ctx* ctx, SortParams p, void* scratch, size_t scratch_bytes) {
   const int hist_blocks = int(std::min<int64_t>((p.n + kHistTile - 1) / kHistTile, int64_t(ctx->num_sms) * 8));
   const int smem_wide = int(sizeof(PassSmem<uint64_t>)), smem_narrow = int(sizeof(PassSmem<uint32_t>));
   if (b200_ctx_once(ctx, 0)) {
-    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_wide));
-    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_narrow));
+    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_wide));
+    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_narrow));
+    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_wide));
+    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_narrow));
   }
   // the caller wants the sorted 64-bit keys back: every pass carries them whole
   p.narrow = p.out_keys ? 0 : 1;
@@ -1126,29 +1378,66 @@ int run_sort(b200_ctx* ctx, SortParams p, void* scratch, size_t scratch_bytes) {
   // flag lives in the context)
   p.tail_fix = p.cls_digit >= 0 ? 1 : 0;
   p.tail_count = reinterpret_cast<uint32_t*>(base + L.err);
+  // high word first (HwState): a 64-bit column sorted for its indices alone; the plan kernel decides on the device
+  p.info2 = reinterpret_cast<PassInfo*>(base + L.info2);
+  p.hws = reinterpret_cast<HwState*>(base + L.hw);
+  p.round2 = 0;
+  p.hw_allowed = 0;
+  if (!p.keys_in && p.width == 8 && p.narrow && !p.gather && ctx->sort_high_word_first >= 0) p.hw_allowed = ctx->sort_high_word_first > 0 ? 2 : 1;
   B200_TIMED(ctx, "sort_hist", (sort_hist_kernel<<<hist_blocks, kHistThreads, 0, ctx->stream>>>(p)));
   sort_scan_kernel<<<1, kHistThreads, 0, ctx->stream>>>(p);
   B200_LAUNCHED(ctx);
-  for (int d = 0; d < p.n_digits; ++d) {
-    const bool narrow = p.narrow && (d >= 4 || p.n_digits <= 4);
-    const unsigned grid = unsigned(p.n_tiles);
-    if (narrow)
-      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<true><<<grid, kThreads, smem_narrow, ctx->stream>>>(p, d)));
-    else
-      B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<false><<<grid, kThreads, smem_wide, ctx->stream>>>(p, d)));
-  }
-  if (p.tail_fix) {
+  const int tail_blocks = std::min(kTailMaxBlocks, ctx->num_sms * 4);
+  auto passes = [&](const SortParams& q) -> int {
+    for (int d = 0; d < q.n_digits; ++d) {
+      const bool narrow = q.narrow && (d >= 4 || q.n_digits <= 4);
+      const unsigned grid = unsigned(q.n_tiles);
+      if (q.round2) {   // normally every launch exits at once
+        const unsigned loop_grid = unsigned(std::min<int64_t>(q.n_tiles, int64_t(ctx->num_sms) * 3));
+        if (narrow)
+          B200_TIMED(ctx, "sort_pass_round2", (sort_pass_kernel<true, true><<<loop_grid, kThreads, smem_narrow, ctx->stream>>>(q, d)));
+        else
+          B200_TIMED(ctx, "sort_pass_round2", (sort_pass_kernel<false, true><<<loop_grid, kThreads, smem_wide, ctx->stream>>>(q, d)));
+      } else if (narrow) {
+        B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<true, false><<<grid, kThreads, smem_narrow, ctx->stream>>>(q, d)));
+      } else {
+        B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<false, false><<<grid, kThreads, smem_wide, ctx->stream>>>(q, d)));
+      }
+    }
+    return B200_OK;
+  };
+  auto tail = [&](const SortParams& q) -> int {
     TailArgs ta;
-    ta.p = p;
-    ta.idx = p.out_idx;
-    ta.tmp = p.keys[0];
+    ta.p = q;
+    ta.idx = q.out_idx;
     ta.counts = reinterpret_cast<uint32_t*>(base + L.tail);
-    const int blocks = std::min(kTailMaxBlocks, ctx->num_sms * 4);
-    B200_TIMED(ctx, "sort_tail", (tail_count_kernel<<<blocks, kTailThreads, 0, ctx->stream>>>(ta)));
-    tail_scan_kernel<<<1, kTailMaxBlocks, 0, ctx->stream>>>(ta.counts, blocks);
+    B200_TIMED(ctx, "sort_tail", (tail_count_kernel<<<tail_blocks, kTailThreads, 0, ctx->stream>>>(ta)));
+    tail_scan_kernel<<<1, kTailMaxBlocks, 0, ctx->stream>>>(ta, tail_blocks);
     B200_LAUNCHED(ctx);
-    B200_TIMED(ctx, "sort_tail", (tail_scatter_kernel<<<blocks, kTailThreads, 0, ctx->stream>>>(ta)));
-    B200_TIMED(ctx, "sort_tail", (tail_copy_kernel<<<blocks, kTailThreads, 0, ctx->stream>>>(ta)));
+    B200_TIMED(ctx, "sort_tail", (tail_scatter_kernel<<<tail_blocks, kTailThreads, 0, ctx->stream>>>(ta)));
+    B200_TIMED(ctx, "sort_tail", (tail_copy_kernel<<<tail_blocks, kTailThreads, 0, ctx->stream>>>(ta)));
+    return B200_OK;
+  };
+  B200_RETURN_NOT_OK(passes(p));
+  if (p.hw_allowed && p.tail_fix) {
+    hw_top_kernel<<<1, 1, 0, ctx->stream>>>(p);
+    B200_LAUNCHED(ctx);
+  }
+  if (p.tail_fix) B200_RETURN_NOT_OK(tail(p));
+  if (p.hw_allowed) {
+    const unsigned fix_grid = unsigned(std::min<int64_t>((p.n + 255) / 256, int64_t(ctx->num_sms) * 16));
+    B200_TIMED(ctx, "sort_tie_repair", (hw_runs_kernel<<<fix_grid, 256, 0, ctx->stream>>>(p)));
+    B200_TIMED(ctx, "sort_tie_repair", (hw_fix_kernel<<<fix_grid, 256, 0, ctx->stream>>>(p)));
+    // round 2: the ordinary plan, every launch gated on the failure flag of the repair (normally they all exit at once)
+    SortParams q = p;
+    q.round2 = 1;
+    q.info = p.info2;
+    q.counters = reinterpret_cast<uint32_t*>(base + L.hw + 64);
+    q.tail_count = reinterpret_cast<uint32_t*>(base + L.hw + 128);
+    hw_rezero_kernel<<<ctx->num_sms * 4, 256, 0, ctx->stream>>>(q);
+    B200_LAUNCHED(ctx);
+    B200_RETURN_NOT_OK(passes(q));
+    if (q.tail_fix) B200_RETURN_NOT_OK(tail(q));
   }
   return B200_OK;
 }
@@ -1160,6 +1449,20 @@ extern "C" {
 int b200_sort_indices_scratch_bytes(int64_t length, size_t* out_bytes) {
   if (!out_bytes || length < 0) return B200_INVALID;
   *out_bytes = layout_for(length).total + 256;
+  return B200_OK;
+}
+
+int b200_sort_indices_plan(b200_ctx* ctx, const void* scratch, int* out_high_word_first, int* out_fell_back) {
+  B200_ENTER(ctx);
+  if (!ctx || !scratch) return B200_INVALID;
+  // the plan of the last b200_sort_indices call that used `scratch` lives at a fixed place inside it
+  const Layout L = layout_for(0);
+  const char* base = reinterpret_cast<const char*>(b200_align_up(reinterpret_cast<uintptr_t>(scratch), 256));
+  HwState h;
+  B200_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  B200_CUDA(ctx, cudaMemcpy(&h, base + L.hw, sizeof(h), cudaMemcpyDeviceToHost));
+  if (out_high_word_first) *out_high_word_first = h.hw ? 1 : 0;
+  if (out_fell_back) *out_fell_back = h.fail ? 1 : 0;
   return B200_OK;
 }
 

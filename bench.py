@@ -142,7 +142,25 @@ class SortWL(Workload):
         # number (12); passes 1, 2 read and write 12; pass 3 reads 12 and writes the upper key word + row (8); passes
         # 4..6 read and write 8; the last reads 8 and writes the 8-byte index
         total = self.n * (8.125 + 12 + 2 * 24 + 12 + 8 + 3 * 16 + 8 + 8)
+        if getattr(self, "high_word_first", False):
+            # high word first (sort.cu HwState): 4 narrow passes over digits 4..7 — the first reads the column and
+            # writes upper word + row (8), two read and write 8, the last reads 8 and writes the index (8) and the
+            # sorted upper word (4); the passes over digits 0..3 are launched and exit at once
+            total = self.n * (8.125 + 8 + 2 * 16 + 8 + 12)
+            return total / 4
         return total / max(launches_per_step, 1)
+
+    def live_launches_per_step(self, launches_per_step):
+        return 4 if getattr(self, "high_word_first", False) else launches_per_step
+
+    def after_timing(self, ctx, bufs):
+        """Which plan the sort took (decided on the device from the digit histograms)."""
+        import ctypes as C
+        from arrow1_b200 import capi
+        hw, fell_back = C.c_int(0), C.c_int(0)
+        ctx.check(capi.lib().b200_sort_indices_plan(ctx._h, C.c_void_p(bufs["scratch"].data_ptr()), C.byref(hw), C.byref(fell_back)))
+        self.high_word_first = bool(hw.value) and not fell_back.value
+        self.plan = {"high_word_first": bool(hw.value), "fell_back_to_8_passes": bool(fell_back.value)}
 
     def prepare(self, ctx, cols_):
         import torch
@@ -607,7 +625,7 @@ def kernel_times(ctx, names):
     return out
 
 
-ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "groupby_consume", "compare_scalar", "arithmetic", "take", "partition_plan", "partition_scatter", "sort_partition",
+ALL_KERNELS = ("filter_plan", "filter_apply", "sort_hist", "sort_pass", "sort_tail", "sort_tie_repair", "sort_pass_round2", "groupby_consume", "compare_scalar", "arithmetic", "take", "partition_plan", "partition_scatter", "sort_partition",
                "groupby_partition", "groupby_import", "groupby_fused", "filter_fused", "groupby_wide_keys")
 
 
@@ -648,6 +666,8 @@ def time_device(ctx, wl, cols_, steps, warmup, world, dist_step=None):
     torch.cuda.synchronize()
     kt = kernel_times(ctx, ALL_KERNELS)
     capi.lib().b200_ctx_set_kernel_timing(ctx._h, 0)
+    if hasattr(wl, "after_timing") and dist_step is None:
+        wl.after_timing(ctx, bufs)
     if world > 1:
         dist.barrier()
     return ms / steps, kt, k2, launches, bufs
@@ -657,12 +677,13 @@ def roofline_of(wl, kt, steps, peak, peak_src):
     total_ms, n = kt.get(wl.kernel, (0.0, 0))
     if n == 0:
         return None
-    per_launch_ms = total_ms / n
+    live = wl.live_launches_per_step(n / steps) if hasattr(wl, "live_launches_per_step") else n / steps
+    per_launch_ms = total_ms / steps / max(live, 1e-9)
     alg = wl.alg_bytes_per_launch(n / steps)
     achieved = alg / (per_launch_ms * 1e-3) / 1e9
     return {"bound": "hbm", "kernel": wl.kernel, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "frac_of_8TBs": achieved / 8000.0, "traffic": None, "peak_source": peak_src,
-            "launches_per_step": n / steps, "avg_launch_ms": per_launch_ms, "algorithmic_bytes_per_launch": alg,
+            "launches_per_step": live, "avg_launch_ms": per_launch_ms, "algorithmic_bytes_per_launch": alg,
             "kernel_share_of_step_events": None}
 
 
@@ -812,7 +833,8 @@ def gpu_arm(args):
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if roof and os.path.exists(traffic_file):
         try:
-            roof["traffic"] = json.load(open(traffic_file)).get(wl.name, {}).get("dram_bytes_per_launch")
+            key = wl.name + ("_high_word_first" if getattr(wl, "high_word_first", False) else "")
+            roof["traffic"] = json.load(open(traffic_file)).get(key, {}).get("dram_bytes_per_launch")
         except Exception:
             pass
 
@@ -885,13 +907,15 @@ def gpu_arm(args):
                 if r2:
                     r2["kernel_share_of_step_events"] = (kt2[w2.kernel][0] / ks2) / ms2
                     try:
-                        r2["traffic"] = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(name, {}).get("dram_bytes_per_launch")
+                        r2["traffic"] = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(name + ("_high_word_first" if getattr(w2, "high_word_first", False) else ""), {}).get("dram_bytes_per_launch")
                     except Exception:
                         pass
                 extras[name] = {"rows": w2.n, "ms_per_step": ms2, "rows_per_s": w2.n / (ms2 * 1e-3),
                                 "input_gbs": w2.input_bytes() / (ms2 * 1e-3) / 1e9, "gpu_launches": l2,
                                 "roofline": r2, "description": w2.description,
                                 "kernel_ms_per_step": {k: v[0] / ks2 for k, v in kt2.items() if v[1]}}
+                if hasattr(w2, "plan"):
+                    extras[name]["plan"] = w2.plan
                 del c2, b2
                 torch.cuda.empty_cache()
                 # the same metric from host buffers (copies timed) and the reference's CPU kernels beside it
@@ -932,6 +956,7 @@ def gpu_arm(args):
             "input_gbs": value * wl.input_bytes() / wl.n / 1e9,
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
             "kernel_ms_per_step": {k: v[0] / kt_steps for k, v in kt.items() if v[1]},
+            "plan": getattr(wl, "plan", None),
             "kernel_timing": "per-launch CUDA events of a second pass of %d steps (the hook is off during the timed steps)" % kt_steps,
         }
         if world == 1 and not args.no_e2e:

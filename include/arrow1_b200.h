@@ -107,6 +107,12 @@ B200_API int b200_ctx_set_stream(b200_ctx* ctx, void* cu_stream);
  * time-sliced GPU) and flags the context; synchronize then returns B200_UNKNOWN_ERROR and clears the flag.  Callers
  * that consume results through their own stream synchronisation should call this once per batch of work. */
 B200_API int b200_ctx_synchronize(b200_ctx* ctx);
+/* Execution knobs of a context (no reference counterpart; results never depend on them).  Names:
+ *   "sort_high_word_first"   b200_sort_indices of a 64-bit column may sort by the upper key word alone (4 passes) and
+ *                            repair the ties afterwards: 0 = decided per call from the digit histograms (default),
+ *                            1 = always try, -1 = never
+ * B200_KEY_ERROR for an unknown name. */
+B200_API int b200_ctx_set_option(b200_ctx* ctx, const char* name, int64_t value);
 /* test hook: sets the flag b200_ctx_synchronize reports */
 B200_API int b200_ctx_inject_async_error(b200_ctx* ctx, uint32_t code);
 /* message of the last failure on this context ("" if none); valid until the next call */
@@ -220,6 +226,11 @@ B200_API int b200_sort_indices_scratch_bytes(int64_t length, size_t* out_bytes);
 B200_API int b200_sort_indices(b200_ctx* ctx, const b200_col* values, int order,
                                uint64_t index_base, uint64_t* out_indices, void* scratch,
                                size_t scratch_bytes);
+/* Which plan the last b200_sort_indices call that used `scratch` took (no reference counterpart; for benchmarks and
+ * tests): *out_high_word_first = the passes ran over the upper key word only and ties were repaired afterwards;
+ * *out_fell_back = that attempt met a tie run beyond the repair's limit and the ordinary 8-pass plan ran after it.
+ * Synchronises the context. */
+B200_API int b200_sort_indices_plan(b200_ctx* ctx, const void* scratch, int* out_high_word_first, int* out_fell_back);
 /* ChunkedArray input (ChunkedArraySorter, vector_sort.cc:657-832): the stable sort of the LOGICAL
  * CONCATENATION of the chunks — indices are global, nulls / NaNs of every chunk come last.  Each chunk's
  * radix keys and global row numbers are written side by side, pair-sorted by key, and one more stable pass

@@ -8,7 +8,7 @@ WL=${1:-}
 cat gpurun_out/prof_all_plain.log
 REP=/tmp/prof_r02_all
 timeout 1700 ncu --set full --clock-control none --import-source on --profile-from-start off \
-  -k regex:"sort_pass|sort_hist|filter_apply|gb_bin32|gb_hp_part|gb_hp_agg|gb_hp_hist|gb_fused8|gb_emit" \
+  -k regex:"sort_pass|sort_hist|hw_fix|tail_|filter_apply|gb_bin32|gb_hp_part|gb_hp_agg|gb_hp_hist|gb_fused8|gb_emit" \
   -o $REP python scripts/prof_all.py $WL > gpurun_out/prof_all_ncu.log 2>&1
 echo "ncu rc $?"; tail -3 gpurun_out/prof_all_ncu.log; ls -la $REP.ncu-rep
 ncu -i $REP.ncu-rep --page raw --csv > gpurun_out/prof_r02_all_raw.csv 2>/dev/null

@@ -285,3 +285,51 @@ def test_sort_indices_multi_key_chunked_table(ctx):
     with pytest.raises(B200Error):
         a = Column.from_numpy(np.arange(10, dtype=np.int32)).to_device()
         capi.sort_indices_multi(ctx, [[a, a], [a]], [0, 0])
+
+
+# ---- high word first (sort.cu HwState): 64-bit columns sorted by the upper key word, ties repaired afterwards -------
+def _hw_cases(rng):
+    n = 50_000
+    rnd = rng.integers(-2**63, 2**63 - 1, size=n, dtype=np.int64)
+    cases = {"random": rnd.copy()}
+    pairs = rnd.copy()                       # many short runs: rows sharing the upper word, lower words in random order
+    pairs[1::2] = (pairs[0::2] & ~np.int64(0xFFFFFFFF)) | rng.integers(0, 2**32, size=n // 2, dtype=np.int64)
+    cases["pairs"] = rng.permutation(pairs)
+    runs = rnd.copy()                        # runs of up to 32 rows (the repair's limit) and exact duplicates
+    for start in range(0, 2000, 40):
+        ln = int(rng.integers(2, 33))
+        runs[start:start + ln] = (runs[start] & ~np.int64(0xFFFFFFFF)) | rng.integers(0, 4, size=ln, dtype=np.int64)
+    cases["runs"] = rng.permutation(runs)
+    long_run = rnd.copy()                    # one run of 33+ rows: the repair gives up, round 2 runs the ordinary plan
+    long_run[:500] = (long_run[0] & ~np.int64(0xFFFFFFFF)) | rng.integers(0, 2**32, size=500, dtype=np.int64)
+    cases["long run"] = rng.permutation(long_run)
+    top = rnd.copy()                         # genuine keys in the run of the all-ones upper word, next to the nulls
+    top[:20] = np.int64(-1) << np.int64(32) | rng.integers(0, 2**32, size=20, dtype=np.int64)
+    top[20:25] = -1
+    top[25:30] = np.iinfo(np.int64).max
+    cases["top run"] = rng.permutation(top)
+    return cases
+
+
+@pytest.mark.parametrize("mode", [1, 0, -1])
+@pytest.mark.parametrize("t", [cols.INT64, cols.UINT64, cols.DOUBLE])
+def test_sort_indices_high_word_first(ctx, t, mode):
+    """Forced (1), decided from the histograms (0) and off (-1): always the reference's permutation."""
+    rng = np.random.default_rng(4242 + t)
+    ctx.set_option("sort_high_word_first", mode)
+    try:
+        for name, v in _hw_cases(rng).items():
+            vals = v.view(cols.NP_OF[t]).copy()
+            if t == cols.DOUBLE:
+                vals[:50] = np.nan
+                vals[50:60] = -0.0
+                vals[60:70] = 0.0
+            for nulls in (0.0, 0.02):
+                col = Column.from_numpy(vals, rng.random(len(vals)) >= nulls if nulls else None)
+                for order in (0, 1):
+                    want = oracle.sort_indices(col, order, kind=ORACLE)
+                    got = capi.sort_indices(ctx, col.to_device(), order, index_base=7).cpu().numpy().view(np.uint64)
+                    np.testing.assert_array_equal(got, want + np.uint64(7), err_msg="%s nulls=%s order=%d" % (name, nulls, order))
+        ctx.synchronize()
+    finally:
+        ctx.set_option("sort_high_word_first", 0)
