@@ -177,7 +177,37 @@ __global__ void __launch_bounds__(kHistThreads) sort_hist_kernel(SortParams p) {
   const int t = threadIdx.x;
   for (int i = t; i < kDigits * kBinStride; i += kHistThreads) (&h[0][0])[i] = 0;
   __syncthreads();
+  const int lane = t & 31, warp = t >> 5;
+  const bool wide = (p.keys_in != nullptr || p.width == 8) && p.n_digits == kDigits;
   for (int64_t base = int64_t(blockIdx.x) * kHistTile; base < p.n; base += int64_t(gridDim.x) * kHistTile) {
+    if (wide && base + kHistTile <= p.n) {
+      // full tile of 64-bit keys (the generic rows below cost ~120 instructions each: type switch, bitmap probe and
+      // 64-bit shifts per digit): a warp takes 512 consecutive rows, all 16 loads of a lane issued together, one
+      // validity word per 32 rows, digits cut out of the two key halves with PRMT
+      const int64_t wrow0 = base + int64_t(warp) * (kHistItems * 32);
+      uint32_t vword = 0xffffffffu;   // validity of rows wrow0 + 32 * lane .. + 31 (lanes 0..15)
+      if (p.vv.words && !p.keys_in && lane < kHistItems) vword = bitmap_load32(p.vv, wrow0 + lane * 32, p.n);
+      uint64_t raw[kHistItems];
+      const uint64_t* src = p.keys_in ? p.keys_in : reinterpret_cast<const uint64_t*>(p.vdata);
+#pragma unroll
+      for (int k = 0; k < kHistItems; ++k) raw[k] = src[wrow0 + k * 32 + lane];
+#pragma unroll
+      for (int k = 0; k < kHistItems; ++k) {
+        uint64_t key = raw[k];
+        if (!p.keys_in) {
+          uint32_t cls;
+          key = transform_key(p, raw[k], &cls);
+          if (!((__shfl_sync(0xffffffffu, vword, k) >> lane) & 1u)) key = p.wmask;
+        }
+        const uint32_t lo = uint32_t(key), hi = uint32_t(key >> 32);
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+          atomicAdd(&h[d][__byte_perm(lo, 0u, 0x4440u | uint32_t(d))], 1u);
+          atomicAdd(&h[d + 4][__byte_perm(hi, 0u, 0x4440u | uint32_t(d))], 1u);
+        }
+      }
+      continue;
+    }
 #pragma unroll 4
     for (int k = 0; k < kHistItems; ++k) {
       const int64_t row = base + k * kHistThreads + t;
