@@ -410,14 +410,15 @@ def sort_pairs(ctx: Context, keys: torch.Tensor, payload: torch.Tensor, want_key
     return (out_k[:n] if want_keys else None), out_p[:n]
 
 
-def sort_pairs32(ctx: Context, keys: torch.Tensor, payload32: torch.Tensor, want_keys: bool = False):
+def sort_pairs32(ctx: Context, keys: torch.Tensor, payload32: torch.Tensor, want_keys: bool = False,
+                 out: Optional[torch.Tensor] = None):
     """b200_sort_pairs32: stable sort of (uint64 key, uint32 payload) pairs; the payload travels through the
-    passes and comes out widened to uint64 (int64-typed tensor)."""
+    passes and comes out widened to uint64 (int64-typed tensor; `out`: a caller-owned slice to write it to)."""
     n = keys.numel()
     nb = C.c_size_t(0)
     ctx.check(lib().b200_sort_pairs_scratch_bytes(C.c_int64(n), C.byref(nb)))
     scratch = ctx.empty(nb.value)
-    out_p = torch.empty(max(n, 1), dtype=torch.int64, device=keys.device)
+    out_p = out if out is not None else torch.empty(max(n, 1), dtype=torch.int64, device=keys.device)
     out_k = torch.empty(max(n, 1), dtype=torch.int64, device=keys.device) if want_keys else None
     ctx.check(lib().b200_sort_pairs32(ctx._h, C.c_void_p(keys.data_ptr()), C.c_void_p(payload32.data_ptr()), C.c_int64(n),
                                       C.c_void_p(out_k.data_ptr()) if want_keys else None,

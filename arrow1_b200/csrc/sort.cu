@@ -84,13 +84,14 @@ struct PassInfo {
 // first split stably into [other keys | genuine maxima | NaNs | nulls] by the tail kernels, and only its first part is a
 // run to repair.  If a run is longer than 32 rows the estimate was wrong (correlated digits): a flag is raised and the
 // ordinary 8-pass plan runs after all (round 2: its launches are gated on the flag and otherwise exit at once).
+constexpr int kHwMaxRun = 32;   // longest run of equal upper words the repair sorts (one thread per run)
 struct HwState {
   uint32_t hw;            // the plan kernel chose high word first
   uint32_t fail;          // a tie run was too long: round 2 runs the ordinary plan
   int64_t top_start;      // first position of the run of the all-ones upper word (n if there is none)
   uint32_t class_total[4];
   uint32_t n_runs;        // runs of equal upper words found by the repair
-  uint32_t pad;
+  uint32_t top_count;     // keys whose upper word is all ones (counted by the histogram kernel)
 };
 
 struct SortParams {
@@ -172,13 +173,19 @@ __device__ __forceinline__ uint64_t source_key(const SortParams& p, int64_t row,
 // All digit histograms in one read of the column: shared-memory atomics, flushed once per CTA.
 // (Measured on B200 at 100 M 64-bit keys: 0.4 ms this way vs 5.3 ms with MATCH.ANY-aggregated
 // warp-private counters.)
+// kWide: 64-bit keys (a 64-bit column or ready-made keys) with all 8 digits live; its own instantiation, so that the
+// generic rows of the other shapes keep their 26 registers and 8 CTAs per SM
+template <bool kWide>
 __global__ void __launch_bounds__(kHistThreads) sort_hist_kernel(SortParams p) {
   __shared__ uint32_t h[kDigits][kBinStride];
+  __shared__ uint32_t top_s;   // keys whose upper word is all ones
   const int t = threadIdx.x;
   for (int i = t; i < kDigits * kBinStride; i += kHistThreads) (&h[0][0])[i] = 0;
+  if (t == 0) top_s = 0;
   __syncthreads();
   const int lane = t & 31, warp = t >> 5;
-  const bool wide = (p.keys_in != nullptr || p.width == 8) && p.n_digits == kDigits;
+  uint32_t top_mine = 0;
+  const bool wide = kWide;
   for (int64_t base = int64_t(blockIdx.x) * kHistTile; base < p.n; base += int64_t(gridDim.x) * kHistTile) {
     if (wide && base + kHistTile <= p.n) {
       // full tile of 64-bit keys (the generic rows below cost ~120 instructions each: type switch, bitmap probe and
@@ -200,6 +207,7 @@ __global__ void __launch_bounds__(kHistThreads) sort_hist_kernel(SortParams p) {
           if (!((__shfl_sync(0xffffffffu, vword, k) >> lane) & 1u)) key = p.wmask;
         }
         const uint32_t lo = uint32_t(key), hi = uint32_t(key >> 32);
+        top_mine += hi == 0xFFFFFFFFu ? 1u : 0u;
 #pragma unroll
         for (int d = 0; d < 4; ++d) {
           atomicAdd(&h[d][__byte_perm(lo, 0u, 0x4440u | uint32_t(d))], 1u);
@@ -214,6 +222,7 @@ __global__ void __launch_bounds__(kHistThreads) sort_hist_kernel(SortParams p) {
       if (row < p.n) {
         uint32_t cls;
         const uint64_t key = source_key(p, row, &cls);
+        top_mine += (key >> 32) == 0xFFFFFFFFull ? 1u : 0u;
 #pragma unroll
         for (int d = 0; d < kDigits; ++d) {
           if (d < p.n_digits) {
@@ -223,11 +232,14 @@ __global__ void __launch_bounds__(kHistThreads) sort_hist_kernel(SortParams p) {
       }
     }
   }
+  top_mine = __reduce_add_sync(0xffffffffu, top_mine);
+  if (lane == 0 && top_mine) atomicAdd(&top_s, top_mine);
   __syncthreads();
   for (int i = t; i < kDigits * kBinStride; i += kHistThreads) {
     const uint32_t c = (&h[0][0])[i];
     if (c) atomicAdd(p.hist + i, c);
   }
+  if (t == 0 && top_s && p.hws) atomicAdd(&p.hws->top_count, top_s);
 }
 
 // the passes of a plan: which digits run, which buffers they read, where the keys become 32-bit
@@ -309,6 +321,9 @@ __global__ void __launch_bounds__(kHistThreads) sort_scan_kernel(SortParams p) {
       const double bits = entropy_s[4] + entropy_s[5] + entropy_s[6] + entropy_s[7];
       hw = bits >= log2(double(p.n)) + 3.0;
       if (p.hw_allowed == 2) hw = !(skip_s[4] && skip_s[5] && skip_s[6] && skip_s[7]);   // forced (tests)
+      // the run of the all-ones upper word: a column sort splits it with the tail kernels (nulls, NaNs); plain
+      // (key, payload) pairs have no such help, and a long run there would only make the repair give up
+      if (!p.tail_fix && p.hws->top_count > uint32_t(kHwMaxRun)) hw = false;
     }
     write_plan(p, skip_s, hw, p.info);
     if (p.hws) {
@@ -418,7 +433,9 @@ struct PassSmem {
 // are ordered by the tail fix-up after the last pass; round 1 ranked every row of the last pass over 258 bins.)
 // kNarrow: the pass looks at one 32-bit word of the key only (digits 4..7 of a 64-bit key, or any digit of a
 // <= 32-bit column) and holds, stages and writes that word alone: 8 B per row and pass instead of 12.
-template <bool kFull, bool kNarrow>
+// kPairs: (key, payload) pairs under a possible high-word-first plan (its own instantiation: the column sorts' kernels
+// stay as they were)
+template <bool kFull, bool kNarrow, bool kPairs>
 __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d, const PassInfo info,
                                                PassSmem<typename std::conditional<kNarrow, uint32_t, uint64_t>::type>& s,
                                                const int64_t tile, const int tile_items) {
@@ -555,7 +572,7 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
 #pragma unroll
   for (int i = 0; i < kItems; ++i) {
     const int local = wbase + 32 * i;
-    if (info.first && !p.pay_in) pay[i] = uint32_t(tile_row0 + local);
+    if (info.first && (!p.pay_in || (kPairs && info.hw))) pay[i] = uint32_t(tile_row0 + local);   // (high word first: the POSITION travels, see below)
     else if (kFull && B200_SORT_TMA && !info.first) pay[i] = s.pay[local];
     else pay[i] = (kFull || local < tile_items) ? (info.first ? p.pay_in : pays_src)[tile_row0 + local] : 0u;
   }
@@ -678,7 +695,14 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
       const uint32_t bin = key_digit(kk, d);
       const uint32_t pos = uint32_t(j) + s.bin_delta[bin];
       if (info.last) {
-        p.out_idx[pos] = p.gather ? p.gather[pv] : (uint64_t(pv) + p.index_base);
+        if (kPairs && info.hw) {
+          // high word first over (key, payload) pairs: the position travelled through the passes (the repair looks
+          // the lower key word up by it); the payload is fetched now and the position kept beside the output
+          p.out_idx[pos] = uint64_t(p.pay_in[pv]);
+          pays_dst[pos] = pv;
+        } else {
+          p.out_idx[pos] = p.gather ? p.gather[pv] : (uint64_t(pv) + p.index_base);
+        }
         if (!kNarrow && p.out_keys) p.out_keys[pos] = kk;
         if (kNarrow && info.hw) keys32_dst[pos] = uint32_t(kk);   // the sorted upper words: the tie repair reads them
       } else {
@@ -694,7 +718,7 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
 // kLoop (round 2 of a failed high-word-first attempt, normally idle): a grid of a few CTAs per SM takes tiles until none
 // is left — tickets are handed out in order, so every tile a look-back waits for is already running — and the idle case
 // costs a few hundred CTAs that exit at once instead of one per tile
-template <bool kNarrow, bool kLoop>
+template <bool kNarrow, bool kLoop, bool kPairs = false>
 __global__ void __launch_bounds__(kThreads, kNarrow ? B200_SORT_NARROW_MINBLOCKS : kMinBlocks) sort_pass_kernel(SortParams p, int d) {
   const PassInfo info = p.info[d];
   if (info.skip) return;
@@ -724,8 +748,8 @@ __global__ void __launch_bounds__(kThreads, kNarrow ? B200_SORT_NARROW_MINBLOCKS
     const int64_t tile = s.tile;
     if (kLoop && tile >= p.n_tiles) return;
     const int tile_items = int(min(int64_t(kTile), p.n - tile * kTile));
-    if (tile_items == kTile) sort_pass_body<true, kNarrow>(p, d, info, s, tile, tile_items);
-    else sort_pass_body<false, kNarrow>(p, d, info, s, tile, tile_items);
+    if (tile_items == kTile) sort_pass_body<true, kNarrow, kPairs>(p, d, info, s, tile, tile_items);
+    else sort_pass_body<false, kNarrow, kPairs>(p, d, info, s, tile, tile_items);
     if (!kLoop) return;
     __syncthreads();   // the staging arrays and the ticket are about to be reused
   }
@@ -882,7 +906,6 @@ __global__ void tail_copy_kernel(const __grid_constant__ TailArgs a) {
 }
 
 // ---- high word first: the repair of the ties (see HwState) ------------------------------------------------------------
-constexpr int kHwMaxRun = 32;
 
 // the sorted upper words the last pass of a high-word-first plan left behind
 __device__ __forceinline__ const uint32_t* hw_words(const SortParams& p) {
@@ -991,6 +1014,8 @@ __global__ void __launch_bounds__(256) hw_fix_kernel(SortParams p) {
   const uint32_t* list = hw_run_list(p);
   const int64_t limit = hw_limit(p);
   const uint32_t n_runs = p.hws->n_runs;
+  const PassInfo last = last_pass(p);
+  const uint32_t* positions = p.pay_in ? p.pays[last.first ? 0 : (last.src ^ 1)] : nullptr;
   for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_runs; r += gridDim.x * blockDim.x) {
     const int64_t i = list[r];
     const uint32_t w = hi[i];
@@ -1005,7 +1030,10 @@ __global__ void __launch_bounds__(256) hw_fix_kernel(SortParams p) {
     for (int j = 0; j < len; ++j) {
       const uint64_t v = p.out_idx[i + j];
       uint32_t cls;
-      const uint32_t l = uint32_t(source_key(p, int64_t(v - p.index_base), &cls));
+      // where the element came from: its row (column sorts: the output is the row number) or, for (key, payload)
+      // pairs, the position the last pass left beside the output
+      const int64_t from = positions ? int64_t(positions[i + j]) : int64_t(v - p.index_base);
+      const uint32_t l = uint32_t(source_key(p, from, &cls));
       // stable insertion: the rows arrive in row order
       int q = j;
       while (q > 0 && low[q - 1] > l) {
@@ -1401,6 +1429,7 @@ int run_sort(b200_ctx* ctx, SortParams p, void* scratch, size_t scratch_bytes) {
     B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_narrow));
     B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_wide));
     B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_narrow));
+    B200_CUDA(ctx, cudaFuncSetAttribute(sort_pass_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_narrow));
   }
   // the caller wants the sorted 64-bit keys back: every pass carries them whole
   p.narrow = p.out_keys ? 0 : 1;
@@ -1413,8 +1442,15 @@ int run_sort(b200_ctx* ctx, SortParams p, void* scratch, size_t scratch_bytes) {
   p.hws = reinterpret_cast<HwState*>(base + L.hw);
   p.round2 = 0;
   p.hw_allowed = 0;
-  if (!p.keys_in && p.width == 8 && p.narrow && !p.gather && ctx->sort_high_word_first >= 0) p.hw_allowed = ctx->sort_high_word_first > 0 ? 2 : 1;
-  B200_TIMED(ctx, "sort_hist", (sort_hist_kernel<<<hist_blocks, kHistThreads, 0, ctx->stream>>>(p)));
+  // ... or 64-bit ready-made keys with a 32-bit payload (the second key of a multi-key sort, the received pairs of the
+  // multi-GPU sample sort)
+  const bool hw_column = !p.keys_in && p.width == 8;
+  const bool hw_pairs = p.keys_in && p.pay_in && p.n_digits == kDigits;
+  if ((hw_column || hw_pairs) && p.narrow && !p.gather && ctx->sort_high_word_first >= 0) p.hw_allowed = ctx->sort_high_word_first > 0 ? 2 : 1;
+  if ((p.keys_in != nullptr || p.width == 8) && p.n_digits == kDigits)
+    B200_TIMED(ctx, "sort_hist", (sort_hist_kernel<true><<<hist_blocks, kHistThreads, 0, ctx->stream>>>(p)));
+  else
+    B200_TIMED(ctx, "sort_hist", (sort_hist_kernel<false><<<hist_blocks, kHistThreads, 0, ctx->stream>>>(p)));
   sort_scan_kernel<<<1, kHistThreads, 0, ctx->stream>>>(p);
   B200_LAUNCHED(ctx);
   const int tail_blocks = std::min(kTailMaxBlocks, ctx->num_sms * 4);
@@ -1428,6 +1464,8 @@ int run_sort(b200_ctx* ctx, SortParams p, void* scratch, size_t scratch_bytes) {
           B200_TIMED(ctx, "sort_pass_round2", (sort_pass_kernel<true, true><<<loop_grid, kThreads, smem_narrow, ctx->stream>>>(q, d)));
         else
           B200_TIMED(ctx, "sort_pass_round2", (sort_pass_kernel<false, true><<<loop_grid, kThreads, smem_wide, ctx->stream>>>(q, d)));
+      } else if (narrow && q.hw_allowed && q.pay_in) {
+        B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<true, false, true><<<grid, kThreads, smem_narrow, ctx->stream>>>(q, d)));
       } else if (narrow) {
         B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<true, false><<<grid, kThreads, smem_narrow, ctx->stream>>>(q, d)));
       } else {

@@ -86,6 +86,10 @@ class CudaOps:
             return keys, torch.empty(0, dtype=torch.int64, device=self.device)
         return self.capi.sort_pairs32(self.ctx, keys, rows32, want_keys=want_keys)
 
+    def sort_pairs32_into(self, keys: torch.Tensor, rows32: torch.Tensor, out: torch.Tensor) -> None:
+        if keys.numel():
+            self.capi.sort_pairs32(self.ctx, keys, rows32, want_keys=False, out=out)
+
     def sample_keys(self, col: Column, order: int, count: int) -> torch.Tensor:
         """Radix keys of `count` regularly spaced rows (plumbing: a gathered mini-column through b200_sort_keys)."""
         from .columns import BITS
@@ -349,7 +353,17 @@ def _exchange_fused(ops, col, order, row_base, spl_unsigned, max_rows, world, ra
     total = incoming[rank]
     rk = ex.keys.tensor(torch.int64, total)
     rr = ex.rows.tensor(torch.int32, total)
-    _, out = ops.sort_pairs32(rk, rr, want_keys=False)
+    if rank == world - 1 and tail and hasattr(ops, "sort_pairs32_into"):
+        # the tail partition (keys >= the NaN key) sits behind the other runs and its size is known from the counts:
+        # it is sorted on its own — thousands of equal keys — so that the rest, keys that nearly identify their
+        # rows, can take the sort's upper-key-word-first plan (sort.cu HwState)
+        out = torch.empty(max(total, 1), dtype=torch.int64, device=dev)[:total]
+        body = total - tail
+        if body:
+            ops.sort_pairs32_into(rk[:body], rr[:body], out[:body])
+        ops.sort_pairs32_into(rk[body:], rr[body:], out[body:])
+    else:
+        _, out = ops.sort_pairs32(rk, rr, want_keys=False)
     _mark("sort_pairs")
     if rank == world - 1 and tail:
         # rows arrive as global row | class << 30; the stable sort left the tail partition at the end in

@@ -333,3 +333,26 @@ def test_sort_indices_high_word_first(ctx, t, mode):
         ctx.synchronize()
     finally:
         ctx.set_option("sort_high_word_first", 0)
+
+
+@pytest.mark.parametrize("mode", [1, 0, -1])
+def test_sort_pairs32_high_word_first(ctx, mode):
+    """(uint64 key, uint32 payload) pairs — the second key of a multi-key sort, the received pairs of the multi-GPU sort:
+    stable by key whatever the plan; a long run of all-ones keys (nulls) keeps the ordinary plan."""
+    import torch
+    rng = np.random.default_rng(99)
+    ctx.set_option("sort_high_word_first", mode)
+    try:
+        cases = _hw_cases(rng)
+        nulls = cases["random"].copy()
+        nulls[rng.random(len(nulls)) < 0.02] = -1          # 2 % all-ones keys
+        cases["all-ones run"] = nulls
+        for name, v in cases.items():
+            keys = v.view(np.uint64)
+            payload = rng.integers(0, 2**32, size=len(keys), dtype=np.uint32)
+            want = payload[np.argsort(keys, kind="stable")].astype(np.uint64)
+            _, got = capi.sort_pairs32(ctx, torch.from_numpy(keys.view(np.int64)).cuda(), torch.from_numpy(payload.view(np.int32)).cuda())
+            np.testing.assert_array_equal(got.cpu().numpy().view(np.uint64), want, err_msg=name)
+        ctx.synchronize()
+    finally:
+        ctx.set_option("sort_high_word_first", 0)
