@@ -205,7 +205,19 @@ class SortMultiWL(Workload):
         # value key: 8 live passes of (8 B key, 4 B row) pairs + 1 class pass; int32 key: 2 live passes
         # (values < 1000); every pass reads and writes 12 B/row, the last of a sort writes 8 B rows
         total = self.n * (11 * 24)
+        if self._high_word_first():
+            # the value key's sort took the upper-key-word-first plan (4 narrow passes, 68 B/row, see SortWL); the int32
+            # key's pair sort: 2 live passes of 24 B/row
+            return self.n * (68.125 + 2 * 24) / 6
         return total / max(launches_per_step, 1)
+
+    def _high_word_first(self):
+        # the tie repair only does work under that plan (0.27 ms per 100 M rows against 0.01 ms idle)
+        kt, steps = getattr(self, "_kt", None), getattr(self, "_kt_steps", 1)
+        return bool(kt) and kt.get("sort_tie_repair", (0.0, 0))[0] / max(steps, 1) > 0.001 * self.n / 1e6
+
+    def live_launches_per_step(self, launches_per_step):
+        return 6 if self._high_word_first() else launches_per_step
 
     def prepare(self, ctx, cols_):
         return {}
@@ -677,6 +689,7 @@ def roofline_of(wl, kt, steps, peak, peak_src):
     total_ms, n = kt.get(wl.kernel, (0.0, 0))
     if n == 0:
         return None
+    wl._kt, wl._kt_steps = kt, steps
     live = wl.live_launches_per_step(n / steps) if hasattr(wl, "live_launches_per_step") else n / steps
     per_launch_ms = total_ms / steps / max(live, 1e-9)
     alg = wl.alg_bytes_per_launch(n / steps)
