@@ -316,6 +316,14 @@ def sort_indices(ctx: Context, values: Column, order: int = 0, index_base: int =
     return out[:n]
 
 
+def sort_indices_plan(ctx: Context, scratch: torch.Tensor):
+    """b200_sort_indices_plan: (took the upper-key-word-first plan, fell back to the 8-pass plan) of the last
+    sort_indices call that used `scratch`."""
+    hw, fell_back = C.c_int(0), C.c_int(0)
+    ctx.check(lib().b200_sort_indices_plan(ctx._h, C.c_void_p(scratch.data_ptr()), C.byref(hw), C.byref(fell_back)))
+    return bool(hw.value), bool(fell_back.value)
+
+
 def sort_keys(ctx: Context, values: Column, order: int = 0) -> torch.Tensor:
     out = torch.empty(max(values.length, 1), dtype=torch.int64, device="cuda:%d" % ctx.device)
     v = values.desc()

@@ -1446,7 +1446,10 @@ int run_sort(b200_ctx* ctx, SortParams p, void* scratch, size_t scratch_bytes) {
   // multi-GPU sample sort)
   const bool hw_column = !p.keys_in && p.width == 8;
   const bool hw_pairs = p.keys_in && p.pay_in && p.n_digits == kDigits;
-  if ((hw_column || hw_pairs) && p.narrow && !p.gather && ctx->sort_high_word_first >= 0) p.hw_allowed = ctx->sort_high_word_first > 0 ? 2 : 1;
+  // (left to the estimate only from 2^18 rows on: the attempt costs a dozen extra launches, more than a small sort takes)
+  if ((hw_column || hw_pairs) && p.narrow && !p.gather && ctx->sort_high_word_first >= 0 &&
+      (ctx->sort_high_word_first > 0 || p.n >= (int64_t(1) << 18)))
+    p.hw_allowed = ctx->sort_high_word_first > 0 ? 2 : 1;
   if ((p.keys_in != nullptr || p.width == 8) && p.n_digits == kDigits)
     B200_TIMED(ctx, "sort_hist", (sort_hist_kernel<true><<<hist_blocks, kHistThreads, 0, ctx->stream>>>(p)));
   else

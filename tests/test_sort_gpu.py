@@ -356,3 +356,23 @@ def test_sort_pairs32_high_word_first(ctx, mode):
         ctx.synchronize()
     finally:
         ctx.set_option("sort_high_word_first", 0)
+
+
+def test_sort_indices_plan_is_chosen_from_the_histograms(ctx):
+    """Left to the estimate: random int64 takes the upper-key-word-first plan, float64 data (few distinct exponent
+    words) and a small column do not, a column with one long run of equal upper words tries and falls back."""
+    rng = np.random.default_rng(31)
+    n = 300_000
+    rnd = rng.integers(-2**63, 2**63 - 1, size=n, dtype=np.int64)
+    long_run = rnd.copy()
+    long_run[:1000] = (long_run[0] & ~np.int64(0xFFFFFFFF)) | rng.integers(0, 2**32, size=1000, dtype=np.int64)
+    cases = [("random int64", Column.from_numpy(rnd, rng.random(n) > 0.01), (True, False)),
+             ("float64 with few distinct upper words", Column.from_numpy(rng.integers(0, 1000, size=n).astype(np.float64) + rng.random(n) * 1e-9,
+                                                                        rng.random(n) > 0.01), (False, False)),
+             ("long run", Column.from_numpy(rng.permutation(long_run)), (True, True)),
+             ("small", Column.from_numpy(rnd[:50_000].copy()), (False, False))]
+    for name, col, plan in cases:
+        scratch = ctx.empty(capi.sort_scratch_bytes(ctx, col.length))
+        got = capi.sort_indices(ctx, col.to_device(), 0, scratch=scratch).cpu().numpy().view(np.uint64)
+        np.testing.assert_array_equal(got, oracle.sort_indices(col, 0, kind=ORACLE), err_msg=name)
+        assert capi.sort_indices_plan(ctx, scratch) == plan, name
