@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """One step of every hot-path workload between cudaProfilerStart / Stop, after an unprofiled warm-up step each, so that
-ONE `ncu --profile-from-start off` command captures one launch sequence of each kernel (scripts/gpu_r2_prof.sh).
+ONE `ncu --profile-from-start off` command captures one launch sequence of each kernel (scripts/gpu_profile.sh).
 Without ncu it just runs the steps and prints their wall times (the command must exit 0 on its own first)."""
 import os
 import sys
