@@ -12,12 +12,5 @@ timeout 1700 ncu --set full --clock-control none --import-source on --profile-fr
   -o $REP python scripts/prof_all.py $WL > gpurun_out/prof_all_ncu.log 2>&1
 echo "ncu rc $?"; tail -3 gpurun_out/prof_all_ncu.log; ls -la $REP.ncu-rep
 ncu -i $REP.ncu-rep --page raw --csv > gpurun_out/prof_r02_all_raw.csv 2>/dev/null
-N=$(python - <<'PY'
-import csv
-rows = list(csv.reader(open('gpurun_out/prof_r02_all_raw.csv')))
-print(max(len(rows) - 2, 0))
-PY
-)
-echo "captured $N launches"
-for i in $(seq 0 $((N-1))); do python scripts/ncu_summary.py $REP.ncu-rep $i > gpurun_out/prof_r02_summary_$i.txt 2>&1; done
+# (the per-launch summaries are made afterwards, off the box: scripts/ncu_summary.py report.ncu-rep <launch>)
 SZ=$(stat -c %s $REP.ncu-rep); if [ "$SZ" -lt 45000000 ]; then cp $REP.ncu-rep gpurun_out/prof_r02_all.ncu-rep; fi
