@@ -165,6 +165,51 @@ def test_grouper_golden(impl, request):
             _grouper_sequence(impl, ctx, seq["key_types"], seq["batches"])
 
 
+def _json_column(values, type_name):
+    if type_name == "binary":
+        return cols.Column.from_strings(values)
+    return column_from_json(values, type_name)
+
+
+@pytest.mark.parametrize("impl", IMPLS[1:])
+def test_grouper_string_keys_golden(impl, request):
+    """Grouper.StringKey / StringInt64Key / DoubleStringInt64Key of the reference's own tests (the C++ restatement in
+    oracle/oracle.cc has no variable-length keys: the compiled reference and the CUDA path are checked)."""
+    g = load_golden("group_by.json")
+    ctx = _ctx(impl, request)
+    for seq in g["grouper_string_sequences"]:
+        types = seq["key_types"]
+        if impl == "gpu":
+            from arrow1_b200 import capi
+            gb = capi.GroupBy(ctx, [TYPE_BY_NAME[t] for t in types], [], [])
+            for b in seq["batches"]:
+                keys = [_json_column(v, t).to_device() for v, t in zip(b["keys"], types)]
+                ids = gb.grouper_consume(keys).cpu().numpy().view(np.uint32)
+                np.testing.assert_array_equal(ids, np.array(b["ids"], dtype=np.uint32), err_msg=str((types, b)))
+            gb.close()
+            continue
+        acc, expected = [[] for _ in types], []
+        for b in seq["batches"]:
+            for i, v in enumerate(b["keys"]):
+                acc[i] += v
+            expected += b["ids"]
+            r = oracle.groupby([_json_column(v, t) for v, t in zip(acc, types)], [], [], want_ids=True, kind=impl)
+            np.testing.assert_array_equal(r.ids, np.array(expected, dtype=np.uint32), err_msg=str((types, b)))
+
+
+@pytest.mark.parametrize("impl", IMPLS[1:])
+def test_group_by_string_key_golden(impl, request):
+    """GroupBy.SumOnlyStringAndDictKeys (utf8 key): sums, the null sum of a group without values, group order, the
+    null key as its own group."""
+    e = load_golden("group_by.json")["sum_only_string_key"]
+    ctx = _ctx(impl, request)
+    r = run_groupby(impl, [Column.from_strings(e["key"])], [AggSpec(cols.HASH_SUM)], [column_from_json(e["argument"], "double")], ctx)
+    assert r.num_groups == 4
+    _cmp(r.aggs[0][0], e["hash_sum"], "double")
+    vals, valid = r.keys[0]
+    assert [v.decode() if ok else None for v, ok in zip(vals, valid)] == e["key_0"]
+
+
 @pytest.mark.parametrize("impl", IMPLS)
 def test_sort_indices_multi_key_golden(impl, request):
     """TestRecordBatchSortIndices / TestTableSortIndices: two sort keys, nulls and NaNs, one chunk and several."""
@@ -188,3 +233,77 @@ def test_sort_indices_multi_key_golden(impl, request):
             else:
                 got = oracle.sort_indices_multi(keys, case["orders"])
             np.testing.assert_array_equal(got, want, err_msg=case["name"])
+
+
+# ---- unique / value_counts / dictionary_encode: the reference's own known-answer tests (vector_hash_test.cc) ----------
+_HASH_NUMERIC = ["uint8", "int8", "uint16", "int16", "uint32", "int32", "uint64", "int64", "float", "double"]
+
+
+def _hash_column(case, type_name):
+    col = _json_column(case["values"], type_name) if not case.get("offset") else None
+    if col is None:
+        off = case["offset"]
+        if type_name == "binary":
+            col = cols.Column.from_strings(case["values"], offset=off)
+        else:
+            col = column_from_json(case["values"], type_name, offset=off)
+        col.length = case["length"]
+        col.null_count = -1
+    return col
+
+
+def _as_list(vals, valid, type_name):
+    if type_name == "binary":
+        return [v.decode() if ok else None for v, ok in zip(vals, valid)]
+    return [(float(v) if type_name in ("float", "double") else int(v)) if ok else None for v, ok in zip(vals, valid)]
+
+
+def _host_pair(col):
+    h = col.to_host()
+    if h.type == cols.BINARY:
+        s = h.strings()
+        return [b"" if x is None else x for x in s], h.valid()
+    return h.values(), h.valid()
+
+
+@pytest.mark.parametrize("impl", IMPLS[1:])
+def test_vector_hash_golden(impl, request):
+    g = load_golden("vector_hash.json")
+    ctx = _ctx(impl, request)
+    if impl == "gpu":
+        from arrow1_b200 import compute
+
+    def types_of(case):
+        return _HASH_NUMERIC if case["type"] == "NUMERIC" else [case["type"]]
+
+    for case in g["unique"]:
+        for t in types_of(case):
+            col = _hash_column(case, t)
+            if impl == "gpu":
+                vals, valid = _host_pair(compute.Unique(col.to_device(), ctx))
+            else:
+                (vals, valid), _ = oracle.value_counts(col, False)
+            assert _as_list(vals, valid, t) == case["expected"], ("unique", t, case)
+    for case in g["value_counts"]:
+        for t in types_of(case):
+            col = _hash_column(case, t)
+            if impl == "gpu":
+                keys, counts = compute.ValueCounts(col.to_device(), ctx)
+                vals, valid = _host_pair(keys)
+                counts = counts.cpu().numpy()
+            else:
+                (vals, valid), counts = oracle.value_counts(col, True)
+            assert _as_list(vals, valid, t) == case["expected"], ("value_counts", t, case)
+            assert [int(c) for c in counts] == case["counts"], ("value_counts", t, case)
+    for case in g["dictionary_encode"]:
+        for t in types_of(case):
+            col = _hash_column(case, t)
+            if impl == "gpu":
+                idx, dictionary = compute.DictionaryEncode(col.to_device(), case["encode_nulls"], ctx)
+                hi = idx.to_host()
+                ivals, ivalid = hi.values(), hi.valid()
+                dvals, dvalid = _host_pair(dictionary)
+            else:
+                ivals, ivalid, (dvals, dvalid) = oracle.dictionary_encode(col, case["encode_nulls"])
+            assert [int(v) if ok else None for v, ok in zip(ivals, ivalid)] == case["indices"], ("dictionary_encode", t, case)
+            assert _as_list(dvals, dvalid, t) == case["dictionary"], ("dictionary_encode", t, case)
