@@ -386,6 +386,12 @@ __device__ __forceinline__ unsigned match_bit(unsigned m, uint32_t bin, uint32_t
 // (round 2, profiles/r02_sort_variants.txt): 5.85 ms per 100 M int64 rows against 5.66 ms with the votes — the pass
 // already spends its shared-memory wavefronts on digit-random addresses (48 % bank conflicts), three more per item
 // cost more than the issue slots they free.
+// digits 0..3 launched in the looping form when the high-word-first plan may skip them (see run_sort).  MEASURED AND
+// LEFT OFF (profiles/r02_sort_variants.txt): a skipped pass costs 4 us instead of 17 (sort_i64 3.15 -> 3.10 ms), but a
+// column that keeps the 8-pass plan runs those four passes in the looping form, which spills more: sort_f64 5.52 -> 6.04 ms
+#ifndef B200_SORT_LOOP_LOW
+#define B200_SORT_LOOP_LOW 0
+#endif
 #ifndef B200_SORT_MATCH_ATOMIC
 #define B200_SORT_MATCH_ATOMIC 0
 #endif
@@ -722,7 +728,7 @@ template <bool kNarrow, bool kLoop, bool kPairs = false>
 __global__ void __launch_bounds__(kThreads, kNarrow ? B200_SORT_NARROW_MINBLOCKS : kMinBlocks) sort_pass_kernel(SortParams p, int d) {
   const PassInfo info = p.info[d];
   if (info.skip) return;
-  if (kLoop && p.hws->fail == 0) return;
+  if (kLoop && p.round2 && p.hws->fail == 0) return;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   using Smem = PassSmem<typename std::conditional<kNarrow, uint32_t, uint64_t>::type>;
   Smem& s = *reinterpret_cast<Smem*>(smem_raw);
@@ -1467,6 +1473,11 @@ int run_sort(b200_ctx* ctx, SortParams p, void* scratch, size_t scratch_bytes) {
           B200_TIMED(ctx, "sort_pass_round2", (sort_pass_kernel<true, true><<<loop_grid, kThreads, smem_narrow, ctx->stream>>>(q, d)));
         else
           B200_TIMED(ctx, "sort_pass_round2", (sort_pass_kernel<false, true><<<loop_grid, kThreads, smem_wide, ctx->stream>>>(q, d)));
+      } else if (!narrow && q.hw_allowed && B200_SORT_LOOP_LOW) {
+        // digits 0..3 of a sort that may take the high-word-first plan (which skips them): the looping form, a few
+        // hundred CTAs instead of one per tile, so that a skipped pass costs 4 us instead of 17
+        const unsigned loop_grid = unsigned(std::min<int64_t>(q.n_tiles, int64_t(ctx->num_sms) * 3));
+        B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<false, true><<<loop_grid, kThreads, smem_wide, ctx->stream>>>(q, d)));
       } else if (narrow && q.hw_allowed && q.pay_in) {
         B200_TIMED(ctx, "sort_pass", (sort_pass_kernel<true, false, true><<<grid, kThreads, smem_narrow, ctx->stream>>>(q, d)));
       } else if (narrow) {
