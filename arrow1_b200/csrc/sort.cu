@@ -455,7 +455,6 @@ __device__ __forceinline__ void sort_pass_body(const SortParams& p, const int d,
   const uint32_t* pays_src = p.pays[info.src];
   uint32_t* state = p.state + (size_t(d) * p.n_tiles + tile) * kBinStride;
   const int wbase = warp * (kItems * 32) + lane;  // item i sits at local index wbase + 32*i
-  const int shift = 8 * d;
 
   // ---- load: all global loads are issued back to back, transforms follow
   KeyT key[kItems];
