@@ -999,7 +999,21 @@ constexpr int kBinThreads = 1024;
 constexpr int kBinRows = kFastSub * kFastSubs;          // rows per thread per tile (8)
 constexpr int kBinSubRows = kBinThreads * kFastSub;     // 4096
 constexpr int kBinTile = kBinThreads * kBinRows;        // 8192
-constexpr int kBinCap = 16;                             // values per group per tile before the overflow path
+// Two knobs measured on C3 (1 B rows, 1 K keys, B200) and left at their defaults (scripts/build_variants.sh):
+//   B200_BIN_CAP  16 -> 14 puts BinSmem under 196 KB, i.e. 60 KB of L1 instead of 28 KB: 6.36 -> 6.51 ms (slower: more
+//                 rows on the CAS overflow path, and the larger L1 buys nothing)
+//   B200_BIN_LD   1 = column loads with L1::no_allocate, 2 = the four values of a thread as ONE 256-bit load: 6.36 ms
+//                 either way.  Together with the steady-state form of the row loop (-25 % instructions, -2 % time)
+//                 this says what bounds the kernel: not the loads, not issue slots, but the one shared-memory rank
+//                 atomic per row (ATOMS with spread addresses retires ~2 cycles per lane: 8192 rows = ~16 K cycles
+//                 per tile per SM, the tile is measured at ~15 K)
+#ifndef B200_BIN_CAP
+#define B200_BIN_CAP 16
+#endif
+#ifndef B200_BIN_LD
+#define B200_BIN_LD 0
+#endif
+constexpr int kBinCap = B200_BIN_CAP;                   // values per group per tile before the overflow path
 constexpr int kBinSlots = 4096;                         // KEY32 table: {key, group id} pairs, load <= 1/4
 constexpr uint32_t kBinGidOverflow = 0xFFFFFFFEu;     // == -2 as int: "cannot be placed"
 
@@ -1460,6 +1474,9 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin_kernel(const __grid_con
 // the few cycles until it is).  Every slot remembers the tile it was born in, because a row that HITS a
 // key born in the current tile may still be the group's first row (warps are not ordered inside a tile).
 constexpr uint32_t kB32Unset = 0xFFFFu, kB32Overflow = 0xFFFEu;
+// whole-word forms of the two markers: a published id word is (birth tile << 16) | id with id < 1024, so
+// "found, placed and born before tile T" is the single unsigned compare  word < (T << 16)  (tiles only grow)
+constexpr uint32_t kB32UnsetWord = 0xFFFFFFFFu, kB32OverflowWord = 0xFFFFFFFEu;
 
 struct Raw32 {
   uint4 k;
@@ -1482,7 +1499,7 @@ __device__ __forceinline__ int b32_find_or_insert(BinSmem& S, uint32_t k, uint32
         cur = atomicCAS(&S.ktab[h].x, kEmpty32, k);
         if (cur == kEmpty32) {
           const uint32_t g = atomicAdd(&S.n_groups, 1u);
-          const uint32_t y = (g < uint32_t(kFastGroups) ? g : kB32Overflow) | (tile << 16);
+          const uint32_t y = g < uint32_t(kFastGroups) ? (g | (tile << 16)) : kB32OverflowWord;
           *reinterpret_cast<volatile uint32_t*>(&S.ktab[h].y) = y;
           *fresh = true;
           return g < uint32_t(kFastGroups) ? int(g) : -2;
@@ -1509,7 +1526,7 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin32_kernel(const __grid_c
   extern __shared__ __align__(16) unsigned char smem[];
   BinSmem& S = *reinterpret_cast<BinSmem*>(smem);
   const int t = threadIdx.x;
-  for (int i = t; i < kBinSlots; i += kBinThreads) S.ktab[i] = make_uint2(kEmpty32, kB32Unset);
+  for (int i = t; i < kBinSlots; i += kBinThreads) S.ktab[i] = make_uint2(kEmpty32, kB32UnsetWord);
   S.sum[t] = 0;
   S.mn[t] = ~uint64_t(0);
   S.mx[t] = 0;
@@ -1543,10 +1560,22 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin32_kernel(const __grid_c
   // half-tile h (4096 rows) of this CTA starts at row begin + h * kBinSubRows; this thread owns 4 rows of it
   auto request = [&](Raw32& r, int64_t r0) {
     if (r0 < end) {
+#if B200_BIN_LD == 0
       r.k = *reinterpret_cast<const uint4*>(kcol + r0);
       const ulonglong2* vp = reinterpret_cast<const ulonglong2*>(vcol + r0);
       r.va = vp[0];
       r.vb = vp[1];
+#else
+      asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                   : "=r"(r.k.x), "=r"(r.k.y), "=r"(r.k.z), "=r"(r.k.w) : "l"(kcol + r0));
+#if B200_BIN_LD == 2
+      asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
+                   : "=l"(r.va.x), "=l"(r.va.y), "=l"(r.vb.x), "=l"(r.vb.y) : "l"(vcol + r0));
+#else
+      asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];" : "=l"(r.va.x), "=l"(r.va.y) : "l"(vcol + r0));
+      asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];" : "=l"(r.vb.x), "=l"(r.vb.y) : "l"(vcol + r0 + 2));
+#endif
+#endif
       if (vbytes) {
         // r0 is a multiple of 4: its 4 validity bits never straddle more than two bytes
         const int64_t byte = ((voff + r0) >> 3) & ~int64_t(1);
@@ -1570,26 +1599,70 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin32_kernel(const __grid_c
     }
     int gid[4];
     uint32_t fresh = 0, defer = 0, over = 0, zeros = 0;
+    // steady state (every tile but the first few): the four keys are in the table, born in an earlier tile, and
+    // the four values are valid.  Four independent probes, two compares per row, then four independent rank
+    // atomics: no branch between them, nothing of the insert / first-row / null machinery below is touched
+    // (the generic form spent ~50 instructions per row here, half of them branch and re-convergence overhead)
+    bool steady;
+    {
+      uint2 e[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      bool f = false;
-      gid[i] = key[i] == kEmpty32 ? -2 : b32_find_or_insert(S, key[i], tile, &f);
-      if (f) fresh |= 1u << i;
-    }
+      for (int i = 0; i < 4; ++i) e[i] = S.ktab[bin_hash32(key[i])];
+      const uint32_t born_before = tile << 16;
+      uint32_t miss = 0;   // no short-circuit: the four loads are in flight together
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int g = gid[i];
-      if (g < 0) {
-        defer |= 1u << i;
-        continue;
+      for (int i = 0; i < 4; ++i) miss |= (e[i].x ^ key[i]) | uint32_t(e[i].y >= born_before);
+      steady = miss == 0;
+      if (steady) {
+        // a null row counts in nulls[] instead of taking a rank: same instruction, other counter array, so that
+        // lanes with and without nulls stay on one path (1 % nulls puts a null into 3 of 4 warps)
+        uint32_t rk[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          gid[i] = int(e[i].y & 0xFFFFu);
+          const bool valid = (vmask >> i) & 1u;
+          const uint32_t r = atomicAdd(valid ? &S.tcnt[gid[i]] : &S.nulls[gid[i]], 1u);
+          rk[i] = valid ? r : 0u;
+        }
+        uint32_t mag = 0xFFFFFFFFu;   // smallest |upper word| of the valid values: 0 <=> one of them may be +-0.0
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          if ((vmask >> i) & 1u) {
+            if (rk[i] < uint32_t(kBinCap)) S.bins[rk[i] * kFastGroups + gid[i]] = vbits[i];
+            mag = min(mag, uint32_t(vbits[i] >> 32) & 0x7FFFFFFFu);
+          }
+        }
+        if ((max(max(rk[0], rk[1]), max(rk[2], rk[3])) >= uint32_t(kBinCap)) | (mag == 0)) {   // rare
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            if (rk[i] >= uint32_t(kBinCap)) over |= 1u << i;
+            if (((vmask >> i) & 1u) && (uint32_t(vbits[i] >> 32) & 0x7FFFFFFFu) == 0) zeros |= 1u << i;   // candidate +-0.0
+          }
+        }
       }
-      if ((vmask >> i) & 1u) {
-        const uint32_t rk = atomicAdd(&S.tcnt[g], 1u);
-        if (rk < uint32_t(kBinCap)) S.bins[rk * kFastGroups + g] = vbits[i];
-        else over |= 1u << i;
-        if ((uint32_t(vbits[i] >> 32) & 0x7FFFFFFFu) == 0) zeros |= 1u << i;   // candidate +-0.0
-      } else {
-        atomicAdd(&S.nulls[g], 1u);
+    }
+    if (!steady) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        bool f = false;
+        gid[i] = key[i] == kEmpty32 ? -2 : b32_find_or_insert(S, key[i], tile, &f);
+        if (f) fresh |= 1u << i;
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int g = gid[i];
+        if (g < 0) {
+          defer |= 1u << i;
+          continue;
+        }
+        if ((vmask >> i) & 1u) {
+          const uint32_t rk = atomicAdd(&S.tcnt[g], 1u);
+          if (rk < uint32_t(kBinCap)) S.bins[rk * kFastGroups + g] = vbits[i];
+          else over |= 1u << i;
+          if ((uint32_t(vbits[i] >> 32) & 0x7FFFFFFFu) == 0) zeros |= 1u << i;   // candidate +-0.0
+        } else {
+          atomicAdd(&S.nulls[g], 1u);
+        }
       }
     }
     fresh &= ~defer;
@@ -1660,16 +1733,14 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin32_kernel(const __grid_c
 #pragma unroll 1
   for (int64_t base = begin; base < end; base += kBinTile, ++tile) {
     const int64_t r0 = base + int64_t(t) * kFastSub;
-    {
-      const Raw32 cur = ra;
-      request(ra, r0 + 2 * kBinSubRows);
-      work(cur, r0, tile & 0xFFFFu);
-    }
-    {
-      const Raw32 cur = rb;
-      request(rb, r0 + 3 * kBinSubRows);
-      work(cur, r0 + kBinSubRows, tile & 0xFFFFu);
-    }
+    // the next request goes into the registers the work has just consumed (a copy of the half-tile kept
+    // beside two outstanding requests did not fit 64 registers: 48 B of stack per thread, i.e. spills to L2
+    // with 205 KB of the SM's memory taken by the bins).  Its lead is still the other half-tile's work, the
+    // reduction and both barriers
+    work(ra, r0, tile & 0xFFFFu);
+    request(ra, r0 + 2 * kBinSubRows);
+    work(rb, r0 + kBinSubRows, tile & 0xFFFFu);
+    request(rb, r0 + 3 * kBinSubRows);
     __syncthreads();
     // ---- every thread reduces the bin of its own group with plain adds / compares
     {
@@ -3059,7 +3130,7 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
         const int smem = binned ? int(sizeof(BinSmem)) : int(sizeof(FastSmem));
         const bool k32 = a.s.n_keys == 1 && a.keys[0].nbits == 32 && !a.keys[0].vv.words && (reinterpret_cast<uintptr_t>(a.keys[0].data) & 15) == 0;
         const bool k64 = a.s.n_keys == 1 && a.keys[0].nbits == 64 && !a.keys[0].vv.words && (reinterpret_cast<uintptr_t>(a.keys[0].data) & 15) == 0;
-        const bool vfast = a.n_cols == 1 && b200_type_bits(a.cols[0].type) == 64 && (reinterpret_cast<uintptr_t>(a.cols[0].data) & 15) == 0;
+        const bool vfast = a.n_cols == 1 && b200_type_bits(a.cols[0].type) == 64 && (reinterpret_cast<uintptr_t>(a.cols[0].data) & (B200_BIN_LD == 2 ? 31 : 15)) == 0;
         if (b200_ctx_once(ctx, 5)) {
           const int mx = int(sizeof(FastSmem));
           B200_CUDA(ctx, cudaFuncSetAttribute(gb_fast_kernel<0, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
