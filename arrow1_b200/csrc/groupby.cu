@@ -1004,14 +1004,19 @@ constexpr int kBinTile = kBinThreads * kBinRows;        // 8192
 //                 rows on the CAS overflow path, and the larger L1 buys nothing)
 //   B200_BIN_LD   1 = column loads with L1::no_allocate, 2 = the four values of a thread as ONE 256-bit load: 6.36 ms
 //                 either way.  Together with the steady-state form of the row loop (-25 % instructions, -2 % time)
-//                 this says what bounds the kernel: not the loads, not issue slots, but the one shared-memory rank
-//                 atomic per row (ATOMS with spread addresses retires ~2 cycles per lane: 8192 rows = ~16 K cycles
-//                 per tile per SM, the tile is measured at ~15 K)
+//                 these pointed away from the memory system — wrongly: the ncu source page of that form showed 20 %
+//                 of the samples on two register moves placed right behind the column loads (see the loop head of
+//                 gb_bin32_kernel); with one load site per buffer and the L2 prefetch below the kernel is at 5.84 ms
 #ifndef B200_BIN_CAP
 #define B200_BIN_CAP 16
 #endif
 #ifndef B200_BIN_LD
 #define B200_BIN_LD 0
+#endif
+// tiles whose key / value bytes are prefetched into L2 ahead of the demand loads, see gb_bin32_kernel.  Measured on C3
+// (kernel ms per 1 B rows): 0 (off) 6.47, 1 5.84, 2 5.91, 3 6.08, 4 6.21
+#ifndef B200_BIN_PF
+#define B200_BIN_PF 1
 #endif
 constexpr int kBinCap = B200_BIN_CAP;                   // values per group per tile before the overflow path
 constexpr int kBinSlots = 4096;                         // KEY32 table: {key, group id} pairs, load <= 1/4
@@ -1481,8 +1486,7 @@ constexpr uint32_t kB32UnsetWord = 0xFFFFFFFFu, kB32OverflowWord = 0xFFFFFFFEu;
 struct Raw32 {
   uint4 k;
   ulonglong2 va, vb;
-  uint16_t vm0;   // validity bytes, kept as loaded: combining them at request time would wait for the loads
-  uint8_t vm1;
+  uint16_t vm0;   // the 16-bit validity word holding the four rows' bits (bit offset % 4 == 0, see the dispatch)
 };
 
 // key -> dense group id (>= 0), or -2 when the CTA's table is full.  *fresh = the group was born in `tile`.
@@ -1558,8 +1562,13 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin32_kernel(const __grid_c
   const int64_t voff = a.cols[0].vv.bit_offset;
 
   // half-tile h (4096 rows) of this CTA starts at row begin + h * kBinSubRows; this thread owns 4 rows of it
+  // (no branch around the loads: past the CTA's last row the thread re-reads its rows of the first half-tile and
+  // nobody looks at them.  With `if (r0 < end)` the two paths met in registers of the compiler's choosing and the
+  // loaded values were MOVED there right behind the loads: the profile showed the whole memory latency on those
+  // two moves, 20 % of the kernel's samples)
   auto request = [&](Raw32& r, int64_t r0) {
-    if (r0 < end) {
+    r0 = r0 < end ? r0 : begin + int64_t(t) * kFastSub;
+    {
 #if B200_BIN_LD == 0
       r.k = *reinterpret_cast<const uint4*>(kcol + r0);
       const ulonglong2* vp = reinterpret_cast<const ulonglong2*>(vcol + r0);
@@ -1577,17 +1586,16 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin32_kernel(const __grid_c
 #endif
 #endif
       if (vbytes) {
-        // r0 is a multiple of 4: its 4 validity bits never straddle more than two bytes
+        // r0 and the bit offset are multiples of 4: the 4 validity bits lie inside one 16-bit aligned word
         const int64_t byte = ((voff + r0) >> 3) & ~int64_t(1);
         r.vm0 = __ldg(reinterpret_cast<const uint16_t*>(vbytes + byte));
-        r.vm1 = __ldg(vbytes + byte + 2);
       }
     }
   };
   // one half-tile of this thread's rows: lookup / insert, slot in the bin, rare side paths
   auto work = [&](const Raw32& r, int64_t r0, uint32_t tile) {
     if (a.dbg & 8) {   // timing experiment: loads only
-      if ((r.k.x ^ r.k.y ^ r.k.z ^ r.k.w ^ uint32_t(r.va.x ^ r.va.y ^ r.vb.x ^ r.vb.y) ^ r.vm0 ^ r.vm1) == 0x12345678u) S.deferred = 1;
+      if ((r.k.x ^ r.k.y ^ r.k.z ^ r.k.w ^ uint32_t(r.va.x ^ r.va.y ^ r.vb.x ^ r.vb.y) ^ r.vm0) == 0x12345678u) S.deferred = 1;
       return;
     }
     const uint32_t key[4] = {r.k.x, r.k.y, r.k.z, r.k.w};
@@ -1595,7 +1603,7 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin32_kernel(const __grid_c
     uint32_t vmask = 0xFu;
     if (vbytes) {
       const int64_t bit = voff + r0;
-      vmask = ((uint32_t(r.vm0) | (uint32_t(r.vm1) << 16)) >> (int(bit & 7) + 8 * int((bit >> 3) & 1))) & 0xFu;
+      vmask = (uint32_t(r.vm0) >> int(bit & 15)) & 0xFu;
     }
     int gid[4];
     uint32_t fresh = 0, defer = 0, over = 0, zeros = 0;
@@ -1725,22 +1733,37 @@ __global__ void __launch_bounds__(kBinThreads, 1) gb_bin32_kernel(const __grid_c
     }
   };
 
+  // The demand loads above are issued at most one tile ahead (registers), and the profile of that form shows the
+  // work phase waiting for them (long scoreboard on the first use of a half-tile, DRAM at 28 %).  Six threads
+  // therefore ask the copy engine to pull the tile after next (.. B200_BIN_PF tiles ahead) into L2, 16 KB each: no
+  // registers, no shared memory, no entry in the L1 miss queue; the demand load then only has L2 latency to cover.
+  auto prefetch_tile = [&](int64_t base) {
+    if (B200_BIN_PF > 0 && t < 6 && base < end) {
+      const void* p = t < 2 ? static_cast<const void*>(kcol + base + t * 4096) : static_cast<const void*>(vcol + base + (t - 2) * 2048);
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(16384) : "memory");
+    }
+  };
+  for (int d = 1; d <= B200_BIN_PF; ++d) prefetch_tile(begin + int64_t(d) * kBinTile);
+  // ONE load site per half-tile buffer: the loop starts one tile early with the work switched off, so that the
+  // first requests are issued by the same instructions as all later ones (a separate prologue request landed in
+  // other registers and cost a move of freshly loaded values, i.e. the whole memory latency, in every iteration)
   Raw32 ra, rb;
-  const int64_t mine = begin + int64_t(t) * kFastSub;
-  request(ra, mine);
-  request(rb, mine + kBinSubRows);
   uint32_t tile = 0;
 #pragma unroll 1
-  for (int64_t base = begin; base < end; base += kBinTile, ++tile) {
+  for (int64_t base = begin - kBinTile; base < end; base += kBinTile) {
+    const bool live = base >= begin;   // uniform
     const int64_t r0 = base + int64_t(t) * kFastSub;
+    prefetch_tile(base + int64_t(1 + B200_BIN_PF) * kBinTile);
     // the next request goes into the registers the work has just consumed (a copy of the half-tile kept
     // beside two outstanding requests did not fit 64 registers: 48 B of stack per thread, i.e. spills to L2
     // with 205 KB of the SM's memory taken by the bins).  Its lead is still the other half-tile's work, the
     // reduction and both barriers
-    work(ra, r0, tile & 0xFFFFu);
+    if (live) work(ra, r0, tile & 0xFFFFu);
     request(ra, r0 + 2 * kBinSubRows);
-    work(rb, r0 + kBinSubRows, tile & 0xFFFFu);
+    if (live) work(rb, r0 + kBinSubRows, tile & 0xFFFFu);
     request(rb, r0 + 3 * kBinSubRows);
+    if (!live) continue;
+    ++tile;
     __syncthreads();
     // ---- every thread reduces the bin of its own group with plain adds / compares
     {
@@ -3162,7 +3185,9 @@ int run_consume(b200_groupby* gb, GbArgs& a) {
     else B200_TIMED(ctx, "groupby_consume", (gb_fast_kernel<KM, VF, false><<<grid, kFastThreads, smem, ctx->stream>>>(a)));        \
   } while (0)
         static const bool pipelined = B200_KNOB("B200_GB_V2") == nullptr;
-        if (binned && pipelined && k32 && vfast && a.keys[0].nbits == 32) {
+        // (value validity at a bit offset that is a multiple of 4: the four bits of a thread's rows then never leave
+        // one 16-bit word, which is all gb_bin32_kernel keeps of them; other offsets take gb_bin_kernel)
+        if (binned && pipelined && k32 && vfast && a.keys[0].nbits == 32 && (a.cols[0].vv.bit_offset & 3) == 0) {
           B200_TIMED(ctx, "groupby_consume", (gb_bin32_kernel<<<grid, kBinThreads, smem, ctx->stream>>>(a)));
         } else if (k32) { if (vfast) B200_FAST_LAUNCH(1, true); else B200_FAST_LAUNCH(1, false); }
         else if (k64) { if (vfast) B200_FAST_LAUNCH(2, true); else B200_FAST_LAUNCH(2, false); }
